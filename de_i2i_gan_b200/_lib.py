@@ -1,0 +1,77 @@
+"""ctypes binding of libdei2i.so (the C ABI declared in include/dei2i.h).
+
+There is no fallback: if the shared object is missing (not built) the import of any compute path raises.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdei2i.so")
+
+
+class ConvGeom(C.Structure):
+    _fields_ = [(n, C.c_int) for n in
+                ("N", "H", "W", "Hs", "Ws", "Cin", "Cout", "Cout_ld", "kh", "kw", "stride", "pad", "pad_mode")]
+
+
+class ConvEpilogue(C.Structure):
+    _fields_ = [("bias", C.c_void_p), ("noise", C.c_void_p), ("noise_weight", C.c_void_p), ("residual", C.c_void_p),
+                ("act", C.c_int), ("out_fp32", C.c_int)]
+
+
+_P, _I, _F, _LL, _SZ = C.c_void_p, C.c_int, C.c_float, C.c_longlong, C.c_size_t
+
+# name -> (restype, argtypes); mirrors include/dei2i.h one to one
+SIGNATURES = {
+    "dei2i_version": (_I, []),
+    "dei2i_last_error": (C.c_char_p, []),
+    "dei2i_set_tuning": (_I, [C.c_char_p, _I]),
+    "dei2i_launch_count": (_LL, []),
+    "dei2i_pack_weight": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
+    "dei2i_conv2d_fwd": (_I, [_P, _P, _P, C.POINTER(ConvGeom), C.POINTER(ConvEpilogue), _P]),
+    "dei2i_conv2d_dgrad": (_I, [_P, _P, _P, C.POINTER(ConvGeom), _I, _P]),
+    "dei2i_reflect_fold": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_conv2d_wgrad_workspace": (_SZ, [C.POINTER(ConvGeom), _I]),
+    "dei2i_conv2d_wgrad": (_I, [_P, _P, _P, _I, _F, C.POINTER(ConvGeom), _P, _P, _P, _P, _P, _SZ, _P]),
+    "dei2i_spectral_norm": (_I, [_P, _P, _P, _I, _I, _I, _F, _P, _P, _P]),
+    "dei2i_nchw_to_nhwc": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_nhwc_to_nchw": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_channel_stats": (_I, [_P, _I, _I, _I, _I, _P, _P]),
+    "dei2i_bn_fwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _I, _P]),
+    "dei2i_bn_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_spade_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _F, _P]),
+    "dei2i_spade_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_act_bwd": (_I, [_P, _P, _P, _P, _LL, _I, _I, _P]),
+    "dei2i_noise_wgrad": (_I, [_P, _P, _P, _LL, _I, _I, _F, _P]),
+    "dei2i_compose_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "dei2i_compose_bwd": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
+    "dei2i_bce_logits": (_I, [_P, _P, _F, _LL, _P, _P, _F, _P]),
+    "dei2i_l1": (_I, [_P, _P, _LL, _P, _P, _P, _F, _I, _P]),
+    "dei2i_adam": (_I, [_P, _P, _P, _P, _LL, _F, _F, _F, _F, _I, _P]),
+}
+
+_lib = None
+
+
+def load():
+    """Loads libdei2i.so and declares every prototype. Raises if the library was not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(there is no CPU / PyTorch fallback for the CUDA path)")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the .so does not export a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        msg = load().dei2i_last_error().decode("utf-8", "replace")
+        raise RuntimeError(f"{what} failed (status {rc}): {msg}")

@@ -1,0 +1,94 @@
+// Library-wide plumbing of the C ABI: error reporting, tuning knobs, launch counter, TMA descriptor encoding.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <atomic>
+
+#include "common.cuh"
+#include "../../include/dei2i.h"
+
+namespace dei2i {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int check_cuda(cudaError_t e, const char* what) {
+  if (e == cudaSuccess) return 0;
+  set_error("CUDA error %d (%s) in %s", (int)e, cudaGetErrorString(e), what);
+  return DEI2I_ERR_CUDA;
+}
+
+int g_tune_conv_stages = 0;
+int g_tune_conv_bn = 0;
+int g_tune_wgrad_bn = 0;
+int g_tune_wgrad_waves = 0;
+static std::atomic<long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeTiledFn)p;
+  }
+  return fn;
+}
+
+int encode_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t row_pitch_bytes,
+                        uint32_t box_inner, uint32_t box_outer, int swizzle128) {
+  EncodeTiledFn fn = get_encode();
+  if (fn == nullptr) {
+    set_error("cuTensorMapEncodeTiled is not available (no CUDA driver / no sm_100 device)");
+    return DEI2I_ERR_CUDA;
+  }
+  if ((reinterpret_cast<uintptr_t>(base) & 15) != 0 || (row_pitch_bytes & 15) != 0) {
+    set_error("TMA operand must be 16-byte aligned (base %p, pitch %llu)", base, (unsigned long long)row_pitch_bytes);
+    return DEI2I_ERR_INVALID;
+  }
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {row_pitch_bytes};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed with CUresult %d (inner %llu outer %llu pitch %llu box %ux%u)", (int)r,
+              (unsigned long long)inner, (unsigned long long)outer, (unsigned long long)row_pitch_bytes, box_inner, box_outer);
+    return DEI2I_ERR_CUDA;
+  }
+  return 0;
+}
+
+}  // namespace dei2i
+
+extern "C" int dei2i_version(void) { return 100; }
+extern "C" const char* dei2i_last_error(void) { return dei2i::g_err; }
+extern "C" long long dei2i_launch_count(void) { return dei2i::g_launches.load(); }
+extern "C" int dei2i_set_tuning(const char* key, int value) {
+  int* slot = nullptr;
+  if (!strcmp(key, "conv_stages")) slot = &dei2i::g_tune_conv_stages;
+  else if (!strcmp(key, "conv_bn")) slot = &dei2i::g_tune_conv_bn;
+  else if (!strcmp(key, "wgrad_bn")) slot = &dei2i::g_tune_wgrad_bn;
+  else if (!strcmp(key, "wgrad_waves")) slot = &dei2i::g_tune_wgrad_waves;
+  if (slot == nullptr) return -1;
+  int old = *slot;
+  *slot = value;
+  return old;
+}

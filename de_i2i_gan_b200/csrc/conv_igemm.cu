@@ -1,0 +1,731 @@
+// Implicit-GEMM convolution kernels for sm_100a: tcgen05.mma (BF16 in, FP32 accumulate in TMEM).
+//
+//   forward / dgrad :  D[m, n] = sum_k A[m, k] * B[n, k]
+//        m = output pixel (n_img, oy, ox), n = output channel, k = (tap, input channel)
+//        A : gathered on the fly from the NHWC activation (im2col never materialised) by 4 producer warps with
+//            16-byte cp.async into the 128B-swizzled K-major UMMA layout (reflect / zero padding, stride,
+//            nearest resize and the transposed-conv index map of dgrad are all just address arithmetic);
+//        B : packed weight matrix [n, k], TMA 2D tiled loads (SWIZZLE_128B), one elected thread;
+//        MMA: one thread issues tcgen05.mma 128 x BLOCK_N x 16, accumulator = BLOCK_N TMEM columns;
+//        epilogue: the 4 producer warps read TMEM (tcgen05.ld 32x32b), fuse bias / noise / activation /
+//            residual and store NHWC rows.  Two CTAs are resident per SM (<= 100 KB smem, 2 x 256 TMEM
+//            columns), so one CTA's epilogue overlaps the other's main loop.
+//   wgrad :  dW[co, k] = sum_m dY[m, co] * A[m, k]   (reduction over pixels, split across CTAs)
+//        both operands are "MN-major" (the reduction index m is the slow one in memory): dY tiles come by TMA,
+//        im2col tiles by the same cp.async gather; FP32 partial tiles go to a workspace, a second pass sums the
+//        splits in a fixed order (deterministic) and applies the spectral-norm backward.
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "common.cuh"
+#include "../../include/dei2i.h"
+
+namespace dei2i {
+
+extern int g_tune_conv_stages;  // 0 = auto
+extern int g_tune_conv_bn;      // 0 = auto
+extern int g_tune_wgrad_bn;     // 0 = auto
+extern int g_tune_wgrad_waves;
+void count_launch(int n = 1);
+
+// ----------------------------------------------------------------------------------------------------------
+struct Gather {
+  const __nv_bfloat16* src;
+  int N, Hl, Wl, Hs, Ws, C;  // logical (Hl, Wl) nearest-mapped onto stored (Hs, Ws); C = channel pitch
+  int Ho, Wo;                // row domain: m -> (img, oy, ox)
+  int kh, kw, stride, pad, pad_mode;
+  int mode;                  // 0: forward (iy = oy*stride + r - pad), 1: dgrad (iy = (oy + off - r) / stride)
+  int off;
+  int cin8;                  // 16-byte chunks per tap along K (= K-channels / 8)
+  int ntaps;
+  long long M;               // N*Ho*Wo
+};
+
+DEVINL bool resolve_axis(const Gather& g, int o, int r, int Ll, int Ls, int& i_out) {
+  if (g.mode == 0) {
+    int i = o * g.stride + r - g.pad;
+    if (g.pad_mode == DEI2I_PAD_REFLECT) {
+      i = i < 0 ? -i : i;
+      i = i >= Ll ? 2 * Ll - 2 - i : i;
+    } else if (i < 0 || i >= Ll) {
+      return false;
+    }
+    if (Ls != Ll) i = (int)(((long long)i * Ls) / Ll);
+    i_out = i;
+    return true;
+  } else {
+    int t = o + g.off - r;
+    if (t < 0) return false;
+    int q = t / g.stride;
+    if (q * g.stride != t || q >= Ls) return false;
+    i_out = q;
+    return true;
+  }
+}
+
+// address of the 8-channel chunk c8 of tap (r, s) for row (img, oy, ox); nullptr => zero fill
+DEVINL const __nv_bfloat16* gather_ptr(const Gather& g, int img, int oy, int ox, int r, int s, int c8) {
+  int iy, ix;
+  if (!resolve_axis(g, oy, r, g.Hl, g.Hs, iy)) return nullptr;
+  if (!resolve_axis(g, ox, s, g.Wl, g.Ws, ix)) return nullptr;
+  return g.src + (((long long)img * g.Hs + iy) * g.Ws + ix) * g.C + c8 * 8;
+}
+
+struct Epilogue {
+  const float* bias;
+  const float* noise;
+  const float* noise_weight;
+  const __nv_bfloat16* residual;
+  void* out;
+  int act;
+  int out_fp32;
+  int ld;     // output pitch (elements)
+  int ncols;  // real columns that carry bias (Cout)
+};
+
+struct ConvKParams {
+  Gather g;
+  Epilogue e;
+  int num_kb;  // K / 64
+};
+
+constexpr int kProducerThreads = 128;
+constexpr int kThreads = 192;
+constexpr int kATileBytes = 128 * 128;  // 128 rows x 64 bf16
+
+template <int BLOCK_N, int STAGES>
+struct ConvSmem {
+  static constexpr int kBTileBytes = BLOCK_N * 128;
+  static constexpr int kStageBytes = kATileBytes + kBTileBytes;
+  static constexpr int kBarrierOff = STAGES * kStageBytes;
+  static constexpr int kTotal = kBarrierOff + (2 * STAGES + 1) * 8 + 16 + 1024 /*alignment slack*/;
+};
+
+template <int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(kThreads, (ConvSmem<BLOCK_N, STAGES>::kTotal <= 112 * 1024) ? 2 : 1)
+conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_b, const ConvKParams p) {
+  using S = ConvSmem<BLOCK_N, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kBarrierOff);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const long long m0 = (long long)blockIdx.x * 128;
+  const int n0 = blockIdx.y * BLOCK_N;
+  constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], kProducerThreads + 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 4 && lane == 0) tma_prefetch_desc(&tmap_b);
+  if (warp == 5) tmem_alloc(tmem_ptr_smem, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp < 4) {
+    // =========================== A producers (im2col gather) ===========================
+    const Gather& g = p.g;
+    const int tid = threadIdx.x;
+    const int j = tid & 7;    // 16-byte chunk inside the 128-byte K row
+    const int rb = tid >> 3;  // rows rb + 16*i
+    int r_img[8], r_oy[8], r_ox[8];
+    const int HoWo = g.Ho * g.Wo;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      long long m = m0 + rb + 16 * i;
+      if (m < g.M) {
+        int img = (int)(m / HoWo);
+        int rem = (int)(m - (long long)img * HoWo);
+        r_img[i] = img;
+        r_oy[i] = rem / g.Wo;
+        r_ox[i] = rem - r_oy[i] * g.Wo;
+      } else {
+        r_img[i] = -1;
+        r_oy[i] = 0;
+        r_ox[i] = 0;
+      }
+    }
+    const uint32_t a_row_off = (uint32_t)(rb * 128 + ((j ^ (rb & 7)) << 4));
+    for (int kb = 0; kb < p.num_kb; ++kb) {
+      const int stage = kb % STAGES;
+      const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+      mbar_wait(&empty_bar[stage], ph ^ 1u);
+      const int q8 = kb * 8 + j;
+      const int tap = q8 / g.cin8;
+      const int c8 = q8 - tap * g.cin8;
+      const bool tap_ok = tap < g.ntaps;
+      const int r = tap / g.kw;
+      const int s = tap - r * g.kw;
+      const uint32_t a_stage = smem_u32(smem + stage * S::kStageBytes) + a_row_off;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const __nv_bfloat16* src = nullptr;
+        if (tap_ok && r_img[i] >= 0) src = gather_ptr(g, r_img[i], r_oy[i], r_ox[i], r, s, c8);
+        cp_async_16(a_stage + i * (16 * 128), src ? (const void*)src : (const void*)g.src, src != nullptr);
+      }
+      cp_async_mbar_arrive_noinc(&full_bar[stage]);
+    }
+
+    // =========================== epilogue ===========================
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    const Epilogue& e = p.e;
+    const long long m = m0 + warp * 32 + lane;
+    const bool row_ok = m < g.M;
+    float nz = 0.f;
+    if (e.noise != nullptr && row_ok) nz = __ldg(e.noise + m) * __ldg(e.noise_weight);
+    constexpr int CH = BLOCK_N >= 32 ? 32 : 16;
+#pragma unroll 1
+    for (int c = 0; c < BLOCK_N; c += CH) {
+      uint32_t v[CH];
+      const uint32_t taddr = tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c;
+      if constexpr (CH == 32) tmem_ld_32x32b_x32(taddr, v);
+      else tmem_ld_32x32b_x16(taddr, v);
+      tc_wait_ld();
+      const int nbase = n0 + c;
+      if (row_ok && nbase < e.ld) {
+        float f[CH];
+#pragma unroll
+        for (int t = 0; t < CH; ++t) {
+          float x = __uint_as_float(v[t]);
+          const int n = nbase + t;
+          if (e.bias != nullptr && n < e.ncols) x += __ldg(e.bias + n);
+          x += nz;
+          f[t] = apply_act(x, e.act);
+        }
+        if (e.residual != nullptr) {
+          const __nv_bfloat16* rp = e.residual + m * e.ld + nbase;
+#pragma unroll
+          for (int t8 = 0; t8 < CH; t8 += 8) {
+            if (nbase + t8 < e.ld) {
+              uint4 rv = __ldg(reinterpret_cast<const uint4*>(rp + t8));
+              f[t8 + 0] += bf16lo(rv.x); f[t8 + 1] += bf16hi(rv.x);
+              f[t8 + 2] += bf16lo(rv.y); f[t8 + 3] += bf16hi(rv.y);
+              f[t8 + 4] += bf16lo(rv.z); f[t8 + 5] += bf16hi(rv.z);
+              f[t8 + 6] += bf16lo(rv.w); f[t8 + 7] += bf16hi(rv.w);
+            }
+          }
+        }
+        if (e.out_fp32) {
+          float* op = reinterpret_cast<float*>(e.out) + m * e.ld + nbase;
+#pragma unroll
+          for (int t4 = 0; t4 < CH; t4 += 4)
+            if (nbase + t4 < e.ld) *reinterpret_cast<float4*>(op + t4) = make_float4(f[t4], f[t4 + 1], f[t4 + 2], f[t4 + 3]);
+        } else {
+          __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(e.out) + m * e.ld + nbase;
+#pragma unroll
+          for (int t8 = 0; t8 < CH; t8 += 8)
+            if (nbase + t8 < e.ld)
+              *reinterpret_cast<uint4*>(op + t8) = make_uint4(pack_bf16(f[t8], f[t8 + 1]), pack_bf16(f[t8 + 2], f[t8 + 3]),
+                                                              pack_bf16(f[t8 + 4], f[t8 + 5]), pack_bf16(f[t8 + 6], f[t8 + 7]));
+        }
+      }
+    }
+  } else if (warp == 4) {
+    // =========================== B producer (TMA) ===========================
+    if (lane == 0) {
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        const int stage = kb % STAGES;
+        const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+        mbar_wait(&empty_bar[stage], ph ^ 1u);
+        mbar_arrive_expect_tx(&full_bar[stage], S::kBTileBytes);
+        tma_load_2d(smem + stage * S::kStageBytes + kATileBytes, &tmap_b, &full_bar[stage], kb * 64, n0);
+      }
+    }
+  } else {
+    // =========================== MMA issuer ===========================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, BLOCK_N, 0, 0);
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        const int stage = kb % STAGES;
+        const uint32_t ph = (uint32_t)(kb / STAGES) & 1u;
+        mbar_wait(&full_bar[stage], ph);
+        fence_proxy_async_smem();  // cp.async (generic proxy) data -> tensor-core (async proxy) reads
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + stage * S::kStageBytes);
+        const uint32_t b_addr = a_addr + kATileBytes;
+        const uint64_t a_desc = make_smem_desc(a_addr, 16, 1024, 2);
+        const uint64_t b_desc = make_smem_desc(b_addr, 16, 1024, 2);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)  // 4 x (K = 16): +32 bytes inside the 128-byte swizzle span
+          tc_mma_bf16(tmem_base, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+        tc_commit(&empty_bar[stage]);
+      }
+      tc_commit(tmem_full_bar);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------------
+// wgrad:  P[co, k] = sum_{m in split} dY[m, co] * A[m, k]       (M' = 128 co, N' = BLOCK_N k, K' = 64 pixels/step)
+struct WgradKParams {
+  Gather g;        // forward gather geometry of x
+  float* partial;  // [splits, Cout_rows, Kf] fp32
+  int cout_rows;   // rows stored per split (= Cout real)
+  int Kf;          // packed K (multiple of 64)
+  int pb_per_split;  // pixel blocks (64 pixels) per split
+  int num_pb;        // total pixel blocks
+};
+
+template <int BLOCK_N, int STAGES>
+struct WgradSmem {
+  static constexpr int kATileBytes = 2 * 8192;              // 64 pixels x 128 co
+  static constexpr int kBTileBytes = (BLOCK_N / 64) * 8192; // 64 pixels x BLOCK_N k
+  static constexpr int kStageBytes = kATileBytes + kBTileBytes;
+  static constexpr int kBarrierOff = STAGES * kStageBytes;
+  static constexpr int kTotal = kBarrierOff + (2 * STAGES + 1) * 8 + 16 + 1024;
+};
+
+template <int BLOCK_N, int STAGES>
+__global__ void __launch_bounds__(kThreads, (WgradSmem<BLOCK_N, STAGES>::kTotal <= 112 * 1024) ? 2 : 1)
+conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const WgradKParams p) {
+  using S = WgradSmem<BLOCK_N, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kBarrierOff);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int k0 = blockIdx.x * BLOCK_N;  // K offset (elements)
+  const int co0 = blockIdx.y * 128;
+  const int split = blockIdx.z;
+  const int pb0 = split * p.pb_per_split;
+  const int pb1 = min(p.num_pb, pb0 + p.pb_per_split);
+  const int nsteps = pb1 - pb0;
+  constexpr uint32_t kTmemCols = BLOCK_N < 32 ? 32 : BLOCK_N;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], kProducerThreads + 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 4 && lane == 0) tma_prefetch_desc(&tmap_dy);
+  if (warp == 5) tmem_alloc(tmem_ptr_smem, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp < 4) {
+    // ---------------- im2col producer: 64 pixels x BLOCK_N k-elements, MN-major 128B-swizzled atoms
+    const Gather& g = p.g;
+    const int tid = threadIdx.x;
+    const int cj = tid & 7;
+    const int pr = tid >> 3;  // pixels pr + 16*i
+    constexpr int NG = BLOCK_N / 64;
+    int t_r[NG], t_s[NG], t_c8[NG];
+    bool t_ok[NG];
+#pragma unroll
+    for (int gi = 0; gi < NG; ++gi) {
+      const int q8 = (k0 / 64 + gi) * 8 + cj;
+      const int tap = q8 / g.cin8;
+      t_c8[gi] = q8 - tap * g.cin8;
+      t_ok[gi] = tap < g.ntaps;
+      t_r[gi] = tap / g.kw;
+      t_s[gi] = tap - t_r[gi] * g.kw;
+    }
+    const int HoWo = g.Ho * g.Wo;
+    const uint32_t row_off = (uint32_t)((pr >> 3) * 1024 + (pr & 7) * 128 + ((cj ^ (pr & 7)) << 4));
+    for (int it = 0; it < nsteps; ++it) {
+      const int stage = it % STAGES;
+      const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
+      mbar_wait(&empty_bar[stage], ph ^ 1u);
+      const uint32_t b_stage = smem_u32(smem + stage * S::kStageBytes + S::kATileBytes) + row_off;
+      const long long mb = (long long)(pb0 + it) * 64;
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const long long m = mb + pr + 16 * i;
+        int img = -1, oy = 0, ox = 0;
+        if (m < g.M) {
+          img = (int)(m / HoWo);
+          int rem = (int)(m - (long long)img * HoWo);
+          oy = rem / g.Wo;
+          ox = rem - oy * g.Wo;
+        }
+#pragma unroll
+        for (int gi = 0; gi < NG; ++gi) {
+          const __nv_bfloat16* src = nullptr;
+          if (img >= 0 && t_ok[gi]) src = gather_ptr(g, img, oy, ox, t_r[gi], t_s[gi], t_c8[gi]);
+          cp_async_16(b_stage + gi * 8192 + i * 2048, src ? (const void*)src : (const void*)g.src, src != nullptr);
+        }
+      }
+      cp_async_mbar_arrive_noinc(&full_bar[stage]);
+    }
+    // ---------------- epilogue: fp32 partial tile -> workspace
+    mbar_wait(tmem_full_bar, 0);
+    tc_fence_after();
+    const int co = co0 + warp * 32 + lane;
+    float* orow = p.partial + ((long long)split * p.cout_rows + co) * p.Kf + k0;
+    constexpr int CH = 32;
+#pragma unroll 1
+    for (int c = 0; c < BLOCK_N; c += CH) {
+      uint32_t v[CH];
+      tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c, v);
+      tc_wait_ld();
+      if (co < p.cout_rows && k0 + c < p.Kf) {
+#pragma unroll
+        for (int t4 = 0; t4 < CH; t4 += 4)
+          *reinterpret_cast<float4*>(orow + c + t4) =
+              make_float4(__uint_as_float(v[t4]), __uint_as_float(v[t4 + 1]), __uint_as_float(v[t4 + 2]), __uint_as_float(v[t4 + 3]));
+      }
+    }
+  } else if (warp == 4) {
+    if (lane == 0) {
+      for (int it = 0; it < nsteps; ++it) {
+        const int stage = it % STAGES;
+        const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
+        mbar_wait(&empty_bar[stage], ph ^ 1u);
+        mbar_arrive_expect_tx(&full_bar[stage], S::kATileBytes);
+        uint8_t* a_dst = smem + stage * S::kStageBytes;
+        tma_load_2d(a_dst, &tmap_dy, &full_bar[stage], co0, (pb0 + it) * 64);
+        tma_load_2d(a_dst + 8192, &tmap_dy, &full_bar[stage], co0 + 64, (pb0 + it) * 64);
+      }
+    }
+  } else {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, BLOCK_N, 1, 1);
+      for (int it = 0; it < nsteps; ++it) {
+        const int stage = it % STAGES;
+        const uint32_t ph = (uint32_t)(it / STAGES) & 1u;
+        mbar_wait(&full_bar[stage], ph);
+        fence_proxy_async_smem();
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + stage * S::kStageBytes);
+        const uint32_t b_addr = a_addr + S::kATileBytes;
+        // MN-major, 128B swizzle: LBO = stride between 64-element MN atoms (8192 B), SBO = between 8-row K atoms (1024 B)
+        const uint64_t a_desc = make_smem_desc(a_addr, 8192, 1024, 2);
+        const uint64_t b_desc = make_smem_desc(b_addr, 8192, 1024, 2);
+#pragma unroll
+        for (int k = 0; k < 4; ++k)  // 16 pixels = 2 K atoms = 2048 B per MMA
+          tc_mma_bf16(tmem_base, a_desc + (uint64_t)(128 * k), b_desc + (uint64_t)(128 * k), idesc, (it | k) != 0);
+        tc_commit(&empty_bar[stage]);
+      }
+      tc_commit(tmem_full_bar);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// second pass: dw[co, ci, r, s] = beta*dw + scale * (sum_splits P[split, co, (r*kw+s)*Cin + ci] - corr * u[co] * v[col])
+__global__ void wgrad_reduce_kernel(const float* __restrict__ partial, int splits, int Cout, int Kf, int Cin, int Cin_real,
+                                    int taps, float* __restrict__ dw, float beta, const float* __restrict__ dot,
+                                    const float* __restrict__ u, const float* __restrict__ v,
+                                    const float* __restrict__ inv_sigma) {
+  const long long total = (long long)Cout * Cin_real * taps;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int cols = Cin_real * taps;
+  const int co = (int)(i / cols);
+  const int col = (int)(i - (long long)co * cols);  // ci*taps + tap  (weight memory order [co][ci][r][s])
+  const int ci = col / taps;
+  const int tap = col - ci * taps;
+  const long long off = (long long)co * Kf + tap * Cin + ci;
+  float acc = 0.f;
+  for (int s = 0; s < splits; ++s) acc += partial[(long long)s * Cout * Kf + off];
+  if (u != nullptr) acc = (acc - dot[0] * u[co] * v[col]) * inv_sigma[0];
+  dw[i] = beta != 0.f ? beta * dw[i] + acc : acc;
+}
+
+// <dW, W/sigma> over the real elements (spectral-norm backward); deterministic: one block, fixed order
+__global__ void wgrad_dot_kernel(const float* __restrict__ partial, int splits, int Cout, int Kf, int Cin, int Cin_real,
+                                 int taps, const float* __restrict__ w_orig, const float* __restrict__ inv_sigma,
+                                 float* __restrict__ blocksums) {
+  const long long total = (long long)Cout * Cin_real * taps;
+  const int cols = Cin_real * taps;
+  float acc = 0.f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int co = (int)(i / cols);
+    const int col = (int)(i - (long long)co * cols);
+    const int ci = col / taps;
+    const int tap = col - ci * taps;
+    const long long off = (long long)co * Kf + tap * Cin + ci;
+    float g = 0.f;
+    for (int s = 0; s < splits; ++s) g += partial[(long long)s * Cout * Kf + off];
+    acc += g * w_orig[i];
+  }
+  __shared__ float sh[32];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.f;
+    t = warp_sum(t);
+    if (threadIdx.x == 0) blocksums[blockIdx.x] = t * inv_sigma[0];
+  }
+}
+__global__ void sum_blocks_kernel(const float* __restrict__ in, int n, float* __restrict__ out) {
+  float acc = 0.f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) acc += in[i];
+  __shared__ float sh[32];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float t = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.f;
+    t = warp_sum(t);
+    if (threadIdx.x == 0) out[0] = t;
+  }
+}
+
+// small-Cout wgrad (heads, discriminator classifiers: Cout_ld < 64): CUDA cores, fp32 atomics on a [Cout, Kf] buffer
+__global__ void wgrad_small_kernel(const Gather g, const __nv_bfloat16* __restrict__ dy, int Cout, int Cout_ld, int Kf,
+                                   float* __restrict__ acc /*[Cout, Kf] zeroed*/, int pix_per_block) {
+  // each block: a range of pixels; thread t handles K elements t, t+blockDim, ...; accumulates over the pixel range
+  const long long m_begin = (long long)blockIdx.x * pix_per_block;
+  const long long m_end = min(g.M, m_begin + pix_per_block);
+  const int HoWo = g.Ho * g.Wo;
+  const int Kreal = g.ntaps * g.cin8 * 8;
+  for (int k = threadIdx.x; k < Kreal; k += blockDim.x) {
+    const int tap = k / (g.cin8 * 8);
+    const int ci = k - tap * g.cin8 * 8;
+    const int r = tap / g.kw, s = tap - r * g.kw;
+    float a[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) a[c] = 0.f;
+    for (long long m = m_begin; m < m_end; ++m) {
+      int img = (int)(m / HoWo);
+      int rem = (int)(m - (long long)img * HoWo);
+      int oy = rem / g.Wo, ox = rem - oy * g.Wo;
+      const __nv_bfloat16* sp = gather_ptr(g, img, oy, ox, r, s, ci >> 3);
+      if (sp == nullptr) continue;
+      const float xv = __bfloat162float(sp[ci & 7]);
+      const __nv_bfloat16* dyr = dy + m * Cout_ld;
+#pragma unroll
+      for (int c = 0; c < 8; ++c)
+        if (c < Cout) a[c] += xv * __bfloat162float(dyr[c]);
+    }
+    for (int c = 0; c < 8 && c < Cout; ++c) atomicAdd(acc + (long long)c * Kf + k, a[c]);
+  }
+}
+
+// ----------------------------------------------------------------------------------------------------------
+// host side
+static int conv_out_dim(int L, int k, int stride, int pad) { return (L + 2 * pad - k) / stride + 1; }
+static int round_up(int a, int b) { return (a + b - 1) / b * b; }
+
+template <int BN, int ST>
+static int launch_conv(const CUtensorMap& tm, const ConvKParams& p, int n_tiles, cudaStream_t st) {
+  using S = ConvSmem<BN, ST>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    DEI2I_CUDA(cudaFuncSetAttribute(conv_igemm_kernel<BN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+    attr_done = true;
+  }
+  long long m_tiles = (p.g.M + 127) / 128;
+  DEI2I_REQUIRE(m_tiles < (1ll << 31), "conv: too many M tiles");
+  dim3 grid((unsigned)m_tiles, (unsigned)n_tiles, 1);
+  conv_igemm_kernel<BN, ST><<<grid, kThreads, S::kTotal, st>>>(tm, p);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "conv_igemm_kernel launch");
+}
+
+static int run_igemm(const ConvKParams& p, const void* wmat, int rows, int K, cudaStream_t st) {
+  // choose the N tile: largest of {256,128,64,32,16} that does not exceed round_up(rows,16)
+  int bn = 256;
+  int want = round_up(rows, 16);
+  while (bn > 16 && bn / 2 >= want) bn /= 2;
+  if (g_tune_conv_bn > 0 && g_tune_conv_bn <= bn) bn = g_tune_conv_bn;
+  CUtensorMap tm;
+  int rc = encode_tmap_2d_bf16(&tm, wmat, (uint64_t)K, (uint64_t)rows, (uint64_t)K * 2, 64, (uint32_t)bn, 1);
+  if (rc) return rc;
+  const int n_tiles = (rows + bn - 1) / bn;
+  const int deep = g_tune_conv_stages;  // 0: two CTAs per SM; 1: one CTA per SM with a deep pipeline
+  switch (bn) {
+    case 256: return deep ? launch_conv<256, 4>(tm, p, n_tiles, st) : launch_conv<256, 2>(tm, p, n_tiles, st);
+    case 128: return deep ? launch_conv<128, 6>(tm, p, n_tiles, st) : launch_conv<128, 3>(tm, p, n_tiles, st);
+    case 64: return launch_conv<64, 4>(tm, p, n_tiles, st);
+    case 32: return launch_conv<32, 4>(tm, p, n_tiles, st);
+    default: return launch_conv<16, 4>(tm, p, n_tiles, st);
+  }
+}
+
+static int check_geom(const dei2i_conv_geom* g) {
+  DEI2I_REQUIRE(g != nullptr, "conv: null geometry");
+  DEI2I_REQUIRE(g->N > 0 && g->H > 0 && g->W > 0 && g->Hs > 0 && g->Ws > 0, "conv: bad sizes");
+  DEI2I_REQUIRE(g->Cin > 0 && g->Cin % 8 == 0, "conv: Cin (%d) must be a positive multiple of 8", g->Cin);
+  DEI2I_REQUIRE(g->Cout > 0 && g->Cout_ld % 8 == 0 && g->Cout_ld >= g->Cout, "conv: bad Cout/Cout_ld (%d/%d)", g->Cout, g->Cout_ld);
+  DEI2I_REQUIRE(g->kh > 0 && g->kw > 0 && g->stride > 0 && g->pad >= 0, "conv: bad kernel geometry");
+  DEI2I_REQUIRE(g->pad_mode == DEI2I_PAD_ZEROS || g->pad_mode == DEI2I_PAD_REFLECT, "conv: bad pad_mode");
+  if (g->pad_mode == DEI2I_PAD_REFLECT)
+    DEI2I_REQUIRE(g->pad < g->H && g->pad < g->W, "conv: reflect padding (%d) must be smaller than the input (%dx%d)", g->pad, g->H, g->W);
+  DEI2I_REQUIRE(conv_out_dim(g->H, g->kh, g->stride, g->pad) > 0 && conv_out_dim(g->W, g->kw, g->stride, g->pad) > 0,
+                "conv: empty output");
+  return 0;
+}
+
+}  // namespace dei2i
+
+using namespace dei2i;
+
+extern "C" int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const dei2i_conv_geom* g,
+                                const dei2i_conv_epilogue* e, dei2i_stream stream) {
+  if (int rc = check_geom(g)) return rc;
+  DEI2I_REQUIRE(x && w_fwd && y && e, "conv2d_fwd: null pointer");
+  DEI2I_REQUIRE(e->noise == nullptr || e->noise_weight != nullptr, "conv2d_fwd: noise without noise_weight");
+  ConvKParams p;
+  memset(&p, 0, sizeof(p));
+  const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
+  p.g.src = (const __nv_bfloat16*)x;
+  p.g.N = g->N; p.g.Hl = g->H; p.g.Wl = g->W; p.g.Hs = g->Hs; p.g.Ws = g->Ws; p.g.C = g->Cin;
+  p.g.Ho = Ho; p.g.Wo = Wo; p.g.kh = g->kh; p.g.kw = g->kw; p.g.stride = g->stride; p.g.pad = g->pad;
+  p.g.pad_mode = g->pad_mode; p.g.mode = 0; p.g.off = 0; p.g.cin8 = g->Cin / 8; p.g.ntaps = g->kh * g->kw;
+  p.g.M = (long long)g->N * Ho * Wo;
+  const int K = round_up(g->kh * g->kw * g->Cin, 64);
+  p.num_kb = K / 64;
+  p.e.bias = e->bias; p.e.noise = e->noise; p.e.noise_weight = e->noise_weight;
+  p.e.residual = (const __nv_bfloat16*)e->residual; p.e.out = y; p.e.act = e->act; p.e.out_fp32 = e->out_fp32;
+  p.e.ld = g->Cout_ld; p.e.ncols = g->Cout;
+  return run_igemm(p, w_fwd, g->Cout, K, (cudaStream_t)stream);
+}
+
+extern "C" int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx, const dei2i_conv_geom* g, int out_fp32,
+                                  dei2i_stream stream) {
+  if (int rc = check_geom(g)) return rc;
+  DEI2I_REQUIRE(dy && w_dgrad && dx, "conv2d_dgrad: null pointer");
+  DEI2I_REQUIRE(g->Hs == g->H && g->Ws == g->W, "conv2d_dgrad: resized inputs are not supported");
+  ConvKParams p;
+  memset(&p, 0, sizeof(p));
+  const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
+  const bool full = g->pad_mode == DEI2I_PAD_REFLECT;
+  const int Hd = full ? g->H + 2 * g->pad : g->H, Wd = full ? g->W + 2 * g->pad : g->W;
+  p.g.src = (const __nv_bfloat16*)dy;
+  p.g.N = g->N; p.g.Hl = Ho; p.g.Wl = Wo; p.g.Hs = Ho; p.g.Ws = Wo; p.g.C = g->Cout_ld;
+  p.g.Ho = Hd; p.g.Wo = Wd; p.g.kh = g->kh; p.g.kw = g->kw; p.g.stride = g->stride; p.g.pad = g->pad;
+  p.g.pad_mode = g->pad_mode; p.g.mode = 1; p.g.off = full ? 0 : g->pad; p.g.cin8 = g->Cout_ld / 8;
+  p.g.ntaps = g->kh * g->kw;
+  p.g.M = (long long)g->N * Hd * Wd;
+  const int K = round_up(g->kh * g->kw * g->Cout_ld, 64);
+  p.num_kb = K / 64;
+  p.e.out = dx; p.e.act = 0; p.e.out_fp32 = out_fp32; p.e.ld = g->Cin; p.e.ncols = g->Cin;
+  return run_igemm(p, w_dgrad, g->Cin, K, (cudaStream_t)stream);
+}
+
+static void wgrad_plan(const dei2i_conv_geom* g, int& bn, int& splits, int& pb_per_split, int& num_pb, int& Kf) {
+  const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
+  const long long M = (long long)g->N * Ho * Wo;
+  Kf = round_up(g->kh * g->kw * g->Cin, 64);
+  bn = 256;
+  while (bn > 64 && (Kf % bn) != 0) bn /= 2;
+  if (g_tune_wgrad_bn > 0 && Kf % g_tune_wgrad_bn == 0) bn = g_tune_wgrad_bn;
+  num_pb = (int)((M + 63) / 64);
+  const int tiles = (Kf / bn) * ((g->Cout + 127) / 128);
+  const int target = 148 * 2 * (g_tune_wgrad_waves > 0 ? g_tune_wgrad_waves : 1);
+  splits = (target + tiles - 1) / tiles;
+  if (splits > num_pb) splits = num_pb;
+  if (splits < 1) splits = 1;
+  // keep at least 8 pixel blocks per split so the prologue/epilogue amortise
+  while (splits > 1 && num_pb / splits < 8) --splits;
+  pb_per_split = (num_pb + splits - 1) / splits;
+  splits = (num_pb + pb_per_split - 1) / pb_per_split;
+}
+
+extern "C" size_t dei2i_conv2d_wgrad_workspace(const dei2i_conv_geom* g, int Cin_real) {
+  (void)Cin_real;
+  if (g == nullptr || check_geom(g)) return 0;
+  int bn, splits, pbs, npb, Kf;
+  wgrad_plan(g, bn, splits, pbs, npb, Kf);
+  if (g->Cout_ld < 64) splits = 1;
+  return (size_t)splits * g->Cout * Kf * sizeof(float) + 1024 * sizeof(float) + 256;
+}
+
+template <int BN, int ST>
+static int launch_wgrad(const CUtensorMap& tm, const WgradKParams& p, dim3 grid, cudaStream_t st) {
+  using S = WgradSmem<BN, ST>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    DEI2I_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel<BN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+    attr_done = true;
+  }
+  conv_wgrad_kernel<BN, ST><<<grid, kThreads, S::kTotal, st>>>(tm, p);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "conv_wgrad_kernel launch");
+}
+
+extern "C" int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int Cin_real, float beta,
+                                  const dei2i_conv_geom* g, const float* sn_w_orig, const float* sn_u, const float* sn_v,
+                                  const float* sn_inv_sigma, void* workspace, size_t workspace_bytes, dei2i_stream stream) {
+  if (int rc = check_geom(g)) return rc;
+  DEI2I_REQUIRE(x && dy && dw && workspace, "conv2d_wgrad: null pointer");
+  DEI2I_REQUIRE(Cin_real > 0 && Cin_real <= g->Cin, "conv2d_wgrad: bad Cin_real");
+  DEI2I_REQUIRE(workspace_bytes >= dei2i_conv2d_wgrad_workspace(g, Cin_real), "conv2d_wgrad: workspace too small");
+  DEI2I_REQUIRE((sn_u == nullptr) == (sn_v == nullptr) && (sn_u == nullptr) == (sn_inv_sigma == nullptr) &&
+                    (sn_u == nullptr) == (sn_w_orig == nullptr),
+                "conv2d_wgrad: spectral-norm pointers must be all set or all NULL");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
+  int bn, splits, pbs, npb, Kf;
+  wgrad_plan(g, bn, splits, pbs, npb, Kf);
+  WgradKParams p;
+  memset(&p, 0, sizeof(p));
+  p.g.src = (const __nv_bfloat16*)x;
+  p.g.N = g->N; p.g.Hl = g->H; p.g.Wl = g->W; p.g.Hs = g->Hs; p.g.Ws = g->Ws; p.g.C = g->Cin;
+  p.g.Ho = Ho; p.g.Wo = Wo; p.g.kh = g->kh; p.g.kw = g->kw; p.g.stride = g->stride; p.g.pad = g->pad;
+  p.g.pad_mode = g->pad_mode; p.g.mode = 0; p.g.off = 0; p.g.cin8 = g->Cin / 8; p.g.ntaps = g->kh * g->kw;
+  p.g.M = (long long)g->N * Ho * Wo;
+  float* partial = (float*)workspace;
+  const int taps = g->kh * g->kw;
+  if (g->Cout_ld < 64) {
+    DEI2I_REQUIRE(g->Cout <= 8, "conv2d_wgrad: Cout_ld < 64 requires Cout <= 8 (got %d)", g->Cout);
+    splits = 1;
+    DEI2I_CUDA(cudaMemsetAsync(partial, 0, (size_t)g->Cout * Kf * sizeof(float), st));
+    const int ppb = 256;
+    long long blocks = (p.g.M + ppb - 1) / ppb;
+    wgrad_small_kernel<<<(unsigned)blocks, 256, 0, st>>>(p.g, (const __nv_bfloat16*)dy, g->Cout, g->Cout_ld, Kf, partial, ppb);
+    count_launch();
+    DEI2I_CUDA(cudaGetLastError());
+  } else {
+    p.partial = partial; p.cout_rows = g->Cout; p.Kf = Kf; p.pb_per_split = pbs; p.num_pb = npb;
+    CUtensorMap tm;
+    int rc = encode_tmap_2d_bf16(&tm, dy, (uint64_t)g->Cout_ld, (uint64_t)p.g.M, (uint64_t)g->Cout_ld * 2, 64, 64, 1);
+    if (rc) return rc;
+    dim3 grid(Kf / bn, (g->Cout + 127) / 128, splits);
+    switch (bn) {
+      case 256: rc = launch_wgrad<256, 2>(tm, p, grid, st); break;
+      case 128: rc = launch_wgrad<128, 3>(tm, p, grid, st); break;
+      default: rc = launch_wgrad<64, 4>(tm, p, grid, st); break;
+    }
+    if (rc) return rc;
+  }
+  float* dot = partial + (size_t)splits * g->Cout * Kf;  // [0] = <dW, W/sigma>, [1..] block sums
+  const long long total = (long long)g->Cout * Cin_real * taps;
+  if (sn_u != nullptr) {
+    const int nb = 512;
+    wgrad_dot_kernel<<<nb, 256, 0, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, sn_w_orig, sn_inv_sigma, dot + 1);
+    sum_blocks_kernel<<<1, 256, 0, st>>>(dot + 1, nb, dot);
+    count_launch(2);
+    DEI2I_CUDA(cudaGetLastError());
+  }
+  wgrad_reduce_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, dw,
+                                                                        beta, dot, sn_u, sn_v, sn_inv_sigma);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "wgrad_reduce_kernel launch");
+}

@@ -1,0 +1,902 @@
+// HBM-streaming kernels of the DefectGAN hot path: everything that is not a dense contraction.
+// All of them are bandwidth bound: 16-byte (8 x bf16) accesses, channel-contiguous (NHWC) so that a warp
+// touches whole 128-byte lines, warp-shuffle + shared-memory reductions for the per-channel statistics.
+#include <string.h>
+
+#include "common.cuh"
+#include "../../include/dei2i.h"
+
+namespace dei2i {
+void count_launch(int n = 1);
+
+static inline unsigned nblocks(long long n, int per) {
+  long long b = (n + per - 1) / per;
+  return (unsigned)(b < 1 ? 1 : b);
+}
+
+DEVINL void unpack8(const uint4& v, float (&f)[8]) {
+  f[0] = bf16lo(v.x); f[1] = bf16hi(v.x); f[2] = bf16lo(v.y); f[3] = bf16hi(v.y);
+  f[4] = bf16lo(v.z); f[5] = bf16hi(v.z); f[6] = bf16lo(v.w); f[7] = bf16hi(v.w);
+}
+DEVINL uint4 pack8(const float (&f)[8]) {
+  return make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+}
+DEVINL float block_sum(float v, float* sh /*>=32 floats*/) {
+  v = warp_sum(v);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  __syncthreads();
+  if (l == 0) sh[w] = v;
+  __syncthreads();
+  float t = (threadIdx.x < (blockDim.x >> 5)) ? sh[threadIdx.x] : 0.f;
+  if (w == 0) t = warp_sum(t);
+  if (threadIdx.x == 0) sh[0] = t;
+  __syncthreads();
+  return sh[0];
+}
+
+// ------------------------------------------------------------------------------------------ weight packing
+__global__ void pack_fwd_kernel(const float* __restrict__ w, const float* __restrict__ inv_sigma, int Cout, int Cin_real,
+                                int taps, int Cin, int Kf, __nv_bfloat16* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)Cout * Kf) return;
+  const int co = (int)(i / Kf), k = (int)(i - (long long)co * Kf);
+  const int tap = k / Cin, ci = k - tap * Cin;
+  float v = 0.f;
+  if (tap < taps && ci < Cin_real) {
+    v = w[((long long)co * Cin_real + ci) * taps + tap];
+    if (inv_sigma) v *= inv_sigma[0];
+  }
+  out[i] = __float2bfloat16(v);
+}
+__global__ void pack_dgrad_kernel(const float* __restrict__ w, const float* __restrict__ inv_sigma, int Cout, int Cin_real,
+                                  int taps, int Cin, int Cout_ld, int Kd, __nv_bfloat16* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)Cin * Kd) return;
+  const int ci = (int)(i / Kd), k = (int)(i - (long long)ci * Kd);
+  const int tap = k / Cout_ld, co = k - tap * Cout_ld;
+  float v = 0.f;
+  if (tap < taps && co < Cout && ci < Cin_real) {
+    v = w[((long long)co * Cin_real + ci) * taps + tap];
+    if (inv_sigma) v *= inv_sigma[0];
+  }
+  out[i] = __float2bfloat16(v);
+}
+
+// ------------------------------------------------------------------------------------------ reflect-pad backward
+__global__ void reflect_fold_kernel(const uint4* __restrict__ dxp, uint4* __restrict__ dx, int N, int H, int W, int C8, int pad) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long total = (long long)N * H * W * C8;
+  if (i >= total) return;
+  const int c8 = (int)(i % C8);
+  long long t = i / C8;
+  const int w = (int)(t % W);
+  t /= W;
+  const int h = (int)(t % H);
+  const int n = (int)(t / H);
+  const int Hp = H + 2 * pad, Wp = W + 2 * pad;
+  int hs[3], ws[3], nh = 0, nw = 0;
+  hs[nh++] = h + pad;
+  if (h >= 1 && h <= pad) hs[nh++] = pad - h;
+  if (h >= H - 1 - pad && h <= H - 2) hs[nh++] = pad + 2 * H - 2 - h;
+  ws[nw++] = w + pad;
+  if (w >= 1 && w <= pad) ws[nw++] = pad - w;
+  if (w >= W - 1 - pad && w <= W - 2) ws[nw++] = pad + 2 * W - 2 - w;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int a = 0; a < nh; ++a)
+    for (int b = 0; b < nw; ++b) {
+      float f[8];
+      unpack8(__ldg(dxp + (((long long)n * Hp + hs[a]) * Wp + ws[b]) * C8 + c8), f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) acc[k] += f[k];
+    }
+  dx[i] = pack8(acc);
+}
+
+// ------------------------------------------------------------------------------------------ spectral norm
+// t_partial[rs, col] = sum_{row in chunk rs} W[row, col] * u[row]
+__global__ void sn_wt_u_kernel(const float* __restrict__ w, const float* __restrict__ u, int rows, int cols, int rows_per,
+                               float* __restrict__ partial) {
+  const int col = blockIdx.x * blockDim.x + threadIdx.x;
+  if (col >= cols) return;
+  const int r0 = blockIdx.y * rows_per, r1 = min(rows, r0 + rows_per);
+  float acc = 0.f;
+#pragma unroll 4
+  for (int r = r0; r < r1; ++r) acc += __ldg(w + (long long)r * cols + col) * __ldg(u + r);
+  partial[(long long)blockIdx.y * cols + col] = acc;
+}
+// v = normalize(sum_rs partial)   (single block)
+__global__ void sn_finish_v_kernel(const float* __restrict__ partial, int rs, int cols, float eps, float* __restrict__ v) {
+  __shared__ float sh[32];
+  float ss = 0.f;
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) {
+    float t = 0.f;
+    for (int r = 0; r < rs; ++r) t += partial[(long long)r * cols + c];
+    v[c] = t;
+    ss += t * t;
+  }
+  const float nrm = sqrtf(block_sum(ss, sh));
+  const float inv = 1.f / fmaxf(nrm, eps);
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) v[c] *= inv;
+}
+// s[row] = sum_col W[row, col] * v[col]    (one warp per row)
+__global__ void sn_w_v_kernel(const float* __restrict__ w, const float* __restrict__ v, int rows, int cols, float* __restrict__ s) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int lane = threadIdx.x & 31;
+  const float* wr = w + (long long)row * cols;
+  float acc = 0.f;
+  for (int c = lane; c < cols; c += 32) acc += __ldg(wr + c) * __ldg(v + c);
+  acc = warp_sum(acc);
+  if (lane == 0) s[row] = acc;
+}
+// power-iter: u = normalize(s), sigma = u.s ; eval: sigma = u_old.s     (single block)
+__global__ void sn_finish_u_kernel(const float* __restrict__ s, int rows, float eps, int do_iter, float* __restrict__ u,
+                                   float* __restrict__ inv_sigma) {
+  __shared__ float sh[32];
+  float acc = 0.f;
+  if (do_iter) {
+    for (int r = threadIdx.x; r < rows; r += blockDim.x) acc += s[r] * s[r];
+    const float ss = block_sum(acc, sh);
+    const float inv = 1.f / fmaxf(sqrtf(ss), eps);
+    for (int r = threadIdx.x; r < rows; r += blockDim.x) u[r] = s[r] * inv;
+    if (threadIdx.x == 0) {
+      const float sigma = ss * inv;
+      inv_sigma[0] = 1.f / sigma;
+      inv_sigma[1] = sigma;
+    }
+  } else {
+    for (int r = threadIdx.x; r < rows; r += blockDim.x) acc += s[r] * u[r];
+    const float sigma = block_sum(acc, sh);
+    if (threadIdx.x == 0) {
+      inv_sigma[0] = 1.f / sigma;
+      inv_sigma[1] = sigma;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------ layout at the model edge
+__global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int N, int C, int HW, int C_ld) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // pixel index n*HW + p
+  if (i >= (long long)N * HW) return;
+  const int n = (int)(i / HW);
+  const int p = (int)(i - (long long)n * HW);
+  for (int c0 = 0; c0 < C_ld; c0 += 8) {
+    float f[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] = (c0 + k < C) ? __ldg(src + ((long long)n * C + c0 + k) * HW + p) : 0.f;
+    *reinterpret_cast<uint4*>(dst + i * C_ld + c0) = pack8(f);
+  }
+}
+__global__ void nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, int N, int C, int HW, int C_ld) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)N * C * HW) return;
+  const int p = (int)(i % HW);
+  const long long t = i / HW;
+  const int c = (int)(t % C);
+  const int n = (int)(t / C);
+  dst[i] = __bfloat162float(src[((long long)n * HW + p) * C_ld + c]);
+}
+
+// ------------------------------------------------------------------------------------------ channel statistics
+// grid (chunks, groups). block 256 threads = (C8 columns) x (256/C8 pixel lanes), needs C8 <= 256.
+__global__ void channel_stats_kernel(const uint4* __restrict__ x, long long pix_per_group, int C8, int chunk,
+                                     float* __restrict__ stats /*[groups,2,C]*/) {
+  extern __shared__ float sh[];  // [lanes][C8*8][2]
+  const int c8 = threadIdx.x % C8;
+  const int lane = threadIdx.x / C8;
+  const int lanes = blockDim.x / C8;
+  const long long g = blockIdx.y;
+  const long long p0 = (long long)blockIdx.x * chunk;
+  const long long p1 = min(pix_per_group, p0 + chunk);
+  float s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (lane < lanes) {
+    const uint4* base = x + g * pix_per_group * C8 + c8;
+    for (long long p = p0 + lane; p < p1; p += lanes) {
+      float f[8];
+      unpack8(__ldg(base + p * C8), f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        s[k] += f[k];
+        q[k] += f[k] * f[k];
+      }
+    }
+  }
+  const int C = C8 * 8;
+  if (lane < lanes) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      sh[(lane * C + c8 * 8 + k) * 2 + 0] = s[k];
+      sh[(lane * C + c8 * 8 + k) * 2 + 1] = q[k];
+    }
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = 0.f, b = 0.f;
+    for (int l = 0; l < lanes; ++l) {
+      a += sh[(l * C + c) * 2 + 0];
+      b += sh[(l * C + c) * 2 + 1];
+    }
+    atomicAdd(stats + (g * 2 + 0) * C + c, a);
+    atomicAdd(stats + (g * 2 + 1) * C + c, b);
+  }
+}
+
+static int launch_channel_reduce_cfg(int C, long long pix_per_group, int groups, int& threads, int& chunk, unsigned& chunks,
+                                     size_t& shmem) {
+  const int C8 = C / 8;
+  DEI2I_REQUIRE(C % 8 == 0 && C8 >= 1 && C8 <= 256, "channel reduce: C (%d) must be a multiple of 8, <= 2048", C);
+  int lanes = 256 / C8;
+  if (lanes < 1) lanes = 1;
+  threads = lanes * C8;
+  // aim for ~4 waves of blocks over the chip
+  long long want_blocks = (148 * 8 + groups - 1) / groups;
+  long long c = (pix_per_group + want_blocks - 1) / want_blocks;
+  if (c < lanes * 4) c = lanes * 4;
+  chunk = (int)c;
+  chunks = (unsigned)((pix_per_group + chunk - 1) / chunk);
+  shmem = (size_t)lanes * C * 2 * sizeof(float);
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------ batch norm
+struct BnCoef {
+  float mean, rstd;
+};
+// every block derives (scale, shift) per channel into smem; block 0 also updates running stats / saves mean,rstd
+__global__ void bn_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, const uint4* __restrict__ residual,
+                              const float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
+                              float* __restrict__ running_mean, float* __restrict__ running_var, float* __restrict__ save_mean,
+                              float* __restrict__ save_rstd, long long npix, int C8, int training, float momentum, float eps,
+                              int act) {
+  extern __shared__ float sh[];  // scale[C], shift[C]
+  const int C = C8 * 8;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float mean, var;
+    if (training) {
+      mean = stats[c] / (float)npix;
+      var = fmaxf(stats[C + c] / (float)npix - mean * mean, 0.f);
+      if (blockIdx.x == 0) {
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+        const float unb = npix > 1 ? var * (float)npix / (float)(npix - 1) : var;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * unb;
+      }
+    } else {
+      mean = running_mean[c];
+      var = running_var[c];
+    }
+    const float rstd = rsqrtf(var + eps);
+    if (blockIdx.x == 0 && save_mean != nullptr) {
+      save_mean[c] = mean;
+      save_rstd[c] = rstd;
+    }
+    const float sc = rstd * gamma[c];
+    sh[c] = sc;
+    sh[C + c] = beta[c] - mean * sc;
+  }
+  __syncthreads();
+  const long long total = npix * C8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % C8) * 8;
+    float f[8];
+    unpack8(__ldg(x + i), f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] = apply_act(f[k] * sh[c0 + k] + sh[C + c0 + k], act);
+    if (residual != nullptr) {
+      float r[8];
+      unpack8(__ldg(residual + i), r);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] += r[k];
+    }
+    y[i] = pack8(f);
+  }
+}
+
+// pass 1 of the backward: per channel  sum(dz), sum(dz * xhat)   with dz = dy * act'(bn(x))
+__global__ void bn_bwd_reduce_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, const float* __restrict__ gamma,
+                                     const float* __restrict__ beta, const float* __restrict__ mean, const float* __restrict__ rstd,
+                                     long long npix, int C8, int chunk, int act, float* __restrict__ out /*[2,C]*/) {
+  extern __shared__ float sh[];
+  const int c8 = threadIdx.x % C8;
+  const int lane = threadIdx.x / C8;
+  const int lanes = blockDim.x / C8;
+  const int C = C8 * 8;
+  const long long p0 = (long long)blockIdx.x * chunk;
+  const long long p1 = min(npix, p0 + chunk);
+  float s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  float mu[8], rs[8], ga[8], be[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    mu[k] = mean[c8 * 8 + k];
+    rs[k] = rstd[c8 * 8 + k];
+    ga[k] = gamma[c8 * 8 + k];
+    be[k] = beta[c8 * 8 + k];
+  }
+  for (long long p = p0 + lane; p < p1; p += lanes) {
+    float fx[8], fd[8];
+    unpack8(__ldg(x + p * C8 + c8), fx);
+    unpack8(__ldg(dy + p * C8 + c8), fd);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float xh = (fx[k] - mu[k]) * rs[k];
+      float dz = fd[k];
+      if (act == ACT_LRELU) dz *= (xh * ga[k] + be[k]) > 0.f ? 1.f : 0.2f;
+      else if (act == ACT_RELU) dz *= (xh * ga[k] + be[k]) > 0.f ? 1.f : 0.f;
+      s[k] += dz;
+      q[k] += dz * xh;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    sh[(lane * C + c8 * 8 + k) * 2 + 0] = s[k];
+    sh[(lane * C + c8 * 8 + k) * 2 + 1] = q[k];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = 0.f, b = 0.f;
+    for (int l = 0; l < lanes; ++l) {
+      a += sh[(l * C + c) * 2 + 0];
+      b += sh[(l * C + c) * 2 + 1];
+    }
+    atomicAdd(out + c, a);
+    atomicAdd(out + C + c, b);
+  }
+}
+__global__ void bn_bwd_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, uint4* __restrict__ dx,
+                                    const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
+                                    const float* __restrict__ rstd, const float* __restrict__ red /*[2,C]*/, float* __restrict__ dgamma,
+                                    float* __restrict__ dbeta, long long npix, int C8, int training, int act) {
+  extern __shared__ float sh[];  // mean, rstd, gamma, beta, k1 (=sum dz / n), k2 (= sum dz xhat / n)
+  const int C = C8 * 8;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    sh[c] = mean[c];
+    sh[C + c] = rstd[c];
+    sh[2 * C + c] = gamma[c];
+    sh[3 * C + c] = beta[c];
+    sh[4 * C + c] = training ? red[c] / (float)npix : 0.f;
+    sh[5 * C + c] = training ? red[C + c] / (float)npix : 0.f;
+    if (blockIdx.x == 0) {
+      dbeta[c] = red[c];
+      dgamma[c] = red[C + c];
+    }
+  }
+  __syncthreads();
+  const long long total = npix * C8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % C8) * 8;
+    float fx[8], fd[8], o[8];
+    unpack8(__ldg(x + i), fx);
+    unpack8(__ldg(dy + i), fd);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = c0 + k;
+      const float xh = (fx[k] - sh[c]) * sh[C + c];
+      float dz = fd[k];
+      const float z = xh * sh[2 * C + c] + sh[3 * C + c];
+      if (act == ACT_LRELU) dz *= z > 0.f ? 1.f : 0.2f;
+      else if (act == ACT_RELU) dz *= z > 0.f ? 1.f : 0.f;
+      o[k] = sh[2 * C + c] * sh[C + c] * (dz - sh[4 * C + c] - xh * sh[5 * C + c]);
+    }
+    dx[i] = pack8(o);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ SPADE
+__global__ void spade_fwd_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb, uint4* __restrict__ out,
+                                 const float* __restrict__ stats, float* __restrict__ mean_rstd, int N, int H, int W, int C8, int up,
+                                 float eps) {
+  // grid.y = image; every block of an image derives that image's mean / rstd into smem
+  extern __shared__ float sh[];  // mean[C], rstd[C]
+  const int C = C8 * 8;
+  const int n = blockIdx.y;
+  const int Hx = H / up, Wx = W / up;
+  const float cnt = (float)Hx * (float)Wx;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float mean = stats[(n * 2 + 0) * C + c] / cnt;
+    const float var = fmaxf(stats[(n * 2 + 1) * C + c] / cnt - mean * mean, 0.f);
+    const float rstd = rsqrtf(var + eps);
+    sh[c] = mean;
+    sh[C + c] = rstd;
+    if (blockIdx.x == 0) {
+      mean_rstd[(n * 2 + 0) * C + c] = mean;
+      mean_rstd[(n * 2 + 1) * C + c] = rstd;
+    }
+  }
+  __syncthreads();
+  const long long per_img = (long long)H * W * C8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img; i += (long long)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % C8);
+    const long long pix = i / C8;
+    const int w = (int)(pix % W), h = (int)(pix / W);
+    float fx[8], fg[8], fb[8], o[8];
+    unpack8(__ldg(x + (((long long)n * Hx + h / up) * Wx + w / up) * C8 + c8), fx);
+    const long long gbase = ((long long)n * H * W + pix) * (2 * C8);
+    unpack8(__ldg(gb + gbase + c8), fg);
+    unpack8(__ldg(gb + gbase + C8 + c8), fb);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float xh = (fx[k] - sh[c8 * 8 + k]) * sh[C + c8 * 8 + k];
+      o[k] = fmaxf(xh * (1.f + fg[k]) + fb[k], 0.f);
+    }
+    out[(long long)n * per_img + i] = pack8(o);
+  }
+}
+
+// backward pass 1: dgb = [g * xhat | g],  g = dout * (out > 0);  accumulates S1 = sum dxhat, S2 = sum dxhat*xhat per (n,c)
+// grid (chunks, N); block = C8 columns x lanes
+__global__ void spade_bwd1_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb, const uint4* __restrict__ out,
+                                  const uint4* __restrict__ dout, uint4* __restrict__ dgb, const float* __restrict__ mean_rstd,
+                                  float* __restrict__ red /*[N,2,C]*/, int H, int W, int C8, int up, int chunk) {
+  extern __shared__ float sh[];
+  const int c8 = threadIdx.x % C8;
+  const int lane = threadIdx.x / C8;
+  const int lanes = blockDim.x / C8;
+  const int C = C8 * 8;
+  const int n = blockIdx.y;
+  const int Hx = H / up, Wx = W / up;
+  const long long npix = (long long)H * W;
+  const long long p0 = (long long)blockIdx.x * chunk, p1 = min(npix, p0 + chunk);
+  float mu[8], rs[8], s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    mu[k] = mean_rstd[(n * 2 + 0) * C + c8 * 8 + k];
+    rs[k] = mean_rstd[(n * 2 + 1) * C + c8 * 8 + k];
+  }
+  for (long long p = p0 + lane; p < p1; p += lanes) {
+    const int w = (int)(p % W), h = (int)(p / W);
+    float fx[8], fg[8], fo[8], fd[8], dg[8], db[8];
+    unpack8(__ldg(x + (((long long)n * Hx + h / up) * Wx + w / up) * C8 + c8), fx);
+    const long long gbase = ((long long)n * npix + p) * (2 * C8);
+    unpack8(__ldg(gb + gbase + c8), fg);
+    unpack8(__ldg(out + ((long long)n * npix + p) * C8 + c8), fo);
+    unpack8(__ldg(dout + ((long long)n * npix + p) * C8 + c8), fd);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float xh = (fx[k] - mu[k]) * rs[k];
+      const float g = fo[k] > 0.f ? fd[k] : 0.f;
+      dg[k] = g * xh;
+      db[k] = g;
+      const float dxh = g * (1.f + fg[k]);
+      s[k] += dxh;
+      q[k] += dxh * xh;
+    }
+    dgb[gbase + c8] = pack8(dg);
+    dgb[gbase + C8 + c8] = pack8(db);
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    sh[(lane * C + c8 * 8 + k) * 2 + 0] = s[k];
+    sh[(lane * C + c8 * 8 + k) * 2 + 1] = q[k];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = 0.f, b = 0.f;
+    for (int l = 0; l < lanes; ++l) {
+      a += sh[(l * C + c) * 2 + 0];
+      b += sh[(l * C + c) * 2 + 1];
+    }
+    atomicAdd(red + (n * 2 + 0) * C + c, a);
+    atomicAdd(red + (n * 2 + 1) * C + c, b);
+  }
+}
+// backward pass 2: dx[n, hx, wx, c] = rstd * (sum_{up x up} dxhat - up^2 * (S1/HW) - xhat * up^2 * (S2/HW))
+__global__ void spade_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb, const uint4* __restrict__ dgb,
+                                  uint4* __restrict__ dx, const float* __restrict__ mean_rstd, const float* __restrict__ red, int H,
+                                  int W, int C8, int up) {
+  extern __shared__ float sh[];  // mean, rstd, k1, k2
+  const int C = C8 * 8;
+  const int n = blockIdx.y;
+  const int Hx = H / up, Wx = W / up;
+  const float cnt = (float)H * (float)W;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    sh[c] = mean_rstd[(n * 2 + 0) * C + c];
+    sh[C + c] = mean_rstd[(n * 2 + 1) * C + c];
+    sh[2 * C + c] = red[(n * 2 + 0) * C + c] / cnt;
+    sh[3 * C + c] = red[(n * 2 + 1) * C + c] / cnt;
+  }
+  __syncthreads();
+  const long long per_img = (long long)Hx * Wx * C8;
+  const float uu = (float)(up * up);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img; i += (long long)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % C8);
+    const long long pix = i / C8;
+    const int wx = (int)(pix % Wx), hx = (int)(pix / Wx);
+    float fx[8], acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, o[8];
+    unpack8(__ldg(x + (long long)n * per_img + i), fx);
+    for (int dy = 0; dy < up; ++dy)
+      for (int dxx = 0; dxx < up; ++dxx) {
+        const long long p = (long long)(hx * up + dy) * W + (wx * up + dxx);
+        const long long gbase = ((long long)n * H * W + p) * (2 * C8);
+        float fg[8], g[8];
+        unpack8(__ldg(gb + gbase + c8), fg);
+        unpack8(__ldg(dgb + gbase + C8 + c8), g);  // beta half of dgb holds g = dout * mask
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] += g[k] * (1.f + fg[k]);
+      }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = c8 * 8 + k;
+      const float xh = (fx[k] - sh[c]) * sh[C + c];
+      o[k] = sh[C + c] * (acc[k] - uu * sh[2 * C + c] - xh * uu * sh[3 * C + c]);
+    }
+    dx[(long long)n * per_img + i] = pack8(o);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ activation backward (+ column sums)
+__global__ void act_bwd_kernel(const uint4* __restrict__ y, const uint4* __restrict__ dy, uint4* __restrict__ dx, float* __restrict__ colsum,
+                               long long M, int C8, int chunk, int act) {
+  extern __shared__ float sh[];
+  const int c8 = threadIdx.x % C8;
+  const int lane = threadIdx.x / C8;
+  const int lanes = blockDim.x / C8;
+  const int C = C8 * 8;
+  const long long p0 = (long long)blockIdx.x * chunk, p1 = min(M, p0 + chunk);
+  float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (long long p = p0 + lane; p < p1; p += lanes) {
+    float fd[8];
+    unpack8(__ldg(dy + p * C8 + c8), fd);
+    if (act != ACT_NONE) {
+      float fy[8];
+      unpack8(__ldg(y + p * C8 + c8), fy);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float d;
+        switch (act) {
+          case ACT_LRELU: d = fy[k] > 0.f ? 1.f : 0.2f; break;
+          case ACT_RELU: d = fy[k] > 0.f ? 1.f : 0.f; break;
+          case ACT_TANH: d = 1.f - fy[k] * fy[k]; break;
+          default: d = fy[k] * (1.f - fy[k]); break;
+        }
+        fd[k] *= d;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) s[k] += fd[k];
+    if (dx != nullptr) dx[p * C8 + c8] = pack8(fd);
+  }
+  if (colsum == nullptr) return;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) sh[lane * C + c8 * 8 + k] = s[k];
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = 0.f;
+    for (int l = 0; l < lanes; ++l) a += sh[l * C + c];
+    atomicAdd(colsum + c, a);
+  }
+}
+
+// ------------------------------------------------------------------------------------------ noise weight gradient
+__global__ void noise_wgrad_kernel(const uint4* __restrict__ dy, const float* __restrict__ noise, long long M, int C8, int C_real,
+                                   float* __restrict__ out) {
+  __shared__ float sh[32];
+  float acc = 0.f;
+  const long long total = M * C8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % C8) * 8;
+    const long long m = i / C8;
+    float f[8];
+    unpack8(__ldg(dy + i), f);
+    float t = 0.f;
+#pragma unroll
+    for (int k = 0; k < 8; ++k)
+      if (c0 + k < C_real) t += f[k];
+    acc += t * __ldg(noise + m);
+  }
+  const float tot = block_sum(acc, sh);
+  if (threadIdx.x == 0) atomicAdd(out, tot);
+}
+__global__ void scale_scalar_kernel(float* p, float beta) { p[0] *= beta; }
+
+// ------------------------------------------------------------------------------------------ heads + composition
+__global__ void compose_fwd_kernel(const float* __restrict__ hd, const float* __restrict__ x, float* __restrict__ out,
+                                   float* __restrict__ prob, __nv_bfloat16* __restrict__ out_nhwc, int N, int HW, int cycle_gan) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)N * HW) return;
+  const int n = (int)(i / HW);
+  const int p = (int)(i - (long long)n * HW);
+  const float4 a = __ldg(reinterpret_cast<const float4*>(hd + i * 8));
+  const float pr = 1.f / (1.f + __expf(-a.w));
+  const float fg[3] = {tanhf(a.x), tanhf(a.y), tanhf(a.z)};
+  float o[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const long long idx = ((long long)n * 3 + c) * HW + p;
+    const float v = cycle_gan ? fg[c] : __ldg(x + idx) * (1.f - pr) + fg[c] * pr;
+    out[idx] = v;
+    o[c] = v;
+  }
+  prob[i] = pr;
+  if (out_nhwc != nullptr) *reinterpret_cast<uint4*>(out_nhwc + i * 8) = pack8(o);
+}
+__global__ void compose_bwd_kernel(const float* __restrict__ hd, const float* __restrict__ x, const float* __restrict__ dout,
+                                   const float* __restrict__ dprob, __nv_bfloat16* __restrict__ dhd, float* __restrict__ dx, int N,
+                                   int HW, int cycle_gan) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (long long)N * HW) return;
+  const int n = (int)(i / HW);
+  const int p = (int)(i - (long long)n * HW);
+  const float4 a = __ldg(reinterpret_cast<const float4*>(hd + i * 8));
+  const float pr = 1.f / (1.f + __expf(-a.w));
+  const float fg[3] = {tanhf(a.x), tanhf(a.y), tanhf(a.z)};
+  float o[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  float dp = dprob != nullptr ? __ldg(dprob + i) : 0.f;
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    const long long idx = ((long long)n * 3 + c) * HW + p;
+    const float go = dout != nullptr ? __ldg(dout + idx) : 0.f;
+    if (cycle_gan) {
+      o[c] = go * (1.f - fg[c] * fg[c]);
+      if (dx != nullptr) dx[idx] = 0.f;
+    } else {
+      const float xv = __ldg(x + idx);
+      o[c] = go * pr * (1.f - fg[c] * fg[c]);
+      dp += go * (fg[c] - xv);
+      if (dx != nullptr) dx[idx] = go * (1.f - pr);
+    }
+  }
+  o[3] = dp * pr * (1.f - pr);
+  *reinterpret_cast<uint4*>(dhd + i * 8) = pack8(o);
+}
+
+// ------------------------------------------------------------------------------------------ losses
+__global__ void bce_logits_kernel(const float* __restrict__ z, const float* __restrict__ t, float tc, long long n, float* __restrict__ loss,
+                                  float* __restrict__ grad, float gscale) {
+  __shared__ float sh[32];
+  float acc = 0.f;
+  const float invn = 1.f / (float)n;
+  for (long long i = threadIdx.x; i < n; i += blockDim.x) {
+    const float zi = z[i], ti = t ? t[i] : tc;
+    acc += fmaxf(zi, 0.f) - zi * ti + log1pf(__expf(-fabsf(zi)));
+    if (grad) grad[i] = (1.f / (1.f + __expf(-zi)) - ti) * invn * gscale;
+  }
+  const float tot = block_sum(acc, sh);
+  if (threadIdx.x == 0) loss[0] = tot * invn;
+}
+__global__ void l1_kernel(const float* __restrict__ a, const float* __restrict__ b, long long n, float* __restrict__ loss,
+                          float* __restrict__ ga, float* __restrict__ gb, float gscale, int accumulate) {
+  __shared__ float sh[32];
+  float acc = 0.f;
+  const float invn = 1.f / (float)n;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float d = a[i] - (b ? b[i] : 0.f);
+    acc += fabsf(d);
+    const float s = (d > 0.f ? 1.f : (d < 0.f ? -1.f : 0.f)) * invn * gscale;
+    if (ga) ga[i] = accumulate ? ga[i] + s : s;
+    if (gb) gb[i] = accumulate ? gb[i] - s : -s;
+  }
+  const float tot = block_sum(acc, sh);
+  if (threadIdx.x == 0) atomicAdd(loss, tot * invn);
+}
+
+// ------------------------------------------------------------------------------------------ Adam
+__global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n,
+                            float step_size, float beta1, float beta2, float eps, float inv_sqrt_bc2) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gi = g[i];
+    const float mi = beta1 * m[i] + (1.f - beta1) * gi;
+    const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] -= step_size * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
+  }
+}
+
+}  // namespace dei2i
+
+using namespace dei2i;
+#define ST ((cudaStream_t)stream)
+#define LAUNCH_OK(name) (count_launch(), check_cuda(cudaGetLastError(), name))
+
+extern "C" int dei2i_pack_weight(const float* w, const float* inv_sigma, int Cout, int Cin_real, int kh, int kw, int Cin,
+                                 int Cout_ld, void* w_fwd, void* w_dgrad, dei2i_stream stream) {
+  DEI2I_REQUIRE(w && w_fwd, "pack_weight: null pointer");
+  DEI2I_REQUIRE(Cin % 8 == 0 && Cin >= Cin_real && Cout_ld % 8 == 0 && Cout_ld >= Cout, "pack_weight: bad channel padding");
+  const int taps = kh * kw;
+  const int Kf = (taps * Cin + 63) / 64 * 64;
+  pack_fwd_kernel<<<nblocks((long long)Cout * Kf, 256), 256, 0, ST>>>(w, inv_sigma, Cout, Cin_real, taps, Cin, Kf,
+                                                                      (__nv_bfloat16*)w_fwd);
+  if (int rc = LAUNCH_OK("pack_fwd_kernel")) return rc;
+  if (w_dgrad != nullptr) {
+    const int Kd = (taps * Cout_ld + 63) / 64 * 64;
+    pack_dgrad_kernel<<<nblocks((long long)Cin * Kd, 256), 256, 0, ST>>>(w, inv_sigma, Cout, Cin_real, taps, Cin, Cout_ld, Kd,
+                                                                         (__nv_bfloat16*)w_dgrad);
+    return LAUNCH_OK("pack_dgrad_kernel");
+  }
+  return 0;
+}
+
+extern "C" int dei2i_reflect_fold(const void* dxp, void* dx, int N, int H, int W, int C, int pad, dei2i_stream stream) {
+  DEI2I_REQUIRE(dxp && dx && C % 8 == 0 && pad >= 0 && pad < H && pad < W, "reflect_fold: bad arguments");
+  const long long total = (long long)N * H * W * (C / 8);
+  reflect_fold_kernel<<<nblocks(total, 256), 256, 0, ST>>>((const uint4*)dxp, (uint4*)dx, N, H, W, C / 8, pad);
+  return LAUNCH_OK("reflect_fold_kernel");
+}
+
+extern "C" int dei2i_spectral_norm(const float* w, float* u, float* v, int rows, int cols, int do_power_iter, float eps,
+                                   float* inv_sigma, float* scratch, dei2i_stream stream) {
+  DEI2I_REQUIRE(w && u && v && inv_sigma && scratch && rows > 0 && cols > 0, "spectral_norm: bad arguments");
+  // scratch: s[rows] followed by partial[RS, cols]; RS chosen so that RS*cols <= the documented budget is the caller's job:
+  // dei2i requires scratch of rows + 17*cols floats.
+  float* s = scratch;
+  float* partial = scratch + rows;
+  if (do_power_iter) {
+    int rs = (rows + 127) / 128;
+    if (rs > 16) rs = 16;
+    const int rows_per = (rows + rs - 1) / rs;
+    rs = (rows + rows_per - 1) / rows_per;
+    dim3 grid((cols + 255) / 256, rs);
+    sn_wt_u_kernel<<<grid, 256, 0, ST>>>(w, u, rows, cols, rows_per, partial);
+    if (int rc = LAUNCH_OK("sn_wt_u_kernel")) return rc;
+    sn_finish_v_kernel<<<1, 1024, 0, ST>>>(partial, rs, cols, eps, v);
+    if (int rc = LAUNCH_OK("sn_finish_v_kernel")) return rc;
+  }
+  sn_w_v_kernel<<<(rows + 7) / 8, 256, 0, ST>>>(w, v, rows, cols, s);
+  if (int rc = LAUNCH_OK("sn_w_v_kernel")) return rc;
+  sn_finish_u_kernel<<<1, 1024, 0, ST>>>(s, rows, eps, do_power_iter, u, inv_sigma);
+  return LAUNCH_OK("sn_finish_u_kernel");
+}
+
+extern "C" int dei2i_nchw_to_nhwc(const float* src, void* dst, int N, int C, int H, int W, int C_ld, dei2i_stream stream) {
+  DEI2I_REQUIRE(src && dst && C_ld % 8 == 0 && C_ld >= C, "nchw_to_nhwc: bad arguments");
+  nchw_to_nhwc_kernel<<<nblocks((long long)N * H * W, 256), 256, 0, ST>>>(src, (__nv_bfloat16*)dst, N, C, H * W, C_ld);
+  return LAUNCH_OK("nchw_to_nhwc_kernel");
+}
+extern "C" int dei2i_nhwc_to_nchw(const void* src, float* dst, int N, int C, int H, int W, int C_ld, dei2i_stream stream) {
+  DEI2I_REQUIRE(src && dst && C_ld >= C, "nhwc_to_nchw: bad arguments");
+  nhwc_to_nchw_kernel<<<nblocks((long long)N * C * H * W, 256), 256, 0, ST>>>((const __nv_bfloat16*)src, dst, N, C, H * W, C_ld);
+  return LAUNCH_OK("nhwc_to_nchw_kernel");
+}
+
+extern "C" int dei2i_channel_stats(const void* x, int N, int HW, int C, int per_sample, float* stats, dei2i_stream stream) {
+  DEI2I_REQUIRE(x && stats, "channel_stats: null pointer");
+  const int groups = per_sample ? N : 1;
+  const long long ppg = per_sample ? (long long)HW : (long long)N * HW;
+  int threads, chunk;
+  unsigned chunks;
+  size_t shmem;
+  if (int rc = launch_channel_reduce_cfg(C, ppg, groups, threads, chunk, chunks, shmem)) return rc;
+  DEI2I_CUDA(cudaMemsetAsync(stats, 0, (size_t)groups * 2 * C * sizeof(float), ST));
+  if (shmem > 48 * 1024)
+    DEI2I_CUDA(cudaFuncSetAttribute(channel_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
+  channel_stats_kernel<<<dim3(chunks, groups), threads, shmem, ST>>>((const uint4*)x, ppg, C / 8, chunk, stats);
+  return LAUNCH_OK("channel_stats_kernel");
+}
+
+extern "C" int dei2i_bn_fwd(const void* x, void* y, const void* residual, const float* stats, const float* gamma, const float* beta,
+                            float* running_mean, float* running_var, float* save_mean, float* save_rstd, int N, int HW, int C,
+                            int training, float momentum, float eps, int act, dei2i_stream stream) {
+  DEI2I_REQUIRE(x && y && gamma && beta && running_mean && running_var && C % 8 == 0, "bn_fwd: bad arguments");
+  DEI2I_REQUIRE(!training || stats, "bn_fwd: training mode needs batch statistics");
+  const long long npix = (long long)N * HW;
+  const long long total = npix * (C / 8);
+  unsigned blocks = nblocks(total, 256 * 4);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  bn_fwd_kernel<<<blocks, 256, 2 * C * sizeof(float), ST>>>((const uint4*)x, (uint4*)y, (const uint4*)residual, stats, gamma, beta,
+                                                            running_mean, running_var, save_mean, save_rstd, npix, C / 8, training,
+                                                            momentum, eps, act);
+  return LAUNCH_OK("bn_fwd_kernel");
+}
+
+extern "C" int dei2i_bn_bwd(const void* x, const void* dy, void* dx, const float* gamma, const float* beta, const float* save_mean,
+                            const float* save_rstd, float* dgamma, float* dbeta, float* scratch, int N, int HW, int C, int training,
+                            int act, dei2i_stream stream) {
+  DEI2I_REQUIRE(x && dy && dx && gamma && beta && save_mean && save_rstd && dgamma && dbeta && scratch && C % 8 == 0,
+                "bn_bwd: bad arguments");
+  const long long npix = (long long)N * HW;
+  int threads, chunk;
+  unsigned chunks;
+  size_t shmem;
+  if (int rc = launch_channel_reduce_cfg(C, npix, 1, threads, chunk, chunks, shmem)) return rc;
+  DEI2I_CUDA(cudaMemsetAsync(scratch, 0, (size_t)2 * C * sizeof(float), ST));
+  if (shmem > 48 * 1024)
+    DEI2I_CUDA(cudaFuncSetAttribute(bn_bwd_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
+  bn_bwd_reduce_kernel<<<chunks, threads, shmem, ST>>>((const uint4*)x, (const uint4*)dy, gamma, beta, save_mean, save_rstd, npix,
+                                                       C / 8, chunk, act, scratch);
+  if (int rc = LAUNCH_OK("bn_bwd_reduce_kernel")) return rc;
+  const long long total = npix * (C / 8);
+  unsigned blocks = nblocks(total, 256 * 4);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  bn_bwd_apply_kernel<<<blocks, 256, 6 * C * sizeof(float), ST>>>((const uint4*)x, (const uint4*)dy, (uint4*)dx, gamma, beta,
+                                                                  save_mean, save_rstd, scratch, dgamma, dbeta, npix, C / 8, training,
+                                                                  act);
+  return LAUNCH_OK("bn_bwd_apply_kernel");
+}
+
+extern "C" int dei2i_spade_fwd(const void* x, const void* gb, void* out, const float* stats, float* mean_rstd, int N, int H, int W,
+                               int C, int up, float eps, dei2i_stream stream) {
+  DEI2I_REQUIRE(x && gb && out && stats && mean_rstd && C % 8 == 0 && up >= 1 && H % up == 0 && W % up == 0, "spade_fwd: bad arguments");
+  const long long per_img = (long long)H * W * (C / 8);
+  unsigned bx = nblocks(per_img, 256 * 2);
+  const unsigned cap = (148 * 16 + N - 1) / N;
+  if (bx > cap) bx = cap;
+  spade_fwd_kernel<<<dim3(bx, N), 256, 2 * C * sizeof(float), ST>>>((const uint4*)x, (const uint4*)gb, (uint4*)out, stats, mean_rstd,
+                                                                    N, H, W, C / 8, up, eps);
+  return LAUNCH_OK("spade_fwd_kernel");
+}
+
+extern "C" int dei2i_spade_bwd(const void* x, const void* gb, const void* out, const void* dout, void* dgb, void* dx,
+                               const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, dei2i_stream stream) {
+  DEI2I_REQUIRE(x && gb && out && dout && dgb && dx && mean_rstd && scratch && C % 8 == 0 && up >= 1, "spade_bwd: bad arguments");
+  int threads, chunk;
+  unsigned chunks;
+  size_t shmem;
+  if (int rc = launch_channel_reduce_cfg(C, (long long)H * W, N, threads, chunk, chunks, shmem)) return rc;
+  DEI2I_CUDA(cudaMemsetAsync(scratch, 0, (size_t)N * 2 * C * sizeof(float), ST));
+  if (shmem > 48 * 1024)
+    DEI2I_CUDA(cudaFuncSetAttribute(spade_bwd1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
+  spade_bwd1_kernel<<<dim3(chunks, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)gb, (const uint4*)out, (const uint4*)dout,
+                                                             (uint4*)dgb, mean_rstd, scratch, H, W, C / 8, up, chunk);
+  if (int rc = LAUNCH_OK("spade_bwd1_kernel")) return rc;
+  const long long per_img = (long long)(H / up) * (W / up) * (C / 8);
+  unsigned bx = nblocks(per_img, 256 * 2);
+  const unsigned cap = (148 * 16 + N - 1) / N;
+  if (bx > cap) bx = cap;
+  spade_bwd2_kernel<<<dim3(bx, N), 256, 4 * C * sizeof(float), ST>>>((const uint4*)x, (const uint4*)gb, (const uint4*)dgb, (uint4*)dx,
+                                                                     mean_rstd, scratch, H, W, C / 8, up);
+  return LAUNCH_OK("spade_bwd2_kernel");
+}
+
+extern "C" int dei2i_act_bwd(const void* y, const void* dy, void* dx, float* bias_grad, long long M, int C, int act,
+                             dei2i_stream stream) {
+  DEI2I_REQUIRE(dy && (y || act == DEI2I_ACT_NONE) && (dx || bias_grad), "act_bwd: bad arguments");
+  int threads, chunk;
+  unsigned chunks;
+  size_t shmem;
+  if (int rc = launch_channel_reduce_cfg(C, M, 1, threads, chunk, chunks, shmem)) return rc;
+  shmem /= 2;
+  if (bias_grad) DEI2I_CUDA(cudaMemsetAsync(bias_grad, 0, (size_t)C * sizeof(float), ST));
+  if (shmem > 48 * 1024)
+    DEI2I_CUDA(cudaFuncSetAttribute(act_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
+  act_bwd_kernel<<<chunks, threads, shmem, ST>>>((const uint4*)y, (const uint4*)dy, (uint4*)dx, bias_grad, M, C / 8, chunk, act);
+  return LAUNCH_OK("act_bwd_kernel");
+}
+
+extern "C" int dei2i_noise_wgrad(const void* dy, const float* noise, float* dw, long long M, int C, int C_real, float beta,
+                                 dei2i_stream stream) {
+  DEI2I_REQUIRE(dy && noise && dw && C % 8 == 0, "noise_wgrad: bad arguments");
+  if (beta == 0.f) DEI2I_CUDA(cudaMemsetAsync(dw, 0, sizeof(float), ST));
+  else if (beta != 1.f) { scale_scalar_kernel<<<1, 1, 0, ST>>>(dw, beta); count_launch(); }
+  unsigned blocks = nblocks(M * (C / 8), 256 * 8);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  noise_wgrad_kernel<<<blocks, 256, 0, ST>>>((const uint4*)dy, noise, M, C / 8, C_real, dw);
+  return LAUNCH_OK("noise_wgrad_kernel");
+}
+
+extern "C" int dei2i_compose_fwd(const float* hd, const float* x, float* out, float* prob, void* out_nhwc, int N, int H, int W,
+                                 int cycle_gan, dei2i_stream stream) {
+  DEI2I_REQUIRE(hd && x && out && prob, "compose_fwd: null pointer");
+  compose_fwd_kernel<<<nblocks((long long)N * H * W, 256), 256, 0, ST>>>(hd, x, out, prob, (__nv_bfloat16*)out_nhwc, N, H * W, cycle_gan);
+  return LAUNCH_OK("compose_fwd_kernel");
+}
+extern "C" int dei2i_compose_bwd(const float* hd, const float* x, const float* dout, const float* dprob, void* dhd, float* dx, int N,
+                                 int H, int W, int cycle_gan, dei2i_stream stream) {
+  DEI2I_REQUIRE(hd && x && dhd, "compose_bwd: null pointer");
+  compose_bwd_kernel<<<nblocks((long long)N * H * W, 256), 256, 0, ST>>>(hd, x, dout, dprob, (__nv_bfloat16*)dhd, dx, N, H * W, cycle_gan);
+  return LAUNCH_OK("compose_bwd_kernel");
+}
+
+extern "C" int dei2i_bce_logits(const float* logits, const float* targets, float target_const, long long n, float* loss, float* grad,
+                                float grad_scale, dei2i_stream stream) {
+  DEI2I_REQUIRE(logits && loss && n > 0, "bce_logits: bad arguments");
+  bce_logits_kernel<<<1, 1024, 0, ST>>>(logits, targets, target_const, n, loss, grad, grad_scale);
+  return LAUNCH_OK("bce_logits_kernel");
+}
+extern "C" int dei2i_l1(const float* a, const float* b, long long n, float* loss, float* grad_a, float* grad_b, float grad_scale,
+                        int accumulate_grad, dei2i_stream stream) {
+  DEI2I_REQUIRE(a && loss && n > 0, "l1: bad arguments");
+  DEI2I_CUDA(cudaMemsetAsync(loss, 0, sizeof(float), ST));
+  unsigned blocks = nblocks(n, 256 * 8);
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  l1_kernel<<<blocks, 256, 0, ST>>>(a, b, n, loss, grad_a, grad_b, grad_scale, accumulate_grad);
+  return LAUNCH_OK("l1_kernel");
+}
+
+extern "C" int dei2i_adam(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2, float eps,
+                          int step, dei2i_stream stream) {
+  DEI2I_REQUIRE(p && g && m && v && n > 0 && step >= 1, "adam: bad arguments");
+  const double bc1 = 1.0 - pow((double)beta1, step), bc2 = 1.0 - pow((double)beta2, step);
+  unsigned blocks = nblocks(n, 256 * 4);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  adam_kernel<<<blocks, 256, 0, ST>>>(p, g, m, v, n, (float)(lr / bc1), beta1, beta2, eps, (float)(1.0 / sqrt(bc2)));
+  return LAUNCH_OK("adam_kernel");
+}

@@ -1,0 +1,313 @@
+"""Thin torch-tensor wrappers over the C ABI (include/dei2i.h).  PyTorch is plumbing here: device memory,
+streams.  Activations are BF16 tensors of shape [N, H, W, C] (NHWC, contiguous, C a multiple of 8)."""
+import ctypes as C
+from dataclasses import dataclass
+
+import torch
+
+from . import _lib
+from ._lib import ConvEpilogue, ConvGeom, check
+
+ACT = {None: 0, "none": 0, "leaky_relu": 1, "relu": 2, "tanh": 3, "sigmoid": 4}
+PAD = {"zeros": 0, "reflect": 1}
+
+
+def pad8(c: int) -> int:
+    return (c + 7) // 8 * 8
+
+
+def _stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def _p(t):
+    if t is None:
+        return None
+    return C.c_void_p(t.data_ptr())
+
+
+def _chk_act(t: torch.Tensor, name: str):
+    if not (t.is_cuda and t.dtype == torch.bfloat16 and t.is_contiguous() and t.dim() == 4 and t.shape[3] % 8 == 0):
+        raise ValueError(f"{name}: expected a contiguous CUDA bf16 [N,H,W,C%8==0] tensor, got {t.dtype} {tuple(t.shape)}")
+
+
+def _chk_f32(t: torch.Tensor, name: str):
+    if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+        raise ValueError(f"{name}: expected a contiguous CUDA fp32 tensor")
+
+
+@dataclass(frozen=True)
+class ConvSpec:
+    """Static description of one nn.Conv2d (reference: models/networks/architecture.py:95-100 etc.)."""
+    cin: int        # real input channels
+    cout: int       # real output channels
+    k: int
+    stride: int = 1
+    pad: int = 0
+    pad_mode: str = "zeros"
+    kw: int = 0     # 0 -> square
+
+    @property
+    def kh(self):
+        return self.k
+
+    @property
+    def kw_(self):
+        return self.kw or self.k
+
+    @property
+    def cin_ld(self):
+        return pad8(self.cin)
+
+    @property
+    def cout_ld(self):
+        return pad8(self.cout)
+
+    def out_hw(self, h, w):
+        return (h + 2 * self.pad - self.kh) // self.stride + 1, (w + 2 * self.pad - self.kw_) // self.stride + 1
+
+    def geom(self, n, h, w, hs=None, ws=None) -> ConvGeom:
+        return ConvGeom(n, h, w, hs or h, ws or w, self.cin_ld, self.cout, self.cout_ld, self.kh, self.kw_, self.stride,
+                        self.pad, PAD[self.pad_mode])
+
+    @property
+    def kf(self):
+        return (self.kh * self.kw_ * self.cin_ld + 63) // 64 * 64
+
+    @property
+    def kd(self):
+        return (self.kh * self.kw_ * self.cout_ld + 63) // 64 * 64
+
+
+def pack_weight(w: torch.Tensor, spec: ConvSpec, inv_sigma: torch.Tensor = None, need_dgrad: bool = True):
+    """fp32 [Cout,Cin,kh,kw] (optionally scaled by the device scalar inv_sigma) -> packed bf16 GEMM operands."""
+    _chk_f32(w, "w")
+    assert tuple(w.shape) == (spec.cout, spec.cin, spec.kh, spec.kw_), (w.shape, spec)
+    w_fwd = torch.empty(spec.cout, spec.kf, dtype=torch.bfloat16, device=w.device)
+    w_dg = torch.empty(spec.cin_ld, spec.kd, dtype=torch.bfloat16, device=w.device) if need_dgrad else None
+    lib = _lib.load()
+    check(lib.dei2i_pack_weight(_p(w), _p(inv_sigma), spec.cout, spec.cin, spec.kh, spec.kw_, spec.cin_ld, spec.cout_ld,
+                                _p(w_fwd), _p(w_dg), _stream()), "dei2i_pack_weight")
+    return w_fwd, w_dg
+
+
+def conv2d_fwd(x, w_fwd, spec: ConvSpec, bias=None, noise=None, noise_weight=None, residual=None, act=None,
+               out_fp32=False, logical_hw=None):
+    """x: bf16 [N,Hs,Ws,Cin_ld]; logical_hw=(H,W) nearest-resizes x on the fly. Returns [N,Ho,Wo,Cout_ld]."""
+    _chk_act(x, "x")
+    n, hs, ws, c = x.shape
+    assert c == spec.cin_ld, (c, spec)
+    h, w = logical_hw or (hs, ws)
+    ho, wo = spec.out_hw(h, w)
+    y = torch.empty(n, ho, wo, spec.cout_ld, dtype=torch.float32 if out_fp32 else torch.bfloat16, device=x.device)
+    if residual is not None:
+        _chk_act(residual, "residual")
+        assert residual.shape == y.shape
+    if noise is not None:
+        _chk_f32(noise, "noise")
+        assert noise.numel() == n * ho * wo
+    g = spec.geom(n, h, w, hs, ws)
+    e = ConvEpilogue(_p(bias), _p(noise), _p(noise_weight), _p(residual), ACT[act], int(out_fp32))
+    check(_lib.load().dei2i_conv2d_fwd(_p(x), _p(w_fwd), _p(y), C.byref(g), C.byref(e), _stream()), "dei2i_conv2d_fwd")
+    return y
+
+
+def conv2d_dgrad(dy, w_dgrad, spec: ConvSpec, in_hw):
+    """dy: bf16 [N,Ho,Wo,Cout_ld] -> dx bf16 [N,H,W,Cin_ld] (reflect padding folded back)."""
+    _chk_act(dy, "dy")
+    n = dy.shape[0]
+    h, w = in_hw
+    assert tuple(dy.shape[1:3]) == spec.out_hw(h, w) and dy.shape[3] == spec.cout_ld
+    g = spec.geom(n, h, w)
+    lib = _lib.load()
+    if spec.pad_mode == "reflect" and spec.pad > 0:
+        p = spec.pad
+        dxp = torch.empty(n, h + 2 * p, w + 2 * p, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
+        check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dxp), C.byref(g), 0, _stream()), "dei2i_conv2d_dgrad")
+        dx = torch.empty(n, h, w, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
+        check(lib.dei2i_reflect_fold(_p(dxp), _p(dx), n, h, w, spec.cin_ld, p, _stream()), "dei2i_reflect_fold")
+        return dx
+    dx = torch.empty(n, h, w, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
+    check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dx), C.byref(g), 0, _stream()), "dei2i_conv2d_dgrad")
+    return dx
+
+
+_ws_cache = {}
+
+
+def _workspace(nbytes, device):
+    key = (device.index, torch.cuda.current_stream().cuda_stream)
+    buf = _ws_cache.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        _ws_cache[key] = buf
+    return buf
+
+
+def conv2d_wgrad(x, dy, dw, spec: ConvSpec, accumulate=False, sn=None, logical_hw=None):
+    """dw (fp32 [Cout,Cin,kh,kw]) = or += grad.  sn = (w_orig, u, v, inv_sigma) applies the spectral-norm backward."""
+    _chk_act(x, "x")
+    _chk_act(dy, "dy")
+    _chk_f32(dw, "dw")
+    n, hs, ws, _ = x.shape
+    h, w = logical_hw or (hs, ws)
+    g = spec.geom(n, h, w, hs, ws)
+    lib = _lib.load()
+    nbytes = lib.dei2i_conv2d_wgrad_workspace(C.byref(g), spec.cin)
+    wsb = _workspace(nbytes, x.device)
+    w0, u, v, inv = sn if sn is not None else (None, None, None, None)
+    check(lib.dei2i_conv2d_wgrad(_p(x), _p(dy), _p(dw), spec.cin, 1.0 if accumulate else 0.0, C.byref(g), _p(w0), _p(u),
+                                 _p(v), _p(inv), _p(wsb), wsb.numel(), _stream()), "dei2i_conv2d_wgrad")
+    return dw
+
+
+def spectral_norm(w, u, v, training: bool, eps: float = 1e-12):
+    """In-place power iteration on (u, v) when training; returns the device tensor [1/sigma, sigma]."""
+    rows = w.shape[0]
+    cols = w.numel() // rows
+    out = torch.empty(2, dtype=torch.float32, device=w.device)
+    scratch = torch.empty(rows + 17 * cols, dtype=torch.float32, device=w.device)
+    check(_lib.load().dei2i_spectral_norm(_p(w), _p(u), _p(v), rows, cols, int(training), eps, _p(out), _p(scratch),
+                                          _stream()), "dei2i_spectral_norm")
+    return out
+
+
+def nchw_to_nhwc(x: torch.Tensor, c_ld: int = None):
+    _chk_f32(x, "x")
+    n, c, h, w = x.shape
+    c_ld = c_ld or pad8(c)
+    y = torch.empty(n, h, w, c_ld, dtype=torch.bfloat16, device=x.device)
+    check(_lib.load().dei2i_nchw_to_nhwc(_p(x), _p(y), n, c, h, w, c_ld, _stream()), "dei2i_nchw_to_nhwc")
+    return y
+
+
+def nhwc_to_nchw(x: torch.Tensor, c: int):
+    _chk_act(x, "x")
+    n, h, w, c_ld = x.shape
+    y = torch.empty(n, c, h, w, dtype=torch.float32, device=x.device)
+    check(_lib.load().dei2i_nhwc_to_nchw(_p(x), _p(y), n, c, h, w, c_ld, _stream()), "dei2i_nhwc_to_nchw")
+    return y
+
+
+def channel_stats(x, per_sample: bool):
+    _chk_act(x, "x")
+    n, h, w, c = x.shape
+    stats = torch.empty(n if per_sample else 1, 2, c, dtype=torch.float32, device=x.device)
+    check(_lib.load().dei2i_channel_stats(_p(x), n, h * w, c, int(per_sample), _p(stats), _stream()), "dei2i_channel_stats")
+    return stats
+
+
+def bn_fwd(x, gamma, beta, running_mean, running_var, training, act=None, residual=None, momentum=0.1, eps=1e-5):
+    _chk_act(x, "x")
+    n, h, w, c = x.shape
+    y = torch.empty_like(x)
+    stats = channel_stats(x, False) if training else None
+    save = torch.empty(2, c, dtype=torch.float32, device=x.device)
+    check(_lib.load().dei2i_bn_fwd(_p(x), _p(y), _p(residual), _p(stats), _p(gamma), _p(beta), _p(running_mean),
+                                   _p(running_var), _p(save[0]), _p(save[1]), n, h * w, c, int(training), momentum, eps,
+                                   ACT[act], _stream()), "dei2i_bn_fwd")
+    return y, save
+
+
+def bn_bwd(x, dy, gamma, beta, save, training, act=None):
+    _chk_act(x, "x")
+    _chk_act(dy, "dy")
+    n, h, w, c = x.shape
+    dx = torch.empty_like(x)
+    dgb = torch.empty(2, c, dtype=torch.float32, device=x.device)
+    scratch = torch.empty(2 * c, dtype=torch.float32, device=x.device)
+    check(_lib.load().dei2i_bn_bwd(_p(x), _p(dy), _p(dx), _p(gamma), _p(beta), _p(save[0]), _p(save[1]), _p(dgb[0]),
+                                   _p(dgb[1]), _p(scratch), n, h * w, c, int(training), ACT[act], _stream()), "dei2i_bn_bwd")
+    return dx, dgb[0], dgb[1]
+
+
+def spade_fwd(x, gb, up: int = 1, eps: float = 1e-5):
+    """x: [N,H/up,W/up,C]; gb: [N,H,W,2C] -> out [N,H,W,C] = relu(IN(x)*(1+gamma)+beta); also returns mean_rstd."""
+    _chk_act(x, "x")
+    _chk_act(gb, "gb")
+    n, hx, wx, c = x.shape
+    h, w = hx * up, wx * up
+    assert tuple(gb.shape) == (n, h, w, 2 * c), (gb.shape, x.shape, up)
+    stats = channel_stats(x, True)
+    out = torch.empty(n, h, w, c, dtype=torch.bfloat16, device=x.device)
+    mr = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
+    check(_lib.load().dei2i_spade_fwd(_p(x), _p(gb), _p(out), _p(stats), _p(mr), n, h, w, c, up, eps, _stream()),
+          "dei2i_spade_fwd")
+    return out, mr
+
+
+def spade_bwd(x, gb, out, dout, mean_rstd, up: int = 1):
+    n, h, w, c = out.shape
+    dgb = torch.empty_like(gb)
+    dx = torch.empty_like(x)
+    scratch = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
+    check(_lib.load().dei2i_spade_bwd(_p(x), _p(gb), _p(out), _p(dout), _p(dgb), _p(dx), _p(mean_rstd), _p(scratch), n, h, w,
+                                      c, up, _stream()), "dei2i_spade_bwd")
+    return dgb, dx
+
+
+def act_bwd(y, dy, act, want_dx=True, want_bias_grad=False):
+    _chk_act(dy, "dy")
+    c = dy.shape[3]
+    m = dy.numel() // c
+    dx = torch.empty_like(dy) if want_dx else None
+    bg = torch.empty(c, dtype=torch.float32, device=dy.device) if want_bias_grad else None
+    check(_lib.load().dei2i_act_bwd(_p(y), _p(dy), _p(dx), _p(bg), m, c, ACT[act], _stream()), "dei2i_act_bwd")
+    return dx, bg
+
+
+def noise_wgrad(dy, noise, dw, c_real, accumulate=False):
+    c = dy.shape[3]
+    m = dy.numel() // c
+    check(_lib.load().dei2i_noise_wgrad(_p(dy), _p(noise), _p(dw), m, c, c_real, 1.0 if accumulate else 0.0, _stream()),
+          "dei2i_noise_wgrad")
+    return dw
+
+
+def compose_fwd(hd, x, cycle_gan=False, want_nhwc=True):
+    """hd: fp32 [N,H,W,8] head logits; x: fp32 NCHW image -> (out NCHW fp32, prob [N,1,H,W] fp32, out NHWC bf16)."""
+    n, h, w, _ = hd.shape
+    out = torch.empty(n, 3, h, w, dtype=torch.float32, device=hd.device)
+    prob = torch.empty(n, 1, h, w, dtype=torch.float32, device=hd.device)
+    onhwc = torch.empty(n, h, w, 8, dtype=torch.bfloat16, device=hd.device) if want_nhwc else None
+    check(_lib.load().dei2i_compose_fwd(_p(hd), _p(x), _p(out), _p(prob), _p(onhwc), n, h, w, int(cycle_gan), _stream()),
+          "dei2i_compose_fwd")
+    return out, prob, onhwc
+
+
+def compose_bwd(hd, x, dout, dprob, cycle_gan=False, want_dx=True):
+    n, h, w, _ = hd.shape
+    dhd = torch.empty(n, h, w, 8, dtype=torch.bfloat16, device=hd.device)
+    dx = torch.empty(n, 3, h, w, dtype=torch.float32, device=hd.device) if want_dx else None
+    check(_lib.load().dei2i_compose_bwd(_p(hd), _p(x), _p(dout), _p(dprob), _p(dhd), _p(dx), n, h, w, int(cycle_gan),
+                                        _stream()), "dei2i_compose_bwd")
+    return dhd, dx
+
+
+def bce_logits(logits, targets=None, target_const=0.0, want_grad=True, grad_scale=1.0):
+    _chk_f32(logits, "logits")
+    loss = torch.empty((), dtype=torch.float32, device=logits.device)
+    grad = torch.empty_like(logits) if want_grad else None
+    check(_lib.load().dei2i_bce_logits(_p(logits), _p(targets), float(target_const), logits.numel(), _p(loss), _p(grad),
+                                       float(grad_scale), _stream()), "dei2i_bce_logits")
+    return loss, grad
+
+
+def l1(a, b=None, grad_a=None, grad_b=None, grad_scale=1.0, accumulate=False):
+    _chk_f32(a, "a")
+    loss = torch.empty((), dtype=torch.float32, device=a.device)
+    check(_lib.load().dei2i_l1(_p(a), _p(b), a.numel(), _p(loss), _p(grad_a), _p(grad_b), float(grad_scale), int(accumulate),
+                               _stream()), "dei2i_l1")
+    return loss
+
+
+def adam(p, g, m, v, lr, beta1, beta2, eps, step):
+    check(_lib.load().dei2i_adam(_p(p), _p(g), _p(m), _p(v), p.numel(), lr, beta1, beta2, eps, step, _stream()), "dei2i_adam")
+
+
+def launch_count() -> int:
+    return int(_lib.load().dei2i_launch_count())
+
+
+def set_tuning(key: str, value: int) -> int:
+    return int(_lib.load().dei2i_set_tuning(key.encode(), int(value)))

@@ -1,0 +1,164 @@
+/* dei2i.h - C ABI of libdei2i.so: the B200 (sm_100a) kernels behind the DefectGAN hot path.
+ *
+ * This is the drop-in boundary.  The reference (jason2714/de-i2i-gan) is pure PyTorch: its "FFI" for this path
+ * is the set of ATen library calls made by its nn.Modules.  Each entry point below names the reference call
+ * site(s) (path:line under /root/reference/defectGAN) whose device work it replaces.  Conventions:
+ *   - plain pointers and sizes only; every pointer is DEVICE memory owned by the caller (PyTorch's allocator);
+ *     the library never allocates, frees or retains device memory;
+ *   - activations are NHWC ("channels_last") BF16 with the channel pitch a multiple of 8; parameters, gradients,
+ *     statistics, losses and optimizer state are FP32;
+ *   - all work is enqueued on `stream`; no host synchronisation, capturable in a CUDA graph;
+ *   - return 0 on success, a negative dei2i_status otherwise; dei2i_last_error() gives the thread-local message;
+ *   - no CPU fallback: on a machine without an sm_100 device every compute entry point fails with DEI2I_ERR_CUDA.
+ */
+#ifndef DEI2I_H
+#define DEI2I_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* dei2i_stream; /* cudaStream_t */
+
+enum dei2i_status { DEI2I_OK = 0, DEI2I_ERR_CUDA = -1, DEI2I_ERR_INVALID = -2 };
+enum dei2i_act { DEI2I_ACT_NONE = 0, DEI2I_ACT_LRELU = 1 /* slope 0.2 */, DEI2I_ACT_RELU = 2, DEI2I_ACT_TANH = 3, DEI2I_ACT_SIGMOID = 4 };
+enum dei2i_pad { DEI2I_PAD_ZEROS = 0, DEI2I_PAD_REFLECT = 1 };
+
+int dei2i_version(void);
+const char* dei2i_last_error(void);
+/* runtime tuning knobs (tile / pipeline selection); returns the previous value, -1 for an unknown key */
+int dei2i_set_tuning(const char* key, int value);
+/* number of kernels launched by this library since process start (bench.py's gpu_launches) */
+long long dei2i_launch_count(void);
+
+/* Geometry of one nn.Conv2d call (architecture.py:51-56,95-100,228-233,320-337; normalization.py:17-22). */
+typedef struct dei2i_conv_geom {
+  int N;        /* batch */
+  int H, W;     /* logical input size seen by the convolution */
+  int Hs, Ws;   /* stored input size; nearest-resized to (H, W) on the fly (F.interpolate(mode='nearest'),
+                   normalization.py:29; nn.Upsample, architecture.py:49,203). Hs == H, Ws == W when no resize */
+  int Cin;      /* stored input channels (pitch), multiple of 8 (real channels first, rest zero) */
+  int Cout;     /* real output channels */
+  int Cout_ld;  /* output channel pitch, multiple of 8, >= Cout */
+  int kh, kw, stride, pad;
+  int pad_mode; /* dei2i_pad */
+} dei2i_conv_geom;
+
+typedef struct dei2i_conv_epilogue {
+  const float* bias;         /* [Cout] or NULL (SPADE convs, normalization.py:17-22) */
+  const float* noise;        /* [N*Ho*Wo] N(0,1) samples or NULL: NoiseInjection, architecture.py:385-389 */
+  const float* noise_weight; /* device scalar; required when noise != NULL */
+  const void* residual;      /* bf16 [N*Ho*Wo, Cout_ld] added last (NormResBlock, architecture.py:350) or NULL */
+  int act;                   /* dei2i_act, applied after bias and noise (ConvBlock, architecture.py:106-107) */
+  int out_fp32;              /* 0: y is bf16, 1: y is fp32 (same pitch) */
+} dei2i_conv_epilogue;
+
+/* Packed K-major BF16 weight matrices consumed by the implicit-GEMM kernels.
+ *   w        fp32 [Cout, Cin_real, kh, kw]  (nn.Conv2d.weight / weight_orig)
+ *   inv_sigma device scalar or NULL: multiplies every element (spectral norm W/sigma, architecture.py:109-112)
+ *   w_fwd    bf16 [Cout, Kf],  Kf = round_up(kh*kw*Cin, 64),      k = (r*kw+s)*Cin + ci
+ *   w_dgrad  bf16 [Cin,  Kd],  Kd = round_up(kh*kw*Cout_ld, 64),  k = (r*kw+s)*Cout_ld + co   (or NULL)      */
+int dei2i_pack_weight(const float* w, const float* inv_sigma, int Cout, int Cin_real, int kh, int kw, int Cin,
+                      int Cout_ld, void* w_fwd, void* w_dgrad, dei2i_stream stream);
+
+/* y = act(conv(x) + bias + noise_weight*noise) + residual          (nn.Conv2d forward + fused followers) */
+int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const dei2i_conv_geom* g,
+                     const dei2i_conv_epilogue* e, dei2i_stream stream);
+
+/* Gradient w.r.t. the convolution input (autograd of nn.Conv2d: conv_transpose of dy with W).
+ * dy: bf16 [N,Ho,Wo,Cout_ld].  pad_mode zeros:   dx is [N,H,W,Cin].
+ *                              pad_mode reflect: dx is over the PADDED domain [N,H+2p,W+2p,Cin]; fold it with
+ *                              dei2i_reflect_fold (the backward of F.pad(mode='reflect')).
+ * The output pitch is Cin; out_fp32 selects fp32 / bf16.  Resized inputs (Hs != H) are not supported here. */
+int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx, const dei2i_conv_geom* g, int out_fp32,
+                       dei2i_stream stream);
+/* dx[n,h,w,c] = sum of dxp over all padded positions that reflect onto (h,w); bf16 in / bf16 out */
+int dei2i_reflect_fold(const void* dxp, void* dx, int N, int H, int W, int C, int pad, dei2i_stream stream);
+
+/* Gradient w.r.t. the weight (autograd of nn.Conv2d), split over pixels, deterministic two-pass reduction.
+ *   dw  fp32 [Cout, Cin_real, kh, kw]; written (beta = 0) or accumulated (beta = 1).
+ *   workspace: dei2i_conv2d_wgrad_workspace(g) bytes of device scratch.
+ *   sn_u/sn_v/sn_w/sn_inv_sigma: when non-NULL apply the spectral-norm backward
+ *        dW_orig = (dW - <dW, W/sigma> u v^T) * inv_sigma            (torch.nn.utils.spectral_norm autograd). */
+size_t dei2i_conv2d_wgrad_workspace(const dei2i_conv_geom* g, int Cin_real);
+int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int Cin_real, float beta, const dei2i_conv_geom* g,
+                       const float* sn_w_orig, const float* sn_u, const float* sn_v, const float* sn_inv_sigma,
+                       void* workspace, size_t workspace_bytes, dei2i_stream stream);
+
+/* One power iteration of torch.nn.utils.spectral_norm (old hook API, architecture.py:7,68-71,109-112):
+ *   v <- normalize(W^T u); u <- normalize(W v); sigma = u^T W v;  W viewed as [rows, cols] fp32.
+ *   do_power_iter = 0 (eval mode) only recomputes sigma.  Writes inv_sigma[0] = 1/sigma, inv_sigma[1] = sigma.
+ *   scratch: (rows + 17 * cols) floats. */
+int dei2i_spectral_norm(const float* w, float* u, float* v, int rows, int cols, int do_power_iter, float eps,
+                        float* inv_sigma, float* scratch, dei2i_stream stream);
+
+/* NCHW fp32 <-> NHWC bf16 (channel pitch C_ld >= C, pad channels zero) at the model edge. */
+int dei2i_nchw_to_nhwc(const float* src, void* dst, int N, int C, int H, int W, int C_ld, dei2i_stream stream);
+int dei2i_nhwc_to_nchw(const void* src, float* dst, int N, int C, int H, int W, int C_ld, dei2i_stream stream);
+
+/* Per-channel (groups = 1) or per-(n,channel) (groups = N) sum and sum of squares of a bf16 NHWC tensor:
+ * nn.BatchNorm2d / nn.InstanceNorm2d statistics (generator.py:71,113,124; normalization.py:14).
+ * stats: fp32 [groups, 2, C] ([g][0][c] = sum, [g][1][c] = sum of squares), overwritten. */
+int dei2i_channel_stats(const void* x, int N, int HW, int C, int per_sample, float* stats, dei2i_stream stream);
+
+/* nn.BatchNorm2d (+ LeakyReLU(0.2) / residual add) forward, ConvBlock architecture.py:103-107, ResBlock :174-176.
+ * training: uses batch statistics from `stats` (dei2i_channel_stats, groups=1), updates running stats
+ * (momentum, unbiased var) and writes save_mean/save_rstd [C]; eval: uses running stats.
+ * y = act(bn(x)) + residual */
+int dei2i_bn_fwd(const void* x, void* y, const void* residual, const float* stats, const float* gamma,
+                 const float* beta, float* running_mean, float* running_var, float* save_mean, float* save_rstd,
+                 int N, int HW, int C, int training, float momentum, float eps, int act, dei2i_stream stream);
+/* backward of the above: dx, dgamma, dbeta (fp32 [C], written). y is the forward OUTPUT before the residual add
+ * is NOT needed: the activation mask is recomputed from x. scratch: fp32 [2*C]. */
+int dei2i_bn_bwd(const void* x, const void* dy, void* dx, const float* gamma, const float* beta, const float* save_mean,
+                 const float* save_rstd, float* dgamma, float* dbeta, float* scratch, int N, int HW, int C, int training,
+                 int act, dei2i_stream stream);
+
+/* SPADE modulation (normalization.py:24-37) + ReLU (architecture.py:244,347-348), optional 2x nearest up-sampling
+ * of x (architecture.py:242): out = relu(IN(x) * (1 + gamma) + beta), gamma/beta = first/second C columns of `gb`
+ * (bf16 [N,H,W,2C], output of the fused gamma|beta convolution).  x is [N,H/up,W/up,C].
+ * stats from dei2i_channel_stats(per_sample=1) on x; writes mean_rstd fp32 [N,2,C] for the backward. */
+int dei2i_spade_fwd(const void* x, const void* gb, void* out, const float* stats, float* mean_rstd, int N, int H,
+                    int W, int C, int up, float eps, dei2i_stream stream);
+/* backward: dgb (bf16 [N,H,W,2C]) and dx (bf16 [N,H/up,W/up,C]); scratch fp32 [N,2,C]. */
+int dei2i_spade_bwd(const void* x, const void* gb, const void* out, const void* dout, void* dgb, void* dx,
+                    const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, dei2i_stream stream);
+
+/* act backward for fused conv epilogues: dx = dy * act'(y) computed from the saved OUTPUT y (bf16);
+ * bias_grad (fp32 [C], may be NULL) receives sum over pixels of dx. */
+int dei2i_act_bwd(const void* y, const void* dy, void* dx, float* bias_grad, long long M, int C, int act,
+                  dei2i_stream stream);
+
+/* NoiseInjection weight gradient: dw[0] (+)= sum_{m,c} dy[m,c] * noise[m]  (architecture.py:389). */
+int dei2i_noise_wgrad(const void* dy, const float* noise, float* dw, long long M, int C, int C_real, float beta,
+                      dei2i_stream stream);
+
+/* Generator heads + composition (generator.py:268-270): hd = fp32 [M,8] raw head convolution output
+ * (cols 0..2 foreground logits, col 3 distribution logit); x, out: fp32 NCHW images; prob: fp32 [N,1,H,W].
+ * out = x*(1-p) + tanh(fg)*p,  p = sigmoid(hd[:,3]).  out_nhwc (bf16, pitch 8, may be NULL) gets a copy of out. */
+int dei2i_compose_fwd(const float* hd, const float* x, float* out, float* prob, void* out_nhwc, int N, int H, int W,
+                      int cycle_gan, dei2i_stream stream);
+/* backward: dhd (bf16 [M,8]) and dx (fp32 NCHW, may be NULL) from dout (fp32 NCHW, may be NULL) and dprob. */
+int dei2i_compose_bwd(const float* hd, const float* x, const float* dout, const float* dprob, void* dhd, float* dx,
+                      int N, int H, int W, int cycle_gan, dei2i_stream stream);
+
+/* Loss reductions (BaseModel._cal_loss, models/base_model.py:68-80).  Each writes loss[0] (mean) and, when grad is
+ * non-NULL, grad = grad_scale * d(mean loss)/d(input) (fp32, same shape as input).
+ * bce: binary_cross_entropy_with_logits(logits, targets) with targets either a constant (targets == NULL,
+ * target_const) or an fp32 tensor;  l1: l1_loss(a, b) with b == NULL meaning zeros. */
+int dei2i_bce_logits(const float* logits, const float* targets, float target_const, long long n, float* loss,
+                     float* grad, float grad_scale, dei2i_stream stream);
+int dei2i_l1(const float* a, const float* b, long long n, float* loss, float* grad_a, float* grad_b, float grad_scale,
+             int accumulate_grad, dei2i_stream stream);
+
+/* torch.optim.Adam step (trainers/base_trainer.py:75-89) over one flat fp32 parameter vector. step is 1-based. */
+int dei2i_adam(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2,
+               float eps, int step, dei2i_stream stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DEI2I_H */

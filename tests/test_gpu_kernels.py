@@ -1,0 +1,371 @@
+"""Kernel-level parity through the C ABI: every CUDA entry point against a plain PyTorch FP32 CPU computation of the
+same op on the same seeded inputs.  Inputs/weights are rounded to BF16 first so the comparison isolates the kernel
+(FP32 accumulation, BF16 output rounding): tolerance 1e-2 of the output's max magnitude for BF16 outputs
+(north-star: 2e-2 in BF16), 2e-3 for FP32 outputs."""
+import json
+import os
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+from conftest import rel_err, ROOT
+
+pytestmark = pytest.mark.gpu
+
+TOL_BF16 = 1e-2
+TOL_F32 = 2e-3
+
+
+def _report(name, **kv):
+    try:
+        os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+        with open(os.path.join(ROOT, "gpurun_out", "kernel_parity.jsonl"), "a") as f:
+            f.write(json.dumps(dict(test=name, **kv)) + "\n")
+    except OSError:
+        pass
+
+
+def q(t):
+    return t.bfloat16().float()
+
+
+def to_dev(x_nchw):
+    """fp32 NCHW CPU -> bf16 NHWC CUDA with the channel pitch padded to 8 (host-side, independent of our kernels)."""
+    n, c, h, w = x_nchw.shape
+    cp = (c + 7) // 8 * 8
+    y = torch.zeros(n, h, w, cp)
+    y[..., :c] = x_nchw.permute(0, 2, 3, 1)
+    return y.bfloat16().cuda().contiguous()
+
+
+def from_dev(y_nhwc, c):
+    return y_nhwc.float().cpu()[..., :c].permute(0, 3, 1, 2).contiguous()
+
+
+def ref_conv(x, w, b, stride, pad, pad_mode, size=None):
+    if size is not None:
+        x = F.interpolate(x, size=size, mode="nearest")
+    if pad and pad_mode == "reflect":
+        x = F.pad(x, (pad,) * 4, mode="reflect")
+        pad = 0
+    return F.conv2d(x, w, b, stride=stride, padding=pad)
+
+
+CONV_CASES = {
+    # name: (N, Cin, H, W, Cout, k, stride, pad, pad_mode, bias, resize_from)
+    "res3x3_64": (2, 64, 16, 16, 64, 3, 1, 1, "reflect", False, None),
+    "res3x3_256": (1, 256, 16, 16, 256, 3, 1, 1, "reflect", False, None),
+    "enc4x4s2": (2, 64, 32, 32, 128, 4, 2, 1, "reflect", False, None),
+    "stem7x7": (2, 3, 24, 24, 64, 7, 1, 3, "reflect", False, None),
+    "spade_shared_1x1seg": (2, 6, 16, 16, 128, 3, 1, 1, "zeros", True, (1, 1)),
+    "spade_shared_8x8seg": (2, 6, 16, 16, 128, 3, 1, 1, "zeros", True, (8, 8)),
+    "spade_gb_512": (1, 128, 16, 16, 512, 3, 1, 1, "zeros", True, None),
+    "heads_4": (2, 64, 16, 16, 4, 3, 1, 1, "reflect", False, None),
+    "cls_valid_k2": (3, 256, 2, 2, 6, 2, 1, 0, "zeros", False, None),
+    "ragged_m": (1, 64, 10, 10, 64, 3, 1, 1, "reflect", False, None),
+    "d_conv0": (2, 3, 32, 32, 64, 4, 2, 1, "reflect", False, None),
+    "d_src_1": (2, 128, 4, 4, 1, 3, 1, 1, "reflect", False, None),
+}
+
+
+def _make(case, seed=0):
+    n, cin, h, w, cout, k, s, p, pm, bias, rs = CONV_CASES[case]
+    g = torch.Generator().manual_seed(seed)
+    hs, ws = rs if rs else (h, w)
+    x = q(torch.randn(n, cin, hs, ws, generator=g))
+    wt = q(torch.randn(cout, cin, k, k, generator=g) * (1.0 / (cin * k * k) ** 0.5))
+    b = torch.randn(cout, generator=g) if bias else None
+    return x, wt, b
+
+
+@pytest.mark.parametrize("case", list(CONV_CASES))
+def test_conv_fwd(case):
+    from de_i2i_gan_b200 import ops
+    n, cin, h, w, cout, k, s, p, pm, bias, rs = CONV_CASES[case]
+    x, wt, b = _make(case)
+    ref = ref_conv(x, wt, b, s, p, pm, (h, w) if rs else None)
+    spec = ops.ConvSpec(cin, cout, k, s, p, pm)
+    w_fwd, _ = ops.pack_weight(wt.cuda(), spec, need_dgrad=False)
+    y = ops.conv2d_fwd(to_dev(x), w_fwd, spec, bias=b.cuda() if bias else None, logical_hw=(h, w) if rs else None)
+    torch.cuda.synchronize()
+    err = rel_err(from_dev(y, cout), ref)
+    _report("conv_fwd/" + case, err=err)
+    assert err < TOL_BF16, err
+    if spec.cout_ld > cout and not bias:  # pad channels stay exactly zero
+        assert y[..., cout:].abs().max().item() == 0.0
+
+
+def test_conv_fwd_fp32_out_and_epilogue():
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    n, c, h, w = 2, 64, 12, 12
+    x, wt = q(torch.randn(n, c, h, w, generator=g)), q(torch.randn(c, c, 3, 3, generator=g) / 24)
+    noise = torch.randn(n, 1, h, w, generator=g)
+    nw = torch.tensor([0.3])
+    res = q(torch.randn(n, c, h, w, generator=g))
+    spec = ops.ConvSpec(c, c, 3, 1, 1, "reflect")
+    w_fwd, _ = ops.pack_weight(wt.cuda(), spec, need_dgrad=False)
+    conv = ref_conv(x, wt, None, 1, 1, "reflect")
+    y = ops.conv2d_fwd(to_dev(x), w_fwd, spec, out_fp32=True)
+    e1 = rel_err(y.cpu().permute(0, 3, 1, 2), conv)
+    y2 = ops.conv2d_fwd(to_dev(x), w_fwd, spec, noise=noise.cuda().contiguous(), noise_weight=nw.cuda(), residual=to_dev(res),
+                        act="leaky_relu")
+    e2 = rel_err(from_dev(y2, c), F.leaky_relu(conv + 0.3 * noise, 0.2) + res)
+    y3 = ops.conv2d_fwd(to_dev(x), w_fwd, spec, act="tanh", out_fp32=True)
+    e3 = rel_err(y3.cpu().permute(0, 3, 1, 2), torch.tanh(conv))
+    _report("conv_fwd/epilogue", fp32=e1, fused=e2, tanh=e3)
+    assert e1 < TOL_F32 and e2 < TOL_BF16 and e3 < TOL_F32
+
+
+DGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "spade_gb_512", "heads_4", "ragged_m", "d_src_1", "cls_valid_k2"]
+
+
+@pytest.mark.parametrize("case", DGRAD_CASES)
+def test_conv_dgrad(case):
+    from de_i2i_gan_b200 import ops
+    n, cin, h, w, cout, k, s, p, pm, bias, rs = CONV_CASES[case]
+    x, wt, b = _make(case)
+    x.requires_grad_(True)
+    y = ref_conv(x, wt, None, s, p, pm)
+    dy = q(torch.randn(y.shape, generator=torch.Generator().manual_seed(9)))
+    (dx_ref,) = torch.autograd.grad(y, x, dy)
+    spec = ops.ConvSpec(cin, cout, k, s, p, pm)
+    _, w_dg = ops.pack_weight(wt.cuda(), spec)
+    dx = ops.conv2d_dgrad(to_dev(dy), w_dg, spec, (h, w))
+    torch.cuda.synchronize()
+    err = rel_err(from_dev(dx, cin), dx_ref)
+    _report("conv_dgrad/" + case, err=err)
+    assert err < TOL_BF16, err
+
+
+WGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "stem7x7", "spade_shared_8x8seg", "spade_gb_512", "heads_4",
+               "ragged_m", "d_conv0", "d_src_1", "cls_valid_k2"]
+
+
+@pytest.mark.parametrize("case", WGRAD_CASES)
+def test_conv_wgrad(case):
+    from de_i2i_gan_b200 import ops
+    n, cin, h, w, cout, k, s, p, pm, bias, rs = CONV_CASES[case]
+    x, wt, b = _make(case)
+    wt.requires_grad_(True)
+    y = ref_conv(x, wt, None, s, p, pm, (h, w) if rs else None)
+    dy = q(torch.randn(y.shape, generator=torch.Generator().manual_seed(11)))
+    (dw_ref,) = torch.autograd.grad(y, wt, dy)
+    spec = ops.ConvSpec(cin, cout, k, s, p, pm)
+    dw = torch.full(wt.shape, 7.0, device="cuda")
+    ops.conv2d_wgrad(to_dev(x), to_dev(dy), dw, spec, logical_hw=(h, w) if rs else None)
+    e1 = rel_err(dw.cpu(), dw_ref)
+    ops.conv2d_wgrad(to_dev(x), to_dev(dy), dw, spec, accumulate=True, logical_hw=(h, w) if rs else None)
+    e2 = rel_err(dw.cpu(), 2 * dw_ref)
+    _report("conv_wgrad/" + case, err=e1, err_acc=e2)
+    assert e1 < TOL_F32 and e2 < TOL_F32, (e1, e2)
+
+
+def test_wgrad_spectral_backward_and_power_iteration():
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(3)
+    cout, cin, k = 64, 64, 3
+    w0 = torch.randn(cout, cin, k, k, generator=g) * 0.05
+    u0 = F.normalize(torch.randn(cout, generator=g), dim=0)
+    v0 = F.normalize(torch.randn(cin * k * k, generator=g), dim=0)
+    # reference: one power iteration, then sigma (torch.nn.utils.spectral_norm, old API)
+    wm = w0.reshape(cout, -1)
+    v1 = F.normalize(wm.t() @ u0, dim=0, eps=1e-12)
+    u1 = F.normalize(wm @ v1, dim=0, eps=1e-12)
+    w0r = w0.clone().requires_grad_(True)
+    sigma = torch.dot(u1, w0r.reshape(cout, -1) @ v1)
+    wsn = w0r / sigma
+    ud, vd = u0.cuda(), v0.cuda()
+    inv = ops.spectral_norm(w0.cuda(), ud, vd, True)
+    assert rel_err(ud.cpu(), u1) < 1e-4 and rel_err(vd.cpu(), v1) < 1e-4
+    assert abs(inv[1].item() - sigma.item()) < 1e-4 * abs(sigma.item())
+    inv_eval = ops.spectral_norm(w0.cuda(), ud, vd, False)
+    assert abs(inv_eval[1].item() - sigma.item()) < 1e-4 * abs(sigma.item())
+    # backward through W/sigma into W_orig
+    x = q(torch.randn(2, cin, 12, 12, generator=g))
+    y = ref_conv(x, wsn, None, 1, 1, "reflect")
+    dy = q(torch.randn(y.shape, generator=g))
+    (dw_ref,) = torch.autograd.grad(y, w0r, dy)
+    spec = ops.ConvSpec(cin, cout, k, 1, 1, "reflect")
+    dw = torch.zeros_like(w0, device="cuda")
+    ops.conv2d_wgrad(to_dev(x), to_dev(dy), dw, spec, sn=(w0.cuda(), ud, vd, inv))
+    err = rel_err(dw.cpu(), dw_ref)
+    _report("wgrad_spectral", err=err)
+    assert err < 5e-3, err
+    # packed forward weight = W/sigma
+    w_fwd, _ = ops.pack_weight(w0.cuda(), spec, inv_sigma=inv, need_dgrad=False)
+    ref_pack = wsn.detach().permute(0, 2, 3, 1).reshape(cout, -1)
+    assert rel_err(w_fwd.float().cpu()[:, : ref_pack.shape[1]], ref_pack) < 1e-2
+
+
+def test_layout_roundtrip_and_fold():
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(1)
+    x = torch.randn(2, 3, 9, 11, generator=g)
+    d = ops.nchw_to_nhwc(x.cuda())
+    assert d.shape == (2, 9, 11, 8) and d[..., 3:].abs().max().item() == 0
+    assert rel_err(ops.nhwc_to_nchw(d, 3).cpu(), q(x)) == 0.0
+
+
+@pytest.mark.parametrize("c,hw,per_sample", [(64, 16, False), (256, 8, True), (8, 32, False), (128, 20, True)])
+def test_channel_stats(c, hw, per_sample):
+    from de_i2i_gan_b200 import ops
+    x = q(torch.randn(3, c, hw, hw, generator=torch.Generator().manual_seed(2)) + 0.5)
+    st = ops.channel_stats(to_dev(x), per_sample).cpu()
+    dims = (2, 3) if per_sample else (0, 2, 3)
+    assert rel_err(st[:, 0], x.sum(dims).reshape(st[:, 0].shape)) < 1e-4
+    assert rel_err(st[:, 1], (x * x).sum(dims).reshape(st[:, 1].shape)) < 1e-4
+
+
+@pytest.mark.parametrize("training,act,with_res", [(True, "leaky_relu", False), (True, None, True), (False, "leaky_relu", False)])
+def test_batchnorm_fwd_bwd(training, act, with_res):
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(4)
+    n, c, h = 3, 64, 12
+    x = q(torch.randn(n, c, h, h, generator=g) * 1.5 + 0.3).requires_grad_(True)
+    gamma = (1 + 0.1 * torch.randn(c, generator=g)).requires_grad_(True)
+    beta = (0.1 * torch.randn(c, generator=g)).requires_grad_(True)
+    rm, rv = torch.randn(c, generator=g) * 0.1, torch.rand(c, generator=g) + 0.5
+    res = q(torch.randn(n, c, h, h, generator=g)) if with_res else None
+    rm_ref, rv_ref = rm.clone(), rv.clone()
+    y_ref = F.batch_norm(x, rm_ref, rv_ref, gamma, beta, training, 0.1, 1e-5)
+    if act:
+        y_ref = F.leaky_relu(y_ref, 0.2)
+    if with_res:
+        y_ref = y_ref + res
+    dy = q(torch.randn(y_ref.shape, generator=g))
+    dx_ref, dg_ref, db_ref = torch.autograd.grad(y_ref, (x, gamma, beta), dy)
+    rmd, rvd = rm.cuda(), rv.cuda()
+    xd = to_dev(x.detach())
+    y, save = ops.bn_fwd(xd, gamma.detach().cuda(), beta.detach().cuda(), rmd, rvd, training, act=act,
+                         residual=to_dev(res) if with_res else None)
+    e_y = rel_err(from_dev(y, c), y_ref)
+    assert e_y < TOL_BF16, e_y
+    if training:
+        assert rel_err(rmd.cpu(), rm_ref) < 1e-3 and rel_err(rvd.cpu(), rv_ref) < 1e-3
+    dx, dgm, dbt = ops.bn_bwd(xd, to_dev(dy), gamma.detach().cuda(), beta.detach().cuda(), save, training, act=act)
+    e = (rel_err(from_dev(dx, c), dx_ref), rel_err(dgm.cpu(), dg_ref), rel_err(dbt.cpu(), db_ref))
+    _report(f"bn/{training}/{act}/{with_res}", y=e_y, dx=e[0], dgamma=e[1], dbeta=e[2])
+    assert e[0] < TOL_BF16 and e[1] < 5e-3 and e[2] < 5e-3, e
+
+
+@pytest.mark.parametrize("up", [1, 2])
+def test_spade_fwd_bwd(up):
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(6)
+    n, c, hx = 2, 64, 8
+    h = hx * up
+    x = q(torch.randn(n, c, hx, hx, generator=g) * 2 + 1).requires_grad_(True)
+    gamma = q(torch.randn(n, c, h, h, generator=g) * 0.5).requires_grad_(True)
+    beta = q(torch.randn(n, c, h, h, generator=g) * 0.5).requires_grad_(True)
+    xu = F.interpolate(x, scale_factor=up, mode="nearest") if up > 1 else x
+    out_ref = F.relu(F.instance_norm(xu, eps=1e-5) * (1 + gamma) + beta)
+    dout = q(torch.randn(out_ref.shape, generator=g))
+    dx_ref, dg_ref, db_ref = torch.autograd.grad(out_ref, (x, gamma, beta), dout)
+    gb = torch.cat([gamma.detach(), beta.detach()], 1)
+    xd, gbd = to_dev(x.detach()), to_dev(gb)
+    out, mr = ops.spade_fwd(xd, gbd, up)
+    e_out = rel_err(from_dev(out, c), out_ref)
+    dgb, dx = ops.spade_bwd(xd, gbd, out, to_dev(dout), mr, up)
+    dgb_h = from_dev(dgb, 2 * c)
+    e = (rel_err(dx.float().cpu().permute(0, 3, 1, 2), dx_ref), rel_err(dgb_h[:, :c], dg_ref), rel_err(dgb_h[:, c:], db_ref))
+    _report(f"spade/up{up}", out=e_out, dx=e[0], dgamma=e[1], dbeta=e[2])
+    assert e_out < TOL_BF16 and max(e) < 2e-2, (e_out, e)
+
+
+@pytest.mark.parametrize("act", ["leaky_relu", "relu", "tanh", "sigmoid", None])
+def test_act_bwd_and_bias_grad(act):
+    from de_i2i_gan_b200 import ops
+    from oracle.defectgan_ref import act as ref_act
+    g = torch.Generator().manual_seed(7)
+    z = torch.randn(2, 64, 9, 9, generator=g).requires_grad_(True)
+    y = ref_act(z, act)
+    dy = q(torch.randn(y.shape, generator=g))
+    (dz_ref,) = torch.autograd.grad(y, z, dy)
+    yq = to_dev(y.detach())
+    dx, bg = ops.act_bwd(yq, to_dev(dy), act, True, True)
+    e1, e2 = rel_err(from_dev(dx, 64), dz_ref), rel_err(bg.cpu(), dz_ref.sum((0, 2, 3)))
+    _report(f"act_bwd/{act}", dx=e1, bias=e2)
+    assert e1 < 2e-2 and e2 < 2e-2
+
+
+def test_noise_wgrad():
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(8)
+    dy = q(torch.randn(2, 64, 10, 10, generator=g))
+    noise = torch.randn(2, 1, 10, 10, generator=g)
+    ref = (dy * noise).sum()
+    dw = torch.zeros(1, device="cuda")
+    ops.noise_wgrad(to_dev(dy), noise.cuda().contiguous(), dw, 64)
+    ops.noise_wgrad(to_dev(dy), noise.cuda().contiguous(), dw, 64, accumulate=True)
+    assert abs(dw.item() - 2 * ref.item()) < 1e-3 * abs(ref.item()) + 1e-3
+
+
+@pytest.mark.parametrize("cycle", [False, True])
+def test_compose_fwd_bwd(cycle):
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(10)
+    n, h = 2, 12
+    hd = torch.randn(n, h, h, 8, generator=g)
+    x = torch.randn(n, 3, h, h, generator=g).clamp(-1, 1).requires_grad_(True)
+    hdr = hd.clone().requires_grad_(True)
+    fg = torch.tanh(hdr[..., :3]).permute(0, 3, 1, 2)
+    p = torch.sigmoid(hdr[..., 3:4]).permute(0, 3, 1, 2)
+    out_ref = fg if cycle else x * (1 - p) + fg * p
+    dout, dprob = torch.randn(n, 3, h, h, generator=g), torch.randn(n, 1, h, h, generator=g)
+    grads = torch.autograd.grad((out_ref, p), (hdr, x), (dout, dprob), allow_unused=True)
+    out, prob, onhwc = ops.compose_fwd(hd.cuda(), x.detach().cuda(), cycle)
+    assert rel_err(out.cpu(), out_ref) < 1e-4 and rel_err(prob.cpu(), p) < 1e-4
+    assert rel_err(onhwc.float().cpu()[..., :3].permute(0, 3, 1, 2), out_ref) < 1e-2
+    dhd, dx = ops.compose_bwd(hd.cuda(), x.detach().cuda(), dout.cuda(), dprob.cuda(), cycle)
+    assert rel_err(dhd.float().cpu()[..., :4], grads[0][..., :4]) < 1e-2
+    if not cycle:
+        assert rel_err(dx.cpu(), grads[1]) < 1e-4
+
+
+def test_losses_and_adam():
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(12)
+    z = (torch.randn(4, 1, 4, 4, generator=g) * 3).requires_grad_(True)
+    for tc in (0.0, 1.0):
+        ref = F.binary_cross_entropy_with_logits(z, torch.full_like(z, tc))
+        (gr,) = torch.autograd.grad(ref, z)
+        loss, grad = ops.bce_logits(z.detach().cuda(), target_const=tc, grad_scale=0.5)
+        assert abs(loss.item() - ref.item()) < 1e-5 and rel_err(grad.cpu(), 0.5 * gr) < 1e-4
+    t = (torch.rand(4, 6, generator=g) > 0.5).float()
+    zz = torch.randn(4, 6, generator=g).requires_grad_(True)
+    ref = F.binary_cross_entropy_with_logits(zz, t)
+    (gr,) = torch.autograd.grad(ref, zz)
+    loss, grad = ops.bce_logits(zz.detach().cuda(), targets=t.cuda())
+    assert abs(loss.item() - ref.item()) < 1e-5 and rel_err(grad.cpu(), gr) < 1e-4
+    a = torch.randn(2, 3, 40, 40, generator=g).requires_grad_(True)
+    b = torch.randn(2, 3, 40, 40, generator=g).requires_grad_(True)
+    ref = F.l1_loss(a, b)
+    ga_ref, gb_ref = torch.autograd.grad(ref, (a, b))
+    ga, gb = torch.zeros_like(a, device="cuda"), torch.zeros_like(b, device="cuda")
+    loss = ops.l1(a.detach().cuda(), b.detach().cuda(), ga, gb, grad_scale=2.0)
+    assert abs(loss.item() - ref.item()) < 1e-5
+    assert rel_err(ga.cpu(), 2 * ga_ref) < 1e-5 and rel_err(gb.cpu(), 2 * gb_ref) < 1e-5
+    loss0 = ops.l1(a.detach().cuda())
+    assert abs(loss0.item() - a.abs().mean().item()) < 1e-5
+    # Adam vs torch.optim.Adam over 3 steps
+    p = torch.randn(1000, generator=g)
+    pt = p.clone().requires_grad_(True)
+    opt = torch.optim.Adam([pt], lr=2e-4, betas=(0.5, 0.999))
+    pd, m, v = p.cuda(), torch.zeros(1000, device="cuda"), torch.zeros(1000, device="cuda")
+    for step in range(1, 4):
+        gr = torch.randn(1000, generator=g)
+        pt.grad = gr.clone()
+        opt.step()
+        ops.adam(pd, gr.cuda(), m, v, 2e-4, 0.5, 0.999, 1e-8, step)
+    assert (pd.cpu() - pt.detach()).abs().max().item() < 1e-6
+
+
+def test_errors_are_reported_not_fatal():
+    from de_i2i_gan_b200 import ops
+    spec = ops.ConvSpec(64, 64, 3, 1, 1, "reflect")
+    x = torch.zeros(1, 1, 1, 64, dtype=torch.bfloat16, device="cuda")  # reflect pad 1 needs H,W > 1
+    w = torch.zeros(64, spec.kf, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(RuntimeError, match="reflect"):
+        ops.conv2d_fwd(x, w, spec)

@@ -15,7 +15,7 @@ class ConvGeom(C.Structure):
 
 
 class ConvEpilogue(C.Structure):
-    _fields_ = [("bias", C.c_void_p), ("noise", C.c_void_p), ("noise_weight", C.c_void_p), ("residual", C.c_void_p),
+    _fields_ = [("scale", C.c_void_p), ("bias", C.c_void_p), ("noise", C.c_void_p), ("noise_weight", C.c_void_p), ("residual", C.c_void_p),
                 ("act", C.c_int), ("out_fp32", C.c_int)]
 
 
@@ -29,7 +29,7 @@ SIGNATURES = {
     "dei2i_launch_count": (_LL, []),
     "dei2i_pack_weight": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     "dei2i_conv2d_fwd": (_I, [_P, _P, _P, C.POINTER(ConvGeom), C.POINTER(ConvEpilogue), _P]),
-    "dei2i_conv2d_dgrad": (_I, [_P, _P, _P, C.POINTER(ConvGeom), _I, _P]),
+    "dei2i_conv2d_dgrad": (_I, [_P, _P, _P, C.POINTER(ConvGeom), _P, _I, _P]),
     "dei2i_reflect_fold": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
     "dei2i_conv2d_wgrad_workspace": (_SZ, [C.POINTER(ConvGeom), _I]),
     "dei2i_conv2d_wgrad": (_I, [_P, _P, _P, _I, _F, C.POINTER(ConvGeom), _P, _P, _P, _P, _P, _SZ, _P]),
@@ -39,8 +39,8 @@ SIGNATURES = {
     "dei2i_channel_stats": (_I, [_P, _I, _I, _I, _I, _P, _P]),
     "dei2i_bn_fwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _I, _P]),
     "dei2i_bn_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
-    "dei2i_spade_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _F, _P]),
-    "dei2i_spade_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_spade_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
+    "dei2i_spade_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
     "dei2i_act_bwd": (_I, [_P, _P, _P, _P, _LL, _I, _I, _P]),
     "dei2i_noise_wgrad": (_I, [_P, _P, _P, _LL, _I, _I, _F, _P]),
     "dei2i_compose_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),

@@ -73,6 +73,7 @@ DEVINL const __nv_bfloat16* gather_ptr(const Gather& g, int img, int oy, int ox,
 }
 
 struct Epilogue {
+  const float* scale;
   const float* bias;
   const float* noise;
   const float* noise_weight;
@@ -186,6 +187,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_b, const ConvKParams 
     const bool row_ok = m < g.M;
     float nz = 0.f;
     if (e.noise != nullptr && row_ok) nz = __ldg(e.noise + m) * __ldg(e.noise_weight);
+    const float osc = e.scale != nullptr ? __ldg(e.scale) : 1.f;
     constexpr int CH = BLOCK_N >= 32 ? 32 : 16;
 #pragma unroll 1
     for (int c = 0; c < BLOCK_N; c += CH) {
@@ -199,7 +201,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_b, const ConvKParams 
         float f[CH];
 #pragma unroll
         for (int t = 0; t < CH; ++t) {
-          float x = __uint_as_float(v[t]);
+          float x = __uint_as_float(v[t]) * osc;
           const int n = nbase + t;
           if (e.bias != nullptr && n < e.ncols) x += __ldg(e.bias + n);
           x += nz;
@@ -601,14 +603,14 @@ extern "C" int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const
   p.g.M = (long long)g->N * Ho * Wo;
   const int K = round_up(g->kh * g->kw * g->Cin, 64);
   p.num_kb = K / 64;
-  p.e.bias = e->bias; p.e.noise = e->noise; p.e.noise_weight = e->noise_weight;
+  p.e.scale = e->scale; p.e.bias = e->bias; p.e.noise = e->noise; p.e.noise_weight = e->noise_weight;
   p.e.residual = (const __nv_bfloat16*)e->residual; p.e.out = y; p.e.act = e->act; p.e.out_fp32 = e->out_fp32;
   p.e.ld = g->Cout_ld; p.e.ncols = g->Cout;
   return run_igemm(p, w_fwd, g->Cout, K, (cudaStream_t)stream);
 }
 
-extern "C" int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx, const dei2i_conv_geom* g, int out_fp32,
-                                  dei2i_stream stream) {
+extern "C" int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx, const dei2i_conv_geom* g, const float* scale,
+                                  int out_fp32, dei2i_stream stream) {
   if (int rc = check_geom(g)) return rc;
   DEI2I_REQUIRE(dy && w_dgrad && dx, "conv2d_dgrad: null pointer");
   DEI2I_REQUIRE(g->Hs == g->H && g->Ws == g->W, "conv2d_dgrad: resized inputs are not supported");
@@ -625,7 +627,7 @@ extern "C" int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx,
   p.g.M = (long long)g->N * Hd * Wd;
   const int K = round_up(g->kh * g->kw * g->Cout_ld, 64);
   p.num_kb = K / 64;
-  p.e.out = dx; p.e.act = 0; p.e.out_fp32 = out_fp32; p.e.ld = g->Cin; p.e.ncols = g->Cin;
+  p.e.scale = scale; p.e.out = dx; p.e.act = 0; p.e.out_fp32 = out_fp32; p.e.ld = g->Cin; p.e.ncols = g->Cin;
   return run_igemm(p, w_dgrad, g->Cin, K, (cudaStream_t)stream);
 }
 

@@ -383,7 +383,7 @@ __global__ void bn_bwd_apply_kernel(const uint4* __restrict__ x, const uint4* __
 // ------------------------------------------------------------------------------------------ SPADE
 __global__ void spade_fwd_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb, uint4* __restrict__ out,
                                  const float* __restrict__ stats, float* __restrict__ mean_rstd, int N, int H, int W, int C8, int up,
-                                 float eps) {
+                                 int relu, float eps) {
   // grid.y = image; every block of an image derives that image's mean / rstd into smem
   extern __shared__ float sh[];  // mean[C], rstd[C]
   const int C = C8 * 8;
@@ -415,7 +415,8 @@ __global__ void spade_fwd_kernel(const uint4* __restrict__ x, const uint4* __res
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const float xh = (fx[k] - sh[c8 * 8 + k]) * sh[C + c8 * 8 + k];
-      o[k] = fmaxf(xh * (1.f + fg[k]) + fb[k], 0.f);
+      const float t = xh * (1.f + fg[k]) + fb[k];
+      o[k] = relu ? fmaxf(t, 0.f) : t;
     }
     out[(long long)n * per_img + i] = pack8(o);
   }
@@ -425,7 +426,7 @@ __global__ void spade_fwd_kernel(const uint4* __restrict__ x, const uint4* __res
 // grid (chunks, N); block = C8 columns x lanes
 __global__ void spade_bwd1_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb, const uint4* __restrict__ out,
                                   const uint4* __restrict__ dout, uint4* __restrict__ dgb, const float* __restrict__ mean_rstd,
-                                  float* __restrict__ red /*[N,2,C]*/, int H, int W, int C8, int up, int chunk) {
+                                  float* __restrict__ red /*[N,2,C]*/, int H, int W, int C8, int up, int chunk, int relu) {
   extern __shared__ float sh[];
   const int c8 = threadIdx.x % C8;
   const int lane = threadIdx.x / C8;
@@ -452,7 +453,7 @@ __global__ void spade_bwd1_kernel(const uint4* __restrict__ x, const uint4* __re
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const float xh = (fx[k] - mu[k]) * rs[k];
-      const float g = fo[k] > 0.f ? fd[k] : 0.f;
+      const float g = (!relu || fo[k] > 0.f) ? fd[k] : 0.f;
       dg[k] = g * xh;
       db[k] = g;
       const float dxh = g * (1.f + fg[k]);
@@ -803,19 +804,20 @@ extern "C" int dei2i_bn_bwd(const void* x, const void* dy, void* dx, const float
 }
 
 extern "C" int dei2i_spade_fwd(const void* x, const void* gb, void* out, const float* stats, float* mean_rstd, int N, int H, int W,
-                               int C, int up, float eps, dei2i_stream stream) {
+                               int C, int up, int relu, float eps, dei2i_stream stream) {
   DEI2I_REQUIRE(x && gb && out && stats && mean_rstd && C % 8 == 0 && up >= 1 && H % up == 0 && W % up == 0, "spade_fwd: bad arguments");
   const long long per_img = (long long)H * W * (C / 8);
   unsigned bx = nblocks(per_img, 256 * 2);
   const unsigned cap = (148 * 16 + N - 1) / N;
   if (bx > cap) bx = cap;
   spade_fwd_kernel<<<dim3(bx, N), 256, 2 * C * sizeof(float), ST>>>((const uint4*)x, (const uint4*)gb, (uint4*)out, stats, mean_rstd,
-                                                                    N, H, W, C / 8, up, eps);
+                                                                    N, H, W, C / 8, up, relu, eps);
   return LAUNCH_OK("spade_fwd_kernel");
 }
 
 extern "C" int dei2i_spade_bwd(const void* x, const void* gb, const void* out, const void* dout, void* dgb, void* dx,
-                               const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, dei2i_stream stream) {
+                               const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, int relu,
+                               dei2i_stream stream) {
   DEI2I_REQUIRE(x && gb && out && dout && dgb && dx && mean_rstd && scratch && C % 8 == 0 && up >= 1, "spade_bwd: bad arguments");
   int threads, chunk;
   unsigned chunks;
@@ -825,7 +827,7 @@ extern "C" int dei2i_spade_bwd(const void* x, const void* gb, const void* out, c
   if (shmem > 48 * 1024)
     DEI2I_CUDA(cudaFuncSetAttribute(spade_bwd1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
   spade_bwd1_kernel<<<dim3(chunks, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)gb, (const uint4*)out, (const uint4*)dout,
-                                                             (uint4*)dgb, mean_rstd, scratch, H, W, C / 8, up, chunk);
+                                                             (uint4*)dgb, mean_rstd, scratch, H, W, C / 8, up, chunk, relu);
   if (int rc = LAUNCH_OK("spade_bwd1_kernel")) return rc;
   const long long per_img = (long long)(H / up) * (W / up) * (C / 8);
   unsigned bx = nblocks(per_img, 256 * 2);

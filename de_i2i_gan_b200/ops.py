@@ -92,7 +92,7 @@ def pack_weight(w: torch.Tensor, spec: ConvSpec, inv_sigma: torch.Tensor = None,
 
 
 def conv2d_fwd(x, w_fwd, spec: ConvSpec, bias=None, noise=None, noise_weight=None, residual=None, act=None,
-               out_fp32=False, logical_hw=None):
+               out_fp32=False, logical_hw=None, scale=None):
     """x: bf16 [N,Hs,Ws,Cin_ld]; logical_hw=(H,W) nearest-resizes x on the fly. Returns [N,Ho,Wo,Cout_ld]."""
     _chk_act(x, "x")
     n, hs, ws, c = x.shape
@@ -107,12 +107,12 @@ def conv2d_fwd(x, w_fwd, spec: ConvSpec, bias=None, noise=None, noise_weight=Non
         _chk_f32(noise, "noise")
         assert noise.numel() == n * ho * wo
     g = spec.geom(n, h, w, hs, ws)
-    e = ConvEpilogue(_p(bias), _p(noise), _p(noise_weight), _p(residual), ACT[act], int(out_fp32))
+    e = ConvEpilogue(_p(scale), _p(bias), _p(noise), _p(noise_weight), _p(residual), ACT[act], int(out_fp32))
     check(_lib.load().dei2i_conv2d_fwd(_p(x), _p(w_fwd), _p(y), C.byref(g), C.byref(e), _stream()), "dei2i_conv2d_fwd")
     return y
 
 
-def conv2d_dgrad(dy, w_dgrad, spec: ConvSpec, in_hw):
+def conv2d_dgrad(dy, w_dgrad, spec: ConvSpec, in_hw, scale=None):
     """dy: bf16 [N,Ho,Wo,Cout_ld] -> dx bf16 [N,H,W,Cin_ld] (reflect padding folded back)."""
     _chk_act(dy, "dy")
     n = dy.shape[0]
@@ -123,12 +123,12 @@ def conv2d_dgrad(dy, w_dgrad, spec: ConvSpec, in_hw):
     if spec.pad_mode == "reflect" and spec.pad > 0:
         p = spec.pad
         dxp = torch.empty(n, h + 2 * p, w + 2 * p, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
-        check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dxp), C.byref(g), 0, _stream()), "dei2i_conv2d_dgrad")
+        check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dxp), C.byref(g), _p(scale), 0, _stream()), "dei2i_conv2d_dgrad")
         dx = torch.empty(n, h, w, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
         check(lib.dei2i_reflect_fold(_p(dxp), _p(dx), n, h, w, spec.cin_ld, p, _stream()), "dei2i_reflect_fold")
         return dx
     dx = torch.empty(n, h, w, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
-    check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dx), C.byref(g), 0, _stream()), "dei2i_conv2d_dgrad")
+    check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dx), C.byref(g), _p(scale), 0, _stream()), "dei2i_conv2d_dgrad")
     return dx
 
 
@@ -221,7 +221,7 @@ def bn_bwd(x, dy, gamma, beta, save, training, act=None):
     return dx, dgb[0], dgb[1]
 
 
-def spade_fwd(x, gb, up: int = 1, eps: float = 1e-5):
+def spade_fwd(x, gb, up: int = 1, relu: bool = True, eps: float = 1e-5):
     """x: [N,H/up,W/up,C]; gb: [N,H,W,2C] -> out [N,H,W,C] = relu(IN(x)*(1+gamma)+beta); also returns mean_rstd."""
     _chk_act(x, "x")
     _chk_act(gb, "gb")
@@ -231,18 +231,18 @@ def spade_fwd(x, gb, up: int = 1, eps: float = 1e-5):
     stats = channel_stats(x, True)
     out = torch.empty(n, h, w, c, dtype=torch.bfloat16, device=x.device)
     mr = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
-    check(_lib.load().dei2i_spade_fwd(_p(x), _p(gb), _p(out), _p(stats), _p(mr), n, h, w, c, up, eps, _stream()),
+    check(_lib.load().dei2i_spade_fwd(_p(x), _p(gb), _p(out), _p(stats), _p(mr), n, h, w, c, up, int(relu), eps, _stream()),
           "dei2i_spade_fwd")
     return out, mr
 
 
-def spade_bwd(x, gb, out, dout, mean_rstd, up: int = 1):
+def spade_bwd(x, gb, out, dout, mean_rstd, up: int = 1, relu: bool = True):
     n, h, w, c = out.shape
     dgb = torch.empty_like(gb)
     dx = torch.empty_like(x)
     scratch = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
     check(_lib.load().dei2i_spade_bwd(_p(x), _p(gb), _p(out), _p(dout), _p(dgb), _p(dx), _p(mean_rstd), _p(scratch), n, h, w,
-                                      c, up, _stream()), "dei2i_spade_bwd")
+                                      c, up, int(relu), _stream()), "dei2i_spade_bwd")
     return dgb, dx
 
 

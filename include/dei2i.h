@@ -48,6 +48,8 @@ typedef struct dei2i_conv_geom {
 } dei2i_conv_geom;
 
 typedef struct dei2i_conv_epilogue {
+  const float* scale;        /* device scalar multiplying the accumulator first (1/sigma of spectral norm, so the packed
+                                weights stay those of W_orig and need no re-packing per forward) or NULL */
   const float* bias;         /* [Cout] or NULL (SPADE convs, normalization.py:17-22) */
   const float* noise;        /* [N*Ho*Wo] N(0,1) samples or NULL: NoiseInjection, architecture.py:385-389 */
   const float* noise_weight; /* device scalar; required when noise != NULL */
@@ -64,7 +66,7 @@ typedef struct dei2i_conv_epilogue {
 int dei2i_pack_weight(const float* w, const float* inv_sigma, int Cout, int Cin_real, int kh, int kw, int Cin,
                       int Cout_ld, void* w_fwd, void* w_dgrad, dei2i_stream stream);
 
-/* y = act(conv(x) + bias + noise_weight*noise) + residual          (nn.Conv2d forward + fused followers) */
+/* y = act(scale*conv(x) + bias + noise_weight*noise) + residual    (nn.Conv2d forward + fused followers) */
 int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const dei2i_conv_geom* g,
                      const dei2i_conv_epilogue* e, dei2i_stream stream);
 
@@ -72,9 +74,10 @@ int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const dei2i_conv
  * dy: bf16 [N,Ho,Wo,Cout_ld].  pad_mode zeros:   dx is [N,H,W,Cin].
  *                              pad_mode reflect: dx is over the PADDED domain [N,H+2p,W+2p,Cin]; fold it with
  *                              dei2i_reflect_fold (the backward of F.pad(mode='reflect')).
- * The output pitch is Cin; out_fp32 selects fp32 / bf16.  Resized inputs (Hs != H) are not supported here. */
-int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx, const dei2i_conv_geom* g, int out_fp32,
-                       dei2i_stream stream);
+ * The output pitch is Cin; out_fp32 selects fp32 / bf16; scale (device scalar or NULL) multiplies the result.
+ * Resized inputs (Hs != H) are not supported here. */
+int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx, const dei2i_conv_geom* g, const float* scale,
+                       int out_fp32, dei2i_stream stream);
 /* dx[n,h,w,c] = sum of dxp over all padded positions that reflect onto (h,w); bf16 in / bf16 out */
 int dei2i_reflect_fold(const void* dxp, void* dx, int N, int H, int W, int C, int pad, dei2i_stream stream);
 
@@ -118,14 +121,15 @@ int dei2i_bn_bwd(const void* x, const void* dy, void* dx, const float* gamma, co
                  int act, dei2i_stream stream);
 
 /* SPADE modulation (normalization.py:24-37) + ReLU (architecture.py:244,347-348), optional 2x nearest up-sampling
- * of x (architecture.py:242): out = relu(IN(x) * (1 + gamma) + beta), gamma/beta = first/second C columns of `gb`
+ * of x (architecture.py:242): out = [relu](IN(x) * (1 + gamma) + beta), gamma/beta = first/second C columns of `gb`
  * (bf16 [N,H,W,2C], output of the fused gamma|beta convolution).  x is [N,H/up,W/up,C].
  * stats from dei2i_channel_stats(per_sample=1) on x; writes mean_rstd fp32 [N,2,C] for the backward. */
 int dei2i_spade_fwd(const void* x, const void* gb, void* out, const float* stats, float* mean_rstd, int N, int H,
-                    int W, int C, int up, float eps, dei2i_stream stream);
+                    int W, int C, int up, int relu, float eps, dei2i_stream stream);
 /* backward: dgb (bf16 [N,H,W,2C]) and dx (bf16 [N,H/up,W/up,C]); scratch fp32 [N,2,C]. */
 int dei2i_spade_bwd(const void* x, const void* gb, const void* out, const void* dout, void* dgb, void* dx,
-                    const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, dei2i_stream stream);
+                    const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, int relu,
+                    dei2i_stream stream);
 
 /* act backward for fused conv epilogues: dx = dy * act'(y) computed from the saved OUTPUT y (bf16);
  * bias_grad (fp32 [C], may be NULL) receives sum over pixels of dx. */

@@ -1,0 +1,318 @@
+"""torch.autograd.Function wrappers that put the CUDA kernels behind PyTorch's autograd graph.
+
+PyTorch only provides the graph, device memory and streams; every forward and backward body calls libdei2i.so.
+Activations travel between blocks as ``Nhwc`` carriers (BF16 [N,H,W,C_ld] + real channel count); NCHW FP32 exists
+only at the model edge (images, logits, losses), exactly where the reference's L2 code touches tensors.
+"""
+from contextlib import contextmanager
+from typing import Optional
+
+import torch
+from torch.autograd import Function
+
+from . import ops
+from .ops import ConvSpec
+
+
+class Nhwc:
+    """BF16 NHWC activation carrier. ``t``: [N,H,W,C_ld] (C_ld % 8 == 0), ``c``: real channels."""
+    __slots__ = ("t", "c")
+
+    def __init__(self, t: torch.Tensor, c: int):
+        self.t, self.c = t, c
+
+    @property
+    def shape(self):  # logical NCHW shape, like the reference's tensors
+        n, h, w, _ = self.t.shape
+        return (n, self.c, h, w)
+
+
+# ------------------------------------------------------------------------------------------------ weight preparation
+_cache = None  # dict while inside weight_cache(), else None
+
+
+@contextmanager
+def weight_cache():
+    """Inside this scope packed BF16 weights are built once per parameter tensor (weights do not change within one
+    loss computation: 4 G + 2 D passes of a G-step share them).  Spectral-norm state is never cached."""
+    global _cache
+    outer = _cache
+    if outer is None:
+        _cache = {}
+    try:
+        yield
+    finally:
+        if outer is None:
+            _cache = None
+
+
+class Weights:
+    __slots__ = ("w_fwd", "w_dgrad", "scale", "sn")
+
+    def __init__(self, w_fwd, w_dgrad, scale, sn):
+        self.w_fwd, self.w_dgrad, self.scale, self.sn = w_fwd, w_dgrad, scale, sn
+
+
+def _pack(w: torch.Tensor, spec: ConvSpec):
+    key = (w.data_ptr(), tuple(w.shape), spec)
+    if _cache is not None and key in _cache:
+        return _cache[key]
+    packed = ops.pack_weight(w.detach().contiguous(), spec, None, True)
+    if _cache is not None:
+        _cache[key] = packed
+    return packed
+
+
+def prepare_conv(conv: torch.nn.Module, spec: ConvSpec, training: bool) -> Weights:
+    """Spectral norm (one power iteration when training, torch.nn.utils.spectral_norm semantics: u, v updated in place
+    per forward call, sigma from the updated vectors) + packed weights of W_orig; 1/sigma is applied in the conv epilogue."""
+    if hasattr(conv, "weight_orig"):
+        w = conv.weight_orig
+        with torch.no_grad():
+            inv = ops.spectral_norm(w.detach(), conv.weight_u, conv.weight_v, training)
+            sn = (w.detach(), conv.weight_u.clone(), conv.weight_v.clone(), inv)
+        w_fwd, w_dg = _pack(w, spec)
+        return Weights(w_fwd, w_dg, inv, sn)
+    w_fwd, w_dg = _pack(conv.weight, spec)
+    return Weights(w_fwd, w_dg, None, None)
+
+
+def conv_param(conv: torch.nn.Module) -> torch.Tensor:
+    return conv.weight_orig if hasattr(conv, "weight_orig") else conv.weight
+
+
+# ------------------------------------------------------------------------------------------------ Functions
+class _ToNhwc(Function):
+    @staticmethod
+    def forward(ctx, x):
+        ctx.c = x.shape[1]
+        return ops.nchw_to_nhwc(x.contiguous().float())
+
+    @staticmethod
+    def backward(ctx, g):
+        return ops.nhwc_to_nchw(g.contiguous(), ctx.c)
+
+
+class _FromNhwc(Function):
+    @staticmethod
+    def forward(ctx, t, c):
+        ctx.c_ld = t.shape[3]
+        return ops.nhwc_to_nchw(t, c)
+
+    @staticmethod
+    def backward(ctx, g):
+        return ops.nchw_to_nhwc(g.contiguous(), ctx.c_ld), None
+
+
+def to_nhwc(x) -> Nhwc:
+    if isinstance(x, Nhwc):
+        return x
+    return Nhwc(_ToNhwc.apply(x), x.shape[1])
+
+
+def from_nhwc(a: Nhwc) -> torch.Tensor:
+    return _FromNhwc.apply(a.t, a.c)
+
+
+class _Conv(Function):
+    """y = act(scale*conv(x) + bias + noise_w*noise) + residual   and its dgrad / wgrad / bias / noise-weight grads."""
+
+    @staticmethod
+    def forward(ctx, x, w_param, bias, noise_w, residual, wts: Weights, spec: ConvSpec, act, noise, out_fp32, logical_hw):
+        assert not (act and residual is not None), "activation mask cannot be recovered once a residual is added"
+        y = ops.conv2d_fwd(x, wts.w_fwd, spec, bias=bias, noise=noise, noise_weight=noise_w, residual=residual, act=act,
+                           out_fp32=out_fp32, logical_hw=logical_hw, scale=wts.scale)
+        ctx.wts, ctx.spec, ctx.act, ctx.noise, ctx.logical_hw = wts, spec, act, noise, logical_hw
+        ctx.has = (bias is not None, noise_w is not None, residual is not None)
+        ctx.save_for_backward(x, y if act else None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, y = ctx.saved_tensors
+        wts, spec = ctx.wts, ctx.spec
+        has_bias, has_noise, has_res = ctx.has
+        if dy.dtype != torch.bfloat16:
+            dy = dy.to(torch.bfloat16)
+        dy = dy.contiguous()
+        d_res = dy if (has_res and ctx.needs_input_grad[4]) else None
+        d_bias = None
+        need_bias = has_bias and ctx.needs_input_grad[2]
+        if ctx.act or need_bias:
+            yb = y if (y is None or y.dtype == torch.bfloat16) else y.to(torch.bfloat16)
+            dz, d_bias = ops.act_bwd(yb, dy, ctx.act, want_dx=bool(ctx.act), want_bias_grad=need_bias)
+            if ctx.act:
+                dy = dz
+            if d_bias is not None:
+                d_bias = d_bias[: spec.cout]
+        d_nw = None
+        if has_noise and ctx.needs_input_grad[3]:
+            d_nw = ops.noise_wgrad(dy, ctx.noise, torch.empty(1, device=dy.device), spec.cout).reshape(1, 1, 1, 1)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            assert ctx.logical_hw is None, "no input gradient through a resized (label map) input"
+            dx = ops.conv2d_dgrad(dy, wts.w_dgrad, spec, (x.shape[1], x.shape[2]), scale=wts.scale)
+        dw = None
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty(spec.cout, spec.cin, spec.kh, spec.kw_, dtype=torch.float32, device=dy.device)
+            ops.conv2d_wgrad(x, dy, dw, spec, sn=wts.sn, logical_hw=ctx.logical_hw)
+        return dx, dw, d_bias, d_nw, d_res, None, None, None, None, None, None
+
+
+def conv(x: Nhwc, conv_mod, spec: ConvSpec, training: bool, bias=None, act=None, noise=None, noise_w=None,
+         residual: Optional[Nhwc] = None, out_fp32=False, logical_hw=None, wts: Weights = None) -> Nhwc:
+    wts = wts or prepare_conv(conv_mod, spec, training)
+    y = _Conv.apply(x.t, conv_param(conv_mod), bias, noise_w, residual.t if residual is not None else None, wts, spec, act,
+                    noise, out_fp32, logical_hw)
+    return Nhwc(y, spec.cout)
+
+
+class _ConvCat(Function):
+    """Two convolutions sharing their input fused into one GEMM with N = Cout_a + Cout_b (SPADE gamma|beta,
+    normalization.py:31-32; generator heads, generator.py:268-269).  Parameters stay separate tensors."""
+
+    @staticmethod
+    def forward(ctx, x, wa, wb, ba, bb, spec: ConvSpec, out_fp32):
+        w_fwd, w_dg = _pack_cat(wa, wb, spec)
+        bias = torch.cat([ba.detach(), bb.detach()]) if ba is not None else None
+        y = ops.conv2d_fwd(x, w_fwd, spec, bias=bias, out_fp32=out_fp32)
+        ctx.spec, ctx.w_dg, ctx.ca, ctx.has_bias = spec, w_dg, wa.shape[0], ba is not None
+        ctx.save_for_backward(x)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (x,) = ctx.saved_tensors
+        spec, ca = ctx.spec, ctx.ca
+        if dy.dtype != torch.bfloat16:
+            dy = dy.to(torch.bfloat16)
+        dy = dy.contiguous()
+        dba = dbb = None
+        if ctx.has_bias:
+            _, db = ops.act_bwd(None, dy, None, want_dx=False, want_bias_grad=True)
+            dba, dbb = db[:ca], db[ca: spec.cout]
+        dx = ops.conv2d_dgrad(dy, ctx.w_dg, spec, (x.shape[1], x.shape[2])) if ctx.needs_input_grad[0] else None
+        dw = torch.empty(spec.cout, spec.cin, spec.kh, spec.kw_, dtype=torch.float32, device=dy.device)
+        ops.conv2d_wgrad(x, dy, dw, spec)
+        return dx, dw[:ca], dw[ca:], dba, dbb, None, None
+
+
+def _pack_cat(wa, wb, spec):
+    key = (wa.data_ptr(), wb.data_ptr(), spec)
+    if _cache is not None and key in _cache:
+        return _cache[key]
+    packed = ops.pack_weight(torch.cat([wa.detach(), wb.detach()], 0).contiguous(), spec, None, True)
+    if _cache is not None:
+        _cache[key] = packed
+    return packed
+
+
+def conv_cat(x: Nhwc, conv_a, conv_b, spec: ConvSpec, out_fp32=False) -> Nhwc:
+    y = _ConvCat.apply(x.t, conv_a.weight, conv_b.weight, conv_a.bias, conv_b.bias, spec, out_fp32)
+    return Nhwc(y, spec.cout)
+
+
+class _BatchNorm(Function):
+    @staticmethod
+    def forward(ctx, x, gamma, beta, residual, bn, training, act):
+        y, save = ops.bn_fwd(x, gamma.detach(), beta.detach(), bn.running_mean, bn.running_var, training, act=act,
+                             residual=residual, momentum=bn.momentum if bn.momentum is not None else 0.1, eps=bn.eps)
+        if training and bn.num_batches_tracked is not None:
+            bn.num_batches_tracked += 1
+        ctx.training, ctx.act, ctx.has_res = training, act, residual is not None
+        ctx.save_for_backward(x, gamma, beta, save)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, gamma, beta, save = ctx.saved_tensors
+        dy = dy.contiguous()
+        dx, dg, db = ops.bn_bwd(x, dy, gamma.detach(), beta.detach(), save, ctx.training, act=ctx.act)
+        return dx, dg, db, (dy if ctx.has_res else None), None, None, None
+
+
+def batch_norm(x: Nhwc, bn: torch.nn.BatchNorm2d, act=None, residual: Optional[Nhwc] = None) -> Nhwc:
+    training = bn.training or not bn.track_running_stats
+    y = _BatchNorm.apply(x.t, bn.weight, bn.bias, residual.t if residual is not None else None, bn, training, act)
+    return Nhwc(y, x.c)
+
+
+class _Spade(Function):
+    @staticmethod
+    def forward(ctx, x, gb, up, relu, eps):
+        out, mr = ops.spade_fwd(x, gb, up, relu, eps)
+        ctx.up, ctx.relu = up, relu
+        ctx.save_for_backward(x, gb, out, mr)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, gb, out, mr = ctx.saved_tensors
+        dgb, dx = ops.spade_bwd(x, gb, out, dout.contiguous(), mr, ctx.up, ctx.relu)
+        return dx, dgb, None, None, None
+
+
+def spade_modulate(x: Nhwc, gb: Nhwc, up=1, relu=True, eps=1e-5) -> Nhwc:
+    return Nhwc(_Spade.apply(x.t, gb.t, up, relu, eps), x.c)
+
+
+class _Compose(Function):
+    @staticmethod
+    def forward(ctx, hd, x, cycle_gan):
+        out, prob, _ = ops.compose_fwd(hd, x, cycle_gan, want_nhwc=False)
+        ctx.cycle = cycle_gan
+        ctx.save_for_backward(hd, x)
+        return out, prob
+
+    @staticmethod
+    def backward(ctx, dout, dprob):
+        hd, x = ctx.saved_tensors
+        dhd, dx = ops.compose_bwd(hd, x, dout.contiguous() if dout is not None else None,
+                                  dprob.contiguous() if dprob is not None else None, ctx.cycle, ctx.needs_input_grad[1])
+        return dhd.float(), dx, None
+
+
+def compose(hd: torch.Tensor, x: torch.Tensor, cycle_gan: bool):
+    return _Compose.apply(hd, x.contiguous().float(), cycle_gan)
+
+
+class _BceLogits(Function):
+    @staticmethod
+    def forward(ctx, logits, targets):
+        z = logits.contiguous().float()
+        if isinstance(targets, (int, float)):
+            loss, grad = ops.bce_logits(z, None, float(targets))
+        else:
+            loss, grad = ops.bce_logits(z, targets.contiguous().float())
+        ctx.save_for_backward(grad)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (grad,) = ctx.saved_tensors
+        return grad * g, None
+
+
+class _L1(Function):
+    @staticmethod
+    def forward(ctx, a, b):
+        a = a.contiguous().float()
+        ga = torch.empty_like(a) if ctx.needs_input_grad[0] else None
+        gb = torch.empty_like(a) if (b is not None and ctx.needs_input_grad[1]) else None
+        loss = ops.l1(a, b.contiguous().float() if b is not None else None, ga, gb)
+        ctx.save_for_backward(ga, gb)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        ga, gb = ctx.saved_tensors
+        return (ga * g if ga is not None else None), (gb * g if gb is not None else None)
+
+
+def bce_with_logits(logits, targets):
+    """binary_cross_entropy_with_logits(mean). ``targets``: tensor or python scalar (all-ones / all-zeros labels)."""
+    return _BceLogits.apply(logits, targets)
+
+
+def l1_loss(a, b=None):
+    return _L1.apply(a, b)

@@ -1,0 +1,315 @@
+"""Building blocks of the DefectGAN networks on the sm_100a kernels.
+
+Mirror of /root/reference/defectGAN/models/networks/architecture.py: same class names, constructor signatures,
+sub-module names and registration order (=> identical ``state_dict`` keys, ``init_weights`` RNG order and optimizer
+parameter order).  ``nn.Conv2d`` / ``nn.BatchNorm2d`` / ``spectral_norm`` objects are kept as parameter containers;
+every ``forward`` body runs the fused CUDA path through ``de_i2i_gan_b200.functional``.
+
+Every block accepts either a plain NCHW tensor (drop-in use: converted at the block edge, result returned as NCHW
+FP32) or an ``Nhwc`` carrier (how the networks chain blocks without layout round trips).
+"""
+import logging
+
+import torch
+from torch import nn
+from torch.nn.utils import spectral_norm  # old hook API, as the reference (architecture.py:7)
+
+from ... import functional as Fn
+from ...ops import ConvSpec
+from .normalization import SPADE
+
+_ACT_NAMES = {nn.LeakyReLU: "leaky_relu", nn.ReLU: "relu", nn.Sigmoid: "sigmoid", nn.Tanh: "tanh", nn.Identity: None}
+
+
+def get_act_layer(act_str):
+    """architecture.py:12-26."""
+    if act_str == "leaky_relu":
+        return nn.LeakyReLU(0.2, inplace=True)
+    if act_str == "relu":
+        return nn.ReLU(inplace=True)
+    if act_str == "sigmoid":
+        return nn.Sigmoid()
+    if act_str == "tanh":
+        return nn.Tanh()
+    if act_str is None:
+        logging.info("create conv block without activation layer")
+        return nn.Identity()
+    raise NameError(f"activation layer named {act_str} not defined")
+
+
+def _first(v):
+    return v[0] if isinstance(v, (tuple, list)) else v
+
+
+def _spec_of(conv: nn.Conv2d) -> ConvSpec:
+    """ConvSpec from an nn.Conv2d container (kernel, stride, padding incl. 'same'/'valid', padding_mode)."""
+    kh, kw = conv.kernel_size
+    pad = conv.padding
+    if isinstance(pad, str):
+        if pad == "same":
+            if kh % 2 == 0 or kw % 2 == 0:
+                raise NotImplementedError("asymmetric 'same' padding of even kernels (WGAN generator) is not on this path yet")
+            pad = (kh - 1) // 2
+        else:
+            pad = 0
+    else:
+        pad = _first(pad)
+    if conv.padding_mode not in ("zeros", "reflect"):
+        raise NotImplementedError(f"padding_mode {conv.padding_mode}")
+    if conv.groups != 1 or _first(conv.dilation) != 1:
+        raise NotImplementedError("grouped / dilated convolutions")
+    return ConvSpec(conv.in_channels, conv.out_channels, kh, _first(conv.stride), pad, conv.padding_mode, kw if kw != kh else 0)
+
+
+# ---------------------------------------------------------------------------------------------- noise
+_noise_source = None
+
+
+def set_noise_source(fn):
+    """Test hook: ``fn(n, h, w, device) -> fp32 [n,1,h,w]`` replaces the torch RNG draw (None restores it)."""
+    global _noise_source
+    _noise_source = fn
+
+
+def draw_noise(n, h, w, device):
+    """Same call, shape and order as the reference (architecture.py:387-388): one N(0,1) map per sample."""
+    if _noise_source is not None:
+        return _noise_source(n, h, w, device).to(device=device, dtype=torch.float32).contiguous()
+    return torch.empty(n, 1, h, w, device=device, dtype=torch.float32).normal_()
+
+
+class NoiseInjection(nn.Module):
+    """architecture.py:374-389.  Inside the blocks the addition is fused into the conv epilogue; a stand-alone call on a
+    plain tensor is the literal formula."""
+
+    def __init__(self, weight_type="constant", nc=None):
+        super().__init__()
+        if weight_type == "constant":
+            self.weight = nn.Parameter(torch.zeros(1, 1, 1, 1))
+        elif weight_type == "vector":
+            raise NotImplementedError("per-channel noise weights are not used by DefectGAN and not on the CUDA path")
+        else:
+            raise NameError(f"weight type named {weight_type} not defined")
+
+    def forward(self, image, noise=None):
+        if noise is None:
+            b, _, h, w = image.shape
+            noise = draw_noise(b, h, w, image.device)
+        return image + self.weight * noise
+
+
+def _noise_args(noise_mod, n, h, w, device):
+    if isinstance(noise_mod, NoiseInjection):
+        return draw_noise(n, h, w, device), noise_mod.weight
+    return None, None
+
+
+# ---------------------------------------------------------------------------------------------- blocks
+def _apply_sn(blocks, use_spectral):
+    if use_spectral:
+        for i, layer in enumerate(blocks):
+            if isinstance(layer, (nn.Conv2d, nn.Linear)):
+                blocks[i] = spectral_norm(layer)
+
+
+class ConvBlock(nn.Module):
+    """architecture.py:79-118: [spectral] Conv2d -> [BatchNorm2d] -> activation."""
+
+    def __init__(self, f_in, f_out, kernel_size=(3, 3), stride=(1, 1), padding=0, padding_mode="zeros", bias=False,
+                 norm_layer=None, act_layer=None, use_spectral=False):
+        super().__init__()
+        blocks = [nn.Conv2d(f_in, f_out, kernel_size=kernel_size, stride=stride, padding=padding,
+                            padding_mode=padding_mode, bias=bias)]
+        if norm_layer is not None:
+            blocks.append(norm_layer(f_out))
+        blocks.append(get_act_layer(act_layer))
+        _apply_sn(blocks, use_spectral)
+        self.conv_block = nn.Sequential(*blocks)
+        self._spec = _spec_of(self.conv_block[0])
+        self._act = act_layer
+        self._has_norm = norm_layer is not None
+        if self._has_norm and not isinstance(self.conv_block[1], nn.BatchNorm2d):
+            raise NotImplementedError("ConvBlock on the CUDA path supports norm_layer in (None, nn.BatchNorm2d)")
+
+    @property
+    def _norm(self):  # not an attribute: registering the sub-module twice would duplicate its state-dict keys
+        return self.conv_block[1] if self._has_norm else None
+
+    def forward(self, x, seg=None, residual=None):
+        plain = not isinstance(x, Fn.Nhwc)
+        xa = Fn.to_nhwc(x)
+        conv = self.conv_block[0]
+        if self._norm is None:
+            assert residual is None
+            y = Fn.conv(xa, conv, self._spec, conv.training, bias=conv.bias, act=self._act,
+                        out_fp32=self._act in ("tanh", "sigmoid"))
+            if y.t.dtype != torch.bfloat16 and not plain:
+                y = Fn.Nhwc(y.t.to(torch.bfloat16), y.c)
+        else:
+            y = Fn.conv(xa, conv, self._spec, conv.training, bias=conv.bias)
+            y = Fn.batch_norm(y, self._norm, act=self._act, residual=residual)
+        return _edge(y) if plain else y
+
+
+def _edge(y: Fn.Nhwc) -> torch.Tensor:
+    if y.t.dtype == torch.float32:
+        return y.t[..., : y.c].permute(0, 3, 1, 2).contiguous()
+    return Fn.from_nhwc(y)
+
+
+class DeConvBlock(nn.Module):
+    """architecture.py:29-76: [Upsample] -> Conv2d -> [NoiseInjection] -> [norm] -> activation.  DefectGAN uses it for
+    the two generator heads only (no up-sampling, noise or norm: generator.py:224-241)."""
+
+    def __init__(self, f_in, f_out, kernel_size=(3, 3), stride=(1, 1), padding=0, padding_mode="zeros", bias=False,
+                 up_scale=True, norm_layer=None, act_layer=None, use_spectral=False, add_noise=False):
+        super().__init__()
+        blocks = []
+        if up_scale:
+            blocks.append(nn.Upsample(scale_factor=2))
+        blocks.append(nn.Conv2d(f_in, f_out, kernel_size=kernel_size, stride=stride, padding=padding,
+                                padding_mode=padding_mode, bias=bias))
+        if add_noise:
+            blocks.append(NoiseInjection())
+        if norm_layer is not None:
+            blocks.append(norm_layer(f_out))
+        blocks.append(get_act_layer(act_layer))
+        _apply_sn(blocks, use_spectral)
+        self.de_conv_block = nn.Sequential(*blocks)
+        self._act = act_layer
+        self._conv_idx = next(i for i, m in enumerate(self.de_conv_block) if isinstance(m, nn.Conv2d))
+        self._simple = not (up_scale or add_noise or norm_layer is not None)
+        self._spec = _spec_of(self._conv) if self._simple else None
+
+    @property
+    def _conv(self):
+        return self.de_conv_block[self._conv_idx]
+
+    def forward(self, x, seg=None):
+        if not self._simple:
+            raise NotImplementedError("DeConvBlock with up-sampling / noise / norm (WGAN generator) is not on the CUDA path yet")
+        plain = not isinstance(x, Fn.Nhwc)
+        y = Fn.conv(Fn.to_nhwc(x), self._conv, self._spec, self._conv.training, bias=self._conv.bias, act=self._act,
+                    out_fp32=True)
+        return _edge(y) if plain else y
+
+
+class ResBlock(nn.Module):
+    """architecture.py:121-176 (down_scale=False as used by DefectGAN, generator.py:118-126):
+    x + ConvBlock(act=None)(ConvBlock(act)(x)); the residual add is fused into the second BatchNorm kernel."""
+
+    def __init__(self, f_in, f_out, kernel_size=(3, 3), stride=(1, 1), padding=0, padding_mode="zeros", bias=False,
+                 norm_layer=nn.InstanceNorm2d, act_layer="relu", use_spectral=False, down_scale=False):
+        super().__init__()
+        if down_scale:
+            raise NotImplementedError("ResBlock(down_scale=True) is not used by DefectGAN and not on the CUDA path")
+        if norm_layer is None:
+            raise NotImplementedError("ResBlock without a norm layer")
+        self.down_scale = down_scale
+        blocks = [ConvBlock(f_in, f_in, kernel_size=kernel_size, stride=stride, padding=padding, padding_mode=padding_mode,
+                            bias=bias, norm_layer=norm_layer, act_layer=act_layer, use_spectral=use_spectral),
+                  ConvBlock(f_in, f_out, kernel_size=kernel_size, stride=stride, padding=padding, padding_mode=padding_mode,
+                            bias=bias, norm_layer=norm_layer, act_layer=None, use_spectral=use_spectral)]
+        self.res_block = nn.Sequential(*blocks)
+
+    def forward(self, x, seg=None):
+        plain = not isinstance(x, Fn.Nhwc)
+        xa = Fn.to_nhwc(x)
+        y = self.res_block[0](xa)
+        y = self.res_block[1](y, residual=xa)
+        return Fn.from_nhwc(y) if plain else y
+
+
+def _style_norm(kind, label_nc, nc, hidden_nc, kernel_size, padding, norm_layer):
+    if kind == "spade":
+        return SPADE(label_nc, nc, hidden_nc=hidden_nc, kernel_size=kernel_size, padding=padding, norm_layer=norm_layer)
+    if kind in ("sean", "adain"):
+        raise NotImplementedError(f"style_norm_block_type={kind!r}: only the SPADE variant is on the CUDA hot path (SURVEY 8f, next)")
+    raise ValueError(f"Unknown style norm block type: {kind}")
+
+
+class NormConvBlock(nn.Module):
+    """architecture.py:179-257: noise(conv(act(SPADE(up2x(x))))) - the 2x nearest up-sampling and the ReLU are fused
+    into the SPADE modulation kernel, the noise into the conv epilogue."""
+
+    def __init__(self, style_norm_block_type, hidden_nc, label_nc, f_in, f_out, style_distill=False, embed_nc=None,
+                 kernel_size=(3, 3), stride=(1, 1), padding=0, padding_mode="zeros", bias=False, up_scale=False,
+                 norm_layer=nn.InstanceNorm2d, act_layer="relu", use_spectral=False, add_noise=False):
+        super().__init__()
+        self.up = nn.Upsample(scale_factor=2) if up_scale else nn.Identity()
+        self.noise = NoiseInjection() if add_noise else nn.Identity()
+        self.style_norm_block_type = style_norm_block_type
+        self.norm = _style_norm(style_norm_block_type, label_nc, f_in, hidden_nc, (3, 3), padding, norm_layer)
+        self.conv = nn.Conv2d(f_in, f_out, kernel_size=kernel_size, stride=stride, padding=padding,
+                              padding_mode=padding_mode, bias=bias)
+        self.act = get_act_layer(act_layer)
+        if use_spectral:
+            self.conv = spectral_norm(self.conv)
+        self._spec = _spec_of(self.conv)
+        self._up = 2 if up_scale else 1
+        if act_layer not in ("relu", None):
+            raise NotImplementedError("NormConvBlock on the CUDA path fuses ReLU (or no activation) into the SPADE kernel")
+        self._relu = act_layer == "relu"
+
+    def forward(self, x, labels, style_feat=None):
+        plain = not isinstance(x, Fn.Nhwc)
+        xa = Fn.to_nhwc(x)
+        s = self.norm(xa, labels, up=self._up, relu=self._relu)
+        n, _, h, w = s.shape
+        ho, wo = self._spec.out_hw(h, w)
+        noise, nw = _noise_args(self.noise, n, ho, wo, s.t.device)
+        y = Fn.conv(s, self.conv, self._spec, self.conv.training, bias=self.conv.bias, noise=noise, noise_w=nw)
+        return Fn.from_nhwc(y) if plain else y
+
+    def update_alpha(self, epoch, num_epochs):
+        pass
+
+
+class NormResBlock(nn.Module):
+    """architecture.py:260-371 with up_scale=False (generator.py:143-155): identity shortcut; ``norm_s`` / ``conv_s``
+    are constructed (state-dict parity) but, exactly as in the reference, never executed."""
+
+    def __init__(self, style_norm_block_type, hidden_nc, label_nc, f_in, f_out, style_distill=False, embed_nc=None,
+                 kernel_size=(3, 3), stride=(1, 1), padding=0, padding_mode="zeros", bias=False, up_scale=False,
+                 norm_layer=nn.InstanceNorm2d, act_layer="relu", use_spectral=False, add_noise=False):
+        super().__init__()
+        if up_scale:
+            raise NotImplementedError("NormResBlock(up_scale=True) is not used by DefectGAN and not on the CUDA path")
+        self.up = nn.Upsample(scale_factor=2)
+        self.up_scale = up_scale
+        self.noise_0 = NoiseInjection() if add_noise else nn.Identity()
+        self.noise_1 = NoiseInjection() if add_noise else nn.Identity()
+        f_mid = min(f_in, f_out)
+        self.style_norm_block_type = style_norm_block_type
+        self.norm_0 = _style_norm(style_norm_block_type, label_nc, f_in, hidden_nc, kernel_size, padding, norm_layer)
+        self.norm_1 = _style_norm(style_norm_block_type, label_nc, f_mid, hidden_nc, kernel_size, padding, norm_layer)
+        self.norm_s = _style_norm(style_norm_block_type, label_nc, f_in, hidden_nc, kernel_size, padding, norm_layer)
+        self.act = get_act_layer(act_layer)
+        mk = lambda a, b: nn.Conv2d(a, b, kernel_size=kernel_size, stride=stride, padding=padding,  # noqa: E731
+                                    padding_mode=padding_mode, bias=bias)
+        self.conv_0, self.conv_1, self.conv_s = mk(f_in, f_mid), mk(f_mid, f_out), mk(f_in, f_out)
+        if use_spectral:
+            self.conv_0 = spectral_norm(self.conv_0)
+            self.conv_1 = spectral_norm(self.conv_1)
+            self.conv_s = spectral_norm(self.conv_s)
+        self._spec0, self._spec1 = _spec_of(self.conv_0), _spec_of(self.conv_1)
+        if act_layer not in ("relu", None):
+            raise NotImplementedError("NormResBlock on the CUDA path fuses ReLU (or no activation) into the SPADE kernel")
+        self._relu = act_layer == "relu"
+
+    def forward(self, x, labels, style_feat=None):
+        plain = not isinstance(x, Fn.Nhwc)
+        xa = Fn.to_nhwc(x)
+        n, _, h, w = xa.shape
+        dev = xa.t.device
+        s = self.norm_0(xa, labels, relu=self._relu)
+        noise, nw = _noise_args(self.noise_0, n, h, w, dev)
+        y = Fn.conv(s, self.conv_0, self._spec0, self.conv_0.training, bias=self.conv_0.bias, noise=noise, noise_w=nw)
+        s = self.norm_1(y, labels, relu=self._relu)
+        noise, nw = _noise_args(self.noise_1, n, h, w, dev)
+        y = Fn.conv(s, self.conv_1, self._spec1, self.conv_1.training, bias=self.conv_1.bias, noise=noise, noise_w=nw,
+                    residual=xa)
+        return Fn.from_nhwc(y) if plain else y
+
+    def update_alpha(self, epoch, num_epochs):
+        pass

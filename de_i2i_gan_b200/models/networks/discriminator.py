@@ -1,0 +1,41 @@
+"""DefectGanDiscriminator (models/networks/discriminator.py:49-98) on the sm_100a kernels."""
+import numpy as np
+import torch
+from torch import nn
+
+from ... import functional as Fn
+from .architecture import ConvBlock
+from .base_network import BaseNetwork
+
+
+class DefectGanDiscriminator(BaseNetwork):
+    def __init__(self, opt):
+        super().__init__()
+        dim = opt.ndf
+        common = dict(kernel_size=(4, 4), stride=(2, 2), padding=1, padding_mode="reflect", norm_layer=None,
+                      act_layer="leaky_relu", use_spectral=opt.use_spectral)
+        blocks = [ConvBlock(opt.input_nc, dim, **common)]
+        for _ in range(opt.num_layers):
+            blocks.append(ConvBlock(dim, dim * 2, **common))
+            dim *= 2
+        k = int(opt.image_size // np.power(2, opt.num_layers + 1))
+        self.enc_blk = nn.Sequential(*blocks)
+        self.cls_clf = ConvBlock(dim, opt.label_nc, kernel_size=(k, k), norm_layer=None, act_layer=None)
+        self.src_clf = ConvBlock(dim, 1, kernel_size=(3, 3), stride=(1, 1), padding="same", padding_mode="reflect",
+                                 norm_layer=None, act_layer=None)
+
+    def forward(self, x):
+        """(src_logits [B,1,h,h], cls_logits [B,label_nc]) like discriminator.py:92-98."""
+        assert isinstance(x, torch.Tensor), "x must be Original Images: Torch.Tensor"
+        feat = Fn.to_nhwc(x)
+        for blk in self.enc_blk:
+            feat = blk(feat)
+        src = self._logits(self.src_clf, feat)
+        cls = self._logits(self.cls_clf, feat)
+        return src, cls.reshape(cls.size(0), cls.size(1))
+
+    @staticmethod
+    def _logits(block: ConvBlock, feat: Fn.Nhwc) -> torch.Tensor:
+        conv = block.conv_block[0]
+        y = Fn.conv(feat, conv, block._spec, conv.training, bias=conv.bias, out_fp32=True)
+        return y.t[..., : y.c].permute(0, 3, 1, 2).contiguous()

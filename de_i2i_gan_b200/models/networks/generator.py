@@ -1,0 +1,74 @@
+"""DefectGanGenerator (models/networks/generator.py:52-275) on the sm_100a kernels; SPADE variant, skip_conn=False."""
+import torch
+from torch import nn
+
+from ... import functional as Fn
+from ...ops import ConvSpec
+from .architecture import ConvBlock, DeConvBlock, NormConvBlock, NormResBlock, ResBlock
+from .base_network import BaseNetwork
+
+
+class DefectGanGenerator(BaseNetwork):
+    def __init__(self, opt):
+        super().__init__()
+        assert (opt.num_res & 1) == 0, "num_res must be even"
+        if getattr(opt, "skip_conn", False):
+            raise NotImplementedError("skip_conn=True is broken in the reference (architecture.py:451 TODO) and not mirrored")
+        self.opt = opt
+        self.cycle_gan = opt.cycle_gan
+        self.label_nc = opt.label_nc
+        self.skip_conn = False
+        sn = opt.use_spectral
+        dim = opt.ngf
+        self.stem = ConvBlock(opt.input_nc, dim, kernel_size=(7, 7), padding="same", padding_mode="reflect",
+                              norm_layer=nn.BatchNorm2d, act_layer="leaky_relu", use_spectral=sn)
+        enc, enc_res, dec_res, dec = [], [], [], []
+        for _ in range(opt.num_scales):
+            enc.append(ConvBlock(dim, dim * 2, kernel_size=(4, 4), stride=(2, 2), padding=1, padding_mode="reflect",
+                                 norm_layer=nn.BatchNorm2d, act_layer="leaky_relu", use_spectral=sn))
+            dim *= 2
+        for _ in range(opt.num_res // 2):
+            enc_res.append(ResBlock(dim, dim, kernel_size=(3, 3), stride=(1, 1), padding="same", padding_mode="reflect",
+                                    norm_layer=nn.BatchNorm2d, act_layer="leaky_relu", use_spectral=sn))
+        style = dict(style_distill=opt.style_distill, embed_nc=opt.embed_nc, kernel_size=(3, 3), stride=(1, 1),
+                     padding="same", padding_mode="reflect", norm_layer=nn.InstanceNorm2d, act_layer="relu",
+                     use_spectral=sn, add_noise=opt.add_noise)
+        for _ in range(opt.num_res // 2, opt.num_res):
+            dec_res.append(NormResBlock(opt.style_norm_block_type, opt.hidden_nc, opt.label_nc, dim, dim, up_scale=False, **style))
+        head = dict(kernel_size=(3, 3), padding="same", padding_mode="reflect", up_scale=False, norm_layer=None,
+                    use_spectral=False, add_noise=False)
+        for _ in range(opt.num_scales):
+            dec.append(NormConvBlock(opt.style_norm_block_type, opt.hidden_nc, opt.label_nc, dim, dim // 2, up_scale=True, **style))
+            dim //= 2
+            # The reference (re)builds the containers and both heads inside this loop (generator.py:206-241), so the
+            # default-initialiser RNG draws of the discarded heads happen there too; mirrored so that the same seed
+            # gives the same parameters.  Registration order: enc_blk, enc_res_blk, dec_res_blk, dec_blk, heads.
+            self.enc_blk = nn.Sequential(*enc)
+            self.enc_res_blk = nn.Sequential(*enc_res)
+            self.dec_res_blk = nn.Sequential(*dec_res)
+            self.dec_blk = nn.Sequential(*dec)
+            self.foreground_head = DeConvBlock(dim, 3, act_layer="tanh", **head)
+            self.distribution_head = DeConvBlock(dim, 1, act_layer="sigmoid", **head)
+        self._head_spec = ConvSpec(dim, 4, 3, 1, 1, "reflect")
+
+    def forward(self, x, labels, style_feat=None):
+        """(output, spatial_prob) like generator.py:243-275; x: [B,3,H,W] FP32 in [-1,1]; labels: [B,label_nc,1,1] or a
+        spatial map [B,label_nc,h,w].  Both heads are one N=4 convolution whose FP32 logits feed the fused
+        tanh / sigmoid / composition kernel (generator.py:268-270)."""
+        assert isinstance(x, torch.Tensor), "x must be Original Images: Torch.Tensor"
+        if labels.dim() == 2:
+            labels = labels.reshape(labels.size(0), labels.size(1), 1, 1)
+        seg = Fn.to_nhwc(labels.float())
+        feat = self.stem(Fn.to_nhwc(x))
+        for blk in self.enc_blk:
+            feat = blk(feat, labels)
+        for blk in self.enc_res_blk:
+            feat = blk(feat, labels)
+        for blk in self.dec_res_blk:
+            feat = blk(feat, seg, style_feat)
+        for blk in self.dec_blk:
+            feat = blk(feat, seg, style_feat)
+        # NOTE generator.py:266-267 (host-synchronising isnan().any() + nan_to_num_) is not reproduced: it is the
+        # identity on finite activations and would cost a device->host sync per forward.
+        hd = Fn.conv_cat(feat, self.foreground_head._conv, self.distribution_head._conv, self._head_spec, out_fp32=True)
+        return Fn.compose(hd.t, x, self.cycle_gan)

@@ -1,0 +1,42 @@
+"""SPADE (models/networks/normalization.py:10-37) on the sm_100a kernels.  The module tree (param_free_norm,
+mlp_shared.0, mlp_gamma, mlp_beta) and therefore the state-dict keys are the reference's; nn.Conv2d objects are
+parameter containers only - forward runs the fused path:
+    seg --3x3 conv + bias + ReLU (nearest resize folded into the gather)--> actv
+    actv --ONE 3x3 conv with N = 2C (gamma | beta)--> gb
+    (x, gb) --instance-norm statistics + modulation (+ ReLU, + 2x nearest up-sampling of x)--> out
+"""
+import torch
+from torch import nn
+
+from ... import functional as Fn
+from ...ops import ConvSpec
+
+
+class SPADE(nn.Module):
+    def __init__(self, label_nc, norm_nc, hidden_nc=128, kernel_size=(3, 3), padding="same", norm_layer=nn.BatchNorm2d):
+        super().__init__()
+        self.param_free_norm = norm_layer(norm_nc, affine=False)
+        if not isinstance(self.param_free_norm, nn.InstanceNorm2d):
+            raise NotImplementedError("the CUDA path implements SPADE over InstanceNorm2d (the DefectGAN configuration)")
+        self.mlp_shared = nn.Sequential(nn.Conv2d(label_nc, hidden_nc, kernel_size=kernel_size, padding=padding),
+                                        nn.ReLU(inplace=True))
+        self.mlp_gamma = nn.Conv2d(hidden_nc, norm_nc, kernel_size=kernel_size, padding=padding)
+        self.mlp_beta = nn.Conv2d(hidden_nc, norm_nc, kernel_size=kernel_size, padding=padding)
+        k = kernel_size[0] if isinstance(kernel_size, (tuple, list)) else kernel_size
+        pad = (k - 1) // 2 if padding == "same" else int(padding)
+        self._shared_spec = ConvSpec(label_nc, hidden_nc, k, 1, pad, "zeros")
+        self._gb_spec = ConvSpec(hidden_nc, 2 * norm_nc, k, 1, pad, "zeros")
+
+    def forward(self, x, segmap, up=1, relu=False):
+        """x: NCHW tensor (drop-in) or Nhwc; segmap: [B,label_nc,h,w] NCHW or Nhwc.  ``up`` / ``relu`` are the fused
+        followers used by NormConvBlock / NormResBlock (architecture.py:242-244,347-348); defaults = reference SPADE."""
+        plain = not isinstance(x, Fn.Nhwc)
+        xa = Fn.to_nhwc(x)
+        seg = Fn.to_nhwc(segmap)
+        n, _, hx, wx = xa.shape
+        h, w = hx * up, wx * up
+        sconv = self.mlp_shared[0]
+        actv = Fn.conv(seg, sconv, self._shared_spec, self.training, bias=sconv.bias, act="relu", logical_hw=(h, w))
+        gb = Fn.conv_cat(actv, self.mlp_gamma, self.mlp_beta, self._gb_spec)
+        out = Fn.spade_modulate(xa, gb, up=up, relu=relu, eps=self.param_free_norm.eps)
+        return Fn.from_nhwc(out) if plain else out

@@ -47,7 +47,12 @@ SIGNATURES = {
     "dei2i_compose_bwd": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "dei2i_bce_logits": (_I, [_P, _P, _F, _LL, _P, _P, _F, _P]),
     "dei2i_l1": (_I, [_P, _P, _LL, _P, _P, _P, _F, _I, _P]),
+    "dei2i_mse": (_I, [_P, _P, _LL, _P, _P, _P, _F, _I, _P]),
+    "dei2i_ce_soft": (_I, [_P, _P, _I, _I, _P, _P, _F, _P]),
     "dei2i_adam": (_I, [_P, _P, _P, _P, _LL, _F, _F, _F, _F, _I, _P]),
+    "dei2i_rmsprop": (_I, [_P, _P, _P, _LL, _F, _F, _F, _P]),
+    "dei2i_clamp": (_I, [_P, _LL, _F, _F, _P]),
+    "dei2i_ema": (_I, [_P, _P, _LL, _F, _P]),
 }
 
 _lib = None

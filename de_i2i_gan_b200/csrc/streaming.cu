@@ -669,6 +669,54 @@ __global__ void l1_kernel(const float* __restrict__ a, const float* __restrict__
   if (threadIdx.x == 0) atomicAdd(loss, tot * invn);
 }
 
+
+__global__ void mse_kernel(const float* __restrict__ a, const float* __restrict__ b, long long n, float* __restrict__ loss,
+                           float* __restrict__ ga, float* __restrict__ gb, float gscale, int accumulate) {
+  __shared__ float sh[32];
+  float acc = 0.f;
+  const float invn = 1.f / (float)n;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float d = a[i] - (b ? b[i] : 0.f);
+    acc += d * d;
+    const float s = 2.f * d * invn * gscale;
+    if (ga) ga[i] = accumulate ? ga[i] + s : s;
+    if (gb) gb[i] = accumulate ? gb[i] - s : -s;
+  }
+  const float tot = block_sum(acc, sh);
+  if (threadIdx.x == 0) atomicAdd(loss, tot * invn);
+}
+// cross_entropy(logits, soft targets): mean_b( -sum_c t[b,c] * log_softmax(z[b])[c] ); one warp per row, one block
+__global__ void ce_soft_kernel(const float* __restrict__ z, const float* __restrict__ t, int B, int Cn, float* __restrict__ loss,
+                               float* __restrict__ grad, float gscale) {
+  __shared__ float sh[32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  float acc = 0.f;
+  for (int b = warp; b < B; b += nw) {
+    const float* zr = z + (long long)b * Cn;
+    const float* tr = t + (long long)b * Cn;
+    float mx = -INFINITY;
+    for (int c = lane; c < Cn; c += 32) mx = fmaxf(mx, zr[c]);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float se = 0.f, st = 0.f, stz = 0.f;
+    for (int c = lane; c < Cn; c += 32) {
+      se += __expf(zr[c] - mx);
+      st += tr[c];
+      stz += tr[c] * zr[c];
+    }
+    se = warp_sum(se);
+    st = warp_sum(st);
+    stz = warp_sum(stz);
+    const float lse = mx + __logf(se);
+    if (lane == 0) acc += st * lse - stz;
+    if (grad != nullptr)
+      for (int c = lane; c < Cn; c += 32)
+        grad[(long long)b * Cn + c] = (__expf(zr[c] - lse) * st - tr[c]) * gscale / (float)B;
+  }
+  const float tot = block_sum(acc, sh);
+  if (threadIdx.x == 0) loss[0] = tot / (float)B;
+}
+
 // ------------------------------------------------------------------------------------------ Adam
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n,
                             float step_size, float beta1, float beta2, float eps, float inv_sqrt_bc2) {
@@ -680,6 +728,25 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
     v[i] = vi;
     p[i] -= step_size * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
   }
+}
+
+__global__ void rmsprop_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ sq, long long n, float lr,
+                               float alpha, float eps) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gi = g[i];
+    const float vi = alpha * sq[i] + (1.f - alpha) * gi * gi;
+    sq[i] = vi;
+    p[i] -= lr * gi / (sqrtf(vi) + eps);
+  }
+}
+__global__ void clamp_kernel(float* __restrict__ p, long long n, float lo, float hi) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    p[i] = fminf(fmaxf(p[i], lo), hi);
+}
+// p_ema = lerp(p, p_ema, beta)  (StarGAN-v2 moving_average, solver.py:549-551)
+__global__ void ema_kernel(const float* __restrict__ p, float* __restrict__ pe, long long n, float beta) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    pe[i] = p[i] + beta * (pe[i] - p[i]);
 }
 
 }  // namespace dei2i
@@ -893,6 +960,23 @@ extern "C" int dei2i_l1(const float* a, const float* b, long long n, float* loss
   return LAUNCH_OK("l1_kernel");
 }
 
+
+extern "C" int dei2i_mse(const float* a, const float* b, long long n, float* loss, float* grad_a, float* grad_b, float grad_scale,
+                         int accumulate_grad, dei2i_stream stream) {
+  DEI2I_REQUIRE(a && loss && n > 0, "mse: bad arguments");
+  DEI2I_CUDA(cudaMemsetAsync(loss, 0, sizeof(float), ST));
+  unsigned blocks = nblocks(n, 256 * 8);
+  if (blocks > 148 * 4) blocks = 148 * 4;
+  mse_kernel<<<blocks, 256, 0, ST>>>(a, b, n, loss, grad_a, grad_b, grad_scale, accumulate_grad);
+  return LAUNCH_OK("mse_kernel");
+}
+extern "C" int dei2i_ce_soft(const float* logits, const float* targets, int B, int C, float* loss, float* grad, float grad_scale,
+                             dei2i_stream stream) {
+  DEI2I_REQUIRE(logits && targets && loss && B > 0 && C > 0, "ce_soft: bad arguments");
+  ce_soft_kernel<<<1, 1024, 0, ST>>>(logits, targets, B, C, loss, grad, grad_scale);
+  return LAUNCH_OK("ce_soft_kernel");
+}
+
 extern "C" int dei2i_adam(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2, float eps,
                           int step, dei2i_stream stream) {
   DEI2I_REQUIRE(p && g && m && v && n > 0 && step >= 1, "adam: bad arguments");
@@ -901,4 +985,26 @@ extern "C" int dei2i_adam(float* p, const float* g, float* m, float* v, long lon
   if (blocks > 148 * 16) blocks = 148 * 16;
   adam_kernel<<<blocks, 256, 0, ST>>>(p, g, m, v, n, (float)(lr / bc1), beta1, beta2, eps, (float)(1.0 / sqrt(bc2)));
   return LAUNCH_OK("adam_kernel");
+}
+
+extern "C" int dei2i_rmsprop(float* p, const float* g, float* sq, long long n, float lr, float alpha, float eps, dei2i_stream stream) {
+  DEI2I_REQUIRE(p && g && sq && n > 0, "rmsprop: bad arguments");
+  unsigned blocks = nblocks(n, 256 * 4);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  rmsprop_kernel<<<blocks, 256, 0, ST>>>(p, g, sq, n, lr, alpha, eps);
+  return LAUNCH_OK("rmsprop_kernel");
+}
+extern "C" int dei2i_clamp(float* p, long long n, float lo, float hi, dei2i_stream stream) {
+  DEI2I_REQUIRE(p && n > 0 && lo <= hi, "clamp: bad arguments");
+  unsigned blocks = nblocks(n, 256 * 4);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  clamp_kernel<<<blocks, 256, 0, ST>>>(p, n, lo, hi);
+  return LAUNCH_OK("clamp_kernel");
+}
+extern "C" int dei2i_ema(const float* p, float* p_ema, long long n, float beta, dei2i_stream stream) {
+  DEI2I_REQUIRE(p && p_ema && n > 0, "ema: bad arguments");
+  unsigned blocks = nblocks(n, 256 * 4);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  ema_kernel<<<blocks, 256, 0, ST>>>(p, p_ema, n, beta);
+  return LAUNCH_OK("ema_kernel");
 }

@@ -309,6 +309,46 @@ class _L1(Function):
         return (ga * g if ga is not None else None), (gb * g if gb is not None else None)
 
 
+class _Mse(Function):
+    @staticmethod
+    def forward(ctx, a, b):
+        a = a.contiguous().float()
+        ga = torch.empty_like(a) if ctx.needs_input_grad[0] else None
+        gb = torch.empty_like(a) if (b is not None and ctx.needs_input_grad[1]) else None
+        loss = ops.mse(a, b.contiguous().float() if b is not None else None, ga, gb)
+        ctx.save_for_backward(ga, gb)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        ga, gb = ctx.saved_tensors
+        return (ga * g if ga is not None else None), (gb * g if gb is not None else None)
+
+
+class _CeSoft(Function):
+    @staticmethod
+    def forward(ctx, logits, targets):
+        loss, grad = ops.ce_soft(logits.contiguous().float(), targets.contiguous().float())
+        ctx.save_for_backward(grad)
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        (grad,) = ctx.saved_tensors
+        return grad * g, None
+
+
+def mse_loss(a, b=None):
+    return _Mse.apply(a, b)
+
+
+def cross_entropy_soft(logits, targets):
+    """F.cross_entropy(logits [B,C], class-probability targets [B,C]) (mean over the batch)."""
+    if targets.dtype in (torch.long, torch.int):
+        targets = torch.nn.functional.one_hot(targets, logits.shape[1]).float()
+    return _CeSoft.apply(logits, targets)
+
+
 def bce_with_logits(logits, targets):
     """binary_cross_entropy_with_logits(mean). ``targets``: tensor or python scalar (all-ones / all-zeros labels)."""
     return _BceLogits.apply(logits, targets)

@@ -1,0 +1,140 @@
+"""DefectGanModel (models/defectgan_model.py:19-104,173-314,385-421) on the sm_100a kernels: the loss graphs of the
+'generator' / 'discriminator' / 'inference' / 'inference_classifier' modes, SPADE variant.
+
+Same constructor, ``__call__(mode, data, labels, df_data=None, img_only=False, mask=None)`` contract, return values
+and network train/eval switching as the reference; the networks are the mirrored modules of ``models.networks`` whose
+forward/backward run libdei2i.so, the losses are ``BaseModel._cal_loss`` (fused reduction kernels).  Packed BF16
+weights are built once per loss computation (``Fn.weight_cache``): the 4 G and 2 D passes of a G-step share them.
+
+Not on this path ("next"): the MAE modes, the SEAN / AdaIN style variants, DiffAugment policies
+and the image-grid helpers - they raise NotImplementedError instead of silently falling back to PyTorch.
+"""
+import torch
+
+from .. import functional as Fn
+from .base_model import BaseModel
+from .networks.discriminator import DefectGanDiscriminator
+from .networks.generator import DefectGanGenerator
+
+
+def _mean(losses):
+    return torch.stack(list(losses)).mean()
+
+
+class DefectGanModel(BaseModel):
+    def __init__(self, opt):
+        super().__init__(opt)
+        image_size = opt.image_size
+        assert image_size & (image_size - 1) == 0, "Image size must be a power of 2"
+        if opt.style_norm_block_type != "spade":
+            raise NotImplementedError(f"style_norm_block_type={opt.style_norm_block_type!r}: only 'spade' is on the CUDA hot path")
+        if getattr(opt, "diff_aug", ""):
+            raise NotImplementedError("DiffAugment policies are not on the CUDA hot path yet (SURVEY.md 8f n3)")
+        self.netG = DefectGanGenerator(opt).to(opt.device, non_blocking=True)
+        self.netD = DefectGanDiscriminator(opt).to(opt.device, non_blocking=True)
+        if getattr(opt, "is_train", False) or hasattr(opt, "clf_loss_type"):
+            assert opt.clf_loss_type is not None, "clf_loss_type should be initialized in dataset"
+            self.clf_loss_type = opt.clf_loss_type
+
+    # ------------------------------------------------------------------------------------------------ dispatch
+    def __call__(self, mode, data, labels, df_data=None, img_only=False, mask=None):
+        dev = self.opt.device
+        data, labels = data.to(dev, non_blocking=True), labels.to(dev, non_blocking=True)
+        if df_data is not None:
+            df_data = df_data.to(dev, non_blocking=True)
+        if mode.startswith("mae"):
+            raise NotImplementedError(f"mode {mode!r}: the MAE pre-training path is not on the CUDA hot path yet (SURVEY.md 8f n1)")
+        if mode == "generator":
+            self.netD.eval()
+            self.netG.train()
+            with Fn.weight_cache():
+                return self._compute_generator_loss(data, labels, df_data)
+        if mode == "discriminator":
+            self.netD.train()
+            self.netG.eval()
+            with Fn.weight_cache():
+                return self._compute_discriminator_loss(data, labels, df_data)
+        if mode == "inference":
+            self.netD.eval()
+            self.netG.eval()
+            with Fn.weight_cache():
+                return self._generate_fake(data, labels)
+        if mode == "inference_classifier":
+            self.netD.eval()
+            self.netG.eval()
+            return self._compute_clf_loss(data, labels)
+        if mode == "generate_grid":
+            raise NotImplementedError("generate_grid (TensorBoard image grids, host side) is out of the hot-path scope")
+        raise ValueError(f"|mode {mode}| is invalid")
+
+    # ------------------------------------------------------------------------------------------------ loss graphs
+    def _compute_generator_loss(self, bg_data, df_labels, df_data):
+        """defectgan_model.py:173-249: normal->defect->normal and defect->normal->defect cycles (4 G passes, train mode),
+        2 D passes (eval mode), adversarial + classification + reconstruction + spatial-distribution cycle / constraint."""
+        nm_labels, df_labels = self._labels(df_labels)
+        fake_defects, df_prob = self.netG(bg_data, df_labels)
+        recover_normals, rec_df_prob = self.netG(fake_defects, nm_labels)
+        fake_normals, nm_prob = self.netG(df_data, nm_labels)
+        recover_defects, rec_nm_prob = self.netG(fake_normals, df_labels)
+
+        fd_src, fd_cls = self.netD(fake_defects)
+        fn_src, fn_cls = self.netD(fake_normals)
+
+        gan = _mean([self._cal_loss(fd_src, 1.0, "bce"), self._cal_loss(fn_src, 1.0, "bce")])
+        clf = _mean([self._cal_loss(fd_cls, df_labels.view_as(fd_cls), self.clf_loss_type),
+                     self._cal_loss(fn_cls, nm_labels.view_as(fn_cls), self.clf_loss_type)])
+        rec = _mean([self._cal_loss(recover_defects, df_data, "l1"), self._cal_loss(recover_normals, bg_data, "l1")])
+        if self.opt.cycle_gan:
+            zero = torch.zeros([], device=rec.device)
+            return gan, clf, rec, zero, zero.clone()
+        cyc = _mean([self._cal_loss(df_prob, rec_df_prob, "l1"), self._cal_loss(nm_prob, rec_nm_prob, "l1")])
+        con = _mean([self._cal_loss(p, 0.0, "l1") for p in (df_prob, nm_prob, rec_df_prob, rec_nm_prob)])
+        return gan, clf, rec, cyc, con
+
+    def _compute_discriminator_loss(self, bg_data, df_labels, df_data):
+        """defectgan_model.py:251-292: 2 G passes without grad (eval mode), 4 D passes (train mode: one spectral-norm
+        power iteration each), 4 adversarial + 2 classification terms."""
+        nm_labels, df_labels = self._labels(df_labels)
+        with torch.no_grad():
+            fake_defects, _ = self.netG(bg_data, df_labels)
+            fake_normals, _ = self.netG(df_data, nm_labels)
+        fd_src, _ = self.netD(fake_defects.detach_())
+        fn_src, _ = self.netD(fake_normals.detach_())
+        rd_src, rd_cls = self.netD(df_data)
+        rn_src, rn_cls = self.netD(bg_data)
+        gan = _mean([self._cal_loss(fd_src, 0.0, "bce"), self._cal_loss(fn_src, 0.0, "bce"),
+                     self._cal_loss(rd_src, 1.0, "bce"), self._cal_loss(rn_src, 1.0, "bce")])
+        clf = _mean([self._cal_loss(rd_cls, df_labels.view_as(rd_cls), self.clf_loss_type),
+                     self._cal_loss(rn_cls, nm_labels.view_as(rn_cls), self.clf_loss_type)])
+        return gan, clf
+
+    def _compute_clf_loss(self, imgs, labels):
+        """defectgan_model.py:294-300."""
+        _, logits = self.netD(imgs)
+        return logits, self._cal_loss(logits, labels, self.clf_loss_type)
+
+    @torch.no_grad()
+    def _generate_fake(self, data, labels):
+        """defectgan_model.py:302-314 (spade branch): labels [B,label_nc] or a spatial map [B,label_nc,h,w]."""
+        return self.netG(data, self._expand_seg(labels))
+
+    # ------------------------------------------------------------------------------------------------ helpers
+    def _cal_loss(self, logits, targets, loss_type):
+        """A python scalar target means a constant target map (the reference materialises ones_like / zeros_like)."""
+        if isinstance(targets, (int, float)) and loss_type == "l1":
+            targets = None if targets == 0 else torch.full_like(logits, float(targets))
+        return super()._cal_loss(logits, targets, loss_type)
+
+    def _expand_seg(self, labels):
+        if labels.dim() == 2:
+            return labels.reshape(labels.size(0), labels.size(1), 1, 1)
+        if labels.dim() == 4:
+            return labels
+        raise ValueError(f"|labels dim {labels.dim()}| is invalid")
+
+    def _labels(self, df_labels):
+        """defectgan_model.py:410-421 (spade branch): normal label = one-hot class 0; both as [B,label_nc,1,1] maps."""
+        df_labels = df_labels.float()
+        nm_labels = torch.zeros_like(df_labels)
+        nm_labels[:, 0] = 1
+        return self._expand_seg(nm_labels), self._expand_seg(df_labels)

@@ -12,6 +12,30 @@ ACT = {None: 0, "none": 0, "leaky_relu": 1, "relu": 2, "tanh": 3, "sigmoid": 4}
 PAD = {"zeros": 0, "reflect": 1}
 
 
+# Optional in-band kernel timing (bench.py's roofline): when PROFILE is a list every convolution launch is bracketed
+# by CUDA events on the launching stream and appended as (kind, algorithmic_flops, start_event, end_event).
+PROFILE = None
+
+
+class _Timed:
+    __slots__ = ("kind", "flops", "e0")
+
+    def __init__(self, kind, flops):
+        self.kind, self.flops = kind, flops
+
+    def __enter__(self):
+        if PROFILE is not None:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+
+    def __exit__(self, *exc):
+        if PROFILE is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            PROFILE.append((self.kind, self.flops, self.e0, e1))
+        return False
+
+
 def pad8(c: int) -> int:
     return (c + 7) // 8 * 8
 
@@ -70,6 +94,10 @@ class ConvSpec:
         return ConvGeom(n, h, w, hs or h, ws or w, self.cin_ld, self.cout, self.cout_ld, self.kh, self.kw_, self.stride,
                         self.pad, PAD[self.pad_mode])
 
+    def flops(self, n, ho, wo) -> int:
+        """Algorithmic FLOPs (2 * MAC over REAL channels) of one forward / dgrad / wgrad pass."""
+        return 2 * n * ho * wo * self.cout * self.cin * self.kh * self.kw_
+
     @property
     def kf(self):
         return (self.kh * self.kw_ * self.cin_ld + 63) // 64 * 64
@@ -108,7 +136,8 @@ def conv2d_fwd(x, w_fwd, spec: ConvSpec, bias=None, noise=None, noise_weight=Non
         assert noise.numel() == n * ho * wo
     g = spec.geom(n, h, w, hs, ws)
     e = ConvEpilogue(_p(scale), _p(bias), _p(noise), _p(noise_weight), _p(residual), ACT[act], int(out_fp32))
-    check(_lib.load().dei2i_conv2d_fwd(_p(x), _p(w_fwd), _p(y), C.byref(g), C.byref(e), _stream()), "dei2i_conv2d_fwd")
+    with _Timed("conv_fwd", spec.flops(n, ho, wo)):
+        check(_lib.load().dei2i_conv2d_fwd(_p(x), _p(w_fwd), _p(y), C.byref(g), C.byref(e), _stream()), "dei2i_conv2d_fwd")
     return y
 
 
@@ -120,15 +149,18 @@ def conv2d_dgrad(dy, w_dgrad, spec: ConvSpec, in_hw, scale=None):
     assert tuple(dy.shape[1:3]) == spec.out_hw(h, w) and dy.shape[3] == spec.cout_ld
     g = spec.geom(n, h, w)
     lib = _lib.load()
+    flops = spec.flops(n, dy.shape[1], dy.shape[2])
     if spec.pad_mode == "reflect" and spec.pad > 0:
         p = spec.pad
         dxp = torch.empty(n, h + 2 * p, w + 2 * p, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
-        check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dxp), C.byref(g), _p(scale), 0, _stream()), "dei2i_conv2d_dgrad")
+        with _Timed("conv_dgrad", flops):
+            check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dxp), C.byref(g), _p(scale), 0, _stream()), "dei2i_conv2d_dgrad")
         dx = torch.empty(n, h, w, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
         check(lib.dei2i_reflect_fold(_p(dxp), _p(dx), n, h, w, spec.cin_ld, p, _stream()), "dei2i_reflect_fold")
         return dx
     dx = torch.empty(n, h, w, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
-    check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dx), C.byref(g), _p(scale), 0, _stream()), "dei2i_conv2d_dgrad")
+    with _Timed("conv_dgrad", flops):
+        check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dx), C.byref(g), _p(scale), 0, _stream()), "dei2i_conv2d_dgrad")
     return dx
 
 
@@ -156,8 +188,9 @@ def conv2d_wgrad(x, dy, dw, spec: ConvSpec, accumulate=False, sn=None, logical_h
     nbytes = lib.dei2i_conv2d_wgrad_workspace(C.byref(g), spec.cin)
     wsb = _workspace(nbytes, x.device)
     w0, u, v, inv = sn if sn is not None else (None, None, None, None)
-    check(lib.dei2i_conv2d_wgrad(_p(x), _p(dy), _p(dw), spec.cin, 1.0 if accumulate else 0.0, C.byref(g), _p(w0), _p(u),
-                                 _p(v), _p(inv), _p(wsb), wsb.numel(), _stream()), "dei2i_conv2d_wgrad")
+    with _Timed("conv_wgrad", spec.flops(n, dy.shape[1], dy.shape[2])):
+        check(lib.dei2i_conv2d_wgrad(_p(x), _p(dy), _p(dw), spec.cin, 1.0 if accumulate else 0.0, C.byref(g), _p(w0), _p(u),
+                                     _p(v), _p(inv), _p(wsb), wsb.numel(), _stream()), "dei2i_conv2d_wgrad")
     return dw
 
 
@@ -301,8 +334,39 @@ def l1(a, b=None, grad_a=None, grad_b=None, grad_scale=1.0, accumulate=False):
     return loss
 
 
+def mse(a, b=None, grad_a=None, grad_b=None, grad_scale=1.0, accumulate=False):
+    _chk_f32(a, "a")
+    loss = torch.empty((), dtype=torch.float32, device=a.device)
+    check(_lib.load().dei2i_mse(_p(a), _p(b), a.numel(), _p(loss), _p(grad_a), _p(grad_b), float(grad_scale), int(accumulate),
+                                _stream()), "dei2i_mse")
+    return loss
+
+
+def ce_soft(logits, targets, want_grad=True, grad_scale=1.0):
+    _chk_f32(logits, "logits")
+    _chk_f32(targets, "targets")
+    b, c = logits.shape
+    loss = torch.empty((), dtype=torch.float32, device=logits.device)
+    grad = torch.empty_like(logits) if want_grad else None
+    check(_lib.load().dei2i_ce_soft(_p(logits), _p(targets), b, c, _p(loss), _p(grad), float(grad_scale), _stream()),
+          "dei2i_ce_soft")
+    return loss, grad
+
+
 def adam(p, g, m, v, lr, beta1, beta2, eps, step):
     check(_lib.load().dei2i_adam(_p(p), _p(g), _p(m), _p(v), p.numel(), lr, beta1, beta2, eps, step, _stream()), "dei2i_adam")
+
+
+def rmsprop(p, g, sq, lr, alpha=0.99, eps=1e-8):
+    check(_lib.load().dei2i_rmsprop(_p(p), _p(g), _p(sq), p.numel(), lr, alpha, eps, _stream()), "dei2i_rmsprop")
+
+
+def clamp_(p, lo, hi):
+    check(_lib.load().dei2i_clamp(_p(p), p.numel(), float(lo), float(hi), _stream()), "dei2i_clamp")
+
+
+def ema_(p, p_ema, beta):
+    check(_lib.load().dei2i_ema(_p(p), _p(p_ema), p.numel(), float(beta), _stream()), "dei2i_ema")
 
 
 def launch_count() -> int:

@@ -1,0 +1,46 @@
+"""Programmatic stand-in for ``TrainOptions().parse()`` (options/defectgan_options.py:77-111 over
+options/base_options.py:12-52 and options/train_options.py:9-43): a Namespace carrying the same option names and
+defaults, so the mirrored trainer / model / networks read exactly the attributes the reference's do.  The reference's
+argparse classes remain the CLI surface (they are host-only code and work unchanged on top of this package); this
+helper exists for the benchmark, the smoke test and the parity tests, which have no command line."""
+from pathlib import Path
+from types import SimpleNamespace
+
+import torch
+
+
+def train_options(**over) -> SimpleNamespace:
+    opt = SimpleNamespace(
+        # base_options.py:14-50 with the DefectGAN overrides of defectgan_options.py:14-45
+        name="exp0", model="defectgan", gpu_ids="0", ckpt_dir=Path("./ckpt"), phase="train",
+        batch_size=4, image_size=128, input_nc=3, output_nc=3, label_nc=6,
+        data_dir=Path("./data"), dataset_name="codebrim", dataset_data_type=None, load_from_opt_file=None,
+        init_type="normal", init_variance=0.02, use_spectral=False, load_model_name=None, which_epoch="latest",
+        ngf=64, num_scales=2, num_res=6, add_noise=False, style_norm_block_type="spade", hidden_nc=128,
+        ndf=64, num_layers=5, cycle_gan=False, skip_conn=False,
+        embed_nc=768, latent_dim=16, embed_path=None, num_embeds=5, sean_alpha=None, style_distill=False,
+        use_running_stats=False,
+        # train_options.py:9-43 with the overrides of defectgan_options.py:87-109
+        num_display_images=8, save_img_freq=4, save_ckpt_freq=10, save_latest_freq=1000,
+        optimizer="adam", lr=[2e-4], num_epochs=-1, num_iters=500_000, scheduler="step", lr_decay=5e-3,
+        loss_weight=[2, 5, 5, 5, 1], num_critics=5, diff_aug="", continue_training=False, log_dir=None,
+        is_train=True,
+        # set by the entry script from the dataset (train_defectgan.py:54, codebrim_dataset.py:12) / loader length
+        clf_loss_type="bce", iters_per_epoch=1000,
+    )
+    for k, v in over.items():
+        if not hasattr(opt, k):
+            raise AttributeError(f"unknown option {k!r}")
+        setattr(opt, k, v)
+    if not hasattr(opt, "device"):
+        # utils/util.py:11-18: cuda:<first gpu id>; under torchrun the local rank picks the device
+        import os
+        opt.device = torch.device("cuda", int(os.environ.get("LOCAL_RANK", opt.gpu_ids.split(",")[0])))
+    return opt
+
+
+def readme_recipe(**over) -> SimpleNamespace:
+    """defectGAN/README.md:21-24: the documented DefectGAN training recipe adds --add_noise --use_spectral."""
+    kw = dict(add_noise=True, use_spectral=True)
+    kw.update(over)
+    return train_options(**kw)

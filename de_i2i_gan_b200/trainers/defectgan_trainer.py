@@ -1,0 +1,115 @@
+"""DefectGanTrainer (trainers/defectgan_trainer.py:19-188): the D-step / G-step of the hot path and the epoch loop.
+
+``_train_discriminator_once`` / ``_train_generator_once`` keep the reference's order of operations (zero_grad -> loss
+graph -> weighted sum -> backward -> optimizer step -> ``.item()`` bookkeeping).  Differences, all invisible to the
+results: the optimizer is FlatAdam (fused kernel), data-parallel gradient buckets are all-reduced under backward, and
+during the G-step the discriminator's parameters do not require grad - the reference computes those gradients and
+throws them away (``optimizers['D'].zero_grad()`` precedes D's next use, :171), we skip the wgrad kernels instead.
+TensorBoard logging is optional (only if ``opt.log_dir`` is set and tensorboard is importable); the FID / IS / LPIPS
+validation of ``--phase val`` needs downloaded weights and is out of the hot-path scope.
+"""
+from collections import defaultdict
+
+import numpy as np
+import torch
+
+from .base_trainer import BaseTrainer
+
+
+class DefectGanTrainer(BaseTrainer):
+    def __init__(self, opt):
+        super().__init__(opt)
+        assert len(opt.loss_weight) == 5, f"length of loss weights must be 5, not {len(opt.loss_weight)}"
+        self.loss_weights = dict(zip(("clf_d", "clf_g", "rec", "sd_cyc", "sd_con"), opt.loss_weight))
+        self.loss_types = ["gan", "clf", "aux"]
+        self._init_losses()
+        if opt.phase == "val":
+            raise NotImplementedError("--phase val (FID / IS / LPIPS with downloaded Inception weights) is out of the hot-path scope")
+        self._d_params = list(self.model.netD.parameters())
+
+    def _init_lr(self, opt):
+        assert len(opt.lr) in (1, 2), f"length of lr must be 1 or 2, not {len(opt.lr)}"
+        self.lr = {"D": opt.lr[0], "G": opt.lr[1]} if len(opt.lr) == 2 else opt.lr[0]
+
+    def _init_losses(self):
+        self.losses = {t: defaultdict(list) for t in self.loss_types}
+
+    # ------------------------------------------------------------------------------------------------ the hot path
+    def _train_generator_once(self, bg_data, df_labels, df_data):
+        """defectgan_trainer.py:138-168."""
+        self.optimizers["G"].zero_grad()
+        for p in self._d_params:
+            p.requires_grad_(False)
+        try:
+            gan, clf, rec, cyc, con = self.model("generator", bg_data, df_labels, df_data)
+            w = self.loss_weights
+            g_loss = gan + clf * w["clf_g"] + rec * w["rec"] + cyc * w["sd_cyc"] + con * w["sd_con"]
+            g_loss.backward()
+        finally:
+            for p in self._d_params:
+                p.requires_grad_(True)
+        self._reduce_and_step("G")
+        vals = torch.stack([gan.detach(), clf.detach(), rec.detach(), cyc.detach(), con.detach()]).tolist()  # one D2H sync
+        self.losses["gan"]["G"].append(vals[0])
+        self.losses["clf"]["G"].append(vals[1])
+        self.losses["aux"]["rec"].append(vals[2])
+        self.losses["aux"]["cyc"].append(vals[3])
+        self.losses["aux"]["con"].append(vals[4])
+
+    def _train_discriminator_once(self, bg_data, df_labels, df_data):
+        """defectgan_trainer.py:170-180."""
+        self.optimizers["D"].zero_grad()
+        gan, clf = self.model("discriminator", bg_data, df_labels, df_data)
+        d_loss = gan + clf * self.loss_weights["clf_d"]
+        d_loss.backward()
+        self._reduce_and_step("D")
+        vals = torch.stack([gan.detach(), clf.detach()]).tolist()
+        self.losses["gan"]["D"].append(vals[0])
+        self.losses["clf"]["D"].append(vals[1])
+
+    # ------------------------------------------------------------------------------------------------ epoch loop
+    def train(self, train_loaders, val_loaders=None):
+        """defectgan_trainer.py:75-89; epochs run from first_epoch to num_epochs inclusive."""
+        writer = self._make_writer()
+        for epoch in range(self.first_epoch, self.opt.num_epochs + 1):
+            self._init_losses()
+            self._train_epoch(train_loaders, epoch)
+            if writer is not None:
+                self._write_tf_log(writer, epoch)
+            if epoch % self.opt.save_ckpt_freq == 0 and self.rank == 0:
+                self.model.save(epoch)
+            self._update_per_epoch(epoch)
+        if writer is not None:
+            writer.close()
+
+    def _train_epoch(self, data_loaders, epoch):
+        """defectgan_trainer.py:91-120 (progress bar omitted): one D-step per iteration, one G-step every
+        ``num_critics`` iterations, 'latest' checkpoint + iter.txt every ``save_latest_freq`` iterations."""
+        for df_data, df_labels, _ in data_loaders["defects"]:
+            self.iters += 1
+            bg_data, _, _ = next(data_loaders["background"])
+            bg_data = bg_data[: df_data.size(0)]
+            self._train_discriminator_once(bg_data, df_labels, df_data)
+            if self.iters % self.opt.num_critics == 0:
+                self._train_generator_once(bg_data, df_labels, df_data)
+            if self.iters % self.opt.save_latest_freq == 0 and self.rank == 0:
+                self.model.save("latest")
+                np.savetxt(self.iter_record_path, (epoch, self.iters), fmt="%i", delimiter=",")
+
+    def _make_writer(self):
+        if self.rank != 0 or getattr(self.opt, "log_dir", None) is None:
+            return None
+        try:
+            from torch.utils.tensorboard import SummaryWriter
+        except Exception:
+            return None
+        return SummaryWriter(self.opt.log_dir / self.opt.name)
+
+    def _write_tf_log(self, writer, epoch):
+        for t in self.loss_types:
+            writer.add_scalars(f"Losses/{t}", {k: sum(v) / (len(v) + 1e-12) for k, v in self.losses[t].items()}, epoch)
+        writer.add_scalars("Lr", {f"net_{n}": s.get_last_lr()[0] for n, s in self.schedulers.items()}, epoch)
+
+    def _update_per_epoch(self, epoch=None):
+        super()._update_per_epoch(epoch)
+        self.model.update_per_epoch(epoch)

@@ -158,9 +158,24 @@ int dei2i_bce_logits(const float* logits, const float* targets, float target_con
 int dei2i_l1(const float* a, const float* b, long long n, float* loss, float* grad_a, float* grad_b, float grad_scale,
              int accumulate_grad, dei2i_stream stream);
 
+/* mse: mse_loss(a, b) (b == NULL: zeros); same gradient conventions as dei2i_l1. */
+int dei2i_mse(const float* a, const float* b, long long n, float* loss, float* grad_a, float* grad_b, float grad_scale,
+              int accumulate_grad, dei2i_stream stream);
+/* cce: cross_entropy(logits [B,C], class-probability targets [B,C]) = mean_b(-sum_c t log_softmax(z)). */
+int dei2i_ce_soft(const float* logits, const float* targets, int B, int C, float* loss, float* grad, float grad_scale,
+                  dei2i_stream stream);
+
 /* torch.optim.Adam step (trainers/base_trainer.py:75-89) over one flat fp32 parameter vector. step is 1-based. */
 int dei2i_adam(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2,
                float eps, int step, dei2i_stream stream);
+
+/* torch.optim.RMSprop step (alpha 0.99, eps 1e-8, no momentum, not centered: trainers/base_trainer.py:76-77 with
+ * options/wgan_options.py:49-57) and the WGAN weight clipping p.data.clamp_(lo, hi) (models/wgan_model.py:18-21). */
+int dei2i_rmsprop(float* p, const float* g, float* square_avg, long long n, float lr, float alpha, float eps,
+                  dei2i_stream stream);
+int dei2i_clamp(float* p, long long n, float lo, float hi, dei2i_stream stream);
+/* p_ema = lerp(p, p_ema, beta): StarGAN-v2 moving_average (stargan-v2/core/solver.py:549-551). */
+int dei2i_ema(const float* p, float* p_ema, long long n, float beta, dei2i_stream stream);
 
 #ifdef __cplusplus
 }

@@ -72,6 +72,11 @@ DEVINL const __nv_bfloat16* gather_ptr(const Gather& g, int img, int oy, int ox,
   return g.src + (((long long)img * g.Hs + iy) * g.Ws + ix) * g.C + c8 * 8;
 }
 
+DEVINL void unpack8_bf16(const uint4& v, float (&f)[8]) {
+  f[0] = bf16lo(v.x); f[1] = bf16hi(v.x); f[2] = bf16lo(v.y); f[3] = bf16hi(v.y);
+  f[4] = bf16lo(v.z); f[5] = bf16hi(v.z); f[6] = bf16lo(v.w); f[7] = bf16hi(v.w);
+}
+
 struct Epilogue {
   const float* scale;
   const float* bias;
@@ -498,12 +503,14 @@ __global__ void sum_blocks_kernel(const float* __restrict__ in, int n, float* __
   }
 }
 
-// small-Cout wgrad (heads, discriminator classifiers: Cout_ld < 64): CUDA cores, fp32 atomics on a [Cout, Kf] buffer
+// narrow-Cout wgrad (heads, discriminator classifiers, reduced-width test networks: Cout_ld < 64): CUDA cores, fp32
+// atomics on a [Cout, Kf] buffer; blockIdx.y selects a group of 8 output channels
 __global__ void wgrad_small_kernel(const Gather g, const __nv_bfloat16* __restrict__ dy, int Cout, int Cout_ld, int Kf,
                                    float* __restrict__ acc /*[Cout, Kf] zeroed*/, int pix_per_block) {
   // each block: a range of pixels; thread t handles K elements t, t+blockDim, ...; accumulates over the pixel range
   const long long m_begin = (long long)blockIdx.x * pix_per_block;
   const long long m_end = min(g.M, m_begin + pix_per_block);
+  const int co0 = blockIdx.y * 8;
   const int HoWo = g.Ho * g.Wo;
   const int Kreal = g.ntaps * g.cin8 * 8;
   for (int k = threadIdx.x; k < Kreal; k += blockDim.x) {
@@ -520,12 +527,12 @@ __global__ void wgrad_small_kernel(const Gather g, const __nv_bfloat16* __restri
       const __nv_bfloat16* sp = gather_ptr(g, img, oy, ox, r, s, ci >> 3);
       if (sp == nullptr) continue;
       const float xv = __bfloat162float(sp[ci & 7]);
-      const __nv_bfloat16* dyr = dy + m * Cout_ld;
+      float d[8];
+      unpack8_bf16(__ldg(reinterpret_cast<const uint4*>(dy + m * Cout_ld + co0)), d);
 #pragma unroll
-      for (int c = 0; c < 8; ++c)
-        if (c < Cout) a[c] += xv * __bfloat162float(dyr[c]);
+      for (int c = 0; c < 8; ++c) a[c] += xv * d[c];
     }
-    for (int c = 0; c < 8 && c < Cout; ++c) atomicAdd(acc + (long long)c * Kf + k, a[c]);
+    for (int c = 0; c < 8 && co0 + c < Cout; ++c) atomicAdd(acc + (long long)(co0 + c) * Kf + k, a[c]);
   }
 }
 
@@ -696,12 +703,11 @@ extern "C" int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int 
   float* partial = (float*)workspace;
   const int taps = g->kh * g->kw;
   if (g->Cout_ld < 64) {
-    DEI2I_REQUIRE(g->Cout <= 8, "conv2d_wgrad: Cout_ld < 64 requires Cout <= 8 (got %d)", g->Cout);
     splits = 1;
     DEI2I_CUDA(cudaMemsetAsync(partial, 0, (size_t)g->Cout * Kf * sizeof(float), st));
     const int ppb = 256;
     long long blocks = (p.g.M + ppb - 1) / ppb;
-    wgrad_small_kernel<<<(unsigned)blocks, 256, 0, st>>>(p.g, (const __nv_bfloat16*)dy, g->Cout, g->Cout_ld, Kf, partial, ppb);
+    wgrad_small_kernel<<<dim3((unsigned)blocks, (unsigned)(g->Cout_ld / 8)), 256, 0, st>>>(p.g, (const __nv_bfloat16*)dy, g->Cout, g->Cout_ld, Kf, partial, ppb);
     count_launch();
     DEI2I_CUDA(cudaGetLastError());
   } else {

@@ -66,6 +66,8 @@ CONV_CASES = {
     "ragged_m": (1, 64, 10, 10, 64, 3, 1, 1, "reflect", False, None),
     "d_conv0": (2, 3, 32, 32, 64, 4, 2, 1, "reflect", False, None),
     "d_src_1": (2, 128, 4, 4, 1, 3, 1, 1, "reflect", False, None),
+    "narrow_16_32": (2, 16, 12, 12, 32, 3, 1, 1, "reflect", False, None),   # reduced-width nets of the golden fixtures
+    "narrow_s2_8_16": (2, 8, 16, 16, 16, 4, 2, 1, "reflect", False, None),
 }
 
 
@@ -118,7 +120,8 @@ def test_conv_fwd_fp32_out_and_epilogue():
     assert e1 < TOL_F32 and e2 < TOL_BF16 and e3 < TOL_F32
 
 
-DGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "spade_gb_512", "heads_4", "ragged_m", "d_src_1", "cls_valid_k2"]
+DGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "spade_gb_512", "heads_4", "ragged_m", "d_src_1", "cls_valid_k2",
+               "narrow_16_32", "narrow_s2_8_16"]
 
 
 @pytest.mark.parametrize("case", DGRAD_CASES)
@@ -140,7 +143,7 @@ def test_conv_dgrad(case):
 
 
 WGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "stem7x7", "spade_shared_8x8seg", "spade_gb_512", "heads_4",
-               "ragged_m", "d_conv0", "d_src_1", "cls_valid_k2"]
+               "ragged_m", "d_conv0", "d_src_1", "cls_valid_k2", "narrow_16_32", "narrow_s2_8_16"]
 
 
 @pytest.mark.parametrize("case", WGRAD_CASES)

@@ -43,6 +43,8 @@ def parse():
     ap.add_argument("--image-size", type=int, default=256)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample-batch", type=int, default=2)
+    ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: skip the pinned-host pass")
+    ap.add_argument("--breakdown", default=None, help="write a per-convolution-geometry timing table (JSON) to this path")
     return ap.parse_args()
 
 
@@ -225,13 +227,26 @@ def run_ours(args):
     ms, prof = timed(resident, args.steps, True)
     launches = ops.launch_count() - l0
     clk = clocks.stop() if rank == 0 else None
-    step(host)  # warm the pinned-host path once
-    ms_e2e, _ = timed(host, args.steps, False)
+    if args.skip_e2e:
+        ms_e2e = float("nan")
+    else:
+        step(host)  # warm the pinned-host path once
+        ms_e2e, _ = timed(host, args.steps, False)
     mem_gb = torch.cuda.max_memory_allocated() / 2 ** 30
 
     # ---- roofline of the convolution kernels from the in-band events
     agg = {}
-    for kind, flops, e0, e1 in prof:
+    if args.breakdown and rank == 0:
+        table = {}
+        for kind, flops, e0, e1, tag in prof:
+            t = table.setdefault(f"{kind} {tag}", [0, 0.0, 0])
+            t[0] += flops; t[1] += e0.elapsed_time(e1); t[2] += 1
+        rows = [dict(kernel=k, launches_per_step=v[2] / args.steps, ms_per_step=v[1] / args.steps, gflop_per_launch=v[0] / v[2] / 1e9,
+                     tflops=(v[0] / (v[1] * 1e-3) / 1e12 if v[1] > 0 else 0.0)) for k, v in table.items()]
+        rows.sort(key=lambda r: -r["ms_per_step"])
+        with open(args.breakdown, "w") as f:
+            json.dump(rows, f, indent=1)
+    for kind, flops, e0, e1, _tag in prof:
         a = agg.setdefault(kind, [0, 0.0, 0])
         a[0] += flops
         a[1] += e0.elapsed_time(e1)

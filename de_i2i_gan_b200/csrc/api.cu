@@ -29,6 +29,7 @@ int g_tune_conv_stages = 0;
 int g_tune_conv_bn = 0;
 int g_tune_wgrad_bn = 0;
 int g_tune_wgrad_waves = 0;
+int g_tune_conv_path = 0;  // 0 = auto (TMA im2col kernels where applicable), 1 = always the cp.async gather kernels
 static std::atomic<long long> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
@@ -76,6 +77,52 @@ int encode_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint
   return 0;
 }
 
+typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                   const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int encode_tmap_im2col_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t W, uint64_t H, uint64_t N, int lower,
+                            int upper, uint32_t stride, uint32_t channels_per_pixel, uint32_t pixels_per_column) {
+  static EncodeIm2colFn fn = nullptr;
+  static bool tried = false;
+  static int driver_version = 0;
+  if (!tried) {
+    tried = true;
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = (EncodeIm2colFn)p;
+    cudaDriverGetVersion(&driver_version);
+  }
+  if (fn == nullptr) {
+    set_error("cuTensorMapEncodeIm2col is not available (no CUDA driver / no sm_100 device)");
+    return DEI2I_ERR_CUDA;
+  }
+  if ((reinterpret_cast<uintptr_t>(base) & 15) != 0 || (C * 2) % 16 != 0) {
+    set_error("im2col TMA operand must be 16-byte aligned (base %p, C %llu)", base, (unsigned long long)C);
+    return DEI2I_ERR_INVALID;
+  }
+  cuuint64_t dims[4] = {C, W, H, N};
+  cuuint64_t strides[3] = {C * 2, W * C * 2, H * W * C * 2};
+  int lo[2] = {lower, lower};
+  int up[2] = {upper, upper};
+  cuuint32_t estr[4] = {1, stride, stride, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lo, up, channels_per_pixel,
+                  pixels_per_column, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeIm2col failed with CUresult %d (C %llu W %llu H %llu N %llu lower %d upper %d stride %u)", (int)r,
+              (unsigned long long)C, (unsigned long long)W, (unsigned long long)H, (unsigned long long)N, lower, upper, stride);
+    return DEI2I_ERR_CUDA;
+  }
+  // Known driver issue (drivers <= 13.1; same workaround as CUTLASS make_im2col_tma_copy_desc): for tensors smaller than
+  // 128 KiB a descriptor bit must be cleared or the load faults.
+  if (driver_version <= 13010 && C * W * H * N * 2 < 131072)
+    reinterpret_cast<uint64_t*>(out)[1] &= ~(1llu << 21);
+  return 0;
+}
+
 }  // namespace dei2i
 
 extern "C" int dei2i_version(void) { return 100; }
@@ -87,6 +134,7 @@ extern "C" int dei2i_set_tuning(const char* key, int value) {
   else if (!strcmp(key, "conv_bn")) slot = &dei2i::g_tune_conv_bn;
   else if (!strcmp(key, "wgrad_bn")) slot = &dei2i::g_tune_wgrad_bn;
   else if (!strcmp(key, "wgrad_waves")) slot = &dei2i::g_tune_wgrad_waves;
+  else if (!strcmp(key, "conv_path")) slot = &dei2i::g_tune_conv_path;
   if (slot == nullptr) return -1;
   int old = *slot;
   *slot = value;

@@ -30,6 +30,10 @@ int check_cuda(cudaError_t e, const char* what);
 int encode_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
                         uint64_t row_pitch_bytes, uint32_t box_inner, uint32_t box_outer, int swizzle128);
 
+// NHWC activation [N, H, W, C] as an im2col tensor map: bounding box [lower, dim + upper) in W and H, traversal stride.
+int encode_tmap_im2col_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t W, uint64_t H, uint64_t N, int lower,
+                            int upper, uint32_t stride, uint32_t channels_per_pixel, uint32_t pixels_per_column);
+
 // ------------------------------------------------------------------ misc
 DEVINL uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -97,6 +101,18 @@ DEVINL void tma_load_2d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(smem_u32(smem_dst)), "l"(m), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+
+// im2col-mode TMA (NHWC activation viewed as (C, W, H, N)): loads `pixelsPerColumn` pixels x `channelsPerPixel`
+// channels starting at base pixel (w, h, n) - traversing W, then H, then N inside the descriptor's bounding box with
+// its traversal stride - displaced by the filter offset (off_w, off_h); out-of-bounds elements are zero-filled.
+DEVINL void tma_load_im2col_4d(void* smem_dst, const CUtensorMap* m, uint64_t* bar, int c, int w, int h, int n,
+                               uint16_t off_w, uint16_t off_h) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2], "
+      "{%7, %8};"
+      ::"r"(smem_u32(smem_dst)), "l"(m), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n), "h"(off_w), "h"(off_h)
       : "memory");
 }
 

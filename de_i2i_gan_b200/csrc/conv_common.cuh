@@ -1,0 +1,52 @@
+// Shared by the convolution kernels (conv_igemm.cu: cp.async-gather kernels; conv_tma.cu: TMA-im2col kernels).
+#pragma once
+#include "common.cuh"
+
+namespace dei2i {
+
+DEVINL void unpack8_bf16(const uint4& v, float (&f)[8]) {
+  f[0] = bf16lo(v.x); f[1] = bf16hi(v.x); f[2] = bf16lo(v.y); f[3] = bf16hi(v.y);
+  f[4] = bf16lo(v.z); f[5] = bf16hi(v.z); f[6] = bf16lo(v.w); f[7] = bf16hi(v.w);
+}
+
+struct Epilogue {
+  const float* scale;
+  const float* bias;
+  const float* noise;
+  const float* noise_weight;
+  const __nv_bfloat16* residual;
+  void* out;
+  int act;
+  int out_fp32;
+  int ld;     // output pitch (elements)
+  int ncols;  // real columns that carry bias (Cout)
+};
+
+
+// Where output row m = (img, p, q) of the GEMM lands: out[img, p*osy + oy0, q*osx + ox0, :] of an [*, OH, OW, ld] tensor.
+// linear = 1 means plain row-major rows (offset m * ld).
+struct OutMap {
+  int linear;
+  int Ho, Wo;  // traversal domain per image
+  int OH, OW, osy, osx, oy0, ox0;
+};
+
+struct TmaConvParams {
+  int Ho, Wo;      // traversal (GEMM row) domain per image
+  long long M;     // N * Ho * Wo
+  int stride;      // traversal stride of the im2col descriptor
+  int lower;       // bounding-box lower corner (W and H)
+  int kh, kw;      // filter size (tap t = r * kw + s)
+  int flip;        // 1: TMA filter offsets are (kh-1-r, kw-1-s) - dgrad as a convolution over dY with the un-flipped weight pack
+  int cin_blocks;  // input channels / 64
+  int num_kb;      // taps * cin_blocks
+  int m_tiles, n_tiles;
+  OutMap om;
+  Epilogue e;
+};
+
+// returns 0 on success; the caller has checked applicability (see tma_conv_applicable)
+int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, int rows, int K, const TmaConvParams& p,
+                 int upper, cudaStream_t st);
+
+}  // namespace dei2i

@@ -19,6 +19,7 @@
 #include <string.h>
 
 #include "common.cuh"
+#include "conv_common.cuh"
 #include "../../include/dei2i.h"
 
 namespace dei2i {
@@ -27,6 +28,7 @@ extern int g_tune_conv_stages;  // 0 = auto
 extern int g_tune_conv_bn;      // 0 = auto
 extern int g_tune_wgrad_bn;     // 0 = auto
 extern int g_tune_wgrad_waves;
+extern int g_tune_conv_path;
 void count_launch(int n = 1);
 
 // ----------------------------------------------------------------------------------------------------------
@@ -71,24 +73,6 @@ DEVINL const __nv_bfloat16* gather_ptr(const Gather& g, int img, int oy, int ox,
   if (!resolve_axis(g, ox, s, g.Wl, g.Ws, ix)) return nullptr;
   return g.src + (((long long)img * g.Hs + iy) * g.Ws + ix) * g.C + c8 * 8;
 }
-
-DEVINL void unpack8_bf16(const uint4& v, float (&f)[8]) {
-  f[0] = bf16lo(v.x); f[1] = bf16hi(v.x); f[2] = bf16lo(v.y); f[3] = bf16hi(v.y);
-  f[4] = bf16lo(v.z); f[5] = bf16hi(v.z); f[6] = bf16lo(v.w); f[7] = bf16hi(v.w);
-}
-
-struct Epilogue {
-  const float* scale;
-  const float* bias;
-  const float* noise;
-  const float* noise_weight;
-  const __nv_bfloat16* residual;
-  void* out;
-  int act;
-  int out_fp32;
-  int ld;     // output pitch (elements)
-  int ncols;  // real columns that carry bias (Cout)
-};
 
 struct ConvKParams {
   Gather g;
@@ -591,6 +575,18 @@ static int check_geom(const dei2i_conv_geom* g) {
   return 0;
 }
 
+// The TMA-im2col kernels take: zero / no padding, no on-the-fly resize, square filters, a K-operand channel count that is
+// a multiple of 64 and whole 128-row tiles.  Everything else (tiny channel counts, resized label maps, ragged sizes,
+// reflect padding that was not pre-applied) runs on the cp.async-gather kernels above.
+static bool tma_applicable(const dei2i_conv_geom* g, int k_channels, long long M) {
+  if (g_tune_conv_path == 1) return false;
+  if (g->pad_mode == DEI2I_PAD_REFLECT && g->pad > 0) return false;
+  if (g->Hs != g->H || g->Ws != g->W) return false;
+  if (g->kh != g->kw || g->kh > 16 || g->pad > 64 || g->stride > 8) return false;
+  if (k_channels % 64 != 0 || M % 128 != 0) return false;
+  return true;
+}
+
 }  // namespace dei2i
 
 using namespace dei2i;
@@ -603,6 +599,18 @@ extern "C" int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const
   ConvKParams p;
   memset(&p, 0, sizeof(p));
   const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
+  if (tma_applicable(g, g->Cin, (long long)g->N * Ho * Wo)) {
+    TmaConvParams t;
+    memset(&t, 0, sizeof(t));
+    t.Ho = Ho; t.Wo = Wo; t.M = (long long)g->N * Ho * Wo; t.stride = g->stride; t.lower = -g->pad;
+    t.kh = g->kh; t.kw = g->kw; t.flip = 0; t.cin_blocks = g->Cin / 64; t.num_kb = g->kh * g->kw * t.cin_blocks;
+    t.om.linear = 1;
+    t.e.scale = e->scale; t.e.bias = e->bias; t.e.noise = e->noise; t.e.noise_weight = e->noise_weight;
+    t.e.residual = (const __nv_bfloat16*)e->residual; t.e.out = y; t.e.act = e->act; t.e.out_fp32 = e->out_fp32;
+    t.e.ld = g->Cout_ld; t.e.ncols = g->Cout;
+    return run_conv_tma(x, g->N, g->H, g->W, g->Cin, w_fwd, g->Cout, g->kh * g->kw * g->Cin, t, g->pad - (g->kh - 1),
+                        (cudaStream_t)stream);
+  }
   p.g.src = (const __nv_bfloat16*)x;
   p.g.N = g->N; p.g.Hl = g->H; p.g.Wl = g->W; p.g.Hs = g->Hs; p.g.Ws = g->Ws; p.g.C = g->Cin;
   p.g.Ho = Ho; p.g.Wo = Wo; p.g.kh = g->kh; p.g.kw = g->kw; p.g.stride = g->stride; p.g.pad = g->pad;
@@ -626,6 +634,17 @@ extern "C" int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx,
   const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
   const bool full = g->pad_mode == DEI2I_PAD_REFLECT;
   const int Hd = full ? g->H + 2 * g->pad : g->H, Wd = full ? g->W + 2 * g->pad : g->W;
+  if (g->stride == 1 && tma_applicable(g, g->Cout_ld, (long long)g->N * Hd * Wd)) {
+    // dX = conv(dY, W) with filter offsets flipped: traversal over dY [N, Ho, Wo, Cout_ld], one position per dX pixel
+    TmaConvParams t;
+    memset(&t, 0, sizeof(t));
+    t.Ho = Hd; t.Wo = Wd; t.M = (long long)g->N * Hd * Wd; t.stride = 1; t.lower = g->pad - (g->kh - 1);
+    t.kh = g->kh; t.kw = g->kw; t.flip = 1; t.cin_blocks = g->Cout_ld / 64; t.num_kb = g->kh * g->kw * t.cin_blocks;
+    t.om.linear = 1;
+    t.e.scale = scale; t.e.out = dx; t.e.act = 0; t.e.out_fp32 = out_fp32; t.e.ld = g->Cin; t.e.ncols = g->Cin;
+    return run_conv_tma(dy, g->N, Ho, Wo, g->Cout_ld, w_dgrad, g->Cin, g->kh * g->kw * g->Cout_ld, t, -g->pad,
+                        (cudaStream_t)stream);
+  }
   p.g.src = (const __nv_bfloat16*)dy;
   p.g.N = g->N; p.g.Hl = Ho; p.g.Wl = Wo; p.g.Hs = Ho; p.g.Ws = Wo; p.g.C = g->Cout_ld;
   p.g.Ho = Hd; p.g.Wo = Wd; p.g.kh = g->kh; p.g.kw = g->kw; p.g.stride = g->stride; p.g.pad = g->pad;

@@ -92,6 +92,24 @@ __global__ void reflect_fold_kernel(const uint4* __restrict__ dxp, uint4* __rest
   dx[i] = pack8(acc);
 }
 
+// forward of F.pad(mode='reflect'): xp[n, hp, wp, :] = x[n, mirror(hp - pad), mirror(wp - pad), :]
+__global__ void reflect_pad_kernel(const uint4* __restrict__ x, uint4* __restrict__ xp, int N, int H, int W, int C8, int pad) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int Hp = H + 2 * pad, Wp = W + 2 * pad;
+  const long long total = (long long)N * Hp * Wp * C8;
+  if (i >= total) return;
+  const int c8 = (int)(i % C8);
+  long long t = i / C8;
+  const int wp = (int)(t % Wp);
+  t /= Wp;
+  const int hp = (int)(t % Hp);
+  const int n = (int)(t / Hp);
+  int h = hp - pad, w = wp - pad;
+  h = h < 0 ? -h : (h >= H ? 2 * H - 2 - h : h);
+  w = w < 0 ? -w : (w >= W ? 2 * W - 2 - w : w);
+  xp[i] = __ldg(x + (((long long)n * H + h) * W + w) * C8 + c8);
+}
+
 // ------------------------------------------------------------------------------------------ spectral norm
 // t_partial[rs, col] = sum_{row in chunk rs} W[row, col] * u[row]
 __global__ void sn_wt_u_kernel(const float* __restrict__ w, const float* __restrict__ u, int rows, int cols, int rows_per,
@@ -778,6 +796,13 @@ extern "C" int dei2i_reflect_fold(const void* dxp, void* dx, int N, int H, int W
   const long long total = (long long)N * H * W * (C / 8);
   reflect_fold_kernel<<<nblocks(total, 256), 256, 0, ST>>>((const uint4*)dxp, (uint4*)dx, N, H, W, C / 8, pad);
   return LAUNCH_OK("reflect_fold_kernel");
+}
+
+extern "C" int dei2i_reflect_pad(const void* x, void* xp, int N, int H, int W, int C, int pad, dei2i_stream stream) {
+  DEI2I_REQUIRE(x && xp && C % 8 == 0 && pad >= 0 && pad < H && pad < W, "reflect_pad: bad arguments");
+  const long long total = (long long)N * (H + 2 * pad) * (W + 2 * pad) * (C / 8);
+  reflect_pad_kernel<<<nblocks(total, 256), 256, 0, ST>>>((const uint4*)x, (uint4*)xp, N, H, W, C / 8, pad);
+  return LAUNCH_OK("reflect_pad_kernel");
 }
 
 extern "C" int dei2i_spectral_norm(const float* w, float* u, float* v, int rows, int cols, int do_power_iter, float eps,

@@ -120,6 +120,12 @@ class _Conv(Function):
     @staticmethod
     def forward(ctx, x, w_param, bias, noise_w, residual, wts: Weights, spec: ConvSpec, act, noise, out_fp32, logical_hw):
         assert not (act and residual is not None), "activation mask cannot be recovered once a residual is added"
+        # nn.Conv2d(padding_mode='reflect') = F.pad(reflect) + valid convolution (torch's own _conv_forward): the mirrored
+        # border is materialised once (it is also what wgrad re-reads), the convolution itself then runs on the TMA path
+        ctx.rpad = spec.pad if (spec.pad_mode == "reflect" and spec.pad > 0 and logical_hw is None) else 0
+        if ctx.rpad:
+            x = ops.reflect_pad(x, ctx.rpad)
+            spec = spec.unpadded()
         y = ops.conv2d_fwd(x, wts.w_fwd, spec, bias=bias, noise=noise, noise_weight=noise_w, residual=residual, act=act,
                            out_fp32=out_fp32, logical_hw=logical_hw, scale=wts.scale)
         ctx.wts, ctx.spec, ctx.act, ctx.noise, ctx.logical_hw = wts, spec, act, noise, logical_hw
@@ -152,6 +158,8 @@ class _Conv(Function):
         if ctx.needs_input_grad[0]:
             assert ctx.logical_hw is None, "no input gradient through a resized (label map) input"
             dx = ops.conv2d_dgrad(dy, wts.w_dgrad, spec, (x.shape[1], x.shape[2]), scale=wts.scale)
+            if ctx.rpad:
+                dx = ops.reflect_fold(dx, ctx.rpad)
         dw = None
         if ctx.needs_input_grad[1]:
             dw = torch.empty(spec.cout, spec.cin, spec.kh, spec.kw_, dtype=torch.float32, device=dy.device)
@@ -175,6 +183,10 @@ class _ConvCat(Function):
     def forward(ctx, x, wa, wb, ba, bb, spec: ConvSpec, out_fp32):
         w_fwd, w_dg = _pack_cat(wa, wb, spec)
         bias = torch.cat([ba.detach(), bb.detach()]) if ba is not None else None
+        ctx.rpad = spec.pad if (spec.pad_mode == "reflect" and spec.pad > 0) else 0
+        if ctx.rpad:
+            x = ops.reflect_pad(x, ctx.rpad)
+            spec = spec.unpadded()
         y = ops.conv2d_fwd(x, w_fwd, spec, bias=bias, out_fp32=out_fp32)
         ctx.spec, ctx.w_dg, ctx.ca, ctx.has_bias = spec, w_dg, wa.shape[0], ba is not None
         ctx.save_for_backward(x)
@@ -192,6 +204,8 @@ class _ConvCat(Function):
             _, db = ops.act_bwd(None, dy, None, want_dx=False, want_bias_grad=True)
             dba, dbb = db[:ca], db[ca: spec.cout]
         dx = ops.conv2d_dgrad(dy, ctx.w_dg, spec, (x.shape[1], x.shape[2])) if ctx.needs_input_grad[0] else None
+        if dx is not None and ctx.rpad:
+            dx = ops.reflect_fold(dx, ctx.rpad)
         dw = torch.empty(spec.cout, spec.cin, spec.kh, spec.kw_, dtype=torch.float32, device=dy.device)
         ops.conv2d_wgrad(x, dy, dw, spec)
         return dx, dw[:ca], dw[ca:], dba, dbb, None, None

@@ -94,6 +94,10 @@ class ConvSpec:
         return ConvGeom(n, h, w, hs or h, ws or w, self.cin_ld, self.cout, self.cout_ld, self.kh, self.kw_, self.stride,
                         self.pad, PAD[self.pad_mode])
 
+    def unpadded(self) -> "ConvSpec":
+        """The same convolution over an input that already carries its (reflect) padding: pad = 0, 'zeros'."""
+        return ConvSpec(self.cin, self.cout, self.k, self.stride, 0, "zeros", self.kw)
+
     def tag(self, n, h, w) -> str:
         return f"N{n} {self.cin}->{self.cout} {self.kh}x{self.kw_} s{self.stride} p{self.pad}{self.pad_mode[0]} in{h}x{w}"
 
@@ -164,6 +168,25 @@ def conv2d_dgrad(dy, w_dgrad, spec: ConvSpec, in_hw, scale=None):
     dx = torch.empty(n, h, w, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
     with _Timed("conv_dgrad", flops, spec.tag(n, h, w)):
         check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dx), C.byref(g), _p(scale), 0, _stream()), "dei2i_conv2d_dgrad")
+    return dx
+
+
+def reflect_pad(x, pad: int):
+    """bf16 [N,H,W,C] -> [N,H+2p,W+2p,C], F.pad(mode='reflect')."""
+    _chk_act(x, "x")
+    n, h, w, c = x.shape
+    xp = torch.empty(n, h + 2 * pad, w + 2 * pad, c, dtype=torch.bfloat16, device=x.device)
+    check(_lib.load().dei2i_reflect_pad(_p(x), _p(xp), n, h, w, c, pad, _stream()), "dei2i_reflect_pad")
+    return xp
+
+
+def reflect_fold(dxp, pad: int):
+    """backward of reflect_pad: bf16 [N,H+2p,W+2p,C] -> [N,H,W,C]."""
+    _chk_act(dxp, "dxp")
+    n, hp, wp, c = dxp.shape
+    h, w = hp - 2 * pad, wp - 2 * pad
+    dx = torch.empty(n, h, w, c, dtype=torch.bfloat16, device=dxp.device)
+    check(_lib.load().dei2i_reflect_fold(_p(dxp), _p(dx), n, h, w, c, pad, _stream()), "dei2i_reflect_fold")
     return dx
 
 

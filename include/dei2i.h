@@ -81,6 +81,12 @@ int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx, const dei2
 /* dx[n,h,w,c] = sum of dxp over all padded positions that reflect onto (h,w); bf16 in / bf16 out */
 int dei2i_reflect_fold(const void* dxp, void* dx, int N, int H, int W, int C, int pad, dei2i_stream stream);
 
+/* F.pad(x, (pad,)*4, mode='reflect') (what nn.Conv2d(padding_mode='reflect') does before its convolution,
+ * architecture.py:95-100): x bf16 [N,H,W,C] -> xp bf16 [N,H+2p,W+2p,C].  The TMA-fed convolution kernels take zero / no
+ * padding only (TMA fills out-of-bounds with zeros, it cannot mirror), so a reflect convolution is this followed by a
+ * pad = 0 convolution; its backward is dei2i_conv2d_dgrad over the padded domain followed by dei2i_reflect_fold. */
+int dei2i_reflect_pad(const void* x, void* xp, int N, int H, int W, int C, int pad, dei2i_stream stream);
+
 /* Gradient w.r.t. the weight (autograd of nn.Conv2d), split over pixels, deterministic two-pass reduction.
  *   dw  fp32 [Cout, Cin_real, kh, kw]; written (beta = 0) or accumulated (beta = 1).
  *   workspace: dei2i_conv2d_wgrad_workspace(g) bytes of device scratch.

@@ -66,6 +66,12 @@ CONV_CASES = {
     "ragged_m": (1, 64, 10, 10, 64, 3, 1, 1, "reflect", False, None),
     "d_conv0": (2, 3, 32, 32, 64, 4, 2, 1, "reflect", False, None),
     "d_src_1": (2, 128, 4, 4, 1, 3, 1, 1, "reflect", False, None),
+    # TMA-im2col path (zero / no padding, Cin % 64 == 0, M % 128 == 0)
+    "tma_valid3x3": (2, 64, 18, 18, 64, 3, 1, 0, "zeros", False, None),
+    "tma_valid4x4s2": (2, 64, 34, 34, 128, 4, 2, 0, "zeros", False, None),
+    "tma_zero3x3_256": (1, 256, 16, 16, 256, 3, 1, 1, "zeros", True, None),
+    "tma_persistent_200tiles": (4, 64, 80, 80, 64, 3, 1, 1, "zeros", False, None),
+    "tma_valid7x7": (2, 64, 22, 22, 64, 7, 1, 0, "zeros", False, None),
     "narrow_16_32": (2, 16, 12, 12, 32, 3, 1, 1, "reflect", False, None),   # reduced-width nets of the golden fixtures
     "narrow_s2_8_16": (2, 8, 16, 16, 16, 4, 2, 1, "reflect", False, None),
 }
@@ -98,6 +104,46 @@ def test_conv_fwd(case):
         assert y[..., cout:].abs().max().item() == 0.0
 
 
+def test_reflect_pad_and_fold():
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(2)
+    for pad in (1, 3):
+        x = q(torch.randn(2, 16, 9, 11, generator=g)).requires_grad_(True)
+        ref = F.pad(x, (pad,) * 4, mode="reflect")
+        xp = ops.reflect_pad(to_dev(x.detach()), pad)
+        assert torch.equal(from_dev(xp, 16), ref.detach())
+        dyp = q(torch.randn(ref.shape, generator=g))
+        (dx_ref,) = torch.autograd.grad(ref, x, dyp)
+        dx = ops.reflect_fold(to_dev(dyp), pad)
+        assert rel_err(from_dev(dx, 16), dx_ref) < TOL_BF16
+
+
+def test_conv_tma_path_epilogue_matches_gather_path():
+    """Same convolution through the TMA-im2col kernel and through the cp.async-gather kernel (tuning knob conv_path)."""
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(5)
+    n, c, h, w = 2, 64, 16, 16
+    x, wt = q(torch.randn(n, c, h, w, generator=g)), q(torch.randn(128, c, 3, 3, generator=g) / 24)
+    noise = torch.randn(n, 1, h, w, generator=g).cuda().contiguous()
+    nw, sc = torch.tensor([0.3]).cuda(), torch.tensor([0.7]).cuda()
+    bias = torch.randn(128, generator=g).cuda()
+    res = q(torch.randn(n, 128, h, w, generator=g))
+    spec = ops.ConvSpec(c, 128, 3, 1, 1, "zeros")
+    w_fwd, _ = ops.pack_weight(wt.cuda(), spec, need_dgrad=False)
+    outs = []
+    for path in (0, 1):
+        ops.set_tuning("conv_path", path)
+        try:
+            outs.append(ops.conv2d_fwd(to_dev(x), w_fwd, spec, bias=bias, noise=noise, noise_weight=nw, residual=to_dev(res),
+                                       scale=sc).float().cpu())
+            outs.append(ops.conv2d_fwd(to_dev(x), w_fwd, spec, bias=bias, act="leaky_relu", out_fp32=True).cpu())
+        finally:
+            ops.set_tuning("conv_path", 0)
+    ref = 0.7 * ref_conv(x, wt, None, 1, 1, "zeros") + bias.cpu()[None, :, None, None] + 0.3 * noise.cpu() + res
+    assert rel_err(outs[0].permute(0, 3, 1, 2), ref) < TOL_BF16
+    assert rel_err(outs[0], outs[2]) < 1e-2 and rel_err(outs[1], outs[3]) < 1e-3
+
+
 def test_conv_fwd_fp32_out_and_epilogue():
     from de_i2i_gan_b200 import ops
     g = torch.Generator().manual_seed(5)
@@ -121,7 +167,8 @@ def test_conv_fwd_fp32_out_and_epilogue():
 
 
 DGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "spade_gb_512", "heads_4", "ragged_m", "d_src_1", "cls_valid_k2",
-               "narrow_16_32", "narrow_s2_8_16"]
+               "narrow_16_32", "narrow_s2_8_16", "tma_valid3x3", "tma_zero3x3_256", "tma_persistent_200tiles", "tma_valid4x4s2",
+               "tma_valid7x7"]
 
 
 @pytest.mark.parametrize("case", DGRAD_CASES)
@@ -143,7 +190,8 @@ def test_conv_dgrad(case):
 
 
 WGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "stem7x7", "spade_shared_8x8seg", "spade_gb_512", "heads_4",
-               "ragged_m", "d_conv0", "d_src_1", "cls_valid_k2", "narrow_16_32", "narrow_s2_8_16"]
+               "ragged_m", "d_conv0", "d_src_1", "cls_valid_k2", "narrow_16_32", "narrow_s2_8_16", "tma_valid3x3",
+               "tma_zero3x3_256", "tma_persistent_200tiles", "tma_valid4x4s2"]
 
 
 @pytest.mark.parametrize("case", WGRAD_CASES)

@@ -41,9 +41,27 @@ struct TmaConvParams {
   int cin_blocks;  // input channels / 64
   int num_kb;      // taps * cin_blocks
   int m_tiles, n_tiles;
+  int dbg;         // experiments only (tuning knob tma_dbg): bit0 skip stores, bit1 skip TMEM loads, bit2 skip MMA wait
   OutMap om;
   Epilogue e;
 };
+
+struct TmaWgradParams {
+  int Ho, Wo;        // output (dY) domain per image = traversal domain of the im2col descriptor over x
+  long long M;       // N * Ho * Wo
+  int stride, lower, kw;
+  int cin_blocks;    // Cin / 64
+  int num_boxes;     // taps * cin_blocks  (64-wide K slices of the packed weight layout)
+  int k_tiles;       // ceil(num_boxes / 4)
+  int co_groups;     // ceil(Cout / (128 * CO_T))
+  int splits, pb_per_split, num_pb;  // 64-pixel blocks
+  float* partial;    // [splits, Cout, Kf] fp32
+  int cout, Kf;
+};
+
+void wgrad_tma_plan(TmaWgradParams& p);
+int run_wgrad_tma(const void* x, int N, int H, int W, int C, const void* dy, int cout_ld, TmaWgradParams& p, int upper,
+                  cudaStream_t st);
 
 // returns 0 on success; the caller has checked applicability (see tma_conv_applicable)
 int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, int rows, int K, const TmaConvParams& p,

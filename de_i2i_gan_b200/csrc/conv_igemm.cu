@@ -657,6 +657,24 @@ extern "C" int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx,
   return run_igemm(p, w_dgrad, g->Cin, K, (cudaStream_t)stream);
 }
 
+static bool wgrad_tma_applicable(const dei2i_conv_geom* g, long long M) {
+  if (g_tune_conv_path == 1) return false;
+  if (g->pad_mode == DEI2I_PAD_REFLECT && g->pad > 0) return false;
+  if (g->Hs != g->H || g->Ws != g->W) return false;
+  if (g->kh != g->kw || g->kh > 16 || g->pad > 64 || g->stride > 8) return false;
+  return g->Cin % 64 == 0 && M % 64 == 0 && g->Cout_ld >= 64;
+}
+static void fill_wgrad_tma(const dei2i_conv_geom* g, TmaWgradParams& t) {
+  memset(&t, 0, sizeof(t));
+  t.Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad);
+  t.Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
+  t.M = (long long)g->N * t.Ho * t.Wo;
+  t.stride = g->stride; t.lower = -g->pad; t.kw = g->kw; t.cin_blocks = g->Cin / 64;
+  t.num_boxes = g->kh * g->kw * t.cin_blocks;
+  t.cout = g->Cout; t.Kf = g->kh * g->kw * g->Cin;
+  wgrad_tma_plan(t);
+}
+
 static void wgrad_plan(const dei2i_conv_geom* g, int& bn, int& splits, int& pb_per_split, int& num_pb, int& Kf) {
   const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
   const long long M = (long long)g->N * Ho * Wo;
@@ -682,6 +700,14 @@ extern "C" size_t dei2i_conv2d_wgrad_workspace(const dei2i_conv_geom* g, int Cin
   int bn, splits, pbs, npb, Kf;
   wgrad_plan(g, bn, splits, pbs, npb, Kf);
   if (g->Cout_ld < 64) splits = 1;
+  {
+    const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
+    if (wgrad_tma_applicable(g, (long long)g->N * Ho * Wo)) {
+      TmaWgradParams t;
+      fill_wgrad_tma(g, t);
+      if (t.splits > splits) splits = t.splits;
+    }
+  }
   return (size_t)splits * g->Cout * Kf * sizeof(float) + 1024 * sizeof(float) + 256;
 }
 
@@ -721,7 +747,13 @@ extern "C" int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int 
   p.g.M = (long long)g->N * Ho * Wo;
   float* partial = (float*)workspace;
   const int taps = g->kh * g->kw;
-  if (g->Cout_ld < 64) {
+  if (wgrad_tma_applicable(g, p.g.M)) {
+    TmaWgradParams t;
+    fill_wgrad_tma(g, t);
+    t.partial = partial;
+    splits = t.splits;
+    if (int rc = run_wgrad_tma(x, g->N, g->H, g->W, g->Cin, dy, g->Cout_ld, t, g->pad - (g->kh - 1), st)) return rc;
+  } else if (g->Cout_ld < 64) {
     splits = 1;
     DEI2I_CUDA(cudaMemsetAsync(partial, 0, (size_t)g->Cout * Kf * sizeof(float), st));
     const int ppb = 256;

@@ -27,7 +27,8 @@ template <int BLOCK_N, int STAGES>
 struct TmaSmem {
   static constexpr int kBTile = BLOCK_N * 128;
   static constexpr int kStage = kTmaATile + kBTile;
-  static constexpr int kBarOff = STAGES * kStage;
+  static constexpr int kStageOut = STAGES * kStage;     // 4 epilogue warps x 4 KB output staging
+  static constexpr int kBarOff = kStageOut + 4 * 4096;
   static constexpr int kTotal = kBarOff + (2 * STAGES + 4) * 8 + 16 + 1024 /*alignment slack*/;
 };
 
@@ -157,48 +158,93 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       if (e.noise != nullptr && row_ok) nz = __ldg(e.noise + m) * nzw;
       mbar_wait(&tfull_bar[buf], bph);
       tc_fence_after();
+      // 128 bytes of output per row and pass: 64 bf16 columns or 32 fp32 columns.  Each lane finalises its own row,
+      // parks it in the warp's 4 KB staging tile (16-byte chunks XOR-swizzled by row: conflict-free both ways) and the
+      // warp then writes 4 full 128-byte rows per store instruction (8 lanes x 16 B per row) - coalesced, whatever the
+      // row -> address map is.  The residual comes in through the same tile, transposed the other way.
+      uint8_t* stage = smem + S::kStageOut + warp * 4096;
+      const int CW = e.out_fp32 ? 32 : 64;  // columns per pass
+      const int sub_r = lane >> 3, sub_j = lane & 7;
 #pragma unroll 1
-      for (int c = 0; c < BLOCK_N; c += 32) {
-        uint32_t v[32];
-        tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + buf * BLOCK_N + (uint32_t)c, v);
-        tc_wait_ld();
+      for (int c = 0; c < BLOCK_N; c += CW) {
         const int nbase = n0 + c;
-        if (row_ok && nbase < e.ld) {
-          float f[32];
+        if (nbase >= e.ld) break;
+        float f[64];
+        {
+          uint32_t v[32];
+          if (!(p.dbg & 2)) tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + buf * BLOCK_N + (uint32_t)c, v);
+          if (!(p.dbg & 2)) tc_wait_ld();
 #pragma unroll
-          for (int t = 0; t < 32; ++t) {
-            float x = __uint_as_float(v[t]) * osc;
-            const int n = nbase + t;
-            if (e.bias != nullptr && n < e.ncols) x += __ldg(e.bias + n);
-            x += nz;
-            f[t] = apply_act(x, e.act);
+          for (int t = 0; t < 32; ++t) f[t] = __uint_as_float(v[t]) * osc;
+          if (CW == 64) {
+            if (!(p.dbg & 2)) tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + buf * BLOCK_N + (uint32_t)(c + 32), v);
+            if (!(p.dbg & 2)) tc_wait_ld();
+#pragma unroll
+            for (int t = 0; t < 32; ++t) f[32 + t] = __uint_as_float(v[t]) * osc;
           }
-          if (e.residual != nullptr) {
-            const __nv_bfloat16* rp = e.residual + m * e.ld + nbase;
+        }
+        if (e.bias != nullptr) {
 #pragma unroll
-            for (int t8 = 0; t8 < 32; t8 += 8) {
-              if (nbase + t8 < e.ld) {
-                float rr[8];
-                unpack8_bf16(__ldg(reinterpret_cast<const uint4*>(rp + t8)), rr);
-#pragma unroll
-                for (int k = 0; k < 8; ++k) f[t8 + k] += rr[k];
+          for (int t4 = 0; t4 < 64; t4 += 4) {
+            if (t4 < CW && nbase + t4 < e.ncols) {  // ncols (= Cout) may end inside a group of 4 only when Cout % 4 != 0
+              if (nbase + t4 + 3 < e.ncols) {
+                const float4 bv = __ldg(reinterpret_cast<const float4*>(e.bias + nbase + t4));
+                f[t4] += bv.x; f[t4 + 1] += bv.y; f[t4 + 2] += bv.z; f[t4 + 3] += bv.w;
+              } else {
+                for (int k = 0; k < 4; ++k)
+                  if (nbase + t4 + k < e.ncols) f[t4 + k] += __ldg(e.bias + nbase + t4 + k);
               }
             }
           }
-          if (e.out_fp32) {
-            float* op = reinterpret_cast<float*>(e.out) + orow * e.ld + nbase;
-#pragma unroll
-            for (int t4 = 0; t4 < 32; t4 += 4)
-              if (nbase + t4 < e.ld) *reinterpret_cast<float4*>(op + t4) = make_float4(f[t4], f[t4 + 1], f[t4 + 2], f[t4 + 3]);
-          } else {
-            __nv_bfloat16* op = reinterpret_cast<__nv_bfloat16*>(e.out) + orow * e.ld + nbase;
-#pragma unroll
-            for (int t8 = 0; t8 < 32; t8 += 8)
-              if (nbase + t8 < e.ld)
-                *reinterpret_cast<uint4*>(op + t8) = make_uint4(pack_bf16(f[t8], f[t8 + 1]), pack_bf16(f[t8 + 2], f[t8 + 3]),
-                                                                pack_bf16(f[t8 + 4], f[t8 + 5]), pack_bf16(f[t8 + 6], f[t8 + 7]));
-          }
         }
+        if (e.noise != nullptr || e.act != ACT_NONE) {
+#pragma unroll
+          for (int t = 0; t < 64; ++t)
+            if (t < CW) f[t] = apply_act(f[t] + nz, e.act);
+        }
+        if (e.residual != nullptr) {  // bf16 [M, ld], linear rows; only with bf16 output (CW == 64)
+#pragma unroll
+          for (int itr = 0; itr < 8; ++itr) {
+            const int r = itr * 4 + sub_r;
+            const long long mr = (long long)m_tile * 128 + warp * 32 + r;
+            uint4 rv = make_uint4(0, 0, 0, 0);
+            if (mr < p.M && nbase + sub_j * 8 < e.ld) rv = __ldg(reinterpret_cast<const uint4*>(e.residual + mr * e.ld + nbase + sub_j * 8));
+            *reinterpret_cast<uint4*>(stage + r * 128 + ((sub_j ^ (r & 7)) << 4)) = rv;
+          }
+          __syncwarp();
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float rr[8];
+            unpack8_bf16(*reinterpret_cast<const uint4*>(stage + lane * 128 + ((j ^ (lane & 7)) << 4)), rr);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) f[j * 8 + k] += rr[k];
+          }
+          __syncwarp();
+        }
+        if (e.out_fp32) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<float4*>(stage + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            *reinterpret_cast<uint4*>(stage + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                make_uint4(pack_bf16(f[8 * j], f[8 * j + 1]), pack_bf16(f[8 * j + 2], f[8 * j + 3]), pack_bf16(f[8 * j + 4], f[8 * j + 5]),
+                           pack_bf16(f[8 * j + 6], f[8 * j + 7]));
+        }
+        __syncwarp();
+        const int esz = e.out_fp32 ? 4 : 2;
+        const int col = nbase + sub_j * (16 / esz);  // first column of this lane's 16-byte chunk
+#pragma unroll
+        for (int itr = 0; itr < 8; ++itr) {
+          const int r = itr * 4 + sub_r;
+          const long long orow_r = __shfl_sync(0xffffffffu, orow, r);
+          const int ok_r = __shfl_sync(0xffffffffu, (int)row_ok, r);
+          const uint4 val = *reinterpret_cast<const uint4*>(stage + r * 128 + ((sub_j ^ (r & 7)) << 4));
+          if (ok_r && col < e.ld && !(p.dbg & 1))
+            *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(e.out) + (orow_r * e.ld + col) * esz) = val;
+        }
+        __syncwarp();
       }
       tc_fence_before();
       mbar_arrive(&tempty_bar[buf]);
@@ -240,9 +286,11 @@ static int launch_tma(const CUtensorMap& ta, const CUtensorMap& tb, const TmaCon
   return check_cuda(cudaGetLastError(), "conv_tma_kernel launch");
 }
 
+extern int g_tune_tma_dbg;
 int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, int rows, int K, const TmaConvParams& p_in,
                  int upper, cudaStream_t st) {
   TmaConvParams p = p_in;
+  p.dbg = g_tune_tma_dbg;
   int bn = 256;
   while (bn > 64 && bn / 2 >= rows) bn /= 2;
   CUtensorMap ta, tb;
@@ -257,6 +305,204 @@ int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, in
     case 128: return launch_tma<128, 6>(ta, tb, p, st);
     default: return launch_tma<64, 8>(ta, tb, p, st);
   }
+}
+
+
+
+// ======================================================================================================================
+// wgrad:  P[co, k] = sum_{m in split} dY[m, co] * A[m, k]      (k = (tap, ci); reduction over output pixels m)
+//   per stage: 64 pixels.  MMA "A" = dY tile [64 pix x 128*CO_T co] (tiled TMA, MN-major), MMA "B" = up to four im2col
+//   boxes [64 pix x 64 ci] of x, one per (tap, 64-channel block) (im2col TMA, MN-major): N' = 64 * boxes.
+//   CO_T = 2 keeps TWO accumulators (co 0-127 and 128-255) on the same B boxes: 64 KB of operands per 2 x 512 MMA cycles.
+//   One work tile per CTA: (co group, k tile, pixel split); FP32 partial tiles go to the workspace through the
+//   coalescing staging tile; wgrad_reduce_kernel (conv_igemm.cu) sums the splits in a fixed order.
+template <int CO_T, int STAGES>
+struct WgTmaSmem {
+  static constexpr int kATile = CO_T * 16384;  // 64 pix x 128*CO_T co
+  static constexpr int kBTile = 4 * 8192;      // 4 boxes of 64 pix x 64 ci
+  static constexpr int kStage = kATile + kBTile;
+  static constexpr int kStageOut = STAGES * kStage;
+  static constexpr int kBarOff = kStageOut + 4 * 4096;
+  static constexpr int kTotal = kBarOff + (2 * STAGES + 1) * 8 + 16 + 1024;
+};
+
+template <int CO_T, int STAGES>
+__global__ void __launch_bounds__(kTmaThreads, 1)
+wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ CUtensorMap tmap_x, const TmaWgradParams p) {
+  using S = WgTmaSmem<CO_T, STAGES>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tfull_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  constexpr uint32_t kTmemCols = CO_T * 256;
+
+  // work tile
+  int t = blockIdx.x;
+  const int split = t % p.splits;
+  t /= p.splits;
+  const int k_tile = t % p.k_tiles;
+  const int co_group = t / p.k_tiles;
+  const int box0 = k_tile * 4;
+  const int nb = min(4, p.num_boxes - box0);  // boxes in this tile
+  const int co0 = co_group * 128 * CO_T;
+  const int pb0 = split * p.pb_per_split;
+  const int pb1 = min(p.num_pb, pb0 + p.pb_per_split);
+  const int nsteps = pb1 - pb0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tfull_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 4 && lane == 0) {
+    tma_prefetch_desc(&tmap_dy);
+    tma_prefetch_desc(&tmap_x);
+  }
+  if (warp == 5) tmem_alloc(tmem_ptr_smem, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 4) {
+    if (lane == 0 && nsteps > 0) {
+      const int HoWo = p.Ho * p.Wo;
+      // filter offsets of this tile's boxes
+      int b_cb[4], b_s[4], b_r[4];
+      for (int g = 0; g < 4; ++g) {
+        const int bx = box0 + (g < nb ? g : 0);
+        const int tap = bx / p.cin_blocks;
+        b_cb[g] = bx - tap * p.cin_blocks;
+        b_r[g] = tap / p.kw;
+        b_s[g] = tap - b_r[g] * p.kw;
+      }
+      const uint32_t stage_bytes = (uint32_t)(S::kATile + nb * 8192);
+      for (int it = 0; it < nsteps; ++it) {
+        const uint32_t stage = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1u;
+        mbar_wait(&empty_bar[stage], ph ^ 1u);
+        uint8_t* a_dst = smem + stage * S::kStage;
+        uint8_t* b_dst = a_dst + S::kATile;
+        mbar_arrive_expect_tx(&full_bar[stage], stage_bytes);
+        const long long m0 = (long long)(pb0 + it) * 64;
+#pragma unroll
+        for (int h = 0; h < 2 * CO_T; ++h) tma_load_2d(a_dst + h * 8192, &tmap_dy, &full_bar[stage], co0 + h * 64, (int)m0);
+        const int img = (int)(m0 / HoWo);
+        const int rem = (int)(m0 - (long long)img * HoWo);
+        const int pr = rem / p.Wo;
+        const int qc = rem - pr * p.Wo;
+        const int cw = qc * p.stride + p.lower, ch = pr * p.stride + p.lower;
+        for (int g = 0; g < nb; ++g)
+          tma_load_im2col_4d(b_dst + g * 8192, &tmap_x, &full_bar[stage], b_cb[g] * 64, cw, ch, img, (uint16_t)b_s[g], (uint16_t)b_r[g]);
+      }
+    }
+  } else if (warp == 5) {
+    if (lane == 0 && nsteps > 0) {
+      const uint32_t idesc = make_idesc_bf16(128, nb * 64, 1, 1);
+      for (int it = 0; it < nsteps; ++it) {
+        const uint32_t stage = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1u;
+        mbar_wait(&full_bar[stage], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + stage * S::kStage);
+        const uint32_t b_addr = a_addr + S::kATile;
+        // MN-major, 128B swizzle: LBO = stride between 64-element MN atoms (8192 B), SBO = between 8-row K groups (1024 B)
+        const uint64_t b_desc = make_smem_desc(b_addr, 8192, 1024, 2);
+#pragma unroll
+        for (int ct = 0; ct < CO_T; ++ct) {
+          const uint64_t a_desc = make_smem_desc(a_addr + ct * 16384, 8192, 1024, 2);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)  // 16 pixels = 2 K atoms = 2048 B per MMA
+            tc_mma_bf16(tmem_base + ct * 256, a_desc + (uint64_t)(128 * k), b_desc + (uint64_t)(128 * k), idesc, (it | k) != 0);
+        }
+        tc_commit(&empty_bar[stage]);
+      }
+      tc_commit(tfull_bar);
+    }
+  } else if (nsteps > 0) {
+    // epilogue: fp32 partial tile -> workspace [split, co, Kf], rows = co, 32 columns (128 B) per pass, coalesced
+    mbar_wait(tfull_bar, 0);
+    tc_fence_after();
+    uint8_t* stage = smem + S::kStageOut + warp * 4096;
+    const int sub_r = lane >> 3, sub_j = lane & 7;
+    const int k0 = box0 * 64;
+#pragma unroll 1
+    for (int ct = 0; ct < CO_T; ++ct) {
+      const int co_w = co0 + ct * 128 + warp * 32;  // first row of this warp
+      if (co_w >= p.cout) break;
+#pragma unroll 1
+      for (int c = 0; c < nb * 64; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + ct * 256 + (uint32_t)c, v);
+        tc_wait_ld();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(stage + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        __syncwarp();
+#pragma unroll
+        for (int itr = 0; itr < 8; ++itr) {
+          const int r = itr * 4 + sub_r;
+          const uint4 val = *reinterpret_cast<const uint4*>(stage + r * 128 + ((sub_j ^ (r & 7)) << 4));
+          if (co_w + r < p.cout)
+            *reinterpret_cast<uint4*>(p.partial + ((long long)split * p.cout + co_w + r) * p.Kf + k0 + c + sub_j * 4) = val;
+        }
+        __syncwarp();
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+template <int CO_T, int ST>
+static int launch_wgrad_tma(const CUtensorMap& tdy, const CUtensorMap& tx, const TmaWgradParams& p, cudaStream_t st) {
+  using S = WgTmaSmem<CO_T, ST>;
+  static_assert(S::kTotal <= 227 * 1024 && S::kTotal > 114 * 1024, "shared memory budget / one CTA per SM");
+  static bool attr_done = false;
+  if (!attr_done) {
+    DEI2I_CUDA(cudaFuncSetAttribute(wgrad_tma_kernel<CO_T, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+    attr_done = true;
+  }
+  const int grid = p.co_groups * p.k_tiles * p.splits;
+  wgrad_tma_kernel<CO_T, ST><<<grid, kTmaThreads, S::kTotal, st>>>(tdy, tx, p);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "wgrad_tma_kernel launch");
+}
+
+// plan shared with the workspace-size query: fills co_groups / k_tiles / splits / pb_per_split / num_pb
+void wgrad_tma_plan(TmaWgradParams& p) {
+  const int co_t = p.cout > 128 ? 2 : 1;
+  p.co_groups = (p.cout + 128 * co_t - 1) / (128 * co_t);
+  p.k_tiles = (p.num_boxes + 3) / 4;
+  p.num_pb = (int)((p.M + 63) / 64);
+  const int tiles = p.co_groups * p.k_tiles;
+  int splits = num_sms() / tiles;
+  if (splits < 1) splits = 1;
+  while (splits > 1 && p.num_pb / splits < 4) --splits;
+  p.pb_per_split = (p.num_pb + splits - 1) / splits;
+  p.splits = (p.num_pb + p.pb_per_split - 1) / p.pb_per_split;
+}
+
+int run_wgrad_tma(const void* x, int N, int H, int W, int C, const void* dy, int cout_ld, TmaWgradParams& p, int upper,
+                  cudaStream_t st) {
+  CUtensorMap tdy, tx;
+  if (int rc = encode_tmap_2d_bf16(&tdy, dy, (uint64_t)cout_ld, (uint64_t)p.M, (uint64_t)cout_ld * 2, 64, 64, 1)) return rc;
+  if (int rc = encode_tmap_im2col_bf16(&tx, x, (uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N, p.lower, upper, (uint32_t)p.stride, 64, 64))
+    return rc;
+  if (p.cout > 128) return launch_wgrad_tma<2, 3>(tdy, tx, p, st);
+  return launch_wgrad_tma<1, 4>(tdy, tx, p, st);
 }
 
 }  // namespace dei2i

@@ -39,6 +39,10 @@ struct TmaConvParams {
   int kh, kw;      // filter size (tap t = r * kw + s)
   int flip;        // 1: TMA filter offsets are (kh-1-r, kw-1-s) - dgrad as a convolution over dY with the un-flipped weight pack
   int cin_blocks;  // input channels / 64
+  // weight-matrix column block of tap (r, s): ((b_py + b_sub*r) * b_kw + (b_px + b_sub*s)) * cin_blocks + cb.
+  // Plain convolutions: b_sub = 1, b_py = b_px = 0, b_kw = kw.  Strided dgrad = stride^2 stride-1 sub-convolutions over dY,
+  // one per output parity (py, px), each using every stride-th tap of the full filter.
+  int b_sub, b_py, b_px, b_kw;
   int num_kb;      // taps * cin_blocks
   int m_tiles, n_tiles;
   int dbg;         // experiments only (tuning knob tma_dbg): bit0 skip stores, bit1 skip TMEM loads, bit2 skip MMA wait

@@ -583,7 +583,8 @@ static bool tma_applicable(const dei2i_conv_geom* g, int k_channels, long long M
   if (g->pad_mode == DEI2I_PAD_REFLECT && g->pad > 0) return false;
   if (g->Hs != g->H || g->Ws != g->W) return false;
   if (g->kh != g->kw || g->kh > 16 || g->pad > 64 || g->stride > 8) return false;
-  if (k_channels % 64 != 0 || M % 128 != 0) return false;
+  (void)M;  // a ragged last tile is fine: im2col TMA zero-fills past the end of the tensor, the epilogue masks rows >= M
+  if (k_channels % 64 != 0) return false;
   return true;
 }
 
@@ -604,6 +605,7 @@ extern "C" int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const
     memset(&t, 0, sizeof(t));
     t.Ho = Ho; t.Wo = Wo; t.M = (long long)g->N * Ho * Wo; t.stride = g->stride; t.lower = -g->pad;
     t.kh = g->kh; t.kw = g->kw; t.flip = 0; t.cin_blocks = g->Cin / 64; t.num_kb = g->kh * g->kw * t.cin_blocks;
+    t.b_sub = 1; t.b_kw = g->kw;
     t.om.linear = 1;
     t.e.scale = e->scale; t.e.bias = e->bias; t.e.noise = e->noise; t.e.noise_weight = e->noise_weight;
     t.e.residual = (const __nv_bfloat16*)e->residual; t.e.out = y; t.e.act = e->act; t.e.out_fp32 = e->out_fp32;
@@ -632,6 +634,27 @@ extern "C" int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx,
   ConvKParams p;
   memset(&p, 0, sizeof(p));
   const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
+  if (g->stride > 1 && g->pad == 0 && g->kh % g->stride == 0 && (g->H - g->kh) % g->stride == 0 &&
+      (g->W - g->kw) % g->stride == 0 && tma_applicable(g, g->Cout_ld, 0)) {
+    // fractionally-strided ("transposed") convolution as stride^2 dense stride-1 sub-convolutions over dY:
+    //   dX[s*a + py, s*b + px] = sum_{t,u} dY[a - t, b - u] * W[py + s*t, px + s*u]      (no multiply-by-zero work)
+    const int sd = g->stride, kt = g->kh / sd;
+    for (int py = 0; py < sd; ++py)
+      for (int px = 0; px < sd; ++px) {
+        TmaConvParams t;
+        memset(&t, 0, sizeof(t));
+        t.Ho = g->H / sd; t.Wo = g->W / sd; t.M = (long long)g->N * t.Ho * t.Wo; t.stride = 1; t.lower = -(kt - 1);
+        t.kh = kt; t.kw = kt; t.flip = 1; t.cin_blocks = g->Cout_ld / 64; t.num_kb = kt * kt * t.cin_blocks;
+        t.b_sub = sd; t.b_py = py; t.b_px = px; t.b_kw = g->kw;
+        t.om.linear = 0; t.om.Ho = t.Ho; t.om.Wo = t.Wo; t.om.OH = g->H; t.om.OW = g->W; t.om.osy = sd; t.om.osx = sd;
+        t.om.oy0 = py; t.om.ox0 = px;
+        t.e.scale = scale; t.e.out = dx; t.e.act = 0; t.e.out_fp32 = out_fp32; t.e.ld = g->Cin; t.e.ncols = g->Cin;
+        if (int rc = run_conv_tma(dy, g->N, Ho, Wo, g->Cout_ld, w_dgrad, g->Cin, g->kh * g->kw * g->Cout_ld, t, 0,
+                                  (cudaStream_t)stream))
+          return rc;
+      }
+    return 0;
+  }
   const bool full = g->pad_mode == DEI2I_PAD_REFLECT;
   const int Hd = full ? g->H + 2 * g->pad : g->H, Wd = full ? g->W + 2 * g->pad : g->W;
   if (g->stride == 1 && tma_applicable(g, g->Cout_ld, (long long)g->N * Hd * Wd)) {
@@ -640,6 +663,7 @@ extern "C" int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx,
     memset(&t, 0, sizeof(t));
     t.Ho = Hd; t.Wo = Wd; t.M = (long long)g->N * Hd * Wd; t.stride = 1; t.lower = g->pad - (g->kh - 1);
     t.kh = g->kh; t.kw = g->kw; t.flip = 1; t.cin_blocks = g->Cout_ld / 64; t.num_kb = g->kh * g->kw * t.cin_blocks;
+    t.b_sub = 1; t.b_kw = g->kw;
     t.om.linear = 1;
     t.e.scale = scale; t.e.out = dx; t.e.act = 0; t.e.out_fp32 = out_fp32; t.e.ld = g->Cin; t.e.ncols = g->Cin;
     return run_conv_tma(dy, g->N, Ho, Wo, g->Cout_ld, w_dgrad, g->Cin, g->kh * g->kw * g->Cout_ld, t, -g->pad,

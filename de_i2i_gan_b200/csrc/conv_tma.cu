@@ -95,7 +95,8 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           const int os = p.flip ? p.kw - 1 - s : s;
           const int orr = p.flip ? p.kh - 1 - r : r;
           tma_load_im2col_4d(a_dst, &tmap_a, &full_bar[stage], cb * 64, cw, ch, img, (uint16_t)os, (uint16_t)orr);
-          tma_load_2d(a_dst + kTmaATile, &tmap_b, &full_bar[stage], kb * 64, n_tile * BLOCK_N);
+          const int bcol = (((p.b_py + p.b_sub * r) * p.b_kw + (p.b_px + p.b_sub * s)) * p.cin_blocks + cb) * 64;
+          tma_load_2d(a_dst + kTmaATile, &tmap_b, &full_bar[stage], bcol, n_tile * BLOCK_N);
           if (++cb == p.cin_blocks) {
             cb = 0;
             ++tap;

@@ -72,6 +72,9 @@ CONV_CASES = {
     "tma_zero3x3_256": (1, 256, 16, 16, 256, 3, 1, 1, "zeros", True, None),
     "tma_persistent_200tiles": (4, 64, 80, 80, 64, 3, 1, 1, "zeros", False, None),
     "tma_valid7x7": (2, 64, 22, 22, 64, 7, 1, 0, "zeros", False, None),
+    "tma_dgrad_s2_to8": (2, 3, 34, 34, 64, 4, 2, 0, "zeros", False, None),   # D conv0 geometry: N tile mostly padding
+    "tma_ragged_m100": (1, 64, 10, 10, 64, 3, 1, 1, "zeros", False, None),
+    "tma_ragged_m75_s2": (3, 64, 12, 12, 72, 4, 2, 0, "zeros", False, None),
     "narrow_16_32": (2, 16, 12, 12, 32, 3, 1, 1, "reflect", False, None),   # reduced-width nets of the golden fixtures
     "narrow_s2_8_16": (2, 8, 16, 16, 16, 4, 2, 1, "reflect", False, None),
 }
@@ -168,7 +171,7 @@ def test_conv_fwd_fp32_out_and_epilogue():
 
 DGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "spade_gb_512", "heads_4", "ragged_m", "d_src_1", "cls_valid_k2",
                "narrow_16_32", "narrow_s2_8_16", "tma_valid3x3", "tma_zero3x3_256", "tma_persistent_200tiles", "tma_valid4x4s2",
-               "tma_valid7x7"]
+               "tma_valid7x7", "tma_ragged_m100", "tma_ragged_m75_s2", "tma_dgrad_s2_to8"]
 
 
 @pytest.mark.parametrize("case", DGRAD_CASES)

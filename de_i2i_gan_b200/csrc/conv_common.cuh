@@ -1,12 +1,56 @@
 // Shared by the convolution kernels (conv_igemm.cu: cp.async-gather kernels; conv_tma.cu: TMA-im2col kernels).
 #pragma once
 #include "common.cuh"
+#include "../../include/dei2i.h"
 
 namespace dei2i {
 
 DEVINL void unpack8_bf16(const uint4& v, float (&f)[8]) {
   f[0] = bf16lo(v.x); f[1] = bf16hi(v.x); f[2] = bf16lo(v.y); f[3] = bf16hi(v.y);
   f[4] = bf16lo(v.z); f[5] = bf16hi(v.z); f[6] = bf16lo(v.w); f[7] = bf16hi(v.w);
+}
+
+// im2col gather geometry shared by the cp.async-gather kernels (conv_igemm.cu) and the skinny kernels (conv_skinny.cu)
+struct Gather {
+  const __nv_bfloat16* src;
+  int N, Hl, Wl, Hs, Ws, C;  // logical (Hl, Wl) nearest-mapped onto stored (Hs, Ws); C = channel pitch
+  int Ho, Wo;                // row domain: m -> (img, oy, ox)
+  int kh, kw, stride, pad, pad_mode;
+  int mode;                  // 0: forward (iy = oy*stride + r - pad), 1: dgrad (iy = (oy + off - r) / stride)
+  int off;
+  int cin8;                  // 16-byte chunks per tap along K (= K-channels / 8)
+  int ntaps;
+  long long M;               // N*Ho*Wo
+};
+
+DEVINL bool resolve_axis(const Gather& g, int o, int r, int Ll, int Ls, int& i_out) {
+  if (g.mode == 0) {
+    int i = o * g.stride + r - g.pad;
+    if (g.pad_mode == DEI2I_PAD_REFLECT) {
+      i = i < 0 ? -i : i;
+      i = i >= Ll ? 2 * Ll - 2 - i : i;
+    } else if (i < 0 || i >= Ll) {
+      return false;
+    }
+    if (Ls != Ll) i = (int)(((long long)i * Ls) / Ll);
+    i_out = i;
+    return true;
+  } else {
+    int t = o + g.off - r;
+    if (t < 0) return false;
+    int q = t / g.stride;
+    if (q * g.stride != t || q >= Ls) return false;
+    i_out = q;
+    return true;
+  }
+}
+
+// address of the 8-channel chunk c8 of tap (r, s) for row (img, oy, ox); nullptr => zero fill
+DEVINL const __nv_bfloat16* gather_ptr(const Gather& g, int img, int oy, int ox, int r, int s, int c8) {
+  int iy, ix;
+  if (!resolve_axis(g, oy, r, g.Hl, g.Hs, iy)) return nullptr;
+  if (!resolve_axis(g, ox, s, g.Wl, g.Ws, ix)) return nullptr;
+  return g.src + (((long long)img * g.Hs + iy) * g.Ws + ix) * g.C + c8 * 8;
 }
 
 struct Epilogue {
@@ -66,6 +110,10 @@ struct TmaWgradParams {
 void wgrad_tma_plan(TmaWgradParams& p);
 int run_wgrad_tma(const void* x, int N, int H, int W, int C, const void* dy, int cout_ld, TmaWgradParams& p, int upper,
                   cudaStream_t st);
+
+// conv_skinny.cu
+int wgrad_narrow_splits(int Kreal, int Cout_ld, long long M);
+int run_wgrad_narrow(const Gather& g, const void* dy, int Cout, int Cout_ld, int Kf, float* partial, int splits, cudaStream_t st);
 
 // returns 0 on success; the caller has checked applicability (see tma_conv_applicable)
 int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, int rows, int K, const TmaConvParams& p,

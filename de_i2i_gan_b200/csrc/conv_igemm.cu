@@ -31,49 +31,6 @@ extern int g_tune_wgrad_waves;
 extern int g_tune_conv_path;
 void count_launch(int n = 1);
 
-// ----------------------------------------------------------------------------------------------------------
-struct Gather {
-  const __nv_bfloat16* src;
-  int N, Hl, Wl, Hs, Ws, C;  // logical (Hl, Wl) nearest-mapped onto stored (Hs, Ws); C = channel pitch
-  int Ho, Wo;                // row domain: m -> (img, oy, ox)
-  int kh, kw, stride, pad, pad_mode;
-  int mode;                  // 0: forward (iy = oy*stride + r - pad), 1: dgrad (iy = (oy + off - r) / stride)
-  int off;
-  int cin8;                  // 16-byte chunks per tap along K (= K-channels / 8)
-  int ntaps;
-  long long M;               // N*Ho*Wo
-};
-
-DEVINL bool resolve_axis(const Gather& g, int o, int r, int Ll, int Ls, int& i_out) {
-  if (g.mode == 0) {
-    int i = o * g.stride + r - g.pad;
-    if (g.pad_mode == DEI2I_PAD_REFLECT) {
-      i = i < 0 ? -i : i;
-      i = i >= Ll ? 2 * Ll - 2 - i : i;
-    } else if (i < 0 || i >= Ll) {
-      return false;
-    }
-    if (Ls != Ll) i = (int)(((long long)i * Ls) / Ll);
-    i_out = i;
-    return true;
-  } else {
-    int t = o + g.off - r;
-    if (t < 0) return false;
-    int q = t / g.stride;
-    if (q * g.stride != t || q >= Ls) return false;
-    i_out = q;
-    return true;
-  }
-}
-
-// address of the 8-channel chunk c8 of tap (r, s) for row (img, oy, ox); nullptr => zero fill
-DEVINL const __nv_bfloat16* gather_ptr(const Gather& g, int img, int oy, int ox, int r, int s, int c8) {
-  int iy, ix;
-  if (!resolve_axis(g, oy, r, g.Hl, g.Hs, iy)) return nullptr;
-  if (!resolve_axis(g, ox, s, g.Wl, g.Ws, ix)) return nullptr;
-  return g.src + (((long long)img * g.Hs + iy) * g.Ws + ix) * g.C + c8 * 8;
-}
-
 struct ConvKParams {
   Gather g;
   Epilogue e;
@@ -487,39 +444,6 @@ __global__ void sum_blocks_kernel(const float* __restrict__ in, int n, float* __
   }
 }
 
-// narrow-Cout wgrad (heads, discriminator classifiers, reduced-width test networks: Cout_ld < 64): CUDA cores, fp32
-// atomics on a [Cout, Kf] buffer; blockIdx.y selects a group of 8 output channels
-__global__ void wgrad_small_kernel(const Gather g, const __nv_bfloat16* __restrict__ dy, int Cout, int Cout_ld, int Kf,
-                                   float* __restrict__ acc /*[Cout, Kf] zeroed*/, int pix_per_block) {
-  // each block: a range of pixels; thread t handles K elements t, t+blockDim, ...; accumulates over the pixel range
-  const long long m_begin = (long long)blockIdx.x * pix_per_block;
-  const long long m_end = min(g.M, m_begin + pix_per_block);
-  const int co0 = blockIdx.y * 8;
-  const int HoWo = g.Ho * g.Wo;
-  const int Kreal = g.ntaps * g.cin8 * 8;
-  for (int k = threadIdx.x; k < Kreal; k += blockDim.x) {
-    const int tap = k / (g.cin8 * 8);
-    const int ci = k - tap * g.cin8 * 8;
-    const int r = tap / g.kw, s = tap - r * g.kw;
-    float a[8];
-#pragma unroll
-    for (int c = 0; c < 8; ++c) a[c] = 0.f;
-    for (long long m = m_begin; m < m_end; ++m) {
-      int img = (int)(m / HoWo);
-      int rem = (int)(m - (long long)img * HoWo);
-      int oy = rem / g.Wo, ox = rem - oy * g.Wo;
-      const __nv_bfloat16* sp = gather_ptr(g, img, oy, ox, r, s, ci >> 3);
-      if (sp == nullptr) continue;
-      const float xv = __bfloat162float(sp[ci & 7]);
-      float d[8];
-      unpack8_bf16(__ldg(reinterpret_cast<const uint4*>(dy + m * Cout_ld + co0)), d);
-#pragma unroll
-      for (int c = 0; c < 8; ++c) a[c] += xv * d[c];
-    }
-    for (int c = 0; c < 8 && co0 + c < Cout; ++c) atomicAdd(acc + (long long)(co0 + c) * Kf + k, a[c]);
-  }
-}
-
 // ----------------------------------------------------------------------------------------------------------
 // host side
 static int conv_out_dim(int L, int k, int stride, int pad) { return (L + 2 * pad - k) / stride + 1; }
@@ -723,7 +647,10 @@ extern "C" size_t dei2i_conv2d_wgrad_workspace(const dei2i_conv_geom* g, int Cin
   if (g == nullptr || check_geom(g)) return 0;
   int bn, splits, pbs, npb, Kf;
   wgrad_plan(g, bn, splits, pbs, npb, Kf);
-  if (g->Cout_ld < 64) splits = 1;
+  if (g->Cout_ld < 64) {
+    const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
+    splits = wgrad_narrow_splits(g->kh * g->kw * g->Cin, g->Cout_ld, (long long)g->N * Ho * Wo);
+  }
   {
     const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
     if (wgrad_tma_applicable(g, (long long)g->N * Ho * Wo)) {
@@ -778,13 +705,8 @@ extern "C" int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int 
     splits = t.splits;
     if (int rc = run_wgrad_tma(x, g->N, g->H, g->W, g->Cin, dy, g->Cout_ld, t, g->pad - (g->kh - 1), st)) return rc;
   } else if (g->Cout_ld < 64) {
-    splits = 1;
-    DEI2I_CUDA(cudaMemsetAsync(partial, 0, (size_t)g->Cout * Kf * sizeof(float), st));
-    const int ppb = 256;
-    long long blocks = (p.g.M + ppb - 1) / ppb;
-    wgrad_small_kernel<<<dim3((unsigned)blocks, (unsigned)(g->Cout_ld / 8)), 256, 0, st>>>(p.g, (const __nv_bfloat16*)dy, g->Cout, g->Cout_ld, Kf, partial, ppb);
-    count_launch();
-    DEI2I_CUDA(cudaGetLastError());
+    splits = wgrad_narrow_splits(taps * g->Cin, g->Cout_ld, p.g.M);
+    if (int rc = run_wgrad_narrow(p.g, dy, g->Cout, g->Cout_ld, Kf, partial, splits, st)) return rc;
   } else {
     p.partial = partial; p.cout_rows = g->Cout; p.Kf = Kf; p.pb_per_split = pbs; p.num_pb = npb;
     CUtensorMap tm;

@@ -115,6 +115,15 @@ int run_wgrad_tma(const void* x, int N, int H, int W, int C, const void* dy, int
 int wgrad_narrow_splits(int Kreal, int Cout_ld, long long M);
 int run_wgrad_narrow(const Gather& g, const void* dy, int Cout, int Cout_ld, int Kf, float* partial, int splits, cudaStream_t st);
 
+bool wgrad_c8_applicable(const Gather& g, int Cout_ld);  // needs g.C, g.ntaps, g.M only
+int wgrad_c8_splits(const Gather& g, int Cout_ld);
+int run_wgrad_c8(const Gather& g, const void* dy, int Cout, int Cout_ld, int Kf, float* partial, cudaStream_t st);
+bool wgrad_heads_applicable(const Gather& g, int Cout, int Cout_ld);
+int wgrad_heads_splits();
+int run_wgrad_heads(const Gather& g, const void* dy, int Cout, int Cout_ld, int Kf, float* partial, cudaStream_t st);
+bool conv_c8_applicable(const Gather& g, int rows_ld);
+int run_conv_c8(const Gather& g, const Epilogue& e, const void* wmat, int rows, int Kf, cudaStream_t st);
+
 // returns 0 on success; the caller has checked applicability (see tma_conv_applicable)
 int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, int rows, int K, const TmaConvParams& p,
                  int upper, cudaStream_t st);

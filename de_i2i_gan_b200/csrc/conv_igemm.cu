@@ -547,6 +547,7 @@ extern "C" int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const
   p.e.scale = e->scale; p.e.bias = e->bias; p.e.noise = e->noise; p.e.noise_weight = e->noise_weight;
   p.e.residual = (const __nv_bfloat16*)e->residual; p.e.out = y; p.e.act = e->act; p.e.out_fp32 = e->out_fp32;
   p.e.ld = g->Cout_ld; p.e.ncols = g->Cout;
+  if (g_tune_conv_path != 1 && conv_c8_applicable(p.g, g->Cout_ld)) return run_conv_c8(p.g, p.e, w_fwd, g->Cout, K, (cudaStream_t)stream);
   return run_igemm(p, w_fwd, g->Cout, K, (cudaStream_t)stream);
 }
 
@@ -602,6 +603,7 @@ extern "C" int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx,
   const int K = round_up(g->kh * g->kw * g->Cout_ld, 64);
   p.num_kb = K / 64;
   p.e.scale = scale; p.e.out = dx; p.e.act = 0; p.e.out_fp32 = out_fp32; p.e.ld = g->Cin; p.e.ncols = g->Cin;
+  if (g_tune_conv_path != 1 && conv_c8_applicable(p.g, g->Cin)) return run_conv_c8(p.g, p.e, w_dgrad, g->Cin, K, (cudaStream_t)stream);
   return run_igemm(p, w_dgrad, g->Cin, K, (cudaStream_t)stream);
 }
 
@@ -647,9 +649,16 @@ extern "C" size_t dei2i_conv2d_wgrad_workspace(const dei2i_conv_geom* g, int Cin
   if (g == nullptr || check_geom(g)) return 0;
   int bn, splits, pbs, npb, Kf;
   wgrad_plan(g, bn, splits, pbs, npb, Kf);
-  if (g->Cout_ld < 64) {
+  {
     const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
-    splits = wgrad_narrow_splits(g->kh * g->kw * g->Cin, g->Cout_ld, (long long)g->N * Ho * Wo);
+    Gather gg;
+    memset(&gg, 0, sizeof(gg));
+    gg.C = g->Cin; gg.ntaps = g->kh * g->kw; gg.M = (long long)g->N * Ho * Wo;
+    int s2 = 0;
+    if (wgrad_c8_applicable(gg, g->Cout_ld)) s2 = wgrad_c8_splits(gg, g->Cout_ld);
+    else if (g->Cout_ld < 64) s2 = wgrad_narrow_splits(g->kh * g->kw * g->Cin, g->Cout_ld, gg.M);
+    if (g->Cout_ld == 8 && s2 < wgrad_heads_splits()) s2 = wgrad_heads_splits();
+    if (s2 > splits) splits = s2;
   }
   {
     const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
@@ -704,6 +713,12 @@ extern "C" int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int 
     t.partial = partial;
     splits = t.splits;
     if (int rc = run_wgrad_tma(x, g->N, g->H, g->W, g->Cin, dy, g->Cout_ld, t, g->pad - (g->kh - 1), st)) return rc;
+  } else if (g_tune_conv_path != 1 && wgrad_c8_applicable(p.g, g->Cout_ld)) {
+    splits = wgrad_c8_splits(p.g, g->Cout_ld);
+    if (int rc = run_wgrad_c8(p.g, dy, g->Cout, g->Cout_ld, Kf, partial, st)) return rc;
+  } else if (g_tune_conv_path != 1 && wgrad_heads_applicable(p.g, g->Cout, g->Cout_ld)) {
+    splits = wgrad_heads_splits();
+    if (int rc = run_wgrad_heads(p.g, dy, g->Cout, g->Cout_ld, Kf, partial, st)) return rc;
   } else if (g->Cout_ld < 64) {
     splits = wgrad_narrow_splits(taps * g->Cin, g->Cout_ld, p.g.M);
     if (int rc = run_wgrad_narrow(p.g, dy, g->Cout, g->Cout_ld, Kf, partial, splits, st)) return rc;

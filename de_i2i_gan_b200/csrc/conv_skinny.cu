@@ -93,4 +93,569 @@ int run_wgrad_narrow(const Gather& g, const void* dy, int Cout, int Cout_ld, int
   return check_cuda(cudaGetLastError(), "wgrad_narrow_kernel launch");
 }
 
+
+// ======================================================================================================================
+// 8-channel-input convolution (forward, or dgrad expressed through Gather mode 1):  D[m, n] = sum_k A[m, k] * W[n, k]
+//   k = tap * 8 + ci.  One warp = 16 output pixels x all (<= NT * 8) output channels; K step = 2 taps (mma m16n8k16).
+//   A fragments are loaded straight from global memory: a (pixel, tap) is 16 contiguous bytes, the 4 lanes of a fragment
+//   group read 4 bytes each, the 8 groups read 8 neighbouring pixels -> 128-byte segments; tap re-use is served by L1.
+DEVINL void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
+               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// like resolve_axis (conv_common.cuh) with the nearest-resize index in 32-bit arithmetic
+DEVINL bool c8_axis(const Gather& g, int o, int r, int Ll, int Ls, int& i_out) {
+  if (g.mode == 0) {
+    int i = o * g.stride + r - g.pad;
+    if (g.pad_mode == DEI2I_PAD_REFLECT) {
+      i = i < 0 ? -i : i;
+      i = i >= Ll ? 2 * Ll - 2 - i : i;
+    } else if (i < 0 || i >= Ll) {
+      return false;
+    }
+    if (Ls != Ll) i = Ls == 1 ? 0 : (int)(((unsigned)i * (unsigned)Ls) / (unsigned)Ll);
+    i_out = i;
+    return true;
+  }
+  return resolve_axis(g, o, r, Ll, Ls, i_out);
+}
+
+struct C8Params {
+  Gather g;  // g.C == 8
+  Epilogue e;
+  const __nv_bfloat16* w;  // [rows, Kf] packed weights, k = tap * 8 + ci
+  int rows;                // real rows of w (output channels)
+  int Kf;                  // row pitch of w
+  int ksteps;              // ceil(ntaps / 2)
+  int m_tiles;             // ceil(M / 128)
+  // affine tap walk (FAST kernels): input row of tap (r, s) for output (oy, ox) is y0 + dir * r with
+  // y0 = oy * ystep + yoff, and the element offset of the tap relative to (y0, x0) is dir * (r * rowp + s * colp)
+  int dir, ystep, yoff, rowp, colp;
+};
+
+// When the gather is affine in the tap index (no reflect padding, no general nearest resize, dgrad only at stride 1) the
+// per-tap address is base(pixel) + table[tap] and the bounds test two unsigned compares; returns false otherwise.
+static bool c8_affine(const Gather& g, int& dir, int& ystep, int& yoff, int& rowp, int& colp) {
+  if (g.pad_mode == DEI2I_PAD_REFLECT && g.pad > 0) return false;
+  if (g.mode == 0) {
+    if (!((g.Hs == g.Hl || g.Hs == 1) && (g.Ws == g.Wl || g.Ws == 1))) return false;
+    dir = 1; ystep = g.stride; yoff = -g.pad;
+  } else {
+    if (g.stride != 1 || g.Hs != g.Hl || g.Ws != g.Wl) return false;
+    dir = -1; ystep = 1; yoff = g.off;
+  }
+  rowp = g.Hs == g.Hl ? g.Ws * 8 : 0;  // a 1 x 1 stored map broadcasts: every in-bounds tap reads the same pixel
+  colp = g.Ws == g.Wl ? 8 : 0;
+  return true;
+}
+
+constexpr int kC8Threads = 256;
+
+template <int NT, bool FAST>
+__global__ void __launch_bounds__(kC8Threads, 2)
+conv_c8_fwd_kernel(const C8Params p) {
+  extern __shared__ __align__(16) uint8_t c8_smem[];
+  __shared__ int4 tap_tab[64];  // (dir * r, dir * s, element offset, 0); taps >= ntaps fail every bounds test
+  const Gather& g = p.g;
+  const Epilogue& e = p.e;
+  const int KP = p.ksteps * 16 + 8;  // weight row pitch in smem (elements): pitch in words == 4 (mod 8) -> conflict-free B reads
+  __nv_bfloat16* w_s = reinterpret_cast<__nv_bfloat16*>(c8_smem);
+  constexpr int kStagePitch = NT * 16 + 16;  // bytes per staged output row (bf16), +16: conflict-free fragment writes
+  uint8_t* stage_base = c8_smem + ((NT * 8 * KP * 2 + 15) & ~15);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int gid = lane >> 2, tq = lane & 3;
+
+  // weights -> smem (zero rows / columns beyond the real ones)
+  {
+    const int kreal = g.ntaps * 8;
+    const int kw8 = KP / 8;
+    for (int i = threadIdx.x; i < NT * 8 * kw8; i += kC8Threads) {
+      const int n = i / kw8, k8 = i - n * kw8;
+      uint4 v = make_uint4(0, 0, 0, 0);
+      if (n < p.rows && k8 * 8 < kreal) v = __ldg(reinterpret_cast<const uint4*>(p.w + (long long)n * p.Kf + k8 * 8));
+      *reinterpret_cast<uint4*>(w_s + n * KP + k8 * 8) = v;
+    }
+    if (threadIdx.x < 64) {
+      const int t = threadIdx.x;
+      const int r = t / g.kw, s = t - r * g.kw;
+      tap_tab[t] = t < g.ntaps ? make_int4(p.dir * r, p.dir * s, p.dir * (r * p.rowp + s * p.colp), 0) : make_int4(-(1 << 28), 0, 0, 0);
+    }
+  }
+  __syncthreads();
+
+  const float osc = e.scale != nullptr ? __ldg(e.scale) : 1.f;
+  const float nzw = e.noise != nullptr ? __ldg(e.noise_weight) : 0.f;
+  const int HoWo = g.Ho * g.Wo;
+  uint8_t* stage = stage_base + warp * (16 * kStagePitch);
+  const uint32_t* w_words = reinterpret_cast<const uint32_t*>(w_s);
+  const int KPW = KP / 2;
+
+  for (int tile = blockIdx.x; tile < p.m_tiles; tile += gridDim.x) {
+    const long long m_w = (long long)tile * 128 + warp * 16;
+    if (m_w >= g.M) continue;
+    int r_img[2], r_oy[2], r_ox[2];
+    bool r_ok[2];
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const long long m = m_w + gid + 8 * h;
+      r_ok[h] = m < g.M;
+      const long long mm = r_ok[h] ? m : 0;
+      r_img[h] = (int)(mm / HoWo);
+      const int rem = (int)(mm - (long long)r_img[h] * HoWo);
+      r_oy[h] = rem / g.Wo;
+      r_ox[h] = rem - r_oy[h] * g.Wo;
+    }
+    float acc[NT][4];
+#pragma unroll
+    for (int j = 0; j < NT; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+
+    // FAST: per-row origin (y0, x0) and base pointer; rows beyond M fail every bounds test
+    int y0[2], x0[2];
+    const __nv_bfloat16* base[2];
+    if (FAST) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        y0[h] = r_ok[h] ? r_oy[h] * p.ystep + p.yoff : -(1 << 28);
+        x0[h] = r_ox[h] * p.ystep + p.yoff;
+        base[h] = g.src + (long long)r_img[h] * g.Hs * g.Ws * 8 + (long long)y0[h] * p.rowp + (long long)x0[h] * p.colp + 2 * tq;
+      }
+    }
+    auto load_a = [&](int ks, uint32_t (&a)[4]) {
+      if (FAST) {
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const int4 t = tap_tab[2 * ks + j];
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            uint32_t v = 0;
+            if ((unsigned)(y0[h] + t.x) < (unsigned)g.Hl && (unsigned)(x0[h] + t.y) < (unsigned)g.Wl)
+              v = __ldg(reinterpret_cast<const uint32_t*>(base[h] + t.z));
+            a[j * 2 + h] = v;
+          }
+        }
+        return;
+      }
+      int tap = 2 * ks;
+      int r = tap / g.kw, s = tap - r * g.kw;
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t v = 0;
+          int iy, ix;
+          if (tap < g.ntaps && r_ok[h] && c8_axis(g, r_oy[h], r, g.Hl, g.Hs, iy) && c8_axis(g, r_ox[h], s, g.Wl, g.Ws, ix))
+            v = __ldg(reinterpret_cast<const uint32_t*>(g.src + (((long long)r_img[h] * g.Hs + iy) * g.Ws + ix) * 8 + 2 * tq));
+          a[j * 2 + h] = v;
+        }
+        ++tap;
+        if (++s == g.kw) { s = 0; ++r; }
+      }
+    };
+
+    uint32_t a_cur[4], a_nxt[4];
+    load_a(0, a_cur);
+    for (int ks = 0; ks < p.ksteps; ++ks) {
+      if (ks + 1 < p.ksteps) load_a(ks + 1, a_nxt);
+      const uint32_t* wb = w_words + gid * KPW + ks * 8 + tq;
+#pragma unroll
+      for (int j = 0; j < NT; ++j) {
+        const uint32_t b0 = wb[j * 8 * KPW];
+        const uint32_t b1 = wb[j * 8 * KPW + 4];
+        mma_bf16_16816(acc[j], a_cur, b0, b1);
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) a_cur[i] = a_nxt[i];
+    }
+
+    // ---- epilogue: rows gid / gid + 8, columns j * 8 + 2 * tq (+1)
+    float nz[2] = {0.f, 0.f};
+    if (e.noise != nullptr) {
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+        if (r_ok[h]) nz[h] = __ldg(e.noise + m_w + gid + 8 * h) * nzw;
+    }
+#pragma unroll
+    for (int j = 0; j < NT; ++j) {
+      const int col = j * 8 + 2 * tq;
+      float b0 = 0.f, b1 = 0.f;
+      if (e.bias != nullptr) {
+        if (col < e.ncols) b0 = __ldg(e.bias + col);
+        if (col + 1 < e.ncols) b1 = __ldg(e.bias + col + 1);
+      }
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        float v0 = apply_act(acc[j][2 * h] * osc + b0 + nz[h], e.act);
+        float v1 = apply_act(acc[j][2 * h + 1] * osc + b1 + nz[h], e.act);
+        const long long m = m_w + gid + 8 * h;
+        if (e.residual != nullptr && r_ok[h] && col < e.ld) {
+          const uint32_t rv = __ldg(reinterpret_cast<const uint32_t*>(e.residual + m * e.ld + col));
+          v0 += bf16lo(rv);
+          v1 += bf16hi(rv);
+        }
+        if (e.out_fp32) {
+          if (r_ok[h] && col < e.ld) *reinterpret_cast<float2*>(reinterpret_cast<float*>(e.out) + m * e.ld + col) = make_float2(v0, v1);
+        } else {
+          *reinterpret_cast<uint32_t*>(stage + (gid + 8 * h) * kStagePitch + col * 2) = pack_bf16(v0, v1);
+        }
+      }
+    }
+    if (!e.out_fp32) {
+      __syncwarp();
+      const int chunks = e.ld / 8;  // 16-byte chunks per output row
+      for (int i = lane; i < 16 * chunks; i += 32) {
+        const int row = i / chunks, ch = i - row * chunks;
+        const long long m = m_w + row;
+        if (m < g.M)
+          *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out) + m * e.ld + ch * 8) =
+              *reinterpret_cast<const uint4*>(stage + row * kStagePitch + ch * 16);
+      }
+      __syncwarp();
+    }
+  }
+}
+
+template <int NT, bool FAST>
+static int launch_c8(const C8Params& p, cudaStream_t st) {
+  const int KP = p.ksteps * 16 + 8;
+  const size_t smem = ((size_t)(NT * 8 * KP * 2 + 15) & ~(size_t)15) + (size_t)(kC8Threads / 32) * 16 * (NT * 16 + 16);
+  if (smem > 200 * 1024) {
+    set_error("conv_c8: filter too large for the resident-weight kernel (%zu bytes of shared memory)", smem);
+    return DEI2I_ERR_INVALID;
+  }
+  static size_t attr = 0;
+  if (smem > attr) {
+    DEI2I_CUDA(cudaFuncSetAttribute(conv_c8_fwd_kernel<NT, FAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr = smem;
+  }
+  const int grid = p.m_tiles < 148 * 2 ? p.m_tiles : 148 * 2;
+  conv_c8_fwd_kernel<NT, FAST><<<grid, kC8Threads, smem, st>>>(p);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "conv_c8_fwd_kernel launch");
+}
+
+bool conv_c8_applicable(const Gather& g, int rows_ld) {
+  if (g.C != 8 || rows_ld > 128) return false;
+  const int ksteps = (g.ntaps + 1) / 2;
+  const int nt = rows_ld <= 64 ? 8 : 16;
+  return (size_t)nt * 8 * (ksteps * 16 + 8) * 2 <= 150 * 1024;
+}
+
+int run_conv_c8(const Gather& g, const Epilogue& e, const void* wmat, int rows, int Kf, cudaStream_t st) {
+  C8Params p;
+  memset(&p, 0, sizeof(p));
+  p.g = g; p.e = e; p.w = (const __nv_bfloat16*)wmat; p.rows = rows; p.Kf = Kf;
+  p.ksteps = (g.ntaps + 1) / 2;
+  p.m_tiles = (int)((g.M + 127) / 128);
+  if (g.ntaps <= 62 && c8_affine(g, p.dir, p.ystep, p.yoff, p.rowp, p.colp))
+    return e.ld <= 64 ? launch_c8<8, true>(p, st) : launch_c8<16, true>(p, st);
+  return e.ld <= 64 ? launch_c8<8, false>(p, st) : launch_c8<16, false>(p, st);
+}
+
+
+// ======================================================================================================================
+// wgrad of an 8-channel-input convolution:  partial[cta, co, tap * 8 + ci] = sum_{m in cta range} dY[m, co] * A[m, tap * 8 + ci]
+//   mma.sync m16n8k16 with M = 16 output channels, N = the 8 channels of one tap, K = 16 pixels.  Both operands have the
+//   reduction index (pixel) as the slow one in memory, so the tiles ([P pixels][Cout] of dY, [P pixels][taps * 8] of the
+//   im2col matrix, 16-byte cp.async with zero fill) are transposed on the way to the registers by ldmatrix.trans.
+//   Warp w owns m-tile (w % warps_m) and taps [ (w / warps_m) * tpw, ... + tpw ).
+DEVINL void ldsm_x4_trans(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];\n"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+DEVINL void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+DEVINL void cp_async_wait_group() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+struct WgC8Params {
+  Gather g;  // forward gather geometry of x, g.C == 8
+  const __nv_bfloat16* dy;
+  float* partial;  // [grid, Cout, Kf]
+  int Cout, Cout_ld, Kf;
+  int warps_m;     // power of two >= ceil(Cout_ld / 16)
+  int tpw;         // taps per warp
+  int chunks_per_cta, num_chunks;  // chunks of P pixels
+};
+
+constexpr int kWgC8Stages = 3;
+
+template <int NT, int P>
+__global__ void __launch_bounds__(256, NT <= 9 ? 2 : 1)
+wgrad_c8_kernel(const WgC8Params p) {
+  extern __shared__ __align__(16) uint8_t wg_smem[];
+  __shared__ int8_t tap_r[64], tap_s[64];
+  const Gather& g = p.g;
+  const int pitch_dy = ((p.Cout_ld / 8) | 1) * 16;
+  const int pitch_a = (g.ntaps | 1) * 16;
+  const int stage_bytes = P * (pitch_dy + pitch_a);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int gid = lane >> 2, tq = lane & 3;
+  if (threadIdx.x < g.ntaps) {
+    tap_r[threadIdx.x] = (int8_t)(threadIdx.x / g.kw);
+    tap_s[threadIdx.x] = (int8_t)(threadIdx.x % g.kw);
+  }
+  __syncthreads();
+
+  const int c_begin = blockIdx.x * p.chunks_per_cta;
+  const int c_end = min(p.num_chunks, c_begin + p.chunks_per_cta);
+  const int HoWo = g.Ho * g.Wo;
+  const uint32_t smem0 = smem_u32(wg_smem);
+
+  // producer role of every thread: pixel slot (tid % P), taps / dY chunks strided by 256 / P
+  constexpr int TPP = 256 / P;  // threads per pixel
+  const int my_pix = threadIdx.x % P, my_sub = threadIdx.x / P;
+  const int dy_chunks = p.Cout_ld / 8;
+  auto issue = [&](int chunk, int stage) {
+    const uint32_t s_dy = smem0 + stage * stage_bytes;
+    const uint32_t s_a = s_dy + P * pitch_dy;
+    const long long m = (long long)chunk * P + my_pix;
+    const bool ok = m < g.M;
+    const long long mm = ok ? m : 0;
+    const int img = (int)(mm / HoWo);
+    const int rem = (int)(mm - (long long)img * HoWo);
+    const int oy = rem / g.Wo, ox = rem - oy * g.Wo;
+    const __nv_bfloat16* dsrc = p.dy + mm * p.Cout_ld;
+    for (int c = my_sub; c < dy_chunks; c += TPP) cp_async_16(s_dy + my_pix * pitch_dy + c * 16, dsrc + c * 8, ok);
+    for (int t = my_sub; t < g.ntaps; t += TPP) {
+      int iy, ix;
+      const bool v = ok && c8_axis(g, oy, tap_r[t], g.Hl, g.Hs, iy) && c8_axis(g, ox, tap_s[t], g.Wl, g.Ws, ix);
+      const __nv_bfloat16* src = v ? g.src + (((long long)img * g.Hs + iy) * g.Ws + ix) * 8 : g.src;
+      cp_async_16(s_a + my_pix * pitch_a + t * 16, src, v);
+    }
+  };
+
+  const int m_tile = warp & (p.warps_m - 1);
+  const int tap0 = (warp / p.warps_m) * p.tpw;
+  const int ntw = max(0, min(p.tpw, g.ntaps - tap0));  // taps of this warp
+  const bool m_active = m_tile * 16 < p.Cout_ld;
+  float acc[NT][4];
+#pragma unroll
+  for (int j = 0; j < NT; ++j) acc[j][0] = acc[j][1] = acc[j][2] = acc[j][3] = 0.f;
+
+  // prologue
+#pragma unroll
+  for (int s = 0; s < kWgC8Stages - 1; ++s) {
+    if (c_begin + s < c_end) issue(c_begin + s, s);
+    cp_async_commit();
+  }
+  for (int c = c_begin; c < c_end; ++c) {
+    const int it = c - c_begin;
+    cp_async_wait_group<kWgC8Stages - 2>();
+    __syncthreads();  // chunk c has landed for everyone; everyone is done with the stage about to be refilled
+    if (c + kWgC8Stages - 1 < c_end) issue(c + kWgC8Stages - 1, (it + kWgC8Stages - 1) % kWgC8Stages);
+    cp_async_commit();
+    if (m_active && ntw > 0) {
+      const uint32_t s_dy = smem0 + (it % kWgC8Stages) * stage_bytes;
+      const uint32_t s_a = s_dy + P * pitch_dy;
+#pragma unroll
+      for (int pp = 0; pp < P; pp += 32) {
+        uint32_t a0[4], a1[4];
+        // matrices: (pix lo, co lo) (pix lo, co hi) (pix hi, co lo) (pix hi, co hi); lane supplies row (lane % 8) of matrix (lane / 8)
+        const int mi = lane >> 3, mr = lane & 7;
+        const uint32_t a_addr = s_dy + (pp + (mi >> 1) * 8 + mr) * pitch_dy + (m_tile * 16 + (mi & 1) * 8) * 2;
+        ldsm_x4_trans(a0, a_addr);
+        ldsm_x4_trans(a1, a_addr + 16 * pitch_dy);
+        // B: four pixel octets of one tap -> (b0, b1) of k-step 0 and of k-step 1
+        const uint32_t b_addr = s_a + (pp + mi * 8 + mr) * pitch_a + tap0 * 16;
+#pragma unroll
+        for (int j = 0; j < NT; ++j) {
+          if (j < ntw) {
+            uint32_t b[4];
+            ldsm_x4_trans(b, b_addr + j * 16);
+            mma_bf16_16816(acc[j], a0, b[0], b[1]);
+            mma_bf16_16816(acc[j], a1, b[2], b[3]);
+          }
+        }
+      }
+    }
+  }
+  cp_async_wait_group<0>();
+  if (m_active) {
+#pragma unroll
+    for (int j = 0; j < NT; ++j) {
+      if (j < ntw) {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          const int co = m_tile * 16 + gid + 8 * h;
+          if (co < p.Cout)
+            *reinterpret_cast<float2*>(p.partial + ((long long)blockIdx.x * p.Cout + co) * p.Kf + (tap0 + j) * 8 + 2 * tq) =
+                make_float2(acc[j][2 * h], acc[j][2 * h + 1]);
+        }
+      }
+    }
+  }
+}
+
+static void wgrad_c8_plan(const Gather& g, int Cout_ld, int& warps_m, int& tpw, int& P, int& grid, int& cpc, int& nchunks) {
+  const int m_tiles = (Cout_ld + 15) / 16;
+  warps_m = 1;
+  while (warps_m < m_tiles) warps_m *= 2;
+  const int warps_n = 8 / warps_m;
+  tpw = (g.ntaps + warps_n - 1) / warps_n;
+  P = tpw <= 9 ? 64 : 32;
+  nchunks = (int)((g.M + P - 1) / P);
+  grid = nchunks < 148 * 2 ? nchunks : 148 * 2;
+  if (tpw > 9 && grid > 148) grid = 148;
+  cpc = (nchunks + grid - 1) / grid;
+  grid = (nchunks + cpc - 1) / cpc;
+}
+
+bool wgrad_c8_applicable(const Gather& g, int Cout_ld) {
+  if (g.C != 8 || Cout_ld < 16 || Cout_ld > 128 || g.ntaps > 64) return false;
+  int warps_m, tpw, P, grid, cpc, nchunks;
+  wgrad_c8_plan(g, Cout_ld, warps_m, tpw, P, grid, cpc, nchunks);
+  return tpw <= 25;
+}
+
+int wgrad_c8_splits(const Gather& g, int Cout_ld) {
+  int warps_m, tpw, P, grid, cpc, nchunks;
+  wgrad_c8_plan(g, Cout_ld, warps_m, tpw, P, grid, cpc, nchunks);
+  return grid;
+}
+
+template <int NT, int P>
+static int launch_wgrad_c8(const WgC8Params& p, int grid, cudaStream_t st) {
+  const int pitch_dy = ((p.Cout_ld / 8) | 1) * 16, pitch_a = (p.g.ntaps | 1) * 16;
+  const size_t smem = (size_t)kWgC8Stages * P * (pitch_dy + pitch_a);
+  static size_t attr = 0;
+  if (smem > attr) {
+    DEI2I_CUDA(cudaFuncSetAttribute(wgrad_c8_kernel<NT, P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr = smem;
+  }
+  wgrad_c8_kernel<NT, P><<<grid, 256, smem, st>>>(p);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "wgrad_c8_kernel launch");
+}
+
+int run_wgrad_c8(const Gather& g, const void* dy, int Cout, int Cout_ld, int Kf, float* partial, cudaStream_t st) {
+  WgC8Params p;
+  memset(&p, 0, sizeof(p));
+  int P, grid;
+  wgrad_c8_plan(g, Cout_ld, p.warps_m, p.tpw, P, grid, p.chunks_per_cta, p.num_chunks);
+  p.g = g; p.dy = (const __nv_bfloat16*)dy; p.partial = partial; p.Cout = Cout; p.Cout_ld = Cout_ld; p.Kf = Kf;
+  if (p.tpw <= 9) return launch_wgrad_c8<9, 64>(p, grid, st);
+  return launch_wgrad_c8<25, 32>(p, grid, st);
+}
+
+
+// ======================================================================================================================
+// wgrad of the generator heads (3x3, stride 1, Cin % 64 == 0, <= 4 output channels; generator.py:224-241):
+//   dW[co, (r, s), ci] = sum_pixels dY[pix, co] * x[pix + (r, s), ci]
+//   A warp owns 64 input channels (lane = channel pair) and walks output rows with a 3 x 3 register window of x: per pixel
+//   3 coalesced 128-byte loads + one broadcast 8-byte dY load feed 72 FMAs per lane (9 taps x 2 channels x 4 outputs).
+//   Warps of a CTA are summed through shared memory in a fixed order; one FP32 partial tile per CTA.
+constexpr int kHeadsWarps = 16;
+
+__global__ void __launch_bounds__(kHeadsWarps * 32, 1)
+wgrad_heads_kernel(const Gather g, const __nv_bfloat16* __restrict__ dy, int Cout, int Cout_ld, int Kf, float* __restrict__ partial) {
+  __shared__ float red[72 * 32 * 2];  // two 64-channel slabs at most share a CTA
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int slabs = g.C / 64;
+  const int total_warps = gridDim.x * kHeadsWarps;
+  const int gw = blockIdx.x * kHeadsWarps + warp;
+  const int slab = gw % slabs;  // kHeadsWarps % slabs == 0: the warps of one slab inside a CTA are warp % slabs == slab
+  const int ci = slab * 64 + 2 * lane;
+  const int rows = g.N * g.Ho;
+  float acc[3][3][4][2];
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int s = 0; s < 3; ++s)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) acc[r][s][c][0] = acc[r][s][c][1] = 0.f;
+
+  for (int row = gw / slabs; row < rows; row += total_warps / slabs) {
+    const int img = row / g.Ho, oy = row - img * g.Ho;
+    const __nv_bfloat16* xr[3];
+    bool yok[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      const int iy = oy - g.pad + r;
+      yok[r] = iy >= 0 && iy < g.Hl;
+      xr[r] = g.src + ((long long)img * g.Hs + (yok[r] ? iy : 0)) * g.Ws * g.C + ci;
+    }
+    auto ldx = [&](int r, int ix) -> uint32_t {
+      return (yok[r] && ix >= 0 && ix < g.Wl) ? __ldg(reinterpret_cast<const uint32_t*>(xr[r] + (long long)ix * g.C)) : 0u;
+    };
+    uint32_t w[3][3], nxt[3];
+#pragma unroll
+    for (int r = 0; r < 3; ++r) {
+      w[r][0] = 0;
+      w[r][1] = ldx(r, -g.pad);
+      w[r][2] = ldx(r, -g.pad + 1);
+      nxt[r] = ldx(r, -g.pad + 2);
+    }
+    const __nv_bfloat16* dyp = dy + (long long)row * g.Wo * Cout_ld;
+    uint2 dcur = __ldg(reinterpret_cast<const uint2*>(dyp));
+    for (int ox = 0; ox < g.Wo; ++ox) {
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        w[r][0] = w[r][1];
+        w[r][1] = w[r][2];
+        w[r][2] = nxt[r];
+      }
+      const uint2 dv = dcur;
+      if (ox + 1 < g.Wo) {
+#pragma unroll
+        for (int r = 0; r < 3; ++r) nxt[r] = ldx(r, ox + 1 - g.pad + 2);
+        dcur = __ldg(reinterpret_cast<const uint2*>(dyp + (long long)(ox + 1) * Cout_ld));
+      }
+      const float d[4] = {bf16lo(dv.x), bf16hi(dv.x), bf16lo(dv.y), bf16hi(dv.y)};
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int s = 0; s < 3; ++s) {
+          const float x0 = bf16lo(w[r][s]), x1 = bf16hi(w[r][s]);
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            acc[r][s][c][0] = fmaf(x0, d[c], acc[r][s][c][0]);
+            acc[r][s][c][1] = fmaf(x1, d[c], acc[r][s][c][1]);
+          }
+        }
+    }
+  }
+  // CTA reduction in warp order (deterministic), one slab at a time
+  for (int sl = 0; sl < slabs; ++sl) {
+    float* buf = red + (sl & 1) * (72 * 32);
+    for (int wv = 0; wv < kHeadsWarps; ++wv) {
+      if (warp == wv && slab == sl) {
+        const bool first = wv < slabs;  // first warp of this slab in the CTA
+        int i = 0;
+#pragma unroll
+        for (int r = 0; r < 3; ++r)
+#pragma unroll
+          for (int s = 0; s < 3; ++s)
+#pragma unroll
+            for (int c = 0; c < 4; ++c)
+#pragma unroll
+              for (int e2 = 0; e2 < 2; ++e2, ++i) {
+                float* q = buf + i * 32 + lane;
+                *q = first ? acc[r][s][c][e2] : *q + acc[r][s][c][e2];
+              }
+      }
+      __syncthreads();
+    }
+    // buf[((r*3+s)*4 + c)*2 + e][lane] -> partial[cta, c, (r*3+s)*C + sl*64 + 2*lane + e]
+    for (int i = threadIdx.x; i < 72 * 32; i += blockDim.x) {
+      const int ln = i & 31, idx = i >> 5;
+      const int e2 = idx & 1, c = (idx >> 1) & 3, tap = idx >> 3;
+      if (c < Cout) partial[((long long)blockIdx.x * Cout + c) * Kf + tap * g.C + sl * 64 + 2 * ln + e2] = buf[i];
+    }
+    __syncthreads();
+  }
+}
+
+bool wgrad_heads_applicable(const Gather& g, int Cout, int Cout_ld) {
+  return g.mode == 0 && g.kh == 3 && g.kw == 3 && g.stride == 1 && g.C % 64 == 0 && kHeadsWarps % (g.C / 64) == 0 && g.C <= 128 &&
+         Cout <= 4 && Cout_ld == 8 && g.Hs == g.Hl && g.Ws == g.Wl && !(g.pad_mode == DEI2I_PAD_REFLECT && g.pad > 0);
+}
+int wgrad_heads_splits() { return 148; }
+int run_wgrad_heads(const Gather& g, const void* dy, int Cout, int Cout_ld, int Kf, float* partial, cudaStream_t st) {
+  wgrad_heads_kernel<<<148, kHeadsWarps * 32, 0, st>>>(g, (const __nv_bfloat16*)dy, Cout, Cout_ld, Kf, partial);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "wgrad_heads_kernel launch");
+}
+
 }  // namespace dei2i

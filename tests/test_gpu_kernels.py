@@ -77,6 +77,13 @@ CONV_CASES = {
     "tma_ragged_m75_s2": (3, 64, 12, 12, 72, 4, 2, 0, "zeros", False, None),
     "narrow_16_32": (2, 16, 12, 12, 32, 3, 1, 1, "reflect", False, None),   # reduced-width nets of the golden fixtures
     "narrow_s2_8_16": (2, 8, 16, 16, 16, 4, 2, 1, "reflect", False, None),
+    # skinny kernels (conv_skinny.cu) at the geometries the model path produces (reflect padding pre-applied)
+    "c8_stem_valid7x7": (2, 3, 70, 70, 64, 7, 1, 0, "zeros", False, None),
+    "c8_zero3x3_nores": (2, 6, 16, 16, 128, 3, 1, 1, "zeros", True, None),
+    "c8_spade_shared_big": (4, 6, 40, 40, 128, 3, 1, 1, "zeros", True, (1, 1)),
+    "heads_valid_4": (2, 64, 18, 18, 4, 3, 1, 0, "zeros", False, None),
+    "heads_valid_128_zero": (1, 128, 12, 12, 3, 3, 1, 1, "zeros", False, None),
+    "d_cls_valid4x4": (4, 128, 4, 4, 6, 4, 1, 0, "zeros", False, None),
 }
 
 
@@ -171,7 +178,8 @@ def test_conv_fwd_fp32_out_and_epilogue():
 
 DGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "spade_gb_512", "heads_4", "ragged_m", "d_src_1", "cls_valid_k2",
                "narrow_16_32", "narrow_s2_8_16", "tma_valid3x3", "tma_zero3x3_256", "tma_persistent_200tiles", "tma_valid4x4s2",
-               "tma_valid7x7", "tma_ragged_m100", "tma_ragged_m75_s2", "tma_dgrad_s2_to8"]
+               "tma_valid7x7", "tma_ragged_m100", "tma_ragged_m75_s2", "tma_dgrad_s2_to8", "heads_valid_4",
+               "heads_valid_128_zero", "d_cls_valid4x4", "c8_stem_valid7x7"]
 
 
 @pytest.mark.parametrize("case", DGRAD_CASES)
@@ -194,7 +202,9 @@ def test_conv_dgrad(case):
 
 WGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "stem7x7", "spade_shared_8x8seg", "spade_gb_512", "heads_4",
                "ragged_m", "d_conv0", "d_src_1", "cls_valid_k2", "narrow_16_32", "narrow_s2_8_16", "tma_valid3x3",
-               "tma_zero3x3_256", "tma_persistent_200tiles", "tma_valid4x4s2"]
+               "tma_zero3x3_256", "tma_persistent_200tiles", "tma_valid4x4s2", "tma_dgrad_s2_to8", "c8_stem_valid7x7",
+               "c8_zero3x3_nores", "c8_spade_shared_big", "spade_shared_1x1seg", "heads_valid_4", "heads_valid_128_zero",
+               "d_cls_valid4x4"]
 
 
 @pytest.mark.parametrize("case", WGRAD_CASES)

@@ -153,21 +153,28 @@ static bool c8_affine(const Gather& g, int& dir, int& ystep, int& yoff, int& row
 
 constexpr int kC8Threads = 256;
 
+DEVINL void ldsm_x4(uint32_t (&r)[4], uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];\n"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
+               : "r"(addr));
+}
+
 template <int NT, bool FAST>
 __global__ void __launch_bounds__(kC8Threads, 2)
 conv_c8_fwd_kernel(const C8Params p) {
   extern __shared__ __align__(16) uint8_t c8_smem[];
   __shared__ int4 tap_tab[64];  // (dir * r, dir * s, element offset, 0); taps >= ntaps fail every bounds test
+  __shared__ __align__(8) float bias_s[NT * 8];
   const Gather& g = p.g;
   const Epilogue& e = p.e;
-  const int KP = p.ksteps * 16 + 8;  // weight row pitch in smem (elements): pitch in words == 4 (mod 8) -> conflict-free B reads
+  const int KP = p.ksteps * 16 + 8;  // weight row pitch in smem (elements): an odd number of 16-byte chunks -> conflict-free ldmatrix
   __nv_bfloat16* w_s = reinterpret_cast<__nv_bfloat16*>(c8_smem);
   constexpr int kStagePitch = NT * 16 + 16;  // bytes per staged output row (bf16), +16: conflict-free fragment writes
   uint8_t* stage_base = c8_smem + ((NT * 8 * KP * 2 + 15) & ~15);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int gid = lane >> 2, tq = lane & 3;
 
-  // weights -> smem (zero rows / columns beyond the real ones)
+  // weights -> smem (zero rows / columns beyond the real ones), tap table, bias
   {
     const int kreal = g.ntaps * 8;
     const int kw8 = KP / 8;
@@ -182,30 +189,39 @@ conv_c8_fwd_kernel(const C8Params p) {
       const int r = t / g.kw, s = t - r * g.kw;
       tap_tab[t] = t < g.ntaps ? make_int4(p.dir * r, p.dir * s, p.dir * (r * p.rowp + s * p.colp), 0) : make_int4(-(1 << 28), 0, 0, 0);
     }
+    if (threadIdx.x < NT * 8) bias_s[threadIdx.x] = (e.bias != nullptr && (int)threadIdx.x < e.ncols) ? __ldg(e.bias + threadIdx.x) : 0.f;
   }
   __syncthreads();
 
   const float osc = e.scale != nullptr ? __ldg(e.scale) : 1.f;
   const float nzw = e.noise != nullptr ? __ldg(e.noise_weight) : 0.f;
-  const int HoWo = g.Ho * g.Wo;
+  // none / leaky-relu / relu are max(v, slope * v); tanh and sigmoid take the (warp-uniform) slow branch
+  const float slope = e.act == ACT_LRELU ? 0.2f : (e.act == ACT_RELU ? 0.f : 1.f);
+  const bool slow_act = e.act == ACT_TANH || e.act == ACT_SIGMOID;
+  const unsigned M = (unsigned)g.M, HoWo = (unsigned)(g.Ho * g.Wo), Wo = (unsigned)g.Wo;
   uint8_t* stage = stage_base + warp * (16 * kStagePitch);
   const uint32_t* w_words = reinterpret_cast<const uint32_t*>(w_s);
   const int KPW = KP / 2;
+  // ldmatrix.x4 of B: matrices (n-tile j, k 0-7) (j, k 8-15) (j+1, k 0-7) (j+1, k 8-15); this lane supplies row (lane % 8) of matrix (lane / 8)
+  const uint32_t b_lane = smem_u32(w_s) + ((((lane >> 4) * 8 + (lane & 7)) * KP + ((lane >> 3) & 1) * 8) * 2);
+  // role in the coalesced copy of the staged tile: 16-byte chunk cp_ch of rows cp_row0, cp_row0 + cp_rows, ...
+  const int chunks = e.ld / 8;
+  const int cp_rows = 32 / chunks;
+  const int cp_row0 = lane / chunks, cp_ch = lane - cp_row0 * chunks;
 
   for (int tile = blockIdx.x; tile < p.m_tiles; tile += gridDim.x) {
-    const long long m_w = (long long)tile * 128 + warp * 16;
-    if (m_w >= g.M) continue;
+    const unsigned m_w = (unsigned)tile * 128u + (unsigned)warp * 16u;
+    if (m_w >= M) continue;
     int r_img[2], r_oy[2], r_ox[2];
     bool r_ok[2];
 #pragma unroll
     for (int h = 0; h < 2; ++h) {
-      const long long m = m_w + gid + 8 * h;
-      r_ok[h] = m < g.M;
-      const long long mm = r_ok[h] ? m : 0;
-      r_img[h] = (int)(mm / HoWo);
-      const int rem = (int)(mm - (long long)r_img[h] * HoWo);
-      r_oy[h] = rem / g.Wo;
-      r_ox[h] = rem - r_oy[h] * g.Wo;
+      const unsigned m = m_w + gid + 8 * h;
+      r_ok[h] = m < M;
+      const unsigned mm = r_ok[h] ? m : 0u;
+      const unsigned img = mm / HoWo, rem = mm - img * HoWo;
+      const unsigned oy = rem / Wo;
+      r_img[h] = (int)img; r_oy[h] = (int)oy; r_ox[h] = (int)(rem - oy * Wo);
     }
     float acc[NT][4];
 #pragma unroll
@@ -258,16 +274,21 @@ conv_c8_fwd_kernel(const C8Params p) {
     load_a(0, a_cur);
     for (int ks = 0; ks < p.ksteps; ++ks) {
       if (ks + 1 < p.ksteps) load_a(ks + 1, a_nxt);
-      const uint32_t* wb = w_words + gid * KPW + ks * 8 + tq;
+      const uint32_t baddr = b_lane + ks * 32;
 #pragma unroll
-      for (int j = 0; j < NT; ++j) {
-        const uint32_t b0 = wb[j * 8 * KPW];
-        const uint32_t b1 = wb[j * 8 * KPW + 4];
-        mma_bf16_16816(acc[j], a_cur, b0, b1);
+      for (int j = 0; j < NT; j += 4) {
+        uint32_t b0[4], b1[4];
+        ldsm_x4(b0, baddr + j * 8 * KP * 2);
+        ldsm_x4(b1, baddr + (j + 2) * 8 * KP * 2);
+        mma_bf16_16816(acc[j], a_cur, b0[0], b0[1]);
+        mma_bf16_16816(acc[j + 1], a_cur, b0[2], b0[3]);
+        mma_bf16_16816(acc[j + 2], a_cur, b1[0], b1[1]);
+        mma_bf16_16816(acc[j + 3], a_cur, b1[2], b1[3]);
       }
 #pragma unroll
       for (int i = 0; i < 4; ++i) a_cur[i] = a_nxt[i];
     }
+    (void)w_words; (void)KPW;
 
     // ---- epilogue: rows gid / gid + 8, columns j * 8 + 2 * tq (+1)
     float nz[2] = {0.f, 0.f};
@@ -279,16 +300,19 @@ conv_c8_fwd_kernel(const C8Params p) {
 #pragma unroll
     for (int j = 0; j < NT; ++j) {
       const int col = j * 8 + 2 * tq;
-      float b0 = 0.f, b1 = 0.f;
-      if (e.bias != nullptr) {
-        if (col < e.ncols) b0 = __ldg(e.bias + col);
-        if (col + 1 < e.ncols) b1 = __ldg(e.bias + col + 1);
-      }
+      const float2 bb = *reinterpret_cast<const float2*>(bias_s + col);
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
-        float v0 = apply_act(acc[j][2 * h] * osc + b0 + nz[h], e.act);
-        float v1 = apply_act(acc[j][2 * h + 1] * osc + b1 + nz[h], e.act);
-        const long long m = m_w + gid + 8 * h;
+        float v0 = fmaf(acc[j][2 * h], osc, bb.x + nz[h]);
+        float v1 = fmaf(acc[j][2 * h + 1], osc, bb.y + nz[h]);
+        if (slow_act) {
+          v0 = apply_act(v0, e.act);
+          v1 = apply_act(v1, e.act);
+        } else {
+          v0 = fmaxf(v0, v0 * slope);
+          v1 = fmaxf(v1, v1 * slope);
+        }
+        const long long m = (long long)m_w + gid + 8 * h;
         if (e.residual != nullptr && r_ok[h] && col < e.ld) {
           const uint32_t rv = __ldg(reinterpret_cast<const uint32_t*>(e.residual + m * e.ld + col));
           v0 += bf16lo(rv);
@@ -303,13 +327,13 @@ conv_c8_fwd_kernel(const C8Params p) {
     }
     if (!e.out_fp32) {
       __syncwarp();
-      const int chunks = e.ld / 8;  // 16-byte chunks per output row
-      for (int i = lane; i < 16 * chunks; i += 32) {
-        const int row = i / chunks, ch = i - row * chunks;
-        const long long m = m_w + row;
-        if (m < g.M)
-          *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out) + m * e.ld + ch * 8) =
-              *reinterpret_cast<const uint4*>(stage + row * kStagePitch + ch * 16);
+      if (cp_row0 < cp_rows) {
+        for (int row = cp_row0; row < 16; row += cp_rows) {
+          const unsigned m = m_w + row;
+          if (m < M)
+            *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(e.out) + (long long)m * e.ld + cp_ch * 8) =
+                *reinterpret_cast<const uint4*>(stage + row * kStagePitch + cp_ch * 16);
+        }
       }
       __syncwarp();
     }
@@ -336,7 +360,7 @@ static int launch_c8(const C8Params& p, cudaStream_t st) {
 }
 
 bool conv_c8_applicable(const Gather& g, int rows_ld) {
-  if (g.C != 8 || rows_ld > 128) return false;
+  if (g.C != 8 || rows_ld > 128 || g.M >= (1ll << 31) - 256) return false;
   const int ksteps = (g.ntaps + 1) / 2;
   const int nt = rows_ld <= 64 ? 8 : 16;
   return (size_t)nt * 8 * (ksteps * 16 + 8) * 2 <= 150 * 1024;
@@ -364,6 +388,12 @@ DEVINL void ldsm_x4_trans(uint32_t (&r)[4], uint32_t addr) {
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];\n"
                : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
                : "r"(addr));
+}
+// 16-byte cp.async through L1 (.ca): neighbouring taps / pixels re-read the same lines, and a 1 x 1 label map is ONE line that
+// every CTA reads for every tap - with .cg all of those requests would queue on a single L2 slice
+DEVINL void cp_async_16_ca(uint32_t dst_smem, const void* src, bool valid) {
+  uint32_t sz = valid ? 16u : 0u;
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst_smem), "l"(src), "r"(sz) : "memory");
 }
 DEVINL void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
 template <int N>
@@ -422,7 +452,7 @@ wgrad_c8_kernel(const WgC8Params p) {
       int iy, ix;
       const bool v = ok && c8_axis(g, oy, tap_r[t], g.Hl, g.Hs, iy) && c8_axis(g, ox, tap_s[t], g.Wl, g.Ws, ix);
       const __nv_bfloat16* src = v ? g.src + (((long long)img * g.Hs + iy) * g.Ws + ix) * 8 : g.src;
-      cp_async_16(s_a + my_pix * pitch_a + t * 16, src, v);
+      cp_async_16_ca(s_a + my_pix * pitch_a + t * 16, src, v);
     }
   };
 

@@ -1,0 +1,20 @@
+"""Print the handful of ncu raw-page metrics that decide what a kernel is bound by.  usage: ncu_brief.py report.ncu-rep"""
+import csv, subprocess, sys, io
+out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+rows = list(csv.reader(io.StringIO(out)))
+hdr, units = rows[0], rows[1]
+keys = ["gpu__time_duration.sum", "launch__grid_size", "launch__block_size", "launch__registers_per_thread",
+        "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active",
+        "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_tensor.sum",
+        "smsp__inst_executed.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed",
+        "lts__t_sectors_op_read.sum", "lts__t_sectors_op_write.sum", "l1tex__t_sectors_pipe_lsu_mem_global_op_ld.sum",
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum"]
+stalls = [h for h in hdr if h.startswith("smsp__average_warps_issue_stalled_") and h.endswith("_per_issue_active.ratio")]
+for r in rows[2:]:
+    print("=====", r[hdr.index("Kernel Name")][:100])
+    for k in keys:
+        if k in hdr:
+            i = hdr.index(k)
+            print(f"  {k:75s} {r[i][:40]:>20s} {units[i]}")
+    st = sorted(((float(r[hdr.index(h)] or 0), h) for h in stalls), reverse=True)[:6]
+    print("  top stalls (warps per issue):", ", ".join(f"{h.split('stalled_')[1].split('_per_issue')[0]}={v:.1f}" for v, h in st))

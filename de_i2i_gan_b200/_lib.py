@@ -51,6 +51,7 @@ SIGNATURES = {
     "dei2i_mse": (_I, [_P, _P, _LL, _P, _P, _P, _F, _I, _P]),
     "dei2i_ce_soft": (_I, [_P, _P, _I, _I, _P, _P, _F, _P]),
     "dei2i_adam": (_I, [_P, _P, _P, _P, _LL, _F, _F, _F, _F, _I, _P]),
+    "dei2i_adam_dev": (_I, [_P, _P, _P, _P, _LL, _P, _F, _F, _F, _P]),
     "dei2i_rmsprop": (_I, [_P, _P, _P, _LL, _F, _F, _F, _P]),
     "dei2i_clamp": (_I, [_P, _LL, _F, _F, _P]),
     "dei2i_ema": (_I, [_P, _P, _LL, _F, _P]),

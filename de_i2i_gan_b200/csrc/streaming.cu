@@ -748,6 +748,21 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
   }
 }
 
+// same update with (step_size, inv_sqrt_bc2) read from device memory: the launch is then identical every step and can live
+// inside a CUDA graph while the learning rate / bias corrections change
+__global__ void adam_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n,
+                                const float* __restrict__ hyper, float beta1, float beta2, float eps) {
+  const float step_size = __ldg(hyper), inv_sqrt_bc2 = __ldg(hyper + 1);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gi = g[i];
+    const float mi = beta1 * m[i] + (1.f - beta1) * gi;
+    const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] -= step_size * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
+  }
+}
+
 __global__ void rmsprop_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ sq, long long n, float lr,
                                float alpha, float eps) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
@@ -1010,6 +1025,15 @@ extern "C" int dei2i_adam(float* p, const float* g, float* m, float* v, long lon
   if (blocks > 148 * 16) blocks = 148 * 16;
   adam_kernel<<<blocks, 256, 0, ST>>>(p, g, m, v, n, (float)(lr / bc1), beta1, beta2, eps, (float)(1.0 / sqrt(bc2)));
   return LAUNCH_OK("adam_kernel");
+}
+
+extern "C" int dei2i_adam_dev(float* p, const float* g, float* m, float* v, long long n, const float* hyper, float beta1, float beta2,
+                              float eps, dei2i_stream stream) {
+  DEI2I_REQUIRE(p && g && m && v && hyper && n > 0, "adam_dev: bad arguments");
+  unsigned blocks = nblocks(n, 256 * 4);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  adam_dev_kernel<<<blocks, 256, 0, ST>>>(p, g, m, v, n, hyper, beta1, beta2, eps);
+  return LAUNCH_OK("adam_dev_kernel");
 }
 
 extern "C" int dei2i_rmsprop(float* p, const float* g, float* sq, long long n, float lr, float alpha, float eps, dei2i_stream stream) {

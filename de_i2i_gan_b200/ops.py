@@ -383,6 +383,11 @@ def adam(p, g, m, v, lr, beta1, beta2, eps, step):
     check(_lib.load().dei2i_adam(_p(p), _p(g), _p(m), _p(v), p.numel(), lr, beta1, beta2, eps, step, _stream()), "dei2i_adam")
 
 
+def adam_dev(p, g, m, v, hyper, beta1, beta2, eps):
+    """Adam step with hyper = device fp32 [lr / (1 - beta1^t), 1 / sqrt(1 - beta2^t)] (CUDA-graph friendly)."""
+    check(_lib.load().dei2i_adam_dev(_p(p), _p(g), _p(m), _p(v), p.numel(), _p(hyper), beta1, beta2, eps, _stream()), "dei2i_adam_dev")
+
+
 def rmsprop(p, g, sq, lr, alpha=0.99, eps=1e-8):
     check(_lib.load().dei2i_rmsprop(_p(p), _p(g), _p(sq), p.numel(), lr, alpha, eps, _stream()), "dei2i_rmsprop")
 

@@ -83,17 +83,32 @@ class FlatAdam(torch.optim.Optimizer):
         for f in self._flat:
             f["g"].zero_()
 
+    def advance(self):
+        """Host half of a step: counts the step and refreshes the two per-step scalars (lr / (1 - beta1^t) and
+        1 / sqrt(1 - beta2^t), computed in double like torch.optim.Adam) in DEVICE memory.  ``step()`` calls it itself, except while a CUDA graph is being captured: a graphed trainer step calls
+        ``advance()`` before every replay, the captured ``dei2i_adam_dev`` launch then reads the fresh values."""
+        for group, f in zip(self.param_groups, self._flat):
+            f["step"] += 1
+            b1, b2 = group["betas"]
+            t = f["step"]
+            if "hyper" not in f:
+                f["hyper"] = torch.zeros(2, dtype=torch.float32, device=f["p"].device)
+            # pageable source: the runtime stages the 8 bytes before returning, so the host may run ahead safely
+            f["hyper"].copy_(torch.tensor([float(group["lr"]) / (1.0 - b1 ** t), 1.0 / (1.0 - b2 ** t) ** 0.5], dtype=torch.float32))
+
     @torch.no_grad()
     def step(self, closure=None):
         loss = None
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
-        self._rebind()
+        capturing = torch.cuda.is_available() and torch.cuda.is_current_stream_capturing()
+        if not capturing:
+            self._rebind()
+            self.advance()
         for group, f in zip(self.param_groups, self._flat):
-            f["step"] += 1
             b1, b2 = group["betas"]
-            ops.adam(f["p"], f["g"], f["m"], f["v"], float(group["lr"]), float(b1), float(b2), float(group["eps"]), f["step"])
+            ops.adam_dev(f["p"], f["g"], f["m"], f["v"], f["hyper"], float(b1), float(b2), float(group["eps"]))
         return loss
 
 

@@ -8,12 +8,55 @@ throws them away (``optimizers['D'].zero_grad()`` precedes D's next use, :171), 
 TensorBoard logging is optional (only if ``opt.log_dir`` is set and tensorboard is importable); the FID / IS / LPIPS
 validation of ``--phase val`` needs downloaded weights and is out of the hot-path scope.
 """
+import os
 from collections import defaultdict
 
 import numpy as np
 import torch
 
 from .base_trainer import BaseTrainer
+
+
+class GraphedStep:
+    """One trainer step (zero_grad .. optimizer step) as a CUDA graph per input-shape signature.
+
+    Call 1 with a new signature runs the body eagerly (a real training step; it also triggers every lazy
+    initialisation: kernel attributes, workspaces, RNG state).  Call 2 captures the body into a graph - capture
+    executes nothing - and replays it; later calls copy the inputs into the static buffers, refresh the optimizer's
+    device-side scalars (FlatAdam.advance) and replay.  Everything inside the body is device work on the capturing
+    stream: libdei2i.so never synchronises or allocates, the noise maps come from torch's graph-safe Philox state,
+    spectral-norm u/v, BN running stats and Adam state are updated in place at fixed addresses."""
+
+    def __init__(self, body, optimizer, enabled, pool):
+        self.body, self.optimizer, self.enabled, self.pool = body, optimizer, enabled, pool
+        self.states = {}
+
+    def __call__(self, *inputs):
+        if not self.enabled:
+            return self.body(*inputs)
+        key = tuple((tuple(t.shape), t.dtype) for t in inputs)
+        st = self.states.get(key)
+        if st is None:
+            self.states[key] = {}
+            return self.body(*inputs)
+        if "graph" not in st:
+            dev = self.optimizer.flat_params[0].device
+            st["static"] = [torch.empty(t.shape, dtype=t.dtype, device=dev) for t in inputs]
+            for s, t in zip(st["static"], inputs):
+                s.copy_(t, non_blocking=True)
+            torch.cuda.synchronize()
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, pool=self.pool[0]):
+                st["out"] = self.body(*st["static"])
+            if self.pool[0] is None:
+                self.pool[0] = graph.pool()
+            st["graph"] = graph
+        else:
+            for s, t in zip(st["static"], inputs):
+                s.copy_(t, non_blocking=True)
+        self.optimizer.advance()
+        st["graph"].replay()
+        return st["out"]
 
 
 class DefectGanTrainer(BaseTrainer):
@@ -26,6 +69,14 @@ class DefectGanTrainer(BaseTrainer):
         if opt.phase == "val":
             raise NotImplementedError("--phase val (FID / IS / LPIPS with downloaded Inception weights) is out of the hot-path scope")
         self._d_params = list(self.model.netD.parameters())
+        # whole-step CUDA graphs: ~1200 launches per step become one graph launch
+        use_graph = getattr(opt, "cuda_graph", None)
+        if use_graph is None:
+            use_graph = os.environ.get("DEI2I_CUDA_GRAPH", "1") != "0"
+        use_graph = bool(use_graph) and torch.device(opt.device).type == "cuda"
+        pool = [None]
+        self._graphed = {"D": GraphedStep(self._d_body, self.optimizers["D"], use_graph, pool),
+                         "G": GraphedStep(self._g_body, self.optimizers["G"], use_graph, pool)}
 
     def _init_lr(self, opt):
         assert len(opt.lr) in (1, 2), f"length of lr must be 1 or 2, not {len(opt.lr)}"
@@ -35,8 +86,8 @@ class DefectGanTrainer(BaseTrainer):
         self.losses = {t: defaultdict(list) for t in self.loss_types}
 
     # ------------------------------------------------------------------------------------------------ the hot path
-    def _train_generator_once(self, bg_data, df_labels, df_data):
-        """defectgan_trainer.py:138-168."""
+    def _g_body(self, bg_data, df_labels, df_data):
+        """zero_grad -> loss graph -> weighted sum -> backward -> (all-reduce) -> Adam; returns the 5 loss scalars stacked."""
         self.optimizers["G"].zero_grad()
         for p in self._d_params:
             p.requires_grad_(False)
@@ -49,7 +100,19 @@ class DefectGanTrainer(BaseTrainer):
             for p in self._d_params:
                 p.requires_grad_(True)
         self._reduce_and_step("G")
-        vals = torch.stack([gan.detach(), clf.detach(), rec.detach(), cyc.detach(), con.detach()]).tolist()  # one D2H sync
+        return torch.stack([gan.detach(), clf.detach(), rec.detach(), cyc.detach(), con.detach()])
+
+    def _d_body(self, bg_data, df_labels, df_data):
+        self.optimizers["D"].zero_grad()
+        gan, clf = self.model("discriminator", bg_data, df_labels, df_data)
+        d_loss = gan + clf * self.loss_weights["clf_d"]
+        d_loss.backward()
+        self._reduce_and_step("D")
+        return torch.stack([gan.detach(), clf.detach()])
+
+    def _train_generator_once(self, bg_data, df_labels, df_data):
+        """defectgan_trainer.py:138-168."""
+        vals = self._graphed["G"](bg_data, df_labels, df_data).tolist()  # one D2H sync
         self.losses["gan"]["G"].append(vals[0])
         self.losses["clf"]["G"].append(vals[1])
         self.losses["aux"]["rec"].append(vals[2])
@@ -58,12 +121,7 @@ class DefectGanTrainer(BaseTrainer):
 
     def _train_discriminator_once(self, bg_data, df_labels, df_data):
         """defectgan_trainer.py:170-180."""
-        self.optimizers["D"].zero_grad()
-        gan, clf = self.model("discriminator", bg_data, df_labels, df_data)
-        d_loss = gan + clf * self.loss_weights["clf_d"]
-        d_loss.backward()
-        self._reduce_and_step("D")
-        vals = torch.stack([gan.detach(), clf.detach()]).tolist()
+        vals = self._graphed["D"](bg_data, df_labels, df_data).tolist()
         self.losses["gan"]["D"].append(vals[0])
         self.losses["clf"]["D"].append(vals[1])
 

@@ -175,6 +175,12 @@ int dei2i_ce_soft(const float* logits, const float* targets, int B, int C, float
 int dei2i_adam(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2,
                float eps, int step, dei2i_stream stream);
 
+/* The same step with the two per-step scalars in DEVICE memory: hyper[0] = lr / (1 - beta1^step),
+ * hyper[1] = 1 / sqrt(1 - beta2^step).  The launch arguments are then constant from step to step, so the optimizer step
+ * can be part of a captured CUDA graph of the whole D-step / G-step (trainers/defectgan_trainer.py:138-180). */
+int dei2i_adam_dev(float* p, const float* g, float* m, float* v, long long n, const float* hyper, float beta1, float beta2,
+                   float eps, dei2i_stream stream);
+
 /* torch.optim.RMSprop step (alpha 0.99, eps 1e-8, no momentum, not centered: trainers/base_trainer.py:76-77 with
  * options/wgan_options.py:49-57) and the WGAN weight clipping p.data.clamp_(lo, hi) (models/wgan_model.py:18-21). */
 int dei2i_rmsprop(float* p, const float* g, float* square_avg, long long n, float lr, float alpha, float eps,

@@ -1,0 +1,71 @@
+"""The trainer's CUDA-graph mode (GraphedStep, trainers/defectgan_trainer.py) against its eager mode: same seeds, same
+device-side deterministic noise, different inputs every step -> the same losses and parameters.  Exercises what a graph
+can get wrong: stale static inputs, Adam bias corrections / learning rate baked at capture, in-place state (spectral-norm
+u/v, BatchNorm running statistics) not advancing."""
+import pathlib
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _trainer(use_graph, tmp):
+    from de_i2i_gan_b200 import options
+    from de_i2i_gan_b200.trainers import find_trainer_using_model_name
+    torch.manual_seed(123)
+    opt = options.readme_recipe(image_size=128, batch_size=2, ngf=16, ndf=8, hidden_nc=32, num_critics=1, num_epochs=10,
+                                iters_per_epoch=100, name="graph_test", ckpt_dir=pathlib.Path(tmp))
+    opt.device = torch.device("cuda", 0)
+    opt.cuda_graph = use_graph
+    return find_trainer_using_model_name(opt.model)(opt)
+
+
+def _noise(n, h, w, device):  # device-side, deterministic, capturable
+    i = torch.arange(n * h * w, device=device, dtype=torch.float32)
+    return torch.sin(i * 0.37 + h).reshape(n, 1, h, w)
+
+
+def test_graphed_steps_match_eager(tmp_path):
+    from de_i2i_gan_b200.models.networks import architecture as A
+    g = torch.Generator().manual_seed(5)
+    batches = []
+    for _ in range(5):
+        bg = torch.randn(2, 3, 128, 128, generator=g).clamp(-1, 1)
+        df = torch.randn(2, 3, 128, 128, generator=g).clamp(-1, 1)
+        lab = (torch.rand(2, 6, generator=g) > 0.5).float()
+        lab[:, 0] = 0
+        batches.append((bg, lab, df))
+    A.set_noise_source(_noise)
+    try:
+        runs = {}
+        for mode in (False, True):
+            tr = _trainer(mode, tmp_path)
+            with torch.no_grad():  # non-zero noise weights so that the noise path matters
+                for n, p in tr.model.netG.named_parameters():
+                    if n.endswith("noise.weight") or "noise_" in n:
+                        p.fill_(0.1)
+            for it, (bg, lab, df) in enumerate(batches):
+                src = (bg, lab, df) if it % 2 else (bg.cuda(), lab.cuda(), df.cuda())  # host and device inputs
+                tr._train_discriminator_once(*src)
+                tr._train_generator_once(*src)
+                if it == 2:  # learning-rate change between replays must reach the captured Adam launch
+                    for o in tr.optimizers.values():
+                        for grp in o.param_groups:
+                            grp["lr"] *= 0.5
+            torch.cuda.synchronize()
+            losses = [tr.losses["gan"]["D"], tr.losses["clf"]["D"], tr.losses["gan"]["G"], tr.losses["aux"]["rec"], tr.losses["aux"]["con"]]
+            params = torch.cat([p.detach().flatten().cpu() for net in tr.model.networks.values() for p in net.parameters()])
+            bufs = torch.cat([b.detach().float().flatten().cpu() for net in tr.model.networks.values() for b in net.buffers()])
+            runs[mode] = (torch.tensor(losses), params, bufs)
+            if mode:
+                assert all("graph" in st for gs in tr._graphed.values() for st in gs.states.values()), "graphs were not captured"
+    finally:
+        A.set_noise_source(None)
+    (l0, p0, b0), (l1, p1, b1) = runs[False], runs[True]
+    assert torch.isfinite(l0).all() and torch.isfinite(l1).all()
+    # not bit-identical: a few FP32 reductions (statistics, losses) use atomics, and Adam amplifies noise-level gradient
+    # differences to +-lr per element; a stale input, learning rate or state buffer would be orders of magnitude off
+    assert (l0 - l1).abs().max().item() <= 2e-3 * l0.abs().max().item(), (l0, l1)
+    assert (p0 - p1).abs().mean().item() <= 2e-5, (p0 - p1).abs().mean().item()
+    assert (b0 - b1).abs().max().item() <= 2e-3 * b0.abs().max().item()

@@ -134,6 +134,8 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_b, const ConvKParams 
     float nz = 0.f;
     if (e.noise != nullptr && row_ok) nz = __ldg(e.noise + m) * __ldg(e.noise_weight);
     const float osc = e.scale != nullptr ? __ldg(e.scale) : 1.f;
+    const float slope = e.act == ACT_LRELU ? 0.2f : (e.act == ACT_RELU ? 0.f : 1.f);  // none / leaky / relu = max(x, slope * x)
+    const bool slow_act = e.act == ACT_TANH || e.act == ACT_SIGMOID;
     constexpr int CH = BLOCK_N >= 32 ? 32 : 16;
 #pragma unroll 1
     for (int c = 0; c < BLOCK_N; c += CH) {
@@ -151,7 +153,7 @@ conv_igemm_kernel(const __grid_constant__ CUtensorMap tmap_b, const ConvKParams 
           const int n = nbase + t;
           if (e.bias != nullptr && n < e.ncols) x += __ldg(e.bias + n);
           x += nz;
-          f[t] = apply_act(x, e.act);
+          f[t] = slow_act ? apply_act(x, e.act) : fmaxf(x, x * slope);
         }
         if (e.residual != nullptr) {
           const __nv_bfloat16* rp = e.residual + m * e.ld + nbase;

@@ -48,6 +48,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   const int lane = threadIdx.x & 31;
   constexpr uint32_t kTmemCols = 2 * BLOCK_N < 32 ? 32 : 2 * BLOCK_N;
   const int total_tiles = p.m_tiles * p.n_tiles;
+  __shared__ __align__(16) float bias_s[1024];
+  const bool bias_in_smem = p.e.bias != nullptr && p.n_tiles * BLOCK_N <= 1024;
+  if (bias_in_smem)
+    for (int i = threadIdx.x; i < p.n_tiles * BLOCK_N; i += kTmaThreads) bias_s[i] = i < p.e.ncols ? __ldg(p.e.bias + i) : 0.f;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < STAGES; ++s) {
@@ -138,6 +142,8 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     const OutMap& om = p.om;
     const float osc = e.scale != nullptr ? __ldg(e.scale) : 1.f;
     const float nzw = e.noise != nullptr ? __ldg(e.noise_weight) : 0.f;
+    const float slope = e.act == ACT_LRELU ? 0.2f : (e.act == ACT_RELU ? 0.f : 1.f);
+    const bool slow_act = e.act == ACT_TANH || e.act == ACT_SIGMOID;
     uint32_t tcount = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
       const uint32_t buf = tcount & 1u;
@@ -184,7 +190,15 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             for (int t = 0; t < 32; ++t) f[32 + t] = __uint_as_float(v[t]) * osc;
           }
         }
-        if (e.bias != nullptr) {
+        if (bias_in_smem) {  // zero-padded copy of the bias vector: no bounds logic, broadcast LDS.128
+#pragma unroll
+          for (int t4 = 0; t4 < 64; t4 += 4) {
+            if (t4 < CW) {
+              const float4 bv = *reinterpret_cast<const float4*>(bias_s + nbase + t4);
+              f[t4] += bv.x; f[t4 + 1] += bv.y; f[t4 + 2] += bv.z; f[t4 + 3] += bv.w;
+            }
+          }
+        } else if (e.bias != nullptr) {
 #pragma unroll
           for (int t4 = 0; t4 < 64; t4 += 4) {
             if (t4 < CW && nbase + t4 < e.ncols) {  // ncols (= Cout) may end inside a group of 4 only when Cout % 4 != 0
@@ -198,10 +212,17 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
             }
           }
         }
-        if (e.noise != nullptr || e.act != ACT_NONE) {
+        if (slow_act) {  // tanh / sigmoid: rare on this kernel (the heads go through the compose kernel)
 #pragma unroll
           for (int t = 0; t < 64; ++t)
             if (t < CW) f[t] = apply_act(f[t] + nz, e.act);
+        } else if (e.noise != nullptr || e.act != ACT_NONE) {  // none / leaky-relu / relu = max(v, slope * v): branch-free, tiny code
+#pragma unroll
+          for (int t = 0; t < 64; ++t)
+            if (t < CW) {
+              const float v = f[t] + nz;
+              f[t] = fmaxf(v, v * slope);
+            }
         }
         if (e.residual != nullptr) {  // bf16 [M, ld], linear rows; only with bf16 output (CW == 64)
 #pragma unroll
@@ -273,7 +294,7 @@ static int num_sms() {
 template <int BN, int ST>
 static int launch_tma(const CUtensorMap& ta, const CUtensorMap& tb, const TmaConvParams& p, cudaStream_t st) {
   using S = TmaSmem<BN, ST>;
-  static_assert(S::kTotal <= 227 * 1024, "shared memory budget");
+  static_assert(S::kTotal + 4096 <= 227 * 1024, "shared memory budget (dynamic + the static bias copy)");
   static_assert(S::kTotal > 114 * 1024, "one CTA per SM is required (the CTA owns up to all 512 TMEM columns)");
   static bool attr_done = false;
   if (!attr_done) {

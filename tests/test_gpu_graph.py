@@ -45,6 +45,7 @@ def test_graphed_steps_match_eager(tmp_path):
                 for n, p in tr.model.netG.named_parameters():
                     if n.endswith("noise.weight") or "noise_" in n:
                         p.fill_(0.1)
+            p_init = torch.cat([p.detach().flatten().cpu() for net in tr.model.networks.values() for p in net.parameters()])
             for it, (bg, lab, df) in enumerate(batches):
                 src = (bg, lab, df) if it % 2 else (bg.cuda(), lab.cuda(), df.cuda())  # host and device inputs
                 tr._train_discriminator_once(*src)
@@ -57,7 +58,7 @@ def test_graphed_steps_match_eager(tmp_path):
             losses = [tr.losses["gan"]["D"], tr.losses["clf"]["D"], tr.losses["gan"]["G"], tr.losses["aux"]["rec"], tr.losses["aux"]["con"]]
             params = torch.cat([p.detach().flatten().cpu() for net in tr.model.networks.values() for p in net.parameters()])
             bufs = torch.cat([b.detach().float().flatten().cpu() for net in tr.model.networks.values() for b in net.buffers()])
-            runs[mode] = (torch.tensor(losses), params, bufs)
+            runs[mode] = (torch.tensor(losses), params - p_init, bufs)
             if mode:
                 assert all("graph" in st for gs in tr._graphed.values() for st in gs.states.values()), "graphs were not captured"
     finally:
@@ -67,5 +68,9 @@ def test_graphed_steps_match_eager(tmp_path):
     # not bit-identical: a few FP32 reductions (statistics, losses) use atomics, and Adam amplifies noise-level gradient
     # differences to +-lr per element; a stale input, learning rate or state buffer would be orders of magnitude off
     assert (l0 - l1).abs().max().item() <= 2e-3 * l0.abs().max().item(), (l0, l1)
-    assert (p0 - p1).abs().mean().item() <= 2e-5, (p0 - p1).abs().mean().item()
+    # p0 / p1 are the 5-step parameter UPDATES: same direction and length (a learning rate frozen at capture time would make
+    # the graphed update ~25 % longer, a frozen bias correction shorter)
+    cos = (torch.dot(p0, p1) / (p0.norm() * p1.norm())).item()
+    ratio = (p1.norm() / p0.norm()).item()
+    assert cos > 0.99 and abs(ratio - 1.0) < 0.03, (cos, ratio)
     assert (b0 - b1).abs().max().item() <= 2e-3 * b0.abs().max().item()

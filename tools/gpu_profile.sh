@@ -1,7 +1,7 @@
 #!/bin/bash
 # ncu launch list of the last (timed) step of a short bench run (B200_PROFILING.md recipe); run only after the plain command exits 0
 mkdir -p gpurun_out
-CMD="python bench.py --steps 1 --warmup 3 --no-cpu-baseline --skip-e2e"
+CMD="env DEI2I_CUDA_GRAPH=0 python bench.py --steps 1 --warmup 3 --no-cpu-baseline --skip-e2e"
 $CMD > gpurun_out/plain.log 2>&1 || { echo "plain run failed"; tail -n 5 gpurun_out/plain.log; exit 1; }
 tail -n 1 gpurun_out/plain.log | cut -c1-300
 L=$(python -c "import json;print(json.loads(open('gpurun_out/plain.log').read().strip().splitlines()[-1])['gpu_launches'])")

@@ -30,6 +30,7 @@ int g_tune_conv_bn = 0;
 int g_tune_wgrad_bn = 0;
 int g_tune_wgrad_waves = 0;
 int g_tune_tma_dbg = 0;
+int g_tune_tma_ms = 0;
 int g_tune_conv_path = 0;  // 0 = auto (TMA im2col kernels where applicable), 1 = always the cp.async gather kernels
 static std::atomic<long long> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
@@ -137,6 +138,7 @@ extern "C" int dei2i_set_tuning(const char* key, int value) {
   else if (!strcmp(key, "wgrad_waves")) slot = &dei2i::g_tune_wgrad_waves;
   else if (!strcmp(key, "conv_path")) slot = &dei2i::g_tune_conv_path;
   else if (!strcmp(key, "tma_dbg")) slot = &dei2i::g_tune_tma_dbg;
+  else if (!strcmp(key, "tma_ms")) slot = &dei2i::g_tune_tma_ms;
   if (slot == nullptr) return -1;
   int old = *slot;
   *slot = value;

@@ -23,19 +23,19 @@ void count_launch(int n = 1);
 constexpr int kTmaThreads = 192;
 constexpr int kTmaATile = 128 * 128;  // 128 pixels x 64 bf16
 
-template <int BLOCK_N, int STAGES>
+template <int BLOCK_N, int STAGES, int MS>
 struct TmaSmem {
   static constexpr int kBTile = BLOCK_N * 128;
-  static constexpr int kStage = kTmaATile + kBTile;
+  static constexpr int kStage = MS * kTmaATile + kBTile;  // MS 128-pixel A tiles share one B tile
   static constexpr int kStageOut = STAGES * kStage;     // 4 epilogue warps x 4 KB output staging
   static constexpr int kBarOff = kStageOut + 4 * 4096;
   static constexpr int kTotal = kBarOff + (2 * STAGES + 4) * 8 + 16 + 1024 /*alignment slack*/;
 };
 
-template <int BLOCK_N, int STAGES>
+template <int BLOCK_N, int STAGES, int MS>
 __global__ void __launch_bounds__(kTmaThreads, 1)
 conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const TmaConvParams p) {
-  using S = TmaSmem<BLOCK_N, STAGES>;
+  using S = TmaSmem<BLOCK_N, STAGES, MS>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
@@ -46,7 +46,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  constexpr uint32_t kTmemCols = 2 * BLOCK_N < 32 ? 32 : 2 * BLOCK_N;
+  constexpr uint32_t kTmemCols = 2 * MS * BLOCK_N < 32 ? 32 : 2 * MS * BLOCK_N;
   const int total_tiles = p.m_tiles * p.n_tiles;
   __shared__ __align__(16) float bias_s[1024];
   const bool bias_in_smem = p.e.bias != nullptr && p.n_tiles * BLOCK_N <= 1024;
@@ -82,13 +82,17 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
         const int m_tile = tile / p.n_tiles;
         const int n_tile = tile - m_tile * p.n_tiles;
-        const long long m0 = (long long)m_tile * 128;
-        const int img = (int)(m0 / HoWo);
-        const int rem = (int)(m0 - (long long)img * HoWo);
-        const int pr = rem / p.Wo;
-        const int qc = rem - pr * p.Wo;
-        const int cw = qc * p.stride + p.lower;
-        const int ch = pr * p.stride + p.lower;
+        int img[MS], cw[MS], ch[MS];
+#pragma unroll
+        for (int ms = 0; ms < MS; ++ms) {
+          const long long m0 = ((long long)m_tile * MS + ms) * 128;
+          img[ms] = (int)(m0 / HoWo);
+          const int rem = (int)(m0 - (long long)img[ms] * HoWo);
+          const int pr = rem / p.Wo;
+          const int qc = rem - pr * p.Wo;
+          cw[ms] = qc * p.stride + p.lower;
+          ch[ms] = pr * p.stride + p.lower;
+        }
         int tap = 0, cb = 0, r = 0, s = 0;
         for (int kb = 0; kb < p.num_kb; ++kb, ++it) {
           const uint32_t stage = it % STAGES;
@@ -98,9 +102,11 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           mbar_arrive_expect_tx(&full_bar[stage], S::kStage);
           const int os = p.flip ? p.kw - 1 - s : s;
           const int orr = p.flip ? p.kh - 1 - r : r;
-          tma_load_im2col_4d(a_dst, &tmap_a, &full_bar[stage], cb * 64, cw, ch, img, (uint16_t)os, (uint16_t)orr);
+#pragma unroll
+          for (int ms = 0; ms < MS; ++ms)
+            tma_load_im2col_4d(a_dst + ms * kTmaATile, &tmap_a, &full_bar[stage], cb * 64, cw[ms], ch[ms], img[ms], (uint16_t)os, (uint16_t)orr);
           const int bcol = (((p.b_py + p.b_sub * r) * p.b_kw + (p.b_px + p.b_sub * s)) * p.cin_blocks + cb) * 64;
-          tma_load_2d(a_dst + kTmaATile, &tmap_b, &full_bar[stage], bcol, n_tile * BLOCK_N);
+          tma_load_2d(a_dst + MS * kTmaATile, &tmap_b, &full_bar[stage], bcol, n_tile * BLOCK_N);
           if (++cb == p.cin_blocks) {
             cb = 0;
             ++tap;
@@ -120,17 +126,20 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         const uint32_t bph = (tcount >> 1) & 1u;
         mbar_wait(&tempty_bar[buf], bph ^ 1u);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + buf * BLOCK_N;
+        const uint32_t d_tmem = tmem_base + buf * (MS * BLOCK_N);
         for (int kb = 0; kb < p.num_kb; ++kb, ++it) {
           const uint32_t stage = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1u;
           mbar_wait(&full_bar[stage], ph);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem + stage * S::kStage);
-          const uint64_t a_desc = make_smem_desc(a_addr, 16, 1024, 2);
-          const uint64_t b_desc = make_smem_desc(a_addr + kTmaATile, 16, 1024, 2);
+          const uint64_t b_desc = make_smem_desc(a_addr + MS * kTmaATile, 16, 1024, 2);
 #pragma unroll
-          for (int k = 0; k < 4; ++k) tc_mma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+          for (int ms = 0; ms < MS; ++ms) {
+            const uint64_t a_desc = make_smem_desc(a_addr + ms * kTmaATile, 16, 1024, 2);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) tc_mma_bf16(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+          }
           tc_commit(&empty_bar[stage]);
         }
         tc_commit(&tfull_bar[buf]);
@@ -150,7 +159,14 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       const uint32_t bph = (tcount >> 1) & 1u;
       const int m_tile = tile / p.n_tiles;
       const int n0 = (tile - m_tile * p.n_tiles) * BLOCK_N;
-      const long long m = (long long)m_tile * 128 + warp * 32 + lane;
+      mbar_wait(&tfull_bar[buf], bph);
+      tc_fence_after();
+#pragma unroll 1
+      for (int ms = 0; ms < MS; ++ms) {
+      const long long m_base = ((long long)m_tile * MS + ms) * 128;
+      if (m_base >= p.M) break;
+      const uint32_t tcol0 = buf * (MS * BLOCK_N) + ms * BLOCK_N;  // first TMEM column of this sub-tile's accumulator
+      const long long m = m_base + warp * 32 + lane;
       const bool row_ok = m < p.M;
       long long orow = m;  // output row index (in units of ld elements)
       if (!om.linear && row_ok) {
@@ -163,8 +179,6 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       }
       float nz = 0.f;
       if (e.noise != nullptr && row_ok) nz = __ldg(e.noise + m) * nzw;
-      mbar_wait(&tfull_bar[buf], bph);
-      tc_fence_after();
       // 128 bytes of output per row and pass: 64 bf16 columns or 32 fp32 columns.  Each lane finalises its own row,
       // parks it in the warp's 4 KB staging tile (16-byte chunks XOR-swizzled by row: conflict-free both ways) and the
       // warp then writes 4 full 128-byte rows per store instruction (8 lanes x 16 B per row) - coalesced, whatever the
@@ -179,12 +193,12 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         float f[64];
         {
           uint32_t v[32];
-          if (!(p.dbg & 2)) tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + buf * BLOCK_N + (uint32_t)c, v);
+          if (!(p.dbg & 2)) tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + tcol0 + (uint32_t)c, v);
           if (!(p.dbg & 2)) tc_wait_ld();
 #pragma unroll
           for (int t = 0; t < 32; ++t) f[t] = __uint_as_float(v[t]) * osc;
           if (CW == 64) {
-            if (!(p.dbg & 2)) tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + buf * BLOCK_N + (uint32_t)(c + 32), v);
+            if (!(p.dbg & 2)) tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + tcol0 + (uint32_t)(c + 32), v);
             if (!(p.dbg & 2)) tc_wait_ld();
 #pragma unroll
             for (int t = 0; t < 32; ++t) f[32 + t] = __uint_as_float(v[t]) * osc;
@@ -228,7 +242,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 #pragma unroll
           for (int itr = 0; itr < 8; ++itr) {
             const int r = itr * 4 + sub_r;
-            const long long mr = (long long)m_tile * 128 + warp * 32 + r;
+            const long long mr = m_base + warp * 32 + r;
             uint4 rv = make_uint4(0, 0, 0, 0);
             if (mr < p.M && nbase + sub_j * 8 < e.ld) rv = __ldg(reinterpret_cast<const uint4*>(e.residual + mr * e.ld + nbase + sub_j * 8));
             *reinterpret_cast<uint4*>(stage + r * 128 + ((sub_j ^ (r & 7)) << 4)) = rv;
@@ -268,6 +282,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         }
         __syncwarp();
       }
+      }  // ms
       tc_fence_before();
       mbar_arrive(&tempty_bar[buf]);
     }
@@ -291,24 +306,26 @@ static int num_sms() {
   return g_num_sms;
 }
 
-template <int BN, int ST>
+template <int BN, int ST, int MS>
 static int launch_tma(const CUtensorMap& ta, const CUtensorMap& tb, const TmaConvParams& p, cudaStream_t st) {
-  using S = TmaSmem<BN, ST>;
+  using S = TmaSmem<BN, ST, MS>;
   static_assert(S::kTotal + 4096 <= 227 * 1024, "shared memory budget (dynamic + the static bias copy)");
   static_assert(S::kTotal > 114 * 1024, "one CTA per SM is required (the CTA owns up to all 512 TMEM columns)");
+  static_assert(2 * MS * BN <= 512, "TMEM columns");
   static bool attr_done = false;
   if (!attr_done) {
-    DEI2I_CUDA(cudaFuncSetAttribute(conv_tma_kernel<BN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+    DEI2I_CUDA(cudaFuncSetAttribute(conv_tma_kernel<BN, ST, MS>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
     attr_done = true;
   }
   const int total = p.m_tiles * p.n_tiles;
   const int grid = total < num_sms() ? total : num_sms();
-  conv_tma_kernel<BN, ST><<<grid, kTmaThreads, S::kTotal, st>>>(ta, tb, p);
+  conv_tma_kernel<BN, ST, MS><<<grid, kTmaThreads, S::kTotal, st>>>(ta, tb, p);
   count_launch();
   return check_cuda(cudaGetLastError(), "conv_tma_kernel launch");
 }
 
 extern int g_tune_tma_dbg;
+extern int g_tune_tma_ms;  // 0 = auto, 1 / 2 = force the number of 128-pixel sub-tiles per work tile
 int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, int rows, int K, const TmaConvParams& p_in,
                  int upper, cudaStream_t st) {
   TmaConvParams p = p_in;
@@ -320,12 +337,18 @@ int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, in
                                        64, 128))
     return rc;
   if (int rc = encode_tmap_2d_bf16(&tb, wmat, (uint64_t)K, (uint64_t)rows, (uint64_t)K * 2, 64, (uint32_t)bn, 1)) return rc;
-  p.m_tiles = (int)((p.M + 127) / 128);
   p.n_tiles = (rows + bn - 1) / bn;
+  // narrow N: two 128-pixel A tiles share each B tile (halves the weight traffic per FLOP through L2 / shared memory) as long
+  // as that still leaves every SM a couple of work tiles
+  const long long mt2 = (p.M + 255) / 256;
+  int ms = (bn <= 128 && mt2 * p.n_tiles >= 2ll * num_sms()) ? 2 : 1;
+  if (g_tune_tma_ms == 1 || (g_tune_tma_ms == 2 && bn <= 128)) ms = g_tune_tma_ms;
+  p.m_tiles = (int)((p.M + 128 * ms - 1) / (128 * ms));
+  if (ms == 2) return bn == 128 ? launch_tma<128, 4, 2>(ta, tb, p, st) : launch_tma<64, 5, 2>(ta, tb, p, st);
   switch (bn) {
-    case 256: return launch_tma<256, 4>(ta, tb, p, st);
-    case 128: return launch_tma<128, 6>(ta, tb, p, st);
-    default: return launch_tma<64, 8>(ta, tb, p, st);
+    case 256: return launch_tma<256, 4, 1>(ta, tb, p, st);
+    case 128: return launch_tma<128, 6, 1>(ta, tb, p, st);
+    default: return launch_tma<64, 8, 1>(ta, tb, p, st);
   }
 }
 

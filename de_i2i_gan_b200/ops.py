@@ -106,6 +106,11 @@ class ConvSpec:
         return 2 * n * ho * wo * self.cout * self.cin * self.kh * self.kw_
 
     @property
+    def klass(self):
+        """'dense': both GEMM dimensions >= 64 channels -> tcgen05 kernels, tensor-bound; 'skinny': HBM-bound kernels."""
+        return "dense" if (self.cin_ld >= 64 and self.cout_ld >= 64) else "skinny"
+
+    @property
     def kf(self):
         return (self.kh * self.kw_ * self.cin_ld + 63) // 64 * 64
 
@@ -143,7 +148,7 @@ def conv2d_fwd(x, w_fwd, spec: ConvSpec, bias=None, noise=None, noise_weight=Non
         assert noise.numel() == n * ho * wo
     g = spec.geom(n, h, w, hs, ws)
     e = ConvEpilogue(_p(scale), _p(bias), _p(noise), _p(noise_weight), _p(residual), ACT[act], int(out_fp32))
-    with _Timed("conv_fwd", spec.flops(n, ho, wo), spec.tag(n, h, w)):
+    with _Timed("conv_fwd_" + spec.klass, spec.flops(n, ho, wo), spec.tag(n, h, w)):
         check(_lib.load().dei2i_conv2d_fwd(_p(x), _p(w_fwd), _p(y), C.byref(g), C.byref(e), _stream()), "dei2i_conv2d_fwd")
     return y
 
@@ -160,13 +165,13 @@ def conv2d_dgrad(dy, w_dgrad, spec: ConvSpec, in_hw, scale=None):
     if spec.pad_mode == "reflect" and spec.pad > 0:
         p = spec.pad
         dxp = torch.empty(n, h + 2 * p, w + 2 * p, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
-        with _Timed("conv_dgrad", flops, spec.tag(n, h, w)):
+        with _Timed("conv_dgrad_" + spec.klass, flops, spec.tag(n, h, w)):
             check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dxp), C.byref(g), _p(scale), 0, _stream()), "dei2i_conv2d_dgrad")
         dx = torch.empty(n, h, w, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
         check(lib.dei2i_reflect_fold(_p(dxp), _p(dx), n, h, w, spec.cin_ld, p, _stream()), "dei2i_reflect_fold")
         return dx
     dx = torch.empty(n, h, w, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
-    with _Timed("conv_dgrad", flops, spec.tag(n, h, w)):
+    with _Timed("conv_dgrad_" + spec.klass, flops, spec.tag(n, h, w)):
         check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dx), C.byref(g), _p(scale), 0, _stream()), "dei2i_conv2d_dgrad")
     return dx
 
@@ -214,7 +219,7 @@ def conv2d_wgrad(x, dy, dw, spec: ConvSpec, accumulate=False, sn=None, logical_h
     nbytes = lib.dei2i_conv2d_wgrad_workspace(C.byref(g), spec.cin)
     wsb = _workspace(nbytes, x.device)
     w0, u, v, inv = sn if sn is not None else (None, None, None, None)
-    with _Timed("conv_wgrad", spec.flops(n, dy.shape[1], dy.shape[2]), spec.tag(n, h, w)):
+    with _Timed("conv_wgrad_" + spec.klass, spec.flops(n, dy.shape[1], dy.shape[2]), spec.tag(n, h, w)):
         check(lib.dei2i_conv2d_wgrad(_p(x), _p(dy), _p(dw), spec.cin, 1.0 if accumulate else 0.0, C.byref(g), _p(w0), _p(u),
                                      _p(v), _p(inv), _p(wsb), wsb.numel(), _stream()), "dei2i_conv2d_wgrad")
     return dw

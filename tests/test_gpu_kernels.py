@@ -433,3 +433,27 @@ def test_errors_are_reported_not_fatal():
     w = torch.zeros(64, spec.kf, dtype=torch.bfloat16, device="cuda")
     with pytest.raises(RuntimeError, match="reflect"):
         ops.conv2d_fwd(x, w, spec)
+
+
+@pytest.mark.parametrize("case", ["tma_valid3x3", "tma_valid4x4s2", "tma_ragged_m100", "tma_ragged_m75_s2", "tma_persistent_200tiles"])
+def test_conv_tma_two_subtiles(case):
+    """conv_tma_kernel with MS = 2 (two 128-pixel A tiles per B tile; picked automatically only for large M): forward and dgrad."""
+    from de_i2i_gan_b200 import ops
+    n, cin, h, w, cout, k, s, p, pm, bias, rs = CONV_CASES[case]
+    x, wt, b = _make(case)
+    x.requires_grad_(True)
+    ref = ref_conv(x, wt, b, s, p, pm)
+    dy = q(torch.randn(ref.shape, generator=torch.Generator().manual_seed(9)))
+    (dx_ref,) = torch.autograd.grad(ref, x, dy)
+    spec = ops.ConvSpec(cin, cout, k, s, p, pm)
+    w_fwd, w_dg = ops.pack_weight(wt.cuda(), spec)
+    ops.set_tuning("tma_ms", 2)
+    try:
+        y = ops.conv2d_fwd(to_dev(x.detach()), w_fwd, spec, bias=b.cuda() if bias else None)
+        dx = ops.conv2d_dgrad(to_dev(dy), w_dg, spec, (h, w))
+        torch.cuda.synchronize()
+    finally:
+        ops.set_tuning("tma_ms", 0)
+    e1, e2 = rel_err(from_dev(y, cout), ref.detach()), rel_err(from_dev(dx, cin), dx_ref)
+    _report("conv_tma_ms2/" + case, err_fwd=e1, err_dgrad=e2)
+    assert e1 < TOL_BF16 and e2 < TOL_BF16, (e1, e2)

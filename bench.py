@@ -44,6 +44,9 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-sample-batch", type=int, default=2)
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: skip the pinned-host pass")
+    ap.add_argument("--spade-dense", action="store_true",
+                    help="evaluate SPADE gamma|beta with the dense full-resolution convolutions even for 1x1 label maps "
+                         "(default: exact 5x5 border-class map, see DESIGN.md 4a)")
     ap.add_argument("--breakdown", default=None, help="write a per-convolution-geometry timing table (JSON) to this path")
     return ap.parse_args()
 
@@ -174,6 +177,9 @@ def run_ours(args):
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device - the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    if args.spade_dense:
+        from de_i2i_gan_b200.models.networks import normalization
+        normalization.CONSTANT_LABEL_CLASSES = False
     rank, local, world = parallel.init_distributed()
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -300,7 +306,11 @@ def run_ours(args):
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic",
         "config": {"workload": f"DefectGAN full training step (1 D-step + 1 G-step) {H}x{H}, batch {B}/GPU, --add_noise --use_spectral",
-                   "global_batch": B * world, "parallelism": f"dp{world}", "algorithmic_tflop_per_step_per_gpu": conv_flops / args.steps / 1e12,
+                   "global_batch": B * world, "parallelism": f"dp{world}", "executed_conv_tflop_per_step_per_gpu": conv_flops / args.steps / 1e12,
+                   "reference_dense_conv_tflop_per_step_per_gpu": 81.3147 * (B / 32) * (H / 256) ** 2,
+                   "spade": ("dense full-resolution gamma|beta convolutions" if args.spade_dense else
+                             "gamma|beta evaluated exactly on the 5x5 border-class map of the 1x1 training label map "
+                             "(results identical; FLOPs of the dense evaluation are NOT credited - see executed vs reference TFLOP)"),
                    "l2": "no flush needed: every step streams its own activations (>> 126 MB L2)", "peak_mem_gb": round(mem_gb, 1),
                    "cuda_graph": graphed},
         "e2e": {"value": B * world / (ms_e2e * 1e-3 / args.steps), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

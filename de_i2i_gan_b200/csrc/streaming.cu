@@ -541,6 +541,169 @@ __global__ void spade_bwd2_kernel(const uint4* __restrict__ x, const uint4* __re
   }
 }
 
+// ------------------------------------------------------------------------------------------ SPADE over a border-class map
+// Training feeds SPADE a 1x1 label map (defectgan_model.py:185-205 -> normalization.py:29 nearest resize), i.e. a spatially
+// CONSTANT segmentation map.  Two stacked 3x3 zero-padded convolutions of a constant map take at most 5 distinct values per
+// axis (rows 0, 1, interior, H-2, H-1), so gamma|beta live on a [N,5,5,2C] map `gb5` and pixel (h,w) reads entry
+// (bcls(h,H), bcls(w,W)).  Exact (not an approximation); the dense kernels above remain for spatial label maps.
+DEVINL int bcls(int i, int n) { return i < 2 ? i : (i >= n - 2 ? i - n + 5 : 2); }
+
+__global__ void spade_cls_fwd_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, uint4* __restrict__ out,
+                                     const float* __restrict__ stats, float* __restrict__ mean_rstd, int N, int H, int W, int C8,
+                                     int up, int relu, float eps) {
+  extern __shared__ float sh[];  // mean[C], rstd[C]
+  const int C = C8 * 8;
+  const int n = blockIdx.y;
+  const int Hx = H / up, Wx = W / up;
+  const float cnt = (float)Hx * (float)Wx;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float mean = stats[(n * 2 + 0) * C + c] / cnt;
+    const float var = fmaxf(stats[(n * 2 + 1) * C + c] / cnt - mean * mean, 0.f);
+    const float rstd = rsqrtf(var + eps);
+    sh[c] = mean;
+    sh[C + c] = rstd;
+    if (blockIdx.x == 0) {
+      mean_rstd[(n * 2 + 0) * C + c] = mean;
+      mean_rstd[(n * 2 + 1) * C + c] = rstd;
+    }
+  }
+  __syncthreads();
+  const long long per_img = (long long)H * W * C8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img; i += (long long)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % C8);
+    const long long pix = i / C8;
+    const int w = (int)(pix % W), h = (int)(pix / W);
+    float fx[8], fg[8], fb[8], o[8];
+    unpack8(__ldg(x + (((long long)n * Hx + h / up) * Wx + w / up) * C8 + c8), fx);
+    const int gbase = ((n * 5 + bcls(h, H)) * 5 + bcls(w, W)) * (2 * C8);
+    unpack8(__ldg(gb5 + gbase + c8), fg);
+    unpack8(__ldg(gb5 + gbase + C8 + c8), fb);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float xh = (fx[k] - sh[c8 * 8 + k]) * sh[C + c8 * 8 + k];
+      const float t = xh * (1.f + fg[k]) + fb[k];
+      o[k] = relu ? fmaxf(t, 0.f) : t;
+    }
+    out[(long long)n * per_img + i] = pack8(o);
+  }
+}
+
+// backward pass 1 over whole rows [r0, r1) of image n: g = dout * (out > 0);  per border class  dgamma5 += g * xhat,
+// dbeta5 += g  (fp32 [N,5,5,2C], atomics);  S1 = sum g(1+gamma), S2 = sum g(1+gamma) xhat  per (n,c) into `red`.
+// smem table: 25 classes x 2C + one row [S1 | S2]; a thread keeps the sums of its current class in registers.
+__global__ void spade_cls_bwd1_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ out,
+                                      const uint4* __restrict__ dout, float* __restrict__ dgb5, const float* __restrict__ mean_rstd,
+                                      float* __restrict__ red /*[N,2,C]*/, int H, int W, int C8, int up, int rows, int relu) {
+  extern __shared__ float tab[];  // [26][2C]
+  const int c8 = threadIdx.x % C8;
+  const int lane = threadIdx.x / C8;
+  const int lanes = blockDim.x / C8;
+  const int C = C8 * 8;
+  const int n = blockIdx.y;
+  const int Hx = H / up, Wx = W / up;
+  const int r0 = blockIdx.x * rows, r1 = min(H, r0 + rows);
+  for (int i = threadIdx.x; i < 26 * 2 * C; i += blockDim.x) tab[i] = 0.f;
+  __syncthreads();
+  float mu[8], rs[8], s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  float ag[8] = {0, 0, 0, 0, 0, 0, 0, 0}, ab[8] = {0, 0, 0, 0, 0, 0, 0, 0}, fg[8];
+  int cur = -1;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    mu[k] = mean_rstd[(n * 2 + 0) * C + c8 * 8 + k];
+    rs[k] = mean_rstd[(n * 2 + 1) * C + c8 * 8 + k];
+  }
+  const long long img = (long long)n * H * W;
+  for (long long p = (long long)r0 * W + lane; p < (long long)r1 * W; p += lanes) {
+    const int w = (int)(p % W), h = (int)(p / W);
+    const int cls = bcls(h, H) * 5 + bcls(w, W);
+    if (cls != cur) {
+      if (cur >= 0) {
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          atomicAdd(&tab[cur * 2 * C + c8 * 8 + k], ag[k]);
+          atomicAdd(&tab[cur * 2 * C + C + c8 * 8 + k], ab[k]);
+          ag[k] = ab[k] = 0.f;
+        }
+      }
+      cur = cls;
+      unpack8(__ldg(gb5 + (n * 25 + cls) * (2 * C8) + c8), fg);
+    }
+    float fx[8], fo[8], fd[8];
+    unpack8(__ldg(x + (((long long)n * Hx + h / up) * Wx + w / up) * C8 + c8), fx);
+    unpack8(__ldg(out + (img + p) * C8 + c8), fo);
+    unpack8(__ldg(dout + (img + p) * C8 + c8), fd);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float xh = (fx[k] - mu[k]) * rs[k];
+      const float g = (!relu || fo[k] > 0.f) ? fd[k] : 0.f;
+      ag[k] += g * xh;
+      ab[k] += g;
+      const float dxh = g * (1.f + fg[k]);
+      s[k] += dxh;
+      q[k] += dxh * xh;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    if (cur >= 0) {
+      atomicAdd(&tab[cur * 2 * C + c8 * 8 + k], ag[k]);
+      atomicAdd(&tab[cur * 2 * C + C + c8 * 8 + k], ab[k]);
+    }
+    atomicAdd(&tab[25 * 2 * C + c8 * 8 + k], s[k]);
+    atomicAdd(&tab[25 * 2 * C + C + c8 * 8 + k], q[k]);
+  }
+  __syncthreads();
+  const int rc0 = bcls(r0, H), rc1 = bcls(r1 - 1, H);
+  const int span = (rc1 - rc0 + 1) * 5 * 2 * C;
+  for (int i = threadIdx.x; i < span; i += blockDim.x) atomicAdd(dgb5 + (size_t)n * 25 * 2 * C + rc0 * 5 * 2 * C + i, tab[rc0 * 5 * 2 * C + i]);
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(red + (size_t)n * 2 * C + i, tab[25 * 2 * C + i]);
+}
+
+// backward pass 2: dx[n,hx,wx,c] = rstd * (sum_{up x up} g (1 + gamma5) - up^2 S1/HW - xhat up^2 S2/HW),  g recomputed
+__global__ void spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ out,
+                                      const uint4* __restrict__ dout, uint4* __restrict__ dx, const float* __restrict__ mean_rstd,
+                                      const float* __restrict__ red, int H, int W, int C8, int up, int relu) {
+  extern __shared__ float sh[];  // mean, rstd, k1, k2
+  const int C = C8 * 8;
+  const int n = blockIdx.y;
+  const int Hx = H / up, Wx = W / up;
+  const float cnt = (float)H * (float)W;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    sh[c] = mean_rstd[(n * 2 + 0) * C + c];
+    sh[C + c] = mean_rstd[(n * 2 + 1) * C + c];
+    sh[2 * C + c] = red[(n * 2 + 0) * C + c] / cnt;
+    sh[3 * C + c] = red[(n * 2 + 1) * C + c] / cnt;
+  }
+  __syncthreads();
+  const long long per_img = (long long)Hx * Wx * C8;
+  const float uu = (float)(up * up);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img; i += (long long)gridDim.x * blockDim.x) {
+    const int c8 = (int)(i % C8);
+    const long long pix = i / C8;
+    const int wx = (int)(pix % Wx), hx = (int)(pix / Wx);
+    float fx[8], acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, o[8];
+    unpack8(__ldg(x + (long long)n * per_img + i), fx);
+    for (int dy = 0; dy < up; ++dy)
+      for (int dxx = 0; dxx < up; ++dxx) {
+        const int h = hx * up + dy, w = wx * up + dxx;
+        const long long p = ((long long)n * H + h) * W + w;
+        float fg[8], fo[8], fd[8];
+        unpack8(__ldg(gb5 + ((n * 5 + bcls(h, H)) * 5 + bcls(w, W)) * (2 * C8) + c8), fg);
+        unpack8(__ldg(out + p * C8 + c8), fo);
+        unpack8(__ldg(dout + p * C8 + c8), fd);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] += ((!relu || fo[k] > 0.f) ? fd[k] : 0.f) * (1.f + fg[k]);
+      }
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = c8 * 8 + k;
+      const float xh = (fx[k] - sh[c]) * sh[C + c];
+      o[k] = sh[C + c] * (acc[k] - uu * sh[2 * C + c] - xh * uu * sh[3 * C + c]);
+    }
+    dx[(long long)n * per_img + i] = pack8(o);
+  }
+}
+
 // ------------------------------------------------------------------------------------------ activation backward (+ column sums)
 __global__ void act_bwd_kernel(const uint4* __restrict__ y, const uint4* __restrict__ dy, uint4* __restrict__ dx, float* __restrict__ colsum,
                                long long M, int C8, int chunk, int act) {
@@ -943,6 +1106,51 @@ extern "C" int dei2i_spade_bwd(const void* x, const void* gb, const void* out, c
   spade_bwd2_kernel<<<dim3(bx, N), 256, 4 * C * sizeof(float), ST>>>((const uint4*)x, (const uint4*)gb, (const uint4*)dgb, (uint4*)dx,
                                                                      mean_rstd, scratch, H, W, C / 8, up);
   return LAUNCH_OK("spade_bwd2_kernel");
+}
+
+extern "C" int dei2i_spade_cls_fwd(const void* x, const void* gb5, void* out, const float* stats, float* mean_rstd, int N, int H,
+                                   int W, int C, int up, int relu, float eps, dei2i_stream stream) {
+  DEI2I_REQUIRE(x && gb5 && out && stats && mean_rstd && C % 8 == 0 && up >= 1 && H % up == 0 && W % up == 0 && H >= 5 && W >= 5,
+                "spade_cls_fwd: bad arguments (needs H, W >= 5)");
+  const long long per_img = (long long)H * W * (C / 8);
+  unsigned bx = nblocks(per_img, 256 * 2);
+  const unsigned cap = (148 * 16 + N - 1) / N;
+  if (bx > cap) bx = cap;
+  spade_cls_fwd_kernel<<<dim3(bx, N), 256, 2 * C * sizeof(float), ST>>>((const uint4*)x, (const uint4*)gb5, (uint4*)out, stats,
+                                                                        mean_rstd, N, H, W, C / 8, up, relu, eps);
+  return LAUNCH_OK("spade_cls_fwd_kernel");
+}
+
+extern "C" int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* out, const void* dout, float* dgb5, void* dx,
+                                   const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, int relu,
+                                   dei2i_stream stream) {
+  DEI2I_REQUIRE(x && gb5 && out && dout && dgb5 && dx && mean_rstd && scratch && C % 8 == 0 && C <= 512 && up >= 1 && H >= 5 && W >= 5,
+                "spade_cls_bwd: bad arguments (needs H, W >= 5, C <= 512)");
+  const int C8 = C / 8;
+  int lanes = 256 / C8;
+  if (lanes < 1) lanes = 1;
+  const int threads = lanes * C8;
+  // ~4 blocks per SM over the chip, whole rows per block
+  const int want = (148 * 4 + N - 1) / N;
+  int rows = (H + want - 1) / want;
+  if (rows < 1) rows = 1;
+  const unsigned gx = (unsigned)((H + rows - 1) / rows);
+  const size_t shmem = (size_t)26 * 2 * C * sizeof(float);
+  DEI2I_CUDA(cudaMemsetAsync(scratch, 0, (size_t)N * 2 * C * sizeof(float), ST));
+  DEI2I_CUDA(cudaMemsetAsync(dgb5, 0, (size_t)N * 25 * 2 * C * sizeof(float), ST));
+  if (shmem > 48 * 1024)
+    DEI2I_CUDA(cudaFuncSetAttribute(spade_cls_bwd1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
+  spade_cls_bwd1_kernel<<<dim3(gx, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out, (const uint4*)dout,
+                                                             dgb5, mean_rstd, scratch, H, W, C8, up, rows, relu);
+  if (int rc = LAUNCH_OK("spade_cls_bwd1_kernel")) return rc;
+  const long long per_img = (long long)(H / up) * (W / up) * C8;
+  unsigned bx = nblocks(per_img, 256 * 2);
+  const unsigned cap = (148 * 16 + N - 1) / N;
+  if (bx > cap) bx = cap;
+  spade_cls_bwd2_kernel<<<dim3(bx, N), 256, 4 * C * sizeof(float), ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out,
+                                                                         (const uint4*)dout, (uint4*)dx, mean_rstd, scratch, H, W, C8,
+                                                                         up, relu);
+  return LAUNCH_OK("spade_cls_bwd2_kernel");
 }
 
 extern "C" int dei2i_act_bwd(const void* y, const void* dy, void* dx, float* bias_grad, long long M, int C, int act,

@@ -16,10 +16,10 @@ from .ops import ConvSpec
 
 class Nhwc:
     """BF16 NHWC activation carrier. ``t``: [N,H,W,C_ld] (C_ld % 8 == 0), ``c``: real channels."""
-    __slots__ = ("t", "c")
+    __slots__ = ("t", "c", "cls5")
 
     def __init__(self, t: torch.Tensor, c: int):
-        self.t, self.c = t, c
+        self.t, self.c, self.cls5 = t, c, None
 
     @property
     def shape(self):  # logical NCHW shape, like the reference's tensors
@@ -268,6 +268,27 @@ class _Spade(Function):
 
 def spade_modulate(x: Nhwc, gb: Nhwc, up=1, relu=True, eps=1e-5) -> Nhwc:
     return Nhwc(_Spade.apply(x.t, gb.t, up, relu, eps), x.c)
+
+
+class _SpadeCls(Function):
+    """SPADE modulation with gamma|beta on the [N,5,5,2C] border-class map of a constant label map."""
+
+    @staticmethod
+    def forward(ctx, x, gb5, up, relu, eps):
+        out, mr = ops.spade_cls_fwd(x, gb5, up, relu, eps)
+        ctx.up, ctx.relu = up, relu
+        ctx.save_for_backward(x, gb5, out, mr)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, gb5, out, mr = ctx.saved_tensors
+        dgb5, dx = ops.spade_cls_bwd(x, gb5, out, dout.contiguous(), mr, ctx.up, ctx.relu)
+        return dx, dgb5.to(torch.bfloat16), None, None, None
+
+
+def spade_modulate_cls(x: Nhwc, gb5: Nhwc, up=1, relu=True, eps=1e-5) -> Nhwc:
+    return Nhwc(_SpadeCls.apply(x.t, gb5.t, up, relu, eps), x.c)
 
 
 class _Compose(Function):

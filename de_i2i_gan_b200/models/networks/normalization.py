@@ -5,11 +5,17 @@ parameter containers only - forward runs the fused path:
     actv --ONE 3x3 conv with N = 2C (gamma | beta)--> gb
     (x, gb) --instance-norm statistics + modulation (+ ReLU, + 2x nearest up-sampling of x)--> out
 """
+import os
+
 import torch
 from torch import nn
 
 from ... import functional as Fn
 from ...ops import ConvSpec
+
+
+# Exact evaluation of gamma|beta on the 5x5 border-class map when the label map is 1x1 (False: always the dense convs)
+CONSTANT_LABEL_CLASSES = os.environ.get("DEI2I_SPADE_DENSE", "0") != "1"
 
 
 class SPADE(nn.Module):
@@ -36,6 +42,16 @@ class SPADE(nn.Module):
         n, _, hx, wx = xa.shape
         h, w = hx * up, wx * up
         sconv = self.mlp_shared[0]
+        if CONSTANT_LABEL_CLASSES and seg.t.shape[1] == 1 and seg.t.shape[2] == 1 and h >= 5 and w >= 5 \
+                and self._shared_spec.k == 3 and self._shared_spec.pad == 1:
+            # 1x1 label map (every training call, defectgan_model.py:185-205): the nearest-resized map is constant, so
+            # mlp_shared -> mlp_gamma|mlp_beta are evaluated on the 5x5 border-class map (exact; dei2i_spade_cls_fwd)
+            if seg.cls5 is None:
+                seg.cls5 = Fn.Nhwc(seg.t.expand(n, 5, 5, seg.t.shape[3]).contiguous(), seg.c)
+            actv = Fn.conv(seg.cls5, sconv, self._shared_spec, self.training, bias=sconv.bias, act="relu")
+            gb5 = Fn.conv_cat(actv, self.mlp_gamma, self.mlp_beta, self._gb_spec)
+            out = Fn.spade_modulate_cls(xa, gb5, up=up, relu=relu, eps=self.param_free_norm.eps)
+            return Fn.from_nhwc(out) if plain else out
         actv = Fn.conv(seg, sconv, self._shared_spec, self.training, bias=sconv.bias, act="relu", logical_hw=(h, w))
         gb = Fn.conv_cat(actv, self.mlp_gamma, self.mlp_beta, self._gb_spec)
         out = Fn.spade_modulate(xa, gb, up=up, relu=relu, eps=self.param_free_norm.eps)

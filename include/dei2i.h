@@ -137,6 +137,19 @@ int dei2i_spade_bwd(const void* x, const void* gb, const void* out, const void* 
                     const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, int relu,
                     dei2i_stream stream);
 
+/* SPADE modulation over a border-class map: the training path feeds SPADE a 1x1 label map (defectgan_model.py:185-205),
+ * which normalization.py:29 nearest-resizes to a spatially constant map; mlp_shared -> mlp_gamma/mlp_beta (two stacked
+ * zero-padded 3x3 convolutions, normalization.py:30-32) then take 5 distinct values per axis (rows 0, 1, interior, H-2,
+ * H-1).  gb5: bf16 [N,5,5,2C] = the same convolutions evaluated on a constant 5x5 map; pixel (h,w) uses entry
+ * (cls(h), cls(w)).  Exact restructuring of normalization.py:24-37, H, W >= 5.
+ * backward: dgb5 fp32 [N,5,5,2C] (class-wise sums of the per-pixel gamma/beta gradients, written), dx bf16;
+ * scratch fp32 [N,2,C]. */
+int dei2i_spade_cls_fwd(const void* x, const void* gb5, void* out, const float* stats, float* mean_rstd, int N, int H,
+                        int W, int C, int up, int relu, float eps, dei2i_stream stream);
+int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* out, const void* dout, float* dgb5, void* dx,
+                        const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, int relu,
+                        dei2i_stream stream);
+
 /* act backward for fused conv epilogues: dx = dy * act'(y) computed from the saved OUTPUT y (bf16);
  * bias_grad (fp32 [C], may be NULL) receives sum over pixels of dx. */
 int dei2i_act_bwd(const void* y, const void* dy, void* dx, float* bias_grad, long long M, int C, int act,

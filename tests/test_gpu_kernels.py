@@ -338,6 +338,89 @@ def test_spade_fwd_bwd(up):
     assert e_out < TOL_BF16 and max(e) < 2e-2, (e_out, e)
 
 
+def _cls_index(n):
+    return torch.tensor([i if i < 2 else (i - n + 5 if i >= n - 2 else 2) for i in range(n)])
+
+
+@pytest.mark.parametrize("up,hx,wx,c", [(1, 8, 8, 64), (2, 8, 6, 64), (1, 5, 7, 256), (2, 16, 16, 128)])
+def test_spade_cls_fwd_bwd(up, hx, wx, c):
+    """SPADE over the 5x5 border-class map vs plain torch on the gathered full-resolution gamma / beta."""
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(16)
+    n = 3
+    h, w = hx * up, wx * up
+    x = q(torch.randn(n, c, hx, wx, generator=g) * 2 + 1).requires_grad_(True)
+    gamma5 = q(torch.randn(n, c, 5, 5, generator=g) * 0.5).requires_grad_(True)
+    beta5 = q(torch.randn(n, c, 5, 5, generator=g) * 0.5).requires_grad_(True)
+    ih, iw = _cls_index(h), _cls_index(w)
+    gamma = gamma5[:, :, ih][:, :, :, iw]
+    beta = beta5[:, :, ih][:, :, :, iw]
+    xu = F.interpolate(x, scale_factor=up, mode="nearest") if up > 1 else x
+    out_ref = F.relu(F.instance_norm(xu, eps=1e-5) * (1 + gamma) + beta)
+    dout = q(torch.randn(out_ref.shape, generator=g))
+    dx_ref, dg_ref, db_ref = torch.autograd.grad(out_ref, (x, gamma5, beta5), dout)
+    xd, gbd = to_dev(x.detach()), to_dev(torch.cat([gamma5.detach(), beta5.detach()], 1))
+    out, mr = ops.spade_cls_fwd(xd, gbd, up)
+    e_out = rel_err(from_dev(out, c), out_ref)
+    dgb5, dx = ops.spade_cls_bwd(xd, gbd, out, to_dev(dout), mr, up)
+    torch.cuda.synchronize()
+    dgb_h = dgb5.cpu().permute(0, 3, 1, 2)
+    e = (rel_err(dx.float().cpu().permute(0, 3, 1, 2), dx_ref), rel_err(dgb_h[:, :c], dg_ref), rel_err(dgb_h[:, c:], db_ref))
+    _report(f"spade_cls/up{up}/{hx}x{wx}x{c}", out=e_out, dx=e[0], dgamma=e[1], dbeta=e[2])
+    assert e_out < TOL_BF16 and e[0] < 2e-2 and max(e[1:]) < 5e-3, (e_out, e)
+
+
+def test_spade_module_class_map_equals_dense():
+    """SPADE module on a 1x1 label map: border-class path == dense path == the reference formula (normalization.py:24-37)."""
+    from de_i2i_gan_b200.models.networks import normalization as nz
+    g = torch.Generator().manual_seed(21)
+    torch.manual_seed(5)
+    n, c, hx, up = 2, 64, 12, 2
+    mod = nz.SPADE(6, c, hidden_nc=128, kernel_size=(3, 3), padding="same", norm_layer=torch.nn.InstanceNorm2d).cuda()
+    with torch.no_grad():
+        for p_ in mod.parameters():
+            p_.copy_(q(p_.detach().cpu() * 3).cuda())
+    x = q(torch.randn(n, c, hx, hx, generator=g))
+    lab = (torch.rand(n, 6, 1, 1, generator=g) > 0.5).float()
+    dout = q(torch.randn(n, c, hx * up, hx * up, generator=g))
+
+    def run(flag):
+        nz.CONSTANT_LABEL_CLASSES = flag
+        xg = x.cuda().requires_grad_(True)
+        mod.zero_grad()
+        out = mod(xg, lab.cuda(), up=up, relu=True)
+        out.backward(dout.cuda())
+        return out.detach().cpu(), xg.grad.cpu(), [p_.grad.detach().cpu().clone() for p_ in mod.parameters()]
+
+    try:
+        o1, dx1, gp1 = run(True)
+        o0, dx0, gp0 = run(False)
+    finally:
+        nz.CONSTANT_LABEL_CLASSES = True
+    # reference formula in fp32 on the CPU
+    xr = x.clone().requires_grad_(True)
+    ps = [p_.detach().cpu().clone().requires_grad_(True) for p_ in mod.parameters()]
+    names = [k for k, _ in mod.named_parameters()]
+    pd = dict(zip(names, ps))
+    xu = F.interpolate(xr, scale_factor=up, mode="nearest")
+    seg = F.interpolate(lab, size=xu.shape[2:], mode="nearest")
+    ste = lambda t: t + (q(t.detach()) - t.detach())  # BF16 storage of the intermediates (straight-through): keeps ReLU masks equal
+    actv = ste(F.relu(F.conv2d(seg, pd["mlp_shared.0.weight"], pd["mlp_shared.0.bias"], padding=1)))
+    gamma = ste(F.conv2d(actv, pd["mlp_gamma.weight"], pd["mlp_gamma.bias"], padding=1))
+    beta = ste(F.conv2d(actv, pd["mlp_beta.weight"], pd["mlp_beta.bias"], padding=1))
+    out_ref = F.relu(F.instance_norm(xu, eps=1e-5) * (1 + gamma) + beta)
+    grads = torch.autograd.grad(out_ref, [xr] + ps, dout)
+    l2 = lambda a, b: ((a - b).norm() / b.norm()).item()  # a flipped ReLU mask is a one-pixel 100 % error: L2, not max
+    e_cls = [rel_err(o1, out_ref), l2(dx1, grads[0])] + [l2(a, b) for a, b in zip(gp1, grads[1:])]
+    e_dense = [rel_err(o0, out_ref), l2(dx0, grads[0])] + [l2(a, b) for a, b in zip(gp0, grads[1:])]
+    _report("spade_module/class_map_vs_ref", errs=e_cls)
+    _report("spade_module/dense_vs_ref", errs=e_dense)
+    print("cls", e_cls, "dense", e_dense, "cls-vs-dense dx", rel_err(dx1, dx0))
+    assert max(e_cls) < 2e-2, e_cls
+    assert max(e_dense) < 2e-2, e_dense
+    assert rel_err(o1, o0) < TOL_BF16
+
+
 @pytest.mark.parametrize("act", ["leaky_relu", "relu", "tanh", "sigmoid", None])
 def test_act_bwd_and_bias_grad(act):
     from de_i2i_gan_b200 import ops

@@ -83,8 +83,9 @@ typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t
                                    const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave,
                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-int encode_tmap_im2col_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t W, uint64_t H, uint64_t N, int lower,
-                            int upper, uint32_t stride, uint32_t channels_per_pixel, uint32_t pixels_per_column) {
+int encode_tmap_im2col_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t W, uint64_t H, uint64_t N, int lower_w,
+                            int upper_w, int lower_h, int upper_h, uint32_t stride, uint32_t channels_per_pixel,
+                            uint32_t pixels_per_column) {
   static EncodeIm2colFn fn = nullptr;
   static bool tried = false;
   static int driver_version = 0;
@@ -107,15 +108,15 @@ int encode_tmap_im2col_bf16(CUtensorMap* out, const void* base, uint64_t C, uint
   }
   cuuint64_t dims[4] = {C, W, H, N};
   cuuint64_t strides[3] = {C * 2, W * C * 2, H * W * C * 2};
-  int lo[2] = {lower, lower};
-  int up[2] = {upper, upper};
+  int lo[2] = {lower_w, lower_h};
+  int up[2] = {upper_w, upper_h};
   cuuint32_t estr[4] = {1, stride, stride, 1};
   CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lo, up, channels_per_pixel,
                   pixels_per_column, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_error("cuTensorMapEncodeIm2col failed with CUresult %d (C %llu W %llu H %llu N %llu lower %d upper %d stride %u)", (int)r,
-              (unsigned long long)C, (unsigned long long)W, (unsigned long long)H, (unsigned long long)N, lower, upper, stride);
+              (unsigned long long)C, (unsigned long long)W, (unsigned long long)H, (unsigned long long)N, lower_h, upper_h, stride);
     return DEI2I_ERR_CUDA;
   }
   // Known driver issue (drivers <= 13.1; same workaround as CUTLASS make_im2col_tma_copy_desc): for tensors smaller than

@@ -31,8 +31,9 @@ int encode_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint
                         uint64_t row_pitch_bytes, uint32_t box_inner, uint32_t box_outer, int swizzle128);
 
 // NHWC activation [N, H, W, C] as an im2col tensor map: bounding box [lower, dim + upper) in W and H, traversal stride.
-int encode_tmap_im2col_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t W, uint64_t H, uint64_t N, int lower,
-                            int upper, uint32_t stride, uint32_t channels_per_pixel, uint32_t pixels_per_column);
+int encode_tmap_im2col_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t W, uint64_t H, uint64_t N, int lower_w,
+                            int upper_w, int lower_h, int upper_h, uint32_t stride, uint32_t channels_per_pixel,
+                            uint32_t pixels_per_column);
 
 // ------------------------------------------------------------------ misc
 DEVINL uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }

@@ -79,7 +79,8 @@ struct TmaConvParams {
   int Ho, Wo;      // traversal (GEMM row) domain per image
   long long M;     // N * Ho * Wo
   int stride;      // traversal stride of the im2col descriptor
-  int lower;       // bounding-box lower corner (W and H)
+  int lower;       // bounding-box lower corner in H
+  int lower_w;     // ... and in W (differs from `lower` for non-square filters)
   int kh, kw;      // filter size (tap t = r * kw + s)
   int flip;        // 1: TMA filter offsets are (kh-1-r, kw-1-s) - dgrad as a convolution over dY with the un-flipped weight pack
   int cin_blocks;  // input channels / 64
@@ -97,7 +98,7 @@ struct TmaConvParams {
 struct TmaWgradParams {
   int Ho, Wo;        // output (dY) domain per image = traversal domain of the im2col descriptor over x
   long long M;       // N * Ho * Wo
-  int stride, lower, kw;
+  int stride, lower, lower_w, kw;  // lower: bounding-box lower corner in H, lower_w: in W
   int cin_blocks;    // Cin / 64
   int num_boxes;     // taps * cin_blocks  (64-wide K slices of the packed weight layout)
   int k_tiles;       // ceil(num_boxes / 4)
@@ -109,7 +110,7 @@ struct TmaWgradParams {
 
 void wgrad_tma_plan(TmaWgradParams& p);
 int run_wgrad_tma(const void* x, int N, int H, int W, int C, const void* dy, int cout_ld, TmaWgradParams& p, int upper,
-                  cudaStream_t st);
+                  int upper_w, cudaStream_t st);
 
 // conv_skinny.cu
 int wgrad_narrow_splits(int Kreal, int Cout_ld, long long M);
@@ -126,6 +127,6 @@ int run_conv_c8(const Gather& g, const Epilogue& e, const void* wmat, int rows, 
 
 // returns 0 on success; the caller has checked applicability (see tma_conv_applicable)
 int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, int rows, int K, const TmaConvParams& p,
-                 int upper, cudaStream_t st);
+                 int upper, int upper_w, cudaStream_t st);
 
 }  // namespace dei2i

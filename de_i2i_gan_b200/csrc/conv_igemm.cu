@@ -508,7 +508,8 @@ static bool tma_applicable(const dei2i_conv_geom* g, int k_channels, long long M
   if (g_tune_conv_path == 1) return false;
   if (g->pad_mode == DEI2I_PAD_REFLECT && g->pad > 0) return false;
   if (g->Hs != g->H || g->Ws != g->W) return false;
-  if (g->kh != g->kw || g->kh > 16 || g->pad > 64 || g->stride > 8) return false;
+  if (g->kh > 16 || g->kw > 16 || g->pad > 64 || g->stride > 8) return false;
+  if (g->kh != g->kw && g->pad != 0) return false;  // non-square filters: 'valid' convolutions only (pre-padded inputs)
   (void)M;  // a ragged last tile is fine: im2col TMA zero-fills past the end of the tensor, the epilogue masks rows >= M
   if (k_channels % 64 != 0) return false;
   return true;
@@ -529,7 +530,7 @@ extern "C" int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const
   if (tma_applicable(g, g->Cin, (long long)g->N * Ho * Wo)) {
     TmaConvParams t;
     memset(&t, 0, sizeof(t));
-    t.Ho = Ho; t.Wo = Wo; t.M = (long long)g->N * Ho * Wo; t.stride = g->stride; t.lower = -g->pad;
+    t.Ho = Ho; t.Wo = Wo; t.M = (long long)g->N * Ho * Wo; t.stride = g->stride; t.lower = -g->pad; t.lower_w = -g->pad;
     t.kh = g->kh; t.kw = g->kw; t.flip = 0; t.cin_blocks = g->Cin / 64; t.num_kb = g->kh * g->kw * t.cin_blocks;
     t.b_sub = 1; t.b_kw = g->kw;
     t.om.linear = 1;
@@ -537,7 +538,7 @@ extern "C" int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const
     t.e.residual = (const __nv_bfloat16*)e->residual; t.e.out = y; t.e.act = e->act; t.e.out_fp32 = e->out_fp32;
     t.e.ld = g->Cout_ld; t.e.ncols = g->Cout;
     return run_conv_tma(x, g->N, g->H, g->W, g->Cin, w_fwd, g->Cout, g->kh * g->kw * g->Cin, t, g->pad - (g->kh - 1),
-                        (cudaStream_t)stream);
+                        g->pad - (g->kw - 1), (cudaStream_t)stream);
   }
   p.g.src = (const __nv_bfloat16*)x;
   p.g.N = g->N; p.g.Hl = g->H; p.g.Wl = g->W; p.g.Hs = g->Hs; p.g.Ws = g->Ws; p.g.C = g->Cin;
@@ -561,7 +562,7 @@ extern "C" int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx,
   ConvKParams p;
   memset(&p, 0, sizeof(p));
   const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
-  if (g->stride > 1 && g->pad == 0 && g->kh % g->stride == 0 && (g->H - g->kh) % g->stride == 0 &&
+  if (g->stride > 1 && g->pad == 0 && g->kh == g->kw && g->kh % g->stride == 0 && (g->H - g->kh) % g->stride == 0 &&
       (g->W - g->kw) % g->stride == 0 && tma_applicable(g, g->Cout_ld, 0)) {
     // fractionally-strided ("transposed") convolution as stride^2 dense stride-1 sub-convolutions over dY:
     //   dX[s*a + py, s*b + px] = sum_{t,u} dY[a - t, b - u] * W[py + s*t, px + s*u]      (no multiply-by-zero work)
@@ -570,13 +571,13 @@ extern "C" int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx,
       for (int px = 0; px < sd; ++px) {
         TmaConvParams t;
         memset(&t, 0, sizeof(t));
-        t.Ho = g->H / sd; t.Wo = g->W / sd; t.M = (long long)g->N * t.Ho * t.Wo; t.stride = 1; t.lower = -(kt - 1);
+        t.Ho = g->H / sd; t.Wo = g->W / sd; t.M = (long long)g->N * t.Ho * t.Wo; t.stride = 1; t.lower = -(kt - 1); t.lower_w = -(kt - 1);
         t.kh = kt; t.kw = kt; t.flip = 1; t.cin_blocks = g->Cout_ld / 64; t.num_kb = kt * kt * t.cin_blocks;
         t.b_sub = sd; t.b_py = py; t.b_px = px; t.b_kw = g->kw;
         t.om.linear = 0; t.om.Ho = t.Ho; t.om.Wo = t.Wo; t.om.OH = g->H; t.om.OW = g->W; t.om.osy = sd; t.om.osx = sd;
         t.om.oy0 = py; t.om.ox0 = px;
         t.e.scale = scale; t.e.out = dx; t.e.act = 0; t.e.out_fp32 = out_fp32; t.e.ld = g->Cin; t.e.ncols = g->Cin;
-        if (int rc = run_conv_tma(dy, g->N, Ho, Wo, g->Cout_ld, w_dgrad, g->Cin, g->kh * g->kw * g->Cout_ld, t, 0,
+        if (int rc = run_conv_tma(dy, g->N, Ho, Wo, g->Cout_ld, w_dgrad, g->Cin, g->kh * g->kw * g->Cout_ld, t, 0, 0,
                                   (cudaStream_t)stream))
           return rc;
       }
@@ -588,12 +589,12 @@ extern "C" int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx,
     // dX = conv(dY, W) with filter offsets flipped: traversal over dY [N, Ho, Wo, Cout_ld], one position per dX pixel
     TmaConvParams t;
     memset(&t, 0, sizeof(t));
-    t.Ho = Hd; t.Wo = Wd; t.M = (long long)g->N * Hd * Wd; t.stride = 1; t.lower = g->pad - (g->kh - 1);
+    t.Ho = Hd; t.Wo = Wd; t.M = (long long)g->N * Hd * Wd; t.stride = 1; t.lower = g->pad - (g->kh - 1); t.lower_w = g->pad - (g->kw - 1);
     t.kh = g->kh; t.kw = g->kw; t.flip = 1; t.cin_blocks = g->Cout_ld / 64; t.num_kb = g->kh * g->kw * t.cin_blocks;
     t.b_sub = 1; t.b_kw = g->kw;
     t.om.linear = 1;
     t.e.scale = scale; t.e.out = dx; t.e.act = 0; t.e.out_fp32 = out_fp32; t.e.ld = g->Cin; t.e.ncols = g->Cin;
-    return run_conv_tma(dy, g->N, Ho, Wo, g->Cout_ld, w_dgrad, g->Cin, g->kh * g->kw * g->Cout_ld, t, -g->pad,
+    return run_conv_tma(dy, g->N, Ho, Wo, g->Cout_ld, w_dgrad, g->Cin, g->kh * g->kw * g->Cout_ld, t, -g->pad, -g->pad,
                         (cudaStream_t)stream);
   }
   p.g.src = (const __nv_bfloat16*)dy;
@@ -613,7 +614,8 @@ static bool wgrad_tma_applicable(const dei2i_conv_geom* g, long long M) {
   if (g_tune_conv_path == 1) return false;
   if (g->pad_mode == DEI2I_PAD_REFLECT && g->pad > 0) return false;
   if (g->Hs != g->H || g->Ws != g->W) return false;
-  if (g->kh != g->kw || g->kh > 16 || g->pad > 64 || g->stride > 8) return false;
+  if (g->kh > 16 || g->kw > 16 || g->pad > 64 || g->stride > 8) return false;
+  if (g->kh != g->kw && g->pad != 0) return false;
   return g->Cin % 64 == 0 && M % 64 == 0 && g->Cout_ld >= 64;
 }
 static void fill_wgrad_tma(const dei2i_conv_geom* g, TmaWgradParams& t) {
@@ -621,7 +623,7 @@ static void fill_wgrad_tma(const dei2i_conv_geom* g, TmaWgradParams& t) {
   t.Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad);
   t.Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
   t.M = (long long)g->N * t.Ho * t.Wo;
-  t.stride = g->stride; t.lower = -g->pad; t.kw = g->kw; t.cin_blocks = g->Cin / 64;
+  t.stride = g->stride; t.lower = -g->pad; t.lower_w = -g->pad; t.kw = g->kw; t.cin_blocks = g->Cin / 64;
   t.num_boxes = g->kh * g->kw * t.cin_blocks;
   t.cout = g->Cout; t.Kf = g->kh * g->kw * g->Cin;
   wgrad_tma_plan(t);
@@ -714,7 +716,7 @@ extern "C" int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int 
     fill_wgrad_tma(g, t);
     t.partial = partial;
     splits = t.splits;
-    if (int rc = run_wgrad_tma(x, g->N, g->H, g->W, g->Cin, dy, g->Cout_ld, t, g->pad - (g->kh - 1), st)) return rc;
+    if (int rc = run_wgrad_tma(x, g->N, g->H, g->W, g->Cin, dy, g->Cout_ld, t, g->pad - (g->kh - 1), g->pad - (g->kw - 1), st)) return rc;
   } else if (g_tune_conv_path != 1 && wgrad_c8_applicable(p.g, g->Cout_ld)) {
     splits = wgrad_c8_splits(p.g, g->Cout_ld);
     if (int rc = run_wgrad_c8(p.g, dy, g->Cout, g->Cout_ld, Kf, partial, st)) return rc;

@@ -90,7 +90,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           const int rem = (int)(m0 - (long long)img[ms] * HoWo);
           const int pr = rem / p.Wo;
           const int qc = rem - pr * p.Wo;
-          cw[ms] = qc * p.stride + p.lower;
+          cw[ms] = qc * p.stride + p.lower_w;
           ch[ms] = pr * p.stride + p.lower;
         }
         int tap = 0, cb = 0, r = 0, s = 0;
@@ -327,13 +327,13 @@ static int launch_tma(const CUtensorMap& ta, const CUtensorMap& tb, const TmaCon
 extern int g_tune_tma_dbg;
 extern int g_tune_tma_ms;  // 0 = auto, 1 / 2 = force the number of 128-pixel sub-tiles per work tile
 int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, int rows, int K, const TmaConvParams& p_in,
-                 int upper, cudaStream_t st) {
+                 int upper, int upper_w, cudaStream_t st) {
   TmaConvParams p = p_in;
   p.dbg = g_tune_tma_dbg;
   int bn = 256;
   while (bn > 64 && bn / 2 >= rows) bn /= 2;
   CUtensorMap ta, tb;
-  if (int rc = encode_tmap_im2col_bf16(&ta, x, (uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N, p.lower, upper, (uint32_t)p.stride,
+  if (int rc = encode_tmap_im2col_bf16(&ta, x, (uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N, p.lower_w, upper_w, p.lower, upper, (uint32_t)p.stride,
                                        64, 128))
     return rc;
   if (int rc = encode_tmap_2d_bf16(&tb, wmat, (uint64_t)K, (uint64_t)rows, (uint64_t)K * 2, 64, (uint32_t)bn, 1)) return rc;
@@ -444,7 +444,7 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_const
         const int rem = (int)(m0 - (long long)img * HoWo);
         const int pr = rem / p.Wo;
         const int qc = rem - pr * p.Wo;
-        const int cw = qc * p.stride + p.lower, ch = pr * p.stride + p.lower;
+        const int cw = qc * p.stride + p.lower_w, ch = pr * p.stride + p.lower;
         for (int g = 0; g < nb; ++g)
           tma_load_im2col_4d(b_dst + g * 8192, &tmap_x, &full_bar[stage], b_cb[g] * 64, cw, ch, img, (uint16_t)b_s[g], (uint16_t)b_r[g]);
       }
@@ -541,10 +541,10 @@ void wgrad_tma_plan(TmaWgradParams& p) {
 }
 
 int run_wgrad_tma(const void* x, int N, int H, int W, int C, const void* dy, int cout_ld, TmaWgradParams& p, int upper,
-                  cudaStream_t st) {
+                  int upper_w, cudaStream_t st) {
   CUtensorMap tdy, tx;
   if (int rc = encode_tmap_2d_bf16(&tdy, dy, (uint64_t)cout_ld, (uint64_t)p.M, (uint64_t)cout_ld * 2, 64, 64, 1)) return rc;
-  if (int rc = encode_tmap_im2col_bf16(&tx, x, (uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N, p.lower, upper, (uint32_t)p.stride, 64, 64))
+  if (int rc = encode_tmap_im2col_bf16(&tx, x, (uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N, p.lower_w, upper_w, p.lower, upper, (uint32_t)p.stride, 64, 64))
     return rc;
   if (p.cout > 128) return launch_wgrad_tma<2, 3>(tdy, tx, p, st);
   return launch_wgrad_tma<1, 4>(tdy, tx, p, st);

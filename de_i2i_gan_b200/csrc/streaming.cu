@@ -195,6 +195,64 @@ __global__ void nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float
   dst[i] = __bfloat162float(src[((long long)n * HW + p) * C_ld + c]);
 }
 
+// ------------------------------------------------------------------------------------------ row-packed image (stem convolution)
+// A kh x kw convolution over a <= 8-channel image has K = kh*kw*8: far too few channels per filter tap for the TMA / tcgen05
+// pipeline.  Packing the kw (<= 8) horizontally adjacent pixels of every position into one 64-channel pixel,
+//     xp[n, hp, w, s*8 + c] = img[n, c, refl(hp - pad), refl(w + s - pad)]      (s < kw, c < C; zero elsewhere)
+// turns it into a kh x 1 'valid' convolution with 64 input channels over xp [N, H + 2 pad, W, 64] - the dense TMA-im2col path.
+DEVINL int reflect_idx(int i, int n) { return i < 0 ? -i : (i >= n ? 2 * n - 2 - i : i); }
+
+__global__ void rowpack_fwd_kernel(const float* __restrict__ img, uint4* __restrict__ xp, int N, int C, int H, int W, int kw, int pad) {
+  const int Hp = H + 2 * pad;
+  const long long total = (long long)N * Hp * W * 8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int s = (int)(i & 7);
+    long long t = i >> 3;
+    const int w = (int)(t % W);
+    t /= W;
+    const int hp = (int)(t % Hp);
+    const int n = (int)(t / Hp);
+    float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    if (s < kw) {
+      const int h = reflect_idx(hp - pad, H), ws = reflect_idx(w + s - pad, W);
+      for (int c = 0; c < C; ++c) f[c] = __ldg(img + (((long long)n * C + c) * H + h) * W + ws);
+    }
+    xp[i] = pack8(f);
+  }
+}
+
+// backward of the packing: dimg[n,c,h,w] = sum over the padded positions (hp, wp) that mirror onto (h, w) and the slots s with
+// 0 <= wp - s < W of dxp[n, hp, wp - s, s*8 + c].  One thread per image pixel (all channels).
+__global__ void rowpack_bwd_kernel(const uint4* __restrict__ dxp, float* __restrict__ dimg, int N, int C, int H, int W, int kw, int pad) {
+  const int Hp = H + 2 * pad;
+  const long long total = (long long)N * H * W;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int w = (int)(i % W);
+    const long long t = i / W;
+    const int h = (int)(t % H);
+    const int n = (int)(t / H);
+    int hs[3], wsrc[3], nh = 0, nw = 0;
+    hs[nh++] = h + pad;
+    if (h >= 1 && h <= pad) hs[nh++] = pad - h;
+    if (h <= H - 2 && h >= H - 1 - pad) hs[nh++] = 2 * H - 2 - h + pad;
+    wsrc[nw++] = w + pad;
+    if (w >= 1 && w <= pad) wsrc[nw++] = pad - w;
+    if (w <= W - 2 && w >= W - 1 - pad) wsrc[nw++] = 2 * W - 2 - w + pad;
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int a = 0; a < nh; ++a)
+      for (int b = 0; b < nw; ++b)
+        for (int s = 0; s < kw; ++s) {
+          const int wq = wsrc[b] - s;
+          if (wq < 0 || wq >= W) continue;
+          float f[8];
+          unpack8(__ldg(dxp + (((long long)n * Hp + hs[a]) * W + wq) * 8 + s), f);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] += f[k];
+        }
+    for (int c = 0; c < C; ++c) dimg[(((long long)n * C + c) * H + h) * W + w] = acc[c];
+  }
+}
+
 // ------------------------------------------------------------------------------------------ channel statistics
 // grid (chunks, groups). block 256 threads = (C8 columns) x (256/C8 pixel lanes), needs C8 <= 256.
 __global__ void channel_stats_kernel(const uint4* __restrict__ x, long long pix_per_group, int C8, int chunk,
@@ -1016,6 +1074,18 @@ extern "C" int dei2i_nhwc_to_nchw(const void* src, float* dst, int N, int C, int
   DEI2I_REQUIRE(src && dst && C_ld >= C, "nhwc_to_nchw: bad arguments");
   nhwc_to_nchw_kernel<<<nblocks((long long)N * C * H * W, 256), 256, 0, ST>>>((const __nv_bfloat16*)src, dst, N, C, H * W, C_ld);
   return LAUNCH_OK("nhwc_to_nchw_kernel");
+}
+
+extern "C" int dei2i_rowpack_fwd(const float* img, void* xp, int N, int C, int H, int W, int kw, int pad, dei2i_stream stream) {
+  DEI2I_REQUIRE(img && xp && C >= 1 && C <= 8 && kw >= 1 && kw <= 8 && pad >= 0 && pad < H && pad < W, "rowpack_fwd: bad arguments");
+  unsigned blocks = nblocks((long long)N * (H + 2 * pad) * W * 8, 256 * 4);
+  rowpack_fwd_kernel<<<blocks, 256, 0, ST>>>(img, (uint4*)xp, N, C, H, W, kw, pad);
+  return LAUNCH_OK("rowpack_fwd_kernel");
+}
+extern "C" int dei2i_rowpack_bwd(const void* dxp, float* dimg, int N, int C, int H, int W, int kw, int pad, dei2i_stream stream) {
+  DEI2I_REQUIRE(dxp && dimg && C >= 1 && C <= 8 && kw >= 1 && kw <= 8 && pad >= 0 && pad < H && pad < W, "rowpack_bwd: bad arguments");
+  rowpack_bwd_kernel<<<nblocks((long long)N * H * W, 256), 256, 0, ST>>>((const uint4*)dxp, dimg, N, C, H, W, kw, pad);
+  return LAUNCH_OK("rowpack_bwd_kernel");
 }
 
 extern "C" int dei2i_channel_stats(const void* x, int N, int HW, int C, int per_sample, float* stats, dei2i_stream stream) {

@@ -175,6 +175,76 @@ def conv(x: Nhwc, conv_mod, spec: ConvSpec, training: bool, bias=None, act=None,
     return Nhwc(y, spec.cout)
 
 
+def rowpack_applicable(spec: ConvSpec) -> bool:
+    """Few-channel wide-filter stride-1 'same' reflect convolutions (the generator stem 3->64 7x7)."""
+    return (spec.cin <= 8 and 1 < spec.kw_ <= 8 and spec.stride == 1 and spec.pad_mode == "reflect"
+            and 2 * spec.pad == spec.kh - 1 and spec.kh == spec.kw_ and spec.cout_ld >= 64)
+
+
+def _rowpack_weight(w: torch.Tensor, spec: ConvSpec, spec2: ConvSpec):
+    """[Cout,C,kh,kw] -> [Cout,64,kh,1] with input channel s*8+c = (filter column s, image channel c); packed GEMM operands."""
+    key = ("rowpack", w.data_ptr(), tuple(w.shape))
+    if _cache is not None and key in _cache:
+        return _cache[key]
+    w2 = torch.zeros(spec.cout, 8, 8, spec.kh, dtype=torch.float32, device=w.device)
+    w2[:, : spec.kw_, : spec.cin] = w.detach().permute(0, 3, 1, 2)
+    packed = ops.pack_weight(w2.reshape(spec.cout, 64, spec.kh, 1), spec2, None, True)
+    if _cache is not None:
+        _cache[key] = packed
+    return packed
+
+
+class _RowpackConv(Function):
+    """scale * conv(x, W) for a fp32 NCHW image x through the row-packed layout (dei2i_rowpack_fwd): the kh x kw convolution
+    over C <= 8 channels runs as a kh x 1 convolution over 64 channels on the TMA / tcgen05 kernels."""
+
+    @staticmethod
+    def forward(ctx, x, w_param, wts_sn, scale, spec: ConvSpec):
+        spec2 = ConvSpec(64, spec.cout, spec.kh, 1, 0, "zeros", 1)
+        w_fwd, w_dg = _rowpack_weight(w_param, spec, spec2)
+        xp = ops.rowpack_fwd(x.contiguous().float(), spec.kw_, spec.pad)
+        y = ops.conv2d_fwd(xp, w_fwd, spec2, scale=scale)
+        ctx.spec, ctx.spec2, ctx.w_dg, ctx.scale, ctx.sn = spec, spec2, w_dg, scale, wts_sn
+        ctx.save_for_backward(xp)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (xp,) = ctx.saved_tensors
+        spec, spec2 = ctx.spec, ctx.spec2
+        dy = dy.contiguous()
+        dx = dw = None
+        if ctx.needs_input_grad[0]:
+            dxp = ops.conv2d_dgrad(dy, ctx.w_dg, spec2, (xp.shape[1], xp.shape[2]), scale=ctx.scale)
+            dx = ops.rowpack_bwd(dxp, spec.cin, spec.kw_, spec.pad)
+        if ctx.needs_input_grad[1]:
+            dw2 = torch.empty(spec.cout, 64, spec.kh, 1, dtype=torch.float32, device=dy.device)
+            ops.conv2d_wgrad(xp, dy, dw2, spec2)
+            g = dw2.view(spec.cout, 8, 8, spec.kh)[:, : spec.kw_, : spec.cin].permute(0, 2, 3, 1)  # [Cout,C,kh,kw]: d/d(W/sigma)
+            if ctx.sn is not None:
+                # spectral_norm backward (u, v constants): dW_orig = (G - <G, W/sigma> u v^T) / sigma
+                w0, u, v, inv = ctx.sn
+                dot = (g * w0).sum() * inv[0]
+                dw = (g - dot * torch.outer(u, v).view_as(w0)) * inv[0]
+            else:
+                dw = g.contiguous()
+        return dx, dw, None, None, None
+
+
+def rowpack_conv(x: torch.Tensor, conv_mod, spec: ConvSpec, training: bool) -> Nhwc:
+    """Stem convolution on a plain fp32 NCHW image (bias-free).  Spectral norm as in prepare_conv."""
+    sn = scale = None
+    if hasattr(conv_mod, "weight_orig"):
+        w = conv_mod.weight_orig
+        with torch.no_grad():
+            inv = ops.spectral_norm(w.detach(), conv_mod.weight_u, conv_mod.weight_v, training)
+            sn = (w.detach(), conv_mod.weight_u.clone(), conv_mod.weight_v.clone(), inv)
+        scale = inv
+    else:
+        w = conv_mod.weight
+    return Nhwc(_RowpackConv.apply(x, w, sn, scale, spec), spec.cout)
+
+
 class _ConvCat(Function):
     """Two convolutions sharing their input fused into one GEMM with N = Cout_a + Cout_b (SPADE gamma|beta,
     normalization.py:31-32; generator heads, generator.py:268-269).  Parameters stay separate tensors."""

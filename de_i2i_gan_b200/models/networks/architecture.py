@@ -9,6 +9,7 @@ Every block accepts either a plain NCHW tensor (drop-in use: converted at the bl
 FP32) or an ``Nhwc`` carrier (how the networks chain blocks without layout round trips).
 """
 import logging
+import os
 
 import torch
 from torch import nn
@@ -18,6 +19,7 @@ from ... import functional as Fn
 from ...ops import ConvSpec
 from .normalization import SPADE
 
+ROWPACK_STEM = os.environ.get("DEI2I_ROWPACK_STEM", "1") != "0"
 _ACT_NAMES = {nn.LeakyReLU: "leaky_relu", nn.ReLU: "relu", nn.Sigmoid: "sigmoid", nn.Tanh: "tanh", nn.Identity: None}
 
 
@@ -135,10 +137,17 @@ class ConvBlock(nn.Module):
     def _norm(self):  # not an attribute: registering the sub-module twice would duplicate its state-dict keys
         return self.conv_block[1] if self._has_norm else None
 
-    def forward(self, x, seg=None, residual=None):
+    def forward(self, x, seg=None, residual=None, carrier_out=False):
         plain = not isinstance(x, Fn.Nhwc)
-        xa = Fn.to_nhwc(x)
         conv = self.conv_block[0]
+        if plain and ROWPACK_STEM and self._norm is not None and conv.bias is None and Fn.rowpack_applicable(self._spec):
+            # generator stem (3->64, 7x7 reflect): row-packed image -> 7x1 convolution over 64 channels on the TMA kernels
+            y = Fn.rowpack_conv(x, conv, self._spec, conv.training)
+            y = Fn.batch_norm(y, self._norm, act=self._act, residual=residual)
+            return y if carrier_out else _edge(y)
+        xa = Fn.to_nhwc(x)
+        if carrier_out:
+            plain = False
         if self._norm is None:
             assert residual is None
             y = Fn.conv(xa, conv, self._spec, conv.training, bias=conv.bias, act=self._act,

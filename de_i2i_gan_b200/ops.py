@@ -253,6 +253,25 @@ def nhwc_to_nchw(x: torch.Tensor, c: int):
     return y
 
 
+def rowpack_fwd(img: torch.Tensor, kw: int, pad: int):
+    """fp32 NCHW [N,C<=8,H,W] -> bf16 [N,H+2*pad,W,64]: kw horizontally adjacent (reflect-padded) pixels per position."""
+    _chk_f32(img, "img")
+    n, c, h, w = img.shape
+    xp = torch.empty(n, h + 2 * pad, w, 64, dtype=torch.bfloat16, device=img.device)
+    check(_lib.load().dei2i_rowpack_fwd(_p(img), _p(xp), n, c, h, w, kw, pad, _stream()), "dei2i_rowpack_fwd")
+    return xp
+
+
+def rowpack_bwd(dxp: torch.Tensor, c: int, kw: int, pad: int):
+    """adjoint of rowpack_fwd: bf16 [N,H+2*pad,W,64] -> fp32 NCHW [N,c,H,W]."""
+    _chk_act(dxp, "dxp")
+    n, hp, w, _ = dxp.shape
+    h = hp - 2 * pad
+    dimg = torch.empty(n, c, h, w, dtype=torch.float32, device=dxp.device)
+    check(_lib.load().dei2i_rowpack_bwd(_p(dxp), _p(dimg), n, c, h, w, kw, pad, _stream()), "dei2i_rowpack_bwd")
+    return dimg
+
+
 def channel_stats(x, per_sample: bool):
     _chk_act(x, "x")
     n, h, w, c = x.shape

@@ -104,6 +104,13 @@ int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int Cin_real, f
 int dei2i_spectral_norm(const float* w, float* u, float* v, int rows, int cols, int do_power_iter, float eps,
                         float* inv_sigma, float* scratch, dei2i_stream stream);
 
+/* Row-packed image for few-channel, wide-filter convolutions (the generator stem: ConvBlock 3->64, 7x7, 'same' reflect
+ * padding, generator.py:76-86 / architecture.py:95-100).  img: fp32 NCHW [N,C<=8,H,W] -> xp: bf16 [N, H+2*pad, W, 64] with
+ * xp[n,hp,w,s*8+c] = img[n,c,refl(hp-pad),refl(w+s-pad)] (s < kw <= 8): the convolution becomes a kh x 1 'valid'
+ * convolution with 64 input channels (weights re-laid accordingly by the caller).  _bwd is the adjoint (gradient w.r.t. img). */
+int dei2i_rowpack_fwd(const float* img, void* xp, int N, int C, int H, int W, int kw, int pad, dei2i_stream stream);
+int dei2i_rowpack_bwd(const void* dxp, float* dimg, int N, int C, int H, int W, int kw, int pad, dei2i_stream stream);
+
 /* NCHW fp32 <-> NHWC bf16 (channel pitch C_ld >= C, pad channels zero) at the model edge. */
 int dei2i_nchw_to_nhwc(const float* src, void* dst, int N, int C, int H, int W, int C_ld, dei2i_stream stream);
 int dei2i_nhwc_to_nchw(const void* src, float* dst, int N, int C, int H, int W, int C_ld, dei2i_stream stream);

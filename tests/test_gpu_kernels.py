@@ -338,6 +338,59 @@ def test_spade_fwd_bwd(up):
     assert e_out < TOL_BF16 and max(e) < 2e-2, (e_out, e)
 
 
+@pytest.mark.parametrize("use_sn,n,h,w", [(True, 2, 24, 32), (False, 3, 16, 16)])
+def test_rowpack_stem_conv(use_sn, n, h, w):
+    """Generator stem (3->64, 7x7, 'same' reflect, spectral norm) through the row-packed 7x1 TMA convolution vs nn.Conv2d."""
+    import copy
+    from de_i2i_gan_b200 import functional as Fn, ops
+    torch.manual_seed(3)
+    conv = torch.nn.Conv2d(3, 64, 7, padding="same", padding_mode="reflect", bias=False)
+    with torch.no_grad():
+        conv.weight.copy_(q(conv.weight))
+    if use_sn:
+        conv = torch.nn.utils.spectral_norm(conv)
+    dev = copy.deepcopy(conv).cuda()
+    g = torch.Generator().manual_seed(4)
+    x = q(torch.randn(n, 3, h, w, generator=g)).requires_grad_(True)
+    y_ref = conv(x)
+    dy = q(torch.randn(y_ref.shape, generator=g))
+    wref = conv.weight_orig if use_sn else conv.weight
+    dx_ref, dw_ref = torch.autograd.grad(y_ref, (x, wref), dy)
+    spec = ops.ConvSpec(3, 64, 7, 1, 3, "reflect")
+    assert Fn.rowpack_applicable(spec)
+    xd = x.detach().cuda().requires_grad_(True)
+    y = Fn.rowpack_conv(xd, dev, spec, True)
+    wdev = dev.weight_orig if use_sn else dev.weight
+    dxd, dwd = torch.autograd.grad(y.t, (xd, wdev), to_dev(dy))
+    torch.cuda.synchronize()
+    e = (rel_err(from_dev(y.t, 64), y_ref), rel_err(dxd, dx_ref), rel_err(dwd, dw_ref))
+    _report(f"rowpack_stem/sn{int(use_sn)}", y=e[0], dx=e[1], dw=e[2])
+    assert e[0] < TOL_BF16 and e[1] < TOL_BF16 and e[2] < TOL_BF16, e
+    if use_sn:
+        assert rel_err(dev.weight_u, conv.weight_u) < 1e-4 and rel_err(dev.weight_v, conv.weight_v) < 1e-4
+
+
+def test_rowpack_roundtrip_adjoint():
+    """rowpack_bwd is the adjoint of rowpack_fwd: <P x, z> == <x, P^T z>."""
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(8)
+    x = q(torch.randn(2, 3, 9, 11, generator=g))
+    xp = ops.rowpack_fwd(x.cuda(), 7, 3).float()
+    ref = F.pad(x, (3, 3, 3, 3), mode="reflect")
+    for s_ in range(7):
+        got = xp[:, :, :, s_ * 8: s_ * 8 + 3].permute(0, 3, 1, 2).cpu()
+        assert torch.equal(got, ref[:, :, :, s_: s_ + 11])
+    assert xp[..., 56:].abs().max().item() == 0 and xp[..., 3:8].abs().max().item() == 0
+    z = q(torch.randn(xp.shape, generator=g))
+    pt = ops.rowpack_bwd(z.to(torch.bfloat16).cuda().contiguous(), 3, 7, 3)
+    zz = z.clone()
+    zz[..., 56:] = 0
+    zz.view(2, 15, 11, 8, 8)[..., 3:] = 0
+    lhs = (xp.cpu() * zz).sum().item()
+    rhs = (x * pt.cpu()).sum().item()
+    assert abs(lhs - rhs) < 1e-2 * max(1.0, abs(lhs)), (lhs, rhs)
+
+
 def _cls_index(n):
     return torch.tensor([i if i < 2 else (i - n + 5 if i >= n - 2 else 2) for i in range(n)])
 

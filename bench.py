@@ -167,6 +167,20 @@ def run_reference(args):
     }))
 
 
+def _finish(world):
+    """Multi-rank exit: every rank meets at a last barrier, flushes and leaves without the NCCL / CUDA-graph teardown
+    (a rank that returns early while another sits in destroy_process_group() hangs the launcher)."""
+    if world <= 1:
+        return
+    import torch
+    import torch.distributed as dist
+    torch.cuda.synchronize()
+    dist.barrier()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)
+
+
 # ---------------------------------------------------------------------------------------------------- our arm
 def run_ours(args):
     import torch
@@ -292,6 +306,7 @@ def run_ours(args):
                     "measured_in": "eager re-run of the same K steps directly after the timed region (identical kernels; a replayed CUDA graph cannot be bracketed per kernel)",
                     "eager_ms_per_step": ms_eager / args.steps, "detail": detail}
     if rank != 0:
+        _finish(world)
         return
     cpu = None
     if not args.no_cpu_baseline and world == 1:
@@ -317,8 +332,7 @@ def run_ours(args):
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
     }))
-    if world > 1:
-        dist.destroy_process_group()
+    _finish(world)
 
 
 def main():

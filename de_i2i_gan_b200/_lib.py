@@ -36,6 +36,14 @@ SIGNATURES = {
     "dei2i_conv2d_wgrad": (_I, [_P, _P, _P, _I, _F, C.POINTER(ConvGeom), _P, _P, _P, _P, _P, _SZ, _P]),
     "dei2i_spectral_norm": (_I, [_P, _P, _P, _I, _I, _I, _F, _P, _P, _P]),
     "dei2i_nchw_to_nhwc": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_upsample_pad_fwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P]),
+    "dei2i_upsample_pad_bwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P]),
+    "dei2i_maxpool_fwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P]),
+    "dei2i_maxpool_bwd": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P]),
+    "dei2i_avgpool_fwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _F, _P]),
+    "dei2i_avgpool_bwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _F, _P]),
+    "dei2i_gap_fwd": (_I, [_P, _P, _I, _I, _I, _P]),
+    "dei2i_gap_bwd": (_I, [_P, _P, _I, _I, _I, _P]),
     "dei2i_rowpack_fwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),
     "dei2i_rowpack_bwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),
     "dei2i_nhwc_to_nchw": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),

@@ -245,6 +245,19 @@ def rowpack_conv(x: torch.Tensor, conv_mod, spec: ConvSpec, training: bool) -> N
     return Nhwc(_RowpackConv.apply(x, w, sn, scale, spec), spec.cout)
 
 
+def linear(x: torch.Tensor, lin: torch.nn.Linear, act=None) -> torch.Tensor:
+    """nn.Linear on fp32 [N, Cin] as a 1x1 convolution over a [N,1,1,Cin] map (same GEMM kernels, FP32 logits out)."""
+    cout, cin = lin.weight.shape
+    spec = ConvSpec(cin, cout, 1)
+    w4 = lin.weight.view(cout, cin, 1, 1)
+    wts = Weights(*_pack(w4, spec), None, None)
+    xb = x.to(torch.bfloat16)
+    if spec.cin_ld != cin:
+        xb = torch.nn.functional.pad(xb, (0, spec.cin_ld - cin))
+    y = _Conv.apply(xb.reshape(x.shape[0], 1, 1, spec.cin_ld).contiguous(), w4, lin.bias, None, None, wts, spec, act, None, True, None)
+    return y[:, 0, 0, :cout]
+
+
 class _ConvCat(Function):
     """Two convolutions sharing their input fused into one GEMM with N = Cout_a + Cout_b (SPADE gamma|beta,
     normalization.py:31-32; generator heads, generator.py:268-269).  Parameters stay separate tensors."""
@@ -359,6 +372,74 @@ class _SpadeCls(Function):
 
 def spade_modulate_cls(x: Nhwc, gb5: Nhwc, up=1, relu=True, eps=1e-5) -> Nhwc:
     return Nhwc(_SpadeCls.apply(x.t, gb5.t, up, relu, eps), x.c)
+
+
+class _UpsamplePad(Function):
+    @staticmethod
+    def forward(ctx, x, up, pad):
+        ctx.up, ctx.pad, ctx.hw = up, pad, (x.shape[1], x.shape[2])
+        return ops.upsample_pad(x, up, pad)
+
+    @staticmethod
+    def backward(ctx, dout):
+        return ops.upsample_pad_bwd(dout.contiguous(), ctx.hw, ctx.up, ctx.pad), None, None
+
+
+def upsample_pad(x: Nhwc, up=1, pad=(0, 0, 0, 0)) -> Nhwc:
+    """nn.Upsample(scale_factor=up) followed by a zero frame (top, left, bottom, right)."""
+    return Nhwc(_UpsamplePad.apply(x.t, up, tuple(pad)), x.c)
+
+
+class _MaxPool(Function):
+    @staticmethod
+    def forward(ctx, x, k, stride, pad):
+        out, idx = ops.maxpool_fwd(x, k, stride, pad)
+        ctx.cfg, ctx.hw = (k, stride, pad), (x.shape[1], x.shape[2])
+        ctx.save_for_backward(idx)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        (idx,) = ctx.saved_tensors
+        return ops.maxpool_bwd(dout.contiguous(), idx, ctx.hw, *ctx.cfg), None, None, None
+
+
+def max_pool(x: Nhwc, k, stride, pad) -> Nhwc:
+    return Nhwc(_MaxPool.apply(x.t, k, stride, pad), x.c)
+
+
+class _AvgPool(Function):
+    @staticmethod
+    def forward(ctx, x, k, scale):
+        ctx.k, ctx.scale = k, scale
+        return ops.avgpool_fwd(x, k, scale)
+
+    @staticmethod
+    def backward(ctx, dout):
+        return ops.avgpool_bwd(dout.contiguous(), ctx.k, ctx.scale), None, None
+
+
+def avg_pool(x: Nhwc, k, scale=1.0) -> Nhwc:
+    return Nhwc(_AvgPool.apply(x.t, k, scale), x.c)
+
+
+class _Gap(Function):
+    @staticmethod
+    def forward(ctx, x, c):
+        ctx.hw, ctx.c_ld = (x.shape[1], x.shape[2]), x.shape[3]
+        return ops.gap_fwd(x)[:, :c]
+
+    @staticmethod
+    def backward(ctx, dout):
+        g = dout.contiguous().float()
+        if g.shape[1] != ctx.c_ld:
+            g = torch.nn.functional.pad(g, (0, ctx.c_ld - g.shape[1]))
+        return ops.gap_bwd(g, ctx.hw), None
+
+
+def global_avg_pool(x: Nhwc) -> torch.Tensor:
+    """nn.AdaptiveAvgPool2d(1) + flatten: fp32 [N, C]."""
+    return _Gap.apply(x.t, x.c)
 
 
 class _Compose(Function):

@@ -50,8 +50,13 @@ def _spec_of(conv: nn.Conv2d) -> ConvSpec:
     if isinstance(pad, str):
         if pad == "same":
             if kh % 2 == 0 or kw % 2 == 0:
-                raise NotImplementedError("asymmetric 'same' padding of even kernels (WGAN generator) is not on this path yet")
-            pad = (kh - 1) // 2
+                # asymmetric 'same' padding of even kernels (WGanGenerator): the zero frame is materialised by
+                # Fn.upsample_pad (see same_frame), the convolution itself is 'valid'
+                if conv.padding_mode != "zeros" or kh != kw:
+                    raise NotImplementedError("'same' padding of even kernels: square filters with zero padding only")
+                pad = 0
+            else:
+                pad = (kh - 1) // 2
         else:
             pad = 0
     else:
@@ -61,6 +66,17 @@ def _spec_of(conv: nn.Conv2d) -> ConvSpec:
     if conv.groups != 1 or _first(conv.dilation) != 1:
         raise NotImplementedError("grouped / dilated convolutions")
     return ConvSpec(conv.in_channels, conv.out_channels, kh, _first(conv.stride), pad, conv.padding_mode, kw if kw != kh else 0)
+
+
+def same_frame(conv: nn.Conv2d):
+    """(top, left, bottom, right) zero frame of nn.Conv2d(padding='same') for even kernels - torch pads total = k - 1,
+    total // 2 before and the remainder after - else None (symmetric padding is part of the ConvSpec)."""
+    kh, kw = conv.kernel_size
+    if conv.padding == "same" and kh % 2 == 0:
+        total = kh - 1
+        lo, hi = total // 2, total - total // 2
+        return (lo, lo, hi, hi)
+    return None
 
 
 # ---------------------------------------------------------------------------------------------- noise
@@ -188,18 +204,41 @@ class DeConvBlock(nn.Module):
         self._act = act_layer
         self._conv_idx = next(i for i, m in enumerate(self.de_conv_block) if isinstance(m, nn.Conv2d))
         self._simple = not (up_scale or add_noise or norm_layer is not None)
-        self._spec = _spec_of(self._conv) if self._simple else None
+        self._spec = _spec_of(self._conv)
+        self._frame = same_frame(self._conv)
+        self._up = 2 if up_scale else 1
+        self._noise_idx = self._conv_idx + 1 if add_noise else None
+        self._norm_idx = (self._conv_idx + 1 + int(add_noise)) if norm_layer is not None else None
+        if norm_layer is not None and not isinstance(self.de_conv_block[self._norm_idx], nn.BatchNorm2d):
+            raise NotImplementedError("DeConvBlock on the CUDA path supports norm_layer in (None, nn.BatchNorm2d)")
 
     @property
     def _conv(self):
         return self.de_conv_block[self._conv_idx]
 
     def forward(self, x, seg=None):
-        if not self._simple:
-            raise NotImplementedError("DeConvBlock with up-sampling / noise / norm (WGAN generator) is not on the CUDA path yet")
         plain = not isinstance(x, Fn.Nhwc)
-        y = Fn.conv(Fn.to_nhwc(x), self._conv, self._spec, self._conv.training, bias=self._conv.bias, act=self._act,
-                    out_fp32=True)
+        xa = Fn.to_nhwc(x)
+        conv = self._conv
+        if self._simple and self._frame is None:  # DefectGAN heads
+            y = Fn.conv(xa, conv, self._spec, conv.training, bias=conv.bias, act=self._act, out_fp32=True)
+            return _edge(y) if plain else y
+        # WGanGenerator blocks (generator.py:18-30): nearest 2x up-sampling and the 'same' zero frame in one pass, 'valid'
+        # convolution with the noise fused into its epilogue, BatchNorm + activation in one pass
+        if self._up > 1 or self._frame is not None:
+            xa = Fn.upsample_pad(xa, self._up, self._frame or (0, 0, 0, 0))
+        n, _, h, w = xa.shape
+        ho, wo = self._spec.out_hw(h, w)
+        noise, nw = _noise_args(self.de_conv_block[self._noise_idx] if self._noise_idx is not None else None, n, ho, wo,
+                                xa.t.device)
+        if self._norm_idx is None:
+            fp32 = self._act in ("tanh", "sigmoid")
+            y = Fn.conv(xa, conv, self._spec, conv.training, bias=conv.bias, noise=noise, noise_w=nw, act=self._act, out_fp32=fp32)
+            if fp32 and not plain:
+                y = Fn.Nhwc(y.t.to(torch.bfloat16), y.c)
+        else:
+            y = Fn.conv(xa, conv, self._spec, conv.training, bias=conv.bias, noise=noise, noise_w=nw)
+            y = Fn.batch_norm(y, self.de_conv_block[self._norm_idx], act=self._act)
         return _edge(y) if plain else y
 
 

@@ -8,6 +8,40 @@ from .architecture import ConvBlock
 from .base_network import BaseNetwork
 
 
+class WGanDiscriminator(BaseNetwork):
+    """models/networks/discriminator.py:10-46: 7x7 s2 reflect conv + BN + ReLU, MaxPool 3/2/1, [3x3 s2 conv + BN + ReLU] x
+    num_layers, global average pool, Linear -> logits [B, 1]."""
+
+    def __init__(self, num_layers, ndf=64):
+        super().__init__()
+        dim = ndf
+        stem = [ConvBlock(3, ndf, kernel_size=(7, 7), stride=(2, 2), padding=3, padding_mode="reflect", norm_layer=nn.BatchNorm2d,
+                          act_layer="relu"),
+                nn.MaxPool2d(kernel_size=(3, 3), stride=(2, 2), padding=1)]
+        backbone = []
+        for _ in range(num_layers):
+            backbone += [ConvBlock(dim, dim * 2, kernel_size=(3, 3), stride=(2, 2), padding=1, bias=False, norm_layer=nn.BatchNorm2d,
+                                   act_layer="relu")]
+            dim *= 2
+        backbone += [nn.AdaptiveAvgPool2d(1)]
+        self.feature_extractor = nn.Sequential(*(stem + backbone))
+        self.classifier = nn.Sequential(nn.Linear(dim, 1))
+
+    def forward(self, x):
+        x = x.to(self.device)
+        feat = Fn.to_nhwc(x)
+        pooled = None
+        for m in self.feature_extractor:
+            if isinstance(m, ConvBlock):
+                feat = m(feat)
+            elif isinstance(m, nn.MaxPool2d):
+                k, s_, p_ = (v[0] if isinstance(v, (tuple, list)) else v for v in (m.kernel_size, m.stride, m.padding))
+                feat = Fn.max_pool(feat, k, s_, p_)
+            else:  # AdaptiveAvgPool2d(1) + view(batch, -1)
+                pooled = Fn.global_avg_pool(feat)
+        return Fn.linear(pooled, self.classifier[0])
+
+
 class DefectGanDiscriminator(BaseNetwork):
     def __init__(self, opt):
         super().__init__()

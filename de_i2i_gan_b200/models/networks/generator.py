@@ -4,8 +4,42 @@ from torch import nn
 
 from ... import functional as Fn
 from ...ops import ConvSpec
-from .architecture import ConvBlock, DeConvBlock, NormConvBlock, NormResBlock, ResBlock
+from .architecture import ConvBlock, DeConvBlock, NormConvBlock, NormResBlock, ResBlock, _edge, _spec_of, same_frame
 from .base_network import BaseNetwork
+
+
+class WGanGenerator(BaseNetwork):
+    """models/networks/generator.py:11-49: Upsample, [Upsample + 4x4 'same' conv + BN + ReLU] x (num_layers + 1), Upsample,
+    4x4 'same' conv, tanh.  Same ``noise_to_image`` Sequential (state-dict keys, init order) as the reference."""
+
+    def __init__(self, num_layers, ngf=64, noise_dim=100):
+        super().__init__()
+        self.noise_dim = noise_dim
+        model = [nn.Upsample(scale_factor=2)]
+        dim = ngf * (2 ** num_layers)
+        model += [DeConvBlock(noise_dim, dim, kernel_size=(4, 4), padding="same", norm_layer=nn.BatchNorm2d, act_layer="relu")]
+        for _ in range(num_layers):
+            model += [DeConvBlock(dim, dim // 2, kernel_size=(4, 4), stride=(1, 1), padding="same", norm_layer=nn.BatchNorm2d,
+                                  act_layer="relu")]
+            dim //= 2
+        model += [nn.Upsample(scale_factor=2), nn.Conv2d(dim, 3, kernel_size=(4, 4), stride=(1, 1), padding="same", bias=False),
+                  nn.Tanh()]
+        self.noise_to_image = nn.Sequential(*model)
+        self._out_spec = _spec_of(self.noise_to_image[-2])
+        self._out_frame = same_frame(self.noise_to_image[-2])
+
+    def forward(self, x):
+        assert isinstance(x, (torch.Tensor, int)), "x must be batch_size (Int) or noise (Torch.Tensor)"
+        noise = x if isinstance(x, torch.Tensor) else torch.rand(x, self.noise_dim, 1, 1)  # uniform, generator.py:46
+        noise = noise.to(self.device)
+        mods = list(self.noise_to_image)
+        feat = Fn.upsample_pad(Fn.to_nhwc(noise.float()), 2)
+        for blk in mods[1:-3]:
+            feat = blk(feat)
+        conv = mods[-2]
+        feat = Fn.upsample_pad(feat, 2, self._out_frame or (0, 0, 0, 0))
+        y = Fn.conv(feat, conv, self._out_spec, conv.training, act="tanh", out_fp32=True)
+        return _edge(y)
 
 
 class DefectGanGenerator(BaseNetwork):

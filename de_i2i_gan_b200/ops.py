@@ -272,6 +272,81 @@ def rowpack_bwd(dxp: torch.Tensor, c: int, kw: int, pad: int):
     return dimg
 
 
+def upsample_pad(x, up: int = 1, pad=(0, 0, 0, 0)):
+    """nearest up-sampling by ``up`` + zero frame pad = (top, left, bottom, right): bf16 [N,H,W,C] -> [N,up*H+pt+pb,up*W+pl+pr,C]."""
+    _chk_act(x, "x")
+    n, h, w, c = x.shape
+    pt, pl, pb, pr = pad
+    out = torch.empty(n, h * up + pt + pb, w * up + pl + pr, c, dtype=torch.bfloat16, device=x.device)
+    check(_lib.load().dei2i_upsample_pad_fwd(_p(x), _p(out), n, h, w, c, up, pt, pl, pb, pr, _stream()), "dei2i_upsample_pad_fwd")
+    return out
+
+
+def upsample_pad_bwd(dout, in_hw, up: int = 1, pad=(0, 0, 0, 0)):
+    _chk_act(dout, "dout")
+    n, _, _, c = dout.shape
+    h, w = in_hw
+    pt, pl, pb, pr = pad
+    assert tuple(dout.shape[1:3]) == (h * up + pt + pb, w * up + pl + pr)
+    dx = torch.empty(n, h, w, c, dtype=torch.bfloat16, device=dout.device)
+    check(_lib.load().dei2i_upsample_pad_bwd(_p(dout), _p(dx), n, h, w, c, up, pt, pl, pb, pr, _stream()), "dei2i_upsample_pad_bwd")
+    return dx
+
+
+def maxpool_fwd(x, k: int, stride: int, pad: int):
+    """nn.MaxPool2d(k, stride, pad) -> (out, idx uint8 [N,Ho,Wo,C])."""
+    _chk_act(x, "x")
+    n, h, w, c = x.shape
+    ho, wo = (h + 2 * pad - k) // stride + 1, (w + 2 * pad - k) // stride + 1
+    out = torch.empty(n, ho, wo, c, dtype=torch.bfloat16, device=x.device)
+    idx = torch.empty(n, ho, wo, c, dtype=torch.uint8, device=x.device)
+    check(_lib.load().dei2i_maxpool_fwd(_p(x), _p(out), _p(idx), n, h, w, c, k, stride, pad, _stream()), "dei2i_maxpool_fwd")
+    return out, idx
+
+
+def maxpool_bwd(dout, idx, in_hw, k: int, stride: int, pad: int):
+    _chk_act(dout, "dout")
+    n, _, _, c = dout.shape
+    h, w = in_hw
+    dx = torch.empty(n, h, w, c, dtype=torch.bfloat16, device=dout.device)
+    check(_lib.load().dei2i_maxpool_bwd(_p(dout), _p(idx), _p(dx), n, h, w, c, k, stride, pad, _stream()), "dei2i_maxpool_bwd")
+    return dx
+
+
+def avgpool_fwd(x, k: int, scale: float = 1.0):
+    _chk_act(x, "x")
+    n, h, w, c = x.shape
+    out = torch.empty(n, h // k, w // k, c, dtype=torch.bfloat16, device=x.device)
+    check(_lib.load().dei2i_avgpool_fwd(_p(x), _p(out), n, h, w, c, k, float(scale), _stream()), "dei2i_avgpool_fwd")
+    return out
+
+
+def avgpool_bwd(dout, k: int, scale: float = 1.0):
+    _chk_act(dout, "dout")
+    n, ho, wo, c = dout.shape
+    dx = torch.empty(n, ho * k, wo * k, c, dtype=torch.bfloat16, device=dout.device)
+    check(_lib.load().dei2i_avgpool_bwd(_p(dout), _p(dx), n, ho * k, wo * k, c, k, float(scale), _stream()), "dei2i_avgpool_bwd")
+    return dx
+
+
+def gap_fwd(x):
+    """nn.AdaptiveAvgPool2d(1): bf16 [N,H,W,C] -> fp32 [N,C]."""
+    _chk_act(x, "x")
+    n, h, w, c = x.shape
+    out = torch.empty(n, c, dtype=torch.float32, device=x.device)
+    check(_lib.load().dei2i_gap_fwd(_p(x), _p(out), n, h * w, c, _stream()), "dei2i_gap_fwd")
+    return out
+
+
+def gap_bwd(dout, hw):
+    _chk_f32(dout, "dout")
+    n, c = dout.shape
+    h, w = hw
+    dx = torch.empty(n, h, w, c, dtype=torch.bfloat16, device=dout.device)
+    check(_lib.load().dei2i_gap_bwd(_p(dout), _p(dx), n, h * w, c, _stream()), "dei2i_gap_bwd")
+    return dx
+
+
 def channel_stats(x, per_sample: bool):
     _chk_act(x, "x")
     n, h, w, c = x.shape

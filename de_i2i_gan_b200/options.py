@@ -39,6 +39,26 @@ def train_options(**over) -> SimpleNamespace:
     return opt
 
 
+def wgan_options(**over) -> SimpleNamespace:
+    """options/wgan_options.py:12-57 defaults (model 'wgan', 64x64, batch 128, noise_dim 100, RMSprop lr 5e-5, clipping 0.03)."""
+    opt = SimpleNamespace(
+        name="exp", model="wgan", gpu_ids="0", ckpt_dir=Path("./ckpt"), phase="train", dataset_name="face",
+        batch_size=128, image_size=64, ngf=64, ndf=64, noise_dim=100,
+        init_type="normal", init_variance=0.02, load_model_name=None, which_epoch="latest",
+        num_display_images=64, save_ckpt_freq=10, save_latest_freq=1000,
+        optimizer="rmsprop", lr=5e-5, num_epochs=120, num_iters=500_000, scheduler="step", lr_decay=1.0,
+        num_critics=5, clipping_limit=0.03, continue_training=False, log_dir=None, is_train=True, iters_per_epoch=1000,
+    )
+    for k, v in over.items():
+        if not hasattr(opt, k):
+            raise AttributeError(f"unknown option {k!r}")
+        setattr(opt, k, v)
+    if not hasattr(opt, "device"):
+        import os
+        opt.device = torch.device("cuda", int(os.environ.get("LOCAL_RANK", opt.gpu_ids.split(",")[0])))
+    return opt
+
+
 def readme_recipe(**over) -> SimpleNamespace:
     """defectGAN/README.md:21-24: the documented DefectGAN training recipe adds --add_noise --use_spectral."""
     kw = dict(add_noise=True, use_spectral=True)

@@ -104,6 +104,27 @@ int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int Cin_real, f
 int dei2i_spectral_norm(const float* w, float* u, float* v, int rows, int cols, int do_power_iter, float eps,
                         float* inv_sigma, float* scratch, dei2i_stream stream);
 
+/* ---- WGAN / StarGAN-v2 resampling (bf16 NHWC, C % 8 == 0) ----
+ * nn.Upsample(scale_factor=up, 'nearest') fused with the zero padding of the following nn.Conv2d(padding='same'), which is
+ * asymmetric for even kernels (WGanGenerator, generator.py:15-37: 4x4 'same' -> pad 1 left/top, 2 right/bottom):
+ * out [N, up*H + pt + pb, up*W + pl + pr, C].  _bwd is the adjoint (sums each up x up window of the interior). */
+int dei2i_upsample_pad_fwd(const void* x, void* out, int N, int H, int W, int C, int up, int pad_top, int pad_left,
+                           int pad_bottom, int pad_right, dei2i_stream stream);
+int dei2i_upsample_pad_bwd(const void* dout, void* dx, int N, int H, int W, int C, int up, int pad_top, int pad_left,
+                           int pad_bottom, int pad_right, dei2i_stream stream);
+/* nn.MaxPool2d(k, stride, pad) (WGanDiscriminator, discriminator.py:23-25).  idx: uint8 [N,Ho,Wo,C] window offset of the first
+ * maximum in scan order (the element torch routes the gradient to); _bwd gathers. */
+int dei2i_maxpool_fwd(const void* x, void* out, void* idx, int N, int H, int W, int C, int k, int stride, int pad,
+                      dei2i_stream stream);
+int dei2i_maxpool_bwd(const void* dout, const void* idx, void* dx, int N, int H, int W, int C, int k, int stride, int pad,
+                      dei2i_stream stream);
+/* F.avg_pool2d(x, k) * scale (stargan-v2/core/model.py:53,60; scale folds the residual 1/sqrt(2), model.py:70) and adjoint. */
+int dei2i_avgpool_fwd(const void* x, void* out, int N, int H, int W, int C, int k, float scale, dei2i_stream stream);
+int dei2i_avgpool_bwd(const void* dout, void* dx, int N, int H, int W, int C, int k, float scale, dei2i_stream stream);
+/* nn.AdaptiveAvgPool2d(1) (discriminator.py:35): out fp32 [N,C]; _bwd: dx bf16 [N,HW,C] = dout / HW. */
+int dei2i_gap_fwd(const void* x, float* out, int N, int HW, int C, dei2i_stream stream);
+int dei2i_gap_bwd(const float* dout, void* dx, int N, int HW, int C, dei2i_stream stream);
+
 /* Row-packed image for few-channel, wide-filter convolutions (the generator stem: ConvBlock 3->64, 7x7, 'same' reflect
  * padding, generator.py:76-86 / architecture.py:95-100).  img: fp32 NCHW [N,C<=8,H,W] -> xp: bf16 [N, H+2*pad, W, 64] with
  * xp[n,hp,w,s*8+c] = img[n,c,refl(hp-pad),refl(w+s-pad)] (s < kw <= 8): the convolution becomes a kh x 1 'valid'

@@ -44,6 +44,10 @@ SIGNATURES = {
     "dei2i_avgpool_bwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _F, _P]),
     "dei2i_gap_fwd": (_I, [_P, _P, _I, _I, _I, _P]),
     "dei2i_gap_bwd": (_I, [_P, _P, _I, _I, _I, _P]),
+    "dei2i_adain_act_fwd": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _F, _P]),
+    "dei2i_adain_act_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _P]),
+    "dei2i_act_fwd": (_I, [_P, _P, _LL, _I, _P]),
+    "dei2i_axpby": (_I, [_P, _P, _P, _LL, _F, _F, _P]),
     "dei2i_rowpack_fwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),
     "dei2i_rowpack_bwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),
     "dei2i_nhwc_to_nchw": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),

@@ -762,6 +762,145 @@ __global__ void spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* 
   }
 }
 
+// ------------------------------------------------------------------------------------------ AdaIN / affine instance norm + LeakyReLU
+// out = lrelu_slope( IN(x) * scale[n,c] + shift[n,c] )   (StarGAN-v2: AdaIN scale = 1 + gamma(s), model.py:73-84; affine
+// InstanceNorm2d scale = weight[c], model.py:42-43; the LeakyReLU(0.2) that always follows, model.py:56-63, is fused; slope = 1
+// -> no activation).  grid.y = image.
+__global__ void adain_act_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ out, const float* __restrict__ stats,
+                                     const float* __restrict__ scale, const float* __restrict__ shift, float* __restrict__ mean_rstd,
+                                     int HW, int C8, float slope, float eps) {
+  extern __shared__ float sh[];  // a[C] = rstd * scale, b[C] = shift - mean * rstd * scale
+  const int C = C8 * 8;
+  const int n = blockIdx.y;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float mean = stats[(n * 2 + 0) * C + c] / (float)HW;
+    const float var = fmaxf(stats[(n * 2 + 1) * C + c] / (float)HW - mean * mean, 0.f);
+    const float rstd = rsqrtf(var + eps);
+    const float a = rstd * scale[n * C + c];
+    sh[c] = a;
+    sh[C + c] = shift[n * C + c] - mean * a;
+    if (blockIdx.x == 0) {
+      mean_rstd[(n * 2 + 0) * C + c] = mean;
+      mean_rstd[(n * 2 + 1) * C + c] = rstd;
+    }
+  }
+  __syncthreads();
+  const long long per_img = (long long)HW * C8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img; i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % C8) * 8;
+    float f[8];
+    unpack8(__ldg(x + (long long)n * per_img + i), f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float t = f[k] * sh[c0 + k] + sh[C + c0 + k];
+      f[k] = t > 0.f ? t : t * slope;
+    }
+    out[(long long)n * per_img + i] = pack8(f);
+  }
+}
+// backward pass 1: red[n,0,c] = sum g (= dshift), red[n,1,c] = sum g * xhat (= dscale),  g = dout * lrelu'(out)
+__global__ void adain_act_bwd1_kernel(const uint4* __restrict__ x, const uint4* __restrict__ out, const uint4* __restrict__ dout,
+                                      const float* __restrict__ mean_rstd, float* __restrict__ red, int HW, int C8, int chunk,
+                                      float slope) {
+  extern __shared__ float sh[];
+  const int c8 = threadIdx.x % C8;
+  const int lane = threadIdx.x / C8;
+  const int lanes = blockDim.x / C8;
+  const int C = C8 * 8;
+  const int n = blockIdx.y;
+  const long long p0 = (long long)blockIdx.x * chunk, p1 = min((long long)HW, p0 + chunk);
+  float mu[8], rs[8], s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    mu[k] = mean_rstd[(n * 2 + 0) * C + c8 * 8 + k];
+    rs[k] = mean_rstd[(n * 2 + 1) * C + c8 * 8 + k];
+  }
+  for (long long p = p0 + lane; p < p1; p += lanes) {
+    const long long o = ((long long)n * HW + p) * C8 + c8;
+    float fx[8], fo[8], fd[8];
+    unpack8(__ldg(x + o), fx);
+    unpack8(__ldg(out + o), fo);
+    unpack8(__ldg(dout + o), fd);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float g = fo[k] > 0.f ? fd[k] : fd[k] * slope;
+      s[k] += g;
+      q[k] += g * (fx[k] - mu[k]) * rs[k];
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    sh[(lane * C + c8 * 8 + k) * 2 + 0] = s[k];
+    sh[(lane * C + c8 * 8 + k) * 2 + 1] = q[k];
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float a = 0.f, b = 0.f;
+    for (int l = 0; l < lanes; ++l) {
+      a += sh[(l * C + c) * 2 + 0];
+      b += sh[(l * C + c) * 2 + 1];
+    }
+    atomicAdd(red + (n * 2 + 0) * C + c, a);
+    atomicAdd(red + (n * 2 + 1) * C + c, b);
+  }
+}
+// backward pass 2: dx = rstd * scale * (g - S_g / HW - xhat * S_gx / HW)
+__global__ void adain_act_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ out, const uint4* __restrict__ dout,
+                                      uint4* __restrict__ dx, const float* __restrict__ mean_rstd, const float* __restrict__ red,
+                                      const float* __restrict__ scale, int HW, int C8, float slope) {
+  extern __shared__ float sh[];  // mean, rstd, rstd*scale, S_g/HW, S_gx/HW
+  const int C = C8 * 8;
+  const int n = blockIdx.y;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float rstd = mean_rstd[(n * 2 + 1) * C + c];
+    sh[c] = mean_rstd[(n * 2 + 0) * C + c];
+    sh[C + c] = rstd;
+    sh[2 * C + c] = rstd * scale[n * C + c];
+    sh[3 * C + c] = red[(n * 2 + 0) * C + c] / (float)HW;
+    sh[4 * C + c] = red[(n * 2 + 1) * C + c] / (float)HW;
+  }
+  __syncthreads();
+  const long long per_img = (long long)HW * C8;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img; i += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(i % C8) * 8;
+    const long long o = (long long)n * per_img + i;
+    float fx[8], fo[8], fd[8], r[8];
+    unpack8(__ldg(x + o), fx);
+    unpack8(__ldg(out + o), fo);
+    unpack8(__ldg(dout + o), fd);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const int c = c0 + k;
+      const float g = fo[k] > 0.f ? fd[k] : fd[k] * slope;
+      const float xh = (fx[k] - sh[c]) * sh[C + c];
+      r[k] = sh[2 * C + c] * (g - sh[3 * C + c] - xh * sh[4 * C + c]);
+    }
+    dx[o] = pack8(r);
+  }
+}
+
+// elementwise: y = act(x)  (pre-activation LeakyReLU of the StarGAN-v2 ResBlk, model.py:56,62)  and  out = sa*a + sb*b
+__global__ void act_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, long long n8, int act) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    float f[8];
+    unpack8(__ldg(x + i), f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] = apply_act(f[k], act);
+    y[i] = pack8(f);
+  }
+}
+__global__ void axpby_kernel(const uint4* __restrict__ a, const uint4* __restrict__ b, uint4* __restrict__ out, long long n8, float sa,
+                             float sb) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    float fa[8], fb[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    unpack8(__ldg(a + i), fa);
+    if (b != nullptr) unpack8(__ldg(b + i), fb);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) fa[k] = sa * fa[k] + sb * fb[k];
+    out[i] = pack8(fa);
+  }
+}
+
 // ------------------------------------------------------------------------------------------ activation backward (+ column sums)
 __global__ void act_bwd_kernel(const uint4* __restrict__ y, const uint4* __restrict__ dy, uint4* __restrict__ dx, float* __restrict__ colsum,
                                long long M, int C8, int chunk, int act) {
@@ -1221,6 +1360,54 @@ extern "C" int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* o
                                                                          (const uint4*)dout, (uint4*)dx, mean_rstd, scratch, H, W, C8,
                                                                          up, relu);
   return LAUNCH_OK("spade_cls_bwd2_kernel");
+}
+
+extern "C" int dei2i_adain_act_fwd(const void* x, void* out, const float* stats, const float* scale, const float* shift,
+                                   float* mean_rstd, int N, int HW, int C, float slope, float eps, dei2i_stream stream) {
+  DEI2I_REQUIRE(x && out && stats && scale && shift && mean_rstd && C % 8 == 0 && HW >= 1, "adain_act_fwd: bad arguments");
+  const long long per_img = (long long)HW * (C / 8);
+  unsigned bx = nblocks(per_img, 256 * 2);
+  const unsigned cap = (148 * 16 + N - 1) / N;
+  if (bx > cap) bx = cap;
+  adain_act_fwd_kernel<<<dim3(bx, N), 256, 2 * C * sizeof(float), ST>>>((const uint4*)x, (uint4*)out, stats, scale, shift, mean_rstd,
+                                                                        HW, C / 8, slope, eps);
+  return LAUNCH_OK("adain_act_fwd_kernel");
+}
+extern "C" int dei2i_adain_act_bwd(const void* x, const void* out, const void* dout, void* dx, const float* scale,
+                                   const float* mean_rstd, float* dshift_dscale, int N, int HW, int C, float slope,
+                                   dei2i_stream stream) {
+  DEI2I_REQUIRE(x && out && dout && dx && scale && mean_rstd && dshift_dscale && C % 8 == 0, "adain_act_bwd: bad arguments");
+  int threads, chunk;
+  unsigned chunks;
+  size_t shmem;
+  if (int rc = launch_channel_reduce_cfg(C, (long long)HW, N, threads, chunk, chunks, shmem)) return rc;
+  DEI2I_CUDA(cudaMemsetAsync(dshift_dscale, 0, (size_t)N * 2 * C * sizeof(float), ST));
+  if (shmem > 48 * 1024)
+    DEI2I_CUDA(cudaFuncSetAttribute(adain_act_bwd1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
+  adain_act_bwd1_kernel<<<dim3(chunks, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)out, (const uint4*)dout, mean_rstd,
+                                                                 dshift_dscale, HW, C / 8, chunk, slope);
+  if (int rc = LAUNCH_OK("adain_act_bwd1_kernel")) return rc;
+  const long long per_img = (long long)HW * (C / 8);
+  unsigned bx = nblocks(per_img, 256 * 2);
+  const unsigned cap = (148 * 16 + N - 1) / N;
+  if (bx > cap) bx = cap;
+  adain_act_bwd2_kernel<<<dim3(bx, N), 256, 5 * C * sizeof(float), ST>>>((const uint4*)x, (const uint4*)out, (const uint4*)dout,
+                                                                         (uint4*)dx, mean_rstd, dshift_dscale, scale, HW, C / 8, slope);
+  return LAUNCH_OK("adain_act_bwd2_kernel");
+}
+extern "C" int dei2i_act_fwd(const void* x, void* y, long long n, int act, dei2i_stream stream) {
+  DEI2I_REQUIRE(x && y && n % 8 == 0, "act_fwd: bad arguments");
+  unsigned blocks = nblocks(n / 8, 256 * 2);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  act_fwd_kernel<<<blocks, 256, 0, ST>>>((const uint4*)x, (uint4*)y, n / 8, act);
+  return LAUNCH_OK("act_fwd_kernel");
+}
+extern "C" int dei2i_axpby(const void* a, const void* b, void* out, long long n, float sa, float sb, dei2i_stream stream) {
+  DEI2I_REQUIRE(a && out && n % 8 == 0, "axpby: bad arguments");
+  unsigned blocks = nblocks(n / 8, 256 * 2);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  axpby_kernel<<<blocks, 256, 0, ST>>>((const uint4*)a, (const uint4*)b, (uint4*)out, n / 8, sa, sb);
+  return LAUNCH_OK("axpby_kernel");
 }
 
 extern "C" int dei2i_act_bwd(const void* y, const void* dy, void* dx, float* bias_grad, long long M, int C, int act,

@@ -90,7 +90,7 @@ class _ToNhwc(Function):
 
     @staticmethod
     def backward(ctx, g):
-        return ops.nhwc_to_nchw(g.contiguous(), ctx.c)
+        return _FromNhwc.apply(g.contiguous(), ctx.c)  # a Function, so that R1 (grad of a grad w.r.t. the image) can pass
 
 
 class _FromNhwc(Function):
@@ -416,7 +416,18 @@ class _AvgPool(Function):
 
     @staticmethod
     def backward(ctx, dout):
-        return ops.avgpool_bwd(dout.contiguous(), ctx.k, ctx.scale), None, None
+        return _AvgPoolBwd.apply(dout, ctx.k, ctx.scale), None, None
+
+
+class _AvgPoolBwd(Function):
+    @staticmethod
+    def forward(ctx, dout, k, scale):
+        ctx.k, ctx.scale = k, scale
+        return ops.avgpool_bwd(dout.contiguous(), k, scale)
+
+    @staticmethod
+    def backward(ctx, ddx):
+        return _AvgPool.apply(ddx.contiguous(), ctx.k, ctx.scale), None, None
 
 
 def avg_pool(x: Nhwc, k, scale=1.0) -> Nhwc:
@@ -440,6 +451,161 @@ class _Gap(Function):
 def global_avg_pool(x: Nhwc) -> torch.Tensor:
     """nn.AdaptiveAvgPool2d(1) + flatten: fp32 [N, C]."""
     return _Gap.apply(x.t, x.c)
+
+
+# ---------------------------------------------------------------------------------------------- twice-differentiable set
+# StarGAN-v2's R1 regulariser (stargan-v2/core/solver.py:573-583) differentiates the discriminator's input gradient again
+# (create_graph=True).  The discriminator is piecewise linear (convolutions, LeakyReLU, average pooling, adds), so the backward
+# of every op below is itself expressed with Functions: the engine can record it and differentiate it once more.
+class _ActBwd(Function):
+    """dz = dy * act'(y) for relu / leaky_relu (derivative piecewise constant in y, linear in dy: its own adjoint)."""
+
+    @staticmethod
+    def forward(ctx, dy, y, act):
+        ctx.act = act
+        ctx.save_for_backward(y)
+        return ops.act_bwd(y, dy.contiguous(), act)[0]
+
+    @staticmethod
+    def backward(ctx, ddz):
+        (y,) = ctx.saved_tensors
+        return _ActBwd.apply(ddz, y, ctx.act), None, None
+
+
+class _Act(Function):
+    @staticmethod
+    def forward(ctx, x, act):
+        assert act in ("relu", "leaky_relu")
+        y = ops.act_fwd(x, act)
+        ctx.act = act
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        return _ActBwd.apply(dy, y, ctx.act), None
+
+
+def activation(x: Nhwc, act="leaky_relu") -> Nhwc:
+    return Nhwc(_Act.apply(x.t, act), x.c)
+
+
+class _Axpby(Function):
+    """sa * a + sb * b."""
+
+    @staticmethod
+    def forward(ctx, a, b, sa, sb):
+        ctx.sa, ctx.sb, ctx.has_b = sa, sb, b is not None
+        return ops.axpby(a.contiguous(), b.contiguous() if b is not None else None, sa, sb)
+
+    @staticmethod
+    def backward(ctx, g):
+        ga = _Axpby.apply(g, None, ctx.sa, 0.0) if ctx.needs_input_grad[0] else None
+        gb = None
+        if ctx.has_b and ctx.needs_input_grad[1]:
+            gb = ga if (ga is not None and ctx.sa == ctx.sb) else _Axpby.apply(g, None, ctx.sb, 0.0)
+        return ga, gb, None, None
+
+
+def add_scaled(a: Nhwc, b: Nhwc, s: float) -> Nhwc:
+    """(a + b) * s - the StarGAN-v2 residual merge (x + r) / sqrt(2)."""
+    return Nhwc(_Axpby.apply(a.t, b.t, s, s), a.c)
+
+
+_input_grad_only = False
+
+
+@contextmanager
+def input_grad_only():
+    """Inside this scope _ConvL.backward computes only the input gradient (torch.autograd.grad(..., inputs=image) of R1)."""
+    global _input_grad_only
+    old, _input_grad_only = _input_grad_only, True
+    try:
+        yield
+    finally:
+        _input_grad_only = old
+
+
+class _DgradL(Function):
+    """dx = dgrad(dy, W); differentiable in dy (-> a forward convolution of the incoming gradient) and in W (-> a wgrad)."""
+
+    @staticmethod
+    def forward(ctx, dy, w, spec, in_hw):
+        ctx.spec = spec
+        ctx.save_for_backward(dy, w)
+        return ops.conv2d_dgrad(dy.contiguous(), _pack(w, spec)[1], spec, in_hw)
+
+    @staticmethod
+    def backward(ctx, ddx):
+        dy, w = ctx.saved_tensors
+        spec = ctx.spec
+        ddx = ddx.contiguous()
+        d_dy = ops.conv2d_fwd(ddx, _pack(w, spec)[0], spec) if ctx.needs_input_grad[0] else None
+        d_w = None
+        if ctx.needs_input_grad[1]:
+            d_w = torch.empty(spec.cout, spec.cin, spec.kh, spec.kw_, dtype=torch.float32, device=ddx.device)
+            ops.conv2d_wgrad(ddx, dy.contiguous(), d_w, spec)
+        return d_dy, d_w, None, None
+
+
+class _ConvL(Function):
+    """y = conv(x, W) + bias ('zeros' padding, no activation): the plain nn.Conv2d of StarGAN-v2, twice differentiable along
+    the input-gradient path (dx is produced by _DgradL)."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias, spec, out_fp32):
+        ctx.spec, ctx.has_bias = spec, bias is not None
+        ctx.save_for_backward(x, w)
+        return ops.conv2d_fwd(x, _pack(w, spec)[0], spec, bias=bias.detach() if bias is not None else None, out_fp32=out_fp32)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        spec = ctx.spec
+        if dy.dtype != torch.bfloat16:
+            dy = dy.to(torch.bfloat16)
+        dx = _DgradL.apply(dy, w, spec, (x.shape[1], x.shape[2])) if ctx.needs_input_grad[0] else None
+        dw = db = None
+        if _input_grad_only:
+            return dx, None, None, None, None
+        dyc = dy.detach().contiguous()
+        if ctx.needs_input_grad[1]:
+            dw = torch.empty(spec.cout, spec.cin, spec.kh, spec.kw_, dtype=torch.float32, device=dy.device)
+            ops.conv2d_wgrad(x, dyc, dw, spec)
+        if ctx.has_bias and ctx.needs_input_grad[2]:
+            db = ops.act_bwd(None, dyc, None, want_dx=False, want_bias_grad=True)[1][: spec.cout]
+        return dx, dw, db, None, None
+
+
+def conv_linear(x: Nhwc, conv_mod, out_fp32=False) -> Nhwc:
+    """nn.Conv2d(k, stride 1, zero padding, optional bias) on the twice-differentiable path."""
+    kh, kw = conv_mod.kernel_size
+    pad = conv_mod.padding[0] if isinstance(conv_mod.padding, (tuple, list)) else conv_mod.padding
+    assert conv_mod.padding_mode == "zeros" and conv_mod.stride[0] == 1 and kh == kw
+    spec = ConvSpec(conv_mod.in_channels, conv_mod.out_channels, kh, 1, pad, "zeros")
+    return Nhwc(_ConvL.apply(x.t, conv_mod.weight, conv_mod.bias, spec, out_fp32), spec.cout)
+
+
+class _AdainAct(Function):
+    @staticmethod
+    def forward(ctx, x, scale, shift, slope, eps):
+        scale = scale.contiguous().float()
+        out, mr = ops.adain_act_fwd(x, scale, shift.contiguous().float(), slope, eps)
+        ctx.slope = slope
+        ctx.save_for_backward(x, out, scale, mr)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        x, out, scale, mr = ctx.saved_tensors
+        dx, dscale, dshift = ops.adain_act_bwd(x, out, dout.contiguous(), scale, mr, ctx.slope)
+        return dx, dscale, dshift, None, None
+
+
+def adain_act(x: Nhwc, scale: torch.Tensor, shift: torch.Tensor, slope=0.2, eps=1e-5) -> Nhwc:
+    """lrelu_slope(IN(x) * scale[n,c] + shift[n,c]); scale / shift fp32 [N,C] (AdaIN: 1 + gamma, beta; affine IN: weight, bias)."""
+    return Nhwc(_AdainAct.apply(x.t, scale, shift, slope, eps), x.c)
 
 
 class _Compose(Function):

@@ -430,6 +430,49 @@ def spade_cls_bwd(x, gb5, out, dout, mean_rstd, up: int = 1, relu: bool = True):
     return dgb5, dx
 
 
+def adain_act_fwd(x, scale, shift, slope: float = 0.2, eps: float = 1e-5):
+    """out = lrelu_slope(IN(x) * scale[n,c] + shift[n,c]); scale / shift fp32 [N,C].  Returns (out, mean_rstd)."""
+    _chk_act(x, "x")
+    _chk_f32(scale, "scale")
+    _chk_f32(shift, "shift")
+    n, h, w, c = x.shape
+    assert tuple(scale.shape) == (n, c) and tuple(shift.shape) == (n, c), (scale.shape, shift.shape, x.shape)
+    stats = channel_stats(x, True)
+    out = torch.empty_like(x)
+    mr = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
+    check(_lib.load().dei2i_adain_act_fwd(_p(x), _p(out), _p(stats), _p(scale), _p(shift), _p(mr), n, h * w, c, float(slope), float(eps),
+                                          _stream()), "dei2i_adain_act_fwd")
+    return out, mr
+
+
+def adain_act_bwd(x, out, dout, scale, mean_rstd, slope: float = 0.2):
+    """-> (dx bf16, dscale fp32 [N,C], dshift fp32 [N,C])."""
+    n, h, w, c = x.shape
+    dx = torch.empty_like(x)
+    red = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
+    check(_lib.load().dei2i_adain_act_bwd(_p(x), _p(out), _p(dout), _p(dx), _p(scale), _p(mean_rstd), _p(red), n, h * w, c, float(slope),
+                                          _stream()), "dei2i_adain_act_bwd")
+    return dx, red[:, 1], red[:, 0]
+
+
+def act_fwd(x, act):
+    _chk_act(x, "x")
+    y = torch.empty_like(x)
+    check(_lib.load().dei2i_act_fwd(_p(x), _p(y), x.numel(), ACT[act], _stream()), "dei2i_act_fwd")
+    return y
+
+
+def axpby(a, b, sa: float, sb: float = 0.0):
+    """sa * a + sb * b over bf16 tensors of equal shape (b may be None)."""
+    _chk_act(a, "a")
+    if b is not None:
+        _chk_act(b, "b")
+        assert b.shape == a.shape, (a.shape, b.shape)
+    out = torch.empty_like(a)
+    check(_lib.load().dei2i_axpby(_p(a), _p(b), _p(out), a.numel(), float(sa), float(sb), _stream()), "dei2i_axpby")
+    return out
+
+
 def act_bwd(y, dy, act, want_dx=True, want_bias_grad=False):
     _chk_act(dy, "dy")
     c = dy.shape[3]

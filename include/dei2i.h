@@ -178,6 +178,22 @@ int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* out, const v
                         const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, int relu,
                         dei2i_stream stream);
 
+/* ---- StarGAN-v2 normalisation (stargan-v2/core/model.py) ----
+ * out = lrelu_slope(IN(x) * scale[n,c] + shift[n,c]): AdaIN with scale = 1 + gamma(s), shift = beta(s) (model.py:73-84), or
+ * InstanceNorm2d(affine=True) with scale = weight[c], shift = bias[c] broadcast over n (model.py:42-43), fused with the
+ * LeakyReLU(0.2) that always follows (model.py:56-63,104-112; slope = 1: none).  stats: dei2i_channel_stats(per_sample=1);
+ * scale / shift fp32 [N,C]; mean_rstd fp32 [N,2,C] (written).
+ * backward: dx bf16 and dshift_dscale fp32 [N,2,C] = (sum g, sum g*xhat), g = dout * lrelu'(out). */
+int dei2i_adain_act_fwd(const void* x, void* out, const float* stats, const float* scale, const float* shift,
+                        float* mean_rstd, int N, int HW, int C, float slope, float eps, dei2i_stream stream);
+int dei2i_adain_act_bwd(const void* x, const void* out, const void* dout, void* dx, const float* scale,
+                        const float* mean_rstd, float* dshift_dscale, int N, int HW, int C, float slope,
+                        dei2i_stream stream);
+/* y = act(x) over n bf16 elements (pre-activation of the StarGAN-v2 ResBlk, model.py:56,62); n % 8 == 0. */
+int dei2i_act_fwd(const void* x, void* y, long long n, int act, dei2i_stream stream);
+/* out = sa * a + sb * b (b may be NULL) over n bf16 elements: residual merge (x + r) / sqrt(2), model.py:66-68,118-121. */
+int dei2i_axpby(const void* a, const void* b, void* out, long long n, float sa, float sb, dei2i_stream stream);
+
 /* act backward for fused conv epilogues: dx = dy * act'(y) computed from the saved OUTPUT y (bf16);
  * bias_grad (fp32 [C], may be NULL) receives sum over pixels of dx. */
 int dei2i_act_bwd(const void* y, const void* dy, void* dx, float* bias_grad, long long M, int C, int act,

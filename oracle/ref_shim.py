@@ -90,3 +90,41 @@ def default_opt(image_size=128, **over):
     for k, v in over.items():
         setattr(opt, k, v)
     return opt
+
+
+REF_STARGAN = os.path.join(REF_ROOT, "stargan-v2")
+_sg = {}
+
+
+def stargan_available() -> bool:
+    return os.path.isdir(os.path.join(REF_STARGAN, "core"))
+
+
+def import_stargan():
+    """The reference's own stargan-v2/core/{model,solver}.py, imported in place.  Absent packages that the hot path never
+    touches (munch, skimage, ffmpeg, lpips, imageio, matplotlib) are satisfied with stubs; Munch gets a working stand-in."""
+    if _sg:
+        return SimpleNamespace(**_sg)
+    if not stargan_available():
+        raise RuntimeError(f"reference not present at {REF_STARGAN}")
+
+    class Munch(dict):
+        __getattr__ = dict.get
+
+        def __setattr__(self, k, v):
+            self[k] = v
+
+    try:
+        import munch  # noqa: F401
+    except Exception:
+        _stub("munch", Munch=Munch)
+    for name in ("skimage", "skimage.filters", "ffmpeg", "lpips", "imageio", "matplotlib", "matplotlib.pyplot"):
+        try:
+            __import__(name)
+        except Exception:
+            _stub(name, gaussian=None)
+    if REF_STARGAN not in sys.path:
+        sys.path.insert(0, REF_STARGAN)
+    from core import model, solver  # type: ignore
+    _sg.update(model=model, solver=solver)
+    return SimpleNamespace(**_sg)

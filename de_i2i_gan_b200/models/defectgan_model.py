@@ -57,8 +57,7 @@ class DefectGanModel(BaseModel):
         if mode == "inference":
             self.netD.eval()
             self.netG.eval()
-            with Fn.weight_cache():
-                return self._generate_fake(data, labels)
+            return self._inference(data, labels)
         if mode == "inference_classifier":
             self.netD.eval()
             self.netG.eval()
@@ -114,6 +113,37 @@ class DefectGanModel(BaseModel):
         return logits, self._cal_loss(logits, labels, self.clf_loss_type)
 
     @torch.no_grad()
+    def _inference(self, data, labels):
+        """``_generate_fake`` under no_grad as a CUDA graph per input-shape signature (configs[4]: at batch <= 16 the ~150
+        launches of a generator pass are host-bound).  Call 1 of a signature runs eagerly, call 2 captures, later calls copy
+        the inputs into the static buffers and replay; the weight packing and the eval-mode spectral-norm sigma are part of the
+        graph and read the parameters in place, so training between two calls is seen.  DEI2I_CUDA_GRAPH=0 disables."""
+        import os
+        graphs = self.__dict__.setdefault("_inf_graphs", {})
+        use = (os.environ.get("DEI2I_CUDA_GRAPH", "1") != "0" and data.is_cuda and not torch.is_grad_enabled()
+               and not torch.cuda.is_current_stream_capturing())
+        if not use:
+            with Fn.weight_cache():
+                return self._generate_fake(data, labels)
+        key = (tuple(data.shape), tuple(labels.shape), data.dtype, labels.dtype)
+        st = graphs.get(key)
+        if st is None:
+            graphs[key] = {}
+            with Fn.weight_cache():
+                return self._generate_fake(data, labels)
+        if "graph" not in st:
+            st["x"], st["l"] = data.clone(), labels.clone()
+            torch.cuda.synchronize()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g), Fn.weight_cache():
+                st["out"] = self._generate_fake(st["x"], st["l"])
+            st["graph"] = g
+        else:
+            st["x"].copy_(data, non_blocking=True)
+            st["l"].copy_(labels, non_blocking=True)
+        st["graph"].replay()
+        return tuple(o.clone() for o in st["out"])
+
     def _generate_fake(self, data, labels):
         """defectgan_model.py:302-314 (spade branch): labels [B,label_nc] or a spatial map [B,label_nc,h,w]."""
         return self.netG(data, self._expand_seg(labels))

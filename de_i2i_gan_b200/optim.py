@@ -6,7 +6,7 @@ into a second one (``p.grad`` are views, zeroed by one memset, accumulated into 
 more.  ``step()`` is then one kernel launch per parameter group, and the gradient vector is exactly what the
 data-parallel bucket all-reduce (de_i2i_gan_b200/parallel.py) sends over NCCL - no gather/scatter copies.
 
-Semantics vs torch.optim.Adam: identical update rule (bias correction, eps outside the sqrt, no weight decay, no
+Semantics vs torch.optim.Adam: identical update rule (bias correction, eps outside the sqrt, optional L2 weight decay, no
 amsgrad).  torch skips parameters whose ``grad is None``; here such parameters see a zero gradient, for which the Adam
 update is exactly zero (m = v = 0  =>  step = 0 / (0 + eps)), so unused parameters (the generator's never-executed
 ``norm_s`` / ``conv_s``) stay bit-identical as well.
@@ -23,8 +23,8 @@ def _align(n: int, a: int = 64) -> int:
 
 
 class FlatAdam(torch.optim.Optimizer):
-    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
-        defaults = dict(lr=lr, betas=betas, eps=eps)
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
+        defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
         super().__init__(params, defaults)
         self._flat = []  # per group: dict(p=, g=, m=, v=, step=)
         for group in self.param_groups:
@@ -108,6 +108,8 @@ class FlatAdam(torch.optim.Optimizer):
             self.advance()
         for group, f in zip(self.param_groups, self._flat):
             b1, b2 = group["betas"]
+            if group.get("weight_decay", 0.0):  # torch.optim.Adam: grad += wd * param (StarGAN-v2 solver.py:72-80)
+                f["g"].add_(f["p"], alpha=float(group["weight_decay"]))
             ops.adam_dev(f["p"], f["g"], f["m"], f["v"], f["hyper"], float(b1), float(b2), float(group["eps"]))
         return loss
 

@@ -74,3 +74,28 @@ def test_graphed_steps_match_eager(tmp_path):
     ratio = (p1.norm() / p0.norm()).item()
     assert cos > 0.9 and abs(ratio - 1.0) < 0.03, (cos, ratio)  # cos ~0.97: Adam turns noise-level gradient differences into sign flips
     assert (b0 - b1).abs().max().item() <= 2e-3 * b0.abs().max().item()
+
+
+def test_graphed_inference_matches_eager(tmp_path, monkeypatch):
+    """DefectGanModel('inference') replayed from its CUDA graph (third call) vs the eager path, with fresh inputs and with the
+    generator's weights changed after capture (the graph packs the weights in place on every replay)."""
+    from de_i2i_gan_b200.models.networks import architecture as A
+    tr = _trainer(False, tmp_path)
+    model = tr.model
+    g = torch.Generator().manual_seed(6)
+    xs = [torch.randn(2, 3, 128, 128, generator=g).clamp(-1, 1).cuda() for _ in range(3)]
+    lab = torch.zeros(2, 6).cuda()
+    lab[:, 2] = 1
+    A.set_noise_source(_noise)
+    try:
+        with torch.no_grad():
+            model("inference", xs[0], lab)
+            model("inference", xs[1], lab)  # captures
+            for p in model.netG.parameters():
+                p.mul_(1.01)
+            out_g, prob_g = model("inference", xs[2], lab)  # replay
+            monkeypatch.setenv("DEI2I_CUDA_GRAPH", "0")
+            out_e, prob_e = model("inference", xs[2], lab)
+    finally:
+        A.set_noise_source(None)
+    assert torch.allclose(out_g, out_e, atol=1e-6) and torch.allclose(prob_g, prob_e, atol=1e-6)

@@ -284,7 +284,8 @@ def run_ours(args):
     conv_ms = sum(v[1] for v in agg.values())
     conv_flops = sum(v[0] for v in agg.values())
     # dominant kernel = the dense tcgen05 convolution class with the largest share of the step (tensor-bound); the skinny
-    # classes (8-channel inputs / <= 4 outputs, HBM-bound by construction) are listed in `detail`
+    # classes (8-channel inputs / <= 4 outputs, HBM-bound by construction) and the tiny class (< 2 GFLOP launches: 5x5 SPADE
+    # class-map convolutions, classifier heads - launch-latency bound) are listed in `detail`
     dense = {k: v for k, v in agg.items() if k.endswith("_dense")}
     dom = max(dense, key=lambda k: dense[k][1]) if dense else (max(agg, key=lambda k: agg[k][1]) if agg else None)
     roofline = None

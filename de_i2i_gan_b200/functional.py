@@ -203,7 +203,8 @@ class _RowpackConv(Function):
         spec2 = ConvSpec(64, spec.cout, spec.kh, 1, 0, "zeros", 1)
         w_fwd, w_dg = _rowpack_weight(w_param, spec, spec2)
         xp = ops.rowpack_fwd(x.contiguous().float(), spec.kw_, spec.pad)
-        y = ops.conv2d_fwd(xp, w_fwd, spec2, scale=scale)
+        ctx.flops = spec.flops(x.shape[0], x.shape[2], x.shape[3])  # algorithmic FLOPs of the ORIGINAL kh x kw x C convolution
+        y = ops.conv2d_fwd(xp, w_fwd, spec2, scale=scale, alg_flops=ctx.flops)
         ctx.spec, ctx.spec2, ctx.w_dg, ctx.scale, ctx.sn = spec, spec2, w_dg, scale, wts_sn
         ctx.save_for_backward(xp)
         return y
@@ -215,11 +216,11 @@ class _RowpackConv(Function):
         dy = dy.contiguous()
         dx = dw = None
         if ctx.needs_input_grad[0]:
-            dxp = ops.conv2d_dgrad(dy, ctx.w_dg, spec2, (xp.shape[1], xp.shape[2]), scale=ctx.scale)
+            dxp = ops.conv2d_dgrad(dy, ctx.w_dg, spec2, (xp.shape[1], xp.shape[2]), scale=ctx.scale, alg_flops=ctx.flops)
             dx = ops.rowpack_bwd(dxp, spec.cin, spec.kw_, spec.pad)
         if ctx.needs_input_grad[1]:
             dw2 = torch.empty(spec.cout, 64, spec.kh, 1, dtype=torch.float32, device=dy.device)
-            ops.conv2d_wgrad(xp, dy, dw2, spec2)
+            ops.conv2d_wgrad(xp, dy, dw2, spec2, alg_flops=ctx.flops)
             g = dw2.view(spec.cout, 8, 8, spec.kh)[:, : spec.kw_, : spec.cin].permute(0, 2, 3, 1)  # [Cout,C,kh,kw]: d/d(W/sigma)
             if ctx.sn is not None:
                 # spectral_norm backward (u, v constants): dW_orig = (G - <G, W/sigma> u v^T) / sigma

@@ -131,8 +131,14 @@ def pack_weight(w: torch.Tensor, spec: ConvSpec, inv_sigma: torch.Tensor = None,
     return w_fwd, w_dg
 
 
+def _kind(op, spec, flops):
+    """Timing class of a convolution launch: 'dense' (tcgen05, tensor-bound), 'skinny' (HBM-bound by construction) or
+    'tiny' (< 2 GFLOP: the 5x5 SPADE class-map convolutions, classifier heads, linears - launch-latency bound)."""
+    return f"conv_{op}_" + ("tiny" if flops < 2e9 else spec.klass)
+
+
 def conv2d_fwd(x, w_fwd, spec: ConvSpec, bias=None, noise=None, noise_weight=None, residual=None, act=None,
-               out_fp32=False, logical_hw=None, scale=None):
+               out_fp32=False, logical_hw=None, scale=None, alg_flops=None):
     """x: bf16 [N,Hs,Ws,Cin_ld]; logical_hw=(H,W) nearest-resizes x on the fly. Returns [N,Ho,Wo,Cout_ld]."""
     _chk_act(x, "x")
     n, hs, ws, c = x.shape
@@ -148,12 +154,13 @@ def conv2d_fwd(x, w_fwd, spec: ConvSpec, bias=None, noise=None, noise_weight=Non
         assert noise.numel() == n * ho * wo
     g = spec.geom(n, h, w, hs, ws)
     e = ConvEpilogue(_p(scale), _p(bias), _p(noise), _p(noise_weight), _p(residual), ACT[act], int(out_fp32))
-    with _Timed("conv_fwd_" + spec.klass, spec.flops(n, ho, wo), spec.tag(n, h, w)):
+    fl = alg_flops or spec.flops(n, ho, wo)
+    with _Timed(_kind("fwd", spec, fl), fl, spec.tag(n, h, w)):
         check(_lib.load().dei2i_conv2d_fwd(_p(x), _p(w_fwd), _p(y), C.byref(g), C.byref(e), _stream()), "dei2i_conv2d_fwd")
     return y
 
 
-def conv2d_dgrad(dy, w_dgrad, spec: ConvSpec, in_hw, scale=None):
+def conv2d_dgrad(dy, w_dgrad, spec: ConvSpec, in_hw, scale=None, alg_flops=None):
     """dy: bf16 [N,Ho,Wo,Cout_ld] -> dx bf16 [N,H,W,Cin_ld] (reflect padding folded back)."""
     _chk_act(dy, "dy")
     n = dy.shape[0]
@@ -161,17 +168,17 @@ def conv2d_dgrad(dy, w_dgrad, spec: ConvSpec, in_hw, scale=None):
     assert tuple(dy.shape[1:3]) == spec.out_hw(h, w) and dy.shape[3] == spec.cout_ld
     g = spec.geom(n, h, w)
     lib = _lib.load()
-    flops = spec.flops(n, dy.shape[1], dy.shape[2])
+    flops = alg_flops or spec.flops(n, dy.shape[1], dy.shape[2])
     if spec.pad_mode == "reflect" and spec.pad > 0:
         p = spec.pad
         dxp = torch.empty(n, h + 2 * p, w + 2 * p, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
-        with _Timed("conv_dgrad_" + spec.klass, flops, spec.tag(n, h, w)):
+        with _Timed(_kind("dgrad", spec, flops), flops, spec.tag(n, h, w)):
             check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dxp), C.byref(g), _p(scale), 0, _stream()), "dei2i_conv2d_dgrad")
         dx = torch.empty(n, h, w, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
         check(lib.dei2i_reflect_fold(_p(dxp), _p(dx), n, h, w, spec.cin_ld, p, _stream()), "dei2i_reflect_fold")
         return dx
     dx = torch.empty(n, h, w, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
-    with _Timed("conv_dgrad_" + spec.klass, flops, spec.tag(n, h, w)):
+    with _Timed(_kind("dgrad", spec, flops), flops, spec.tag(n, h, w)):
         check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dx), C.byref(g), _p(scale), 0, _stream()), "dei2i_conv2d_dgrad")
     return dx
 
@@ -207,7 +214,7 @@ def _workspace(nbytes, device):
     return buf
 
 
-def conv2d_wgrad(x, dy, dw, spec: ConvSpec, accumulate=False, sn=None, logical_hw=None):
+def conv2d_wgrad(x, dy, dw, spec: ConvSpec, accumulate=False, sn=None, logical_hw=None, alg_flops=None):
     """dw (fp32 [Cout,Cin,kh,kw]) = or += grad.  sn = (w_orig, u, v, inv_sigma) applies the spectral-norm backward."""
     _chk_act(x, "x")
     _chk_act(dy, "dy")
@@ -219,7 +226,8 @@ def conv2d_wgrad(x, dy, dw, spec: ConvSpec, accumulate=False, sn=None, logical_h
     nbytes = lib.dei2i_conv2d_wgrad_workspace(C.byref(g), spec.cin)
     wsb = _workspace(nbytes, x.device)
     w0, u, v, inv = sn if sn is not None else (None, None, None, None)
-    with _Timed("conv_wgrad_" + spec.klass, spec.flops(n, dy.shape[1], dy.shape[2]), spec.tag(n, h, w)):
+    fl = alg_flops or spec.flops(n, dy.shape[1], dy.shape[2])
+    with _Timed(_kind("wgrad", spec, fl), fl, spec.tag(n, h, w)):
         check(lib.dei2i_conv2d_wgrad(_p(x), _p(dy), _p(dw), spec.cin, 1.0 if accumulate else 0.0, C.byref(g), _p(w0), _p(u),
                                      _p(v), _p(inv), _p(wsb), wsb.numel(), _stream()), "dei2i_conv2d_wgrad")
     return dw

@@ -56,8 +56,8 @@ SIGNATURES = {
     "dei2i_bn_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dei2i_spade_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
     "dei2i_spade_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
-    "dei2i_spade_cls_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
-    "dei2i_spade_cls_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
+    "dei2i_spade_cls_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _I, _P]),
+    "dei2i_spade_cls_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P]),
     "dei2i_act_bwd": (_I, [_P, _P, _P, _P, _LL, _I, _I, _P]),
     "dei2i_noise_wgrad": (_I, [_P, _P, _P, _LL, _I, _I, _F, _P]),
     "dei2i_compose_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),

@@ -608,7 +608,7 @@ DEVINL int bcls(int i, int n) { return i < 2 ? i : (i >= n - 2 ? i - n + 5 : 2);
 
 __global__ void spade_cls_fwd_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, uint4* __restrict__ out,
                                      const float* __restrict__ stats, float* __restrict__ mean_rstd, int N, int H, int W, int C8,
-                                     int up, int relu, float eps) {
+                                     int up, int relu, float eps, int pad) {
   extern __shared__ float sh[];  // mean[C], rstd[C]
   const int C = C8 * 8;
   const int n = blockIdx.y;
@@ -626,11 +626,14 @@ __global__ void spade_cls_fwd_kernel(const uint4* __restrict__ x, const uint4* _
     }
   }
   __syncthreads();
-  const long long per_img = (long long)H * W * C8;
+  // pad > 0: the output carries the reflect padding of the convolution that consumes it (out is [N, H+2pad, W+2pad, C]):
+  // padded pixel (hp, wp) is computed from its mirror source - 3 % more pixels instead of a separate pad pass
+  const int Wp = W + 2 * pad;
+  const long long per_img = (long long)(H + 2 * pad) * Wp * C8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img; i += (long long)gridDim.x * blockDim.x) {
     const int c8 = (int)(i % C8);
     const long long pix = i / C8;
-    const int w = (int)(pix % W), h = (int)(pix / W);
+    const int w = reflect_idx((int)(pix % Wp) - pad, W), h = reflect_idx((int)(pix / Wp) - pad, H);
     float fx[8], fg[8], fb[8], o[8];
     unpack8(__ldg(x + (((long long)n * Hx + h / up) * Wx + w / up) * C8 + c8), fx);
     const int gbase = ((n * 5 + bcls(h, H)) * 5 + bcls(w, W)) * (2 * C8);
@@ -646,12 +649,37 @@ __global__ void spade_cls_fwd_kernel(const uint4* __restrict__ x, const uint4* _
   }
 }
 
+// out / dout of a consumer-padded SPADE output ([N, H+2pad, W+2pad, C]): the activation at (h, w) sits at (h+pad, w+pad); its
+// gradient is the sum over every padded position that mirrors onto (h, w) (the adjoint of the reflect padding, <= 4 reads).
+DEVINL void load_folded(const uint4* __restrict__ t, long long img_base, int h, int w, int H, int W, int pad, int C8, int c8,
+                        float (&f)[8]) {
+  const int Wp = W + 2 * pad;
+  unpack8(__ldg(t + (img_base + (long long)(h + pad) * Wp + (w + pad)) * C8 + c8), f);
+  if (pad == 0) return;
+  int hs[3], ws[3], nh = 0, nw = 0;
+  hs[nh++] = h + pad;
+  if (h >= 1 && h <= pad) hs[nh++] = pad - h;
+  if (h <= H - 2 && h >= H - 1 - pad) hs[nh++] = 2 * H - 2 - h + pad;
+  ws[nw++] = w + pad;
+  if (w >= 1 && w <= pad) ws[nw++] = pad - w;
+  if (w <= W - 2 && w >= W - 1 - pad) ws[nw++] = 2 * W - 2 - w + pad;
+  if (nh == 1 && nw == 1) return;
+  for (int a = 0; a < nh; ++a)
+    for (int b = 0; b < nw; ++b) {
+      if (a == 0 && b == 0) continue;
+      float g[8];
+      unpack8(__ldg(t + (img_base + (long long)hs[a] * Wp + ws[b]) * C8 + c8), g);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] += g[k];
+    }
+}
+
 // backward pass 1 over whole rows [r0, r1) of image n: g = dout * (out > 0);  per border class  dgamma5 += g * xhat,
 // dbeta5 += g  (fp32 [N,5,5,2C], atomics);  S1 = sum g(1+gamma), S2 = sum g(1+gamma) xhat  per (n,c) into `red`.
 // smem table: 25 classes x 2C + one row [S1 | S2]; a thread keeps the sums of its current class in registers.
 __global__ void spade_cls_bwd1_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ out,
                                       const uint4* __restrict__ dout, float* __restrict__ dgb5, const float* __restrict__ mean_rstd,
-                                      float* __restrict__ red /*[N,2,C]*/, int H, int W, int C8, int up, int rows, int relu) {
+                                      float* __restrict__ red /*[N,2,C]*/, int H, int W, int C8, int up, int rows, int relu, int pad) {
   extern __shared__ float tab[];  // [26][2C]
   const int c8 = threadIdx.x % C8;
   const int lane = threadIdx.x / C8;
@@ -670,7 +698,8 @@ __global__ void spade_cls_bwd1_kernel(const uint4* __restrict__ x, const uint4* 
     mu[k] = mean_rstd[(n * 2 + 0) * C + c8 * 8 + k];
     rs[k] = mean_rstd[(n * 2 + 1) * C + c8 * 8 + k];
   }
-  const long long img = (long long)n * H * W;
+  const int Wp = W + 2 * pad;
+  const long long img = (long long)n * (H + 2 * pad) * Wp;
   for (long long p = (long long)r0 * W + lane; p < (long long)r1 * W; p += lanes) {
     const int w = (int)(p % W), h = (int)(p / W);
     const int cls = bcls(h, H) * 5 + bcls(w, W);
@@ -688,8 +717,8 @@ __global__ void spade_cls_bwd1_kernel(const uint4* __restrict__ x, const uint4* 
     }
     float fx[8], fo[8], fd[8];
     unpack8(__ldg(x + (((long long)n * Hx + h / up) * Wx + w / up) * C8 + c8), fx);
-    unpack8(__ldg(out + (img + p) * C8 + c8), fo);
-    unpack8(__ldg(dout + (img + p) * C8 + c8), fd);
+    unpack8(__ldg(out + (img + (long long)(h + pad) * Wp + (w + pad)) * C8 + c8), fo);
+    load_folded(dout, img, h, w, H, W, pad, C8, c8, fd);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const float xh = (fx[k] - mu[k]) * rs[k];
@@ -720,7 +749,7 @@ __global__ void spade_cls_bwd1_kernel(const uint4* __restrict__ x, const uint4* 
 // backward pass 2: dx[n,hx,wx,c] = rstd * (sum_{up x up} g (1 + gamma5) - up^2 S1/HW - xhat up^2 S2/HW),  g recomputed
 __global__ void spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ out,
                                       const uint4* __restrict__ dout, uint4* __restrict__ dx, const float* __restrict__ mean_rstd,
-                                      const float* __restrict__ red, int H, int W, int C8, int up, int relu) {
+                                      const float* __restrict__ red, int H, int W, int C8, int up, int relu, int pad) {
   extern __shared__ float sh[];  // mean, rstd, k1, k2
   const int C = C8 * 8;
   const int n = blockIdx.y;
@@ -744,11 +773,12 @@ __global__ void spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* 
     for (int dy = 0; dy < up; ++dy)
       for (int dxx = 0; dxx < up; ++dxx) {
         const int h = hx * up + dy, w = wx * up + dxx;
-        const long long p = ((long long)n * H + h) * W + w;
+        const int Wp = W + 2 * pad;
+        const long long img = (long long)n * (H + 2 * pad) * Wp;
         float fg[8], fo[8], fd[8];
         unpack8(__ldg(gb5 + ((n * 5 + bcls(h, H)) * 5 + bcls(w, W)) * (2 * C8) + c8), fg);
-        unpack8(__ldg(out + p * C8 + c8), fo);
-        unpack8(__ldg(dout + p * C8 + c8), fd);
+        unpack8(__ldg(out + (img + (long long)(h + pad) * Wp + (w + pad)) * C8 + c8), fo);
+        load_folded(dout, img, h, w, H, W, pad, C8, c8, fd);
 #pragma unroll
         for (int k = 0; k < 8; ++k) acc[k] += ((!relu || fo[k] > 0.f) ? fd[k] : 0.f) * (1.f + fg[k]);
       }
@@ -1318,21 +1348,23 @@ extern "C" int dei2i_spade_bwd(const void* x, const void* gb, const void* out, c
 }
 
 extern "C" int dei2i_spade_cls_fwd(const void* x, const void* gb5, void* out, const float* stats, float* mean_rstd, int N, int H,
-                                   int W, int C, int up, int relu, float eps, dei2i_stream stream) {
+                                   int W, int C, int up, int relu, float eps, int out_pad, dei2i_stream stream) {
+  DEI2I_REQUIRE(out_pad >= 0 && 2 * out_pad + 1 < H && 2 * out_pad + 1 < W, "spade_cls_fwd: out_pad (%d) too large", out_pad);
   DEI2I_REQUIRE(x && gb5 && out && stats && mean_rstd && C % 8 == 0 && up >= 1 && H % up == 0 && W % up == 0 && H >= 5 && W >= 5,
                 "spade_cls_fwd: bad arguments (needs H, W >= 5)");
-  const long long per_img = (long long)H * W * (C / 8);
+  const long long per_img = (long long)(H + 2 * out_pad) * (W + 2 * out_pad) * (C / 8);
   unsigned bx = nblocks(per_img, 256 * 2);
   const unsigned cap = (148 * 16 + N - 1) / N;
   if (bx > cap) bx = cap;
   spade_cls_fwd_kernel<<<dim3(bx, N), 256, 2 * C * sizeof(float), ST>>>((const uint4*)x, (const uint4*)gb5, (uint4*)out, stats,
-                                                                        mean_rstd, N, H, W, C / 8, up, relu, eps);
+                                                                        mean_rstd, N, H, W, C / 8, up, relu, eps, out_pad);
   return LAUNCH_OK("spade_cls_fwd_kernel");
 }
 
 extern "C" int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* out, const void* dout, float* dgb5, void* dx,
                                    const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, int relu,
-                                   dei2i_stream stream) {
+                                   int out_pad, dei2i_stream stream) {
+  DEI2I_REQUIRE(out_pad >= 0 && 2 * out_pad + 1 < H && 2 * out_pad + 1 < W, "spade_cls_bwd: out_pad (%d) too large", out_pad);
   DEI2I_REQUIRE(x && gb5 && out && dout && dgb5 && dx && mean_rstd && scratch && C % 8 == 0 && C <= 512 && up >= 1 && H >= 5 && W >= 5,
                 "spade_cls_bwd: bad arguments (needs H, W >= 5, C <= 512)");
   const int C8 = C / 8;
@@ -1350,7 +1382,7 @@ extern "C" int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* o
   if (shmem > 48 * 1024)
     DEI2I_CUDA(cudaFuncSetAttribute(spade_cls_bwd1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
   spade_cls_bwd1_kernel<<<dim3(gx, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out, (const uint4*)dout,
-                                                             dgb5, mean_rstd, scratch, H, W, C8, up, rows, relu);
+                                                             dgb5, mean_rstd, scratch, H, W, C8, up, rows, relu, out_pad);
   if (int rc = LAUNCH_OK("spade_cls_bwd1_kernel")) return rc;
   const long long per_img = (long long)(H / up) * (W / up) * C8;
   unsigned bx = nblocks(per_img, 256 * 2);
@@ -1358,7 +1390,7 @@ extern "C" int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* o
   if (bx > cap) bx = cap;
   spade_cls_bwd2_kernel<<<dim3(bx, N), 256, 4 * C * sizeof(float), ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out,
                                                                          (const uint4*)dout, (uint4*)dx, mean_rstd, scratch, H, W, C8,
-                                                                         up, relu);
+                                                                         up, relu, out_pad);
   return LAUNCH_OK("spade_cls_bwd2_kernel");
 }
 

@@ -16,15 +16,16 @@ from .ops import ConvSpec
 
 class Nhwc:
     """BF16 NHWC activation carrier. ``t``: [N,H,W,C_ld] (C_ld % 8 == 0), ``c``: real channels."""
-    __slots__ = ("t", "c", "cls5")
+    __slots__ = ("t", "c", "cls5", "pad")
 
     def __init__(self, t: torch.Tensor, c: int):
         self.t, self.c, self.cls5 = t, c, None
+        self.pad = 0  # pixels of reflect padding already present on every side of ``t`` (written by the producer for its consumer)
 
     @property
     def shape(self):  # logical NCHW shape, like the reference's tensors
         n, h, w, _ = self.t.shape
-        return (n, self.c, h, w)
+        return (n, self.c, h - 2 * self.pad, w - 2 * self.pad)
 
 
 # ------------------------------------------------------------------------------------------------ weight preparation
@@ -358,21 +359,21 @@ class _SpadeCls(Function):
     """SPADE modulation with gamma|beta on the [N,5,5,2C] border-class map of a constant label map."""
 
     @staticmethod
-    def forward(ctx, x, gb5, up, relu, eps):
-        out, mr = ops.spade_cls_fwd(x, gb5, up, relu, eps)
-        ctx.up, ctx.relu = up, relu
+    def forward(ctx, x, gb5, up, relu, eps, out_pad):
+        out, mr = ops.spade_cls_fwd(x, gb5, up, relu, eps, out_pad)
+        ctx.up, ctx.relu, ctx.out_pad = up, relu, out_pad
         ctx.save_for_backward(x, gb5, out, mr)
         return out
 
     @staticmethod
     def backward(ctx, dout):
         x, gb5, out, mr = ctx.saved_tensors
-        dgb5, dx = ops.spade_cls_bwd(x, gb5, out, dout.contiguous(), mr, ctx.up, ctx.relu)
-        return dx, dgb5.to(torch.bfloat16), None, None, None
+        dgb5, dx = ops.spade_cls_bwd(x, gb5, out, dout.contiguous(), mr, ctx.up, ctx.relu, ctx.out_pad)
+        return dx, dgb5.to(torch.bfloat16), None, None, None, None
 
 
-def spade_modulate_cls(x: Nhwc, gb5: Nhwc, up=1, relu=True, eps=1e-5) -> Nhwc:
-    return Nhwc(_SpadeCls.apply(x.t, gb5.t, up, relu, eps), x.c)
+def spade_modulate_cls(x: Nhwc, gb5: Nhwc, up=1, relu=True, eps=1e-5, out_pad=0) -> Nhwc:
+    return Nhwc(_SpadeCls.apply(x.t, gb5.t, up, relu, eps, out_pad), x.c)
 
 
 class _UpsamplePad(Function):

@@ -19,6 +19,7 @@ from ... import functional as Fn
 from ...ops import ConvSpec
 from .normalization import SPADE
 
+FUSE_REFLECT_PAD = os.environ.get("DEI2I_FUSE_REFLECT_PAD", "1") != "0"
 ROWPACK_STEM = os.environ.get("DEI2I_ROWPACK_STEM", "1") != "0"
 _ACT_NAMES = {nn.LeakyReLU: "leaky_relu", nn.ReLU: "relu", nn.Sigmoid: "sigmoid", nn.Tanh: "tanh", nn.Identity: None}
 
@@ -268,6 +269,19 @@ class ResBlock(nn.Module):
         return Fn.from_nhwc(y) if plain else y
 
 
+def _fusable_pad(spec: ConvSpec) -> int:
+    """Reflect padding a producer may write for this convolution (0: zero padding / none)."""
+    return spec.pad if (FUSE_REFLECT_PAD and spec.pad_mode == "reflect" and spec.pad > 0) else 0
+
+
+def _consumer_spec(spec: ConvSpec, x: "Fn.Nhwc") -> ConvSpec:
+    """The convolution as seen by an input that already carries its reflect padding (x.pad == spec.pad) or not (x.pad == 0)."""
+    if x.pad:
+        assert x.pad == spec.pad and spec.pad_mode == "reflect"
+        return spec.unpadded()
+    return spec
+
+
 def _style_norm(kind, label_nc, nc, hidden_nc, kernel_size, padding, norm_layer):
     if kind == "spade":
         return SPADE(label_nc, nc, hidden_nc=hidden_nc, kernel_size=kernel_size, padding=padding, norm_layer=norm_layer)
@@ -302,11 +316,11 @@ class NormConvBlock(nn.Module):
     def forward(self, x, labels, style_feat=None):
         plain = not isinstance(x, Fn.Nhwc)
         xa = Fn.to_nhwc(x)
-        s = self.norm(xa, labels, up=self._up, relu=self._relu)
+        s = self.norm(xa, labels, up=self._up, relu=self._relu, out_pad=_fusable_pad(self._spec))
         n, _, h, w = s.shape
         ho, wo = self._spec.out_hw(h, w)
         noise, nw = _noise_args(self.noise, n, ho, wo, s.t.device)
-        y = Fn.conv(s, self.conv, self._spec, self.conv.training, bias=self.conv.bias, noise=noise, noise_w=nw)
+        y = Fn.conv(s, self.conv, _consumer_spec(self._spec, s), self.conv.training, bias=self.conv.bias, noise=noise, noise_w=nw)
         return Fn.from_nhwc(y) if plain else y
 
     def update_alpha(self, epoch, num_epochs):
@@ -350,12 +364,12 @@ class NormResBlock(nn.Module):
         xa = Fn.to_nhwc(x)
         n, _, h, w = xa.shape
         dev = xa.t.device
-        s = self.norm_0(xa, labels, relu=self._relu)
+        s = self.norm_0(xa, labels, relu=self._relu, out_pad=_fusable_pad(self._spec0))
         noise, nw = _noise_args(self.noise_0, n, h, w, dev)
-        y = Fn.conv(s, self.conv_0, self._spec0, self.conv_0.training, bias=self.conv_0.bias, noise=noise, noise_w=nw)
-        s = self.norm_1(y, labels, relu=self._relu)
+        y = Fn.conv(s, self.conv_0, _consumer_spec(self._spec0, s), self.conv_0.training, bias=self.conv_0.bias, noise=noise, noise_w=nw)
+        s = self.norm_1(y, labels, relu=self._relu, out_pad=_fusable_pad(self._spec1))
         noise, nw = _noise_args(self.noise_1, n, h, w, dev)
-        y = Fn.conv(s, self.conv_1, self._spec1, self.conv_1.training, bias=self.conv_1.bias, noise=noise, noise_w=nw,
+        y = Fn.conv(s, self.conv_1, _consumer_spec(self._spec1, s), self.conv_1.training, bias=self.conv_1.bias, noise=noise, noise_w=nw,
                     residual=xa)
         return Fn.from_nhwc(y) if plain else y
 

@@ -33,9 +33,11 @@ class SPADE(nn.Module):
         self._shared_spec = ConvSpec(label_nc, hidden_nc, k, 1, pad, "zeros")
         self._gb_spec = ConvSpec(hidden_nc, 2 * norm_nc, k, 1, pad, "zeros")
 
-    def forward(self, x, segmap, up=1, relu=False):
+    def forward(self, x, segmap, up=1, relu=False, out_pad=0):
         """x: NCHW tensor (drop-in) or Nhwc; segmap: [B,label_nc,h,w] NCHW or Nhwc.  ``up`` / ``relu`` are the fused
-        followers used by NormConvBlock / NormResBlock (architecture.py:242-244,347-348); defaults = reference SPADE."""
+        followers used by NormConvBlock / NormResBlock (architecture.py:242-244,347-348); defaults = reference SPADE.
+        ``out_pad`` > 0 asks for the reflect padding of the consuming convolution to be written with the output; the returned
+        carrier's ``.pad`` says how much of it was (0 on the paths that do not fuse it)."""
         plain = not isinstance(x, Fn.Nhwc)
         xa = Fn.to_nhwc(x)
         seg = Fn.to_nhwc(segmap)
@@ -50,7 +52,9 @@ class SPADE(nn.Module):
                 seg.cls5 = Fn.Nhwc(seg.t.expand(n, 5, 5, seg.t.shape[3]).contiguous(), seg.c)
             actv = Fn.conv(seg.cls5, sconv, self._shared_spec, self.training, bias=sconv.bias, act="relu")
             gb5 = Fn.conv_cat(actv, self.mlp_gamma, self.mlp_beta, self._gb_spec)
-            out = Fn.spade_modulate_cls(xa, gb5, up=up, relu=relu, eps=self.param_free_norm.eps)
+            pad = 0 if plain else out_pad
+            out = Fn.spade_modulate_cls(xa, gb5, up=up, relu=relu, eps=self.param_free_norm.eps, out_pad=pad)
+            out.pad = pad
             return Fn.from_nhwc(out) if plain else out
         actv = Fn.conv(seg, sconv, self._shared_spec, self.training, bias=sconv.bias, act="relu", logical_hw=(h, w))
         gb = Fn.conv_cat(actv, self.mlp_gamma, self.mlp_beta, self._gb_spec)

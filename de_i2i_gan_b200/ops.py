@@ -412,29 +412,32 @@ def spade_bwd(x, gb, out, dout, mean_rstd, up: int = 1, relu: bool = True):
     return dgb, dx
 
 
-def spade_cls_fwd(x, gb5, up: int = 1, relu: bool = True, eps: float = 1e-5):
-    """SPADE over a border-class map (constant label map): gb5 bf16 [N,5,5,2C]; otherwise like spade_fwd."""
+def spade_cls_fwd(x, gb5, up: int = 1, relu: bool = True, eps: float = 1e-5, out_pad: int = 0):
+    """SPADE over a border-class map (constant label map): gb5 bf16 [N,5,5,2C]; otherwise like spade_fwd.  out_pad > 0: the
+    output is [N,H+2p,W+2p,C] with the reflect padding of the consuming convolution already in place."""
     _chk_act(x, "x")
     _chk_act(gb5, "gb5")
     n, hx, wx, c = x.shape
     h, w = hx * up, wx * up
     assert tuple(gb5.shape) == (n, 5, 5, 2 * c), (gb5.shape, x.shape)
     stats = channel_stats(x, True)
-    out = torch.empty(n, h, w, c, dtype=torch.bfloat16, device=x.device)
+    out = torch.empty(n, h + 2 * out_pad, w + 2 * out_pad, c, dtype=torch.bfloat16, device=x.device)
     mr = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
-    check(_lib.load().dei2i_spade_cls_fwd(_p(x), _p(gb5), _p(out), _p(stats), _p(mr), n, h, w, c, up, int(relu), eps, _stream()),
-          "dei2i_spade_cls_fwd")
+    check(_lib.load().dei2i_spade_cls_fwd(_p(x), _p(gb5), _p(out), _p(stats), _p(mr), n, h, w, c, up, int(relu), eps, out_pad,
+                                          _stream()), "dei2i_spade_cls_fwd")
     return out, mr
 
 
-def spade_cls_bwd(x, gb5, out, dout, mean_rstd, up: int = 1, relu: bool = True):
-    """-> (dgb5 fp32 [N,5,5,2C], dx bf16)."""
+def spade_cls_bwd(x, gb5, out, dout, mean_rstd, up: int = 1, relu: bool = True, out_pad: int = 0):
+    """-> (dgb5 fp32 [N,5,5,2C], dx bf16).  out / dout carry ``out_pad`` pixels of reflect padding (folded on read)."""
     n, h, w, c = out.shape
+    h, w = h - 2 * out_pad, w - 2 * out_pad
+    assert dout.shape == out.shape
     dgb5 = torch.empty(n, 5, 5, 2 * c, dtype=torch.float32, device=x.device)
     dx = torch.empty_like(x)
     scratch = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
     check(_lib.load().dei2i_spade_cls_bwd(_p(x), _p(gb5), _p(out), _p(dout), _p(dgb5), _p(dx), _p(mean_rstd), _p(scratch), n, h,
-                                          w, c, up, int(relu), _stream()), "dei2i_spade_cls_bwd")
+                                          w, c, up, int(relu), out_pad, _stream()), "dei2i_spade_cls_bwd")
     return dgb5, dx
 
 

@@ -171,12 +171,15 @@ int dei2i_spade_bwd(const void* x, const void* gb, const void* out, const void* 
  * H-1).  gb5: bf16 [N,5,5,2C] = the same convolutions evaluated on a constant 5x5 map; pixel (h,w) uses entry
  * (cls(h), cls(w)).  Exact restructuring of normalization.py:24-37, H, W >= 5.
  * backward: dgb5 fp32 [N,5,5,2C] (class-wise sums of the per-pixel gamma/beta gradients, written), dx bf16;
- * scratch fp32 [N,2,C]. */
+ * scratch fp32 [N,2,C].
+ * out_pad > 0: `out` (and `dout` of the backward) is [N, H+2*out_pad, W+2*out_pad, C] and already carries the reflect
+ * padding of the convolution that consumes it (architecture.py:228-233,320-337 padding_mode='reflect'): the forward writes the
+ * mirrored border itself, the backward folds the padded gradient while reading it. */
 int dei2i_spade_cls_fwd(const void* x, const void* gb5, void* out, const float* stats, float* mean_rstd, int N, int H,
-                        int W, int C, int up, int relu, float eps, dei2i_stream stream);
+                        int W, int C, int up, int relu, float eps, int out_pad, dei2i_stream stream);
 int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* out, const void* dout, float* dgb5, void* dx,
                         const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, int relu,
-                        dei2i_stream stream);
+                        int out_pad, dei2i_stream stream);
 
 /* ---- StarGAN-v2 normalisation (stargan-v2/core/model.py) ----
  * out = lrelu_slope(IN(x) * scale[n,c] + shift[n,c]): AdaIN with scale = 1 + gamma(s), shift = beta(s) (model.py:73-84), or

@@ -423,6 +423,27 @@ def test_spade_cls_fwd_bwd(up, hx, wx, c):
     assert e_out < TOL_BF16 and e[0] < 2e-2 and max(e[1:]) < 5e-3, (e_out, e)
 
 
+@pytest.mark.parametrize("up,pad", [(1, 1), (2, 1), (1, 2)])
+def test_spade_cls_fused_reflect_pad(up, pad):
+    """out_pad: the class-map SPADE writes its consumer's reflect padding and folds the padded gradient - equal to the
+    unfused kernels followed by reflect_pad / preceded by reflect_fold."""
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(17)
+    n, c, hx, wx = 2, 64, 7, 9
+    h, w = hx * up, wx * up
+    xd = to_dev(q(torch.randn(n, c, hx, wx, generator=g) * 2 + 1))
+    gbd = to_dev(q(torch.randn(n, 2 * c, 5, 5, generator=g) * 0.5))
+    out0, mr = ops.spade_cls_fwd(xd, gbd, up)
+    outp, mrp = ops.spade_cls_fwd(xd, gbd, up, out_pad=pad)
+    assert torch.equal(outp, ops.reflect_pad(out0, pad)) and torch.equal(mr, mrp)
+    doutp = to_dev(q(torch.randn(n, c, h + 2 * pad, w + 2 * pad, generator=g)))
+    dgb_p, dx_p = ops.spade_cls_bwd(xd, gbd, outp, doutp, mr, up, out_pad=pad)
+    dgb_0, dx_0 = ops.spade_cls_bwd(xd, gbd, out0, ops.reflect_fold(doutp, pad), mr, up)
+    torch.cuda.synchronize()
+    # the unfused path rounds the folded gradient to BF16 once more
+    assert rel_err(dx_p.float(), dx_0.float()) < 1e-2 and rel_err(dgb_p, dgb_0) < 1e-2
+
+
 def test_spade_module_class_map_equals_dense():
     """SPADE module on a 1x1 label map: border-class path == dense path == the reference formula (normalization.py:24-37)."""
     from de_i2i_gan_b200.models.networks import normalization as nz

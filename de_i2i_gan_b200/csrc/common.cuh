@@ -193,6 +193,15 @@ DEVINL uint32_t pack_bf16(float a, float b) {
   __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
   return *reinterpret_cast<uint32_t*>(&h);
 }
+// 64-bit division by a run-time divisor costs ~100 instructions on the GPU - more than the whole per-element work of a streaming
+// kernel.  Element / pixel indices almost always fit 32 bits: take the 32-bit path then (the branch is warp-uniform).
+DEVINL long long fast_div(long long a, int b) {
+  return ((unsigned long long)a >> 32) == 0 ? (long long)((unsigned)a / (unsigned)b) : a / b;
+}
+DEVINL int fast_mod(long long a, int b) {
+  return ((unsigned long long)a >> 32) == 0 ? (int)((unsigned)a % (unsigned)b) : (int)(a % b);
+}
+
 DEVINL float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

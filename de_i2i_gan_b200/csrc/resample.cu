@@ -25,12 +25,12 @@ __global__ void upsample_pad_fwd_kernel(const uint4* __restrict__ x, uint4* __re
                                         int pt, int pl, int Ho, int Wo) {
   const long long total = (long long)N * Ho * Wo * C8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    long long t = i / C8;
-    const int wo = (int)(t % Wo);
-    t /= Wo;
-    const int ho = (int)(t % Ho);
-    const int n = (int)(t / Ho);
+    const int c8 = fast_mod(i, C8);
+    long long t = fast_div(i, C8);
+    const int wo = fast_mod(t, Wo);
+    t = fast_div(t, Wo);
+    const int ho = fast_mod(t, Ho);
+    const int n = (int)fast_div(t, Ho);
     const int hu = ho - pt, wu = wo - pl;
     uint4 v = make_uint4(0, 0, 0, 0);
     if (hu >= 0 && hu < H * up && wu >= 0 && wu < W * up) v = __ldg(x + (((long long)n * H + hu / up) * W + wu / up) * C8 + c8);
@@ -42,12 +42,12 @@ __global__ void upsample_pad_bwd_kernel(const uint4* __restrict__ dout, uint4* _
                                         int pt, int pl, int Ho, int Wo) {
   const long long total = (long long)N * H * W * C8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    long long t = i / C8;
-    const int w = (int)(t % W);
-    t /= W;
-    const int h = (int)(t % H);
-    const int n = (int)(t / H);
+    const int c8 = fast_mod(i, C8);
+    long long t = fast_div(i, C8);
+    const int w = fast_mod(t, W);
+    t = fast_div(t, W);
+    const int h = fast_mod(t, H);
+    const int n = (int)fast_div(t, H);
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (int dy = 0; dy < up; ++dy)
       for (int dxx = 0; dxx < up; ++dxx) {
@@ -66,12 +66,12 @@ __global__ void maxpool_fwd_kernel(const uint4* __restrict__ x, uint4* __restric
                                    int C8, int k, int s, int p, int Ho, int Wo) {
   const long long total = (long long)N * Ho * Wo * C8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    long long t = i / C8;
-    const int wo = (int)(t % Wo);
-    t /= Wo;
-    const int ho = (int)(t % Ho);
-    const int n = (int)(t / Ho);
+    const int c8 = fast_mod(i, C8);
+    long long t = fast_div(i, C8);
+    const int wo = fast_mod(t, Wo);
+    t = fast_div(t, Wo);
+    const int ho = fast_mod(t, Ho);
+    const int n = (int)fast_div(t, Ho);
     float best[8];
     unsigned bi[8];
 #pragma unroll
@@ -106,12 +106,12 @@ __global__ void maxpool_bwd_kernel(const uint4* __restrict__ dout, const uint2* 
                                    int W, int C8, int k, int s, int p, int Ho, int Wo) {
   const long long total = (long long)N * H * W * C8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    long long t = i / C8;
-    const int w = (int)(t % W);
-    t /= W;
-    const int h = (int)(t % H);
-    const int n = (int)(t / H);
+    const int c8 = fast_mod(i, C8);
+    long long t = fast_div(i, C8);
+    const int w = fast_mod(t, W);
+    t = fast_div(t, W);
+    const int h = fast_mod(t, H);
+    const int n = (int)fast_div(t, H);
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (int r = 0; r < k; ++r) {
       const int hn = h + p - r;
@@ -146,12 +146,12 @@ __global__ void avgpool_fwd_kernel(const uint4* __restrict__ x, uint4* __restric
   const long long total = (long long)N * Ho * Wo * C8;
   const float m = scale / (float)(k * k);
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    long long t = i / C8;
-    const int wo = (int)(t % Wo);
-    t /= Wo;
-    const int ho = (int)(t % Ho);
-    const int n = (int)(t / Ho);
+    const int c8 = fast_mod(i, C8);
+    long long t = fast_div(i, C8);
+    const int wo = fast_mod(t, Wo);
+    t = fast_div(t, Wo);
+    const int ho = fast_mod(t, Ho);
+    const int n = (int)fast_div(t, Ho);
     float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (int r = 0; r < k; ++r)
       for (int c = 0; c < k; ++c) {
@@ -170,12 +170,12 @@ __global__ void avgpool_bwd_kernel(const uint4* __restrict__ dout, uint4* __rest
   const long long total = (long long)N * H * W * C8;
   const float m = scale / (float)(k * k);
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    long long t = i / C8;
-    const int w = (int)(t % W);
-    t /= W;
-    const int h = (int)(t % H);
-    const int n = (int)(t / H);
+    const int c8 = fast_mod(i, C8);
+    long long t = fast_div(i, C8);
+    const int w = fast_mod(t, W);
+    t = fast_div(t, W);
+    const int h = fast_mod(t, H);
+    const int n = (int)fast_div(t, H);
     float f[8];
     unpack8(__ldg(dout + (((long long)n * Ho + h / k) * Wo + w / k) * C8 + c8), f);
 #pragma unroll
@@ -207,7 +207,7 @@ __global__ void gap_bwd_kernel(const float* __restrict__ dout, uint4* __restrict
   const long long total = (long long)N * HW * C8;
   const float m = 1.f / (float)HW;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
+    const int c8 = fast_mod(i, C8);
     const int n = (int)(i / ((long long)HW * C8));
     float f[8];
 #pragma unroll

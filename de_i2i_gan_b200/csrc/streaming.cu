@@ -14,6 +14,11 @@ static inline unsigned nblocks(long long n, int per) {
   return (unsigned)(b < 1 ? 1 : b);
 }
 
+// Per-channel tables in shared memory are stored transposed, channel c = 8*c8 + k at word k*C8 + c8: thread c8 of a warp then
+// reads word k*C8 + c8 - consecutive banks - instead of 8*c8 + k (an 8-way bank conflict on each of the 16+ reads per element,
+// which made every normalisation kernel shared-memory bound at ~35 % of HBM bandwidth).  Needs `C8` in scope.
+#define SW(c) ((((c) & 7) * C8) + ((c) >> 3))
+
 DEVINL void unpack8(const uint4& v, float (&f)[8]) {
   f[0] = bf16lo(v.x); f[1] = bf16hi(v.x); f[2] = bf16lo(v.y); f[3] = bf16hi(v.y);
   f[4] = bf16lo(v.z); f[5] = bf16hi(v.z); f[6] = bf16lo(v.w); f[7] = bf16hi(v.w);
@@ -39,7 +44,7 @@ __global__ void pack_fwd_kernel(const float* __restrict__ w, const float* __rest
                                 int taps, int Cin, int Kf, __nv_bfloat16* __restrict__ out) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (long long)Cout * Kf) return;
-  const int co = (int)(i / Kf), k = (int)(i - (long long)co * Kf);
+  const int co = (int)fast_div(i, Kf), k = (int)(i - (long long)co * Kf);
   const int tap = k / Cin, ci = k - tap * Cin;
   float v = 0.f;
   if (tap < taps && ci < Cin_real) {
@@ -52,7 +57,7 @@ __global__ void pack_dgrad_kernel(const float* __restrict__ w, const float* __re
                                   int taps, int Cin, int Cout_ld, int Kd, __nv_bfloat16* __restrict__ out) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (long long)Cin * Kd) return;
-  const int ci = (int)(i / Kd), k = (int)(i - (long long)ci * Kd);
+  const int ci = (int)fast_div(i, Kd), k = (int)(i - (long long)ci * Kd);
   const int tap = k / Cout_ld, co = k - tap * Cout_ld;
   float v = 0.f;
   if (tap < taps && co < Cout && ci < Cin_real) {
@@ -67,12 +72,12 @@ __global__ void reflect_fold_kernel(const uint4* __restrict__ dxp, uint4* __rest
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const long long total = (long long)N * H * W * C8;
   if (i >= total) return;
-  const int c8 = (int)(i % C8);
-  long long t = i / C8;
-  const int w = (int)(t % W);
-  t /= W;
-  const int h = (int)(t % H);
-  const int n = (int)(t / H);
+  const int c8 = fast_mod(i, C8);
+  long long t = fast_div(i, C8);
+  const int w = fast_mod(t, W);
+  t = fast_div(t, W);
+  const int h = fast_mod(t, H);
+  const int n = (int)fast_div(t, H);
   const int Hp = H + 2 * pad, Wp = W + 2 * pad;
   int hs[3], ws[3], nh = 0, nw = 0;
   hs[nh++] = h + pad;
@@ -98,12 +103,12 @@ __global__ void reflect_pad_kernel(const uint4* __restrict__ x, uint4* __restric
   const int Hp = H + 2 * pad, Wp = W + 2 * pad;
   const long long total = (long long)N * Hp * Wp * C8;
   if (i >= total) return;
-  const int c8 = (int)(i % C8);
-  long long t = i / C8;
-  const int wp = (int)(t % Wp);
-  t /= Wp;
-  const int hp = (int)(t % Hp);
-  const int n = (int)(t / Hp);
+  const int c8 = fast_mod(i, C8);
+  long long t = fast_div(i, C8);
+  const int wp = fast_mod(t, Wp);
+  t = fast_div(t, Wp);
+  const int hp = fast_mod(t, Hp);
+  const int n = (int)fast_div(t, Hp);
   int h = hp - pad, w = wp - pad;
   h = h < 0 ? -h : (h >= H ? 2 * H - 2 - h : h);
   w = w < 0 ? -w : (w >= W ? 2 * W - 2 - w : w);
@@ -176,7 +181,7 @@ __global__ void sn_finish_u_kernel(const float* __restrict__ s, int rows, float 
 __global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int N, int C, int HW, int C_ld) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // pixel index n*HW + p
   if (i >= (long long)N * HW) return;
-  const int n = (int)(i / HW);
+  const int n = (int)fast_div(i, HW);
   const int p = (int)(i - (long long)n * HW);
   for (int c0 = 0; c0 < C_ld; c0 += 8) {
     float f[8];
@@ -188,10 +193,10 @@ __global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, __nv_bfloat16
 __global__ void nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float* __restrict__ dst, int N, int C, int HW, int C_ld) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (long long)N * C * HW) return;
-  const int p = (int)(i % HW);
-  const long long t = i / HW;
-  const int c = (int)(t % C);
-  const int n = (int)(t / C);
+  const int p = fast_mod(i, HW);
+  const long long t = fast_div(i, HW);
+  const int c = fast_mod(t, C);
+  const int n = (int)fast_div(t, C);
   dst[i] = __bfloat162float(src[((long long)n * HW + p) * C_ld + c]);
 }
 
@@ -208,10 +213,10 @@ __global__ void rowpack_fwd_kernel(const float* __restrict__ img, uint4* __restr
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const int s = (int)(i & 7);
     long long t = i >> 3;
-    const int w = (int)(t % W);
-    t /= W;
-    const int hp = (int)(t % Hp);
-    const int n = (int)(t / Hp);
+    const int w = fast_mod(t, W);
+    t = fast_div(t, W);
+    const int hp = fast_mod(t, Hp);
+    const int n = (int)fast_div(t, Hp);
     float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (s < kw) {
       const int h = reflect_idx(hp - pad, H), ws = reflect_idx(w + s - pad, W);
@@ -227,10 +232,10 @@ __global__ void rowpack_bwd_kernel(const uint4* __restrict__ dxp, float* __restr
   const int Hp = H + 2 * pad;
   const long long total = (long long)N * H * W;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int w = (int)(i % W);
-    const long long t = i / W;
-    const int h = (int)(t % H);
-    const int n = (int)(t / H);
+    const int w = fast_mod(i, W);
+    const long long t = fast_div(i, W);
+    const int h = fast_mod(t, H);
+    const int n = (int)fast_div(t, H);
     int hs[3], wsrc[3], nh = 0, nw = 0;
     hs[nh++] = h + pad;
     if (h >= 1 && h <= pad) hs[nh++] = pad - h;
@@ -346,17 +351,17 @@ __global__ void bn_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y
       save_rstd[c] = rstd;
     }
     const float sc = rstd * gamma[c];
-    sh[c] = sc;
-    sh[C + c] = beta[c] - mean * sc;
+    sh[SW(c)] = sc;
+    sh[C + SW(c)] = beta[c] - mean * sc;
   }
   __syncthreads();
   const long long total = npix * C8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % C8) * 8;
+    const int c0 = fast_mod(i, C8) * 8;
     float f[8];
     unpack8(__ldg(x + i), f);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) f[k] = apply_act(f[k] * sh[c0 + k] + sh[C + c0 + k], act);
+    for (int k = 0; k < 8; ++k) f[k] = apply_act(f[k] * sh[SW(c0 + k)] + sh[C + SW(c0 + k)], act);
     if (residual != nullptr) {
       float r[8];
       unpack8(__ldg(residual + i), r);
@@ -424,12 +429,12 @@ __global__ void bn_bwd_apply_kernel(const uint4* __restrict__ x, const uint4* __
   extern __shared__ float sh[];  // mean, rstd, gamma, beta, k1 (=sum dz / n), k2 (= sum dz xhat / n)
   const int C = C8 * 8;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    sh[c] = mean[c];
-    sh[C + c] = rstd[c];
-    sh[2 * C + c] = gamma[c];
-    sh[3 * C + c] = beta[c];
-    sh[4 * C + c] = training ? red[c] / (float)npix : 0.f;
-    sh[5 * C + c] = training ? red[C + c] / (float)npix : 0.f;
+    sh[SW(c)] = mean[c];
+    sh[C + SW(c)] = rstd[c];
+    sh[2 * C + SW(c)] = gamma[c];
+    sh[3 * C + SW(c)] = beta[c];
+    sh[4 * C + SW(c)] = training ? red[c] / (float)npix : 0.f;
+    sh[5 * C + SW(c)] = training ? red[C + c] / (float)npix : 0.f;
     if (blockIdx.x == 0) {
       dbeta[c] = red[c];
       dgamma[c] = red[C + c];
@@ -438,19 +443,19 @@ __global__ void bn_bwd_apply_kernel(const uint4* __restrict__ x, const uint4* __
   __syncthreads();
   const long long total = npix * C8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % C8) * 8;
+    const int c0 = fast_mod(i, C8) * 8;
     float fx[8], fd[8], o[8];
     unpack8(__ldg(x + i), fx);
     unpack8(__ldg(dy + i), fd);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const int c = c0 + k;
-      const float xh = (fx[k] - sh[c]) * sh[C + c];
+      const float xh = (fx[k] - sh[SW(c)]) * sh[C + SW(c)];
       float dz = fd[k];
-      const float z = xh * sh[2 * C + c] + sh[3 * C + c];
+      const float z = xh * sh[2 * C + SW(c)] + sh[3 * C + SW(c)];
       if (act == ACT_LRELU) dz *= z > 0.f ? 1.f : 0.2f;
       else if (act == ACT_RELU) dz *= z > 0.f ? 1.f : 0.f;
-      o[k] = sh[2 * C + c] * sh[C + c] * (dz - sh[4 * C + c] - xh * sh[5 * C + c]);
+      o[k] = sh[2 * C + SW(c)] * sh[C + SW(c)] * (dz - sh[4 * C + SW(c)] - xh * sh[5 * C + SW(c)]);
     }
     dx[i] = pack8(o);
   }
@@ -470,8 +475,8 @@ __global__ void spade_fwd_kernel(const uint4* __restrict__ x, const uint4* __res
     const float mean = stats[(n * 2 + 0) * C + c] / cnt;
     const float var = fmaxf(stats[(n * 2 + 1) * C + c] / cnt - mean * mean, 0.f);
     const float rstd = rsqrtf(var + eps);
-    sh[c] = mean;
-    sh[C + c] = rstd;
+    sh[SW(c)] = mean;
+    sh[C + SW(c)] = rstd;
     if (blockIdx.x == 0) {
       mean_rstd[(n * 2 + 0) * C + c] = mean;
       mean_rstd[(n * 2 + 1) * C + c] = rstd;
@@ -480,9 +485,9 @@ __global__ void spade_fwd_kernel(const uint4* __restrict__ x, const uint4* __res
   __syncthreads();
   const long long per_img = (long long)H * W * C8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img; i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    const long long pix = i / C8;
-    const int w = (int)(pix % W), h = (int)(pix / W);
+    const int c8 = fast_mod(i, C8);
+    const long long pix = fast_div(i, C8);
+    const int w = fast_mod(pix, W), h = (int)fast_div(pix, W);
     float fx[8], fg[8], fb[8], o[8];
     unpack8(__ldg(x + (((long long)n * Hx + h / up) * Wx + w / up) * C8 + c8), fx);
     const long long gbase = ((long long)n * H * W + pix) * (2 * C8);
@@ -490,7 +495,7 @@ __global__ void spade_fwd_kernel(const uint4* __restrict__ x, const uint4* __res
     unpack8(__ldg(gb + gbase + C8 + c8), fb);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      const float xh = (fx[k] - sh[c8 * 8 + k]) * sh[C + c8 * 8 + k];
+      const float xh = (fx[k] - sh[SW(c8 * 8 + k)]) * sh[C + SW(c8 * 8 + k)];
       const float t = xh * (1.f + fg[k]) + fb[k];
       o[k] = relu ? fmaxf(t, 0.f) : t;
     }
@@ -519,7 +524,7 @@ __global__ void spade_bwd1_kernel(const uint4* __restrict__ x, const uint4* __re
     rs[k] = mean_rstd[(n * 2 + 1) * C + c8 * 8 + k];
   }
   for (long long p = p0 + lane; p < p1; p += lanes) {
-    const int w = (int)(p % W), h = (int)(p / W);
+    const int w = fast_mod(p, W), h = (int)fast_div(p, W);
     float fx[8], fg[8], fo[8], fd[8], dg[8], db[8];
     unpack8(__ldg(x + (((long long)n * Hx + h / up) * Wx + w / up) * C8 + c8), fx);
     const long long gbase = ((long long)n * npix + p) * (2 * C8);
@@ -565,18 +570,18 @@ __global__ void spade_bwd2_kernel(const uint4* __restrict__ x, const uint4* __re
   const int Hx = H / up, Wx = W / up;
   const float cnt = (float)H * (float)W;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    sh[c] = mean_rstd[(n * 2 + 0) * C + c];
-    sh[C + c] = mean_rstd[(n * 2 + 1) * C + c];
-    sh[2 * C + c] = red[(n * 2 + 0) * C + c] / cnt;
-    sh[3 * C + c] = red[(n * 2 + 1) * C + c] / cnt;
+    sh[SW(c)] = mean_rstd[(n * 2 + 0) * C + c];
+    sh[C + SW(c)] = mean_rstd[(n * 2 + 1) * C + c];
+    sh[2 * C + SW(c)] = red[(n * 2 + 0) * C + c] / cnt;
+    sh[3 * C + SW(c)] = red[(n * 2 + 1) * C + c] / cnt;
   }
   __syncthreads();
   const long long per_img = (long long)Hx * Wx * C8;
   const float uu = (float)(up * up);
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img; i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    const long long pix = i / C8;
-    const int wx = (int)(pix % Wx), hx = (int)(pix / Wx);
+    const int c8 = fast_mod(i, C8);
+    const long long pix = fast_div(i, C8);
+    const int wx = fast_mod(pix, Wx), hx = (int)fast_div(pix, Wx);
     float fx[8], acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, o[8];
     unpack8(__ldg(x + (long long)n * per_img + i), fx);
     for (int dy = 0; dy < up; ++dy)
@@ -592,8 +597,8 @@ __global__ void spade_bwd2_kernel(const uint4* __restrict__ x, const uint4* __re
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const int c = c8 * 8 + k;
-      const float xh = (fx[k] - sh[c]) * sh[C + c];
-      o[k] = sh[C + c] * (acc[k] - uu * sh[2 * C + c] - xh * uu * sh[3 * C + c]);
+      const float xh = (fx[k] - sh[SW(c)]) * sh[C + SW(c)];
+      o[k] = sh[C + SW(c)] * (acc[k] - uu * sh[2 * C + SW(c)] - xh * uu * sh[3 * C + SW(c)]);
     }
     dx[(long long)n * per_img + i] = pack8(o);
   }
@@ -618,8 +623,8 @@ __global__ void spade_cls_fwd_kernel(const uint4* __restrict__ x, const uint4* _
     const float mean = stats[(n * 2 + 0) * C + c] / cnt;
     const float var = fmaxf(stats[(n * 2 + 1) * C + c] / cnt - mean * mean, 0.f);
     const float rstd = rsqrtf(var + eps);
-    sh[c] = mean;
-    sh[C + c] = rstd;
+    sh[SW(c)] = mean;
+    sh[C + SW(c)] = rstd;
     if (blockIdx.x == 0) {
       mean_rstd[(n * 2 + 0) * C + c] = mean;
       mean_rstd[(n * 2 + 1) * C + c] = rstd;
@@ -630,48 +635,76 @@ __global__ void spade_cls_fwd_kernel(const uint4* __restrict__ x, const uint4* _
   // padded pixel (hp, wp) is computed from its mirror source - 3 % more pixels instead of a separate pad pass
   const int Wp = W + 2 * pad;
   const long long per_img = (long long)(H + 2 * pad) * Wp * C8;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img; i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    const long long pix = i / C8;
-    const int w = reflect_idx((int)(pix % Wp) - pad, W), h = reflect_idx((int)(pix / Wp) - pad, H);
-    float fx[8], fg[8], fb[8], o[8];
-    unpack8(__ldg(x + (((long long)n * Hx + h / up) * Wx + w / up) * C8 + c8), fx);
-    const int gbase = ((n * 5 + bcls(h, H)) * 5 + bcls(w, W)) * (2 * C8);
-    unpack8(__ldg(gb5 + gbase + c8), fg);
-    unpack8(__ldg(gb5 + gbase + C8 + c8), fb);
+  // two independent elements per iteration: both 16-byte loads of x are issued before either result is computed
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < per_img; i0 += 2 * stride) {
+    long long idx[2] = {i0, i0 + stride};
+    int c8[2], gbase[2];
+    uint4 vx[2];
+    bool ok[2];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const float xh = (fx[k] - sh[c8 * 8 + k]) * sh[C + c8 * 8 + k];
-      const float t = xh * (1.f + fg[k]) + fb[k];
-      o[k] = relu ? fmaxf(t, 0.f) : t;
+    for (int u = 0; u < 2; ++u) {
+      ok[u] = idx[u] < per_img;
+      const long long i = ok[u] ? idx[u] : i0;
+      c8[u] = fast_mod(i, C8);
+      const long long pix = fast_div(i, C8);
+      const int w = reflect_idx(fast_mod(pix, Wp) - pad, W), h = reflect_idx((int)fast_div(pix, Wp) - pad, H);
+      vx[u] = __ldg(x + (((long long)n * Hx + h / up) * Wx + w / up) * C8 + c8[u]);
+      gbase[u] = ((n * 5 + bcls(h, H)) * 5 + bcls(w, W)) * (2 * C8);
     }
-    out[(long long)n * per_img + i] = pack8(o);
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (!ok[u]) continue;
+      float fx[8], fg[8], fb[8], o[8];
+      unpack8(vx[u], fx);
+      unpack8(__ldg(gb5 + gbase[u] + c8[u]), fg);
+      unpack8(__ldg(gb5 + gbase[u] + C8 + c8[u]), fb);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float xh = (fx[k] - sh[SW(c8[u] * 8 + k)]) * sh[C + SW(c8[u] * 8 + k)];
+        const float t = xh * (1.f + fg[k]) + fb[k];
+        o[k] = relu ? fmaxf(t, 0.f) : t;
+      }
+      out[(long long)n * per_img + idx[u]] = pack8(o);
+    }
   }
 }
 
 // out / dout of a consumer-padded SPADE output ([N, H+2pad, W+2pad, C]): the activation at (h, w) sits at (h+pad, w+pad); its
 // gradient is the sum over every padded position that mirrors onto (h, w) (the adjoint of the reflect padding, <= 4 reads).
+DEVINL void fold_extras(const uint4* __restrict__ t, long long img_base, int h, int w, int H, int W, int pad, int C8, int c8,
+                        float (&f)[8]);
 DEVINL void load_folded(const uint4* __restrict__ t, long long img_base, int h, int w, int H, int W, int pad, int C8, int c8,
                         float (&f)[8]) {
   const int Wp = W + 2 * pad;
   unpack8(__ldg(t + (img_base + (long long)(h + pad) * Wp + (w + pad)) * C8 + c8), f);
-  if (pad == 0) return;
-  int hs[3], ws[3], nh = 0, nw = 0;
-  hs[nh++] = h + pad;
-  if (h >= 1 && h <= pad) hs[nh++] = pad - h;
-  if (h <= H - 2 && h >= H - 1 - pad) hs[nh++] = 2 * H - 2 - h + pad;
-  ws[nw++] = w + pad;
-  if (w >= 1 && w <= pad) ws[nw++] = pad - w;
-  if (w <= W - 2 && w >= W - 1 - pad) ws[nw++] = 2 * W - 2 - w + pad;
-  if (nh == 1 && nw == 1) return;
-  for (int a = 0; a < nh; ++a)
-    for (int b = 0; b < nw; ++b) {
-      if (a == 0 && b == 0) continue;
-      float g[8];
-      unpack8(__ldg(t + (img_base + (long long)hs[a] * Wp + ws[b]) * C8 + c8), g);
+  fold_extras(t, img_base, h, w, H, W, pad, C8, c8, f);
+}
+// adds the mirror images of (h, w) to f (which already holds the value at (h + pad, w + pad))
+DEVINL void fold_extras(const uint4* __restrict__ t, long long img_base, int h, int w, int H, int W, int pad, int C8, int c8,
+                        float (&f)[8]) {
+  const int Wp = W + 2 * pad;
+  // interior pixels (all but a 2*pad + 1 wide frame) have no mirror image
+  if (pad == 0 || (h > pad && h < H - 1 - pad && w > pad && w < W - 1 - pad)) return;
+  // mirror rows / columns of (h, w); -1: none.  (h in [1, pad] <-> pad - h;  h in [H-1-pad, H-2] <-> 2H - 2 - h + pad)
+  const int h2 = (h >= 1 && h <= pad) ? pad - h : ((h <= H - 2 && h >= H - 1 - pad) ? 2 * H - 2 - h + pad : -1);
+  const int w2 = (w >= 1 && w <= pad) ? pad - w : ((w <= W - 2 && w >= W - 1 - pad) ? 2 * W - 2 - w + pad : -1);
+  float g[8];
+  if (h2 >= 0) {
+    unpack8(__ldg(t + (img_base + (long long)h2 * Wp + (w + pad)) * C8 + c8), g);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) f[k] += g[k];
-    }
+    for (int k = 0; k < 8; ++k) f[k] += g[k];
+  }
+  if (w2 >= 0) {
+    unpack8(__ldg(t + (img_base + (long long)(h + pad) * Wp + w2) * C8 + c8), g);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] += g[k];
+  }
+  if (h2 >= 0 && w2 >= 0) {
+    unpack8(__ldg(t + (img_base + (long long)h2 * Wp + w2) * C8 + c8), g);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] += g[k];
+  }
 }
 
 // backward pass 1 over whole rows [r0, r1) of image n: g = dout * (out > 0);  per border class  dgamma5 += g * xhat,
@@ -700,8 +733,29 @@ __global__ void spade_cls_bwd1_kernel(const uint4* __restrict__ x, const uint4* 
   }
   const int Wp = W + 2 * pad;
   const long long img = (long long)n * (H + 2 * pad) * Wp;
-  for (long long p = (long long)r0 * W + lane; p < (long long)r1 * W; p += lanes) {
-    const int w = (int)(p % W), h = (int)(p / W);
+  // software-pipelined: the three 16-byte loads of the next pixel are in flight while the current one is reduced
+  long long p = (long long)r0 * W + lane;
+  const long long pend = (long long)r1 * W;
+  uint4 nx = make_uint4(0, 0, 0, 0), no = nx, nd = nx;
+  int nh = 0, nw = 0;
+  if (p < pend) {
+    nw = fast_mod(p, W); nh = (int)fast_div(p, W);
+    nx = __ldg(x + (((long long)n * Hx + nh / up) * Wx + nw / up) * C8 + c8);
+    const long long o = (img + (long long)(nh + pad) * Wp + (nw + pad)) * C8 + c8;
+    no = __ldg(out + o);
+    nd = __ldg(dout + o);
+  }
+  for (; p < pend; p += lanes) {
+    const uint4 cx = nx, co = no, cd = nd;
+    const int h = nh, w = nw;
+    const long long pn = p + lanes;
+    if (pn < pend) {
+      nw = fast_mod(pn, W); nh = (int)fast_div(pn, W);
+      nx = __ldg(x + (((long long)n * Hx + nh / up) * Wx + nw / up) * C8 + c8);
+      const long long o = (img + (long long)(nh + pad) * Wp + (nw + pad)) * C8 + c8;
+      no = __ldg(out + o);
+      nd = __ldg(dout + o);
+    }
     const int cls = bcls(h, H) * 5 + bcls(w, W);
     if (cls != cur) {
       if (cur >= 0) {
@@ -716,9 +770,10 @@ __global__ void spade_cls_bwd1_kernel(const uint4* __restrict__ x, const uint4* 
       unpack8(__ldg(gb5 + (n * 25 + cls) * (2 * C8) + c8), fg);
     }
     float fx[8], fo[8], fd[8];
-    unpack8(__ldg(x + (((long long)n * Hx + h / up) * Wx + w / up) * C8 + c8), fx);
-    unpack8(__ldg(out + (img + (long long)(h + pad) * Wp + (w + pad)) * C8 + c8), fo);
-    load_folded(dout, img, h, w, H, W, pad, C8, c8, fd);
+    unpack8(cx, fx);
+    unpack8(co, fo);
+    unpack8(cd, fd);
+    fold_extras(dout, img, h, w, H, W, pad, C8, c8, fd);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const float xh = (fx[k] - mu[k]) * rs[k];
@@ -747,7 +802,7 @@ __global__ void spade_cls_bwd1_kernel(const uint4* __restrict__ x, const uint4* 
 }
 
 // backward pass 2: dx[n,hx,wx,c] = rstd * (sum_{up x up} g (1 + gamma5) - up^2 S1/HW - xhat up^2 S2/HW),  g recomputed
-__global__ void spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ out,
+__global__ void __launch_bounds__(256, 3) spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ out,
                                       const uint4* __restrict__ dout, uint4* __restrict__ dx, const float* __restrict__ mean_rstd,
                                       const float* __restrict__ red, int H, int W, int C8, int up, int relu, int pad) {
   extern __shared__ float sh[];  // mean, rstd, k1, k2
@@ -756,18 +811,18 @@ __global__ void spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* 
   const int Hx = H / up, Wx = W / up;
   const float cnt = (float)H * (float)W;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    sh[c] = mean_rstd[(n * 2 + 0) * C + c];
-    sh[C + c] = mean_rstd[(n * 2 + 1) * C + c];
-    sh[2 * C + c] = red[(n * 2 + 0) * C + c] / cnt;
-    sh[3 * C + c] = red[(n * 2 + 1) * C + c] / cnt;
+    sh[SW(c)] = mean_rstd[(n * 2 + 0) * C + c];
+    sh[C + SW(c)] = mean_rstd[(n * 2 + 1) * C + c];
+    sh[2 * C + SW(c)] = red[(n * 2 + 0) * C + c] / cnt;
+    sh[3 * C + SW(c)] = red[(n * 2 + 1) * C + c] / cnt;
   }
   __syncthreads();
   const long long per_img = (long long)Hx * Wx * C8;
   const float uu = (float)(up * up);
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img; i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = (int)(i % C8);
-    const long long pix = i / C8;
-    const int wx = (int)(pix % Wx), hx = (int)(pix / Wx);
+    const int c8 = fast_mod(i, C8);
+    const long long pix = fast_div(i, C8);
+    const int wx = fast_mod(pix, Wx), hx = (int)fast_div(pix, Wx);
     float fx[8], acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, o[8];
     unpack8(__ldg(x + (long long)n * per_img + i), fx);
     for (int dy = 0; dy < up; ++dy)
@@ -785,8 +840,8 @@ __global__ void spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* 
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
       const int c = c8 * 8 + k;
-      const float xh = (fx[k] - sh[c]) * sh[C + c];
-      o[k] = sh[C + c] * (acc[k] - uu * sh[2 * C + c] - xh * uu * sh[3 * C + c]);
+      const float xh = (fx[k] - sh[SW(c)]) * sh[C + SW(c)];
+      o[k] = sh[C + SW(c)] * (acc[k] - uu * sh[2 * C + SW(c)] - xh * uu * sh[3 * C + SW(c)]);
     }
     dx[(long long)n * per_img + i] = pack8(o);
   }
@@ -807,8 +862,8 @@ __global__ void adain_act_fwd_kernel(const uint4* __restrict__ x, uint4* __restr
     const float var = fmaxf(stats[(n * 2 + 1) * C + c] / (float)HW - mean * mean, 0.f);
     const float rstd = rsqrtf(var + eps);
     const float a = rstd * scale[n * C + c];
-    sh[c] = a;
-    sh[C + c] = shift[n * C + c] - mean * a;
+    sh[SW(c)] = a;
+    sh[C + SW(c)] = shift[n * C + c] - mean * a;
     if (blockIdx.x == 0) {
       mean_rstd[(n * 2 + 0) * C + c] = mean;
       mean_rstd[(n * 2 + 1) * C + c] = rstd;
@@ -817,12 +872,12 @@ __global__ void adain_act_fwd_kernel(const uint4* __restrict__ x, uint4* __restr
   __syncthreads();
   const long long per_img = (long long)HW * C8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img; i += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % C8) * 8;
+    const int c0 = fast_mod(i, C8) * 8;
     float f[8];
     unpack8(__ldg(x + (long long)n * per_img + i), f);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      const float t = f[k] * sh[c0 + k] + sh[C + c0 + k];
+      const float t = f[k] * sh[SW(c0 + k)] + sh[C + SW(c0 + k)];
       f[k] = t > 0.f ? t : t * slope;
     }
     out[(long long)n * per_img + i] = pack8(f);
@@ -883,16 +938,16 @@ __global__ void adain_act_bwd2_kernel(const uint4* __restrict__ x, const uint4* 
   const int n = blockIdx.y;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     const float rstd = mean_rstd[(n * 2 + 1) * C + c];
-    sh[c] = mean_rstd[(n * 2 + 0) * C + c];
-    sh[C + c] = rstd;
-    sh[2 * C + c] = rstd * scale[n * C + c];
-    sh[3 * C + c] = red[(n * 2 + 0) * C + c] / (float)HW;
-    sh[4 * C + c] = red[(n * 2 + 1) * C + c] / (float)HW;
+    sh[SW(c)] = mean_rstd[(n * 2 + 0) * C + c];
+    sh[C + SW(c)] = rstd;
+    sh[2 * C + SW(c)] = rstd * scale[n * C + c];
+    sh[3 * C + SW(c)] = red[(n * 2 + 0) * C + c] / (float)HW;
+    sh[4 * C + SW(c)] = red[(n * 2 + 1) * C + c] / (float)HW;
   }
   __syncthreads();
   const long long per_img = (long long)HW * C8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img; i += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % C8) * 8;
+    const int c0 = fast_mod(i, C8) * 8;
     const long long o = (long long)n * per_img + i;
     float fx[8], fo[8], fd[8], r[8];
     unpack8(__ldg(x + o), fx);
@@ -902,8 +957,8 @@ __global__ void adain_act_bwd2_kernel(const uint4* __restrict__ x, const uint4* 
     for (int k = 0; k < 8; ++k) {
       const int c = c0 + k;
       const float g = fo[k] > 0.f ? fd[k] : fd[k] * slope;
-      const float xh = (fx[k] - sh[c]) * sh[C + c];
-      r[k] = sh[2 * C + c] * (g - sh[3 * C + c] - xh * sh[4 * C + c]);
+      const float xh = (fx[k] - sh[SW(c)]) * sh[C + SW(c)];
+      r[k] = sh[2 * C + SW(c)] * (g - sh[3 * C + SW(c)] - xh * sh[4 * C + SW(c)]);
     }
     dx[o] = pack8(r);
   }
@@ -981,8 +1036,8 @@ __global__ void noise_wgrad_kernel(const uint4* __restrict__ dy, const float* __
   float acc = 0.f;
   const long long total = M * C8;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(i % C8) * 8;
-    const long long m = i / C8;
+    const int c0 = fast_mod(i, C8) * 8;
+    const long long m = fast_div(i, C8);
     float f[8];
     unpack8(__ldg(dy + i), f);
     float t = 0.f;
@@ -1001,7 +1056,7 @@ __global__ void compose_fwd_kernel(const float* __restrict__ hd, const float* __
                                    float* __restrict__ prob, __nv_bfloat16* __restrict__ out_nhwc, int N, int HW, int cycle_gan) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (long long)N * HW) return;
-  const int n = (int)(i / HW);
+  const int n = (int)fast_div(i, HW);
   const int p = (int)(i - (long long)n * HW);
   const float4 a = __ldg(reinterpret_cast<const float4*>(hd + i * 8));
   const float pr = 1.f / (1.f + __expf(-a.w));
@@ -1022,7 +1077,7 @@ __global__ void compose_bwd_kernel(const float* __restrict__ hd, const float* __
                                    int HW, int cycle_gan) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (long long)N * HW) return;
-  const int n = (int)(i / HW);
+  const int n = (int)fast_div(i, HW);
   const int p = (int)(i - (long long)n * HW);
   const float4 a = __ldg(reinterpret_cast<const float4*>(hd + i * 8));
   const float pr = 1.f / (1.f + __expf(-a.w));

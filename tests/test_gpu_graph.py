@@ -98,4 +98,8 @@ def test_graphed_inference_matches_eager(tmp_path, monkeypatch):
             out_e, prob_e = model("inference", xs[2], lab)
     finally:
         A.set_noise_source(None)
-    assert torch.allclose(out_g, out_e, atol=1e-6) and torch.allclose(prob_g, prob_e, atol=1e-6)
+    # not bit-equal: the per-channel statistics are reduced with FP32 atomics, whose order differs from launch to launch; one
+    # flipped BF16 rounding then travels through the remaining layers (eager vs eager differs by up to 1e-2 as well, while a
+    # replay with stale weights or inputs is off by > 1e-1: tools/debug_graph_inf.py)
+    assert (out_g - out_e).abs().max().item() < 3e-2 and (prob_g - prob_e).abs().max().item() < 3e-2
+    assert (out_g - out_e).abs().mean().item() < 2e-3

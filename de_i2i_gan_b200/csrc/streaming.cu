@@ -611,61 +611,72 @@ __global__ void spade_bwd2_kernel(const uint4* __restrict__ x, const uint4* __re
 // (bcls(h,H), bcls(w,W)).  Exact (not an approximation); the dense kernels above remain for spatial label maps.
 DEVINL int bcls(int i, int n) { return i < 2 ? i : (i >= n - 2 ? i - n + 5 : 2); }
 
+// Thread = (8-channel group c8 = tid % C8, pixel lane): the per-channel constants live in registers, the pixel index advances
+// incrementally (no division in the loop) and gamma|beta are re-read only when the border class changes.  (The first version
+// - flat element index, constants in shared memory - was instruction-issue bound at 78 % issue-active and 20 % of HBM bandwidth:
+// ~340 instructions per 16-byte element, profiles/r01f_ncu_full_spade.txt.)
 __global__ void spade_cls_fwd_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, uint4* __restrict__ out,
                                      const float* __restrict__ stats, float* __restrict__ mean_rstd, int N, int H, int W, int C8,
                                      int up, int relu, float eps, int pad) {
-  extern __shared__ float sh[];  // mean[C], rstd[C]
   const int C = C8 * 8;
   const int n = blockIdx.y;
+  const int c8 = threadIdx.x % C8;
+  const int lane = threadIdx.x / C8;
+  const int lanes = blockDim.x / C8;
   const int Hx = H / up, Wx = W / up;
   const float cnt = (float)Hx * (float)Wx;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+  float a[8], b[8];  // xhat = x * a + b
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = c8 * 8 + k;
     const float mean = stats[(n * 2 + 0) * C + c] / cnt;
     const float var = fmaxf(stats[(n * 2 + 1) * C + c] / cnt - mean * mean, 0.f);
     const float rstd = rsqrtf(var + eps);
-    sh[SW(c)] = mean;
-    sh[C + SW(c)] = rstd;
-    if (blockIdx.x == 0) {
+    a[k] = rstd;
+    b[k] = -mean * rstd;
+    if (blockIdx.x == 0 && lane == 0) {
       mean_rstd[(n * 2 + 0) * C + c] = mean;
       mean_rstd[(n * 2 + 1) * C + c] = rstd;
     }
   }
-  __syncthreads();
   // pad > 0: the output carries the reflect padding of the convolution that consumes it (out is [N, H+2pad, W+2pad, C]):
   // padded pixel (hp, wp) is computed from its mirror source - 3 % more pixels instead of a separate pad pass
-  const int Wp = W + 2 * pad;
-  const long long per_img = (long long)(H + 2 * pad) * Wp * C8;
-  // two independent elements per iteration: both 16-byte loads of x are issued before either result is computed
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < per_img; i0 += 2 * stride) {
-    long long idx[2] = {i0, i0 + stride};
-    int c8[2], gbase[2];
-    uint4 vx[2];
-    bool ok[2];
+  const int Hp = H + 2 * pad, Wp = W + 2 * pad;
+  const int npix = Hp * Wp;
+  const int stride = gridDim.x * lanes;
+  const int sh_ = stride / Wp, sw_ = stride - sh_ * Wp;
+  int pix = blockIdx.x * lanes + lane;
+  int hp = pix / Wp, wp = pix - hp * Wp;
+  float g1[8], be[8];  // 1 + gamma, beta of the current border class
+  int cur = -1;
+  const uint4* xin = x + (long long)n * Hx * Wx * C8 + c8;
+  uint4* o = out + (long long)n * npix * C8 + c8;
+  const uint4* gbn = gb5 + n * 25 * 2 * C8 + c8;
+  for (; pix < npix; pix += stride) {
+    const int h = reflect_idx(hp - pad, H), w = reflect_idx(wp - pad, W);
+    const uint4 vx = __ldg(xin + ((up == 2 ? (h >> 1) : h / up) * Wx + (up == 2 ? (w >> 1) : w / up)) * C8);
+    const int cls = bcls(h, H) * 5 + bcls(w, W);
+    if (cls != cur) {
+      cur = cls;
+      float t[8];
+      unpack8(__ldg(gbn + cls * 2 * C8), t);
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      ok[u] = idx[u] < per_img;
-      const long long i = ok[u] ? idx[u] : i0;
-      c8[u] = fast_mod(i, C8);
-      const long long pix = fast_div(i, C8);
-      const int w = reflect_idx(fast_mod(pix, Wp) - pad, W), h = reflect_idx((int)fast_div(pix, Wp) - pad, H);
-      vx[u] = __ldg(x + (((long long)n * Hx + h / up) * Wx + w / up) * C8 + c8[u]);
-      gbase[u] = ((n * 5 + bcls(h, H)) * 5 + bcls(w, W)) * (2 * C8);
+      for (int k = 0; k < 8; ++k) g1[k] = 1.f + t[k];
+      unpack8(__ldg(gbn + cls * 2 * C8 + C8), be);
     }
+    float f[8];
+    unpack8(vx, f);
 #pragma unroll
-    for (int u = 0; u < 2; ++u) {
-      if (!ok[u]) continue;
-      float fx[8], fg[8], fb[8], o[8];
-      unpack8(vx[u], fx);
-      unpack8(__ldg(gb5 + gbase[u] + c8[u]), fg);
-      unpack8(__ldg(gb5 + gbase[u] + C8 + c8[u]), fb);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const float xh = (fx[k] - sh[SW(c8[u] * 8 + k)]) * sh[C + SW(c8[u] * 8 + k)];
-        const float t = xh * (1.f + fg[k]) + fb[k];
-        o[k] = relu ? fmaxf(t, 0.f) : t;
-      }
-      out[(long long)n * per_img + idx[u]] = pack8(o);
+    for (int k = 0; k < 8; ++k) {
+      const float t = fmaf(fmaf(f[k], a[k], b[k]), g1[k], be[k]);
+      f[k] = relu ? fmaxf(t, 0.f) : t;
+    }
+    o[(long long)pix * C8] = pack8(f);
+    wp += sw_;
+    hp += sh_;
+    if (wp >= Wp) {
+      wp -= Wp;
+      ++hp;
     }
   }
 }
@@ -801,49 +812,77 @@ __global__ void spade_cls_bwd1_kernel(const uint4* __restrict__ x, const uint4* 
   for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(red + (size_t)n * 2 * C + i, tab[25 * 2 * C + i]);
 }
 
-// backward pass 2: dx[n,hx,wx,c] = rstd * (sum_{up x up} g (1 + gamma5) - up^2 S1/HW - xhat up^2 S2/HW),  g recomputed
-__global__ void __launch_bounds__(256, 3) spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ out,
-                                      const uint4* __restrict__ dout, uint4* __restrict__ dx, const float* __restrict__ mean_rstd,
-                                      const float* __restrict__ red, int H, int W, int C8, int up, int relu, int pad) {
-  extern __shared__ float sh[];  // mean, rstd, k1, k2
+// backward pass 2: dx[n,hx,wx,c] = rstd * (sum_{up x up} g (1 + gamma5) - up^2 S1/HW - xhat up^2 S2/HW),  g recomputed.
+// Same thread mapping as the forward: fixed 8-channel group per thread, incremental source-pixel index, constants in registers.
+__global__ void __launch_bounds__(256, 3)
+spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ out,
+                      const uint4* __restrict__ dout, uint4* __restrict__ dx, const float* __restrict__ mean_rstd,
+                      const float* __restrict__ red, int H, int W, int C8, int up, int relu, int pad) {
   const int C = C8 * 8;
   const int n = blockIdx.y;
+  const int c8 = threadIdx.x % C8;
+  const int lane = threadIdx.x / C8;
+  const int lanes = blockDim.x / C8;
   const int Hx = H / up, Wx = W / up;
   const float cnt = (float)H * (float)W;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    sh[SW(c)] = mean_rstd[(n * 2 + 0) * C + c];
-    sh[C + SW(c)] = mean_rstd[(n * 2 + 1) * C + c];
-    sh[2 * C + SW(c)] = red[(n * 2 + 0) * C + c] / cnt;
-    sh[3 * C + SW(c)] = red[(n * 2 + 1) * C + c] / cnt;
-  }
-  __syncthreads();
-  const long long per_img = (long long)Hx * Wx * C8;
   const float uu = (float)(up * up);
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < per_img; i += (long long)gridDim.x * blockDim.x) {
-    const int c8 = fast_mod(i, C8);
-    const long long pix = fast_div(i, C8);
-    const int wx = fast_mod(pix, Wx), hx = (int)fast_div(pix, Wx);
-    float fx[8], acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, o[8];
-    unpack8(__ldg(x + (long long)n * per_img + i), fx);
+  // dx = rstd * (acc - K1 - xhat * K2) with xhat = (x - mean) * rstd  ==  a * acc + c1 * x + c0   (three constants per channel)
+  float a[8], c0[8], c1[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = c8 * 8 + k;
+    const float mean = mean_rstd[(n * 2 + 0) * C + c], rstd = mean_rstd[(n * 2 + 1) * C + c];
+    const float K1 = uu * red[(n * 2 + 0) * C + c] / cnt, K2 = uu * red[(n * 2 + 1) * C + c] / cnt;
+    a[k] = rstd;
+    c1[k] = -rstd * rstd * K2;
+    c0[k] = -rstd * K1 - c1[k] * mean;
+  }
+  const int Wp = W + 2 * pad;
+  const long long img = (long long)n * (H + 2 * pad) * Wp;
+  const int npix = Hx * Wx;
+  const int stride = gridDim.x * lanes;
+  const int sh_ = stride / Wx, sw_ = stride - sh_ * Wx;
+  int pix = blockIdx.x * lanes + lane;
+  int hx = pix / Wx, wx = pix - hx * Wx;
+  const uint4* xin = x + (long long)n * npix * C8 + c8;
+  uint4* o = dx + (long long)n * npix * C8 + c8;
+  const uint4* gbn = gb5 + n * 25 * 2 * C8 + c8;
+  float g1[8];
+  int cur = -1;
+  for (; pix < npix; pix += stride) {
+    const uint4 vx = __ldg(xin + (long long)pix * C8);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     for (int dy = 0; dy < up; ++dy)
       for (int dxx = 0; dxx < up; ++dxx) {
         const int h = hx * up + dy, w = wx * up + dxx;
-        const int Wp = W + 2 * pad;
-        const long long img = (long long)n * (H + 2 * pad) * Wp;
-        float fg[8], fo[8], fd[8];
-        unpack8(__ldg(gb5 + ((n * 5 + bcls(h, H)) * 5 + bcls(w, W)) * (2 * C8) + c8), fg);
-        unpack8(__ldg(out + (img + (long long)(h + pad) * Wp + (w + pad)) * C8 + c8), fo);
-        load_folded(dout, img, h, w, H, W, pad, C8, c8, fd);
+        const long long q = (img + (long long)(h + pad) * Wp + (w + pad)) * C8 + c8;
+        const uint4 vo = __ldg(out + q), vd = __ldg(dout + q);
+        const int cls = bcls(h, H) * 5 + bcls(w, W);
+        if (cls != cur) {
+          cur = cls;
+          float t[8];
+          unpack8(__ldg(gbn + cls * 2 * C8), t);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] += ((!relu || fo[k] > 0.f) ? fd[k] : 0.f) * (1.f + fg[k]);
+          for (int k = 0; k < 8; ++k) g1[k] = 1.f + t[k];
+        }
+        float fo[8], fd[8];
+        unpack8(vo, fo);
+        unpack8(vd, fd);
+        fold_extras(dout, img, h, w, H, W, pad, C8, c8, fd);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] += ((!relu || fo[k] > 0.f) ? fd[k] : 0.f) * g1[k];
       }
+    float f[8];
+    unpack8(vx, f);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int c = c8 * 8 + k;
-      const float xh = (fx[k] - sh[SW(c)]) * sh[C + SW(c)];
-      o[k] = sh[C + SW(c)] * (acc[k] - uu * sh[2 * C + SW(c)] - xh * uu * sh[3 * C + SW(c)]);
+    for (int k = 0; k < 8; ++k) f[k] = fmaf(a[k], acc[k], fmaf(c1[k], f[k], c0[k]));
+    o[(long long)pix * C8] = pack8(f);
+    wx += sw_;
+    hx += sh_;
+    if (wx >= Wx) {
+      wx -= Wx;
+      ++hx;
     }
-    dx[(long long)n * per_img + i] = pack8(o);
   }
 }
 
@@ -1405,14 +1444,16 @@ extern "C" int dei2i_spade_bwd(const void* x, const void* gb, const void* out, c
 extern "C" int dei2i_spade_cls_fwd(const void* x, const void* gb5, void* out, const float* stats, float* mean_rstd, int N, int H,
                                    int W, int C, int up, int relu, float eps, int out_pad, dei2i_stream stream) {
   DEI2I_REQUIRE(out_pad >= 0 && 2 * out_pad + 1 < H && 2 * out_pad + 1 < W, "spade_cls_fwd: out_pad (%d) too large", out_pad);
-  DEI2I_REQUIRE(x && gb5 && out && stats && mean_rstd && C % 8 == 0 && up >= 1 && H % up == 0 && W % up == 0 && H >= 5 && W >= 5,
+  DEI2I_REQUIRE(x && gb5 && out && stats && mean_rstd && C % 8 == 0 && C <= 2048 && up >= 1 && H % up == 0 && W % up == 0 && H >= 5 && W >= 5,
                 "spade_cls_fwd: bad arguments (needs H, W >= 5)");
-  const long long per_img = (long long)(H + 2 * out_pad) * (W + 2 * out_pad) * (C / 8);
-  unsigned bx = nblocks(per_img, 256 * 2);
+  const int C8 = C / 8;
+  const int lanes = 256 / C8 > 0 ? 256 / C8 : 1;
+  const long long npix = (long long)(H + 2 * out_pad) * (W + 2 * out_pad);
+  unsigned bx = nblocks(npix, lanes * 4);
   const unsigned cap = (148 * 16 + N - 1) / N;
   if (bx > cap) bx = cap;
-  spade_cls_fwd_kernel<<<dim3(bx, N), 256, 2 * C * sizeof(float), ST>>>((const uint4*)x, (const uint4*)gb5, (uint4*)out, stats,
-                                                                        mean_rstd, N, H, W, C / 8, up, relu, eps, out_pad);
+  spade_cls_fwd_kernel<<<dim3(bx, N), lanes * C8, 0, ST>>>((const uint4*)x, (const uint4*)gb5, (uint4*)out, stats, mean_rstd, N, H, W,
+                                                          C8, up, relu, eps, out_pad);
   return LAUNCH_OK("spade_cls_fwd_kernel");
 }
 
@@ -1439,11 +1480,11 @@ extern "C" int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* o
   spade_cls_bwd1_kernel<<<dim3(gx, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out, (const uint4*)dout,
                                                              dgb5, mean_rstd, scratch, H, W, C8, up, rows, relu, out_pad);
   if (int rc = LAUNCH_OK("spade_cls_bwd1_kernel")) return rc;
-  const long long per_img = (long long)(H / up) * (W / up) * C8;
-  unsigned bx = nblocks(per_img, 256 * 2);
+  const long long src_pix = (long long)(H / up) * (W / up);
+  unsigned bx = nblocks(src_pix, lanes * 2);
   const unsigned cap = (148 * 16 + N - 1) / N;
   if (bx > cap) bx = cap;
-  spade_cls_bwd2_kernel<<<dim3(bx, N), 256, 4 * C * sizeof(float), ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out,
+  spade_cls_bwd2_kernel<<<dim3(bx, N), threads, 0, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out,
                                                                          (const uint4*)dout, (uint4*)dx, mean_rstd, scratch, H, W, C8,
                                                                          up, relu, out_pad);
   return LAUNCH_OK("spade_cls_bwd2_kernel");

@@ -39,6 +39,17 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+// The tensor-map encoders are DRIVER entry points: unlike runtime calls they do not bind the primary context to the calling
+// thread, and fail with CUDA_ERROR_INVALID_CONTEXT when they are the first CUDA call a thread makes (e.g. a convolution
+// backward as the first node an autograd worker thread runs).  One runtime call per thread binds it.
+static void bind_primary_context() {
+  static thread_local bool bound = false;
+  if (!bound) {
+    cudaFree(nullptr);
+    bound = true;
+  }
+}
+
 static EncodeTiledFn get_encode() {
   static EncodeTiledFn fn = nullptr;
   static bool tried = false;
@@ -55,6 +66,7 @@ static EncodeTiledFn get_encode() {
 
 int encode_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t row_pitch_bytes,
                         uint32_t box_inner, uint32_t box_outer, int swizzle128) {
+  bind_primary_context();
   EncodeTiledFn fn = get_encode();
   if (fn == nullptr) {
     set_error("cuTensorMapEncodeTiled is not available (no CUDA driver / no sm_100 device)");
@@ -86,6 +98,7 @@ typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t
 int encode_tmap_im2col_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t W, uint64_t H, uint64_t N, int lower_w,
                             int upper_w, int lower_h, int upper_h, uint32_t stride, uint32_t channels_per_pixel,
                             uint32_t pixels_per_column) {
+  bind_primary_context();
   static EncodeIm2colFn fn = nullptr;
   static bool tried = false;
   static int driver_version = 0;

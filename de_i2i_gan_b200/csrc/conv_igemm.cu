@@ -385,49 +385,160 @@ conv_wgrad_kernel(const __grid_constant__ CUtensorMap tmap_dy, const WgradKParam
   }
 }
 
-// second pass: dw[co, ci, r, s] = beta*dw + scale * (sum_splits P[split, co, (r*kw+s)*Cin + ci] - corr * u[co] * v[col])
-__global__ void wgrad_reduce_kernel(const float* __restrict__ partial, int splits, int Cout, int Kf, int Cin, int Cin_real,
-                                    int taps, float* __restrict__ dw, float beta, const float* __restrict__ dot,
-                                    const float* __restrict__ u, const float* __restrict__ v,
-                                    const float* __restrict__ inv_sigma) {
-  const long long total = (long long)Cout * Cin_real * taps;
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= total) return;
-  const int cols = Cin_real * taps;
-  const int co = (int)(i / cols);
-  const int col = (int)(i - (long long)co * cols);  // ci*taps + tap  (weight memory order [co][ci][r][s])
-  const int ci = col / taps;
-  const int tap = col - ci * taps;
-  const long long off = (long long)co * Kf + tap * Cin + ci;
-  float acc = 0.f;
-  for (int s = 0; s < splits; ++s) acc += partial[(long long)s * Cout * Kf + off];
-  if (u != nullptr) acc = (acc - dot[0] * u[co] * v[col]) * inv_sigma[0];
-  dw[i] = beta != 0.f ? beta * dw[i] + acc : acc;
+// second pass over the FP32 partial tiles P[split, co, tap*Cin + ci]: the weight gradient lives in weight memory order
+// [co][ci][tap], i.e. (tap, ci) transposed.  One work tile = (co, CT input channels, all taps), staged through shared
+// memory so that both the reads of P (CT consecutive ci per tap) and the accesses in weight order (CT*taps consecutive
+// floats) are coalesced 16-byte accesses; 256 threads.  CT = 256 for the large discriminator weights (16 KB+ in flight per
+// block), 64 / 16 for small problems so that enough blocks exist.  Split sums run in a fixed order (deterministic).
+// Requires Cin_real % 4 == 0 for the vector path (VEC); the scalar path handles 3- and 6-channel inputs.
+template <bool VEC>
+__device__ __forceinline__ void wgrad_tile_load(const float* __restrict__ partial, int splits, long long split_stride, int Kf, int Cin,
+                                                int Cin_real, int taps, int co, int ci0, int sh, int pitch, float* __restrict__ T) {
+  const float* base = partial + (long long)co * Kf + ci0;
+  if (VEC) {
+    const int sh4 = sh - 2;
+    for (int idx = threadIdx.x; idx < (taps << sh4); idx += blockDim.x) {
+      const int tap = idx >> sh4, j = (idx & ((1 << sh4) - 1)) * 4;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (ci0 + j < Cin_real) {
+        const float* q = base + tap * Cin + j;
+        for (int s = 0; s < splits; ++s) {
+          const float4 t = __ldg(reinterpret_cast<const float4*>(q + (long long)s * split_stride));
+          acc.x += t.x; acc.y += t.y; acc.z += t.z; acc.w += t.w;
+        }
+      }
+      *reinterpret_cast<float4*>(T + tap * pitch + j) = acc;
+    }
+  } else {
+    for (int idx = threadIdx.x; idx < (taps << sh); idx += blockDim.x) {
+      const int tap = idx >> sh, j = idx & ((1 << sh) - 1);
+      float acc = 0.f;
+      if (ci0 + j < Cin_real) {
+        const float* q = base + tap * Cin + j;
+        for (int s = 0; s < splits; ++s) acc += q[(long long)s * split_stride];
+      }
+      T[tap * pitch + j] = acc;
+    }
+  }
 }
 
-// <dW, W/sigma> over the real elements (spectral-norm backward); deterministic: one block, fixed order
-__global__ void wgrad_dot_kernel(const float* __restrict__ partial, int splits, int Cout, int Kf, int Cin, int Cin_real,
-                                 int taps, const float* __restrict__ w_orig, const float* __restrict__ inv_sigma,
-                                 float* __restrict__ blocksums) {
-  const long long total = (long long)Cout * Cin_real * taps;
+//   dw[co, ci, r, s] = beta*dw + scale * (sum_splits P - corr * u[co] * v[col])
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+wgrad_reduce_kernel(const float* __restrict__ partial, int splits, int Cout, int Kf, int Cin, int Cin_real, int taps,
+                    float* __restrict__ dw, float beta, const float* __restrict__ dot, const float* __restrict__ u,
+                    const float* __restrict__ v, const float* __restrict__ inv_sigma, int sh) {
+  extern __shared__ float4 T4[];
+  float* T = reinterpret_cast<float*>(T4);
+  const int ct = 1 << sh, pitch = ct + 4;
+  const int ci_tiles = (Cin_real + ct - 1) >> sh;
+  const int co = blockIdx.x / ci_tiles;
+  const int ci0 = (blockIdx.x - co * ci_tiles) << sh;
+  wgrad_tile_load<VEC>(partial, splits, (long long)Cout * Kf, Kf, Cin, Cin_real, taps, co, ci0, sh, pitch, T);
+  __syncthreads();
+  const int n = min(ct, Cin_real - ci0) * taps;
+  const int cols = Cin_real * taps;
+  const int col0 = ci0 * taps;
+  float* out = dw + (long long)co * cols + col0;
+  float corr = 0.f, scale = 1.f;
+  if (u != nullptr) {
+    corr = dot[0] * u[co];
+    scale = inv_sigma[0];
+  }
+  if (VEC) {
+    for (int o = threadIdx.x * 4; o < n; o += blockDim.x * 4) {
+      float a[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int cl = (o + k) / taps, tap = (o + k) - cl * taps;
+        a[k] = T[tap * pitch + cl];
+      }
+      if (u != nullptr) {
+        const float4 vv = __ldg(reinterpret_cast<const float4*>(v + col0 + o));
+        a[0] = (a[0] - corr * vv.x) * scale; a[1] = (a[1] - corr * vv.y) * scale;
+        a[2] = (a[2] - corr * vv.z) * scale; a[3] = (a[3] - corr * vv.w) * scale;
+      }
+      float4* q = reinterpret_cast<float4*>(out + o);
+      if (beta != 0.f) {
+        const float4 old = *q;
+        a[0] += beta * old.x; a[1] += beta * old.y; a[2] += beta * old.z; a[3] += beta * old.w;
+      }
+      *q = make_float4(a[0], a[1], a[2], a[3]);
+    }
+  } else {
+    for (int o = threadIdx.x; o < n; o += blockDim.x) {
+      const int cl = o / taps, tap = o - cl * taps;
+      float acc = T[tap * pitch + cl];
+      if (u != nullptr) acc = (acc - corr * v[col0 + o]) * scale;
+      out[o] = beta != 0.f ? beta * out[o] + acc : acc;
+    }
+  }
+}
+
+// <dW, W/sigma> over the real elements (spectral-norm backward); deterministic: fixed tile -> block assignment, fixed order
+template <bool VEC>
+__global__ void __launch_bounds__(256)
+wgrad_dot_kernel(const float* __restrict__ partial, int splits, int Cout, int Kf, int Cin, int Cin_real, int taps,
+                 const float* __restrict__ w_orig, const float* __restrict__ inv_sigma, float* __restrict__ blocksums, int sh) {
+  extern __shared__ float4 T4[];
+  float* T = reinterpret_cast<float*>(T4);
+  const int ct = 1 << sh, pitch = ct + 4;
+  const int ci_tiles = (Cin_real + ct - 1) >> sh;
+  const int tiles = Cout * ci_tiles;
   const int cols = Cin_real * taps;
   float acc = 0.f;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int co = (int)(i / cols);
-    const int col = (int)(i - (long long)co * cols);
-    const int ci = col / taps;
-    const int tap = col - ci * taps;
-    const long long off = (long long)co * Kf + tap * Cin + ci;
-    float g = 0.f;
-    for (int s = 0; s < splits; ++s) g += partial[(long long)s * Cout * Kf + off];
-    acc += g * w_orig[i];
+  for (int t = blockIdx.x; t < tiles; t += gridDim.x) {
+    const int co = t / ci_tiles;
+    const int ci0 = (t - co * ci_tiles) << sh;
+    const int n = min(ct, Cin_real - ci0) * taps;
+    const float* w = w_orig + (long long)co * cols + ci0 * taps;
+    // the weight values of this tile are fetched before the barrier so that both streams are in flight together
+    float4 wv[4];
+    if (VEC) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int o = (threadIdx.x + r * 256) * 4;
+        wv[r] = o < n ? __ldg(reinterpret_cast<const float4*>(w + o)) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+    __syncthreads();
+    wgrad_tile_load<VEC>(partial, splits, (long long)Cout * Kf, Kf, Cin, Cin_real, taps, co, ci0, sh, pitch, T);
+    __syncthreads();
+    if (VEC) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int o = (threadIdx.x + r * 256) * 4;
+        if (o < n) {
+          const float wk[4] = {wv[r].x, wv[r].y, wv[r].z, wv[r].w};
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const int cl = (o + k) / taps, tap = (o + k) - cl * taps;
+            acc += T[tap * pitch + cl] * wk[k];
+          }
+        }
+      }
+      for (int o = (threadIdx.x + 1024) * 4; o < n; o += blockDim.x * 4) {  // tiles beyond 4096 elements (taps > 16)
+        const float4 t4 = __ldg(reinterpret_cast<const float4*>(w + o));
+        const float wk[4] = {t4.x, t4.y, t4.z, t4.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int cl = (o + k) / taps, tap = (o + k) - cl * taps;
+          acc += T[tap * pitch + cl] * wk[k];
+        }
+      }
+    } else {
+      for (int o = threadIdx.x; o < n; o += blockDim.x) {
+        const int cl = o / taps, tap = o - cl * taps;
+        acc += T[tap * pitch + cl] * w[o];
+      }
+    }
   }
-  __shared__ float sh[32];
+  __shared__ float wsum[32];
   acc = warp_sum(acc);
-  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = acc;
   __syncthreads();
   if (threadIdx.x < 32) {
-    float t = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.f;
+    float t = threadIdx.x < (blockDim.x >> 5) ? wsum[threadIdx.x] : 0.f;
     t = warp_sum(t);
     if (threadIdx.x == 0) blocksums[blockIdx.x] = t * inv_sigma[0];
   }
@@ -741,15 +852,33 @@ extern "C" int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int 
   }
   float* dot = partial + (size_t)splits * g->Cout * Kf;  // [0] = <dW, W/sigma>, [1..] block sums
   const long long total = (long long)g->Cout * Cin_real * taps;
+  // reduction tile width (input channels): 256 when that still leaves >= 4 blocks per SM and the tile fits 48 KB, else 64 / 16
+  const bool red_vec = Cin_real % 4 == 0 && (((uintptr_t)dw | (uintptr_t)sn_v | (uintptr_t)sn_w_orig) & 15) == 0;
+  int red_sh = 4;
+  if (red_vec && Cin_real % 256 == 0 && (long long)g->Cout * (Cin_real / 256) >= 4 * 148 && taps * 260 * 4 <= 48 * 1024) red_sh = 8;
+  else if ((long long)g->Cout * ((Cin_real + 63) / 64) >= 2 * 148) red_sh = 6;
+  const int red_ci = 1 << red_sh;
+  const int red_tiles = g->Cout * ((Cin_real + red_ci - 1) / red_ci);
+  const size_t red_smem = (size_t)taps * (red_ci + 4) * sizeof(float);
+  DEI2I_REQUIRE(red_smem <= 48 * 1024, "conv2d_wgrad: filter too large for the reduction tile");
   if (sn_u != nullptr) {
-    const int nb = 512;
-    wgrad_dot_kernel<<<nb, 256, 0, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, sn_w_orig, sn_inv_sigma, dot + 1);
+    const int nb = red_tiles < 1023 ? red_tiles : 1023;
+    if (red_vec)
+      wgrad_dot_kernel<true><<<nb, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, sn_w_orig, sn_inv_sigma,
+                                                        dot + 1, red_sh);
+    else
+      wgrad_dot_kernel<false><<<nb, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, sn_w_orig, sn_inv_sigma,
+                                                         dot + 1, red_sh);
     sum_blocks_kernel<<<1, 256, 0, st>>>(dot + 1, nb, dot);
     count_launch(2);
     DEI2I_CUDA(cudaGetLastError());
   }
-  wgrad_reduce_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, dw,
-                                                                        beta, dot, sn_u, sn_v, sn_inv_sigma);
+  if (red_vec)
+    wgrad_reduce_kernel<true><<<(unsigned)red_tiles, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, dw, beta,
+                                                                          dot, sn_u, sn_v, sn_inv_sigma, red_sh);
+  else
+    wgrad_reduce_kernel<false><<<(unsigned)red_tiles, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, dw, beta,
+                                                                           dot, sn_u, sn_v, sn_inv_sigma, red_sh);
   count_launch();
   return check_cuda(cudaGetLastError(), "wgrad_reduce_kernel launch");
 }

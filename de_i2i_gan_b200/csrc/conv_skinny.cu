@@ -21,6 +21,7 @@
 namespace dei2i {
 
 void count_launch(int n = 1);
+extern int g_tune_conv_path;  // 2: CUDA-core heads wgrad kernel instead of the mma.sync one (A/B testing)
 
 // ======================================================================================================================
 // narrow-Cout wgrad:  partial[split, co, k] = sum_{m in split} dY[m, co] * A[m, k],  co in [co0, co0 + 8)
@@ -677,12 +678,150 @@ wgrad_heads_kernel(const Gather g, const __nv_bfloat16* __restrict__ dy, int Cou
   }
 }
 
+// ----------------------------------------------------------------------------------------------------------------------
+// The same weight gradient on the tensor pipe (mma.sync m16n8k16; M = 16 input channels, N = the 8 stored output channels,
+// K = 16 pixels), for Cin = 64:  a CTA walks a strip of output rows with a ring of four x rows ((Wo32 + 2) pixels x 128 B,
+// 16-byte chunks XOR-swizzled by pixel so that ldmatrix.trans is conflict-free) and a double-buffered dY row in shared
+// memory (cp.async, zero fill for the zero frame and for columns past Wo); every x row is read from HBM once per strip.
+// Warp w: channel group w % 4, 32-pixel chunks (w / 4) mod 4; 9 taps x 4 FP32 accumulators per lane; the four pixel quarters
+// are summed through shared memory in a fixed order.  One FP32 partial tile per CTA (same layout as above).
+constexpr int kHmWarps = 16;
+constexpr int kHmRing = 4;
+
+__global__ void __launch_bounds__(kHmWarps * 32, 1)
+wgrad_heads_mma_kernel(const Gather g, const __nv_bfloat16* __restrict__ dy, int Cout, int Kf, float* __restrict__ partial,
+                       int rows_per_cta) {
+  extern __shared__ __align__(128) uint8_t hm_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int gid = lane >> 2, tq = lane & 3;
+  const int cig = warp & 3, quarter = warp >> 2;
+  const int Wo32 = (g.Wo + 31) & ~31;
+  const int XW = Wo32 + 2;                 // pixels per staged x row
+  const int x_row_bytes = XW * 128;
+  const uint32_t s_x = smem_u32(hm_smem);
+  const uint32_t s_dy = s_x + kHmRing * x_row_bytes;  // 2 x Wo32 x 16 B
+  const int rows = g.N * g.Ho;
+  const int rb = blockIdx.x * rows_per_cta;
+  const int re = min(rows, rb + rows_per_cta);
+
+  auto issue_x = [&](int img, int iy) {  // stored row iy of image img (zero row when outside the frame) -> slot (iy + 4) & 3
+    const bool rok = iy >= 0 && iy < g.Hl;
+    const __nv_bfloat16* src = g.src + ((long long)img * g.Hs + (rok ? iy : 0)) * g.Ws * 64;
+    const uint32_t dst = s_x + ((iy + 4) & 3) * x_row_bytes;
+    for (int i = threadIdx.x; i < XW * 8; i += blockDim.x) {
+      const int j = i >> 3, c = i & 7;
+      const int ix = j - g.pad;
+      const bool ok = rok && ix >= 0 && ix < g.Wl;
+      cp_async_16(dst + j * 128 + ((c ^ (j & 7)) << 4), src + (ok ? ix * 64 + c * 8 : 0), ok);
+    }
+  };
+  auto issue_dy = [&](int row) {
+    const __nv_bfloat16* src = dy + (long long)row * g.Wo * 8;
+    const uint32_t dst = s_dy + (row & 1) * Wo32 * 16;
+    for (int i = threadIdx.x; i < Wo32; i += blockDim.x) cp_async_16(dst + i * 16, src + (i < g.Wo ? i * 8 : 0), i < g.Wo);
+  };
+
+  float acc[9][4];
+#pragma unroll
+  for (int t = 0; t < 9; ++t) acc[t][0] = acc[t][1] = acc[t][2] = acc[t][3] = 0.f;
+  const int mi = lane >> 3, mr = lane & 7;
+
+  for (int row = rb; row < re; ++row) {
+    const int img = row / g.Ho, oy = row - img * g.Ho;
+    const int iy0 = oy - g.pad;
+    if (row == rb || oy == 0) {  // (re)start of an image: nothing of it is staged yet
+      __syncthreads();
+      issue_x(img, iy0);
+      issue_x(img, iy0 + 1);
+      issue_x(img, iy0 + 2);
+      issue_dy(row);
+    }
+    cp_async_commit();
+    if (row + 1 < re && oy + 1 < g.Ho) {  // next output row of the same image: one new x row, the next dY row
+      issue_x(img, iy0 + 3);
+      issue_dy(row + 1);
+    }
+    cp_async_commit();
+    cp_async_wait_group<1>();
+    __syncthreads();
+    const uint32_t dyr = s_dy + (row & 1) * Wo32 * 16;
+    for (int q = quarter; q * 32 < g.Wo; q += 4) {
+      const int ox0 = q * 32;
+      uint32_t b[4];
+      ldsm_x4_trans(b, dyr + (ox0 + mi * 8 + mr) * 16);
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const uint32_t xr = s_x + ((iy0 + r + 4) & 3) * x_row_bytes;
+#pragma unroll
+        for (int sx = 0; sx < 3; ++sx) {
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const int pix = ox0 + h * 16 + (mi >> 1) * 8 + mr + sx;
+            const int chunk = cig * 2 + (mi & 1);
+            uint32_t a[4];
+            ldsm_x4_trans(a, xr + pix * 128 + ((chunk ^ (pix & 7)) << 4));
+            mma_bf16_16816(acc[r * 3 + sx], a, b[2 * h], b[2 * h + 1]);
+          }
+        }
+      }
+    }
+    __syncthreads();  // everyone is done with the slots the next iteration refills
+  }
+  cp_async_wait_group<0>();
+  __syncthreads();
+  // quarters 1..3 park their accumulators in shared memory, quarter 0 adds them in order and stores
+  float* red = reinterpret_cast<float*>(hm_smem);
+  if (quarter > 0) {
+#pragma unroll
+    for (int t = 0; t < 9; ++t)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) red[(((quarter - 1) * 4 + cig) * 36 + t * 4 + e) * 32 + lane] = acc[t][e];
+  }
+  __syncthreads();
+  if (quarter == 0) {
+#pragma unroll
+    for (int t = 0; t < 9; ++t) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        float v = acc[t][e];
+        for (int qq = 0; qq < 3; ++qq) v += red[((qq * 4 + cig) * 36 + t * 4 + e) * 32 + lane];
+        const int ci = cig * 16 + gid + 8 * (e >> 1);
+        const int co = 2 * tq + (e & 1);
+        if (co < Cout) partial[((long long)blockIdx.x * Cout + co) * Kf + t * 64 + ci] = v;
+      }
+    }
+  }
+}
+
+static size_t wgrad_heads_mma_smem(int Wo) {
+  const int Wo32 = (Wo + 31) & ~31;
+  return (size_t)kHmRing * (Wo32 + 2) * 128 + 2 * (size_t)Wo32 * 16;
+}
+static bool wgrad_heads_mma_applicable(const Gather& g) {
+  const size_t sm = wgrad_heads_mma_smem(g.Wo);
+  return g.C == 64 && g.pad <= 1 && sm <= 200 * 1024 && sm >= (size_t)12 * 36 * 32 * 4 && g.Ho >= 1;
+}
+
 bool wgrad_heads_applicable(const Gather& g, int Cout, int Cout_ld) {
   return g.mode == 0 && g.kh == 3 && g.kw == 3 && g.stride == 1 && g.C % 64 == 0 && kHeadsWarps % (g.C / 64) == 0 && g.C <= 128 &&
          Cout <= 4 && Cout_ld == 8 && g.Hs == g.Hl && g.Ws == g.Wl && !(g.pad_mode == DEI2I_PAD_REFLECT && g.pad > 0);
 }
 int wgrad_heads_splits() { return 148; }
 int run_wgrad_heads(const Gather& g, const void* dy, int Cout, int Cout_ld, int Kf, float* partial, cudaStream_t st) {
+  if (g_tune_conv_path != 2 && wgrad_heads_mma_applicable(g)) {
+    const size_t sm = wgrad_heads_mma_smem(g.Wo);
+    static size_t attr = 0;
+    if (sm > attr) {
+      DEI2I_CUDA(cudaFuncSetAttribute(wgrad_heads_mma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+      attr = sm;
+    }
+    const int rows = g.N * g.Ho;
+    const int rpc = (rows + 147) / 148;
+    // CTAs past the last strip still write their (zero) partial tile: the second pass sums all 148
+    wgrad_heads_mma_kernel<<<148, kHmWarps * 32, sm, st>>>(g, (const __nv_bfloat16*)dy, Cout, Kf, partial, rpc);
+    count_launch();
+    return check_cuda(cudaGetLastError(), "wgrad_heads_mma_kernel launch");
+  }
   wgrad_heads_kernel<<<148, kHeadsWarps * 32, 0, st>>>(g, (const __nv_bfloat16*)dy, Cout, Cout_ld, Kf, partial);
   count_launch();
   return check_cuda(cudaGetLastError(), "wgrad_heads_kernel launch");

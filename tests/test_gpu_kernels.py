@@ -83,6 +83,8 @@ CONV_CASES = {
     "c8_spade_shared_big": (4, 6, 40, 40, 128, 3, 1, 1, "zeros", True, (1, 1)),
     "heads_valid_4": (2, 64, 18, 18, 4, 3, 1, 0, "zeros", False, None),
     "heads_valid_128_zero": (1, 128, 12, 12, 3, 3, 1, 1, "zeros", False, None),
+    "heads_zero_64_wide": (3, 64, 9, 150, 4, 3, 1, 1, "zeros", False, None),   # 5 pixel chunks, zero frame, image restarts
+    "heads_valid_64_rows": (2, 64, 163, 34, 3, 3, 1, 0, "zeros", False, None),  # > 148 output rows per image: multi-row strips
     "d_cls_valid4x4": (4, 128, 4, 4, 6, 4, 1, 0, "zeros", False, None),
 }
 
@@ -204,7 +206,7 @@ WGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "stem7x7", "spade_shared_8
                "ragged_m", "d_conv0", "d_src_1", "cls_valid_k2", "narrow_16_32", "narrow_s2_8_16", "tma_valid3x3",
                "tma_zero3x3_256", "tma_persistent_200tiles", "tma_valid4x4s2", "tma_dgrad_s2_to8", "c8_stem_valid7x7",
                "c8_zero3x3_nores", "c8_spade_shared_big", "spade_shared_1x1seg", "heads_valid_4", "heads_valid_128_zero",
-               "d_cls_valid4x4"]
+               "d_cls_valid4x4", "heads_zero_64_wide", "heads_valid_64_rows"]
 
 
 @pytest.mark.parametrize("case", WGRAD_CASES)

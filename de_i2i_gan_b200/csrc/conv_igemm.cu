@@ -638,6 +638,16 @@ extern "C" int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const
   ConvKParams p;
   memset(&p, 0, sizeof(p));
   const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
+  p.g.src = (const __nv_bfloat16*)x;
+  p.g.N = g->N; p.g.Hl = g->H; p.g.Wl = g->W; p.g.Hs = g->Hs; p.g.Ws = g->Ws; p.g.C = g->Cin;
+  p.g.Ho = Ho; p.g.Wo = Wo; p.g.kh = g->kh; p.g.kw = g->kw; p.g.stride = g->stride; p.g.pad = g->pad;
+  p.g.pad_mode = g->pad_mode; p.g.mode = 0; p.g.off = 0; p.g.cin8 = g->Cin / 8; p.g.ntaps = g->kh * g->kw;
+  p.g.M = (long long)g->N * Ho * Wo;
+  p.e.scale = e->scale; p.e.bias = e->bias; p.e.noise = e->noise; p.e.noise_weight = e->noise_weight;
+  p.e.residual = (const __nv_bfloat16*)e->residual; p.e.out = y; p.e.act = e->act; p.e.out_fp32 = e->out_fp32;
+  p.e.ld = g->Cout_ld; p.e.ncols = g->Cout;
+  if (conv_heads_fwd_applicable(p.g, g->Cout_ld))
+    return run_conv_heads_fwd(p.g, p.e, w_fwd, g->Cout, round_up(g->kh * g->kw * g->Cin, 64), (cudaStream_t)stream);
   if (tma_applicable(g, g->Cin, (long long)g->N * Ho * Wo)) {
     TmaConvParams t;
     memset(&t, 0, sizeof(t));

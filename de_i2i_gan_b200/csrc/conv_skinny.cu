@@ -802,6 +802,134 @@ static bool wgrad_heads_mma_applicable(const Gather& g) {
   return g.C == 64 && g.pad <= 1 && sm <= 200 * 1024 && sm >= (size_t)12 * 36 * 32 * 4 && g.Ho >= 1;
 }
 
+// ----------------------------------------------------------------------------------------------------------------------
+// Forward of the heads (64 -> <= 8 stored output channels, 3x3, stride 1; generator.py:224-241) on the same row ring:
+// mma.sync m16n8k16 with M = 16 pixels, N = 8 output channels, K = 16 input channels; the 9 x 4 B fragments (all weights)
+// stay in registers, A fragments come from the swizzled x rows by ldmatrix.  A warp owns 16-pixel chunks of the row.
+// HBM traffic = x once + y once (the tcgen05 path would pad N to 64 and run 16x the FLOPs).
+__global__ void __launch_bounds__(kHmWarps * 32, 1)
+conv_heads_fwd_kernel(const Gather g, const Epilogue e, const __nv_bfloat16* __restrict__ w, int rows_w, int Kf, int rows_per_cta) {
+  extern __shared__ __align__(128) uint8_t hm_smem[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int gid = lane >> 2, tq = lane & 3;
+  const int Wo16 = (g.Wo + 15) & ~15;
+  const int XW = Wo16 + 2;
+  const int x_row_bytes = XW * 128;
+  const uint32_t s_x = smem_u32(hm_smem);
+  const int rows = g.N * g.Ho;
+  const int rb = blockIdx.x * rows_per_cta;
+  const int re = min(rows, rb + rows_per_cta);
+
+  auto issue_x = [&](int img, int iy) {
+    const bool rok = iy >= 0 && iy < g.Hl;
+    const __nv_bfloat16* src = g.src + ((long long)img * g.Hs + (rok ? iy : 0)) * g.Ws * 64;
+    const uint32_t dst = s_x + ((iy + 4) & 3) * x_row_bytes;
+    for (int i = threadIdx.x; i < XW * 8; i += blockDim.x) {
+      const int j = i >> 3, c = i & 7;
+      const int ix = j - g.pad;
+      const bool ok = rok && ix >= 0 && ix < g.Wl;
+      cp_async_16(dst + j * 128 + ((c ^ (j & 7)) << 4), src + (ok ? ix * 64 + c * 8 : 0), ok);
+    }
+  };
+
+  // B fragments: b0 = W[co = gid][tap*64 + ks*16 + 2*tq .. +1], b1 = ... + 8
+  uint32_t bw[36][2];
+#pragma unroll
+  for (int i = 0; i < 36; ++i) {
+    bw[i][0] = bw[i][1] = 0u;
+    if (gid < rows_w) {
+      const __nv_bfloat16* q = w + (long long)gid * Kf + i * 16 + 2 * tq;
+      bw[i][0] = __ldg(reinterpret_cast<const uint32_t*>(q));
+      bw[i][1] = __ldg(reinterpret_cast<const uint32_t*>(q + 8));
+    }
+  }
+  const float osc = e.scale != nullptr ? __ldg(e.scale) : 1.f;
+  const float nzw = e.noise != nullptr ? __ldg(e.noise_weight) : 0.f;
+  float bias[2] = {0.f, 0.f};
+  if (e.bias != nullptr) {
+    if (2 * tq < e.ncols) bias[0] = __ldg(e.bias + 2 * tq);
+    if (2 * tq + 1 < e.ncols) bias[1] = __ldg(e.bias + 2 * tq + 1);
+  }
+  const int mi = lane >> 3, mr = lane & 7;
+
+  for (int row = rb; row < re; ++row) {
+    const int img = row / g.Ho, oy = row - img * g.Ho;
+    const int iy0 = oy - g.pad;
+    if (row == rb || oy == 0) {
+      __syncthreads();
+      issue_x(img, iy0);
+      issue_x(img, iy0 + 1);
+      issue_x(img, iy0 + 2);
+    }
+    cp_async_commit();
+    if (row + 1 < re && oy + 1 < g.Ho) issue_x(img, iy0 + 3);
+    cp_async_commit();
+    cp_async_wait_group<1>();
+    __syncthreads();
+    for (int ox0 = warp * 16; ox0 < g.Wo; ox0 += kHmWarps * 16) {
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+      for (int r = 0; r < 3; ++r) {
+        const uint32_t xr = s_x + ((iy0 + r + 4) & 3) * x_row_bytes;
+#pragma unroll
+        for (int sx = 0; sx < 3; ++sx) {
+          const int pix = ox0 + (mi & 1) * 8 + mr + sx;
+          const uint32_t prow = xr + pix * 128;
+#pragma unroll
+          for (int ks = 0; ks < 4; ++ks) {
+            uint32_t a[4];
+            ldsm_x4(a, prow + (((ks * 2 + (mi >> 1)) ^ (pix & 7)) << 4));
+            mma_bf16_16816(acc, a, bw[(r * 3 + sx) * 4 + ks][0], bw[(r * 3 + sx) * 4 + ks][1]);
+          }
+        }
+      }
+      // epilogue: rows (pixels) gid / gid + 8, columns 2*tq, 2*tq + 1
+      const int col = 2 * tq;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int ox = ox0 + gid + 8 * h;
+        if (ox >= g.Wo) continue;
+        const long long m = (long long)row * g.Wo + ox;
+        const float nz = e.noise != nullptr ? __ldg(e.noise + m) * nzw : 0.f;
+        float v0 = apply_act(fmaf(acc[2 * h], osc, bias[0] + nz), e.act);
+        float v1 = apply_act(fmaf(acc[2 * h + 1], osc, bias[1] + nz), e.act);
+        if (col < e.ld) {
+          if (e.residual != nullptr) {
+            const uint32_t rv = __ldg(reinterpret_cast<const uint32_t*>(e.residual + m * e.ld + col));
+            v0 += bf16lo(rv);
+            v1 += bf16hi(rv);
+          }
+          if (e.out_fp32) *reinterpret_cast<float2*>(reinterpret_cast<float*>(e.out) + m * e.ld + col) = make_float2(v0, v1);
+          else *reinterpret_cast<uint32_t*>(reinterpret_cast<__nv_bfloat16*>(e.out) + m * e.ld + col) = pack_bf16(v0, v1);
+        }
+      }
+    }
+    __syncthreads();
+  }
+  cp_async_wait_group<0>();
+}
+
+bool conv_heads_fwd_applicable(const Gather& g, int rows_ld) {
+  const size_t sm = (size_t)kHmRing * (((g.Wo + 15) & ~15) + 2) * 128;
+  return g_tune_conv_path == 0 && g.mode == 0 && g.kh == 3 && g.kw == 3 && g.stride == 1 && g.C == 64 && rows_ld == 8 && g.pad <= 1 &&
+         g.Hs == g.Hl && g.Ws == g.Wl && !(g.pad_mode == DEI2I_PAD_REFLECT && g.pad > 0) && sm <= 200 * 1024 &&
+         g.M < (1ll << 31);
+}
+int run_conv_heads_fwd(const Gather& g, const Epilogue& e, const void* wmat, int rows, int Kf, cudaStream_t st) {
+  const size_t sm = (size_t)kHmRing * (((g.Wo + 15) & ~15) + 2) * 128;
+  static size_t attr = 0;
+  if (sm > attr) {
+    DEI2I_CUDA(cudaFuncSetAttribute(conv_heads_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    attr = sm;
+  }
+  const int nrows = g.N * g.Ho;
+  const int rpc = (nrows + 147) / 148;
+  const int grid = (nrows + rpc - 1) / rpc;
+  conv_heads_fwd_kernel<<<grid, kHmWarps * 32, sm, st>>>(g, e, (const __nv_bfloat16*)wmat, rows, Kf, rpc);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "conv_heads_fwd_kernel launch");
+}
+
 bool wgrad_heads_applicable(const Gather& g, int Cout, int Cout_ld) {
   return g.mode == 0 && g.kh == 3 && g.kw == 3 && g.stride == 1 && g.C % 64 == 0 && kHeadsWarps % (g.C / 64) == 0 && g.C <= 128 &&
          Cout <= 4 && Cout_ld == 8 && g.Hs == g.Hl && g.Ws == g.Wl && !(g.pad_mode == DEI2I_PAD_REFLECT && g.pad > 0);

@@ -178,6 +178,25 @@ def test_conv_fwd_fp32_out_and_epilogue():
     assert e1 < TOL_F32 and e2 < TOL_BF16 and e3 < TOL_F32
 
 
+def test_conv_heads_fwd_epilogue():
+    """generator heads geometry (64 -> 4, 3x3 on a pre-padded map) through conv_heads_fwd_kernel: scale, bias, FP32 / BF16 out"""
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(6)
+    n, c, h, w, co = 2, 64, 21, 37, 4
+    x, wt = q(torch.randn(n, c, h, w, generator=g)), q(torch.randn(co, c, 3, 3, generator=g) / 24)
+    b = torch.randn(co, generator=g)
+    sc = torch.tensor([0.6])
+    spec = ops.ConvSpec(c, co, 3, 1, 0, "zeros")
+    w_fwd, _ = ops.pack_weight(wt.cuda(), spec, need_dgrad=False)
+    conv = 0.6 * ref_conv(x, wt, None, 1, 0, "zeros") + b[None, :, None, None]
+    y = ops.conv2d_fwd(to_dev(x), w_fwd, spec, bias=b.cuda(), scale=sc.cuda(), out_fp32=True)
+    e1 = rel_err(y.cpu().permute(0, 3, 1, 2)[:, :co], conv)
+    y2 = ops.conv2d_fwd(to_dev(x), w_fwd, spec, bias=b.cuda(), scale=sc.cuda(), act="tanh")
+    e2 = rel_err(from_dev(y2, co), torch.tanh(conv))
+    _report("conv_fwd/heads_epilogue", fp32=e1, tanh=e2)
+    assert e1 < TOL_F32 and e2 < TOL_BF16, (e1, e2)
+
+
 DGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "spade_gb_512", "heads_4", "ragged_m", "d_src_1", "cls_valid_k2",
                "narrow_16_32", "narrow_s2_8_16", "tma_valid3x3", "tma_zero3x3_256", "tma_persistent_200tiles", "tma_valid4x4s2",
                "tma_valid7x7", "tma_ragged_m100", "tma_ragged_m75_s2", "tma_dgrad_s2_to8", "heads_valid_4",

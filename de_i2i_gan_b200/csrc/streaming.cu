@@ -754,9 +754,12 @@ DEVINL void fold_extras(const uint4* __restrict__ t, long long img_base, int h, 
 // backward pass 1 over whole rows [r0, r1) of image n: g = dout * (out > 0);  per border class  dgamma5 += g * xhat,
 // dbeta5 += g  (fp32 [N,5,5,2C], atomics);  S1 = sum g(1+gamma), S2 = sum g(1+gamma) xhat  per (n,c) into `red`.
 // smem table: 25 classes x 2C + one row [S1 | S2]; a thread keeps the sums of its current class in registers.
-__global__ void spade_cls_bwd1_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ out,
-                                      const uint4* __restrict__ dout, float* __restrict__ dgb5, const float* __restrict__ mean_rstd,
-                                      float* __restrict__ red /*[N,2,C]*/, int H, int W, int C8, int up, int rows, int relu, int pad) {
+template <int UP>
+__global__ void __launch_bounds__(256, 2)
+spade_cls_bwd1_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ out,
+                      const uint4* __restrict__ dout, float* __restrict__ dgb5, const float* __restrict__ mean_rstd,
+                      float* __restrict__ red /*[N,2,C]*/, int H, int W, int C8, int rows, int relu, int pad) {
+  constexpr int up = UP;
   extern __shared__ float tab[];  // [26][2C]
   const int c8 = threadIdx.x % C8;
   const int lane = threadIdx.x / C8;
@@ -768,89 +771,109 @@ __global__ void spade_cls_bwd1_kernel(const uint4* __restrict__ x, const uint4* 
   for (int i = threadIdx.x; i < 26 * 2 * C; i += blockDim.x) tab[i] = 0.f;
   __syncthreads();
   float mu[8], rs[8], s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  float ag[8] = {0, 0, 0, 0, 0, 0, 0, 0}, ab[8] = {0, 0, 0, 0, 0, 0, 0, 0}, fg[8];
+  float ag[8] = {0, 0, 0, 0, 0, 0, 0, 0}, ab[8] = {0, 0, 0, 0, 0, 0, 0, 0}, fg[8], fb[8];  // fg = 1 + gamma, fb = beta
   int cur = -1;
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
-    mu[k] = mean_rstd[(n * 2 + 0) * C + c8 * 8 + k];
     rs[k] = mean_rstd[(n * 2 + 1) * C + c8 * 8 + k];
+    mu[k] = -mean_rstd[(n * 2 + 0) * C + c8 * 8 + k] * rs[k];  // xhat = fma(x, rs, mu): the forward's expression, bit for bit
   }
   const int Wp = W + 2 * pad;
   const long long img = (long long)n * (H + 2 * pad) * Wp;
-  // software-pipelined: the three 16-byte loads of the next pixel are in flight while the current one is reduced
-  long long p = (long long)r0 * W + lane;
-  const long long pend = (long long)r1 * W;
-  uint4 nx = make_uint4(0, 0, 0, 0), no = nx, nd = nx;
-  int nh = 0, nw = 0;
-  if (p < pend) {
-    nw = fast_mod(p, W); nh = (int)fast_div(p, W);
-    nx = __ldg(x + (((long long)n * Hx + nh / up) * Wx + nw / up) * C8 + c8);
-    const long long o = (img + (long long)(nh + pad) * Wp + (nw + pad)) * C8 + c8;
-    no = __ldg(out + o);
-    nd = __ldg(dout + o);
-  }
-  for (; p < pend; p += lanes) {
-    const uint4 cx = nx, co = no, cd = nd;
-    const int h = nh, w = nw;
-    const long long pn = p + lanes;
-    if (pn < pend) {
-      nw = fast_mod(pn, W); nh = (int)fast_div(pn, W);
-      nx = __ldg(x + (((long long)n * Hx + nh / up) * Wx + nw / up) * C8 + c8);
-      const long long o = (img + (long long)(nh + pad) * Wp + (nw + pad)) * C8 + c8;
-      no = __ldg(out + o);
-      nd = __ldg(dout + o);
-    }
-    const int cls = bcls(h, H) * 5 + bcls(w, W);
-    if (cls != cur) {
-      if (cur >= 0) {
+  // the ReLU mask is recomputed from x (out = relu(fma(xhat, 1 + gamma, beta)) exactly as the forward evaluates it) instead
+  // of reading `out` back: one tensor pass less.
+  // memory-level parallelism: the loads of kB pixels (2 x 16 B each) are issued before any of them is reduced - at 2 blocks
+  // per SM that is 64 KB in flight per SM, enough to cover the HBM latency (one-deep prefetch left the kernel latency-bound)
+  constexpr int kB = 4;
+  // pixel walk without divisions: (ph, pw) advances by `lanes` pixels per step; the source index uses a shift (UP is 1 or 2)
+  int ph = r0 + lane / W, pw = lane % W;
+  const uint4* xn = x + (long long)n * Hx * Wx * C8 + c8;
+  const uint4* dn = dout + (img + (long long)pad * Wp + pad) * C8 + c8;
+  while (ph < r1) {
+    uint4 vx[kB], vd[kB];
+    int hh[kB], ww[kB];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          atomicAdd(&tab[cur * 2 * C + c8 * 8 + k], ag[k]);
-          atomicAdd(&tab[cur * 2 * C + C + c8 * 8 + k], ab[k]);
-          ag[k] = ab[k] = 0.f;
-        }
+    for (int j = 0; j < kB; ++j) {
+      hh[j] = ph; ww[j] = pw;
+      if (ph < r1) {
+        vx[j] = __ldg(xn + ((ph >> (UP - 1)) * Wx + (pw >> (UP - 1))) * C8);
+        vd[j] = __ldg(dn + (ph * Wp + pw) * C8);
       }
-      cur = cls;
-      unpack8(__ldg(gb5 + (n * 25 + cls) * (2 * C8) + c8), fg);
+      pw += lanes;
+      while (pw >= W) {
+        pw -= W;
+        ++ph;
+      }
     }
-    float fx[8], fo[8], fd[8];
-    unpack8(cx, fx);
-    unpack8(co, fo);
-    unpack8(cd, fd);
-    fold_extras(dout, img, h, w, H, W, pad, C8, c8, fd);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const float xh = (fx[k] - mu[k]) * rs[k];
-      const float g = (!relu || fo[k] > 0.f) ? fd[k] : 0.f;
-      ag[k] += g * xh;
-      ab[k] += g;
-      const float dxh = g * (1.f + fg[k]);
-      s[k] += dxh;
-      q[k] += dxh * xh;
+    for (int j = 0; j < kB; ++j) {
+      if (hh[j] >= r1) break;
+      const int h = hh[j], w = ww[j];
+      const int cls = bcls(h, H) * 5 + bcls(w, W);
+      if (cls != cur) {
+        if (cur >= 0) {
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            atomicAdd(&tab[cur * 2 * C + k * C8 + c8], ag[k]);
+            atomicAdd(&tab[cur * 2 * C + C + k * C8 + c8], ab[k]);
+            s[k] = fmaf(fg[k], ab[k], s[k]);  // S1, S2 are (1 + gamma)-weighted class sums: no per-pixel work for them
+            q[k] = fmaf(fg[k], ag[k], q[k]);
+            ag[k] = ab[k] = 0.f;
+          }
+        }
+        cur = cls;
+        unpack8(__ldg(gb5 + (n * 25 + cls) * (2 * C8) + c8), fg);
+        unpack8(__ldg(gb5 + (n * 25 + cls) * (2 * C8) + C8 + c8), fb);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) fg[k] += 1.f;
+      }
+      float fx[8], fd[8];
+      unpack8(vx[j], fx);
+      unpack8(vd[j], fd);
+      fold_extras(dout, img, h, w, H, W, pad, C8, c8, fd);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        const float xh = fmaf(fx[k], rs[k], mu[k]);
+        const float g = (!relu || fmaf(xh, fg[k], fb[k]) > 0.f) ? fd[k] : 0.f;
+        ag[k] = fmaf(g, xh, ag[k]);
+        ab[k] += g;
+      }
     }
   }
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
     if (cur >= 0) {
-      atomicAdd(&tab[cur * 2 * C + c8 * 8 + k], ag[k]);
-      atomicAdd(&tab[cur * 2 * C + C + c8 * 8 + k], ab[k]);
+      atomicAdd(&tab[cur * 2 * C + k * C8 + c8], ag[k]);
+      atomicAdd(&tab[cur * 2 * C + C + k * C8 + c8], ab[k]);
+      s[k] = fmaf(fg[k], ab[k], s[k]);
+      q[k] = fmaf(fg[k], ag[k], q[k]);
     }
-    atomicAdd(&tab[25 * 2 * C + c8 * 8 + k], s[k]);
-    atomicAdd(&tab[25 * 2 * C + C + c8 * 8 + k], q[k]);
+    atomicAdd(&tab[25 * 2 * C + k * C8 + c8], s[k]);
+    atomicAdd(&tab[25 * 2 * C + C + k * C8 + c8], q[k]);
   }
   __syncthreads();
   const int rc0 = bcls(r0, H), rc1 = bcls(r1 - 1, H);
   const int span = (rc1 - rc0 + 1) * 5 * 2 * C;
-  for (int i = threadIdx.x; i < span; i += blockDim.x) atomicAdd(dgb5 + (size_t)n * 25 * 2 * C + rc0 * 5 * 2 * C + i, tab[rc0 * 5 * 2 * C + i]);
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) atomicAdd(red + (size_t)n * 2 * C + i, tab[25 * 2 * C + i]);
+  // rows of the table are stored channel-transposed (SW: element (c8, k) at k * C8 + c8) so that a warp's shared-memory atomics
+  // hit consecutive banks; un-swizzle on the way out
+  for (int i = threadIdx.x; i < span; i += blockDim.x) {
+    const int row = i / C, c = i - row * C;
+    atomicAdd(dgb5 + (size_t)n * 25 * 2 * C + rc0 * 5 * 2 * C + i, tab[rc0 * 5 * 2 * C + row * C + SW(c)]);
+  }
+  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) {
+    const int row = i / C, c = i - row * C;
+    atomicAdd(red + (size_t)n * 2 * C + i, tab[25 * 2 * C + row * C + SW(c)]);
+  }
 }
 
 // backward pass 2: dx[n,hx,wx,c] = rstd * (sum_{up x up} g (1 + gamma5) - up^2 S1/HW - xhat up^2 S2/HW),  g recomputed.
 // Same thread mapping as the forward: fixed 8-channel group per thread, incremental source-pixel index, constants in registers.
-__global__ void __launch_bounds__(256, 3)
+template <int UP, int KB>
+__global__ void __launch_bounds__(256, 2)
 spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ out,
                       const uint4* __restrict__ dout, uint4* __restrict__ dx, const float* __restrict__ mean_rstd,
-                      const float* __restrict__ red, int H, int W, int C8, int up, int relu, int pad) {
+                      const float* __restrict__ red, int H, int W, int C8, int relu, int pad) {
+  constexpr int up = UP;
   const int C = C8 * 8;
   const int n = blockIdx.y;
   const int c8 = threadIdx.x % C8;
@@ -860,13 +883,14 @@ spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5
   const float cnt = (float)H * (float)W;
   const float uu = (float)(up * up);
   // dx = rstd * (acc - K1 - xhat * K2) with xhat = (x - mean) * rstd  ==  a * acc + c1 * x + c0   (three constants per channel)
-  float a[8], c0[8], c1[8];
+  float a[8], c0[8], c1[8], b0[8];  // b0 = -mean * rstd: xhat = fma(x, a, b0) as in the forward (ReLU mask recomputed, no read of out)
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
     const int c = c8 * 8 + k;
     const float mean = mean_rstd[(n * 2 + 0) * C + c], rstd = mean_rstd[(n * 2 + 1) * C + c];
     const float K1 = uu * red[(n * 2 + 0) * C + c] / cnt, K2 = uu * red[(n * 2 + 1) * C + c] / cnt;
     a[k] = rstd;
+    b0[k] = -mean * rstd;
     c1[k] = -rstd * rstd * K2;
     c0[k] = -rstd * K1 - c1[k] * mean;
   }
@@ -880,41 +904,61 @@ spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5
   const uint4* xin = x + (long long)n * npix * C8 + c8;
   uint4* o = dx + (long long)n * npix * C8 + c8;
   const uint4* gbn = gb5 + n * 25 * 2 * C8 + c8;
-  float g1[8];
+  float g1[8], be[8];
   int cur = -1;
-  for (; pix < npix; pix += stride) {
-    const uint4 vx = __ldg(xin + (long long)pix * C8);
-    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    for (int dy = 0; dy < up; ++dy)
-      for (int dxx = 0; dxx < up; ++dxx) {
-        const int h = hx * up + dy, w = wx * up + dxx;
-        const long long q = (img + (long long)(h + pad) * Wp + (w + pad)) * C8 + c8;
-        const uint4 vo = __ldg(out + q), vd = __ldg(dout + q);
-        const int cls = bcls(h, H) * 5 + bcls(w, W);
-        if (cls != cur) {
-          cur = cls;
-          float t[8];
-          unpack8(__ldg(gbn + cls * 2 * C8), t);
+  // memory-level parallelism: all loads of KB source pixels (x + UP*UP gradient pixels each) are issued before the first is used
+  constexpr int U2 = UP * UP;
+  for (; pix < npix; pix += KB * stride) {
+    uint4 vx[KB], vd[KB][U2];
+    int hs[KB], ws[KB];
 #pragma unroll
-          for (int k = 0; k < 8; ++k) g1[k] = 1.f + t[k];
-        }
-        float fo[8], fd[8];
-        unpack8(vo, fo);
-        unpack8(vd, fd);
-        fold_extras(dout, img, h, w, H, W, pad, C8, c8, fd);
+    for (int j = 0; j < KB; ++j) {
+      hs[j] = hx; ws[j] = wx;
+      if (pix + j * stride < npix) {
+        vx[j] = __ldg(xin + (long long)(pix + j * stride) * C8);
 #pragma unroll
-        for (int k = 0; k < 8; ++k) acc[k] += ((!relu || fo[k] > 0.f) ? fd[k] : 0.f) * g1[k];
+        for (int dy = 0; dy < UP; ++dy)
+#pragma unroll
+          for (int dxx = 0; dxx < UP; ++dxx)
+            vd[j][dy * UP + dxx] = __ldg(dout + (img + (long long)(hx * UP + dy + pad) * Wp + (wx * UP + dxx + pad)) * C8 + c8);
       }
-    float f[8];
-    unpack8(vx, f);
+      wx += sw_;
+      hx += sh_;
+      if (wx >= Wx) {
+        wx -= Wx;
+        ++hx;
+      }
+    }
 #pragma unroll
-    for (int k = 0; k < 8; ++k) f[k] = fmaf(a[k], acc[k], fmaf(c1[k], f[k], c0[k]));
-    o[(long long)pix * C8] = pack8(f);
-    wx += sw_;
-    hx += sh_;
-    if (wx >= Wx) {
-      wx -= Wx;
-      ++hx;
+    for (int j = 0; j < KB; ++j) {
+      if (pix + j * stride >= npix) break;
+      float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, xh[8], f[8];
+      unpack8(vx[j], f);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) xh[k] = fmaf(f[k], a[k], b0[k]);
+#pragma unroll
+      for (int dy = 0; dy < UP; ++dy)
+#pragma unroll
+        for (int dxx = 0; dxx < UP; ++dxx) {
+          const int h = hs[j] * UP + dy, w = ws[j] * UP + dxx;
+          const int cls = bcls(h, H) * 5 + bcls(w, W);
+          if (cls != cur) {
+            cur = cls;
+            float t[8];
+            unpack8(__ldg(gbn + cls * 2 * C8), t);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) g1[k] = 1.f + t[k];
+            unpack8(__ldg(gbn + cls * 2 * C8 + C8), be);
+          }
+          float fd[8];
+          unpack8(vd[j][dy * UP + dxx], fd);
+          fold_extras(dout, img, h, w, H, W, pad, C8, c8, fd);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[k] += ((!relu || fmaf(xh[k], g1[k], be[k]) > 0.f) ? fd[k] : 0.f) * g1[k];
+        }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] = fmaf(a[k], acc[k], fmaf(c1[k], f[k], c0[k]));
+      o[(long long)(pix + j * stride) * C8] = pack8(f);
     }
   }
 }
@@ -1500,32 +1544,43 @@ extern "C" int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* o
                                    const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, int relu,
                                    int out_pad, dei2i_stream stream) {
   DEI2I_REQUIRE(out_pad >= 0 && 2 * out_pad + 1 < H && 2 * out_pad + 1 < W, "spade_cls_bwd: out_pad (%d) too large", out_pad);
-  DEI2I_REQUIRE(x && gb5 && out && dout && dgb5 && dx && mean_rstd && scratch && C % 8 == 0 && C <= 512 && up >= 1 && H >= 5 && W >= 5,
+  DEI2I_REQUIRE(x && gb5 && dout && dgb5 && dx && mean_rstd && scratch && C % 8 == 0 && C <= 512 && up >= 1 && H >= 5 && W >= 5,
                 "spade_cls_bwd: bad arguments (needs H, W >= 5, C <= 512)");
   const int C8 = C / 8;
   int lanes = 256 / C8;
   if (lanes < 1) lanes = 1;
   const int threads = lanes * C8;
-  // ~4 blocks per SM over the chip, whole rows per block
-  const int want = (148 * 4 + N - 1) / N;
+  // one wave at the kernel's 2 blocks per SM (__launch_bounds__), whole rows per block
+  const int want = (148 * 2) / N > 0 ? (148 * 2) / N : 1;
   int rows = (H + want - 1) / want;
   if (rows < 1) rows = 1;
   const unsigned gx = (unsigned)((H + rows - 1) / rows);
   const size_t shmem = (size_t)26 * 2 * C * sizeof(float);
   DEI2I_CUDA(cudaMemsetAsync(scratch, 0, (size_t)N * 2 * C * sizeof(float), ST));
   DEI2I_CUDA(cudaMemsetAsync(dgb5, 0, (size_t)N * 25 * 2 * C * sizeof(float), ST));
-  if (shmem > 48 * 1024)
-    DEI2I_CUDA(cudaFuncSetAttribute(spade_cls_bwd1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
-  spade_cls_bwd1_kernel<<<dim3(gx, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out, (const uint4*)dout,
-                                                             dgb5, mean_rstd, scratch, H, W, C8, up, rows, relu, out_pad);
+  DEI2I_REQUIRE(up == 1 || up == 2, "spade_cls_bwd: up must be 1 or 2 (got %d)", up);
+  DEI2I_REQUIRE((long long)(H + 2 * out_pad) * (W + 2 * out_pad) * C8 < (1ll << 31), "spade_cls_bwd: image too large for 32-bit pixel offsets");
+  if (shmem > 48 * 1024) {
+    DEI2I_CUDA(cudaFuncSetAttribute(spade_cls_bwd1_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
+    DEI2I_CUDA(cudaFuncSetAttribute(spade_cls_bwd1_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
+  }
+  if (up == 1)
+    spade_cls_bwd1_kernel<1><<<dim3(gx, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out, (const uint4*)dout,
+                                                                  dgb5, mean_rstd, scratch, H, W, C8, rows, relu, out_pad);
+  else
+    spade_cls_bwd1_kernel<2><<<dim3(gx, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out, (const uint4*)dout,
+                                                                  dgb5, mean_rstd, scratch, H, W, C8, rows, relu, out_pad);
   if (int rc = LAUNCH_OK("spade_cls_bwd1_kernel")) return rc;
   const long long src_pix = (long long)(H / up) * (W / up);
-  unsigned bx = nblocks(src_pix, lanes * 2);
+  unsigned bx = nblocks(src_pix, lanes * 8);
   const unsigned cap = (148 * 16 + N - 1) / N;
   if (bx > cap) bx = cap;
-  spade_cls_bwd2_kernel<<<dim3(bx, N), threads, 0, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out,
-                                                                         (const uint4*)dout, (uint4*)dx, mean_rstd, scratch, H, W, C8,
-                                                                         up, relu, out_pad);
+  if (up == 1)
+    spade_cls_bwd2_kernel<1, 4><<<dim3(bx, N), threads, 0, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out, (const uint4*)dout,
+                                                                 (uint4*)dx, mean_rstd, scratch, H, W, C8, relu, out_pad);
+  else
+    spade_cls_bwd2_kernel<2, 2><<<dim3(bx, N), threads, 0, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out, (const uint4*)dout,
+                                                                 (uint4*)dx, mean_rstd, scratch, H, W, C8, relu, out_pad);
   return LAUNCH_OK("spade_cls_bwd2_kernel");
 }
 

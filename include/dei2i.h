@@ -174,7 +174,9 @@ int dei2i_spade_bwd(const void* x, const void* gb, const void* out, const void* 
  * scratch fp32 [N,2,C].
  * out_pad > 0: `out` (and `dout` of the backward) is [N, H+2*out_pad, W+2*out_pad, C] and already carries the reflect
  * padding of the convolution that consumes it (architecture.py:228-233,320-337 padding_mode='reflect'): the forward writes the
- * mirrored border itself, the backward folds the padded gradient while reading it. */
+ * mirrored border itself, the backward folds the padded gradient while reading it.
+ * The backward supports up = 1 or 2 (what architecture.py uses) and does not read `out`: the ReLU mask is re-evaluated from x
+ * with the forward's own expression (`out` stays in the signature; it may be NULL). */
 int dei2i_spade_cls_fwd(const void* x, const void* gb5, void* out, const float* stats, float* mean_rstd, int N, int H,
                         int W, int C, int up, int relu, float eps, int out_pad, dei2i_stream stream);
 int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* out, const void* dout, float* dgb5, void* dx,

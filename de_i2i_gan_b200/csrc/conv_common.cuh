@@ -119,6 +119,8 @@ int run_wgrad_narrow(const Gather& g, const void* dy, int Cout, int Cout_ld, int
 bool wgrad_c8_applicable(const Gather& g, int Cout_ld);  // needs g.C, g.ntaps, g.M only
 int wgrad_c8_splits(const Gather& g, int Cout_ld);
 int run_wgrad_c8(const Gather& g, const void* dy, int Cout, int Cout_ld, int Kf, float* partial, cudaStream_t st);
+bool conv_narrow_fwd_applicable(const Gather& g, int rows_ld);
+int run_conv_narrow_fwd(const Gather& g, const Epilogue& e, const void* wmat, int rows, int Kf, cudaStream_t st);
 bool conv_heads_fwd_applicable(const Gather& g, int rows_ld);
 int run_conv_heads_fwd(const Gather& g, const Epilogue& e, const void* wmat, int rows, int Kf, cudaStream_t st);
 bool wgrad_heads_applicable(const Gather& g, int Cout, int Cout_ld);

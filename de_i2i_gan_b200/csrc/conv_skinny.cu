@@ -930,6 +930,71 @@ int run_conv_heads_fwd(const Gather& g, const Epilogue& e, const void* wmat, int
   return check_cuda(cudaGetLastError(), "conv_heads_fwd_kernel launch");
 }
 
+// ----------------------------------------------------------------------------------------------------------------------
+// Forward of the discriminator's two output convolutions (2048 -> 1, 3x3 on the 4x4 map; 2048 -> label_nc, 4x4 'valid':
+// discriminator.py:60-75): <= 8 output channels, a handful of output pixels and K = taps * Cin of 18-32 k.  On the UMMA path
+// that is ONE CTA walking 300-500 K blocks (145 us); here one CTA per output pixel streams its taps (contiguous 16-byte
+// chunks of x against the <= 8 weight rows, which stay in L1/L2) and reduces in a fixed order.
+__global__ void __launch_bounds__(256)
+conv_narrow_fwd_kernel(const Gather g, const Epilogue e, const __nv_bfloat16* __restrict__ w, int rows_w, int Kf) {
+  __shared__ float red[8][8];
+  const int m = blockIdx.x;
+  const int HoWo = g.Ho * g.Wo;
+  const int img = m / HoWo, rem = m - img * HoWo;
+  const int oy = rem / g.Wo, ox = rem - oy * g.Wo;
+  const int c8n = g.C >> 3;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int tap = 0; tap < g.ntaps; ++tap) {
+    const int r = tap / g.kw, s_ = tap - r * g.kw;
+    const int iy = oy * g.stride + r - g.pad, ix = ox * g.stride + s_ - g.pad;
+    if (iy < 0 || iy >= g.Hl || ix < 0 || ix >= g.Wl) continue;  // zero frame (block-uniform)
+    const uint4* xp = reinterpret_cast<const uint4*>(g.src + (((long long)img * g.Hs + iy) * g.Ws + ix) * g.C);
+    const uint4* wp = reinterpret_cast<const uint4*>(w + (long long)tap * g.C);
+    for (int c8 = threadIdx.x; c8 < c8n; c8 += blockDim.x) {
+      float fx[8];
+      unpack8_bf16(__ldg(xp + c8), fx);
+#pragma unroll
+      for (int co = 0; co < 8; ++co) {
+        if (co < rows_w) {
+          float fw[8];
+          unpack8_bf16(__ldg(wp + (long long)co * (Kf >> 3) + c8), fw);
+#pragma unroll
+          for (int k = 0; k < 8; ++k) acc[co] = fmaf(fx[k], fw[k], acc[co]);
+        }
+      }
+    }
+  }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+  for (int co = 0; co < 8; ++co) {
+    float v = acc[co];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) red[warp][co] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 8 && (int)threadIdx.x < e.ld) {
+    const int co = threadIdx.x;
+    float v = 0.f;
+    for (int wv = 0; wv < 8; ++wv) v += red[wv][co];
+    const float osc = e.scale != nullptr ? __ldg(e.scale) : 1.f;
+    v = v * osc + ((e.bias != nullptr && co < e.ncols) ? __ldg(e.bias + co) : 0.f);
+    v = apply_act(v, e.act);
+    if (e.out_fp32) reinterpret_cast<float*>(e.out)[(long long)m * e.ld + co] = v;
+    else reinterpret_cast<__nv_bfloat16*>(e.out)[(long long)m * e.ld + co] = __float2bfloat16(v);
+  }
+}
+
+bool conv_narrow_fwd_applicable(const Gather& g, int rows_ld) {
+  return g_tune_conv_path == 0 && g.mode == 0 && rows_ld == 8 && g.C % 8 == 0 && g.Hs == g.Hl && g.Ws == g.Wl &&
+         !(g.pad_mode == DEI2I_PAD_REFLECT && g.pad > 0) && (long long)g.ntaps * g.C >= 4096 && g.M <= 8192;
+}
+int run_conv_narrow_fwd(const Gather& g, const Epilogue& e, const void* wmat, int rows, int Kf, cudaStream_t st) {
+  conv_narrow_fwd_kernel<<<(unsigned)g.M, 256, 0, st>>>(g, e, (const __nv_bfloat16*)wmat, rows < 8 ? rows : 8, Kf);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "conv_narrow_fwd_kernel launch");
+}
+
 bool wgrad_heads_applicable(const Gather& g, int Cout, int Cout_ld) {
   return g.mode == 0 && g.kh == 3 && g.kw == 3 && g.stride == 1 && g.C % 64 == 0 && kHeadsWarps % (g.C / 64) == 0 && g.C <= 128 &&
          Cout <= 4 && Cout_ld == 8 && g.Hs == g.Hl && g.Ws == g.Wl && !(g.pad_mode == DEI2I_PAD_REFLECT && g.pad > 0);

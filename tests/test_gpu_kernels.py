@@ -75,6 +75,7 @@ CONV_CASES = {
     "tma_dgrad_s2_to8": (2, 3, 34, 34, 64, 4, 2, 0, "zeros", False, None),   # D conv0 geometry: N tile mostly padding
     "tma_ragged_m100": (1, 64, 10, 10, 64, 3, 1, 1, "zeros", False, None),
     "tma_ragged_m75_s2": (3, 64, 12, 12, 72, 4, 2, 0, "zeros", False, None),
+    "spade_cls_gb_5x5": (32, 128, 5, 5, 512, 3, 1, 1, "zeros", True, None),  # gamma|beta on the border-class map: M = 800
     "narrow_16_32": (2, 16, 12, 12, 32, 3, 1, 1, "reflect", False, None),   # reduced-width nets of the golden fixtures
     "narrow_s2_8_16": (2, 8, 16, 16, 16, 4, 2, 1, "reflect", False, None),
     # skinny kernels (conv_skinny.cu) at the geometries the model path produces (reflect padding pre-applied)
@@ -86,6 +87,10 @@ CONV_CASES = {
     "heads_zero_64_wide": (3, 64, 9, 150, 4, 3, 1, 1, "zeros", False, None),   # 5 pixel chunks, zero frame, image restarts
     "heads_valid_64_rows": (2, 64, 163, 34, 3, 3, 1, 0, "zeros", False, None),  # > 148 output rows per image: multi-row strips
     "d_cls_valid4x4": (4, 128, 4, 4, 6, 4, 1, 0, "zeros", False, None),
+    # discriminator outputs at full width (conv_narrow_fwd_kernel: <= 8 output channels, K = taps * 2048)
+    "d_cls_full_k32768": (4, 2048, 4, 4, 6, 4, 1, 0, "zeros", True, None),
+    "d_src_full_valid3x3": (2, 2048, 6, 6, 1, 3, 1, 0, "zeros", False, None),
+    "d_src_full_zero3x3": (2, 1024, 4, 4, 1, 3, 1, 1, "zeros", False, None),
 }
 
 
@@ -200,7 +205,7 @@ def test_conv_heads_fwd_epilogue():
 DGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "spade_gb_512", "heads_4", "ragged_m", "d_src_1", "cls_valid_k2",
                "narrow_16_32", "narrow_s2_8_16", "tma_valid3x3", "tma_zero3x3_256", "tma_persistent_200tiles", "tma_valid4x4s2",
                "tma_valid7x7", "tma_ragged_m100", "tma_ragged_m75_s2", "tma_dgrad_s2_to8", "heads_valid_4",
-               "heads_valid_128_zero", "d_cls_valid4x4", "c8_stem_valid7x7"]
+               "heads_valid_128_zero", "d_cls_valid4x4", "c8_stem_valid7x7", "spade_cls_gb_5x5"]
 
 
 @pytest.mark.parametrize("case", DGRAD_CASES)
@@ -225,7 +230,8 @@ WGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "stem7x7", "spade_shared_8
                "ragged_m", "d_conv0", "d_src_1", "cls_valid_k2", "narrow_16_32", "narrow_s2_8_16", "tma_valid3x3",
                "tma_zero3x3_256", "tma_persistent_200tiles", "tma_valid4x4s2", "tma_dgrad_s2_to8", "c8_stem_valid7x7",
                "c8_zero3x3_nores", "c8_spade_shared_big", "spade_shared_1x1seg", "heads_valid_4", "heads_valid_128_zero",
-               "d_cls_valid4x4", "heads_zero_64_wide", "heads_valid_64_rows"]
+               "d_cls_valid4x4", "heads_zero_64_wide", "heads_valid_64_rows", "tma_ragged_m100", "tma_ragged_m75_s2",
+               "spade_cls_gb_5x5"]
 
 
 @pytest.mark.parametrize("case", WGRAD_CASES)

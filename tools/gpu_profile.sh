@@ -8,5 +8,5 @@ L=$(python -c "import json;print(json.loads(open('gpurun_out/plain.log').read().
 echo "launches per step: $L"
 ncu --metrics gpu__time_duration.sum --clock-control none --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
 echo "== ncu list exit $?"; tail -n 3 gpurun_out/ncu_list.log | cut -c1-300
-python tools/summarize_launches.py gpurun_out/launches.csv $L > gpurun_out/launch_summary.txt 2>&1
+python tools/summarize_launches.py gpurun_out/launches.csv -1 > gpurun_out/launch_summary.txt 2>&1
 head -n 60 gpurun_out/launch_summary.txt

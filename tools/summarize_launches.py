@@ -1,4 +1,6 @@
-"""Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list: per-kernel totals over the LAST n launches."""
+"""Summarise an `ncu --metrics gpu__time_duration.sum --csv` launch list: per-kernel totals over the LAST n launches, or
+(n = -1) over the last whole training step = everything after the optimizer launch that ended the previous step (the list
+holds torch's own kernels too, so bench.py's `gpu_launches` per step is not the right count)."""
 import csv
 import re
 import sys
@@ -15,7 +17,11 @@ for r in csv.DictReader(lines):
     unit = r.get("Metric Unit", "ns")
     ns = v * {"ns": 1.0, "us": 1e3, "usecond": 1e3, "ms": 1e6, "msecond": 1e6, "nsecond": 1.0, "s": 1e9, "second": 1e9}.get(unit, 1.0)
     rows.append((re.sub(r"\(.*", "", r["Kernel Name"]), ns))
-if last_n:
+if last_n == -1:
+    opt = [i for i, (n, _) in enumerate(rows) if "adam_dev_kernel" in n]  # two per step: D then G
+    assert len(opt) >= 3, "need at least two steps in the list"
+    rows = rows[opt[-3] + 1: opt[-1] + 1]
+elif last_n:
     rows = rows[-last_n:]
 agg = defaultdict(lambda: [0, 0.0])
 for name, ns in rows:

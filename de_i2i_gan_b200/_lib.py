@@ -19,6 +19,11 @@ class ConvEpilogue(C.Structure):
                 ("act", C.c_int), ("out_fp32", C.c_int)]
 
 
+class SnItem(C.Structure):  # dei2i_sn_item
+    _fields_ = [("w", C.c_void_p), ("u", C.c_void_p), ("v", C.c_void_p), ("inv_sigma", C.c_void_p), ("u_snap", C.c_void_p),
+                ("v_snap", C.c_void_p), ("rows", C.c_int), ("cols", C.c_int)]
+
+
 _P, _I, _F, _LL, _SZ = C.c_void_p, C.c_int, C.c_float, C.c_longlong, C.c_size_t
 
 # name -> (restype, argtypes); mirrors include/dei2i.h one to one
@@ -35,6 +40,8 @@ SIGNATURES = {
     "dei2i_conv2d_wgrad_workspace": (_SZ, [C.POINTER(ConvGeom), _I]),
     "dei2i_conv2d_wgrad": (_I, [_P, _P, _P, _I, _F, C.POINTER(ConvGeom), _P, _P, _P, _P, _P, _SZ, _P]),
     "dei2i_spectral_norm": (_I, [_P, _P, _P, _I, _I, _I, _F, _P, _P, _P]),
+    "dei2i_spectral_norm_multi_scratch": (_SZ, [C.POINTER(SnItem), _I]),
+    "dei2i_spectral_norm_multi": (_I, [C.POINTER(SnItem), _I, _I, _F, _P, _SZ, _P]),
     "dei2i_nchw_to_nhwc": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
     "dei2i_upsample_pad_fwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P]),
     "dei2i_upsample_pad_bwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P]),

@@ -211,6 +211,114 @@ __global__ void sn_finish_u_kernel(const float* __restrict__ s, int rows, float 
   }
 }
 
+// ---- the same four phases for up to kSnBatch weights per launch (a network has ~45 spectral-normalised convolutions, most
+// of them a few hundred KB: per-weight launches are pure launch latency).  Identical arithmetic and summation order as the
+// single-weight kernels above; the descriptor table travels by value in the kernel parameters (CUDA-graph friendly).
+constexpr int kSnBatch = 40;
+struct SnBatch {
+  const float* w[kSnBatch];
+  float* u[kSnBatch];
+  float* v[kSnBatch];
+  float* inv_sigma[kSnBatch];
+  float* u_snap[kSnBatch];  // copies of the updated u / v for the backward (may be NULL)
+  float* v_snap[kSnBatch];
+  int rows[kSnBatch], cols[kSnBatch], rs[kSnBatch], rows_per[kSnBatch];
+  int s_off[kSnBatch], p_off[kSnBatch];  // offsets of s[rows] and partial[rs, cols] in the scratch buffer
+  int blk1[kSnBatch + 1], blk3[kSnBatch + 1];  // block prefix sums of phases 1 and 3
+  int count;
+};
+DEVINL int sn_find(const int* prefix, int count, int b) {
+  int i = 0;
+  while (i + 1 < count && b >= prefix[i + 1]) ++i;
+  return i;
+}
+__global__ void sn_multi_wt_u_kernel(const __grid_constant__ SnBatch t, float* __restrict__ scratch) {
+  const int i = sn_find(t.blk1, t.count, blockIdx.x);
+  const int cols = t.cols[i], rows = t.rows[i];
+  const int bx = (cols + 255) / 256;
+  const int lb = blockIdx.x - t.blk1[i];
+  const int by = lb / bx;
+  const int col = (lb - by * bx) * 256 + threadIdx.x;
+  if (col >= cols) return;
+  const int r0 = by * t.rows_per[i], r1 = min(rows, r0 + t.rows_per[i]);
+  const float* w = t.w[i];
+  const float* u = t.u[i];
+  float acc = 0.f;
+#pragma unroll 4
+  for (int r = r0; r < r1; ++r) acc += __ldg(w + (long long)r * cols + col) * __ldg(u + r);
+  scratch[t.p_off[i] + (long long)by * cols + col] = acc;
+}
+__global__ void sn_multi_finish_v_kernel(const __grid_constant__ SnBatch t, const float* __restrict__ scratch, float eps) {
+  __shared__ float sh[32];
+  const int i = blockIdx.x;
+  const int cols = t.cols[i], rs = t.rs[i];
+  const float* partial = scratch + t.p_off[i];
+  float* v = t.v[i];
+  float ss = 0.f;
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) {
+    float a = 0.f;
+    for (int r = 0; r < rs; ++r) a += partial[(long long)r * cols + c];
+    v[c] = a;
+    ss += a * a;
+  }
+  const float nrm = sqrtf(block_sum(ss, sh));
+  const float inv = 1.f / fmaxf(nrm, eps);
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) {
+    const float a = v[c] * inv;
+    v[c] = a;
+    if (t.v_snap[i] != nullptr) t.v_snap[i][c] = a;
+  }
+}
+__global__ void sn_multi_w_v_kernel(const __grid_constant__ SnBatch t, float* __restrict__ scratch) {
+  const int i = sn_find(t.blk3, t.count, blockIdx.x);
+  const int row = (blockIdx.x - t.blk3[i]) * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= t.rows[i]) return;
+  const int cols = t.cols[i];
+  const int lane = threadIdx.x & 31;
+  const float* wr = t.w[i] + (long long)row * cols;
+  const float* v = t.v[i];
+  float acc = 0.f;
+  for (int c = lane; c < cols; c += 32) acc += __ldg(wr + c) * v[c];
+  acc = warp_sum(acc);
+  if (lane == 0) scratch[t.s_off[i] + row] = acc;
+}
+__global__ void sn_multi_finish_u_kernel(const __grid_constant__ SnBatch t, const float* __restrict__ scratch, float eps, int do_iter) {
+  __shared__ float sh[32];
+  const int i = blockIdx.x;
+  const int rows = t.rows[i];
+  const float* s = scratch + t.s_off[i];
+  float* u = t.u[i];
+  float* inv_sigma = t.inv_sigma[i];
+  float acc = 0.f;
+  if (do_iter) {
+    for (int r = threadIdx.x; r < rows; r += blockDim.x) acc += s[r] * s[r];
+    const float ss = block_sum(acc, sh);
+    const float inv = 1.f / fmaxf(sqrtf(ss), eps);
+    for (int r = threadIdx.x; r < rows; r += blockDim.x) {
+      const float a = s[r] * inv;
+      u[r] = a;
+      if (t.u_snap[i] != nullptr) t.u_snap[i][r] = a;
+    }
+    if (threadIdx.x == 0) {
+      const float sigma = ss * inv;
+      inv_sigma[0] = 1.f / sigma;
+      inv_sigma[1] = sigma;
+    }
+  } else {
+    for (int r = threadIdx.x; r < rows; r += blockDim.x) {
+      acc += s[r] * u[r];
+      if (t.u_snap[i] != nullptr) t.u_snap[i][r] = u[r];
+    }
+    if (t.v_snap[i] != nullptr)
+      for (int c = threadIdx.x; c < t.cols[i]; c += blockDim.x) t.v_snap[i][c] = t.v[i][c];
+    const float sigma = block_sum(acc, sh);
+    if (threadIdx.x == 0) {
+      inv_sigma[0] = 1.f / sigma;
+      inv_sigma[1] = sigma;
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------ layout at the model edge
 __global__ void nchw_to_nhwc_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int N, int C, int HW, int C_ld) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;  // pixel index n*HW + p
@@ -1409,6 +1517,51 @@ extern "C" int dei2i_spectral_norm(const float* w, float* u, float* v, int rows,
   if (int rc = LAUNCH_OK("sn_w_v_kernel")) return rc;
   sn_finish_u_kernel<<<1, 1024, 0, ST>>>(s, rows, eps, do_power_iter, u, inv_sigma);
   return LAUNCH_OK("sn_finish_u_kernel");
+}
+
+extern "C" size_t dei2i_spectral_norm_multi_scratch(const dei2i_sn_item* items, int count) {
+  size_t n = 0;
+  for (int i = 0; i < count; ++i) n += (size_t)items[i].rows + 17 * (size_t)items[i].cols;
+  return n;
+}
+extern "C" int dei2i_spectral_norm_multi(const dei2i_sn_item* items, int count, int do_power_iter, float eps, float* scratch,
+                                         size_t scratch_floats, dei2i_stream stream) {
+  DEI2I_REQUIRE(items && count >= 0 && scratch, "spectral_norm_multi: bad arguments");
+  DEI2I_REQUIRE(scratch_floats >= dei2i_spectral_norm_multi_scratch(items, count), "spectral_norm_multi: scratch too small");
+  size_t off = 0;
+  for (int base = 0; base < count; base += kSnBatch) {
+    SnBatch t;
+    memset(&t, 0, sizeof(t));
+    t.count = count - base < kSnBatch ? count - base : kSnBatch;
+    for (int j = 0; j < t.count; ++j) {
+      const dei2i_sn_item& it = items[base + j];
+      DEI2I_REQUIRE(it.w && it.u && it.v && it.inv_sigma && it.rows > 0 && it.cols > 0, "spectral_norm_multi: bad item %d", base + j);
+      t.w[j] = it.w; t.u[j] = it.u; t.v[j] = it.v; t.inv_sigma[j] = it.inv_sigma; t.u_snap[j] = it.u_snap; t.v_snap[j] = it.v_snap;
+      t.rows[j] = it.rows; t.cols[j] = it.cols;
+      int rs = (it.rows + 127) / 128;  // same row split as dei2i_spectral_norm
+      if (rs > 16) rs = 16;
+      const int rows_per = (it.rows + rs - 1) / rs;
+      rs = (it.rows + rows_per - 1) / rows_per;
+      t.rs[j] = rs; t.rows_per[j] = rows_per;
+      DEI2I_REQUIRE(off + it.rows + (size_t)rs * it.cols < (1ull << 31), "spectral_norm_multi: scratch offsets exceed 32 bits");
+      t.s_off[j] = (int)off; off += it.rows;
+      t.p_off[j] = (int)off; off += (size_t)17 * it.cols;
+      t.blk1[j + 1] = t.blk1[j] + ((it.cols + 255) / 256) * rs;
+      t.blk3[j + 1] = t.blk3[j] + (it.rows + 7) / 8;
+    }
+    if (t.count == 0) break;
+    if (do_power_iter) {
+      sn_multi_wt_u_kernel<<<t.blk1[t.count], 256, 0, ST>>>(t, scratch);
+      if (int rc = LAUNCH_OK("sn_multi_wt_u_kernel")) return rc;
+      sn_multi_finish_v_kernel<<<t.count, 1024, 0, ST>>>(t, scratch, eps);
+      if (int rc = LAUNCH_OK("sn_multi_finish_v_kernel")) return rc;
+    }
+    sn_multi_w_v_kernel<<<t.blk3[t.count], 256, 0, ST>>>(t, scratch);
+    if (int rc = LAUNCH_OK("sn_multi_w_v_kernel")) return rc;
+    sn_multi_finish_u_kernel<<<t.count, 1024, 0, ST>>>(t, scratch, eps, do_power_iter);
+    if (int rc = LAUNCH_OK("sn_multi_finish_u_kernel")) return rc;
+  }
+  return 0;
 }
 
 extern "C" int dei2i_nchw_to_nhwc(const float* src, void* dst, int N, int C, int H, int W, int C_ld, dei2i_stream stream) {

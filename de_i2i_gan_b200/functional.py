@@ -7,6 +7,8 @@ only at the model edge (images, logits, losses), exactly where the reference's L
 from contextlib import contextmanager
 from typing import Optional
 
+import os
+
 import torch
 from torch.autograd import Function
 
@@ -64,14 +66,57 @@ def _pack(w: torch.Tensor, spec: ConvSpec):
     return packed
 
 
+SN_MULTI = os.environ.get("DEI2I_SN_MULTI", "1") != "0"
+_sn_ready = {}  # id(conv) -> (inv_sigma, u_snapshot, v_snapshot, training) produced by prefetch_spectral_norm, consumed once
+
+
+_sn_recording = {}  # id(net) -> set of id(conv) seen by prepare_conv / rowpack_conv since that net's first forward
+
+
+def prefetch_spectral_norm(net: torch.nn.Module, training: bool):
+    """Power iteration of the spectral-normalised convolutions of `net` in four launches (ops.spectral_norm_multi) at the top
+    of its forward, instead of four launches + two copies per layer.  Same per-forward semantics as torch.nn.utils.spectral_norm
+    (architecture.py:68-71): exactly the wrapped convolutions that a forward call runs are iterated - which ones those are
+    (the learned shortcuts of some SPADE blocks exist but never run) is recorded during the net's first forward, which still
+    takes the per-layer path."""
+    if not SN_MULTI:
+        return
+    used = getattr(net, "_sn_used", None)
+    if used is None:
+        rec = _sn_recording.get(id(net))
+        if rec is None:  # first forward: record only
+            _sn_recording[id(net)] = set()
+            return
+        used = [m for m in net.modules() if hasattr(m, "weight_orig") and hasattr(m, "weight_u") and id(m) in rec]
+        net._sn_used = used
+        del _sn_recording[id(net)]
+    if not used:
+        return
+    with torch.no_grad():
+        res = ops.spectral_norm_multi([(m.weight_orig.detach(), m.weight_u, m.weight_v) for m in used], training)
+    for m, (inv, us, vs) in zip(used, res):
+        _sn_ready[id(m)] = (inv, us, vs, training)
+
+
+def _sn_lookup(conv, training):
+    for rec in _sn_recording.values():
+        rec.add(id(conv))
+    ready = _sn_ready.pop(id(conv), None)
+    return ready if ready is not None and ready[3] == training else None
+
+
 def prepare_conv(conv: torch.nn.Module, spec: ConvSpec, training: bool) -> Weights:
     """Spectral norm (one power iteration when training, torch.nn.utils.spectral_norm semantics: u, v updated in place
     per forward call, sigma from the updated vectors) + packed weights of W_orig; 1/sigma is applied in the conv epilogue."""
     if hasattr(conv, "weight_orig"):
         w = conv.weight_orig
-        with torch.no_grad():
-            inv = ops.spectral_norm(w.detach(), conv.weight_u, conv.weight_v, training)
-            sn = (w.detach(), conv.weight_u.clone(), conv.weight_v.clone(), inv)
+        ready = _sn_lookup(conv, training)
+        if ready is not None:
+            inv, sn = ready[0], (w.detach(), ready[1], ready[2], ready[0])
+        else:
+            with torch.no_grad():
+                inv = ops.spectral_norm(w.detach(), conv.weight_u, conv.weight_v, training)
+                sn = (w.detach(), conv.weight_u.clone(), conv.weight_v.clone(), inv)
         w_fwd, w_dg = _pack(w, spec)
         return Weights(w_fwd, w_dg, inv, sn)
     w_fwd, w_dg = _pack(conv.weight, spec)
@@ -238,9 +283,13 @@ def rowpack_conv(x: torch.Tensor, conv_mod, spec: ConvSpec, training: bool) -> N
     sn = scale = None
     if hasattr(conv_mod, "weight_orig"):
         w = conv_mod.weight_orig
-        with torch.no_grad():
-            inv = ops.spectral_norm(w.detach(), conv_mod.weight_u, conv_mod.weight_v, training)
-            sn = (w.detach(), conv_mod.weight_u.clone(), conv_mod.weight_v.clone(), inv)
+        ready = _sn_lookup(conv_mod, training)
+        if ready is not None:
+            inv, sn = ready[0], (w.detach(), ready[1], ready[2], ready[0])
+        else:
+            with torch.no_grad():
+                inv = ops.spectral_norm(w.detach(), conv_mod.weight_u, conv_mod.weight_v, training)
+                sn = (w.detach(), conv_mod.weight_u.clone(), conv_mod.weight_v.clone(), inv)
         scale = inv
     else:
         w = conv_mod.weight

@@ -62,6 +62,7 @@ class DefectGanDiscriminator(BaseNetwork):
         """(src_logits [B,1,h,h], cls_logits [B,label_nc]) like discriminator.py:92-98."""
         assert isinstance(x, torch.Tensor), "x must be Original Images: Torch.Tensor"
         feat = Fn.to_nhwc(x)
+        Fn.prefetch_spectral_norm(self, self.training)
         for blk in self.enc_blk:
             feat = blk(feat)
         src = self._logits(self.src_clf, feat)

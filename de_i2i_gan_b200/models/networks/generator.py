@@ -93,6 +93,7 @@ class DefectGanGenerator(BaseNetwork):
         if labels.dim() == 2:
             labels = labels.reshape(labels.size(0), labels.size(1), 1, 1)
         seg = Fn.to_nhwc(labels.float())
+        Fn.prefetch_spectral_norm(self, self.training)
         feat = self.stem(x, carrier_out=True)
         for blk in self.enc_blk:
             feat = blk(feat, labels)

@@ -244,6 +244,35 @@ def spectral_norm(w, u, v, training: bool, eps: float = 1e-12):
     return out
 
 
+def spectral_norm_multi(weights, training: bool, eps: float = 1e-12):
+    """One power iteration (training) / sigma only (eval) for a list of (w, u, v) in four launches; u, v updated in place.
+    Returns [(inv_sigma[2], u_snapshot, v_snapshot)] - the snapshots are what the spectral-norm backward needs once later
+    forward passes have advanced u and v."""
+    if not weights:
+        return []
+    dev = weights[0][0].device
+    n = len(weights)
+    rows = [w.shape[0] for w, _, _ in weights]
+    cols = [w.numel() // w.shape[0] for w, _, _ in weights]
+    out = torch.empty(n, 2, dtype=torch.float32, device=dev)
+    snap = torch.empty(sum(rows) + sum(cols), dtype=torch.float32, device=dev)
+    items = (_lib.SnItem * n)()
+    off, res = 0, []
+    for i, (w, u, v) in enumerate(weights):
+        _chk_f32(w, "w")
+        us, vs = snap[off:off + rows[i]], snap[off + rows[i]:off + rows[i] + cols[i]]
+        off += rows[i] + cols[i]
+        it = items[i]
+        it.w, it.u, it.v, it.inv_sigma, it.u_snap, it.v_snap = _p(w), _p(u), _p(v), _p(out[i]), _p(us), _p(vs)
+        it.rows, it.cols = rows[i], cols[i]
+        res.append((out[i], us, vs))
+    lib = _lib.load()
+    need = lib.dei2i_spectral_norm_multi_scratch(items, n)
+    scratch = torch.empty(need, dtype=torch.float32, device=dev)
+    check(lib.dei2i_spectral_norm_multi(items, n, int(training), eps, _p(scratch), need, _stream()), "dei2i_spectral_norm_multi")
+    return res
+
+
 def nchw_to_nhwc(x: torch.Tensor, c_ld: int = None):
     _chk_f32(x, "x")
     n, c, h, w = x.shape

@@ -104,6 +104,24 @@ int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int Cin_real, f
 int dei2i_spectral_norm(const float* w, float* u, float* v, int rows, int cols, int do_power_iter, float eps,
                         float* inv_sigma, float* scratch, dei2i_stream stream);
 
+/* The same power iteration for many weights in four launches (a DefectGAN network has ~45 spectral-normalised convolutions;
+ * architecture.py:68-71,109-112 wrap every one).  Arithmetic and summation order are those of dei2i_spectral_norm, so the
+ * results are bit-identical.  items is a HOST array.  u_snap / v_snap (optional, device) receive copies of the u / v the
+ * returned sigma belongs to - what the spectral-norm backward of dei2i_conv2d_wgrad needs after later calls have moved u, v on.
+ * scratch: dei2i_spectral_norm_multi_scratch(items, count) floats of device memory. */
+typedef struct dei2i_sn_item {
+  const float* w;
+  float* u;
+  float* v;
+  float* inv_sigma; /* [2]: 1/sigma, sigma */
+  float* u_snap;
+  float* v_snap;
+  int rows, cols;
+} dei2i_sn_item;
+size_t dei2i_spectral_norm_multi_scratch(const dei2i_sn_item* items, int count);
+int dei2i_spectral_norm_multi(const dei2i_sn_item* items, int count, int do_power_iter, float eps, float* scratch,
+                              size_t scratch_floats, dei2i_stream stream);
+
 /* ---- WGAN / StarGAN-v2 resampling (bf16 NHWC, C % 8 == 0) ----
  * nn.Upsample(scale_factor=up, 'nearest') fused with the zero padding of the following nn.Conv2d(padding='same'), which is
  * asymmetric for even kernels (WGanGenerator, generator.py:15-37: 4x4 'same' -> pad 1 left/top, 2 right/bottom):

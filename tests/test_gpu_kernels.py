@@ -641,3 +641,63 @@ def test_conv_tma_two_subtiles(case):
     e1, e2 = rel_err(from_dev(y, cout), ref.detach()), rel_err(from_dev(dx, cin), dx_ref)
     _report("conv_tma_ms2/" + case, err_fwd=e1, err_dgrad=e2)
     assert e1 < TOL_BF16 and e2 < TOL_BF16, (e1, e2)
+
+
+@pytest.mark.parametrize("training", [True, False])
+def test_spectral_norm_multi_matches_single(training):
+    """dei2i_spectral_norm_multi (four launches for a whole network) is bit-identical to the per-weight entry point."""
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(11)
+    shapes = [(64, 3, 7, 7), (128, 64, 4, 4), (256, 256, 3, 3), (2304, 40, 1, 1), (8, 2048, 3, 3)] + [(16 + i, 8 + i, 3, 3) for i in range(45)]
+    ws = [torch.randn(s_, generator=g).cuda() for s_ in shapes]
+    us = [F.normalize(torch.randn(s_[0], generator=g), dim=0).cuda() for s_ in shapes]
+    vs = [F.normalize(torch.randn(s_[1] * s_[2] * s_[3], generator=g), dim=0).cuda() for s_ in shapes]
+    u1, v1 = [u.clone() for u in us], [v.clone() for v in vs]
+    ref = [ops.spectral_norm(w, u, v, training).clone() for w, u, v in zip(ws, u1, v1)]
+    u2, v2 = [u.clone() for u in us], [v.clone() for v in vs]
+    got = ops.spectral_norm_multi(list(zip(ws, u2, v2)), training)
+    torch.cuda.synchronize()
+    for i, (inv, su, sv) in enumerate(got):
+        assert torch.equal(inv, ref[i]), (i, inv, ref[i])
+        assert torch.equal(u2[i], u1[i]) and torch.equal(v2[i], v1[i]), i
+        assert torch.equal(su, u2[i]) and torch.equal(sv, v2[i]), i
+        if not training:
+            assert torch.equal(u2[i], us[i]) and torch.equal(v2[i], vs[i])
+    # sigma is the top singular value direction estimate: sanity against torch for the first weight
+    w0 = ws[2].reshape(256, -1)
+    assert abs(got[2][0][1].item() - torch.dot(u2[2], w0 @ v2[2]).item()) < 1e-3 * got[2][0][1].item()
+
+
+def test_spectral_norm_prefetch_in_networks():
+    """The generator / discriminator forward consumes every prefetched entry and leaves u, v exactly as the per-layer path."""
+    from pathlib import Path
+    import copy
+    from de_i2i_gan_b200 import functional as Fn, options
+    from de_i2i_gan_b200.models.networks.generator import DefectGanGenerator
+    from de_i2i_gan_b200.models.networks.discriminator import DefectGanDiscriminator
+    opt = options.readme_recipe(image_size=128, batch_size=2, ckpt_dir=Path("/tmp/dei2i_sn_test"), ngf=8, ndf=8)
+    torch.manual_seed(5)
+    G0, D0 = DefectGanGenerator(opt).cuda(), DefectGanDiscriminator(opt).cuda()
+    x = torch.randn(2, 3, 128, 128, device="cuda").clamp_(-1, 1)
+    lab = torch.zeros(2, opt.label_nc, device="cuda")
+    lab[:, 1] = 1
+    state = {}
+    for multi in (True, False):
+        Fn.SN_MULTI = multi
+        try:
+            G, D = copy.deepcopy(G0), copy.deepcopy(D0)
+            for _ in range(3):  # the first forward records which wrapped convolutions run, the later ones prefetch them
+                with Fn.weight_cache():
+                    out = G(x, lab)
+                    D(x)
+            assert not Fn._sn_ready, "prefetched spectral-norm entries left unconsumed"
+            assert not multi or (len(G._sn_used) == 17 and len(D._sn_used) == 6)
+        finally:
+            Fn.SN_MULTI = True
+        state[multi] = {f"{i}.{n}": b.clone() for i, net in enumerate((G, D)) for n, b in net.named_buffers()
+                        if n.endswith("weight_u") or n.endswith("weight_v")}
+    assert len(state[True]) == 2 * (20 + 6)
+    for n, b in state[True].items():
+        assert torch.equal(b, state[False][n]), n
+        if "conv_s" in n:  # learned shortcuts that never run keep their initial vectors
+            assert torch.equal(b, dict(G0.named_buffers())[n[2:]].to(b.device))

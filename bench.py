@@ -208,7 +208,10 @@ def run_ours(args):
     bg, labels, df = R.synthetic_batch(B, H, seed=rank)  # per-rank shard of the global batch
     host = [t.pin_memory() for t in (bg, labels, df)]
     resident = [t.to(dev) for t in host]
-    h2d = 2 * sum(t.numel() * t.element_size() for t in host)  # D-step and G-step each copy bg, labels, df
+    # one trip over PCIe per iteration, as the reference's loop does (data.to(device) once, then D-step and G-step,
+    # defectgan_trainer.py:91-112): the D-step copies bg, labels, df from the pinned host batch, the G-step of the same
+    # iteration takes a device-to-device copy of them (GraphedStep._stage)
+    h2d = sum(t.numel() * t.element_size() for t in host)
     d2h = 7 * 4                                               # 2 + 5 loss scalars
 
     def step(inputs):

@@ -255,13 +255,16 @@ def spectral_norm_multi(weights, training: bool, eps: float = 1e-12):
     rows = [w.shape[0] for w, _, _ in weights]
     cols = [w.numel() // w.shape[0] for w, _, _ in weights]
     out = torch.empty(n, 2, dtype=torch.float32, device=dev)
-    snap = torch.empty(sum(rows) + sum(cols), dtype=torch.float32, device=dev)
+    al = lambda k: (k + 63) // 64 * 64  # 256-byte aligned snapshots: the wgrad second pass reads v with 16-byte loads
+    snap = torch.empty(sum(al(r) for r in rows) + sum(al(c) for c in cols), dtype=torch.float32, device=dev)
     items = (_lib.SnItem * n)()
     off, res = 0, []
     for i, (w, u, v) in enumerate(weights):
         _chk_f32(w, "w")
-        us, vs = snap[off:off + rows[i]], snap[off + rows[i]:off + rows[i] + cols[i]]
-        off += rows[i] + cols[i]
+        us = snap[off:off + rows[i]]
+        off += al(rows[i])
+        vs = snap[off:off + cols[i]]
+        off += al(cols[i])
         it = items[i]
         it.w, it.u, it.v, it.inv_sigma, it.u_snap, it.v_snap = _p(w), _p(u), _p(v), _p(out[i]), _p(us), _p(vs)
         it.rows, it.cols = rows[i], cols[i]

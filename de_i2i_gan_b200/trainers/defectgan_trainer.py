@@ -27,9 +27,25 @@ class GraphedStep:
     stream: libdei2i.so never synchronises or allocates, the noise maps come from torch's graph-safe Philox state,
     spectral-norm u/v, BN running stats and Adam state are updated in place at fixed addresses."""
 
-    def __init__(self, body, optimizer, enabled, pool):
+    def __init__(self, body, optimizer, enabled, pool, staged=None, reuse_staged=False):
         self.body, self.optimizer, self.enabled, self.pool = body, optimizer, enabled, pool
+        self.reuse_staged = reuse_staged  # only the G-step reuses (the D-step of every iteration reads the host batch afresh)
         self.states = {}
+        # host tensors already on the device: (data_ptr, version, shape, dtype) -> static buffer of the step that copied them last.
+        # The D-step and the G-step of one iteration are fed the same batch (defectgan_trainer.py:91-112): the second step takes
+        # a device-to-device copy instead of a second trip over PCIe.  Shared between the two GraphedSteps of a trainer.
+        self.staged = staged if staged is not None else {}
+
+    def _stage(self, statics, inputs):
+        fresh = {}
+        for s, t in zip(statics, inputs):
+            key = (t.data_ptr(), t._version, tuple(t.shape), t.dtype)
+            src = self.staged.get(key) if (self.reuse_staged and not t.is_cuda) else None
+            s.copy_(src if src is not None else t, non_blocking=True)
+            if not t.is_cuda:
+                fresh[key] = s
+        self.staged.clear()
+        self.staged.update(fresh)
 
     def __call__(self, *inputs):
         if not self.enabled:
@@ -42,8 +58,7 @@ class GraphedStep:
         if "graph" not in st:
             dev = self.optimizer.flat_params[0].device
             st["static"] = [torch.empty(t.shape, dtype=t.dtype, device=dev) for t in inputs]
-            for s, t in zip(st["static"], inputs):
-                s.copy_(t, non_blocking=True)
+            self._stage(st["static"], inputs)
             torch.cuda.synchronize()
             graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(graph, pool=self.pool[0]):
@@ -52,8 +67,7 @@ class GraphedStep:
                 self.pool[0] = graph.pool()
             st["graph"] = graph
         else:
-            for s, t in zip(st["static"], inputs):
-                s.copy_(t, non_blocking=True)
+            self._stage(st["static"], inputs)
         self.optimizer.advance()
         st["graph"].replay()
         return st["out"]
@@ -74,9 +88,9 @@ class DefectGanTrainer(BaseTrainer):
         if use_graph is None:
             use_graph = os.environ.get("DEI2I_CUDA_GRAPH", "1") != "0"
         use_graph = bool(use_graph) and torch.device(opt.device).type == "cuda"
-        pool = [None]
-        self._graphed = {"D": GraphedStep(self._d_body, self.optimizers["D"], use_graph, pool),
-                         "G": GraphedStep(self._g_body, self.optimizers["G"], use_graph, pool)}
+        pool, staged = [None], {}
+        self._graphed = {"D": GraphedStep(self._d_body, self.optimizers["D"], use_graph, pool, staged),
+                         "G": GraphedStep(self._g_body, self.optimizers["G"], use_graph, pool, staged, reuse_staged=True)}
 
     def _init_lr(self, opt):
         assert len(opt.lr) in (1, 2), f"length of lr must be 1 or 2, not {len(opt.lr)}"

@@ -513,6 +513,77 @@ __global__ void bn_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y
   }
 }
 
+// The same normalisation writing the reflect padding of the convolution that consumes it: y is [N, H+2p, W+2p, C], padded
+// pixel (hp, wp) is computed from its mirror source (a few % more pixels instead of a separate pad pass over the tensor;
+// the adjoint - folding the padded gradient - stays with dei2i_reflect_fold).  grid.y = image; thread = (8-channel group,
+// pixel lane) with scale / shift in registers.
+__global__ void bn_fwd_pad_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, const uint4* __restrict__ residual,
+                                  const float* __restrict__ stats, const float* __restrict__ gamma, const float* __restrict__ beta,
+                                  float* __restrict__ running_mean, float* __restrict__ running_var, float* __restrict__ save_mean,
+                                  float* __restrict__ save_rstd, long long npix, int H, int W, int C8, int training, float momentum,
+                                  float eps, int act, int pad) {
+  const int C = C8 * 8;
+  const int n = blockIdx.y;
+  const int c8 = threadIdx.x % C8;
+  const int lane = threadIdx.x / C8;
+  const int lanes = blockDim.x / C8;
+  const bool first = blockIdx.x == 0 && blockIdx.y == 0 && lane == 0;
+  float sc[8], sf[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int c = c8 * 8 + k;
+    float mean, var;
+    if (training) {
+      mean = stats[c] / (float)npix;
+      var = fmaxf(stats[C + c] / (float)npix - mean * mean, 0.f);
+      if (first) {
+        running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+        const float unb = npix > 1 ? var * (float)npix / (float)(npix - 1) : var;
+        running_var[c] = (1.f - momentum) * running_var[c] + momentum * unb;
+      }
+    } else {
+      mean = running_mean[c];
+      var = running_var[c];
+    }
+    const float rstd = rsqrtf(var + eps);
+    if (first && save_mean != nullptr) {
+      save_mean[c] = mean;
+      save_rstd[c] = rstd;
+    }
+    sc[k] = rstd * gamma[c];
+    sf[k] = beta[c] - mean * sc[k];
+  }
+  const int Hp = H + 2 * pad, Wp = W + 2 * pad;
+  const int npixp = Hp * Wp;
+  const int stride = gridDim.x * lanes;
+  const int sh_ = stride / Wp, sw_ = stride - sh_ * Wp;
+  int pix = blockIdx.x * lanes + lane;
+  int hp = pix / Wp, wp = pix - hp * Wp;
+  const uint4* xin = x + (long long)n * H * W * C8 + c8;
+  const uint4* rin = residual != nullptr ? residual + (long long)n * H * W * C8 + c8 : nullptr;
+  uint4* o = y + (long long)n * npixp * C8 + c8;
+  for (; pix < npixp; pix += stride) {
+    const int src = (reflect_idx(hp - pad, H) * W + reflect_idx(wp - pad, W)) * C8;
+    float f[8];
+    unpack8(__ldg(xin + src), f);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] = apply_act(fmaf(f[k], sc[k], sf[k]), act);
+    if (rin != nullptr) {
+      float r[8];
+      unpack8(__ldg(rin + src), r);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) f[k] += r[k];
+    }
+    o[(long long)pix * C8] = pack8(f);
+    wp += sw_;
+    hp += sh_;
+    if (wp >= Wp) {
+      wp -= Wp;
+      ++hp;
+    }
+  }
+}
+
 // pass 1 of the backward: per channel  sum(dz), sum(dz * xhat)   with dz = dy * act'(bn(x))
 __global__ void bn_bwd_reduce_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, const float* __restrict__ gamma,
                                      const float* __restrict__ beta, const float* __restrict__ mean, const float* __restrict__ rstd,
@@ -1615,6 +1686,26 @@ extern "C" int dei2i_bn_fwd(const void* x, void* y, const void* residual, const 
                                                             running_mean, running_var, save_mean, save_rstd, npix, C / 8, training,
                                                             momentum, eps, act);
   return LAUNCH_OK("bn_fwd_kernel");
+}
+
+extern "C" int dei2i_bn_fwd_pad(const void* x, void* y, const void* residual, const float* stats, const float* gamma,
+                                const float* beta, float* running_mean, float* running_var, float* save_mean, float* save_rstd, int N,
+                                int H, int W, int C, int training, float momentum, float eps, int act, int out_pad,
+                                dei2i_stream stream) {
+  DEI2I_REQUIRE(x && y && gamma && beta && running_mean && running_var && C % 8 == 0 && C <= 2048, "bn_fwd_pad: bad arguments");
+  DEI2I_REQUIRE(!training || stats, "bn_fwd_pad: training mode needs batch statistics");
+  DEI2I_REQUIRE(out_pad >= 1 && out_pad < H && out_pad < W, "bn_fwd_pad: out_pad (%d) must be in [1, min(H, W))", out_pad);
+  DEI2I_REQUIRE((long long)(H + 2 * out_pad) * (W + 2 * out_pad) * (C / 8) < (1ll << 31), "bn_fwd_pad: image too large");
+  const int C8 = C / 8;
+  const int lanes = 256 / C8 > 0 ? 256 / C8 : 1;
+  const long long npixp = (long long)(H + 2 * out_pad) * (W + 2 * out_pad);
+  unsigned bx = nblocks(npixp, lanes * 4);
+  const unsigned cap = (148 * 16 + N - 1) / N;
+  if (bx > cap) bx = cap;
+  bn_fwd_pad_kernel<<<dim3(bx, N), lanes * C8, 0, ST>>>((const uint4*)x, (uint4*)y, (const uint4*)residual, stats, gamma, beta,
+                                                        running_mean, running_var, save_mean, save_rstd, (long long)N * H * W, H, W,
+                                                        C8, training, momentum, eps, act, out_pad);
+  return LAUNCH_OK("bn_fwd_pad_kernel");
 }
 
 extern "C" int dei2i_bn_bwd(const void* x, const void* dy, void* dx, const float* gamma, const float* beta, const float* save_mean,

@@ -362,12 +362,13 @@ def conv_cat(x: Nhwc, conv_a, conv_b, spec: ConvSpec, out_fp32=False) -> Nhwc:
 
 class _BatchNorm(Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, bn, training, act):
+    def forward(ctx, x, gamma, beta, residual, bn, training, act, out_pad):
         y, save = ops.bn_fwd(x, gamma.detach(), beta.detach(), bn.running_mean, bn.running_var, training, act=act,
-                             residual=residual, momentum=bn.momentum if bn.momentum is not None else 0.1, eps=bn.eps)
+                             residual=residual, momentum=bn.momentum if bn.momentum is not None else 0.1, eps=bn.eps,
+                             out_pad=out_pad)
         if training and bn.num_batches_tracked is not None:
             bn.num_batches_tracked += 1
-        ctx.training, ctx.act, ctx.has_res = training, act, residual is not None
+        ctx.training, ctx.act, ctx.has_res, ctx.out_pad = training, act, residual is not None, out_pad
         ctx.save_for_backward(x, gamma, beta, save)
         return y
 
@@ -375,14 +376,19 @@ class _BatchNorm(Function):
     def backward(ctx, dy):
         x, gamma, beta, save = ctx.saved_tensors
         dy = dy.contiguous()
+        if ctx.out_pad:  # the consumer's gradient covers the padded frame: fold the mirrored border back (adjoint of the padding)
+            dy = ops.reflect_fold(dy, ctx.out_pad)
         dx, dg, db = ops.bn_bwd(x, dy, gamma.detach(), beta.detach(), save, ctx.training, act=ctx.act)
-        return dx, dg, db, (dy if ctx.has_res else None), None, None, None
+        return dx, dg, db, (dy if ctx.has_res else None), None, None, None, None
 
 
-def batch_norm(x: Nhwc, bn: torch.nn.BatchNorm2d, act=None, residual: Optional[Nhwc] = None) -> Nhwc:
+def batch_norm(x: Nhwc, bn: torch.nn.BatchNorm2d, act=None, residual: Optional[Nhwc] = None, out_pad: int = 0) -> Nhwc:
+    """out_pad > 0: the result already carries the reflect padding of the convolution that consumes it (Nhwc.pad)."""
     training = bn.training or not bn.track_running_stats
-    y = _BatchNorm.apply(x.t, bn.weight, bn.bias, residual.t if residual is not None else None, bn, training, act)
-    return Nhwc(y, x.c)
+    y = _BatchNorm.apply(x.t, bn.weight, bn.bias, residual.t if residual is not None else None, bn, training, act, out_pad)
+    out = Nhwc(y, x.c)
+    out.pad = out_pad
+    return out
 
 
 class _Spade(Function):

@@ -154,27 +154,36 @@ class ConvBlock(nn.Module):
     def _norm(self):  # not an attribute: registering the sub-module twice would duplicate its state-dict keys
         return self.conv_block[1] if self._has_norm else None
 
-    def forward(self, x, seg=None, residual=None, carrier_out=False):
+    def forward(self, x, seg=None, residual=None, carrier_out=False, out_pad=0):
+        """out_pad (carrier output with a BatchNorm only): the reflect padding of the NEXT convolution, written by the
+        BatchNorm kernel itself (`reflect_pad_of(next_block)`); the result then has ``.pad == out_pad``."""
         plain = not isinstance(x, Fn.Nhwc)
         conv = self.conv_block[0]
         if plain and ROWPACK_STEM and self._norm is not None and conv.bias is None and Fn.rowpack_applicable(self._spec):
             # generator stem (3->64, 7x7 reflect): row-packed image -> 7x1 convolution over 64 channels on the TMA kernels
             y = Fn.rowpack_conv(x, conv, self._spec, conv.training)
-            y = Fn.batch_norm(y, self._norm, act=self._act, residual=residual)
+            y = Fn.batch_norm(y, self._norm, act=self._act, residual=residual, out_pad=out_pad if carrier_out else 0)
             return y if carrier_out else _edge(y)
         xa = Fn.to_nhwc(x)
         if carrier_out:
             plain = False
+        if plain or self._norm is None:
+            out_pad = 0
+        spec = _consumer_spec(self._spec, xa)
         if self._norm is None:
             assert residual is None
-            y = Fn.conv(xa, conv, self._spec, conv.training, bias=conv.bias, act=self._act,
+            y = Fn.conv(xa, conv, spec, conv.training, bias=conv.bias, act=self._act,
                         out_fp32=self._act in ("tanh", "sigmoid"))
             if y.t.dtype != torch.bfloat16 and not plain:
                 y = Fn.Nhwc(y.t.to(torch.bfloat16), y.c)
         else:
-            y = Fn.conv(xa, conv, self._spec, conv.training, bias=conv.bias)
-            y = Fn.batch_norm(y, self._norm, act=self._act, residual=residual)
+            y = Fn.conv(xa, conv, spec, conv.training, bias=conv.bias)
+            y = Fn.batch_norm(y, self._norm, act=self._act, residual=residual, out_pad=out_pad)
         return _edge(y) if plain else y
+
+    def reflect_pad_in(self) -> int:
+        """Reflect padding this block's convolution wants on its input (what a producer may pre-write), else 0."""
+        return _fusable_pad(self._spec)
 
 
 def _edge(y: Fn.Nhwc) -> torch.Tensor:
@@ -264,9 +273,16 @@ class ResBlock(nn.Module):
     def forward(self, x, seg=None):
         plain = not isinstance(x, Fn.Nhwc)
         xa = Fn.to_nhwc(x)
-        y = self.res_block[0](xa)
+        y = self.res_block[0](xa, out_pad=self.res_block[1].reflect_pad_in())
         y = self.res_block[1](y, residual=xa)
         return Fn.from_nhwc(y) if plain else y
+
+
+def next_pad(blocks, i) -> int:
+    """Reflect padding the block after blocks[i] wants pre-written on its input (0 at the end of the chain or when the next
+    block is not a plain ConvBlock, e.g. a ResBlock that also uses its input as the residual)."""
+    nxt = blocks[i + 1] if i + 1 < len(blocks) else None
+    return nxt.reflect_pad_in() if isinstance(nxt, ConvBlock) else 0
 
 
 def _fusable_pad(spec: ConvSpec) -> int:

@@ -4,7 +4,7 @@ import torch
 from torch import nn
 
 from ... import functional as Fn
-from .architecture import ConvBlock
+from .architecture import ConvBlock, next_pad
 from .base_network import BaseNetwork
 
 
@@ -63,8 +63,9 @@ class DefectGanDiscriminator(BaseNetwork):
         assert isinstance(x, torch.Tensor), "x must be Original Images: Torch.Tensor"
         feat = Fn.to_nhwc(x)
         Fn.prefetch_spectral_norm(self, self.training)
-        for blk in self.enc_blk:
-            feat = blk(feat)
+        enc = list(self.enc_blk)
+        for i, blk in enumerate(enc):
+            feat = blk(feat, out_pad=next_pad(enc, i)) if isinstance(blk, ConvBlock) else blk(feat)
         src = self._logits(self.src_clf, feat)
         cls = self._logits(self.cls_clf, feat)
         return src, cls.reshape(cls.size(0), cls.size(1))

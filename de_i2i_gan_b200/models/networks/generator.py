@@ -4,7 +4,7 @@ from torch import nn
 
 from ... import functional as Fn
 from ...ops import ConvSpec
-from .architecture import ConvBlock, DeConvBlock, NormConvBlock, NormResBlock, ResBlock, _edge, _spec_of, same_frame
+from .architecture import ConvBlock, DeConvBlock, NormConvBlock, NormResBlock, ResBlock, _edge, _spec_of, next_pad, same_frame
 from .base_network import BaseNetwork
 
 
@@ -94,9 +94,10 @@ class DefectGanGenerator(BaseNetwork):
             labels = labels.reshape(labels.size(0), labels.size(1), 1, 1)
         seg = Fn.to_nhwc(labels.float())
         Fn.prefetch_spectral_norm(self, self.training)
-        feat = self.stem(x, carrier_out=True)
-        for blk in self.enc_blk:
-            feat = blk(feat, labels)
+        enc = list(self.enc_blk)
+        feat = self.stem(x, carrier_out=True, out_pad=next_pad([self.stem] + enc, 0))
+        for i, blk in enumerate(enc):
+            feat = blk(feat, labels, out_pad=next_pad(enc, i)) if isinstance(blk, ConvBlock) else blk(feat, labels)
         for blk in self.enc_res_blk:
             feat = blk(feat, labels)
         for blk in self.dec_res_blk:

@@ -395,12 +395,19 @@ def channel_stats(x, per_sample: bool):
     return stats
 
 
-def bn_fwd(x, gamma, beta, running_mean, running_var, training, act=None, residual=None, momentum=0.1, eps=1e-5):
+def bn_fwd(x, gamma, beta, running_mean, running_var, training, act=None, residual=None, momentum=0.1, eps=1e-5, out_pad=0):
+    """out_pad > 0: y is [N, H+2p, W+2p, C] and carries the reflect padding of its consumer (dei2i_bn_fwd_pad)."""
     _chk_act(x, "x")
     n, h, w, c = x.shape
-    y = torch.empty_like(x)
     stats = channel_stats(x, False) if training else None
     save = torch.empty(2, c, dtype=torch.float32, device=x.device)
+    if out_pad:
+        y = torch.empty(n, h + 2 * out_pad, w + 2 * out_pad, c, dtype=x.dtype, device=x.device)
+        check(_lib.load().dei2i_bn_fwd_pad(_p(x), _p(y), _p(residual), _p(stats), _p(gamma), _p(beta), _p(running_mean),
+                                           _p(running_var), _p(save[0]), _p(save[1]), n, h, w, c, int(training), momentum, eps,
+                                           ACT[act], int(out_pad), _stream()), "dei2i_bn_fwd_pad")
+        return y, save
+    y = torch.empty_like(x)
     check(_lib.load().dei2i_bn_fwd(_p(x), _p(y), _p(residual), _p(stats), _p(gamma), _p(beta), _p(running_mean),
                                    _p(running_var), _p(save[0]), _p(save[1]), n, h * w, c, int(training), momentum, eps,
                                    ACT[act], _stream()), "dei2i_bn_fwd")

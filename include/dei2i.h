@@ -166,6 +166,13 @@ int dei2i_channel_stats(const void* x, int N, int HW, int C, int per_sample, flo
 int dei2i_bn_fwd(const void* x, void* y, const void* residual, const float* stats, const float* gamma,
                  const float* beta, float* running_mean, float* running_var, float* save_mean, float* save_rstd,
                  int N, int HW, int C, int training, float momentum, float eps, int act, dei2i_stream stream);
+/* The same forward writing the reflect padding of the convolution that consumes it (ConvBlock -> ConvBlock chains of the
+ * discriminator and of the generator's encoder, architecture.py:95-100 padding_mode='reflect'): y is
+ * [N, H+2*out_pad, W+2*out_pad, C]; residual (optional) is unpadded like x.  The backward takes the gradient folded by
+ * dei2i_reflect_fold and calls dei2i_bn_bwd. */
+int dei2i_bn_fwd_pad(const void* x, void* y, const void* residual, const float* stats, const float* gamma, const float* beta,
+                     float* running_mean, float* running_var, float* save_mean, float* save_rstd, int N, int H, int W, int C,
+                     int training, float momentum, float eps, int act, int out_pad, dei2i_stream stream);
 /* backward of the above: dx, dgamma, dbeta (fp32 [C], written). y is the forward OUTPUT before the residual add
  * is NOT needed: the activation mask is recomputed from x. scratch: fp32 [2*C]. */
 int dei2i_bn_bwd(const void* x, const void* dy, void* dx, const float* gamma, const float* beta, const float* save_mean,

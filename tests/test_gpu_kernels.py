@@ -701,3 +701,25 @@ def test_spectral_norm_prefetch_in_networks():
         assert torch.equal(b, state[False][n]), n
         if "conv_s" in n:  # learned shortcuts that never run keep their initial vectors
             assert torch.equal(b, dict(G0.named_buffers())[n[2:]].to(b.device))
+
+
+@pytest.mark.parametrize("pad,act,with_res", [(1, "leaky_relu", False), (3, "relu", True), (1, None, True)])
+def test_bn_fwd_writes_consumer_padding(pad, act, with_res):
+    """dei2i_bn_fwd_pad == reflect_pad(dei2i_bn_fwd): output, saved statistics and running statistics."""
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(12)
+    n, c, h, w = 3, 64, 9, 11
+    x = to_dev(q(torch.randn(n, c, h, w, generator=g) * 1.5 + 0.3))
+    res = to_dev(q(torch.randn(n, c, h, w, generator=g))) if with_res else None
+    gamma, beta = (1 + 0.3 * torch.randn(c, generator=g)).cuda(), (0.2 * torch.randn(c, generator=g)).cuda()
+    rm0, rv0 = torch.zeros(c, device="cuda"), torch.ones(c, device="cuda")
+    rm1, rv1 = rm0.clone(), rv0.clone()
+    y0, save0 = ops.bn_fwd(x, gamma, beta, rm0, rv0, True, act=act, residual=res)
+    yp, savep = ops.bn_fwd(x, gamma, beta, rm1, rv1, True, act=act, residual=res, out_pad=pad)
+    torch.cuda.synchronize()
+    ref = ops.reflect_pad(y0, pad)
+    assert yp.shape == ref.shape
+    assert rel_err(yp.float(), ref.float()) < 1e-2  # one BF16 ulp where the two kernels contract the FMA differently
+    assert (yp != ref).float().mean().item() < 0.01
+    assert torch.allclose(savep, save0, rtol=1e-6, atol=1e-7) and torch.allclose(rm1, rm0, rtol=1e-6, atol=1e-7)
+    assert torch.allclose(rv1, rv0, rtol=1e-6, atol=1e-7)

@@ -18,10 +18,11 @@ from .ops import ConvSpec
 
 class Nhwc:
     """BF16 NHWC activation carrier. ``t``: [N,H,W,C_ld] (C_ld % 8 == 0), ``c``: real channels."""
-    __slots__ = ("t", "c", "cls5", "pad")
+    __slots__ = ("t", "c", "cls5", "pad", "key")
 
     def __init__(self, t: torch.Tensor, c: int):
         self.t, self.c, self.cls5 = t, c, None
+        self.key = None  # identity of the tensor a label map was made from (SPADE caches gamma|beta per label tensor)
         self.pad = 0  # pixels of reflect padding already present on every side of ``t`` (written by the producer for its consumer)
 
     @property

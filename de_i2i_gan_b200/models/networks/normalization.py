@@ -50,8 +50,19 @@ class SPADE(nn.Module):
             # mlp_shared -> mlp_gamma|mlp_beta are evaluated on the 5x5 border-class map (exact; dei2i_spade_cls_fwd)
             if seg.cls5 is None:
                 seg.cls5 = Fn.Nhwc(seg.t.expand(n, 5, 5, seg.t.shape[3]).contiguous(), seg.c)
-            actv = Fn.conv(seg.cls5, sconv, self._shared_spec, self.training, bias=sconv.bias, act="relu")
-            gb5 = Fn.conv_cat(actv, self.mlp_gamma, self.mlp_beta, self._gb_spec)
+            # gamma|beta depend on the label tensor and this module's weights only: the four generator passes of a G-step use
+            # two label tensors (df_labels, nm_labels, nm_labels, df_labels - defectgan_model.py:185-205), so inside one
+            # weight_cache() scope (= one loss computation, weights fixed) each is evaluated once and shared; autograd sums
+            # the gradients of the passes that used it before the one backward through the two small convolutions
+            ck = None
+            if Fn._cache is not None and seg.key is not None:
+                ck = ("gb5", id(self), seg.key, n, self.training, torch.is_grad_enabled())
+            gb5 = Fn._cache.get(ck) if ck is not None else None
+            if gb5 is None:
+                actv = Fn.conv(seg.cls5, sconv, self._shared_spec, self.training, bias=sconv.bias, act="relu")
+                gb5 = Fn.conv_cat(actv, self.mlp_gamma, self.mlp_beta, self._gb_spec)
+                if ck is not None:
+                    Fn._cache[ck] = gb5
             pad = 0 if plain else out_pad
             out = Fn.spade_modulate_cls(xa, gb5, up=up, relu=relu, eps=self.param_free_norm.eps, out_pad=pad)
             out.pad = pad

@@ -1,12 +1,13 @@
-"""Data parallelism for the training step: one process per GPU, batch-sharded, bucketed gradient all-reduce over
-NCCL (NVLink 5 / NVSwitch) overlapped with backward.
+"""Data parallelism for the training step: one process per GPU, batch-sharded, gradient all-reduce over NCCL (NVLink 5 /
+NVSwitch) - by default ONE collective over the flat gradient vector after the backward, optionally (DEI2I_DDP_OVERLAP=1)
+bucketed and overlapped with the backward (see OVERLAP below for the measurement behind the default).
 
 The reference has no distributed code for DefectGAN (single device, utils/util.py:11-18): this layer is
 added *under* the trainer.  Replicas keep local BatchNorm statistics (DDP semantics = a reference run at the per-GPU
 batch); spectral-norm u/v stay identical across ranks without communication because they are a function of the
 (identical) weights only.
 
-Mechanics: FlatAdam keeps each network's gradients in one contiguous FP32 vector.  That vector is cut into
+Mechanics: FlatAdam keeps each network's gradients in one contiguous FP32 vector.  In the overlapped mode that vector is cut into
 contiguous buckets from the END (backward produces gradients roughly in reverse parameter order); a
 post-accumulate-grad hook per parameter counts its bucket down and, when a bucket is complete, enqueues
 ``all_reduce(AVG)`` of that slice on a side stream that waits for the backward stream at that point - so the collective

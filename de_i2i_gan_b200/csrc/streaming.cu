@@ -349,21 +349,22 @@ __global__ void nhwc_to_nchw_kernel(const __nv_bfloat16* __restrict__ src, float
 // turns it into a kh x 1 'valid' convolution with 64 input channels over xp [N, H + 2 pad, W, 64] - the dense TMA-im2col path.
 
 __global__ void rowpack_fwd_kernel(const float* __restrict__ img, uint4* __restrict__ xp, int N, int C, int H, int W, int kw, int pad) {
+  // one block per padded row (n, hp): no index divisions, the three source rows are resolved once
   const int Hp = H + 2 * pad;
-  const long long total = (long long)N * Hp * W * 8;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int s = (int)(i & 7);
-    long long t = i >> 3;
-    const int w = fast_mod(t, W);
-    t = fast_div(t, W);
-    const int hp = fast_mod(t, Hp);
-    const int n = (int)fast_div(t, Hp);
+  const int row = blockIdx.x;
+  const int n = row / Hp, hp = row - n * Hp;
+  const int h = reflect_idx(hp - pad, H);
+  const float* src = img + ((long long)n * C * H + h) * W;  // channel c at + c * H * W
+  const long long cstride = (long long)H * W;
+  uint4* dst = xp + (long long)row * W * 8;
+  for (int i = threadIdx.x; i < W * 8; i += blockDim.x) {
+    const int s = i & 7, w = i >> 3;
     float f[8] = {0, 0, 0, 0, 0, 0, 0, 0};
     if (s < kw) {
-      const int h = reflect_idx(hp - pad, H), ws = reflect_idx(w + s - pad, W);
-      for (int c = 0; c < C; ++c) f[c] = __ldg(img + (((long long)n * C + c) * H + h) * W + ws);
+      const int ws = reflect_idx(w + s - pad, W);
+      for (int c = 0; c < C; ++c) f[c] = __ldg(src + c * cstride + ws);
     }
-    xp[i] = pack8(f);
+    dst[i] = pack8(f);
   }
 }
 
@@ -1648,8 +1649,7 @@ extern "C" int dei2i_nhwc_to_nchw(const void* src, float* dst, int N, int C, int
 
 extern "C" int dei2i_rowpack_fwd(const float* img, void* xp, int N, int C, int H, int W, int kw, int pad, dei2i_stream stream) {
   DEI2I_REQUIRE(img && xp && C >= 1 && C <= 8 && kw >= 1 && kw <= 8 && pad >= 0 && pad < H && pad < W, "rowpack_fwd: bad arguments");
-  unsigned blocks = nblocks((long long)N * (H + 2 * pad) * W * 8, 256 * 4);
-  rowpack_fwd_kernel<<<blocks, 256, 0, ST>>>(img, (uint4*)xp, N, C, H, W, kw, pad);
+  rowpack_fwd_kernel<<<(unsigned)(N * (H + 2 * pad)), 256, 0, ST>>>(img, (uint4*)xp, N, C, H, W, kw, pad);
   return LAUNCH_OK("rowpack_fwd_kernel");
 }
 extern "C" int dei2i_rowpack_bwd(const void* dxp, float* dimg, int N, int C, int H, int W, int kw, int pad, dei2i_stream stream) {

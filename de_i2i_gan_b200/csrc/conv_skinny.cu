@@ -867,22 +867,28 @@ conv_heads_fwd_kernel(const Gather g, const Epilogue e, const __nv_bfloat16* __r
     cp_async_wait_group<1>();
     __syncthreads();
     for (int ox0 = warp * 16; ox0 < g.Wo; ox0 += kHmWarps * 16) {
-      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      // one accumulator per filter row: three independent mma chains of 12 instead of one of 36 (the kernel is bound by the
+      // ldmatrix -> mma.sync latency chain, profiles/r01l_ncu_full_conv_heads_fwd.txt)
+      float accr[3][4];
 #pragma unroll
-      for (int r = 0; r < 3; ++r) {
-        const uint32_t xr = s_x + ((iy0 + r + 4) & 3) * x_row_bytes;
+      for (int r = 0; r < 3; ++r) accr[r][0] = accr[r][1] = accr[r][2] = accr[r][3] = 0.f;
 #pragma unroll
-        for (int sx = 0; sx < 3; ++sx) {
-          const int pix = ox0 + (mi & 1) * 8 + mr + sx;
-          const uint32_t prow = xr + pix * 128;
+      for (int sx = 0; sx < 3; ++sx) {
+        const int pix = ox0 + (mi & 1) * 8 + mr + sx;
 #pragma unroll
-          for (int ks = 0; ks < 4; ++ks) {
+        for (int ks = 0; ks < 4; ++ks) {
+          const uint32_t coff = pix * 128 + (((ks * 2 + (mi >> 1)) ^ (pix & 7)) << 4);
+#pragma unroll
+          for (int r = 0; r < 3; ++r) {
             uint32_t a[4];
-            ldsm_x4(a, prow + (((ks * 2 + (mi >> 1)) ^ (pix & 7)) << 4));
-            mma_bf16_16816(acc, a, bw[(r * 3 + sx) * 4 + ks][0], bw[(r * 3 + sx) * 4 + ks][1]);
+            ldsm_x4(a, s_x + ((iy0 + r + 4) & 3) * x_row_bytes + coff);
+            mma_bf16_16816(accr[r], a, bw[(r * 3 + sx) * 4 + ks][0], bw[(r * 3 + sx) * 4 + ks][1]);
           }
         }
       }
+      float acc[4];
+#pragma unroll
+      for (int e2 = 0; e2 < 4; ++e2) acc[e2] = accr[0][e2] + accr[1][e2] + accr[2][e2];
       // epilogue: rows (pixels) gid / gid + 8, columns 2*tq, 2*tq + 1
       const int col = 2 * tq;
 #pragma unroll

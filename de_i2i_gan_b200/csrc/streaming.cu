@@ -962,61 +962,89 @@ spade_cls_bwd1_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5
   const long long img = (long long)n * (H + 2 * pad) * Wp;
   // the ReLU mask is recomputed from x (out = relu(fma(xhat, 1 + gamma, beta)) exactly as the forward evaluates it) instead
   // of reading `out` back: one tensor pass less.
-  // memory-level parallelism: the loads of kB pixels (2 x 16 B each) are issued before any of them is reduced - at 2 blocks
-  // per SM that is 64 KB in flight per SM, enough to cover the HBM latency (one-deep prefetch left the kernel latency-bound)
-  constexpr int kB = 4;
-  // pixel walk without divisions: (ph, pw) advances by `lanes` pixels per step; the source index uses a shift (UP is 1 or 2)
-  int ph = r0 + lane / W, pw = lane % W;
   const uint4* xn = x + (long long)n * Hx * Wx * C8 + c8;
   const uint4* dn = dout + (img + (long long)pad * Wp + pad) * C8 + c8;
-  while (ph < r1) {
-    uint4 vx[kB], vd[kB];
-    int hh[kB], ww[kB];
+  // one output pixel (h, w) with its gradient vd and the normalised source value xh: class bookkeeping + accumulation
+  auto reduce_pixel = [&](int h, int w, const uint4& vd, const float (&xh)[8]) {
+    const int cls = bcls(h, H) * 5 + bcls(w, W);
+    if (cls != cur) {
+      if (cur >= 0) {
 #pragma unroll
-    for (int j = 0; j < kB; ++j) {
-      hh[j] = ph; ww[j] = pw;
-      if (ph < r1) {
-        vx[j] = __ldg(xn + ((ph >> (UP - 1)) * Wx + (pw >> (UP - 1))) * C8);
-        vd[j] = __ldg(dn + (ph * Wp + pw) * C8);
+        for (int k = 0; k < 8; ++k) {
+          atomicAdd(&tab[cur * 2 * C + k * C8 + c8], ag[k]);
+          atomicAdd(&tab[cur * 2 * C + C + k * C8 + c8], ab[k]);
+          s[k] = fmaf(fg[k], ab[k], s[k]);  // S1, S2 are (1 + gamma)-weighted class sums: no per-pixel work for them
+          q[k] = fmaf(fg[k], ag[k], q[k]);
+          ag[k] = ab[k] = 0.f;
+        }
       }
-      pw += lanes;
-      while (pw >= W) {
-        pw -= W;
-        ++ph;
+      cur = cls;
+      unpack8(__ldg(gb5 + (n * 25 + cls) * (2 * C8) + c8), fg);
+      unpack8(__ldg(gb5 + (n * 25 + cls) * (2 * C8) + C8 + c8), fb);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) fg[k] += 1.f;
+    }
+    float fd[8];
+    unpack8(vd, fd);
+    fold_extras(dout, img, h, w, H, W, pad, C8, c8, fd);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      const float g = (!relu || fmaf(xh[k], fg[k], fb[k]) > 0.f) ? fd[k] : 0.f;
+      ag[k] = fmaf(g, xh[k], ag[k]);
+      ab[k] += g;
+    }
+  };
+  if (UP == 2) {
+    // walk SOURCE pixels of the rows [r0/2, r1/2) (r0, r1 even): x is loaded and normalised once for its 2 x 2 output block,
+    // all five loads are issued before the first is used
+    int sh_ = (r0 >> 1) + lane / Wx, sw_ = lane % Wx;
+    const int sr1 = r1 >> 1;
+    while (sh_ < sr1) {
+      const uint4 vx = __ldg(xn + (sh_ * Wx + sw_) * C8);
+      uint4 vd[4];
+#pragma unroll
+      for (int qd = 0; qd < 4; ++qd) vd[qd] = __ldg(dn + ((2 * sh_ + (qd >> 1)) * Wp + 2 * sw_ + (qd & 1)) * C8);
+      float xh[8];
+      unpack8(vx, xh);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) xh[k] = fmaf(xh[k], rs[k], mu[k]);
+#pragma unroll
+      for (int qd = 0; qd < 4; ++qd) reduce_pixel(2 * sh_ + (qd >> 1), 2 * sw_ + (qd & 1), vd[qd], xh);
+      sw_ += lanes;
+      while (sw_ >= Wx) {
+        sw_ -= Wx;
+        ++sh_;
       }
     }
+  } else {
+    // memory-level parallelism: the loads of kB pixels (2 x 16 B each) are issued before any of them is reduced
+    constexpr int kB = 4;
+    // pixel walk without divisions: (ph, pw) advances by `lanes` pixels per step
+    int ph = r0 + lane / W, pw = lane % W;
+    while (ph < r1) {
+      uint4 vx[kB], vd[kB];
+      int hh[kB], ww[kB];
 #pragma unroll
-    for (int j = 0; j < kB; ++j) {
-      if (hh[j] >= r1) break;
-      const int h = hh[j], w = ww[j];
-      const int cls = bcls(h, H) * 5 + bcls(w, W);
-      if (cls != cur) {
-        if (cur >= 0) {
-#pragma unroll
-          for (int k = 0; k < 8; ++k) {
-            atomicAdd(&tab[cur * 2 * C + k * C8 + c8], ag[k]);
-            atomicAdd(&tab[cur * 2 * C + C + k * C8 + c8], ab[k]);
-            s[k] = fmaf(fg[k], ab[k], s[k]);  // S1, S2 are (1 + gamma)-weighted class sums: no per-pixel work for them
-            q[k] = fmaf(fg[k], ag[k], q[k]);
-            ag[k] = ab[k] = 0.f;
-          }
+      for (int j = 0; j < kB; ++j) {
+        hh[j] = ph; ww[j] = pw;
+        if (ph < r1) {
+          vx[j] = __ldg(xn + (ph * Wx + pw) * C8);
+          vd[j] = __ldg(dn + (ph * Wp + pw) * C8);
         }
-        cur = cls;
-        unpack8(__ldg(gb5 + (n * 25 + cls) * (2 * C8) + c8), fg);
-        unpack8(__ldg(gb5 + (n * 25 + cls) * (2 * C8) + C8 + c8), fb);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) fg[k] += 1.f;
+        pw += lanes;
+        while (pw >= W) {
+          pw -= W;
+          ++ph;
+        }
       }
-      float fx[8], fd[8];
-      unpack8(vx[j], fx);
-      unpack8(vd[j], fd);
-      fold_extras(dout, img, h, w, H, W, pad, C8, c8, fd);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const float xh = fmaf(fx[k], rs[k], mu[k]);
-        const float g = (!relu || fmaf(xh, fg[k], fb[k]) > 0.f) ? fd[k] : 0.f;
-        ag[k] = fmaf(g, xh, ag[k]);
-        ab[k] += g;
+      for (int j = 0; j < kB; ++j) {
+        if (hh[j] >= r1) break;
+        float xh[8];
+        unpack8(vx[j], xh);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) xh[k] = fmaf(xh[k], rs[k], mu[k]);
+        reduce_pixel(hh[j], ww[j], vd[j], xh);
       }
     }
   }
@@ -1798,6 +1826,7 @@ extern "C" int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* o
   const int want = (148 * 2) / N > 0 ? (148 * 2) / N : 1;
   int rows = (H + want - 1) / want;
   if (rows < 1) rows = 1;
+  if (up == 2) rows += rows & 1;  // the up == 2 kernel walks 2 x 2 output blocks: whole source rows per block
   const unsigned gx = (unsigned)((H + rows - 1) / rows);
   const size_t shmem = (size_t)26 * 2 * C * sizeof(float);
   DEI2I_CUDA(cudaMemsetAsync(scratch, 0, (size_t)N * 2 * C * sizeof(float), ST));

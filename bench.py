@@ -1,21 +1,29 @@
 #!/usr/bin/env python
-"""Benchmark of the DefectGAN hot path: one "step" = one _train_discriminator_once + one _train_generator_once
-(num_critics = 1) on a synthetic batch; metric = images / second (B * n_gpus / step time).
+"""Benchmark of the de-i2i-gan hot path on B200 (BASELINE.json).  One JSON line per run.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python bench.py [--config c2|c1|wgan|stargan|inference[=B]] [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 ... bench.py --gpus N ...
 
-Ours: DefectGanTrainer (de_i2i_gan_b200.trainers) -> mirrored modules -> libdei2i.so (sm_100a kernels), BF16 storage /
-tcgen05 MMA with FP32 accumulation, workload BASELINE.json configs[1]: 256x256, batch 32 per GPU.
-  value : device-timed (CUDA events) over K steps with the inputs already resident in HBM;
-  e2e   : the same K steps through the same trainer API fed from PINNED HOST tensors (H2D of both image batches and
-          the labels inside the timed region, losses read back to the host every step);
-  roofline : every convolution launch of the timed region is bracketed by CUDA events on the launching stream;
-          achieved = sum(algorithmic FLOPs) / sum(durations) of the dominant kernel class vs MEASURED_PEAKS.json;
-  cpu_baseline : the CPU restatement of the reference (oracle/, plain torch FP32) timed on this box's host cores on a
-          bounded sample (one D+G step at 256x256, batch 2).
-Reference arm (--impl reference): the same CPU restatement timed for K steps with all host threads (the reference
-itself is Python under /root/reference, which does not exist on the GPU box).
+--config (default c2 = BASELINE.json's headline, configs[1]):
+  c2        DefectGAN training step (1 D-step + 1 G-step, num_critics = 1), 256x256, batch 32 per GPU, BF16
+  c1        the same step at 128x128, batch 4 (configs[0], the reference's own CPU-runnable case)
+  wgan      WGAN weight-clipping D-step + G-step, 128x128, batch 64 per GPU (configs[2])
+  stargan   StarGAN-v2 iteration (2 D-losses with R1 double backward, 2 G-losses, EMA), 256x256, batch 16 per GPU (configs[3])
+  inference DefectGAN defect synthesis (_generate_fake) with a SPATIAL label map, 256x256, batch B (default 64) (configs[4])
+
+Ours: the mirrored trainer / solver entry points (de_i2i_gan_b200) -> libdei2i.so (sm_100a kernels), BF16 storage, tcgen05
+MMA with FP32 accumulation.
+  value    : device-timed (CUDA events) over K steps, inputs resident in HBM, max over ranks;
+  e2e      : the same K steps through the same public entry point fed from PINNED HOST tensors (H2D inside the timed region,
+             results read back to the host every step);
+  roofline : every convolution launch of an eager re-run of the same K steps is bracketed by CUDA events on the launching
+             stream; achieved = sum(algorithmic FLOPs) / sum(durations) over ALL convolution kernels (the north-star
+             criterion), the best dense class beside it; the HBM-streaming kernels are timed the same way against their
+             algorithmic bytes (roofline.streaming_gbs);
+  cpu_baseline / --impl reference : the CPU restatement of the reference (oracle/, plain torch FP32; the reference itself is
+             Python under /root/reference, which does not exist on the GPU box) on this box's host cores;
+  incumbent: the same restatement moved to the GPU = stock torch / cuDNN (FP32, TF32, autocast-BF16) - the number a user of
+             the reference gets on this B200 today.
 """
 import argparse
 import json
@@ -29,8 +37,9 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-METRIC = "DefectGAN train img/s at 256x256 (D-step + G-step, batch 32/GPU)"
 UNIT = "img/s"
+# per-image algorithmic convolution FLOPs of one D-step + G-step at 256x256: 14 G_f + 16 D_f
+DENSE_TFLOP_PER_IMG_256 = 81.3147 / 32
 
 
 def parse():
@@ -39,15 +48,16 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=32, help="per-GPU batch (BASELINE.json configs[1]: 32)")
-    ap.add_argument("--image-size", type=int, default=256)
+    ap.add_argument("--config", default="c2", help="c2 | c1 | wgan | stargan | inference[=B]")
+    ap.add_argument("--batch", type=int, default=0, help="per-GPU batch override (default: the configuration's own)")
+    ap.add_argument("--image-size", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--cpu-sample-batch", type=int, default=2)
+    ap.add_argument("--no-incumbent", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true", help="profiling runs only: skip the pinned-host pass")
     ap.add_argument("--spade-dense", action="store_true",
                     help="evaluate SPADE gamma|beta with the dense full-resolution convolutions even for 1x1 label maps "
                          "(default: exact 5x5 border-class map, see DESIGN.md 4a)")
-    ap.add_argument("--breakdown", default=None, help="write a per-convolution-geometry timing table (JSON) to this path")
+    ap.add_argument("--breakdown", default=None, help="write a per-kernel-geometry timing table (JSON) to this path")
     return ap.parse_args()
 
 
@@ -107,60 +117,113 @@ def load_peaks():
         with open(path) as f:
             p = json.load(f)
         return dict(hbm=p["hbm_gbs"], burst=p["bf16_tflops"], sustained=p.get("bf16_tflops_sustained", p["bf16_tflops"]),
-                    source="MEASURED_PEAKS.json")
-    return dict(hbm=6650.0, burst=1590.0, sustained=1400.0, source="fallback (B200_PROFILING.md)")
+                    sustained_mhz=(p.get("clocks_under_load") or {}).get("sm_mhz_median"), source="MEASURED_PEAKS.json")
+    return dict(hbm=6650.0, burst=1590.0, sustained=1400.0, sustained_mhz=None, source="fallback (B200_PROFILING.md)")
 
 
-# ---------------------------------------------------------------------------------------------------- CPU arm
-def cpu_oracle_steps(image_size, batch, steps, warmup, threads):
-    """Times D-step + G-step of the CPU restatement (oracle/defectgan_ref.py, full-width nets, FP32).  Returns the
-    list of per-step seconds."""
+# ---------------------------------------------------------------------------------------------------- CPU arm / incumbent
+def oracle_steps(image_size, batch, steps, warmup, device="cpu", mode="fp32", threads=None):
+    """Times D-step + G-step of the restatement of the reference (oracle/defectgan_ref.py, full-width nets) on ``device``.
+    mode: 'fp32' | 'tf32' | 'autocast_bf16' (GPU incumbent variants).  Returns the per-step seconds of the timed steps."""
     import torch
     from oracle import defectgan_ref as R
-    torch.set_num_threads(threads)
-    g = R.random_generator_state(noise_weight=0.0)
-    d = R.random_discriminator_state(image_size=image_size)
+    from de_i2i_gan_b200.synthetic import synthetic_batch
+    if threads:
+        torch.set_num_threads(threads)
+    dev = torch.device(device)
+    g = {k: v.to(dev) for k, v in R.random_generator_state(noise_weight=0.0).items()}
+    d = {k: v.to(dev) for k, v in R.random_discriminator_state(image_size=image_size).items()}
     tr = R.Trainer(g, d)
-    bg, labels, df = R.synthetic_batch(batch, image_size, seed=0)
+    bg, labels, df = [t.to(dev) for t in synthetic_batch(batch, image_size, seed=0)]
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = (mode == "tf32")
     times = []
-    for i in range(warmup + steps):
-        t0 = time.perf_counter()
-        tr.train_discriminator_once(bg, labels, df)
-        tr.train_generator_once(bg, labels, df)
-        dt = time.perf_counter() - t0
-        if i >= warmup:
-            times.append(dt)
+    try:
+        for i in range(warmup + steps):
+            if dev.type == "cuda":
+                torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            with torch.autocast("cuda", dtype=torch.bfloat16, enabled=(mode == "autocast_bf16")):
+                tr.train_discriminator_once(bg, labels, df)
+                tr.train_generator_once(bg, labels, df)
+            if dev.type == "cuda":
+                torch.cuda.synchronize()
+            if i >= warmup:
+                times.append(time.perf_counter() - t0)
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
     return times
 
 
-def run_reference(args):
-    """--impl reference: the reference's CPU path (restated in oracle/, see module docstring) on the host cores."""
+def incumbent_block(image_size, batches=(32, 16, 8)):
+    """Stock torch / cuDNN on this GPU running the reference's training step (the restatement moved to cuda): img/s per mode.
+    The FP32 autograd graph of four generator passes at batch 32 needs > 150 GB at 256x256, so the largest batch that fits is used."""
+    import torch
+    out = {"what": "oracle/defectgan_ref.py (restatement of the reference's D-step + G-step) on cuda:0, stock torch/cuDNN kernels, "
+                   "1 warm-up + 2 timed steps per mode", "image_size": image_size}
+    for mode in ("fp32", "tf32", "autocast_bf16"):
+        for b in batches:
+            try:
+                t = oracle_steps(image_size, b, 2, 1, device="cuda", mode=mode)
+                out[mode] = {"img_per_s": b / (sum(t) / len(t)), "batch": b, "ms_per_step": 1e3 * sum(t) / len(t)}
+                break
+            except torch.cuda.OutOfMemoryError:
+                out[mode] = {"error": f"out of memory at batch {b}"}
+            finally:
+                import gc
+                gc.collect()
+                torch.cuda.empty_cache()
+    return out
+
+
+def cpu_baseline_block(image_size, cores):
+    """Bounded CPU sample for the GPU arm's line: config 1 exactly (128x128, batch 4) with 3 warm-ups,
+    and one warmed step at the metric's own image size so that `value` is in the metric's unit."""
+    c1 = oracle_steps(128, 4, 3, 3, threads=cores)
+    s1 = sum(c1) / len(c1)
+    blk = {"cores": cores, "kind": "port", "unit": UNIT,
+           "c1": {"s_per_step": s1, "img_per_s": 4 / s1, "tflops_effective": 0.637 * 4 / s1,
+                  "sample": "BASELINE config 1: 128x128, batch 4, FP32, 3 warm-up + 3 timed D+G steps"}}
+    if image_size == 128:
+        blk["value"] = 4 / s1
+        blk["sample"] = blk["c1"]["sample"]
+    else:
+        t = oracle_steps(image_size, 2, 1, 1, threads=cores)[0]
+        blk["value"] = 2 / t
+        blk["sample"] = (f"1 warm-up + 1 timed D-step + G-step at {image_size}x{image_size}, batch 2, FP32 torch CPU restatement "
+                         f"(oracle/defectgan_ref.py), {t:.1f} s/step")
+    return blk
+
+
+def run_reference(args, cfg):
+    """--impl reference: the reference's CPU path (restated in oracle/, see module docstring) on the host cores, rank 0 only.
+    DefectGAN configurations: steps of the configuration's image size on a bounded batch; the other configurations have no
+    separately timed CPU arm (their oracles are pinned by tests/; timing them adds nothing to the headline) and report so."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import torch
     cores = os.cpu_count() or 1
-    bs = args.cpu_sample_batch
-    # bound the whole run to a few minutes: probe one step, shrink the sample if needed
-    probe = cpu_oracle_steps(args.image_size, bs, 1, 0, cores)[0]
-    budget = 240.0
-    while bs > 1 and probe * (args.steps + args.warmup) > budget:
-        bs //= 2
-        probe = cpu_oracle_steps(args.image_size, bs, 1, 0, cores)[0]
-    steps, warmup = args.steps, args.warmup
+    if cfg["kind"] != "defectgan":
+        print(json.dumps({"impl": "reference", "unavailable": f"no timed CPU arm for --config {args.config} (DefectGAN configurations only)"}))
+        return
+    H = cfg["image_size"]
+    bs = 4 if H <= 128 else 2
+    probe = oracle_steps(H, bs, 1, 1, threads=cores)[0]
+    budget = 300.0
+    steps, warmup = args.steps, min(args.warmup, 3)
     if probe * (steps + warmup) > budget:
-        warmup = 0
-        steps = max(1, min(steps, int(budget / probe)))
-    times = cpu_oracle_steps(args.image_size, bs, steps, warmup, cores)
+        warmup = 1
+        steps = max(1, min(steps, int(budget / probe) - 1))
+    times = oracle_steps(H, bs, steps, warmup, threads=cores)
     sec = sum(times) / len(times)
     val = bs / sec
-    sample = f"D-step + G-step at {args.image_size}x{args.image_size}, batch {bs} per step, FP32, torch CPU ({torch.__version__})"
+    sample = f"D-step + G-step at {H}x{H}, batch {bs} per step, FP32, torch CPU ({torch.__version__}), {warmup} warm-up + {steps} timed"
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "impl": "reference", "metric": cfg["metric"], "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
         "warmup": warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"DefectGAN D+G training step {args.image_size}x{args.image_size}", "sample_batch": bs,
-                   "device": "host CPU"},
+        "config": {"workload": cfg["workload"], "sample_batch": bs, "device": "host CPU"},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -181,43 +244,161 @@ def _finish(world):
     os._exit(0)
 
 
-# ---------------------------------------------------------------------------------------------------- our arm
-def run_ours(args):
-    import torch
-    import torch.distributed as dist
-    from de_i2i_gan_b200 import ops, options, parallel
-    from de_i2i_gan_b200.trainers import find_trainer_using_model_name
-    from oracle import defectgan_ref as R  # synthetic_batch only (seeded input factory); never on the compute path
+# ---------------------------------------------------------------------------------------------------- configurations
+def resolve_config(args):
+    name, _, arg = args.config.partition("=")
+    if name in ("c2", "c1"):
+        H = args.image_size or (256 if name == "c2" else 128)
+        B = args.batch or (32 if name == "c2" else 4)
+        return dict(kind="defectgan", name=name, image_size=H, batch=B,
+                    metric=f"DefectGAN train img/s at {H}x{H} (D-step + G-step, batch {B}/GPU)",
+                    workload=f"DefectGAN full training step (1 D-step + 1 G-step) {H}x{H}, batch {B}/GPU, --add_noise --use_spectral")
+    if name == "wgan":
+        B = args.batch or 64
+        return dict(kind="wgan", name=name, image_size=128, batch=B, metric=f"WGAN train img/s at 128x128 (D-step + G-step, batch {B}/GPU)",
+                    workload=f"WGAN weight-clipping D-step + G-step (train_wgan.py), 128x128, batch {B}/GPU")
+    if name == "stargan":
+        B = args.batch or 16
+        return dict(kind="stargan", name=name, image_size=256, batch=B,
+                    metric=f"StarGAN-v2 train img/s at 256x256 (2 D-losses with R1 + 2 G-losses + EMA per iteration, batch {B}/GPU)",
+                    workload=f"StarGAN-v2 iteration (adain, w_hpf=0): D latent/ref with R1 double backward, G latent/ref, EMA; 256x256, batch {B}/GPU")
+    if name == "inference":
+        B = args.batch or int(arg or 64)
+        return dict(kind="inference", name=name, image_size=256, batch=B,
+                    metric=f"DefectGAN inference img/s at 256x256 (defect synthesis with a spatial label map, batch {B})",
+                    workload=f"DefectGanModel('inference') = _generate_fake, 256x256, batch {B}, spatial [B,6,256,256] label map (dense SPADE path)")
+    raise SystemExit(f"bench.py: unknown --config {args.config!r}")
 
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device - the product path has no CPU fallback (use --impl reference for the CPU arm)")
+
+def setup_defectgan(args, cfg, dev, rank):
+    import torch
+    from de_i2i_gan_b200 import options
+    from de_i2i_gan_b200.synthetic import synthetic_batch
+    from de_i2i_gan_b200.trainers import find_trainer_using_model_name
     if args.spade_dense:
         from de_i2i_gan_b200.models.networks import normalization
         normalization.CONSTANT_LABEL_CLASSES = False
-    rank, local, world = parallel.init_distributed()
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    B, H = args.batch, args.image_size
-
+    B, H = cfg["batch"], cfg["image_size"]
     torch.manual_seed(123)  # fix_rand_seed(123), train_defectgan.py:120 - identical initial weights on every rank
     opt = options.readme_recipe(image_size=H, batch_size=B, num_critics=1, num_epochs=10, iters_per_epoch=10 ** 6,
                                 name="bench", ckpt_dir=__import__("pathlib").Path("/tmp/dei2i_bench_ckpt"))
     opt.device = dev
     trainer = find_trainer_using_model_name(opt.model)(opt)
     torch.manual_seed(1000 + rank)  # per-rank noise stream
-    bg, labels, df = R.synthetic_batch(B, H, seed=rank)  # per-rank shard of the global batch
-    host = [t.pin_memory() for t in (bg, labels, df)]
-    resident = [t.to(dev) for t in host]
     # one trip over PCIe per iteration, as the reference's loop does (data.to(device) once, then D-step and G-step,
     # defectgan_trainer.py:91-112): the D-step copies bg, labels, df from the pinned host batch, the G-step of the same
     # iteration takes a device-to-device copy of them (GraphedStep._stage)
-    h2d = sum(t.numel() * t.element_size() for t in host)
-    d2h = 7 * 4                                               # 2 + 5 loss scalars
+    host = [t.pin_memory() for t in synthetic_batch(B, H, seed=rank)]  # per-rank shard of the global batch
 
     def step(inputs):
         b, l, d = inputs
         trainer._train_discriminator_once(b, l, d)
         trainer._train_generator_once(b, l, d)
+
+    def eager():
+        was = any(g.enabled for g in trainer._graphed.values())
+        for g in trainer._graphed.values():
+            g.enabled = False
+        return was
+    return dict(step=step, host=host, d2h=7 * 4, eager=eager, dense_ref_tflop=DENSE_TFLOP_PER_IMG_256 * B * (H / 256) ** 2,
+                extra={"spade": ("dense full-resolution gamma|beta convolutions" if args.spade_dense else
+                                 "gamma|beta evaluated exactly on the 5x5 border-class map of the 1x1 training label map "
+                                 "(results identical; FLOPs of the dense evaluation are NOT credited - see executed vs reference TFLOP)")})
+
+
+def setup_wgan(args, cfg, dev, rank):
+    import torch
+    from pathlib import Path
+    from de_i2i_gan_b200 import options
+    from de_i2i_gan_b200.trainers.wgan_trainer import WGanTrainer
+    B, H = cfg["batch"], cfg["image_size"]
+    opt = options.wgan_options(image_size=H, batch_size=B, ckpt_dir=Path("/tmp/dei2i_wgan_bench"), num_display_images=4)
+    opt.device = dev
+    torch.manual_seed(123)
+    tr = WGanTrainer(opt)
+    torch.manual_seed(1000 + rank)
+    host = [torch.randn(B, 3, H, H).clamp_(-1, 1).pin_memory()]
+
+    def step(inputs):
+        real = inputs[0].to(dev, non_blocking=True)
+        tr._train_discriminator_once(real)
+        tr._train_generator_once(B)
+
+    def eager():
+        was = any(g.enabled for g in getattr(tr, "_graphed", {}).values())
+        for g in getattr(tr, "_graphed", {}).values():
+            g.enabled = False
+        return was
+    return dict(step=step, host=host, d2h=2 * 4 + 2 * B * 4, eager=eager, dense_ref_tflop=None, extra={})
+
+
+def setup_stargan(args, cfg, dev, rank):
+    import torch
+    from types import SimpleNamespace
+    from de_i2i_gan_b200.stargan_v2.core import solver as S
+    B, H = cfg["batch"], cfg["image_size"]
+    a = SimpleNamespace(img_size=H, style_dim=64, latent_dim=16, num_domains=3, w_hpf=0, norm_type="adain", num_embeds=1,
+                        lambda_reg=1.0, lambda_sty=1.0, lambda_ds=2.0, lambda_cyc=1.0, lr=1e-4, f_lr=1e-6, beta1=0.0, beta2=0.99,
+                        weight_decay=1e-4, ds_iter=100000)
+    torch.manual_seed(777)  # main.py:227
+    st = S.build_training_state(a, dev)
+    g = torch.Generator().manual_seed(rank)
+    img = lambda: torch.randn(B, 3, H, H, generator=g).clamp_(-1, 1).pin_memory()  # noqa: E731
+    host = [img(), img(), img(), torch.randint(0, 3, (B,), generator=g).pin_memory(), torch.randint(0, 3, (B,), generator=g).pin_memory(),
+            torch.randn(B, 16, generator=g).pin_memory(), torch.randn(B, 16, generator=g).pin_memory()]
+
+    def step(inputs):
+        x, xr, xr2, y_org, y_trg, z, z2 = [t.to(dev, non_blocking=True) for t in inputs]
+        inp = SimpleNamespace(x_src=x, y_src=y_org, x_ref=xr, x_ref2=xr2, y_ref=y_trg, z_trg=z, z_trg2=z2)
+        S.train_iteration(st, a, inp)
+    return dict(step=step, host=host, d2h=14 * 4, eager=lambda: False, dense_ref_tflop=None, extra={})
+
+
+def setup_inference(args, cfg, dev, rank):
+    import torch
+    from pathlib import Path
+    from de_i2i_gan_b200 import options
+    from de_i2i_gan_b200.models import create_model
+    from de_i2i_gan_b200.synthetic import spatial_labels, synthetic_batch
+    B, H = cfg["batch"], cfg["image_size"]
+    opt = options.readme_recipe(image_size=H, batch_size=B, ckpt_dir=Path("/tmp/dei2i_inf_bench"), phase="test", is_train=False)
+    opt.device = dev
+    torch.manual_seed(123)
+    model = create_model(opt)
+    model.init_weights()
+    x, _, _ = synthetic_batch(B, H, seed=rank)
+    host = [x.pin_memory(), spatial_labels(B, H, seed=rank).pin_memory()]
+    out_host = [torch.empty(B, 3, H, H).pin_memory(), torch.empty(B, 1, H, H).pin_memory()]
+
+    def step(inputs):
+        out, prob = model("inference", inputs[0], inputs[1])
+        if not inputs[0].is_cuda:  # end-to-end call: the synthesised images go back to the host
+            out_host[0].copy_(out, non_blocking=True)
+            out_host[1].copy_(prob, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+
+    def eager():
+        os.environ["DEI2I_CUDA_GRAPH"] = "0"
+        return True
+    return dict(step=step, host=host, d2h=sum(t.numel() * 4 for t in out_host), eager=eager, dense_ref_tflop=None, extra={})
+
+
+# ---------------------------------------------------------------------------------------------------- our arm
+def run_ours(args, cfg):
+    import torch
+    import torch.distributed as dist
+    from de_i2i_gan_b200 import ops, parallel
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the product path has no CPU fallback (use --impl reference for the CPU arm)")
+    rank, local, world = parallel.init_distributed()
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    B = cfg["batch"]
+    S = {"defectgan": setup_defectgan, "wgan": setup_wgan, "stargan": setup_stargan, "inference": setup_inference}[cfg["kind"]](args, cfg, dev, rank)
+    step, host = S["step"], S["host"]
+    resident = [t.to(dev) for t in host]
+    h2d = sum(t.numel() * t.element_size() for t in host)
 
     def barrier():
         if world > 1:
@@ -241,7 +422,8 @@ def run_ours(args):
             ms = t.item()
         return ms, prof
 
-    for _ in range(max(args.warmup, 3)):  # call 1 eager, call 2 captures the D-step / G-step CUDA graphs, call 3+ replay
+    warm = max(args.warmup, 3)
+    for _ in range(warm):  # call 1 eager, call 2 captures the CUDA graphs, call 3+ replay
         step(resident)
     clocks = ClockSampler(local)
     if rank == 0:
@@ -255,96 +437,119 @@ def run_ours(args):
         ms_e2e, _ = timed(host, args.steps, False)
     mem_gb = torch.cuda.max_memory_allocated() / 2 ** 30
     # per-kernel pass: a replayed CUDA graph cannot be bracketed kernel by kernel, so the SAME kernels are launched eagerly for
-    # the same K steps right after the timed region, every convolution between two CUDA events on the launching stream
-    graphed = any(g.enabled for g in trainer._graphed.values())
-    for g in trainer._graphed.values():
-        g.enabled = False
+    # the same K steps right after the timed region, every convolution / streaming launch between two CUDA events on the
+    # launching stream
+    graphed = S["eager"]()
     step(resident)
     l0 = ops.launch_count()
     ms_eager, prof = timed(resident, args.steps, True)
-    launches = ops.launch_count() - l0
+    launches = (ops.launch_count() - l0) // max(args.steps, 1)
 
-    # ---- roofline of the convolution kernels from the in-band events
-    agg = {}
+    agg, table = {}, {}
+    for kind, work, e0, e1, tag in prof:
+        dt = e0.elapsed_time(e1)
+        a = agg.setdefault(kind, [0, 0.0, 0])
+        a[0] += work; a[1] += dt; a[2] += 1
+        t = table.setdefault(f"{kind} {tag}".strip(), [0, 0.0, 0])
+        t[0] += work; t[1] += dt; t[2] += 1
     if args.breakdown and rank == 0:
-        table = {}
-        for kind, flops, e0, e1, tag in prof:
-            t = table.setdefault(f"{kind} {tag}", [0, 0.0, 0])
-            t[0] += flops; t[1] += e0.elapsed_time(e1); t[2] += 1
-        rows = [dict(kernel=k, launches_per_step=v[2] / args.steps, ms_per_step=v[1] / args.steps, gflop_per_launch=v[0] / v[2] / 1e9,
-                     tflops=(v[0] / (v[1] * 1e-3) / 1e12 if v[1] > 0 else 0.0)) for k, v in table.items()]
+        rows = []
+        for k, v in table.items():
+            per = v[0] / (v[1] * 1e-3) if v[1] > 0 else 0.0
+            row = dict(kernel=k, launches_per_step=v[2] / args.steps, ms_per_step=v[1] / args.steps)
+            if k.startswith("stream_"):
+                row.update(mb_per_launch=v[0] / v[2] / 1e6, gbs=per / 1e9)
+            else:
+                row.update(gflop_per_launch=v[0] / v[2] / 1e9, tflops=per / 1e12)
+            rows.append(row)
         rows.sort(key=lambda r: -r["ms_per_step"])
         with open(args.breakdown, "w") as f:
             json.dump(rows, f, indent=1)
-    for kind, flops, e0, e1, _tag in prof:
-        a = agg.setdefault(kind, [0, 0.0, 0])
-        a[0] += flops
-        a[1] += e0.elapsed_time(e1)
-        a[2] += 1
     peaks = load_peaks()
-    detail = {k: {"launches": v[2], "ms_per_step": v[1] / args.steps, "tflops": v[0] / (v[1] * 1e-3) / 1e12 if v[1] > 0 else 0.0,
-                  "gflop_per_launch": v[0] / v[2] / 1e9} for k, v in agg.items()}
-    conv_ms = sum(v[1] for v in agg.values())
-    conv_flops = sum(v[0] for v in agg.values())
-    # dominant kernel = the dense tcgen05 convolution class with the largest share of the step (tensor-bound); the skinny
-    # classes (8-channel inputs / <= 4 outputs, HBM-bound by construction) and the tiny class (< 2 GFLOP launches: 5x5 SPADE
-    # class-map convolutions, classifier heads - launch-latency bound) are listed in `detail`
-    dense = {k: v for k, v in agg.items() if k.endswith("_dense")}
-    dom = max(dense, key=lambda k: dense[k][1]) if dense else (max(agg, key=lambda k: agg[k][1]) if agg else None)
+    conv = {k: v for k, v in agg.items() if k.startswith("conv_")}
+    stream = {k: v for k, v in agg.items() if k.startswith("stream_")}
     roofline = None
-    if dom is not None:
-        a = detail[dom]
+    if conv and rank == 0:
+        tf = lambda v: v[0] / (v[1] * 1e-3) / 1e12 if v[1] > 0 else 0.0  # noqa: E731
+        conv_ms, conv_flops = sum(v[1] for v in conv.values()), sum(v[0] for v in conv.values())
+        dense = {k: v for k, v in conv.items() if k.endswith("_dense")}
+        dense_ms, dense_flops = sum(v[1] for v in dense.values()), sum(v[0] for v in dense.values())
+        best = max(dense, key=lambda k: tf(dense[k])) if dense else None
+        all_tf = conv_flops / (conv_ms * 1e-3) / 1e12
+        # which peak: the sustained figure was measured with the SM clock at sustained_mhz (power-capped matmul loop); when
+        # this run's clocks sat well above that, the burst figure is the honest denominator
+        burst_clock = bool(clk and clk.get("sm_mhz") and peaks["sustained_mhz"] and clk["sm_mhz"] > 1.1 * peaks["sustained_mhz"])
+        peak = peaks["burst"] if burst_clock else peaks["sustained"]
         traffic = None
         tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
         if os.path.exists(tpath):  # dram__bytes_read.sum + dram__bytes_write.sum per launch from a committed `ncu --set full` capture
             with open(tpath) as f:
-                traffic = json.load(f).get(dom)
-        dense_ms = sum(v[1] for v in dense.values())
-        dense_flops = sum(v[0] for v in dense.values())
-        roofline = {"bound": "tensor", "kernel": dom + " (conv_tma_kernel / wgrad_tma_kernel, tcgen05)", "achieved": a["tflops"],
-                    "peak": peaks["sustained"], "unit": "TFLOP/s", "frac": a["tflops"] / peaks["sustained"], "traffic": traffic,
-                    "peak_source": peaks["source"] + " bf16_tflops_sustained (kernels timed inside a long step)",
-                    "all_dense_conv_tflops": dense_flops / (dense_ms * 1e-3) / 1e12 if dense_ms > 0 else None,
-                    "dense_conv_share_of_step": dense_ms / ms_eager,
-                    "all_conv_tflops": conv_flops / (conv_ms * 1e-3) / 1e12, "conv_share_of_step": conv_ms / ms_eager,
-                    "measured_in": "eager re-run of the same K steps directly after the timed region (identical kernels; a replayed CUDA graph cannot be bracketed per kernel)",
-                    "eager_ms_per_step": ms_eager / args.steps, "detail": detail}
+                traffic = json.load(f).get("conv_fwd_dense")
+        # algorithmic bytes of the streaming kernels: channel_stats re-reads a tensor its consumer reads again, so its bytes are
+        # not algorithmic work - its TIME counts against the family
+        s_bytes = sum(v[0] for k, v in stream.items() if k != "stream_channel_stats")
+        s_ms = sum(v[1] for v in stream.values())
+        roofline = {
+            "bound": "tensor", "kernel": "all convolution kernels (conv_tma / wgrad_tma tcgen05 + skinny mma.sync + tiny)",
+            "achieved": all_tf, "peak": peak, "unit": "TFLOP/s", "frac": all_tf / peak, "traffic": traffic,
+            "peak_kind": ("bf16_tflops (burst)" if burst_clock else "bf16_tflops_sustained") + " from " + peaks["source"],
+            "all_conv_tflops": all_tf, "all_conv_frac_burst": all_tf / peaks["burst"], "all_conv_frac_sustained": all_tf / peaks["sustained"],
+            "dense_conv_tflops": dense_flops / (dense_ms * 1e-3) / 1e12 if dense_ms > 0 else None,
+            "best_class": best, "best_class_tflops": tf(dense[best]) if best else None,
+            "conv_share_of_step": conv_ms / ms_eager, "dense_conv_share_of_step": dense_ms / ms_eager,
+            "streaming_gbs": s_bytes / (s_ms * 1e-3) / 1e9 if s_ms > 0 else None,
+            "streaming_frac_hbm": s_bytes / (s_ms * 1e-3) / 1e9 / peaks["hbm"] if s_ms > 0 else None,
+            "streaming_share_of_step": s_ms / ms_eager, "hbm_peak_gbs": peaks["hbm"],
+            "eager_ms_per_step": ms_eager / args.steps,
+            "measured_in": "eager re-run of the same K steps directly after the timed region (identical kernels; a replayed CUDA graph cannot be bracketed per kernel)",
+            "classes": {k: {"launches_per_step": v[2] / args.steps, "ms_per_step": v[1] / args.steps,
+                            **({"gbs": v[0] / (v[1] * 1e-3) / 1e9} if k.startswith("stream_") else {"tflops": tf(v)})}
+                        for k, v in sorted(agg.items(), key=lambda kv: -kv[1][1])},
+        }
     if rank != 0:
         _finish(world)
         return
-    cpu = None
-    if not args.no_cpu_baseline and world == 1:
-        cores = os.cpu_count() or 1
-        bs = args.cpu_sample_batch
-        t = cpu_oracle_steps(H, bs, 1, 0, cores)[0]
-        cpu = {"value": bs / t, "unit": UNIT, "cores": cores, "kind": "port",
-               "sample": f"1 D-step + G-step at {H}x{H}, batch {bs}, FP32 torch CPU restatement (oracle/defectgan_ref.py), {t:.1f} s"}
+    d2h, dense_ref, extra = S["d2h"], S["dense_ref_tflop"], S["extra"]
     sec = ms * 1e-3 / args.steps
+    conv_flops_step = sum(v[0] for k, v in agg.items() if k.startswith("conv_")) / args.steps
+    config = {"workload": cfg["workload"], "global_batch": B * world, "parallelism": f"dp{world}",
+              "executed_conv_tflop_per_step_per_gpu": conv_flops_step / 1e12,
+              "l2": "no flush needed: every step streams its own activations (>> 126 MB L2)", "peak_mem_gb": round(mem_gb, 1),
+              "cuda_graph": graphed}
+    if dense_ref is not None:
+        config["reference_dense_conv_tflop_per_step_per_gpu"] = dense_ref
+    config.update(extra)
+    cpu = inc = None
+    if cfg["kind"] == "defectgan" and world == 1:
+        if not args.no_cpu_baseline:
+            cpu = cpu_baseline_block(cfg["image_size"], os.cpu_count() or 1)
+        if not args.no_incumbent:
+            try:  # the headline must survive a failing baseline leg
+                import gc
+                del S, step, resident, prof
+                gc.collect()
+                torch.cuda.empty_cache()
+                inc = incumbent_block(cfg["image_size"], (cfg["batch"], 16, 8) if cfg["batch"] > 16 else (cfg["batch"],))
+            except Exception as e:
+                inc = {"error": repr(e)[:300]}
     print(json.dumps({
-        "metric": METRIC, "value": B * world / sec, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "metric": cfg["metric"], "value": B * world / sec, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": warm,
         "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
-        "data": "synthetic",
-        "config": {"workload": f"DefectGAN full training step (1 D-step + 1 G-step) {H}x{H}, batch {B}/GPU, --add_noise --use_spectral",
-                   "global_batch": B * world, "parallelism": f"dp{world}", "executed_conv_tflop_per_step_per_gpu": conv_flops / args.steps / 1e12,
-                   "reference_dense_conv_tflop_per_step_per_gpu": 81.3147 * (B / 32) * (H / 256) ** 2,
-                   "spade": ("dense full-resolution gamma|beta convolutions" if args.spade_dense else
-                             "gamma|beta evaluated exactly on the 5x5 border-class map of the 1x1 training label map "
-                             "(results identical; FLOPs of the dense evaluation are NOT credited - see executed vs reference TFLOP)"),
-                   "l2": "no flush needed: every step streams its own activations (>> 126 MB L2)", "peak_mem_gb": round(mem_gb, 1),
-                   "cuda_graph": graphed},
+        "data": "synthetic", "config": config,
         "e2e": {"value": B * world / (ms_e2e * 1e-3 / args.steps), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / args.steps},
-        "gpu_launches": launches, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu,
+        "gpu_launches": launches, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "incumbent": inc,
     }))
     _finish(world)
 
 
 def main():
     args = parse()
+    cfg = resolve_config(args)
     if args.impl == "reference":
-        run_reference(args)
+        run_reference(args, cfg)
     else:
-        run_ours(args)
+        run_ours(args, cfg)
 
 
 if __name__ == "__main__":

@@ -32,6 +32,7 @@ SIGNATURES = {
     "dei2i_last_error": (C.c_char_p, []),
     "dei2i_set_tuning": (_I, [C.c_char_p, _I]),
     "dei2i_launch_count": (_LL, []),
+    "dei2i_last_kernel": (C.c_char_p, []),
     "dei2i_pack_weight": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     "dei2i_conv2d_fwd": (_I, [_P, _P, _P, C.POINTER(ConvGeom), C.POINTER(ConvEpilogue), _P]),
     "dei2i_conv2d_dgrad": (_I, [_P, _P, _P, C.POINTER(ConvGeom), _P, _I, _P]),

@@ -4,6 +4,7 @@
 #include <string.h>
 
 #include <atomic>
+#include <mutex>
 
 #include "common.cuh"
 #include "../../include/dei2i.h"
@@ -29,11 +30,25 @@ int g_tune_conv_stages = 0;
 int g_tune_conv_bn = 0;
 int g_tune_wgrad_bn = 0;
 int g_tune_wgrad_waves = 0;
-int g_tune_tma_dbg = 0;
 int g_tune_tma_ms = 0;
 int g_tune_conv_path = 0;  // 0 = auto (TMA im2col kernels where applicable), 1 = always the cp.async gather kernels
 static std::atomic<long long> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+// Which kernel variants the calling thread's most recent convolution entry point enqueued ("conv_tma<128,4,2>",
+// "wgrad_tma<1,4>+wgrad_reduce", ...): lets the parity tests assert that a geometry really ran on the variant it is meant to
+// cover (dei2i_last_kernel).  Host-side bookkeeping only.
+static thread_local char g_trace[256] = "";
+void trace_begin() { g_trace[0] = 0; }
+void trace_kernel(const char* fmt, ...) {
+  size_t n = strlen(g_trace);
+  if (n + 2 >= sizeof(g_trace)) return;
+  if (n) g_trace[n++] = '+';
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_trace + n, sizeof(g_trace) - n, fmt, ap);
+  va_end(ap);
+}
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -50,17 +65,17 @@ static void bind_primary_context() {
   }
 }
 
+// resolved once, thread-safely (the autograd worker thread and the main thread both encode descriptors)
 static EncodeTiledFn get_encode() {
   static EncodeTiledFn fn = nullptr;
-  static bool tried = false;
-  if (!tried) {
-    tried = true;
+  static std::once_flag once;
+  std::call_once(once, [] {
     void* p = nullptr;
     cudaDriverEntryPointQueryResult q;
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
         q == cudaDriverEntryPointSuccess)
       fn = (EncodeTiledFn)p;
-  }
+  });
   return fn;
 }
 
@@ -100,17 +115,16 @@ int encode_tmap_im2col_bf16(CUtensorMap* out, const void* base, uint64_t C, uint
                             uint32_t pixels_per_column) {
   bind_primary_context();
   static EncodeIm2colFn fn = nullptr;
-  static bool tried = false;
   static int driver_version = 0;
-  if (!tried) {
-    tried = true;
+  static std::once_flag once;
+  std::call_once(once, [] {
     void* p = nullptr;
     cudaDriverEntryPointQueryResult q;
     if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &q) == cudaSuccess &&
         q == cudaDriverEntryPointSuccess)
       fn = (EncodeIm2colFn)p;
     cudaDriverGetVersion(&driver_version);
-  }
+  });
   if (fn == nullptr) {
     set_error("cuTensorMapEncodeIm2col is not available (no CUDA driver / no sm_100 device)");
     return DEI2I_ERR_CUDA;
@@ -144,6 +158,7 @@ int encode_tmap_im2col_bf16(CUtensorMap* out, const void* base, uint64_t C, uint
 extern "C" int dei2i_version(void) { return 100; }
 extern "C" const char* dei2i_last_error(void) { return dei2i::g_err; }
 extern "C" long long dei2i_launch_count(void) { return dei2i::g_launches.load(); }
+extern "C" const char* dei2i_last_kernel(void) { return dei2i::g_trace; }
 extern "C" int dei2i_set_tuning(const char* key, int value) {
   int* slot = nullptr;
   if (!strcmp(key, "conv_stages")) slot = &dei2i::g_tune_conv_stages;
@@ -151,7 +166,6 @@ extern "C" int dei2i_set_tuning(const char* key, int value) {
   else if (!strcmp(key, "wgrad_bn")) slot = &dei2i::g_tune_wgrad_bn;
   else if (!strcmp(key, "wgrad_waves")) slot = &dei2i::g_tune_wgrad_waves;
   else if (!strcmp(key, "conv_path")) slot = &dei2i::g_tune_conv_path;
-  else if (!strcmp(key, "tma_dbg")) slot = &dei2i::g_tune_tma_dbg;
   else if (!strcmp(key, "tma_ms")) slot = &dei2i::g_tune_tma_ms;
   if (slot == nullptr) return -1;
   int old = *slot;

@@ -90,7 +90,6 @@ struct TmaConvParams {
   int b_sub, b_py, b_px, b_kw;
   int num_kb;      // taps * cin_blocks
   int m_tiles, n_tiles;
-  int dbg;         // experiments only (tuning knob tma_dbg): bit0 skip stores, bit1 skip TMEM loads, bit2 skip MMA wait
   OutMap om;
   Epilogue e;
 };

@@ -30,6 +30,8 @@ extern int g_tune_wgrad_bn;     // 0 = auto
 extern int g_tune_wgrad_waves;
 extern int g_tune_conv_path;
 void count_launch(int n = 1);
+void trace_kernel(const char* fmt, ...);
+void trace_begin();
 
 struct ConvKParams {
   Gather g;
@@ -575,6 +577,7 @@ static int launch_conv(const CUtensorMap& tm, const ConvKParams& p, int n_tiles,
   dim3 grid((unsigned)m_tiles, (unsigned)n_tiles, 1);
   conv_igemm_kernel<BN, ST><<<grid, kThreads, S::kTotal, st>>>(tm, p);
   count_launch();
+  trace_kernel("conv_igemm<%d,%d>", BN, ST);
   return check_cuda(cudaGetLastError(), "conv_igemm_kernel launch");
 }
 
@@ -632,6 +635,7 @@ using namespace dei2i;
 
 extern "C" int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const dei2i_conv_geom* g,
                                 const dei2i_conv_epilogue* e, dei2i_stream stream) {
+  trace_begin();
   if (int rc = check_geom(g)) return rc;
   DEI2I_REQUIRE(x && w_fwd && y && e, "conv2d_fwd: null pointer");
   DEI2I_REQUIRE(e->noise == nullptr || e->noise_weight != nullptr, "conv2d_fwd: noise without noise_weight");
@@ -679,6 +683,7 @@ extern "C" int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const
 
 extern "C" int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx, const dei2i_conv_geom* g, const float* scale,
                                   int out_fp32, dei2i_stream stream) {
+  trace_begin();
   if (int rc = check_geom(g)) return rc;
   DEI2I_REQUIRE(dy && w_dgrad && dx, "conv2d_dgrad: null pointer");
   DEI2I_REQUIRE(g->Hs == g->H && g->Ws == g->W, "conv2d_dgrad: resized inputs are not supported");
@@ -811,12 +816,14 @@ static int launch_wgrad(const CUtensorMap& tm, const WgradKParams& p, dim3 grid,
   }
   conv_wgrad_kernel<BN, ST><<<grid, kThreads, S::kTotal, st>>>(tm, p);
   count_launch();
+  trace_kernel("conv_wgrad<%d,%d>", BN, ST);
   return check_cuda(cudaGetLastError(), "conv_wgrad_kernel launch");
 }
 
 extern "C" int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int Cin_real, float beta,
                                   const dei2i_conv_geom* g, const float* sn_w_orig, const float* sn_u, const float* sn_v,
                                   const float* sn_inv_sigma, void* workspace, size_t workspace_bytes, dei2i_stream stream) {
+  trace_begin();
   if (int rc = check_geom(g)) return rc;
   DEI2I_REQUIRE(x && dy && dw && workspace, "conv2d_wgrad: null pointer");
   DEI2I_REQUIRE(Cin_real > 0 && Cin_real <= g->Cin, "conv2d_wgrad: bad Cin_real");

@@ -21,6 +21,7 @@
 namespace dei2i {
 
 void count_launch(int n = 1);
+void trace_kernel(const char* fmt, ...);
 extern int g_tune_conv_path;  // 2: CUDA-core heads wgrad kernel instead of the mma.sync one (A/B testing)
 
 // ======================================================================================================================
@@ -91,6 +92,7 @@ int run_wgrad_narrow(const Gather& g, const void* dy, int Cout, int Cout_ld, int
   // columns [Kreal, Kf) of the partial buffer are never read by wgrad_reduce_kernel (it walks real taps / channels only)
   wgrad_narrow_kernel<<<grid, 256, 0, st>>>(g, (const __nv_bfloat16*)dy, Cout, Cout_ld, Kf, partial, pps);
   count_launch();
+  trace_kernel("wgrad_narrow");
   return check_cuda(cudaGetLastError(), "wgrad_narrow_kernel launch");
 }
 
@@ -357,6 +359,7 @@ static int launch_c8(const C8Params& p, cudaStream_t st) {
   const int grid = p.m_tiles < 148 * 2 ? p.m_tiles : 148 * 2;
   conv_c8_fwd_kernel<NT, FAST><<<grid, kC8Threads, smem, st>>>(p);
   count_launch();
+  trace_kernel("conv_c8_fwd<%d,%d>", NT, (int)FAST);
   return check_cuda(cudaGetLastError(), "conv_c8_fwd_kernel launch");
 }
 
@@ -557,6 +560,7 @@ static int launch_wgrad_c8(const WgC8Params& p, int grid, cudaStream_t st) {
   }
   wgrad_c8_kernel<NT, P><<<grid, 256, smem, st>>>(p);
   count_launch();
+  trace_kernel("wgrad_c8<%d,%d>", NT, P);
   return check_cuda(cudaGetLastError(), "wgrad_c8_kernel launch");
 }
 
@@ -933,6 +937,7 @@ int run_conv_heads_fwd(const Gather& g, const Epilogue& e, const void* wmat, int
   const int grid = (nrows + rpc - 1) / rpc;
   conv_heads_fwd_kernel<<<grid, kHmWarps * 32, sm, st>>>(g, e, (const __nv_bfloat16*)wmat, rows, Kf, rpc);
   count_launch();
+  trace_kernel("conv_heads_fwd");
   return check_cuda(cudaGetLastError(), "conv_heads_fwd_kernel launch");
 }
 
@@ -998,6 +1003,7 @@ bool conv_narrow_fwd_applicable(const Gather& g, int rows_ld) {
 int run_conv_narrow_fwd(const Gather& g, const Epilogue& e, const void* wmat, int rows, int Kf, cudaStream_t st) {
   conv_narrow_fwd_kernel<<<(unsigned)g.M, 256, 0, st>>>(g, e, (const __nv_bfloat16*)wmat, rows < 8 ? rows : 8, Kf);
   count_launch();
+  trace_kernel("conv_narrow_fwd");
   return check_cuda(cudaGetLastError(), "conv_narrow_fwd_kernel launch");
 }
 
@@ -1019,10 +1025,12 @@ int run_wgrad_heads(const Gather& g, const void* dy, int Cout, int Cout_ld, int 
     // CTAs past the last strip still write their (zero) partial tile: the second pass sums all 148
     wgrad_heads_mma_kernel<<<148, kHmWarps * 32, sm, st>>>(g, (const __nv_bfloat16*)dy, Cout, Kf, partial, rpc);
     count_launch();
+  trace_kernel("wgrad_heads_mma");
     return check_cuda(cudaGetLastError(), "wgrad_heads_mma_kernel launch");
   }
   wgrad_heads_kernel<<<148, kHeadsWarps * 32, 0, st>>>(g, (const __nv_bfloat16*)dy, Cout, Cout_ld, Kf, partial);
   count_launch();
+  trace_kernel("wgrad_heads");
   return check_cuda(cudaGetLastError(), "wgrad_heads_kernel launch");
 }
 

@@ -19,6 +19,7 @@
 namespace dei2i {
 
 void count_launch(int n = 1);
+void trace_kernel(const char* fmt, ...);
 
 constexpr int kTmaThreads = 192;
 constexpr int kTmaATile = 128 * 128;  // 128 pixels x 64 bf16
@@ -193,13 +194,13 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         float f[64];
         {
           uint32_t v[32];
-          if (!(p.dbg & 2)) tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + tcol0 + (uint32_t)c, v);
-          if (!(p.dbg & 2)) tc_wait_ld();
+          tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + tcol0 + (uint32_t)c, v);
+          tc_wait_ld();
 #pragma unroll
           for (int t = 0; t < 32; ++t) f[t] = __uint_as_float(v[t]) * osc;
           if (CW == 64) {
-            if (!(p.dbg & 2)) tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + tcol0 + (uint32_t)(c + 32), v);
-            if (!(p.dbg & 2)) tc_wait_ld();
+            tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + tcol0 + (uint32_t)(c + 32), v);
+            tc_wait_ld();
 #pragma unroll
             for (int t = 0; t < 32; ++t) f[32 + t] = __uint_as_float(v[t]) * osc;
           }
@@ -277,7 +278,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           const long long orow_r = __shfl_sync(0xffffffffu, orow, r);
           const int ok_r = __shfl_sync(0xffffffffu, (int)row_ok, r);
           const uint4 val = *reinterpret_cast<const uint4*>(stage + r * 128 + ((sub_j ^ (r & 7)) << 4));
-          if (ok_r && col < e.ld && !(p.dbg & 1))
+          if (ok_r && col < e.ld)
             *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(e.out) + (orow_r * e.ld + col) * esz) = val;
         }
         __syncwarp();
@@ -321,15 +322,14 @@ static int launch_tma(const CUtensorMap& ta, const CUtensorMap& tb, const TmaCon
   const int grid = total < num_sms() ? total : num_sms();
   conv_tma_kernel<BN, ST, MS><<<grid, kTmaThreads, S::kTotal, st>>>(ta, tb, p);
   count_launch();
+  trace_kernel("conv_tma<%d,%d,%d>", BN, ST, MS);
   return check_cuda(cudaGetLastError(), "conv_tma_kernel launch");
 }
 
-extern int g_tune_tma_dbg;
 extern int g_tune_tma_ms;  // 0 = auto, 1 / 2 = force the number of 128-pixel sub-tiles per work tile
 int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, int rows, int K, const TmaConvParams& p_in,
                  int upper, int upper_w, cudaStream_t st) {
   TmaConvParams p = p_in;
-  p.dbg = g_tune_tma_dbg;
   int bn = 256;
   while (bn > 64 && bn / 2 >= rows) bn /= 2;
   CUtensorMap ta, tb;
@@ -523,6 +523,7 @@ static int launch_wgrad_tma(const CUtensorMap& tdy, const CUtensorMap& tx, const
   const int grid = p.co_groups * p.k_tiles * p.splits;
   wgrad_tma_kernel<CO_T, ST><<<grid, kTmaThreads, S::kTotal, st>>>(tdy, tx, p);
   count_launch();
+  trace_kernel("wgrad_tma<%d,%d>", CO_T, ST);
   return check_cuda(cudaGetLastError(), "wgrad_tma_kernel launch");
 }
 

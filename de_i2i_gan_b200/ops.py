@@ -15,6 +15,13 @@ PAD = {"zeros": 0, "reflect": 1}
 # Optional in-band kernel timing (bench.py's roofline): when PROFILE is a list every convolution launch is bracketed
 # by CUDA events on the launching stream and appended as (kind, algorithmic_flops, start_event, end_event).
 PROFILE = None
+# Optional kernel-variant log (parity tests): when a list, every convolution call appends (op, geometry tag, dei2i_last_kernel()).
+KERNEL_LOG = None
+
+
+def _log_kernel(op, tag):
+    if KERNEL_LOG is not None:
+        KERNEL_LOG.append((op, tag, last_kernel()))
 
 
 class _Timed:
@@ -157,6 +164,7 @@ def conv2d_fwd(x, w_fwd, spec: ConvSpec, bias=None, noise=None, noise_weight=Non
     fl = alg_flops or spec.flops(n, ho, wo)
     with _Timed(_kind("fwd", spec, fl), fl, spec.tag(n, h, w)):
         check(_lib.load().dei2i_conv2d_fwd(_p(x), _p(w_fwd), _p(y), C.byref(g), C.byref(e), _stream()), "dei2i_conv2d_fwd")
+    _log_kernel("fwd", spec.tag(n, h, w))
     return y
 
 
@@ -174,12 +182,14 @@ def conv2d_dgrad(dy, w_dgrad, spec: ConvSpec, in_hw, scale=None, alg_flops=None)
         dxp = torch.empty(n, h + 2 * p, w + 2 * p, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
         with _Timed(_kind("dgrad", spec, flops), flops, spec.tag(n, h, w)):
             check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dxp), C.byref(g), _p(scale), 0, _stream()), "dei2i_conv2d_dgrad")
+        _log_kernel("dgrad", spec.tag(n, h, w))
         dx = torch.empty(n, h, w, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
         check(lib.dei2i_reflect_fold(_p(dxp), _p(dx), n, h, w, spec.cin_ld, p, _stream()), "dei2i_reflect_fold")
         return dx
     dx = torch.empty(n, h, w, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
     with _Timed(_kind("dgrad", spec, flops), flops, spec.tag(n, h, w)):
         check(lib.dei2i_conv2d_dgrad(_p(dy), _p(w_dgrad), _p(dx), C.byref(g), _p(scale), 0, _stream()), "dei2i_conv2d_dgrad")
+    _log_kernel("dgrad", spec.tag(n, h, w))
     return dx
 
 
@@ -188,7 +198,8 @@ def reflect_pad(x, pad: int):
     _chk_act(x, "x")
     n, h, w, c = x.shape
     xp = torch.empty(n, h + 2 * pad, w + 2 * pad, c, dtype=torch.bfloat16, device=x.device)
-    check(_lib.load().dei2i_reflect_pad(_p(x), _p(xp), n, h, w, c, pad, _stream()), "dei2i_reflect_pad")
+    with _Timed("stream_reflect_pad", x.numel() * 2 + xp.numel() * 2, ""):
+        check(_lib.load().dei2i_reflect_pad(_p(x), _p(xp), n, h, w, c, pad, _stream()), "dei2i_reflect_pad")
     return xp
 
 
@@ -198,18 +209,22 @@ def reflect_fold(dxp, pad: int):
     n, hp, wp, c = dxp.shape
     h, w = hp - 2 * pad, wp - 2 * pad
     dx = torch.empty(n, h, w, c, dtype=torch.bfloat16, device=dxp.device)
-    check(_lib.load().dei2i_reflect_fold(_p(dxp), _p(dx), n, h, w, c, pad, _stream()), "dei2i_reflect_fold")
+    with _Timed("stream_reflect_fold", dxp.numel() * 2 + dx.numel() * 2, ""):
+        check(_lib.load().dei2i_reflect_fold(_p(dxp), _p(dx), n, h, w, c, pad, _stream()), "dei2i_reflect_fold")
     return dx
 
 
 _ws_cache = {}
+_ws_retired = []  # outgrown workspaces stay alive: a captured CUDA graph may still hold their address
 
 
 def _workspace(nbytes, device):
     key = (device.index, torch.cuda.current_stream().cuda_stream)
     buf = _ws_cache.get(key)
     if buf is None or buf.numel() < nbytes:
-        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, device=device)
+        if buf is not None:
+            _ws_retired.append(buf)
+        buf = torch.empty(max(nbytes, 64 << 20), dtype=torch.uint8, device=device)
         _ws_cache[key] = buf
     return buf
 
@@ -230,6 +245,7 @@ def conv2d_wgrad(x, dy, dw, spec: ConvSpec, accumulate=False, sn=None, logical_h
     with _Timed(_kind("wgrad", spec, fl), fl, spec.tag(n, h, w)):
         check(lib.dei2i_conv2d_wgrad(_p(x), _p(dy), _p(dw), spec.cin, 1.0 if accumulate else 0.0, C.byref(g), _p(w0), _p(u),
                                      _p(v), _p(inv), _p(wsb), wsb.numel(), _stream()), "dei2i_conv2d_wgrad")
+    _log_kernel("wgrad", spec.tag(n, h, w))
     return dw
 
 
@@ -298,7 +314,8 @@ def rowpack_fwd(img: torch.Tensor, kw: int, pad: int):
     _chk_f32(img, "img")
     n, c, h, w = img.shape
     xp = torch.empty(n, h + 2 * pad, w, 64, dtype=torch.bfloat16, device=img.device)
-    check(_lib.load().dei2i_rowpack_fwd(_p(img), _p(xp), n, c, h, w, kw, pad, _stream()), "dei2i_rowpack_fwd")
+    with _Timed("stream_rowpack", img.numel() * 4 + xp.numel() * 2, ""):
+        check(_lib.load().dei2i_rowpack_fwd(_p(img), _p(xp), n, c, h, w, kw, pad, _stream()), "dei2i_rowpack_fwd")
     return xp
 
 
@@ -308,7 +325,8 @@ def rowpack_bwd(dxp: torch.Tensor, c: int, kw: int, pad: int):
     n, hp, w, _ = dxp.shape
     h = hp - 2 * pad
     dimg = torch.empty(n, c, h, w, dtype=torch.float32, device=dxp.device)
-    check(_lib.load().dei2i_rowpack_bwd(_p(dxp), _p(dimg), n, c, h, w, kw, pad, _stream()), "dei2i_rowpack_bwd")
+    with _Timed("stream_rowpack", dimg.numel() * 4 + dxp.numel() * 2, ""):
+        check(_lib.load().dei2i_rowpack_bwd(_p(dxp), _p(dimg), n, c, h, w, kw, pad, _stream()), "dei2i_rowpack_bwd")
     return dimg
 
 
@@ -391,7 +409,8 @@ def channel_stats(x, per_sample: bool):
     _chk_act(x, "x")
     n, h, w, c = x.shape
     stats = torch.empty(n if per_sample else 1, 2, c, dtype=torch.float32, device=x.device)
-    check(_lib.load().dei2i_channel_stats(_p(x), n, h * w, c, int(per_sample), _p(stats), _stream()), "dei2i_channel_stats")
+    with _Timed("stream_channel_stats", x.numel() * 2, ""):
+        check(_lib.load().dei2i_channel_stats(_p(x), n, h * w, c, int(per_sample), _p(stats), _stream()), "dei2i_channel_stats")
     return stats
 
 
@@ -403,14 +422,16 @@ def bn_fwd(x, gamma, beta, running_mean, running_var, training, act=None, residu
     save = torch.empty(2, c, dtype=torch.float32, device=x.device)
     if out_pad:
         y = torch.empty(n, h + 2 * out_pad, w + 2 * out_pad, c, dtype=x.dtype, device=x.device)
-        check(_lib.load().dei2i_bn_fwd_pad(_p(x), _p(y), _p(residual), _p(stats), _p(gamma), _p(beta), _p(running_mean),
-                                           _p(running_var), _p(save[0]), _p(save[1]), n, h, w, c, int(training), momentum, eps,
-                                           ACT[act], int(out_pad), _stream()), "dei2i_bn_fwd_pad")
+        with _Timed("stream_bn_fwd", x.numel() * 2 + y.numel() * 2 + (residual.numel() * 2 if residual is not None else 0), ""):
+            check(_lib.load().dei2i_bn_fwd_pad(_p(x), _p(y), _p(residual), _p(stats), _p(gamma), _p(beta), _p(running_mean),
+                                               _p(running_var), _p(save[0]), _p(save[1]), n, h, w, c, int(training), momentum, eps,
+                                               ACT[act], int(out_pad), _stream()), "dei2i_bn_fwd_pad")
         return y, save
     y = torch.empty_like(x)
-    check(_lib.load().dei2i_bn_fwd(_p(x), _p(y), _p(residual), _p(stats), _p(gamma), _p(beta), _p(running_mean),
-                                   _p(running_var), _p(save[0]), _p(save[1]), n, h * w, c, int(training), momentum, eps,
-                                   ACT[act], _stream()), "dei2i_bn_fwd")
+    with _Timed("stream_bn_fwd", x.numel() * 2 * (2 + int(residual is not None)), ""):
+        check(_lib.load().dei2i_bn_fwd(_p(x), _p(y), _p(residual), _p(stats), _p(gamma), _p(beta), _p(running_mean),
+                                       _p(running_var), _p(save[0]), _p(save[1]), n, h * w, c, int(training), momentum, eps,
+                                       ACT[act], _stream()), "dei2i_bn_fwd")
     return y, save
 
 
@@ -421,8 +442,9 @@ def bn_bwd(x, dy, gamma, beta, save, training, act=None):
     dx = torch.empty_like(x)
     dgb = torch.empty(2, c, dtype=torch.float32, device=x.device)
     scratch = torch.empty(2 * c, dtype=torch.float32, device=x.device)
-    check(_lib.load().dei2i_bn_bwd(_p(x), _p(dy), _p(dx), _p(gamma), _p(beta), _p(save[0]), _p(save[1]), _p(dgb[0]),
-                                   _p(dgb[1]), _p(scratch), n, h * w, c, int(training), ACT[act], _stream()), "dei2i_bn_bwd")
+    with _Timed("stream_bn_bwd", x.numel() * 2 * 3, ""):
+        check(_lib.load().dei2i_bn_bwd(_p(x), _p(dy), _p(dx), _p(gamma), _p(beta), _p(save[0]), _p(save[1]), _p(dgb[0]),
+                                       _p(dgb[1]), _p(scratch), n, h * w, c, int(training), ACT[act], _stream()), "dei2i_bn_bwd")
     return dx, dgb[0], dgb[1]
 
 
@@ -436,8 +458,9 @@ def spade_fwd(x, gb, up: int = 1, relu: bool = True, eps: float = 1e-5):
     stats = channel_stats(x, True)
     out = torch.empty(n, h, w, c, dtype=torch.bfloat16, device=x.device)
     mr = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
-    check(_lib.load().dei2i_spade_fwd(_p(x), _p(gb), _p(out), _p(stats), _p(mr), n, h, w, c, up, int(relu), eps, _stream()),
-          "dei2i_spade_fwd")
+    with _Timed("stream_spade_fwd", x.numel() * 2 + gb.numel() * 2 + out.numel() * 2, ""):
+        check(_lib.load().dei2i_spade_fwd(_p(x), _p(gb), _p(out), _p(stats), _p(mr), n, h, w, c, up, int(relu), eps, _stream()),
+              "dei2i_spade_fwd")
     return out, mr
 
 
@@ -446,8 +469,9 @@ def spade_bwd(x, gb, out, dout, mean_rstd, up: int = 1, relu: bool = True):
     dgb = torch.empty_like(gb)
     dx = torch.empty_like(x)
     scratch = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
-    check(_lib.load().dei2i_spade_bwd(_p(x), _p(gb), _p(out), _p(dout), _p(dgb), _p(dx), _p(mean_rstd), _p(scratch), n, h, w,
-                                      c, up, int(relu), _stream()), "dei2i_spade_bwd")
+    with _Timed("stream_spade_bwd", x.numel() * 2 + 2 * gb.numel() * 2 + 2 * out.numel() * 2 + dx.numel() * 2, ""):
+        check(_lib.load().dei2i_spade_bwd(_p(x), _p(gb), _p(out), _p(dout), _p(dgb), _p(dx), _p(mean_rstd), _p(scratch), n, h, w,
+                                          c, up, int(relu), _stream()), "dei2i_spade_bwd")
     return dgb, dx
 
 
@@ -462,8 +486,9 @@ def spade_cls_fwd(x, gb5, up: int = 1, relu: bool = True, eps: float = 1e-5, out
     stats = channel_stats(x, True)
     out = torch.empty(n, h + 2 * out_pad, w + 2 * out_pad, c, dtype=torch.bfloat16, device=x.device)
     mr = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
-    check(_lib.load().dei2i_spade_cls_fwd(_p(x), _p(gb5), _p(out), _p(stats), _p(mr), n, h, w, c, up, int(relu), eps, out_pad,
-                                          _stream()), "dei2i_spade_cls_fwd")
+    with _Timed("stream_spade_cls_fwd", x.numel() * 2 + out.numel() * 2, ""):
+        check(_lib.load().dei2i_spade_cls_fwd(_p(x), _p(gb5), _p(out), _p(stats), _p(mr), n, h, w, c, up, int(relu), eps, out_pad,
+                                              _stream()), "dei2i_spade_cls_fwd")
     return out, mr
 
 
@@ -475,8 +500,9 @@ def spade_cls_bwd(x, gb5, out, dout, mean_rstd, up: int = 1, relu: bool = True, 
     dgb5 = torch.empty(n, 5, 5, 2 * c, dtype=torch.float32, device=x.device)
     dx = torch.empty_like(x)
     scratch = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
-    check(_lib.load().dei2i_spade_cls_bwd(_p(x), _p(gb5), _p(out), _p(dout), _p(dgb5), _p(dx), _p(mean_rstd), _p(scratch), n, h,
-                                          w, c, up, int(relu), out_pad, _stream()), "dei2i_spade_cls_bwd")
+    with _Timed("stream_spade_cls_bwd", x.numel() * 2 * 2 + dout.numel() * 2, ""):
+        check(_lib.load().dei2i_spade_cls_bwd(_p(x), _p(gb5), _p(out), _p(dout), _p(dgb5), _p(dx), _p(mean_rstd), _p(scratch), n, h,
+                                              w, c, up, int(relu), out_pad, _stream()), "dei2i_spade_cls_bwd")
     return dgb5, dx
 
 
@@ -529,15 +555,17 @@ def act_bwd(y, dy, act, want_dx=True, want_bias_grad=False):
     m = dy.numel() // c
     dx = torch.empty_like(dy) if want_dx else None
     bg = torch.empty(c, dtype=torch.float32, device=dy.device) if want_bias_grad else None
-    check(_lib.load().dei2i_act_bwd(_p(y), _p(dy), _p(dx), _p(bg), m, c, ACT[act], _stream()), "dei2i_act_bwd")
+    with _Timed("stream_act_bwd", dy.numel() * 2 * (int(y is not None) + 1 + int(want_dx)), ""):
+        check(_lib.load().dei2i_act_bwd(_p(y), _p(dy), _p(dx), _p(bg), m, c, ACT[act], _stream()), "dei2i_act_bwd")
     return dx, bg
 
 
 def noise_wgrad(dy, noise, dw, c_real, accumulate=False):
     c = dy.shape[3]
     m = dy.numel() // c
-    check(_lib.load().dei2i_noise_wgrad(_p(dy), _p(noise), _p(dw), m, c, c_real, 1.0 if accumulate else 0.0, _stream()),
-          "dei2i_noise_wgrad")
+    with _Timed("stream_noise_wgrad", dy.numel() * 2, ""):
+        check(_lib.load().dei2i_noise_wgrad(_p(dy), _p(noise), _p(dw), m, c, c_real, 1.0 if accumulate else 0.0, _stream()),
+              "dei2i_noise_wgrad")
     return dw
 
 
@@ -547,8 +575,9 @@ def compose_fwd(hd, x, cycle_gan=False, want_nhwc=True):
     out = torch.empty(n, 3, h, w, dtype=torch.float32, device=hd.device)
     prob = torch.empty(n, 1, h, w, dtype=torch.float32, device=hd.device)
     onhwc = torch.empty(n, h, w, 8, dtype=torch.bfloat16, device=hd.device) if want_nhwc else None
-    check(_lib.load().dei2i_compose_fwd(_p(hd), _p(x), _p(out), _p(prob), _p(onhwc), n, h, w, int(cycle_gan), _stream()),
-          "dei2i_compose_fwd")
+    with _Timed("stream_compose", hd.numel() * 4 + x.numel() * 4 + out.numel() * 4 + prob.numel() * 4, ""):
+        check(_lib.load().dei2i_compose_fwd(_p(hd), _p(x), _p(out), _p(prob), _p(onhwc), n, h, w, int(cycle_gan), _stream()),
+              "dei2i_compose_fwd")
     return out, prob, onhwc
 
 
@@ -556,8 +585,9 @@ def compose_bwd(hd, x, dout, dprob, cycle_gan=False, want_dx=True):
     n, h, w, _ = hd.shape
     dhd = torch.empty(n, h, w, 8, dtype=torch.bfloat16, device=hd.device)
     dx = torch.empty(n, 3, h, w, dtype=torch.float32, device=hd.device) if want_dx else None
-    check(_lib.load().dei2i_compose_bwd(_p(hd), _p(x), _p(dout), _p(dprob), _p(dhd), _p(dx), n, h, w, int(cycle_gan),
-                                        _stream()), "dei2i_compose_bwd")
+    with _Timed("stream_compose", hd.numel() * 4 + x.numel() * 4 + dhd.numel() * 2 + (dout.numel() * 4 if dout is not None else 0), ""):
+        check(_lib.load().dei2i_compose_bwd(_p(hd), _p(x), _p(dout), _p(dprob), _p(dhd), _p(dx), n, h, w, int(cycle_gan),
+                                            _stream()), "dei2i_compose_bwd")
     return dhd, dx
 
 
@@ -620,6 +650,11 @@ def ema_(p, p_ema, beta):
 
 def launch_count() -> int:
     return int(_lib.load().dei2i_launch_count())
+
+
+def last_kernel() -> str:
+    """Kernel variants the most recent conv2d_fwd / dgrad / wgrad call of this thread enqueued ('conv_tma<128,4,2>', ...)."""
+    return _lib.load().dei2i_last_kernel().decode()
 
 
 def set_tuning(key: str, value: int) -> int:

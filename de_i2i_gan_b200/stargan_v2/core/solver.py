@@ -75,3 +75,80 @@ def moving_average(model, model_test, beta=0.999):
     """solver.py:549-551: param_test = lerp(param, param_test, beta) (dei2i_ema, in place)."""
     for param, param_test in zip(model.parameters(), model_test.parameters()):
         ops.ema_(param.data.contiguous(), param_test.data, beta)
+
+
+# ------------------------------------------------------------------------------------------------ training iteration
+def he_init(module):
+    """core/utils.py:38-46: Kaiming-normal weights, zero bias, for every nn.Conv2d / nn.Linear."""
+    if isinstance(module, (torch.nn.Conv2d, torch.nn.Linear)):
+        torch.nn.init.kaiming_normal_(module.weight, mode="fan_in", nonlinearity="relu")
+        if module.bias is not None:
+            torch.nn.init.constant_(module.bias, 0)
+
+
+def build_training_state(args, device):
+    """What ``Solver.__init__`` sets up for training in adain mode (solver.py:49-91): the four networks + their EMA copies
+    (``build_model``), he_init of every network, and one Adam per network (lr ``args.lr``, the mapping network ``args.f_lr``,
+    betas (beta1, beta2), weight decay) - FlatAdam on the fused kernel.  Returns a namespace (nets, nets_ema, optims,
+    initial_lambda_ds)."""
+    from ...optim import FlatAdam
+    from . import model as M
+    nets, nets_ema = M.build_nets(args)
+    for name, net in vars(nets).items():
+        net.apply(he_init)
+        net.to(device)
+    for name, net in vars(nets_ema).items():
+        net.load_state_dict(getattr(nets, name).state_dict())  # solver.py: the EMA copies start as deep copies of the live nets
+        net.to(device)
+    optims = SimpleNamespace(**{
+        name: FlatAdam(list(net.parameters()), lr=getattr(args, "f_lr", 1e-6) if name == "mapping_network" else getattr(args, "lr", 1e-4),
+                       betas=(getattr(args, "beta1", 0.0), getattr(args, "beta2", 0.99)), weight_decay=getattr(args, "weight_decay", 1e-4))
+        for name, net in vars(nets).items()})
+    return SimpleNamespace(nets=nets, nets_ema=nets_ema, optims=optims, initial_lambda_ds=args.lambda_ds)
+
+
+def _reset_grad(optims):
+    """solver.py:127-129."""
+    for o in vars(optims).values():
+        o.zero_grad()
+
+
+def train_iteration(state, args, inputs, masks=None):
+    """One pass of the loop body of ``Solver.train`` in adain mode (solver.py:258-308): discriminator on latent-generated and
+    on reference-generated fakes (each with the R1 double backward), generator on latent codes (+ mapping network and style
+    encoder steps) and on reference images, the three EMA updates, and the linear decay of the diversity-loss weight.
+    ``inputs``: namespace with x_src, y_src, x_ref, x_ref2, y_ref, z_trg, z_trg2 (what InputFetcher yields).  Returns the four log
+    namespaces (d_latent, d_ref, g_latent, g_ref)."""
+    nets, nets_ema, optims = state.nets, state.nets_ema, state.optims
+    x_real, y_org = inputs.x_src, inputs.y_src
+    x_ref, x_ref2, y_trg = inputs.x_ref, inputs.x_ref2, inputs.y_ref
+    z_trg, z_trg2 = inputs.z_trg, inputs.z_trg2
+    with Fn.weight_cache():
+        # compute_d_loss marks its image argument as requiring grad (R1); a detached alias keeps that off ``x_real`` itself
+        d_loss, d_latent = compute_d_loss(nets, args, x_real.detach(), y_org, y_trg, z_trg=z_trg, masks=masks)
+        _reset_grad(optims)
+        d_loss.backward()
+    optims.discriminator.step()
+    with Fn.weight_cache():
+        d_loss, d_ref = compute_d_loss(nets, args, x_real.detach(), y_org, y_trg, x_ref=x_ref, masks=masks)
+        _reset_grad(optims)
+        d_loss.backward()
+    optims.discriminator.step()
+    with Fn.weight_cache():
+        g_loss, g_latent = compute_g_loss(nets, args, x_real, y_org, y_trg, z_trgs=[z_trg, z_trg2], masks=masks)
+        _reset_grad(optims)
+        g_loss.backward()
+    optims.generator.step()
+    optims.mapping_network.step()
+    optims.style_encoder.step()
+    with Fn.weight_cache():
+        g_loss, g_ref = compute_g_loss(nets, args, x_real, y_org, y_trg, x_refs=[x_ref, x_ref2], masks=masks)
+        _reset_grad(optims)
+        g_loss.backward()
+    optims.generator.step()
+    moving_average(nets.generator, nets_ema.generator, beta=0.999)
+    moving_average(nets.mapping_network, nets_ema.mapping_network, beta=0.999)
+    moving_average(nets.style_encoder, nets_ema.style_encoder, beta=0.999)
+    if args.lambda_ds > 0:  # solver.py:303-304
+        args.lambda_ds -= state.initial_lambda_ds / args.ds_iter
+    return d_latent, d_ref, g_latent, g_ref

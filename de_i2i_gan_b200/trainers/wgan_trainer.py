@@ -27,6 +27,68 @@ class WGanTrainer(BaseTrainer):
         fake = self.model.netG(self.fix_noise)
         return (fake / 2 + 0.5).detach().cpu()
 
+    # ------------------------------------------------------------------------------------------------ epoch loop
+    def train(self, train_loader, val_loader=None):
+        """wgan_trainer.py:69-84: epochs 1..num_epochs; per epoch the losses / D(x) records are cleared, the loader is walked
+        (_train_epoch), the optional validation pass records D(x) on held-out images, TensorBoard scalars + an image grid of the
+        fixed noise are written (only when ``opt.log_dir`` is set and tensorboard is importable) and a checkpoint is saved every
+        ``save_ckpt_freq`` epochs."""
+        writer = self._make_writer()
+        for epoch in range(1, self.opt.num_epochs + 1):
+            self.losses.clear()
+            self.dis_outputs.clear()
+            self._train_epoch(train_loader, epoch)
+            if val_loader is not None:
+                self._val_epoch(val_loader)
+            if writer is not None:
+                self._write_tf_log(writer, epoch)
+            if epoch % self.opt.save_ckpt_freq == 0 and self.rank == 0:
+                self.model.save(epoch)
+        if writer is not None:
+            writer.close()
+
+    def _train_epoch(self, data_loader, epoch):
+        """wgan_trainer.py:86-107 (progress bar omitted): one critic step per batch, one generator step every ``num_critics``
+        iterations, the 'latest' checkpoint every ``save_latest_freq`` iterations, one scheduler step per epoch."""
+        for batch_data in data_loader:
+            self.iters += 1
+            batch_data = batch_data.to(self.opt.device, non_blocking=True)
+            self._train_discriminator_once(batch_data)
+            if self.iters % self.opt.num_critics == 0:
+                self._train_generator_once(batch_data.shape[0])
+            if self.iters % self.opt.save_latest_freq == 0 and self.rank == 0:
+                self.model.save("latest")
+        for sched in self.schedulers.values():
+            sched.step()
+
+    @torch.no_grad()
+    def _val_epoch(self, data_loader):
+        """wgan_trainer.py:109-113: critic outputs on validation images (the reference leaves netD in its current mode)."""
+        for batch_data in data_loader:
+            batch_data = batch_data.to(self.opt.device, non_blocking=True)
+            with Fn.weight_cache():
+                val_logits = self.model.netD(batch_data)
+            self.dis_outputs["val"] += val_logits.flatten().tolist()
+
+    def _make_writer(self):
+        if self.rank != 0 or getattr(self.opt, "log_dir", None) is None:
+            return None
+        try:
+            from torch.utils.tensorboard import SummaryWriter
+        except Exception:
+            return None
+        return SummaryWriter(self.opt.log_dir / self.opt.name)
+
+    def _write_tf_log(self, writer, epoch):
+        """wgan_trainer.py:54-67."""
+        for key, value in self.losses.items():
+            writer.add_scalar(f"Loss/{key}", sum(value) / len(value), epoch)
+        writer.add_scalars("D(x)", {k: sum(v) / len(v) for k, v in self.dis_outputs.items()}, epoch)
+        from torchvision.utils import make_grid
+        nrow = int(math.sqrt(self.opt.num_display_images))
+        writer.add_image("Generated Image", make_grid(self._generate_image(), nrow=nrow), epoch)
+
+    # ------------------------------------------------------------------------------------------------ the hot path
     def _train_generator_once(self, batch_size):
         """wgan_trainer.py:115-122.  ``batch_size`` may also be a noise tensor (netG accepts both, generator.py:41-47)."""
         d_params = list(self.model.netD.parameters())

@@ -33,6 +33,9 @@ const char* dei2i_last_error(void);
 int dei2i_set_tuning(const char* key, int value);
 /* number of kernels launched by this library since process start (bench.py's gpu_launches) */
 long long dei2i_launch_count(void);
+/* kernel variants enqueued by the calling thread's most recent dei2i_conv2d_{fwd,dgrad,wgrad} call, joined by '+'
+ * (e.g. "conv_tma<128,4,2>", "wgrad_tma<1,4>"): lets parity tests assert which variant a geometry exercised */
+const char* dei2i_last_kernel(void);
 
 /* Geometry of one nn.Conv2d call (architecture.py:51-56,95-100,228-233,320-337; normalization.py:17-22). */
 typedef struct dei2i_conv_geom {

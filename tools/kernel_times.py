@@ -15,7 +15,7 @@ from torch.profiler import ProfilerActivity, profile  # noqa: E402
 def main():
     from de_i2i_gan_b200 import options
     from de_i2i_gan_b200.trainers import find_trainer_using_model_name
-    from oracle import defectgan_ref as R
+    from de_i2i_gan_b200 import synthetic as R
     B, H = int(os.environ.get("B", 32)), int(os.environ.get("H", 256))
     torch.manual_seed(123)
     opt = options.readme_recipe(image_size=H, batch_size=B, num_critics=1, num_epochs=10, iters_per_epoch=10 ** 6, name="kt",

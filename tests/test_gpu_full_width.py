@@ -84,9 +84,18 @@ def _clear():
     A.set_noise_source(None)
 
 
-def _states(image_size, noise_weight=0.1):
+def _states(image_size, noise_weight=0.1, sn_warm=5):
+    """Random-init full-width states.  The random u / v of the spectral-norm buffers are advanced by a few power iterations
+    first: with un-iterated u, v sigma is underestimated by orders of magnitude, the six stacked discriminator layers then
+    produce logits of 1e10 and every comparison downstream is about an ill-conditioned graph rather than about the kernels."""
     from oracle import defectgan_ref as R
-    return R.random_generator_state(noise_weight=noise_weight), R.random_discriminator_state(image_size=image_size)
+    g, d = R.random_generator_state(noise_weight=noise_weight), R.random_discriminator_state(image_size=image_size)
+    for st in (g, d):
+        for k in list(st):
+            if k.endswith("weight_orig"):
+                for _ in range(sn_warm):
+                    R.spectral_weight(st, k[: -len("weight_orig")], True)
+    return g, d
 
 
 def _to(state, dev):

@@ -16,7 +16,7 @@ class ConvGeom(C.Structure):
 
 class ConvEpilogue(C.Structure):
     _fields_ = [("scale", C.c_void_p), ("bias", C.c_void_p), ("noise", C.c_void_p), ("noise_weight", C.c_void_p), ("residual", C.c_void_p),
-                ("act", C.c_int), ("out_fp32", C.c_int)]
+                ("act", C.c_int), ("out_fp32", C.c_int), ("stats_partial", C.c_void_p), ("out_pad", C.c_int)]
 
 
 class SnItem(C.Structure):  # dei2i_sn_item
@@ -35,6 +35,8 @@ SIGNATURES = {
     "dei2i_last_kernel": (C.c_char_p, []),
     "dei2i_pack_weight": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
     "dei2i_conv2d_fwd": (_I, [_P, _P, _P, C.POINTER(ConvGeom), C.POINTER(ConvEpilogue), _P]),
+    "dei2i_conv2d_fwd_path": (_I, [C.POINTER(ConvGeom)]),
+    "dei2i_reflect_border": (_I, [_P, _I, _I, _I, _I, _I, _P]),
     "dei2i_conv2d_dgrad": (_I, [_P, _P, _P, C.POINTER(ConvGeom), _P, _I, _P]),
     "dei2i_reflect_fold": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
     "dei2i_reflect_pad": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),

@@ -64,6 +64,7 @@ struct Epilogue {
   int out_fp32;
   int ld;     // output pitch (elements)
   int ncols;  // real columns that carry bias (Cout)
+  float* stats;  // optional [ceil(M / 128)][2][ld] per-tile (mean, M2) of the stored output (TMA kernels, bf16 output only)
 };
 
 

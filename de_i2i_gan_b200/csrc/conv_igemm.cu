@@ -633,12 +633,33 @@ static bool tma_applicable(const dei2i_conv_geom* g, int k_channels, long long M
 
 using namespace dei2i;
 
+// 1: the TMA-im2col tcgen05 kernel runs this forward geometry (the dispatch order of dei2i_conv2d_fwd)
+static int fwd_path(const dei2i_conv_geom* g, bool plain_epilogue) {
+  Gather gg;
+  memset(&gg, 0, sizeof(gg));
+  const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
+  gg.N = g->N; gg.Hl = g->H; gg.Wl = g->W; gg.Hs = g->Hs; gg.Ws = g->Ws; gg.C = g->Cin; gg.Ho = Ho; gg.Wo = Wo; gg.kh = g->kh;
+  gg.kw = g->kw; gg.stride = g->stride; gg.pad = g->pad; gg.pad_mode = g->pad_mode; gg.mode = 0; gg.cin8 = g->Cin / 8;
+  gg.ntaps = g->kh * g->kw; gg.M = (long long)g->N * Ho * Wo;
+  if (plain_epilogue && conv_narrow_fwd_applicable(gg, g->Cout_ld)) return 0;
+  if (conv_heads_fwd_applicable(gg, g->Cout_ld)) return 0;
+  return tma_applicable(g, g->Cin, gg.M) ? 1 : 0;
+}
+
+extern "C" int dei2i_conv2d_fwd_path(const dei2i_conv_geom* g) {
+  if (g == nullptr || check_geom(g)) return 0;
+  return fwd_path(g, false);
+}
+
 extern "C" int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const dei2i_conv_geom* g,
                                 const dei2i_conv_epilogue* e, dei2i_stream stream) {
   trace_begin();
   if (int rc = check_geom(g)) return rc;
   DEI2I_REQUIRE(x && w_fwd && y && e, "conv2d_fwd: null pointer");
   DEI2I_REQUIRE(e->noise == nullptr || e->noise_weight != nullptr, "conv2d_fwd: noise without noise_weight");
+  if (e->stats_partial != nullptr || e->out_pad > 0)
+    DEI2I_REQUIRE(fwd_path(g, false) == 1 && !e->out_fp32 && e->out_pad >= 0,
+                  "conv2d_fwd: stats_partial / out_pad need the TMA kernel (dei2i_conv2d_fwd_path) and a bf16 output");
   ConvKParams p;
   memset(&p, 0, sizeof(p));
   const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
@@ -650,7 +671,8 @@ extern "C" int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const
   p.e.scale = e->scale; p.e.bias = e->bias; p.e.noise = e->noise; p.e.noise_weight = e->noise_weight;
   p.e.residual = (const __nv_bfloat16*)e->residual; p.e.out = y; p.e.act = e->act; p.e.out_fp32 = e->out_fp32;
   p.e.ld = g->Cout_ld; p.e.ncols = g->Cout;
-  if (e->noise == nullptr && e->residual == nullptr && conv_narrow_fwd_applicable(p.g, g->Cout_ld))
+  if (e->noise == nullptr && e->residual == nullptr && e->stats_partial == nullptr && e->out_pad == 0 &&
+      conv_narrow_fwd_applicable(p.g, g->Cout_ld))
     return run_conv_narrow_fwd(p.g, p.e, w_fwd, g->Cout, round_up(g->kh * g->kw * g->Cin, 64), (cudaStream_t)stream);
   if (conv_heads_fwd_applicable(p.g, g->Cout_ld))
     return run_conv_heads_fwd(p.g, p.e, w_fwd, g->Cout, round_up(g->kh * g->kw * g->Cin, 64), (cudaStream_t)stream);
@@ -661,11 +683,18 @@ extern "C" int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const
     t.kh = g->kh; t.kw = g->kw; t.flip = 0; t.cin_blocks = g->Cin / 64; t.num_kb = g->kh * g->kw * t.cin_blocks;
     t.b_sub = 1; t.b_kw = g->kw;
     t.om.linear = 1;
+    if (e->out_pad > 0) {  // interior of the consumer-padded output; the frame is mirrored below
+      t.om.linear = 0; t.om.Ho = Ho; t.om.Wo = Wo; t.om.OH = Ho + 2 * e->out_pad; t.om.OW = Wo + 2 * e->out_pad;
+      t.om.osy = 1; t.om.osx = 1; t.om.oy0 = e->out_pad; t.om.ox0 = e->out_pad;
+    }
     t.e.scale = e->scale; t.e.bias = e->bias; t.e.noise = e->noise; t.e.noise_weight = e->noise_weight;
     t.e.residual = (const __nv_bfloat16*)e->residual; t.e.out = y; t.e.act = e->act; t.e.out_fp32 = e->out_fp32;
-    t.e.ld = g->Cout_ld; t.e.ncols = g->Cout;
-    return run_conv_tma(x, g->N, g->H, g->W, g->Cin, w_fwd, g->Cout, g->kh * g->kw * g->Cin, t, g->pad - (g->kh - 1),
-                        g->pad - (g->kw - 1), (cudaStream_t)stream);
+    t.e.ld = g->Cout_ld; t.e.ncols = g->Cout; t.e.stats = e->stats_partial;
+    if (int rc = run_conv_tma(x, g->N, g->H, g->W, g->Cin, w_fwd, g->Cout, g->kh * g->kw * g->Cin, t, g->pad - (g->kh - 1),
+                              g->pad - (g->kw - 1), (cudaStream_t)stream))
+      return rc;
+    if (e->out_pad > 0) return dei2i_reflect_border(y, g->N, Ho, Wo, g->Cout_ld, e->out_pad, stream);
+    return 0;
   }
   p.g.src = (const __nv_bfloat16*)x;
   p.g.N = g->N; p.g.Hl = g->H; p.g.Wl = g->W; p.g.Hs = g->Hs; p.g.Ws = g->Ws; p.g.C = g->Cin;

@@ -21,17 +21,30 @@ namespace dei2i {
 void count_launch(int n = 1);
 void trace_kernel(const char* fmt, ...);
 
-constexpr int kTmaThreads = 192;
+constexpr int kTmaThreads = 320;      // warps 0-7: two epilogue groups of 4, warp 8: TMA producer, warp 9: MMA issuer
+constexpr int kWgTmaThreads = 192;    // wgrad kernel: warps 0-3 epilogue, warp 4 TMA, warp 5 MMA
 constexpr int kTmaATile = 128 * 128;  // 128 pixels x 64 bf16
 
 template <int BLOCK_N, int STAGES, int MS>
 struct TmaSmem {
   static constexpr int kBTile = BLOCK_N * 128;
   static constexpr int kStage = MS * kTmaATile + kBTile;  // MS 128-pixel A tiles share one B tile
-  static constexpr int kStageOut = STAGES * kStage;     // 4 epilogue warps x 4 KB output staging
-  static constexpr int kBarOff = kStageOut + 4 * 4096;
+  static constexpr int kStageOut = STAGES * kStage;     // 8 epilogue warps x 2 KB output staging (32 rows x 64 B)
+  static constexpr int kBarOff = kStageOut + 8 * 2048;
   static constexpr int kTotal = kBarOff + (2 * STAGES + 4) * 8 + 16 + 1024 /*alignment slack*/;
 };
+
+DEVINL void named_bar_sync(int id, int nthreads) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory"); }
+
+// Chan et al. merge of two (count, mean, M2) summaries; fixed evaluation order
+DEVINL void chan_merge(float& n, float& mean, float& m2, float nb, float mb, float m2b) {
+  if (nb <= 0.f) return;
+  const float nt = n + nb;
+  const float d = mb - mean;
+  mean += d * (nb / nt);
+  m2 += m2b + d * d * (n * nb / nt);
+  n = nt;
+}
 
 template <int BLOCK_N, int STAGES, int MS>
 __global__ void __launch_bounds__(kTmaThreads, 1)
@@ -50,6 +63,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   constexpr uint32_t kTmemCols = 2 * MS * BLOCK_N < 32 ? 32 : 2 * MS * BLOCK_N;
   const int total_tiles = p.m_tiles * p.n_tiles;
   __shared__ __align__(16) float bias_s[1024];
+  __shared__ float2 wstat[2][2][4][32];  // [epilogue group][parity][row quarter][column]: (mean, M2) of 32 rows
   const bool bias_in_smem = p.e.bias != nullptr && p.n_tiles * BLOCK_N <= 1024;
   if (bias_in_smem)
     for (int i = threadIdx.x; i < p.n_tiles * BLOCK_N; i += kTmaThreads) bias_s[i] = i < p.e.ncols ? __ldg(p.e.bias + i) : 0.f;
@@ -65,17 +79,17 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     }
     fence_barrier_init();
   }
-  if (warp == 4 && lane == 0) {
+  if (warp == 8 && lane == 0) {
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
   }
-  if (warp == 5) tmem_alloc(tmem_ptr_smem, kTmemCols);
+  if (warp == 9) tmem_alloc(tmem_ptr_smem, kTmemCols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
-  if (warp == 4) {
+  if (warp == 8) {
     // =========================== TMA producer ===========================
     if (lane == 0) {
       const int HoWo = p.Ho * p.Wo;
@@ -94,7 +108,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           cw[ms] = qc * p.stride + p.lower_w;
           ch[ms] = pr * p.stride + p.lower;
         }
-        int tap = 0, cb = 0, r = 0, s = 0;
+        int cb = 0, r = 0, s = 0;
         for (int kb = 0; kb < p.num_kb; ++kb, ++it) {
           const uint32_t stage = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1u;
@@ -110,14 +124,12 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           tma_load_2d(a_dst + MS * kTmaATile, &tmap_b, &full_bar[stage], bcol, n_tile * BLOCK_N);
           if (++cb == p.cin_blocks) {
             cb = 0;
-            ++tap;
             if (++s == p.kw) { s = 0; ++r; }
           }
         }
-        (void)tap;
       }
     }
-  } else if (warp == 5) {
+  } else if (warp == 9) {
     // =========================== MMA issuer ===========================
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc_bf16(128, BLOCK_N, 0, 0);
@@ -147,150 +159,182 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       }
     }
   } else {
-    // =========================== epilogue (warps 0-3: TMEM lanes 32*warp ..) ===========================
+    // =========================== epilogue ===========================
+    // Two groups of four warps; group g drains accumulator buffer g, i.e. every other tile of this CTA, so each group has two
+    // main loops of time per tile and two warps per scheduler hide each other's TMEM / shared-memory latencies (with one group the
+    // N = 64 layers were bound by this loop: 32 % tensor-pipe activity, profiles/r02c_ncu_full_fwd64.txt).  Warp (g, q) owns TMEM
+    // lanes 32q .. 32q + 31 = rows 32q .. of the 128-row tile.
+    const int eg = warp >> 2, qw = warp & 3;
     const Epilogue& e = p.e;
     const OutMap& om = p.om;
     const float osc = e.scale != nullptr ? __ldg(e.scale) : 1.f;
     const float nzw = e.noise != nullptr ? __ldg(e.noise_weight) : 0.f;
     const float slope = e.act == ACT_LRELU ? 0.2f : (e.act == ACT_RELU ? 0.f : 1.f);
     const bool slow_act = e.act == ACT_TANH || e.act == ACT_SIGMOID;
-    uint32_t tcount = 0;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
-      const uint32_t buf = tcount & 1u;
-      const uint32_t bph = (tcount >> 1) & 1u;
+    // 64 bytes of output per row and pass: 32 bf16 columns or 16 fp32 columns.  Each lane finalises its own row, parks it in
+    // the warp's 2 KB staging tile (16-byte chunks XOR-swizzled by row pair: conflict-free both ways) and the warp then writes 8
+    // rows x 64 B per store instruction - coalesced whatever the row -> address map is.  The residual comes in the same way.
+    uint8_t* stage = smem + S::kStageOut + warp * 2048;
+    const int CW = e.out_fp32 ? 16 : 32;
+    const int esz = e.out_fp32 ? 4 : 2;
+    const int sub_r = lane >> 2, sub_j = lane & 3;
+    const int my_sw = (lane >> 1) & 3;  // swizzle of this lane's own row
+    uint32_t ti = 0, spar = 0;
+    for (int tile = blockIdx.x + eg * gridDim.x; tile < total_tiles; tile += 2 * gridDim.x, ++ti) {
       const int m_tile = tile / p.n_tiles;
       const int n0 = (tile - m_tile * p.n_tiles) * BLOCK_N;
-      mbar_wait(&tfull_bar[buf], bph);
+      mbar_wait(&tfull_bar[eg], ti & 1u);
       tc_fence_after();
 #pragma unroll 1
       for (int ms = 0; ms < MS; ++ms) {
-      const long long m_base = ((long long)m_tile * MS + ms) * 128;
-      if (m_base >= p.M) break;
-      const uint32_t tcol0 = buf * (MS * BLOCK_N) + ms * BLOCK_N;  // first TMEM column of this sub-tile's accumulator
-      const long long m = m_base + warp * 32 + lane;
-      const bool row_ok = m < p.M;
-      long long orow = m;  // output row index (in units of ld elements)
-      if (!om.linear && row_ok) {
-        const int HoWo = om.Ho * om.Wo;
-        const int img = (int)(m / HoWo);
-        const int rem = (int)(m - (long long)img * HoWo);
-        const int pr = rem / om.Wo;
-        const int qc = rem - pr * om.Wo;
-        orow = ((long long)img * om.OH + (pr * om.osy + om.oy0)) * om.OW + (qc * om.osx + om.ox0);
-      }
-      float nz = 0.f;
-      if (e.noise != nullptr && row_ok) nz = __ldg(e.noise + m) * nzw;
-      // 128 bytes of output per row and pass: 64 bf16 columns or 32 fp32 columns.  Each lane finalises its own row,
-      // parks it in the warp's 4 KB staging tile (16-byte chunks XOR-swizzled by row: conflict-free both ways) and the
-      // warp then writes 4 full 128-byte rows per store instruction (8 lanes x 16 B per row) - coalesced, whatever the
-      // row -> address map is.  The residual comes in through the same tile, transposed the other way.
-      uint8_t* stage = smem + S::kStageOut + warp * 4096;
-      const int CW = e.out_fp32 ? 32 : 64;  // columns per pass
-      const int sub_r = lane >> 3, sub_j = lane & 7;
-#pragma unroll 1
-      for (int c = 0; c < BLOCK_N; c += CW) {
-        const int nbase = n0 + c;
-        if (nbase >= e.ld) break;
-        float f[64];
-        {
-          uint32_t v[32];
-          tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + tcol0 + (uint32_t)c, v);
-          tc_wait_ld();
-#pragma unroll
-          for (int t = 0; t < 32; ++t) f[t] = __uint_as_float(v[t]) * osc;
-          if (CW == 64) {
-            tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + tcol0 + (uint32_t)(c + 32), v);
-            tc_wait_ld();
-#pragma unroll
-            for (int t = 0; t < 32; ++t) f[32 + t] = __uint_as_float(v[t]) * osc;
-          }
+        const long long m_base = ((long long)m_tile * MS + ms) * 128;
+        if (m_base >= p.M) break;
+        const uint32_t tcol0 = eg * (MS * BLOCK_N) + ms * BLOCK_N;  // first TMEM column of this sub-tile's accumulator
+        const long long m = m_base + qw * 32 + lane;
+        const bool row_ok = m < p.M;
+        long long orow = m;  // output row index (in units of ld elements)
+        if (!om.linear && row_ok) {
+          const int HoWo = om.Ho * om.Wo;
+          const int img = (int)(m / HoWo);
+          const int rem = (int)(m - (long long)img * HoWo);
+          const int pr = rem / om.Wo;
+          const int qc = rem - pr * om.Wo;
+          orow = ((long long)img * om.OH + (pr * om.osy + om.oy0)) * om.OW + (qc * om.osx + om.ox0);
         }
-        if (bias_in_smem) {  // zero-padded copy of the bias vector: no bounds logic, broadcast LDS.128
+        float nz = 0.f;
+        if (e.noise != nullptr && row_ok) nz = __ldg(e.noise + m) * nzw;
+#pragma unroll 1
+        for (int c = 0; c < BLOCK_N; c += CW) {
+          const int nbase = n0 + c;
+          if (nbase >= e.ld) break;
+          float f[32];
+          {
+            const uint32_t taddr = tmem_base + ((uint32_t)(qw * 32) << 16) + tcol0 + (uint32_t)c;
+            if (CW == 32) {
+              uint32_t v[32];
+              tmem_ld_32x32b_x32(taddr, v);
+              tc_wait_ld();
 #pragma unroll
-          for (int t4 = 0; t4 < 64; t4 += 4) {
-            if (t4 < CW) {
-              const float4 bv = *reinterpret_cast<const float4*>(bias_s + nbase + t4);
-              f[t4] += bv.x; f[t4 + 1] += bv.y; f[t4 + 2] += bv.z; f[t4 + 3] += bv.w;
+              for (int t = 0; t < 32; ++t) f[t] = __uint_as_float(v[t]) * osc;
+            } else {
+              uint32_t v[16];
+              tmem_ld_32x32b_x16(taddr, v);
+              tc_wait_ld();
+#pragma unroll
+              for (int t = 0; t < 16; ++t) f[t] = __uint_as_float(v[t]) * osc;
+#pragma unroll
+              for (int t = 16; t < 32; ++t) f[t] = 0.f;
             }
           }
-        } else if (e.bias != nullptr) {
+          if (bias_in_smem) {  // zero-padded copy of the bias vector: no bounds logic, broadcast LDS.128
 #pragma unroll
-          for (int t4 = 0; t4 < 64; t4 += 4) {
-            if (t4 < CW && nbase + t4 < e.ncols) {  // ncols (= Cout) may end inside a group of 4 only when Cout % 4 != 0
-              if (nbase + t4 + 3 < e.ncols) {
-                const float4 bv = __ldg(reinterpret_cast<const float4*>(e.bias + nbase + t4));
+            for (int t4 = 0; t4 < 32; t4 += 4) {
+              if (t4 < CW) {
+                const float4 bv = *reinterpret_cast<const float4*>(bias_s + nbase + t4);
                 f[t4] += bv.x; f[t4 + 1] += bv.y; f[t4 + 2] += bv.z; f[t4 + 3] += bv.w;
-              } else {
-                for (int k = 0; k < 4; ++k)
-                  if (nbase + t4 + k < e.ncols) f[t4 + k] += __ldg(e.bias + nbase + t4 + k);
               }
             }
+          } else if (e.bias != nullptr) {
+#pragma unroll
+            for (int t = 0; t < 32; ++t)
+              if (t < CW && nbase + t < e.ncols) f[t] += __ldg(e.bias + nbase + t);
           }
-        }
-        if (slow_act) {  // tanh / sigmoid: rare on this kernel (the heads go through the compose kernel)
+          if (slow_act) {  // tanh / sigmoid: rare on this kernel (the heads go through the compose kernel)
 #pragma unroll
-          for (int t = 0; t < 64; ++t)
-            if (t < CW) f[t] = apply_act(f[t] + nz, e.act);
-        } else if (e.noise != nullptr || e.act != ACT_NONE) {  // none / leaky-relu / relu = max(v, slope * v): branch-free, tiny code
+            for (int t = 0; t < 32; ++t)
+              if (t < CW) f[t] = apply_act(f[t] + nz, e.act);
+          } else if (e.noise != nullptr || e.act != ACT_NONE) {  // none / leaky-relu / relu = max(v, slope * v): branch-free
 #pragma unroll
-          for (int t = 0; t < 64; ++t)
-            if (t < CW) {
+            for (int t = 0; t < 32; ++t) {
               const float v = f[t] + nz;
               f[t] = fmaxf(v, v * slope);
             }
-        }
-        if (e.residual != nullptr) {  // bf16 [M, ld], linear rows; only with bf16 output (CW == 64)
+          }
+          if (e.residual != nullptr) {  // bf16 [M, ld], linear rows; only with bf16 output (CW == 32)
 #pragma unroll
-          for (int itr = 0; itr < 8; ++itr) {
-            const int r = itr * 4 + sub_r;
-            const long long mr = m_base + warp * 32 + r;
-            uint4 rv = make_uint4(0, 0, 0, 0);
-            if (mr < p.M && nbase + sub_j * 8 < e.ld) rv = __ldg(reinterpret_cast<const uint4*>(e.residual + mr * e.ld + nbase + sub_j * 8));
-            *reinterpret_cast<uint4*>(stage + r * 128 + ((sub_j ^ (r & 7)) << 4)) = rv;
+            for (int itr = 0; itr < 4; ++itr) {
+              const int r = itr * 8 + sub_r;
+              const long long mr = m_base + qw * 32 + r;
+              uint4 rv = make_uint4(0, 0, 0, 0);
+              if (mr < p.M && nbase + sub_j * 8 < e.ld) rv = __ldg(reinterpret_cast<const uint4*>(e.residual + mr * e.ld + nbase + sub_j * 8));
+              *reinterpret_cast<uint4*>(stage + r * 64 + ((sub_j ^ ((r >> 1) & 3)) << 4)) = rv;
+            }
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float rr[8];
+              unpack8_bf16(*reinterpret_cast<const uint4*>(stage + lane * 64 + ((j ^ my_sw) << 4)), rr);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) f[j * 8 + k] += rr[k];
+            }
+            __syncwarp();
+          }
+          if (e.out_fp32) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              *reinterpret_cast<float4*>(stage + lane * 64 + ((j ^ my_sw) << 4)) = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              *reinterpret_cast<uint4*>(stage + lane * 64 + ((j ^ my_sw) << 4)) =
+                  make_uint4(pack_bf16(f[8 * j], f[8 * j + 1]), pack_bf16(f[8 * j + 2], f[8 * j + 3]), pack_bf16(f[8 * j + 4], f[8 * j + 5]),
+                             pack_bf16(f[8 * j + 6], f[8 * j + 7]));
           }
           __syncwarp();
+          if (e.stats != nullptr) {
+            // per-channel (mean, M2) of this 128-row sub-tile over the STORED (BF16-rounded) values - what the consuming
+            // BatchNorm / InstanceNorm would otherwise re-read the tensor for.  Lane = column: two exact passes over the warp's
+            // 32 rows, then the four row quarters are merged in a fixed order (Chan) -> stats[tile128][2][ld]
+            const int cnt_w = (int)max(0ll, min(32ll, p.M - (m_base + qw * 32)));
+            const int cchunk = lane >> 3, coff = (lane & 7) * 2;
+            float v[32], sum = 0.f;
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            float rr[8];
-            unpack8_bf16(*reinterpret_cast<const uint4*>(stage + lane * 128 + ((j ^ (lane & 7)) << 4)), rr);
+            for (int r = 0; r < 32; ++r) {
+              const uint16_t h = *reinterpret_cast<const uint16_t*>(stage + r * 64 + ((cchunk ^ ((r >> 1) & 3)) << 4) + coff);
+              v[r] = __uint_as_float((uint32_t)h << 16);
+              if (r < cnt_w) sum += v[r];
+            }
+            const float mean_w = cnt_w > 0 ? sum / (float)cnt_w : 0.f;
+            float m2_w = 0.f;
 #pragma unroll
-            for (int k = 0; k < 8; ++k) f[j * 8 + k] += rr[k];
+            for (int r = 0; r < 32; ++r)
+              if (r < cnt_w) m2_w = fmaf(v[r] - mean_w, v[r] - mean_w, m2_w);
+            wstat[eg][spar][qw][lane] = make_float2(mean_w, m2_w);
+            named_bar_sync(1 + eg, 128);
+            if (qw == 0 && nbase + lane < e.ld) {
+              float nn = 0.f, mean = 0.f, m2 = 0.f;
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                const float cq = (float)max(0ll, min(32ll, p.M - (m_base + q * 32)));
+                const float2 t = wstat[eg][spar][q][lane];
+                chan_merge(nn, mean, m2, cq, t.x, t.y);
+              }
+              float* dst = e.stats + (size_t)(m_base >> 7) * 2 * e.ld + nbase + lane;
+              dst[0] = mean;
+              dst[e.ld] = m2;
+            }
+            spar ^= 1u;
+          }
+          const int col = nbase + sub_j * (16 / esz);  // first column of this lane's 16-byte chunk
+#pragma unroll
+          for (int itr = 0; itr < 4; ++itr) {
+            const int r = itr * 8 + sub_r;
+            const long long orow_r = __shfl_sync(0xffffffffu, orow, r);
+            const int ok_r = __shfl_sync(0xffffffffu, (int)row_ok, r);
+            const uint4 val = *reinterpret_cast<const uint4*>(stage + r * 64 + ((sub_j ^ ((r >> 1) & 3)) << 4));
+            if (ok_r && col < e.ld)
+              *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(e.out) + (orow_r * e.ld + col) * esz) = val;
           }
           __syncwarp();
         }
-        if (e.out_fp32) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<float4*>(stage + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_float4(f[4 * j], f[4 * j + 1], f[4 * j + 2], f[4 * j + 3]);
-        } else {
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            *reinterpret_cast<uint4*>(stage + lane * 128 + ((j ^ (lane & 7)) << 4)) =
-                make_uint4(pack_bf16(f[8 * j], f[8 * j + 1]), pack_bf16(f[8 * j + 2], f[8 * j + 3]), pack_bf16(f[8 * j + 4], f[8 * j + 5]),
-                           pack_bf16(f[8 * j + 6], f[8 * j + 7]));
-        }
-        __syncwarp();
-        const int esz = e.out_fp32 ? 4 : 2;
-        const int col = nbase + sub_j * (16 / esz);  // first column of this lane's 16-byte chunk
-#pragma unroll
-        for (int itr = 0; itr < 8; ++itr) {
-          const int r = itr * 4 + sub_r;
-          const long long orow_r = __shfl_sync(0xffffffffu, orow, r);
-          const int ok_r = __shfl_sync(0xffffffffu, (int)row_ok, r);
-          const uint4 val = *reinterpret_cast<const uint4*>(stage + r * 128 + ((sub_j ^ (r & 7)) << 4));
-          if (ok_r && col < e.ld)
-            *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(e.out) + (orow_r * e.ld + col) * esz) = val;
-        }
-        __syncwarp();
-      }
       }  // ms
       tc_fence_before();
-      mbar_arrive(&tempty_bar[buf]);
+      mbar_arrive(&tempty_bar[eg]);
     }
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 5) {
+  if (warp == 9) {
     tc_fence_after();
     tmem_dealloc(tmem_base, kTmemCols);
   }
@@ -310,7 +354,7 @@ static int num_sms() {
 template <int BN, int ST, int MS>
 static int launch_tma(const CUtensorMap& ta, const CUtensorMap& tb, const TmaConvParams& p, cudaStream_t st) {
   using S = TmaSmem<BN, ST, MS>;
-  static_assert(S::kTotal + 4096 <= 227 * 1024, "shared memory budget (dynamic + the static bias copy)");
+  static_assert(S::kTotal + 4096 + 4096 <= 227 * 1024, "shared memory budget (dynamic + the static bias copy + the statistics scratch)");
   static_assert(S::kTotal > 114 * 1024, "one CTA per SM is required (the CTA owns up to all 512 TMEM columns)");
   static_assert(2 * MS * BN <= 512, "TMEM columns");
   static bool attr_done = false;
@@ -372,7 +416,7 @@ struct WgTmaSmem {
 };
 
 template <int CO_T, int STAGES>
-__global__ void __launch_bounds__(kTmaThreads, 1)
+__global__ void __launch_bounds__(kWgTmaThreads, 1)
 wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ CUtensorMap tmap_x, const TmaWgradParams p) {
   using S = WgTmaSmem<CO_T, STAGES>;
   extern __shared__ uint8_t smem_raw[];
@@ -521,7 +565,7 @@ static int launch_wgrad_tma(const CUtensorMap& tdy, const CUtensorMap& tx, const
     attr_done = true;
   }
   const int grid = p.co_groups * p.k_tiles * p.splits;
-  wgrad_tma_kernel<CO_T, ST><<<grid, kTmaThreads, S::kTotal, st>>>(tdy, tx, p);
+  wgrad_tma_kernel<CO_T, ST><<<grid, kWgTmaThreads, S::kTotal, st>>>(tdy, tx, p);
   count_launch();
   trace_kernel("wgrad_tma<%d,%d>", CO_T, ST);
   return check_cuda(cudaGetLastError(), "wgrad_tma_kernel launch");

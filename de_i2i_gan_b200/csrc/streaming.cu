@@ -149,6 +149,27 @@ __global__ void reflect_pad_kernel(const uint4* __restrict__ x, uint4* __restric
   for (int wp = lane; wp < Wp; wp += lanes) dst[wp * C8] = __ldg(src + reflect_idx(wp - pad, W) * C8);
 }
 
+// F.pad(mode='reflect') in place: y is [N, H+2p, W+2p, C] with its interior written (a convolution epilogue's OutMap); one block
+// per padded row fills that row's frame pixels from their mirror sources in the interior - O(perimeter) traffic instead of a
+// pass over the tensor.  Frame rows (hp < p or hp >= H + p): every pixel; interior rows: the 2p left / right pixels.
+__global__ void reflect_border_kernel(uint4* __restrict__ y, int N, int H, int W, int C8, int pad) {
+  const int Hp = H + 2 * pad, Wp = W + 2 * pad;
+  const int n = blockIdx.x / Hp, hp = blockIdx.x - n * Hp;
+  const int c8 = threadIdx.x % C8, lane = threadIdx.x / C8, lanes = blockDim.x / C8;
+  const int h = reflect_idx(hp - pad, H);
+  uint4* img = y + (long long)n * Hp * Wp * C8 + c8;
+  const uint4* src = img + (long long)(h + pad) * Wp * C8;
+  uint4* dst = img + (long long)hp * Wp * C8;
+  if (hp < pad || hp >= H + pad) {
+    for (int wp = lane; wp < Wp; wp += lanes) dst[wp * C8] = src[(reflect_idx(wp - pad, W) + pad) * C8];
+  } else {
+    for (int i = lane; i < 2 * pad; i += lanes) {
+      const int wp = i < pad ? i : W + i;  // i in [pad, 2 pad) -> W + pad + (i - pad)
+      dst[wp * C8] = src[(reflect_idx(wp - pad, W) + pad) * C8];
+    }
+  }
+}
+
 // ------------------------------------------------------------------------------------------ spectral norm
 // t_partial[rs, col] = sum_{row in chunk rs} W[row, col] * u[row]
 __global__ void sn_wt_u_kernel(const float* __restrict__ w, const float* __restrict__ u, int rows, int cols, int rows_per,
@@ -1593,6 +1614,13 @@ extern "C" int dei2i_reflect_pad(const void* x, void* xp, int N, int H, int W, i
   const int C8 = C / 8, lanes = 256 / C8 > 0 ? 256 / C8 : 1;
   reflect_pad_kernel<<<(unsigned)(N * (H + 2 * pad)), lanes * C8, 0, ST>>>((const uint4*)x, (uint4*)xp, N, H, W, C8, pad);
   return LAUNCH_OK("reflect_pad_kernel");
+}
+
+extern "C" int dei2i_reflect_border(void* y, int N, int H, int W, int C, int pad, dei2i_stream stream) {
+  DEI2I_REQUIRE(y && C % 8 == 0 && pad >= 1 && pad < H && pad < W && C <= 2048, "reflect_border: bad arguments");
+  const int C8 = C / 8, lanes = 256 / C8 > 0 ? 256 / C8 : 1;
+  reflect_border_kernel<<<(unsigned)(N * (H + 2 * pad)), lanes * C8, 0, ST>>>((uint4*)y, N, H, W, C8, pad);
+  return LAUNCH_OK("reflect_border_kernel");
 }
 
 extern "C" int dei2i_spectral_norm(const float* w, float* u, float* v, int rows, int cols, int do_power_iter, float eps,

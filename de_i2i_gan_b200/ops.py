@@ -160,7 +160,7 @@ def conv2d_fwd(x, w_fwd, spec: ConvSpec, bias=None, noise=None, noise_weight=Non
         _chk_f32(noise, "noise")
         assert noise.numel() == n * ho * wo
     g = spec.geom(n, h, w, hs, ws)
-    e = ConvEpilogue(_p(scale), _p(bias), _p(noise), _p(noise_weight), _p(residual), ACT[act], int(out_fp32))
+    e = ConvEpilogue(_p(scale), _p(bias), _p(noise), _p(noise_weight), _p(residual), ACT[act], int(out_fp32), None, 0)
     fl = alg_flops or spec.flops(n, ho, wo)
     with _Timed(_kind("fwd", spec, fl), fl, spec.tag(n, h, w)):
         check(_lib.load().dei2i_conv2d_fwd(_p(x), _p(w_fwd), _p(y), C.byref(g), C.byref(e), _stream()), "dei2i_conv2d_fwd")

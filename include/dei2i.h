@@ -59,6 +59,12 @@ typedef struct dei2i_conv_epilogue {
   const void* residual;      /* bf16 [N*Ho*Wo, Cout_ld] added last (NormResBlock, architecture.py:350) or NULL */
   int act;                   /* dei2i_act, applied after bias and noise (ConvBlock, architecture.py:106-107) */
   int out_fp32;              /* 0: y is bf16, 1: y is fp32 (same pitch) */
+  /* The two fields below need the TMA / tcgen05 kernel (dei2i_conv2d_fwd_path(g) == 1) and a bf16 output: */
+  float* stats_partial;      /* NULL, or fp32 [ceil(N*Ho*Wo / 128)][2][Cout_ld]: per 128-pixel tile the per-channel (mean, M2) of
+                                the stored output - the producer-side half of the BatchNorm / InstanceNorm statistics
+                                (generator.py:71,113,124; normalization.py:14), finished by dei2i_stats_finalize */
+  int out_pad;               /* > 0: y is [N, Ho+2p, Wo+2p, Cout_ld]; the convolution writes the interior and the same call mirrors
+                                the frame (the reflect padding of the NEXT convolution, architecture.py:95-100) */
 } dei2i_conv_epilogue;
 
 /* Packed K-major BF16 weight matrices consumed by the implicit-GEMM kernels.
@@ -72,6 +78,10 @@ int dei2i_pack_weight(const float* w, const float* inv_sigma, int Cout, int Cin_
 /* y = act(scale*conv(x) + bias + noise_weight*noise) + residual    (nn.Conv2d forward + fused followers) */
 int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const dei2i_conv_geom* g,
                      const dei2i_conv_epilogue* e, dei2i_stream stream);
+/* which forward kernel family dei2i_conv2d_fwd picks for g: 1 = TMA-im2col tcgen05 (supports stats_partial / out_pad), 0 = other */
+int dei2i_conv2d_fwd_path(const dei2i_conv_geom* g);
+/* mirrors the frame of an [N, H+2p, W+2p, C] bf16 tensor whose interior is written (F.pad(mode='reflect') in place) */
+int dei2i_reflect_border(void* y, int N, int H, int W, int C, int pad, dei2i_stream stream);
 
 /* Gradient w.r.t. the convolution input (autograd of nn.Conv2d: conv_transpose of dy with W).
  * dy: bf16 [N,Ho,Wo,Cout_ld].  pad_mode zeros:   dx is [N,H,W,Cin].

@@ -5,6 +5,7 @@ There is no fallback: if the shared object is missing (not built) the import of 
 import ctypes as C
 import os
 
+REDUCE_BLOCKS = 2048  # DEI2I_REDUCE_BLOCKS
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libdei2i.so")
 
@@ -55,27 +56,32 @@ SIGNATURES = {
     "dei2i_gap_fwd": (_I, [_P, _P, _I, _I, _I, _P]),
     "dei2i_gap_bwd": (_I, [_P, _P, _I, _I, _I, _P]),
     "dei2i_adain_act_fwd": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _F, _P]),
-    "dei2i_adain_act_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _P]),
+    "dei2i_adain_act_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _SZ, _I, _I, _I, _F, _P]),
     "dei2i_act_fwd": (_I, [_P, _P, _LL, _I, _P]),
     "dei2i_axpby": (_I, [_P, _P, _P, _LL, _F, _F, _P]),
     "dei2i_rowpack_fwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),
     "dei2i_rowpack_bwd": (_I, [_P, _P, _I, _I, _I, _I, _I, _I, _P]),
     "dei2i_nhwc_to_nchw": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
-    "dei2i_channel_stats": (_I, [_P, _I, _I, _I, _I, _P, _P]),
+    "dei2i_channel_stats_scratch": (_SZ, [_I, _I, _I, _I]),
+    "dei2i_channel_stats": (_I, [_P, _I, _I, _I, _I, _P, _P, _SZ, _P]),
+    "dei2i_stats_finalize": (_I, [_P, _I, _I, _LL, _I, _I, _I, _P, _P]),
     "dei2i_bn_fwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _I, _P]),
     "dei2i_bn_fwd_pad": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _F, _F, _I, _I, _P]),
-    "dei2i_bn_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_bn_bwd_scratch": (_SZ, [_I, _I, _I]),
+    "dei2i_bn_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _SZ, _I, _I, _I, _I, _I, _I, _I, _P]),
     "dei2i_spade_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
-    "dei2i_spade_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _P]),
+    "dei2i_image_reduce_scratch": (_SZ, [_I, _I, _I]),
+    "dei2i_spade_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _SZ, _I, _I, _I, _I, _I, _I, _P]),
     "dei2i_spade_cls_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _I, _P]),
-    "dei2i_spade_cls_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P]),
-    "dei2i_act_bwd": (_I, [_P, _P, _P, _P, _LL, _I, _I, _P]),
-    "dei2i_noise_wgrad": (_I, [_P, _P, _P, _LL, _I, _I, _F, _P]),
+    "dei2i_spade_cls_bwd_scratch": (_SZ, [_I, _I, _I, _I, _I]),
+    "dei2i_spade_cls_bwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _SZ, _I, _I, _I, _I, _I, _I, _I, _P]),
+    "dei2i_act_bwd": (_I, [_P, _P, _P, _P, _P, _LL, _I, _I, _I, _I, _I, _P]),
+    "dei2i_noise_wgrad": (_I, [_P, _P, _P, _P, _LL, _I, _I, _F, _P]),
     "dei2i_compose_fwd": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "dei2i_compose_bwd": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "dei2i_bce_logits": (_I, [_P, _P, _F, _LL, _P, _P, _F, _P]),
-    "dei2i_l1": (_I, [_P, _P, _LL, _P, _P, _P, _F, _I, _P]),
-    "dei2i_mse": (_I, [_P, _P, _LL, _P, _P, _P, _F, _I, _P]),
+    "dei2i_l1": (_I, [_P, _P, _LL, _P, _P, _P, _F, _I, _P, _P]),
+    "dei2i_mse": (_I, [_P, _P, _LL, _P, _P, _P, _F, _I, _P, _P]),
     "dei2i_ce_soft": (_I, [_P, _P, _I, _I, _P, _P, _F, _P]),
     "dei2i_adam": (_I, [_P, _P, _P, _P, _LL, _F, _F, _F, _F, _I, _P]),
     "dei2i_adam_dev": (_I, [_P, _P, _P, _P, _LL, _P, _F, _F, _F, _P]),

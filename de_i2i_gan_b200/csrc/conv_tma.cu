@@ -376,6 +376,8 @@ int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, in
   TmaConvParams p = p_in;
   int bn = 256;
   while (bn > 64 && bn / 2 >= rows) bn /= 2;
+  // (Narrowing BLOCK_N to put more CTAs on the few-pixel / many-channel discriminator tail was measured and dropped: 1024 -> 2048
+  // at 4 x 4 went 101 -> 90 us but 512 -> 1024 at 8 x 8 went 50 -> 89 us - every extra N tile re-loads the same A tiles.)
   CUtensorMap ta, tb;
   if (int rc = encode_tmap_im2col_bf16(&ta, x, (uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N, p.lower_w, upper_w, p.lower, upper, (uint32_t)p.stride,
                                        64, 128))

@@ -69,6 +69,96 @@ __global__ void pack_dgrad_kernel(const float* __restrict__ w, const float* __re
 
 DEVINL int reflect_idx(int i, int n) { return i < 0 ? -i : (i >= n ? 2 * n - 2 - i : i); }
 
+// out / dout of a consumer-padded SPADE output ([N, H+2pad, W+2pad, C]): the activation at (h, w) sits at (h+pad, w+pad); its
+// gradient is the sum over every padded position that mirrors onto (h, w) (the adjoint of the reflect padding, <= 4 reads).
+DEVINL void fold_extras(const uint4* __restrict__ t, long long img_base, int h, int w, int H, int W, int pad, int C8, int c8,
+                        float (&f)[8]);
+DEVINL void load_folded(const uint4* __restrict__ t, long long img_base, int h, int w, int H, int W, int pad, int C8, int c8,
+                        float (&f)[8]) {
+  const int Wp = W + 2 * pad;
+  unpack8(__ldg(t + (img_base + (long long)(h + pad) * Wp + (w + pad)) * C8 + c8), f);
+  fold_extras(t, img_base, h, w, H, W, pad, C8, c8, f);
+}
+// adds the mirror images of (h, w) to f (which already holds the value at (h + pad, w + pad))
+DEVINL void fold_extras(const uint4* __restrict__ t, long long img_base, int h, int w, int H, int W, int pad, int C8, int c8,
+                        float (&f)[8]) {
+  const int Wp = W + 2 * pad;
+  // interior pixels (all but a 2*pad + 1 wide frame) have no mirror image
+  if (pad == 0 || (h > pad && h < H - 1 - pad && w > pad && w < W - 1 - pad)) return;
+  // mirror rows / columns of (h, w); -1: none.  (h in [1, pad] <-> pad - h;  h in [H-1-pad, H-2] <-> 2H - 2 - h + pad)
+  const int h2 = (h >= 1 && h <= pad) ? pad - h : ((h <= H - 2 && h >= H - 1 - pad) ? 2 * H - 2 - h + pad : -1);
+  const int w2 = (w >= 1 && w <= pad) ? pad - w : ((w <= W - 2 && w >= W - 1 - pad) ? 2 * W - 2 - w + pad : -1);
+  float g[8];
+  if (h2 >= 0) {
+    unpack8(__ldg(t + (img_base + (long long)h2 * Wp + (w + pad)) * C8 + c8), g);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] += g[k];
+  }
+  if (w2 >= 0) {
+    unpack8(__ldg(t + (img_base + (long long)(h + pad) * Wp + w2) * C8 + c8), g);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] += g[k];
+  }
+  if (h2 >= 0 && w2 >= 0) {
+    unpack8(__ldg(t + (img_base + (long long)h2 * Wp + w2) * C8 + c8), g);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) f[k] += g[k];
+  }
+}
+
+
+// Fixed-order finish of a block-partial reduction: out[v] = beta * out[v] + scale * sum_b part[b * V + v]  (b ascending per lane,
+// lanes combined in order).  grid ceil(V / 32), block 32 outputs x 32 lanes.  Replaces global float atomics (run-to-run different
+// sums) and the zero-fill memsets they needed.  out2 (optional) receives the same values (BatchNorm: red -> dbeta | dgamma).
+__global__ void __launch_bounds__(1024)
+partial_sum_kernel(const float* __restrict__ part, int nblk, int V, float* __restrict__ out, float* __restrict__ out2, float scale,
+                   float beta) {
+  __shared__ float sh[32][33];
+  const int vi = threadIdx.x & 31, ln = threadIdx.x >> 5;
+  const int v = blockIdx.x * 32 + vi;
+  part += (size_t)blockIdx.y * nblk * V;  // grid.y = group (image): its own nblk partial rows and V outputs
+  out += (size_t)blockIdx.y * V;
+  if (out2 != nullptr) out2 += (size_t)blockIdx.y * V;
+  float a = 0.f;
+  if (v < V)
+    for (int b = ln; b < nblk; b += 32) a += part[(size_t)b * V + v];
+  sh[ln][vi] = a;
+  __syncthreads();
+  if (ln == 0 && v < V) {
+    float t = 0.f;
+#pragma unroll
+    for (int l = 0; l < 32; ++l) t += sh[l][vi];
+    t *= scale;
+    if (beta != 0.f) t += beta * out[v];
+    out[v] = t;
+    if (out2 != nullptr) out2[v] = t;
+  }
+}
+static int launch_partial_sum(const float* part, int nblk, int V, float* out, float* out2, float scale, float beta, cudaStream_t st,
+                              int groups = 1) {
+  partial_sum_kernel<<<dim3((V + 31) / 32, groups), 1024, 0, st>>>(part, nblk, V, out, out2, scale, beta);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "partial_sum_kernel");
+}
+
+// incremental (image, row, column) walk of a pixel index that advances by a fixed step: no divisions in the loop
+struct PixWalk {
+  int n, h, w, dh, dw, H, W;
+  DEVINL void init(long long p, int step, int H_, int W_) {
+    H = H_; W = W_;
+    const long long row = p / W;
+    w = (int)(p - row * W);
+    n = (int)(row / H);
+    h = (int)(row - (long long)n * H);
+    dh = step / W; dw = step - dh * W;
+  }
+  DEVINL void next() {
+    w += dw; h += dh;
+    if (w >= W) { w -= W; ++h; }
+    while (h >= H) { h -= H; ++n; }
+  }
+};
+
 // ------------------------------------------------------------------------------------------ reflect padding
 // One block per output row; thread = (8-channel group c8, pixel lane): no index division per element (the flat-index versions
 // spent ~80 instructions per 16-byte element on it).
@@ -422,47 +512,111 @@ __global__ void rowpack_bwd_kernel(const uint4* __restrict__ dxp, float* __restr
 }
 
 // ------------------------------------------------------------------------------------------ channel statistics
-// grid (chunks, groups). block 256 threads = (C8 columns) x (256/C8 pixel lanes), needs C8 <= 256.
-__global__ void channel_stats_kernel(const uint4* __restrict__ x, long long pix_per_group, int C8, int chunk,
-                                     float* __restrict__ stats /*[groups,2,C]*/) {
-  extern __shared__ float sh[];  // [lanes][C8*8][2]
+// Deterministic and cancellation-free (torch uses Welford; sum(x^2)/n - mean^2 in FP32 loses the variance when |mean| >> std):
+//   stage 1  every block reduces its rows to a per-channel (mean, M2 = sum (x - mean)^2) pair - shifted sums inside the block
+//            (pivot = the chunk's first pixel), lanes combined in a fixed order through shared memory, NO atomics;
+//            the convolution epilogue (conv_tma.cu) can emit the same per-tile pairs for its own output instead;
+//   stage 2  stats_finalize_kernel merges the tiles of a group in a fixed order (Chan: M2 = sum M2_t + n_t (mean_t - mean)^2)
+//            and writes (mean, biased variance).
+// grid (chunks, groups). block = (C8 columns) x (lanes pixel lanes), needs C8 <= 256.  part: [groups * chunks][2][C]
+__global__ void channel_stats_partial_kernel(const uint4* __restrict__ x, long long pix_per_group, int C8, int chunk,
+                                             float* __restrict__ part) {
+  extern __shared__ float sh[];  // [lanes][2][C] (channel-transposed rows)
   const int c8 = threadIdx.x % C8;
   const int lane = threadIdx.x / C8;
   const int lanes = blockDim.x / C8;
+  const int C = C8 * 8;
   const long long g = blockIdx.y;
   const long long p0 = (long long)blockIdx.x * chunk;
   const long long p1 = min(pix_per_group, p0 + chunk);
-  float s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  if (lane < lanes) {
-    const uint4* base = x + g * pix_per_group * C8 + c8;
-    for (long long p = p0 + lane; p < p1; p += lanes) {
-      float f[8];
-      unpack8(__ldg(base + p * C8), f);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        s[k] += f[k];
-        q[k] += f[k] * f[k];
-      }
-    }
-  }
-  const int C = C8 * 8;
-  if (lane < lanes) {
+  const uint4* base = x + g * pix_per_group * C8 + c8;
+  float piv[8], s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  unpack8(__ldg(base + p0 * C8), piv);
+  for (long long p = p0 + lane; p < p1; p += lanes) {
+    float f[8];
+    unpack8(__ldg(base + p * C8), f);
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-      sh[(lane * C + c8 * 8 + k) * 2 + 0] = s[k];
-      sh[(lane * C + c8 * 8 + k) * 2 + 1] = q[k];
+      const float d = f[k] - piv[k];
+      s[k] += d;
+      q[k] = fmaf(d, d, q[k]);
     }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    sh[(lane * 2 + 0) * C + k * C8 + c8] = s[k];
+    sh[(lane * 2 + 1) * C + k * C8 + c8] = q[k];
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+  const float n = (float)(p1 - p0);
+  float* dst = part + ((size_t)g * gridDim.x + blockIdx.x) * 2 * C;
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {  // i = k * C8 + c8 (transposed), channel c = c8 * 8 + k
     float a = 0.f, b = 0.f;
     for (int l = 0; l < lanes; ++l) {
-      a += sh[(l * C + c) * 2 + 0];
-      b += sh[(l * C + c) * 2 + 1];
+      a += sh[(l * 2 + 0) * C + i];
+      b += sh[(l * 2 + 1) * C + i];
     }
-    atomicAdd(stats + (g * 2 + 0) * C + c, a);
-    atomicAdd(stats + (g * 2 + 1) * C + c, b);
+    const int k = i / C8, cc8 = i - k * C8, c = cc8 * 8 + k;
+    float pk[8];
+    unpack8(__ldg(x + g * pix_per_group * C8 + p0 * C8 + cc8), pk);
+    const float dm = a / n;
+    dst[c] = pk[k] + dm;
+    dst[C + c] = fmaxf(b - a * dm, 0.f);
   }
+}
+
+// Fixed-order merge of per-tile (mean, M2) pairs.  part: [groups * T][2][ld]; tile t of a group covers rows [t * R, min((t+1) * R,
+// rows)) of that group.  out: [groups][2][C] = (mean, biased variance).  grid (ceil(C / CH), groups), block CH x LN threads:
+// thread (ch, ln) walks tiles ln, ln + LN, ... (pass 1: weighted mean; pass 2: M2 about that mean), lanes combined in order.
+template <int CH, int LN>
+__global__ void __launch_bounds__(CH * LN)
+stats_finalize_kernel(const float* __restrict__ part, int T, int R, long long rows, int C, int ld, float* __restrict__ out) {
+  __shared__ float sh[LN][CH];
+  __shared__ float mean_s[CH];
+  const int ch = threadIdx.x % CH, ln = threadIdx.x / CH;
+  const int c = blockIdx.x * CH + ch;
+  const int g = blockIdx.y;
+  const bool ok = c < C;
+  const float* pg = part + (size_t)g * T * 2 * ld + c;
+  float acc = 0.f;
+  if (ok)
+    for (int t = ln; t < T; t += LN) {
+      const float cnt = (float)min((long long)R, rows - (long long)t * R);
+      acc = fmaf(cnt, pg[(size_t)t * 2 * ld], acc);
+    }
+  sh[ln][ch] = acc;
+  __syncthreads();
+  if (ln == 0) {
+    float a = 0.f;
+    for (int l = 0; l < LN; ++l) a += sh[l][ch];
+    mean_s[ch] = a / (float)rows;
+  }
+  __syncthreads();
+  const float mean = mean_s[ch];
+  acc = 0.f;
+  if (ok)
+    for (int t = ln; t < T; t += LN) {
+      const float cnt = (float)min((long long)R, rows - (long long)t * R);
+      const float d = pg[(size_t)t * 2 * ld] - mean;
+      acc += pg[(size_t)t * 2 * ld + ld] + cnt * d * d;
+    }
+  sh[ln][ch] = acc;
+  __syncthreads();
+  if (ln == 0 && ok) {
+    float a = 0.f;
+    for (int l = 0; l < LN; ++l) a += sh[l][ch];
+    out[((size_t)g * 2 + 0) * C + c] = mean;
+    out[((size_t)g * 2 + 1) * C + c] = a / (float)rows;
+  }
+}
+
+static int launch_stats_finalize(const float* part, int T, int R, long long rows, int groups, int C, int ld, float* out, cudaStream_t st) {
+  if (T >= 64)
+    stats_finalize_kernel<8, 128><<<dim3((C + 7) / 8, groups), 1024, 0, st>>>(part, T, R, rows, C, ld, out);
+  else
+    stats_finalize_kernel<32, 8><<<dim3((C + 31) / 32, groups), 256, 0, st>>>(part, T, R, rows, C, ld, out);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "stats_finalize_kernel");
 }
 
 static int launch_channel_reduce_cfg(int C, long long pix_per_group, int groups, int& threads, int& chunk, unsigned& chunks,
@@ -497,8 +651,8 @@ __global__ void bn_fwd_kernel(const uint4* __restrict__ x, uint4* __restrict__ y
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     float mean, var;
     if (training) {
-      mean = stats[c] / (float)npix;
-      var = fmaxf(stats[C + c] / (float)npix - mean * mean, 0.f);
+      mean = stats[c];
+      var = stats[C + c];
       if (blockIdx.x == 0) {
         running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
         const float unb = npix > 1 ? var * (float)npix / (float)(npix - 1) : var;
@@ -556,8 +710,8 @@ __global__ void bn_fwd_pad_kernel(const uint4* __restrict__ x, uint4* __restrict
     const int c = c8 * 8 + k;
     float mean, var;
     if (training) {
-      mean = stats[c] / (float)npix;
-      var = fmaxf(stats[C + c] / (float)npix - mean * mean, 0.f);
+      mean = stats[c];
+      var = stats[C + c];
       if (first) {
         running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
         const float unb = npix > 1 ? var * (float)npix / (float)(npix - 1) : var;
@@ -606,11 +760,15 @@ __global__ void bn_fwd_pad_kernel(const uint4* __restrict__ x, uint4* __restrict
   }
 }
 
-// pass 1 of the backward: per channel  sum(dz), sum(dz * xhat)   with dz = dy * act'(bn(x))
-__global__ void bn_bwd_reduce_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, const float* __restrict__ gamma,
-                                     const float* __restrict__ beta, const float* __restrict__ mean, const float* __restrict__ rstd,
-                                     long long npix, int C8, int chunk, int act, float* __restrict__ out /*[2,C]*/) {
-  extern __shared__ float sh[];
+// Backward of BatchNorm (+ fused activation).  `pad` > 0: dy is the gradient of the consumer-PADDED output ([N, H+2p, W+2p, C]) and
+// is folded while it is read (adjoint of the reflect padding the forward wrote), so no separate fold pass runs before this.
+// Thread = (8-channel group, pixel lane), per-channel constants in registers.
+// pass 1: per channel  sum(dz), sum(dz * xhat)  with dz = dy * act'(bn(x));  per-block partials [blk][2][C], no atomics.
+__global__ void __launch_bounds__(256, 2)
+bn_bwd_reduce_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, const float* __restrict__ mean, const float* __restrict__ rstd,
+                     long long npix, int H, int W, int C8, int chunk, int act, int pad, float* __restrict__ part) {
+  extern __shared__ float sh[];  // [lanes][2][C]
   const int c8 = threadIdx.x % C8;
   const int lane = threadIdx.x / C8;
   const int lanes = blockDim.x / C8;
@@ -618,80 +776,135 @@ __global__ void bn_bwd_reduce_kernel(const uint4* __restrict__ x, const uint4* _
   const long long p0 = (long long)blockIdx.x * chunk;
   const long long p1 = min(npix, p0 + chunk);
   float s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  float mu[8], rs[8], ga[8], be[8];
+  float rs[8], mb[8], za[8], zb[8];  // xhat = fma(x, rs, mb);  z = fma(x, za, zb)
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
-    mu[k] = mean[c8 * 8 + k];
-    rs[k] = rstd[c8 * 8 + k];
-    ga[k] = gamma[c8 * 8 + k];
-    be[k] = beta[c8 * 8 + k];
+    const int c = c8 * 8 + k;
+    rs[k] = rstd[c];
+    mb[k] = -mean[c] * rs[k];
+    za[k] = rs[k] * gamma[c];
+    zb[k] = beta[c] - mean[c] * za[k];
   }
-  for (long long p = p0 + lane; p < p1; p += lanes) {
-    float fx[8], fd[8];
-    unpack8(__ldg(x + p * C8 + c8), fx);
-    unpack8(__ldg(dy + p * C8 + c8), fd);
+  const float neg = act == ACT_LRELU ? 0.2f : 0.f;
+  const bool masked = act == ACT_LRELU || act == ACT_RELU;
+  PixWalk pw;
+  if (pad > 0) pw.init(p0 + lane, lanes, H, W);
+  const int Wp = W + 2 * pad;
+  const long long img_pix = (long long)(H + 2 * pad) * Wp;
+  constexpr int KB = 4;  // loads of KB pixels are in flight before the first is reduced
+  for (long long p = p0 + lane; p < p1; p += (long long)KB * lanes) {
+    uint4 vx[KB], vd[KB];
+    int hh[KB], ww[KB], nn[KB];
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const float xh = (fx[k] - mu[k]) * rs[k];
-      float dz = fd[k];
-      if (act == ACT_LRELU) dz *= (xh * ga[k] + be[k]) > 0.f ? 1.f : 0.2f;
-      else if (act == ACT_RELU) dz *= (xh * ga[k] + be[k]) > 0.f ? 1.f : 0.f;
-      s[k] += dz;
-      q[k] += dz * xh;
+    for (int j = 0; j < KB; ++j) {
+      const long long pj = p + (long long)j * lanes;
+      if (pj < p1) {
+        vx[j] = __ldg(x + pj * C8 + c8);
+        if (pad > 0) {
+          hh[j] = pw.h; ww[j] = pw.w; nn[j] = pw.n;
+          vd[j] = __ldg(dy + ((long long)pw.n * img_pix + (long long)(pw.h + pad) * Wp + (pw.w + pad)) * C8 + c8);
+          pw.next();
+        } else {
+          vd[j] = __ldg(dy + pj * C8 + c8);
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < KB; ++j) {
+      if (p + (long long)j * lanes >= p1) break;
+      float fx[8], fd[8];
+      unpack8(vx[j], fx);
+      unpack8(vd[j], fd);
+      if (pad > 0) fold_extras(dy, (long long)nn[j] * img_pix, hh[j], ww[j], H, W, pad, C8, c8, fd);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float dz = fd[k];
+        if (masked) dz *= fmaf(fx[k], za[k], zb[k]) > 0.f ? 1.f : neg;
+        s[k] += dz;
+        q[k] = fmaf(dz, fmaf(fx[k], rs[k], mb[k]), q[k]);
+      }
     }
   }
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
-    sh[(lane * C + c8 * 8 + k) * 2 + 0] = s[k];
-    sh[(lane * C + c8 * 8 + k) * 2 + 1] = q[k];
+    sh[(lane * 2 + 0) * C + k * C8 + c8] = s[k];
+    sh[(lane * 2 + 1) * C + k * C8 + c8] = q[k];
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+  float* dst = part + (size_t)blockIdx.x * 2 * C;
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
     float a = 0.f, b = 0.f;
     for (int l = 0; l < lanes; ++l) {
-      a += sh[(l * C + c) * 2 + 0];
-      b += sh[(l * C + c) * 2 + 1];
+      a += sh[(l * 2 + 0) * C + i];
+      b += sh[(l * 2 + 1) * C + i];
     }
-    atomicAdd(out + c, a);
-    atomicAdd(out + C + c, b);
+    const int k = i / C8, c = (i - k * C8) * 8 + k;
+    dst[c] = a;
+    dst[C + c] = b;
   }
 }
-__global__ void bn_bwd_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, uint4* __restrict__ dx,
-                                    const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
-                                    const float* __restrict__ rstd, const float* __restrict__ red /*[2,C]*/, float* __restrict__ dgamma,
-                                    float* __restrict__ dbeta, long long npix, int C8, int training, int act) {
-  extern __shared__ float sh[];  // mean, rstd, gamma, beta, k1 (=sum dz / n), k2 (= sum dz xhat / n)
-  const int C = C8 * 8;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    sh[SW(c)] = mean[c];
-    sh[C + SW(c)] = rstd[c];
-    sh[2 * C + SW(c)] = gamma[c];
-    sh[3 * C + SW(c)] = beta[c];
-    sh[4 * C + SW(c)] = training ? red[c] / (float)npix : 0.f;
-    sh[5 * C + SW(c)] = training ? red[C + c] / (float)npix : 0.f;
-    if (blockIdx.x == 0) {
-      dbeta[c] = red[c];
-      dgamma[c] = red[C + c];
-    }
-  }
-  __syncthreads();
-  const long long total = npix * C8;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int c0 = fast_mod(i, C8) * 8;
-    float fx[8], fd[8], o[8];
-    unpack8(__ldg(x + i), fx);
-    unpack8(__ldg(dy + i), fd);
+// pass 2: dx = gamma * rstd * (dz - sum(dz) / n - xhat * sum(dz xhat) / n)  =  A * dz + B * x + D  (three constants per channel)
+__global__ void __launch_bounds__(256, 2)
+bn_bwd_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, uint4* __restrict__ dx,
+                    const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
+                    const float* __restrict__ rstd, const float* __restrict__ red /*[2,C]*/, long long npix, int H, int W,
+                    int C8, int training, int act, int pad) {
+  const int c8 = threadIdx.x % C8;
+  const int lane = threadIdx.x / C8;
+  const int lanes = blockDim.x / C8;
+  float A[8], B[8], D[8], zb[8];  // z = fma(x, A, zb)
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const int c = c0 + k;
-      const float xh = (fx[k] - sh[SW(c)]) * sh[C + SW(c)];
-      float dz = fd[k];
-      const float z = xh * sh[2 * C + SW(c)] + sh[3 * C + SW(c)];
-      if (act == ACT_LRELU) dz *= z > 0.f ? 1.f : 0.2f;
-      else if (act == ACT_RELU) dz *= z > 0.f ? 1.f : 0.f;
-      o[k] = sh[2 * C + SW(c)] * sh[C + SW(c)] * (dz - sh[4 * C + SW(c)] - xh * sh[5 * C + SW(c)]);
+  for (int k = 0; k < 8; ++k) {
+    const int c = c8 * 8 + k;
+    const float r = rstd[c], m = mean[c], g = gamma[c];
+    const float k1 = training ? red[c] / (float)npix : 0.f, k2 = training ? red[C8 * 8 + c] / (float)npix : 0.f;
+    A[k] = g * r;
+    B[k] = -A[k] * k2 * r;
+    D[k] = -A[k] * k1 - B[k] * m;
+    zb[k] = beta[c] - m * A[k];
+  }
+  const float neg = act == ACT_LRELU ? 0.2f : 0.f;
+  const bool masked = act == ACT_LRELU || act == ACT_RELU;
+  const long long stride = (long long)gridDim.x * lanes;
+  long long p = (long long)blockIdx.x * lanes + lane;
+  PixWalk pw;
+  if (pad > 0) pw.init(p, (int)stride, H, W);
+  const int Wp = W + 2 * pad;
+  const long long img_pix = (long long)(H + 2 * pad) * Wp;
+  constexpr int KB = 4;
+  for (; p < npix; p += KB * stride) {
+    uint4 vx[KB], vd[KB];
+    int hh[KB], ww[KB], nn[KB];
+#pragma unroll
+    for (int j = 0; j < KB; ++j) {
+      const long long pj = p + j * stride;
+      if (pj < npix) {
+        vx[j] = __ldg(x + pj * C8 + c8);
+        if (pad > 0) {
+          hh[j] = pw.h; ww[j] = pw.w; nn[j] = pw.n;
+          vd[j] = __ldg(dy + ((long long)pw.n * img_pix + (long long)(pw.h + pad) * Wp + (pw.w + pad)) * C8 + c8);
+          pw.next();
+        } else {
+          vd[j] = __ldg(dy + pj * C8 + c8);
+        }
+      }
     }
-    dx[i] = pack8(o);
+#pragma unroll
+    for (int j = 0; j < KB; ++j) {
+      const long long pj = p + j * stride;
+      if (pj >= npix) break;
+      float fx[8], fd[8];
+      unpack8(vx[j], fx);
+      unpack8(vd[j], fd);
+      if (pad > 0) fold_extras(dy, (long long)nn[j] * img_pix, hh[j], ww[j], H, W, pad, C8, c8, fd);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        float dz = fd[k];
+        if (masked) dz *= fmaf(fx[k], A[k], zb[k]) > 0.f ? 1.f : neg;
+        fd[k] = fmaf(A[k], dz, fmaf(B[k], fx[k], D[k]));
+      }
+      dx[pj * C8 + c8] = pack8(fd);
+    }
   }
 }
 
@@ -706,8 +919,8 @@ __global__ void spade_fwd_kernel(const uint4* __restrict__ x, const uint4* __res
   const int Hx = H / up, Wx = W / up;
   const float cnt = (float)Hx * (float)Wx;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const float mean = stats[(n * 2 + 0) * C + c] / cnt;
-    const float var = fmaxf(stats[(n * 2 + 1) * C + c] / cnt - mean * mean, 0.f);
+    const float mean = stats[(n * 2 + 0) * C + c];
+    const float var = stats[(n * 2 + 1) * C + c];
     const float rstd = rsqrtf(var + eps);
     sh[SW(c)] = mean;
     sh[C + SW(c)] = rstd;
@@ -784,14 +997,15 @@ __global__ void spade_bwd1_kernel(const uint4* __restrict__ x, const uint4* __re
     sh[(lane * C + c8 * 8 + k) * 2 + 1] = q[k];
   }
   __syncthreads();
+  float* dst = red + ((size_t)n * gridDim.x + blockIdx.x) * 2 * C;  // per-block partial [2][C]; summed in order by partial_sum_kernel
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     float a = 0.f, b = 0.f;
     for (int l = 0; l < lanes; ++l) {
       a += sh[(l * C + c) * 2 + 0];
       b += sh[(l * C + c) * 2 + 1];
     }
-    atomicAdd(red + (n * 2 + 0) * C + c, a);
-    atomicAdd(red + (n * 2 + 1) * C + c, b);
+    dst[c] = a;
+    dst[C + c] = b;
   }
 }
 // backward pass 2: dx[n, hx, wx, c] = rstd * (sum_{up x up} dxhat - up^2 * (S1/HW) - xhat * up^2 * (S2/HW))
@@ -863,8 +1077,8 @@ __global__ void spade_cls_fwd_kernel(const uint4* __restrict__ x, const uint4* _
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
     const int c = c8 * 8 + k;
-    const float mean = stats[(n * 2 + 0) * C + c] / cnt;
-    const float var = fmaxf(stats[(n * 2 + 1) * C + c] / cnt - mean * mean, 0.f);
+    const float mean = stats[(n * 2 + 0) * C + c];
+    const float var = stats[(n * 2 + 1) * C + c];
     const float rstd = rsqrtf(var + eps);
     a[k] = rstd;
     b[k] = -mean * rstd;
@@ -915,194 +1129,217 @@ __global__ void spade_cls_fwd_kernel(const uint4* __restrict__ x, const uint4* _
   }
 }
 
-// out / dout of a consumer-padded SPADE output ([N, H+2pad, W+2pad, C]): the activation at (h, w) sits at (h+pad, w+pad); its
-// gradient is the sum over every padded position that mirrors onto (h, w) (the adjoint of the reflect padding, <= 4 reads).
-DEVINL void fold_extras(const uint4* __restrict__ t, long long img_base, int h, int w, int H, int W, int pad, int C8, int c8,
-                        float (&f)[8]);
-DEVINL void load_folded(const uint4* __restrict__ t, long long img_base, int h, int w, int H, int W, int pad, int C8, int c8,
-                        float (&f)[8]) {
-  const int Wp = W + 2 * pad;
-  unpack8(__ldg(t + (img_base + (long long)(h + pad) * Wp + (w + pad)) * C8 + c8), f);
-  fold_extras(t, img_base, h, w, H, W, pad, C8, c8, f);
-}
-// adds the mirror images of (h, w) to f (which already holds the value at (h + pad, w + pad))
-DEVINL void fold_extras(const uint4* __restrict__ t, long long img_base, int h, int w, int H, int W, int pad, int C8, int c8,
-                        float (&f)[8]) {
-  const int Wp = W + 2 * pad;
-  // interior pixels (all but a 2*pad + 1 wide frame) have no mirror image
-  if (pad == 0 || (h > pad && h < H - 1 - pad && w > pad && w < W - 1 - pad)) return;
-  // mirror rows / columns of (h, w); -1: none.  (h in [1, pad] <-> pad - h;  h in [H-1-pad, H-2] <-> 2H - 2 - h + pad)
-  const int h2 = (h >= 1 && h <= pad) ? pad - h : ((h <= H - 2 && h >= H - 1 - pad) ? 2 * H - 2 - h + pad : -1);
-  const int w2 = (w >= 1 && w <= pad) ? pad - w : ((w <= W - 2 && w >= W - 1 - pad) ? 2 * W - 2 - w + pad : -1);
-  float g[8];
-  if (h2 >= 0) {
-    unpack8(__ldg(t + (img_base + (long long)h2 * Wp + (w + pad)) * C8 + c8), g);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) f[k] += g[k];
-  }
-  if (w2 >= 0) {
-    unpack8(__ldg(t + (img_base + (long long)(h + pad) * Wp + w2) * C8 + c8), g);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) f[k] += g[k];
-  }
-  if (h2 >= 0 && w2 >= 0) {
-    unpack8(__ldg(t + (img_base + (long long)h2 * Wp + w2) * C8 + c8), g);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) f[k] += g[k];
-  }
-}
-
-// backward pass 1 over whole rows [r0, r1) of image n: g = dout * (out > 0);  per border class  dgamma5 += g * xhat,
-// dbeta5 += g  (fp32 [N,5,5,2C], atomics);  S1 = sum g(1+gamma), S2 = sum g(1+gamma) xhat  per (n,c) into `red`.
-// smem table: 25 classes x 2C + one row [S1 | S2]; a thread keeps the sums of its current class in registers.
+// Backward over the border-class map, deterministic (no atomics) and split by class:
+//   interior class (2,2) - every pixel outside the 2-wide frame, 97 % of a 256 x 256 map - goes through a branch-free kernel: one
+//     (1 + gamma, beta) pair in registers, no class bookkeeping, no fold (pad <= 1 only touches the frame), and with 2x up-sampling
+//     the four outputs of a source pixel share xhat AND the ReLU mask, so their gradients are summed first;
+//     per-band partials [N][bands][2][C], lanes combined in a fixed order;
+//   the 24 frame classes get one block each per image (spade_cls_bwd1_border_kernel) that owns its dgamma5 | dbeta5 entry;
+//   spade_cls_bwd1_finish_kernel sums the bands into class (2,2) and forms S1 = sum g (1 + gamma), S2 = sum g (1 + gamma) xhat
+//     per (n, c) from the 25 class sums.
+// (The first version kept a class table in shared memory behind atomics: 109 instructions per 16 bytes of gradient, issue-bound at
+// 28 % of HBM bandwidth, and run-to-run different sums - profiles/r02c_ncu_full_spade_bwd1.txt.)
 template <int UP>
-__global__ void __launch_bounds__(256, 2)
-spade_cls_bwd1_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ out,
-                      const uint4* __restrict__ dout, float* __restrict__ dgb5, const float* __restrict__ mean_rstd,
-                      float* __restrict__ red /*[N,2,C]*/, int H, int W, int C8, int rows, int relu, int pad) {
-  constexpr int up = UP;
-  extern __shared__ float tab[];  // [26][2C]
+__global__ void __launch_bounds__(256)
+spade_cls_bwd1_int_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ dout,
+                          const float* __restrict__ mean_rstd, float* __restrict__ part, int H, int W, int C8, int rows, int relu,
+                          int pad) {
+  extern __shared__ float sh[];  // [lanes][2][C]
   const int c8 = threadIdx.x % C8;
   const int lane = threadIdx.x / C8;
   const int lanes = blockDim.x / C8;
   const int C = C8 * 8;
   const int n = blockIdx.y;
-  const int Hx = H / up, Wx = W / up;
-  const int r0 = blockIdx.x * rows, r1 = min(H, r0 + rows);
-  for (int i = threadIdx.x; i < 26 * 2 * C; i += blockDim.x) tab[i] = 0.f;
-  __syncthreads();
-  float mu[8], rs[8], s[8] = {0, 0, 0, 0, 0, 0, 0, 0}, q[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  float ag[8] = {0, 0, 0, 0, 0, 0, 0, 0}, ab[8] = {0, 0, 0, 0, 0, 0, 0, 0}, fg[8], fb[8];  // fg = 1 + gamma, fb = beta
-  int cur = -1;
+  const int Hx = H / UP, Wx = W / UP;
+  constexpr int LO = 2 / UP;  // first interior source row / column
+  const int sr0 = LO + blockIdx.x * rows, sr1 = min(Hx - LO, sr0 + rows);
+  const int wi = Wx - 2 * LO;  // interior source columns
+  float rs[8], mu[8], fg[8], fb[8], ag[8] = {0, 0, 0, 0, 0, 0, 0, 0}, ab[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  unpack8(__ldg(gb5 + (n * 25 + 12) * (2 * C8) + c8), fg);
+  unpack8(__ldg(gb5 + (n * 25 + 12) * (2 * C8) + C8 + c8), fb);
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
     rs[k] = mean_rstd[(n * 2 + 1) * C + c8 * 8 + k];
     mu[k] = -mean_rstd[(n * 2 + 0) * C + c8 * 8 + k] * rs[k];  // xhat = fma(x, rs, mu): the forward's expression, bit for bit
+    fg[k] += 1.f;
   }
   const int Wp = W + 2 * pad;
-  const long long img = (long long)n * (H + 2 * pad) * Wp;
-  // the ReLU mask is recomputed from x (out = relu(fma(xhat, 1 + gamma, beta)) exactly as the forward evaluates it) instead
-  // of reading `out` back: one tensor pass less.
   const uint4* xn = x + (long long)n * Hx * Wx * C8 + c8;
-  const uint4* dn = dout + (img + (long long)pad * Wp + pad) * C8 + c8;
-  // one output pixel (h, w) with its gradient vd and the normalised source value xh: class bookkeeping + accumulation
-  auto reduce_pixel = [&](int h, int w, const uint4& vd, const float (&xh)[8]) {
-    const int cls = bcls(h, H) * 5 + bcls(w, W);
-    if (cls != cur) {
-      if (cur >= 0) {
+  const uint4* dn = dout + ((long long)n * (H + 2 * pad) * Wp + (long long)pad * Wp + pad) * C8 + c8;
+  constexpr int KB = UP == 2 ? 2 : 4;
+  constexpr int U2 = UP * UP;
+  int sh_ = sr0 + lane / wi, sw_ = LO + lane % wi;
+  const int dh = lanes / wi, dw = lanes - dh * wi;
+  while (sh_ < sr1) {
+    uint4 vx[KB], vd[KB][U2];
+    bool ok[KB];
 #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-          atomicAdd(&tab[cur * 2 * C + k * C8 + c8], ag[k]);
-          atomicAdd(&tab[cur * 2 * C + C + k * C8 + c8], ab[k]);
-          s[k] = fmaf(fg[k], ab[k], s[k]);  // S1, S2 are (1 + gamma)-weighted class sums: no per-pixel work for them
-          q[k] = fmaf(fg[k], ag[k], q[k]);
-          ag[k] = ab[k] = 0.f;
-        }
+    for (int j = 0; j < KB; ++j) {
+      ok[j] = sh_ < sr1;
+      if (ok[j]) {
+        vx[j] = __ldg(xn + (sh_ * Wx + sw_) * C8);
+#pragma unroll
+        for (int qd = 0; qd < U2; ++qd)
+          vd[j][qd] = __ldg(dn + ((UP * sh_ + qd / UP) * Wp + UP * sw_ + (qd % UP)) * C8);
       }
-      cur = cls;
-      unpack8(__ldg(gb5 + (n * 25 + cls) * (2 * C8) + c8), fg);
-      unpack8(__ldg(gb5 + (n * 25 + cls) * (2 * C8) + C8 + c8), fb);
-#pragma unroll
-      for (int k = 0; k < 8; ++k) fg[k] += 1.f;
+      sw_ += dw; sh_ += dh;
+      if (sw_ >= Wx - LO) { sw_ -= wi; ++sh_; }
     }
-    float fd[8];
-    unpack8(vd, fd);
-    fold_extras(dout, img, h, w, H, W, pad, C8, c8, fd);
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      const float g = (!relu || fmaf(xh[k], fg[k], fb[k]) > 0.f) ? fd[k] : 0.f;
-      ag[k] = fmaf(g, xh[k], ag[k]);
-      ab[k] += g;
-    }
-  };
-  if (UP == 2) {
-    // walk SOURCE pixels of the rows [r0/2, r1/2) (r0, r1 even): x is loaded and normalised once for its 2 x 2 output block,
-    // all five loads are issued before the first is used
-    int sh_ = (r0 >> 1) + lane / Wx, sw_ = lane % Wx;
-    const int sr1 = r1 >> 1;
-    while (sh_ < sr1) {
-      const uint4 vx = __ldg(xn + (sh_ * Wx + sw_) * C8);
-      uint4 vd[4];
+    for (int j = 0; j < KB; ++j) {
+      if (!ok[j]) break;
+      float xh[8], g[8];
+      unpack8(vx[j], xh);
+      unpack8(vd[j][0], g);
 #pragma unroll
-      for (int qd = 0; qd < 4; ++qd) vd[qd] = __ldg(dn + ((2 * sh_ + (qd >> 1)) * Wp + 2 * sw_ + (qd & 1)) * C8);
-      float xh[8];
-      unpack8(vx, xh);
+      for (int qd = 1; qd < U2; ++qd) {
+        float t[8];
+        unpack8(vd[j][qd], t);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) xh[k] = fmaf(xh[k], rs[k], mu[k]);
-#pragma unroll
-      for (int qd = 0; qd < 4; ++qd) reduce_pixel(2 * sh_ + (qd >> 1), 2 * sw_ + (qd & 1), vd[qd], xh);
-      sw_ += lanes;
-      while (sw_ >= Wx) {
-        sw_ -= Wx;
-        ++sh_;
-      }
-    }
-  } else {
-    // memory-level parallelism: the loads of kB pixels (2 x 16 B each) are issued before any of them is reduced
-    constexpr int kB = 4;
-    // pixel walk without divisions: (ph, pw) advances by `lanes` pixels per step
-    int ph = r0 + lane / W, pw = lane % W;
-    while (ph < r1) {
-      uint4 vx[kB], vd[kB];
-      int hh[kB], ww[kB];
-#pragma unroll
-      for (int j = 0; j < kB; ++j) {
-        hh[j] = ph; ww[j] = pw;
-        if (ph < r1) {
-          vx[j] = __ldg(xn + (ph * Wx + pw) * C8);
-          vd[j] = __ldg(dn + (ph * Wp + pw) * C8);
-        }
-        pw += lanes;
-        while (pw >= W) {
-          pw -= W;
-          ++ph;
-        }
+        for (int k = 0; k < 8; ++k) g[k] += t[k];
       }
 #pragma unroll
-      for (int j = 0; j < kB; ++j) {
-        if (hh[j] >= r1) break;
-        float xh[8];
-        unpack8(vx[j], xh);
-#pragma unroll
-        for (int k = 0; k < 8; ++k) xh[k] = fmaf(xh[k], rs[k], mu[k]);
-        reduce_pixel(hh[j], ww[j], vd[j], xh);
+      for (int k = 0; k < 8; ++k) {
+        xh[k] = fmaf(xh[k], rs[k], mu[k]);
+        const float gm = (!relu || fmaf(xh[k], fg[k], fb[k]) > 0.f) ? g[k] : 0.f;
+        ag[k] = fmaf(gm, xh[k], ag[k]);
+        ab[k] += gm;
       }
     }
   }
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
-    if (cur >= 0) {
-      atomicAdd(&tab[cur * 2 * C + k * C8 + c8], ag[k]);
-      atomicAdd(&tab[cur * 2 * C + C + k * C8 + c8], ab[k]);
-      s[k] = fmaf(fg[k], ab[k], s[k]);
-      q[k] = fmaf(fg[k], ag[k], q[k]);
-    }
-    atomicAdd(&tab[25 * 2 * C + k * C8 + c8], s[k]);
-    atomicAdd(&tab[25 * 2 * C + C + k * C8 + c8], q[k]);
+    sh[(lane * 2 + 0) * C + k * C8 + c8] = ag[k];
+    sh[(lane * 2 + 1) * C + k * C8 + c8] = ab[k];
   }
   __syncthreads();
-  const int rc0 = bcls(r0, H), rc1 = bcls(r1 - 1, H);
-  const int span = (rc1 - rc0 + 1) * 5 * 2 * C;
-  // rows of the table are stored channel-transposed (SW: element (c8, k) at k * C8 + c8) so that a warp's shared-memory atomics
-  // hit consecutive banks; un-swizzle on the way out
-  for (int i = threadIdx.x; i < span; i += blockDim.x) {
-    const int row = i / C, c = i - row * C;
-    atomicAdd(dgb5 + (size_t)n * 25 * 2 * C + rc0 * 5 * 2 * C + i, tab[rc0 * 5 * 2 * C + row * C + SW(c)]);
+  float* dst = part + ((size_t)n * gridDim.x + blockIdx.x) * 2 * C;
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    float a = 0.f, b2 = 0.f;
+    for (int l = 0; l < lanes; ++l) {
+      a += sh[(l * 2 + 0) * C + i];
+      b2 += sh[(l * 2 + 1) * C + i];
+    }
+    const int k = i / C8, c = (i - k * C8) * 8 + k;
+    dst[c] = a;       // dgamma5 contribution
+    dst[C + c] = b2;  // dbeta5 contribution
   }
-  for (int i = threadIdx.x; i < 2 * C; i += blockDim.x) {
-    const int row = i / C, c = i - row * C;
-    atomicAdd(red + (size_t)n * 2 * C + i, tab[25 * 2 * C + row * C + SW(c)]);
+}
+
+// one block per (frame class, image): the class's strip of output pixels (row 0 / 1 / H-2 / H-1 and / or column 0 / 1 / W-2 / W-1)
+__global__ void __launch_bounds__(256)
+spade_cls_bwd1_border_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ dout,
+                             const float* __restrict__ mean_rstd, float* __restrict__ dgb5, int H, int W, int C8, int up, int relu,
+                             int pad) {
+  extern __shared__ float sh[];  // [lanes][2][C]
+  const int c8 = threadIdx.x % C8;
+  const int lane = threadIdx.x / C8;
+  const int lanes = blockDim.x / C8;
+  const int C = C8 * 8;
+  const int n = blockIdx.y;
+  const int cls = blockIdx.x < 12 ? blockIdx.x : blockIdx.x + 1;
+  const int ch = cls / 5, cw = cls - ch * 5;
+  const int h0 = ch < 2 ? ch : (ch == 2 ? 2 : H - 5 + ch), h1 = ch == 2 ? H - 2 : h0 + 1;
+  const int w0 = cw < 2 ? cw : (cw == 2 ? 2 : W - 5 + cw), w1 = cw == 2 ? W - 2 : w0 + 1;
+  const int nw = w1 - w0, npx = (h1 - h0) * nw;
+  const int Hx = H / up, Wx = W / up;
+  float rs[8], mu[8], fg[8], fb[8], ag[8] = {0, 0, 0, 0, 0, 0, 0, 0}, ab[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  unpack8(__ldg(gb5 + (n * 25 + cls) * (2 * C8) + c8), fg);
+  unpack8(__ldg(gb5 + (n * 25 + cls) * (2 * C8) + C8 + c8), fb);
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    rs[k] = mean_rstd[(n * 2 + 1) * C + c8 * 8 + k];
+    mu[k] = -mean_rstd[(n * 2 + 0) * C + c8 * 8 + k] * rs[k];
+    fg[k] += 1.f;
+  }
+  const long long img = (long long)n * (H + 2 * pad) * (W + 2 * pad);
+  const uint4* xn = x + (long long)n * Hx * Wx * C8 + c8;
+  const int Wp = W + 2 * pad;
+  constexpr int KB = 4;  // the strip is short (<= max(H, W) pixels over `lanes` lanes): keep KB pixels in flight per lane
+  for (int i0 = lane; i0 < npx; i0 += KB * lanes) {
+    uint4 vx[KB], vd[KB];
+    int hh[KB], ww[KB];
+#pragma unroll
+    for (int j = 0; j < KB; ++j) {
+      const int i = i0 + j * lanes;
+      if (i < npx) {
+        const int r = i / nw;
+        hh[j] = h0 + r;
+        ww[j] = w0 + (i - r * nw);
+        vx[j] = __ldg(xn + ((hh[j] / up) * Wx + (ww[j] / up)) * C8);
+        vd[j] = __ldg(dout + (img + (long long)(hh[j] + pad) * Wp + (ww[j] + pad)) * C8 + c8);
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < KB; ++j) {
+      if (i0 + j * lanes >= npx) break;
+      float xh[8], fd[8];
+      unpack8(vx[j], xh);
+      unpack8(vd[j], fd);
+      fold_extras(dout, img, hh[j], ww[j], H, W, pad, C8, c8, fd);
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        xh[k] = fmaf(xh[k], rs[k], mu[k]);
+        const float gm = (!relu || fmaf(xh[k], fg[k], fb[k]) > 0.f) ? fd[k] : 0.f;
+        ag[k] = fmaf(gm, xh[k], ag[k]);
+        ab[k] += gm;
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    sh[(lane * 2 + 0) * C + k * C8 + c8] = ag[k];
+    sh[(lane * 2 + 1) * C + k * C8 + c8] = ab[k];
+  }
+  __syncthreads();
+  float* dst = dgb5 + ((size_t)n * 25 + cls) * 2 * C;
+  for (int i = threadIdx.x; i < C; i += blockDim.x) {
+    float a = 0.f, b2 = 0.f;
+    for (int l = 0; l < lanes; ++l) {
+      a += sh[(l * 2 + 0) * C + i];
+      b2 += sh[(l * 2 + 1) * C + i];
+    }
+    const int k = i / C8, c = (i - k * C8) * 8 + k;
+    dst[c] = a;
+    dst[C + c] = b2;
+  }
+}
+
+// class (2,2) = sum of the interior bands (fixed order);  red[n] = [S1 | S2] from the 25 class sums.  grid N, block 256.
+__global__ void __launch_bounds__(256)
+spade_cls_bwd1_finish_kernel(const float* __restrict__ part, int bands, const __nv_bfloat16* __restrict__ gb5, float* __restrict__ dgb5,
+                             float* __restrict__ red, int C) {
+  const int n = blockIdx.x;
+  float* d12 = dgb5 + ((size_t)n * 25 + 12) * 2 * C;
+  for (int t = threadIdx.x; t < 2 * C; t += blockDim.x) {
+    float a = 0.f;
+    for (int b = 0; b < bands; ++b) a += part[((size_t)n * bands + b) * 2 * C + t];
+    d12[t] = a;
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float s1 = 0.f, s2 = 0.f;
+    for (int cls = 0; cls < 25; ++cls) {
+      const float g1 = 1.f + __bfloat162float(gb5[((size_t)n * 25 + cls) * 2 * C + c]);
+      const float* d = dgb5 + ((size_t)n * 25 + cls) * 2 * C;
+      s1 = fmaf(g1, d[C + c], s1);
+      s2 = fmaf(g1, d[c], s2);
+    }
+    red[(size_t)n * 2 * C + c] = s1;
+    red[(size_t)n * 2 * C + C + c] = s2;
   }
 }
 
 // backward pass 2: dx[n,hx,wx,c] = rstd * (sum_{up x up} g (1 + gamma5) - up^2 S1/HW - xhat up^2 S2/HW),  g recomputed.
 // Same thread mapping as the forward: fixed 8-channel group per thread, incremental source-pixel index, constants in registers.
+// Source pixels whose outputs all lie in the interior class take the branch-free path (gradients summed, one mask).
 template <int UP, int KB>
 __global__ void __launch_bounds__(256, 2)
 spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5, const uint4* __restrict__ out,
                       const uint4* __restrict__ dout, uint4* __restrict__ dx, const float* __restrict__ mean_rstd,
                       const float* __restrict__ red, int H, int W, int C8, int relu, int pad) {
   constexpr int up = UP;
+  constexpr int LO = 2 / UP;
   const int C = C8 * 8;
   const int n = blockIdx.y;
   const int c8 = threadIdx.x % C8;
@@ -1113,6 +1350,9 @@ spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5
   const float uu = (float)(up * up);
   // dx = rstd * (acc - K1 - xhat * K2) with xhat = (x - mean) * rstd  ==  a * acc + c1 * x + c0   (three constants per channel)
   float a[8], c0[8], c1[8], b0[8];  // b0 = -mean * rstd: xhat = fma(x, a, b0) as in the forward (ReLU mask recomputed, no read of out)
+  float g12[8], b12[8];             // 1 + gamma, beta of the interior class
+  unpack8(__ldg(gb5 + (n * 25 + 12) * (2 * C8) + c8), g12);
+  unpack8(__ldg(gb5 + (n * 25 + 12) * (2 * C8) + C8 + c8), b12);
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
     const int c = c8 * 8 + k;
@@ -1122,6 +1362,7 @@ spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5
     b0[k] = -mean * rstd;
     c1[k] = -rstd * rstd * K2;
     c0[k] = -rstd * K1 - c1[k] * mean;
+    g12[k] += 1.f;
   }
   const int Wp = W + 2 * pad;
   const long long img = (long long)n * (H + 2 * pad) * Wp;
@@ -1165,26 +1406,40 @@ spade_cls_bwd2_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gb5
       unpack8(vx[j], f);
 #pragma unroll
       for (int k = 0; k < 8; ++k) xh[k] = fmaf(f[k], a[k], b0[k]);
+      if (hs[j] >= LO && hs[j] < Hx - LO && ws[j] >= LO && ws[j] < Wx - LO) {
+        float g[8];
+        unpack8(vd[j][0], g);
 #pragma unroll
-      for (int dy = 0; dy < UP; ++dy)
+        for (int qd = 1; qd < U2; ++qd) {
+          float t[8];
+          unpack8(vd[j][qd], t);
 #pragma unroll
-        for (int dxx = 0; dxx < UP; ++dxx) {
-          const int h = hs[j] * UP + dy, w = ws[j] * UP + dxx;
-          const int cls = bcls(h, H) * 5 + bcls(w, W);
-          if (cls != cur) {
-            cur = cls;
-            float t[8];
-            unpack8(__ldg(gbn + cls * 2 * C8), t);
-#pragma unroll
-            for (int k = 0; k < 8; ++k) g1[k] = 1.f + t[k];
-            unpack8(__ldg(gbn + cls * 2 * C8 + C8), be);
-          }
-          float fd[8];
-          unpack8(vd[j][dy * UP + dxx], fd);
-          fold_extras(dout, img, h, w, H, W, pad, C8, c8, fd);
-#pragma unroll
-          for (int k = 0; k < 8; ++k) acc[k] += ((!relu || fmaf(xh[k], g1[k], be[k]) > 0.f) ? fd[k] : 0.f) * g1[k];
+          for (int k = 0; k < 8; ++k) g[k] += t[k];
         }
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = (!relu || fmaf(xh[k], g12[k], b12[k]) > 0.f) ? g[k] * g12[k] : 0.f;
+      } else {
+#pragma unroll
+        for (int dy = 0; dy < UP; ++dy)
+#pragma unroll
+          for (int dxx = 0; dxx < UP; ++dxx) {
+            const int h = hs[j] * UP + dy, w = ws[j] * UP + dxx;
+            const int cls = bcls(h, H) * 5 + bcls(w, W);
+            if (cls != cur) {
+              cur = cls;
+              float t[8];
+              unpack8(__ldg(gbn + cls * 2 * C8), t);
+#pragma unroll
+              for (int k = 0; k < 8; ++k) g1[k] = 1.f + t[k];
+              unpack8(__ldg(gbn + cls * 2 * C8 + C8), be);
+            }
+            float fd[8];
+            unpack8(vd[j][dy * UP + dxx], fd);
+            fold_extras(dout, img, h, w, H, W, pad, C8, c8, fd);
+#pragma unroll
+            for (int k = 0; k < 8; ++k) acc[k] += ((!relu || fmaf(xh[k], g1[k], be[k]) > 0.f) ? fd[k] : 0.f) * g1[k];
+          }
+      }
 #pragma unroll
       for (int k = 0; k < 8; ++k) f[k] = fmaf(a[k], acc[k], fmaf(c1[k], f[k], c0[k]));
       o[(long long)(pix + j * stride) * C8] = pack8(f);
@@ -1203,8 +1458,8 @@ __global__ void adain_act_fwd_kernel(const uint4* __restrict__ x, uint4* __restr
   const int C = C8 * 8;
   const int n = blockIdx.y;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const float mean = stats[(n * 2 + 0) * C + c] / (float)HW;
-    const float var = fmaxf(stats[(n * 2 + 1) * C + c] / (float)HW - mean * mean, 0.f);
+    const float mean = stats[(n * 2 + 0) * C + c];
+    const float var = stats[(n * 2 + 1) * C + c];
     const float rstd = rsqrtf(var + eps);
     const float a = rstd * scale[n * C + c];
     sh[SW(c)] = a;
@@ -1264,14 +1519,15 @@ __global__ void adain_act_bwd1_kernel(const uint4* __restrict__ x, const uint4* 
     sh[(lane * C + c8 * 8 + k) * 2 + 1] = q[k];
   }
   __syncthreads();
+  float* dst = red + ((size_t)n * gridDim.x + blockIdx.x) * 2 * C;  // per-block partial [2][C]; summed in order by partial_sum_kernel
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     float a = 0.f, b = 0.f;
     for (int l = 0; l < lanes; ++l) {
       a += sh[(l * C + c) * 2 + 0];
       b += sh[(l * C + c) * 2 + 1];
     }
-    atomicAdd(red + (n * 2 + 0) * C + c, a);
-    atomicAdd(red + (n * 2 + 1) * C + c, b);
+    dst[c] = a;
+    dst[C + c] = b;
   }
 }
 // backward pass 2: dx = rstd * scale * (g - S_g / HW - xhat * S_gx / HW)
@@ -1332,8 +1588,10 @@ __global__ void axpby_kernel(const uint4* __restrict__ a, const uint4* __restric
 }
 
 // ------------------------------------------------------------------------------------------ activation backward (+ column sums)
-__global__ void act_bwd_kernel(const uint4* __restrict__ y, const uint4* __restrict__ dy, uint4* __restrict__ dx, float* __restrict__ colsum,
-                               long long M, int C8, int chunk, int act) {
+__global__ void act_bwd_kernel(const uint4* __restrict__ y, const uint4* __restrict__ dy, uint4* __restrict__ dx, float* __restrict__ part,
+                               long long M, int H, int W, int C8, int chunk, int act, int pad) {
+  // pad > 0: y and dy are consumer-padded [N, H+2p, W+2p, C] (the convolution epilogue wrote its output that way): y is read at the
+  // interior, dy folded on read (adjoint of the mirrored frame); dx is dense [N, H, W, C].  M = N * H * W dense pixels.
   extern __shared__ float sh[];
   const int c8 = threadIdx.x % C8;
   const int lane = threadIdx.x / C8;
@@ -1341,12 +1599,24 @@ __global__ void act_bwd_kernel(const uint4* __restrict__ y, const uint4* __restr
   const int C = C8 * 8;
   const long long p0 = (long long)blockIdx.x * chunk, p1 = min(M, p0 + chunk);
   float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  PixWalk pw;
+  if (pad > 0) pw.init(p0 + lane, lanes, H, W);
+  const int Wp = W + 2 * pad;
+  const long long img_pix = (long long)(H + 2 * pad) * Wp;
   for (long long p = p0 + lane; p < p1; p += lanes) {
     float fd[8];
-    unpack8(__ldg(dy + p * C8 + c8), fd);
+    long long yi = p;
+    if (pad > 0) {
+      const long long img = (long long)pw.n * img_pix;
+      load_folded(dy, img, pw.h, pw.w, H, W, pad, C8, c8, fd);
+      yi = img + (long long)(pw.h + pad) * Wp + (pw.w + pad);
+      pw.next();
+    } else {
+      unpack8(__ldg(dy + p * C8 + c8), fd);
+    }
     if (act != ACT_NONE) {
       float fy[8];
-      unpack8(__ldg(y + p * C8 + c8), fy);
+      unpack8(__ldg(y + yi * C8 + c8), fy);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         float d;
@@ -1363,14 +1633,14 @@ __global__ void act_bwd_kernel(const uint4* __restrict__ y, const uint4* __restr
     for (int k = 0; k < 8; ++k) s[k] += fd[k];
     if (dx != nullptr) dx[p * C8 + c8] = pack8(fd);
   }
-  if (colsum == nullptr) return;
+  if (part == nullptr) return;
 #pragma unroll
   for (int k = 0; k < 8; ++k) sh[lane * C + c8 * 8 + k] = s[k];
   __syncthreads();
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     float a = 0.f;
     for (int l = 0; l < lanes; ++l) a += sh[l * C + c];
-    atomicAdd(colsum + c, a);
+    part[(size_t)blockIdx.x * C + c] = a;
   }
 }
 
@@ -1392,9 +1662,8 @@ __global__ void noise_wgrad_kernel(const uint4* __restrict__ dy, const float* __
     acc += t * __ldg(noise + m);
   }
   const float tot = block_sum(acc, sh);
-  if (threadIdx.x == 0) atomicAdd(out, tot);
+  if (threadIdx.x == 0) out[blockIdx.x] = tot;  // per-block partial; finished in a fixed order by partial_sum_kernel
 }
-__global__ void scale_scalar_kernel(float* p, float beta) { p[0] *= beta; }
 
 // ------------------------------------------------------------------------------------------ heads + composition
 __global__ void compose_fwd_kernel(const float* __restrict__ hd, const float* __restrict__ x, float* __restrict__ out,
@@ -1474,7 +1743,7 @@ __global__ void l1_kernel(const float* __restrict__ a, const float* __restrict__
     if (gb) gb[i] = accumulate ? gb[i] - s : -s;
   }
   const float tot = block_sum(acc, sh);
-  if (threadIdx.x == 0) atomicAdd(loss, tot * invn);
+  if (threadIdx.x == 0) loss[blockIdx.x] = tot * invn;  // per-block partial (loss = scratch here)
 }
 
 
@@ -1491,7 +1760,7 @@ __global__ void mse_kernel(const float* __restrict__ a, const float* __restrict_
     if (gb) gb[i] = accumulate ? gb[i] - s : -s;
   }
   const float tot = block_sum(acc, sh);
-  if (threadIdx.x == 0) atomicAdd(loss, tot * invn);
+  if (threadIdx.x == 0) loss[blockIdx.x] = tot * invn;  // per-block partial (loss = scratch here)
 }
 // cross_entropy(logits, soft targets): mean_b( -sum_c t[b,c] * log_softmax(z[b])[c] ); one warp per row, one block
 __global__ void ce_soft_kernel(const float* __restrict__ z, const float* __restrict__ t, int B, int Cn, float* __restrict__ loss,
@@ -1714,19 +1983,40 @@ extern "C" int dei2i_rowpack_bwd(const void* dxp, float* dimg, int N, int C, int
   return LAUNCH_OK("rowpack_bwd_kernel");
 }
 
-extern "C" int dei2i_channel_stats(const void* x, int N, int HW, int C, int per_sample, float* stats, dei2i_stream stream) {
-  DEI2I_REQUIRE(x && stats, "channel_stats: null pointer");
+extern "C" size_t dei2i_channel_stats_scratch(int N, int HW, int C, int per_sample) {
+  const int groups = per_sample ? N : 1;
+  const long long ppg = per_sample ? (long long)HW : (long long)N * HW;
+  int threads, chunk;
+  unsigned chunks;
+  size_t shmem;
+  if (launch_channel_reduce_cfg(C, ppg, groups, threads, chunk, chunks, shmem)) return 0;
+  return (size_t)groups * chunks * 2 * C;
+}
+
+extern "C" int dei2i_channel_stats(const void* x, int N, int HW, int C, int per_sample, float* stats, float* scratch,
+                                   size_t scratch_floats, dei2i_stream stream) {
+  DEI2I_REQUIRE(x && stats && scratch, "channel_stats: null pointer");
   const int groups = per_sample ? N : 1;
   const long long ppg = per_sample ? (long long)HW : (long long)N * HW;
   int threads, chunk;
   unsigned chunks;
   size_t shmem;
   if (int rc = launch_channel_reduce_cfg(C, ppg, groups, threads, chunk, chunks, shmem)) return rc;
-  DEI2I_CUDA(cudaMemsetAsync(stats, 0, (size_t)groups * 2 * C * sizeof(float), ST));
+  DEI2I_REQUIRE(scratch_floats >= (size_t)groups * chunks * 2 * C, "channel_stats: scratch too small (dei2i_channel_stats_scratch)");
   if (shmem > 48 * 1024)
-    DEI2I_CUDA(cudaFuncSetAttribute(channel_stats_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
-  channel_stats_kernel<<<dim3(chunks, groups), threads, shmem, ST>>>((const uint4*)x, ppg, C / 8, chunk, stats);
-  return LAUNCH_OK("channel_stats_kernel");
+    DEI2I_CUDA(cudaFuncSetAttribute(channel_stats_partial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
+  channel_stats_partial_kernel<<<dim3(chunks, groups), threads, shmem, ST>>>((const uint4*)x, ppg, C / 8, chunk, scratch);
+  if (int rc = LAUNCH_OK("channel_stats_partial_kernel")) return rc;
+  return launch_stats_finalize(scratch, (int)chunks, chunk, ppg, groups, C, C, stats, ST);
+}
+
+extern "C" int dei2i_stats_finalize(const float* partial, int tiles_per_group, int rows_per_tile, long long rows_per_group, int groups,
+                                    int C, int ld, float* stats, dei2i_stream stream) {
+  DEI2I_REQUIRE(partial && stats && tiles_per_group >= 1 && rows_per_tile >= 1 && rows_per_group >= 1 && groups >= 1 && C >= 1 && ld >= C,
+                "stats_finalize: bad arguments");
+  DEI2I_REQUIRE((long long)tiles_per_group * rows_per_tile >= rows_per_group && (long long)(tiles_per_group - 1) * rows_per_tile < rows_per_group,
+                "stats_finalize: %d tiles of %d rows do not cover %lld rows", tiles_per_group, rows_per_tile, rows_per_group);
+  return launch_stats_finalize(partial, tiles_per_group, rows_per_tile, rows_per_group, groups, C, ld, stats, ST);
 }
 
 extern "C" int dei2i_bn_fwd(const void* x, void* y, const void* residual, const float* stats, const float* gamma, const float* beta,
@@ -1764,28 +2054,39 @@ extern "C" int dei2i_bn_fwd_pad(const void* x, void* y, const void* residual, co
   return LAUNCH_OK("bn_fwd_pad_kernel");
 }
 
+extern "C" size_t dei2i_bn_bwd_scratch(int N, int HW, int C) {
+  int threads, chunk;
+  unsigned chunks;
+  size_t shmem;
+  if (launch_channel_reduce_cfg(C, (long long)N * HW, 1, threads, chunk, chunks, shmem)) return 0;
+  return (size_t)(chunks + 1) * 2 * C;
+}
+
 extern "C" int dei2i_bn_bwd(const void* x, const void* dy, void* dx, const float* gamma, const float* beta, const float* save_mean,
-                            const float* save_rstd, float* dgamma, float* dbeta, float* scratch, int N, int HW, int C, int training,
-                            int act, dei2i_stream stream) {
-  DEI2I_REQUIRE(x && dy && dx && gamma && beta && save_mean && save_rstd && dgamma && dbeta && scratch && C % 8 == 0,
+                            const float* save_rstd, float* dgamma, float* dbeta, float* scratch, size_t scratch_floats, int N, int H,
+                            int W, int C, int training, int act, int dy_pad, dei2i_stream stream) {
+  DEI2I_REQUIRE(x && dy && dx && gamma && beta && save_mean && save_rstd && dgamma && dbeta && scratch && C % 8 == 0 && C <= 2048,
                 "bn_bwd: bad arguments");
-  const long long npix = (long long)N * HW;
+  DEI2I_REQUIRE(dy_pad >= 0 && 2 * dy_pad + 1 < H && 2 * dy_pad + 1 < W, "bn_bwd: dy_pad (%d) too large", dy_pad);
+  DEI2I_REQUIRE(dgamma == dbeta + C, "bn_bwd: dbeta | dgamma must be one [2, C] buffer (dbeta first)");
+  const long long npix = (long long)N * H * W;
   int threads, chunk;
   unsigned chunks;
   size_t shmem;
   if (int rc = launch_channel_reduce_cfg(C, npix, 1, threads, chunk, chunks, shmem)) return rc;
-  DEI2I_CUDA(cudaMemsetAsync(scratch, 0, (size_t)2 * C * sizeof(float), ST));
+  DEI2I_REQUIRE(scratch_floats >= (size_t)(chunks + 1) * 2 * C, "bn_bwd: scratch too small (dei2i_bn_bwd_scratch)");
   if (shmem > 48 * 1024)
     DEI2I_CUDA(cudaFuncSetAttribute(bn_bwd_reduce_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
-  bn_bwd_reduce_kernel<<<chunks, threads, shmem, ST>>>((const uint4*)x, (const uint4*)dy, gamma, beta, save_mean, save_rstd, npix,
-                                                       C / 8, chunk, act, scratch);
+  float* red = scratch + (size_t)chunks * 2 * C;
+  bn_bwd_reduce_kernel<<<chunks, threads, shmem, ST>>>((const uint4*)x, (const uint4*)dy, gamma, beta, save_mean, save_rstd, npix, H, W,
+                                                       C / 8, chunk, act, dy_pad, scratch);
   if (int rc = LAUNCH_OK("bn_bwd_reduce_kernel")) return rc;
-  const long long total = npix * (C / 8);
-  unsigned blocks = nblocks(total, 256 * 4);
-  if (blocks > 148 * 16) blocks = 148 * 16;
-  bn_bwd_apply_kernel<<<blocks, 256, 6 * C * sizeof(float), ST>>>((const uint4*)x, (const uint4*)dy, (uint4*)dx, gamma, beta,
-                                                                  save_mean, save_rstd, scratch, dgamma, dbeta, npix, C / 8, training,
-                                                                  act);
+  if (int rc = launch_partial_sum(scratch, (int)chunks, 2 * C, red, dbeta, 1.f, 0.f, ST)) return rc;  // red = [sum dz | sum dz xhat] = dbeta | dgamma
+  const int C8 = C / 8, lanes = 256 / C8 > 0 ? 256 / C8 : 1;
+  unsigned blocks = nblocks(npix, lanes * 4);
+  if (blocks > 148 * 4) blocks = 148 * 4;  // two resident blocks per SM, two waves
+  bn_bwd_apply_kernel<<<blocks, lanes * C8, 0, ST>>>((const uint4*)x, (const uint4*)dy, (uint4*)dx, gamma, beta, save_mean, save_rstd, red,
+                                                     npix, H, W, C8, training, act, dy_pad);
   return LAUNCH_OK("bn_bwd_apply_kernel");
 }
 
@@ -1801,26 +2102,37 @@ extern "C" int dei2i_spade_fwd(const void* x, const void* gb, void* out, const f
   return LAUNCH_OK("spade_fwd_kernel");
 }
 
+// scratch floats of the per-image reductions (dense SPADE / AdaIN backward): N * (chunks + 1) * 2C
+extern "C" size_t dei2i_image_reduce_scratch(int N, int HW, int C) {
+  int threads, chunk;
+  unsigned chunks;
+  size_t shmem;
+  if (launch_channel_reduce_cfg(C, (long long)HW, N, threads, chunk, chunks, shmem)) return 0;
+  return (size_t)N * (chunks + 1) * 2 * C;
+}
+
 extern "C" int dei2i_spade_bwd(const void* x, const void* gb, const void* out, const void* dout, void* dgb, void* dx,
-                               const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, int relu,
-                               dei2i_stream stream) {
+                               const float* mean_rstd, float* scratch, size_t scratch_floats, int N, int H, int W, int C, int up,
+                               int relu, dei2i_stream stream) {
   DEI2I_REQUIRE(x && gb && out && dout && dgb && dx && mean_rstd && scratch && C % 8 == 0 && up >= 1, "spade_bwd: bad arguments");
   int threads, chunk;
   unsigned chunks;
   size_t shmem;
   if (int rc = launch_channel_reduce_cfg(C, (long long)H * W, N, threads, chunk, chunks, shmem)) return rc;
-  DEI2I_CUDA(cudaMemsetAsync(scratch, 0, (size_t)N * 2 * C * sizeof(float), ST));
+  DEI2I_REQUIRE(scratch_floats >= (size_t)N * (chunks + 1) * 2 * C, "spade_bwd: scratch too small (dei2i_image_reduce_scratch)");
+  float* red = scratch + (size_t)N * chunks * 2 * C;
   if (shmem > 48 * 1024)
     DEI2I_CUDA(cudaFuncSetAttribute(spade_bwd1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
   spade_bwd1_kernel<<<dim3(chunks, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)gb, (const uint4*)out, (const uint4*)dout,
                                                              (uint4*)dgb, mean_rstd, scratch, H, W, C / 8, up, chunk, relu);
   if (int rc = LAUNCH_OK("spade_bwd1_kernel")) return rc;
+  if (int rc = launch_partial_sum(scratch, (int)chunks, 2 * C, red, nullptr, 1.f, 0.f, ST, N)) return rc;
   const long long per_img = (long long)(H / up) * (W / up) * (C / 8);
   unsigned bx = nblocks(per_img, 256 * 2);
   const unsigned cap = (148 * 16 + N - 1) / N;
   if (bx > cap) bx = cap;
   spade_bwd2_kernel<<<dim3(bx, N), 256, 4 * C * sizeof(float), ST>>>((const uint4*)x, (const uint4*)gb, (const uint4*)dgb, (uint4*)dx,
-                                                                     mean_rstd, scratch, H, W, C / 8, up);
+                                                                     mean_rstd, red, H, W, C / 8, up);
   return LAUNCH_OK("spade_bwd2_kernel");
 }
 
@@ -1840,48 +2152,64 @@ extern "C" int dei2i_spade_cls_fwd(const void* x, const void* gb5, void* out, co
   return LAUNCH_OK("spade_cls_fwd_kernel");
 }
 
+// interior bands of spade_cls_bwd1_int_kernel: about two blocks per SM over all images
+static void spade_cls_bands(int N, int H, int up, int& rows, int& bands) {
+  const int Hx = H / up, lo = 2 / up;
+  const int hi = Hx - 2 * lo > 0 ? Hx - 2 * lo : 0;  // interior source rows
+  const int want = (148 * 2 + N - 1) / N;
+  rows = (hi + want - 1) / want;
+  if (rows < 1) rows = 1;
+  bands = hi > 0 ? (hi + rows - 1) / rows : 0;
+}
+extern "C" size_t dei2i_spade_cls_bwd_scratch(int N, int H, int W, int C, int up) {
+  (void)W;
+  if (up < 1 || H % up != 0) return 0;
+  int rows, bands;
+  spade_cls_bands(N, H, up, rows, bands);
+  return (size_t)N * (bands + 1) * 2 * C;
+}
+
 extern "C" int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* out, const void* dout, float* dgb5, void* dx,
-                                   const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, int relu,
-                                   int out_pad, dei2i_stream stream) {
-  DEI2I_REQUIRE(out_pad >= 0 && 2 * out_pad + 1 < H && 2 * out_pad + 1 < W, "spade_cls_bwd: out_pad (%d) too large", out_pad);
-  DEI2I_REQUIRE(x && gb5 && dout && dgb5 && dx && mean_rstd && scratch && C % 8 == 0 && C <= 512 && up >= 1 && H >= 5 && W >= 5,
+                                   const float* mean_rstd, float* scratch, size_t scratch_floats, int N, int H, int W, int C, int up,
+                                   int relu, int out_pad, dei2i_stream stream) {
+  DEI2I_REQUIRE(out_pad >= 0 && out_pad <= 1, "spade_cls_bwd: out_pad (%d) must be 0 or 1 (3x3 consumers)", out_pad);
+  DEI2I_REQUIRE(x && gb5 && dout && dgb5 && dx && mean_rstd && scratch && C % 8 == 0 && C <= 512 && H >= 5 && W >= 5,
                 "spade_cls_bwd: bad arguments (needs H, W >= 5, C <= 512)");
+  DEI2I_REQUIRE((up == 1 || up == 2) && H % up == 0 && W % up == 0, "spade_cls_bwd: up must be 1 or 2 and divide H, W (got %d)", up);
+  DEI2I_REQUIRE((long long)(H + 2 * out_pad) * (W + 2 * out_pad) * (C / 8) < (1ll << 31), "spade_cls_bwd: image too large for 32-bit pixel offsets");
   const int C8 = C / 8;
   int lanes = 256 / C8;
   if (lanes < 1) lanes = 1;
   const int threads = lanes * C8;
-  // one wave at the kernel's 2 blocks per SM (__launch_bounds__), whole rows per block
-  const int want = (148 * 2) / N > 0 ? (148 * 2) / N : 1;
-  int rows = (H + want - 1) / want;
-  if (rows < 1) rows = 1;
-  if (up == 2) rows += rows & 1;  // the up == 2 kernel walks 2 x 2 output blocks: whole source rows per block
-  const unsigned gx = (unsigned)((H + rows - 1) / rows);
-  const size_t shmem = (size_t)26 * 2 * C * sizeof(float);
-  DEI2I_CUDA(cudaMemsetAsync(scratch, 0, (size_t)N * 2 * C * sizeof(float), ST));
-  DEI2I_CUDA(cudaMemsetAsync(dgb5, 0, (size_t)N * 25 * 2 * C * sizeof(float), ST));
-  DEI2I_REQUIRE(up == 1 || up == 2, "spade_cls_bwd: up must be 1 or 2 (got %d)", up);
-  DEI2I_REQUIRE((long long)(H + 2 * out_pad) * (W + 2 * out_pad) * C8 < (1ll << 31), "spade_cls_bwd: image too large for 32-bit pixel offsets");
-  if (shmem > 48 * 1024) {
-    DEI2I_CUDA(cudaFuncSetAttribute(spade_cls_bwd1_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
-    DEI2I_CUDA(cudaFuncSetAttribute(spade_cls_bwd1_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
+  int rows, bands;
+  spade_cls_bands(N, H, up, rows, bands);
+  DEI2I_REQUIRE(scratch_floats >= (size_t)N * (bands + 1) * 2 * C, "spade_cls_bwd: scratch too small (dei2i_spade_cls_bwd_scratch)");
+  float* red = scratch + (size_t)N * bands * 2 * C;
+  const size_t shmem = (size_t)lanes * 2 * C * sizeof(float);
+  if (bands > 0) {
+    if (up == 1)
+      spade_cls_bwd1_int_kernel<1><<<dim3(bands, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)dout, mean_rstd,
+                                                                          scratch, H, W, C8, rows, relu, out_pad);
+    else
+      spade_cls_bwd1_int_kernel<2><<<dim3(bands, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)dout, mean_rstd,
+                                                                          scratch, H, W, C8, rows, relu, out_pad);
+    if (int rc = LAUNCH_OK("spade_cls_bwd1_int_kernel")) return rc;
   }
-  if (up == 1)
-    spade_cls_bwd1_kernel<1><<<dim3(gx, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out, (const uint4*)dout,
-                                                                  dgb5, mean_rstd, scratch, H, W, C8, rows, relu, out_pad);
-  else
-    spade_cls_bwd1_kernel<2><<<dim3(gx, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out, (const uint4*)dout,
-                                                                  dgb5, mean_rstd, scratch, H, W, C8, rows, relu, out_pad);
-  if (int rc = LAUNCH_OK("spade_cls_bwd1_kernel")) return rc;
+  spade_cls_bwd1_border_kernel<<<dim3(24, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)dout, mean_rstd, dgb5,
+                                                                    H, W, C8, up, relu, out_pad);
+  if (int rc = LAUNCH_OK("spade_cls_bwd1_border_kernel")) return rc;
+  spade_cls_bwd1_finish_kernel<<<N, 256, 0, ST>>>(scratch, bands, (const __nv_bfloat16*)gb5, dgb5, red, C);
+  if (int rc = LAUNCH_OK("spade_cls_bwd1_finish_kernel")) return rc;
   const long long src_pix = (long long)(H / up) * (W / up);
   unsigned bx = nblocks(src_pix, lanes * 8);
   const unsigned cap = (148 * 16 + N - 1) / N;
   if (bx > cap) bx = cap;
   if (up == 1)
     spade_cls_bwd2_kernel<1, 4><<<dim3(bx, N), threads, 0, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out, (const uint4*)dout,
-                                                                 (uint4*)dx, mean_rstd, scratch, H, W, C8, relu, out_pad);
+                                                                 (uint4*)dx, mean_rstd, red, H, W, C8, relu, out_pad);
   else
     spade_cls_bwd2_kernel<2, 2><<<dim3(bx, N), threads, 0, ST>>>((const uint4*)x, (const uint4*)gb5, (const uint4*)out, (const uint4*)dout,
-                                                                 (uint4*)dx, mean_rstd, scratch, H, W, C8, relu, out_pad);
+                                                                 (uint4*)dx, mean_rstd, red, H, W, C8, relu, out_pad);
   return LAUNCH_OK("spade_cls_bwd2_kernel");
 }
 
@@ -1897,19 +2225,20 @@ extern "C" int dei2i_adain_act_fwd(const void* x, void* out, const float* stats,
   return LAUNCH_OK("adain_act_fwd_kernel");
 }
 extern "C" int dei2i_adain_act_bwd(const void* x, const void* out, const void* dout, void* dx, const float* scale,
-                                   const float* mean_rstd, float* dshift_dscale, int N, int HW, int C, float slope,
-                                   dei2i_stream stream) {
-  DEI2I_REQUIRE(x && out && dout && dx && scale && mean_rstd && dshift_dscale && C % 8 == 0, "adain_act_bwd: bad arguments");
+                                   const float* mean_rstd, float* dshift_dscale, float* scratch, size_t scratch_floats, int N, int HW,
+                                   int C, float slope, dei2i_stream stream) {
+  DEI2I_REQUIRE(x && out && dout && dx && scale && mean_rstd && dshift_dscale && scratch && C % 8 == 0, "adain_act_bwd: bad arguments");
   int threads, chunk;
   unsigned chunks;
   size_t shmem;
   if (int rc = launch_channel_reduce_cfg(C, (long long)HW, N, threads, chunk, chunks, shmem)) return rc;
-  DEI2I_CUDA(cudaMemsetAsync(dshift_dscale, 0, (size_t)N * 2 * C * sizeof(float), ST));
+  DEI2I_REQUIRE(scratch_floats >= (size_t)N * chunks * 2 * C, "adain_act_bwd: scratch too small (dei2i_image_reduce_scratch)");
   if (shmem > 48 * 1024)
     DEI2I_CUDA(cudaFuncSetAttribute(adain_act_bwd1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
   adain_act_bwd1_kernel<<<dim3(chunks, N), threads, shmem, ST>>>((const uint4*)x, (const uint4*)out, (const uint4*)dout, mean_rstd,
-                                                                 dshift_dscale, HW, C / 8, chunk, slope);
+                                                                 scratch, HW, C / 8, chunk, slope);
   if (int rc = LAUNCH_OK("adain_act_bwd1_kernel")) return rc;
+  if (int rc = launch_partial_sum(scratch, (int)chunks, 2 * C, dshift_dscale, nullptr, 1.f, 0.f, ST, N)) return rc;
   const long long per_img = (long long)HW * (C / 8);
   unsigned bx = nblocks(per_img, 256 * 2);
   const unsigned cap = (148 * 16 + N - 1) / N;
@@ -1933,30 +2262,33 @@ extern "C" int dei2i_axpby(const void* a, const void* b, void* out, long long n,
   return LAUNCH_OK("axpby_kernel");
 }
 
-extern "C" int dei2i_act_bwd(const void* y, const void* dy, void* dx, float* bias_grad, long long M, int C, int act,
-                             dei2i_stream stream) {
-  DEI2I_REQUIRE(dy && (y || act == DEI2I_ACT_NONE) && (dx || bias_grad), "act_bwd: bad arguments");
+extern "C" int dei2i_act_bwd(const void* y, const void* dy, void* dx, float* bias_grad, float* scratch, long long M, int C, int act,
+                             int H, int W, int pad, dei2i_stream stream) {
+  DEI2I_REQUIRE(dy && (y || act == DEI2I_ACT_NONE) && (dx || bias_grad) && (!bias_grad || scratch), "act_bwd: bad arguments");
+  DEI2I_REQUIRE(pad == 0 || (H > 2 * pad + 1 && W > 2 * pad + 1 && M % ((long long)H * W) == 0), "act_bwd: bad padded geometry");
   int threads, chunk;
   unsigned chunks;
   size_t shmem;
   if (int rc = launch_channel_reduce_cfg(C, M, 1, threads, chunk, chunks, shmem)) return rc;
+  DEI2I_REQUIRE(chunks <= DEI2I_REDUCE_BLOCKS, "act_bwd: internal: too many blocks");
   shmem /= 2;
-  if (bias_grad) DEI2I_CUDA(cudaMemsetAsync(bias_grad, 0, (size_t)C * sizeof(float), ST));
   if (shmem > 48 * 1024)
     DEI2I_CUDA(cudaFuncSetAttribute(act_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
-  act_bwd_kernel<<<chunks, threads, shmem, ST>>>((const uint4*)y, (const uint4*)dy, (uint4*)dx, bias_grad, M, C / 8, chunk, act);
-  return LAUNCH_OK("act_bwd_kernel");
+  act_bwd_kernel<<<chunks, threads, shmem, ST>>>((const uint4*)y, (const uint4*)dy, (uint4*)dx, bias_grad ? scratch : nullptr, M, H, W,
+                                                 C / 8, chunk, act, pad);
+  if (int rc = LAUNCH_OK("act_bwd_kernel")) return rc;
+  if (bias_grad) return launch_partial_sum(scratch, (int)chunks, C, bias_grad, nullptr, 1.f, 0.f, ST);
+  return 0;
 }
 
-extern "C" int dei2i_noise_wgrad(const void* dy, const float* noise, float* dw, long long M, int C, int C_real, float beta,
+extern "C" int dei2i_noise_wgrad(const void* dy, const float* noise, float* dw, float* scratch, long long M, int C, int C_real, float beta,
                                  dei2i_stream stream) {
-  DEI2I_REQUIRE(dy && noise && dw && C % 8 == 0, "noise_wgrad: bad arguments");
-  if (beta == 0.f) DEI2I_CUDA(cudaMemsetAsync(dw, 0, sizeof(float), ST));
-  else if (beta != 1.f) { scale_scalar_kernel<<<1, 1, 0, ST>>>(dw, beta); count_launch(); }
+  DEI2I_REQUIRE(dy && noise && dw && scratch && C % 8 == 0, "noise_wgrad: bad arguments");
   unsigned blocks = nblocks(M * (C / 8), 256 * 8);
   if (blocks > 148 * 8) blocks = 148 * 8;
-  noise_wgrad_kernel<<<blocks, 256, 0, ST>>>((const uint4*)dy, noise, M, C / 8, C_real, dw);
-  return LAUNCH_OK("noise_wgrad_kernel");
+  noise_wgrad_kernel<<<blocks, 256, 0, ST>>>((const uint4*)dy, noise, M, C / 8, C_real, scratch);
+  if (int rc = LAUNCH_OK("noise_wgrad_kernel")) return rc;
+  return launch_partial_sum(scratch, (int)blocks, 1, dw, nullptr, 1.f, beta, ST);
 }
 
 extern "C" int dei2i_compose_fwd(const float* hd, const float* x, float* out, float* prob, void* out_nhwc, int N, int H, int W,
@@ -1979,24 +2311,24 @@ extern "C" int dei2i_bce_logits(const float* logits, const float* targets, float
   return LAUNCH_OK("bce_logits_kernel");
 }
 extern "C" int dei2i_l1(const float* a, const float* b, long long n, float* loss, float* grad_a, float* grad_b, float grad_scale,
-                        int accumulate_grad, dei2i_stream stream) {
-  DEI2I_REQUIRE(a && loss && n > 0, "l1: bad arguments");
-  DEI2I_CUDA(cudaMemsetAsync(loss, 0, sizeof(float), ST));
+                        int accumulate_grad, float* scratch, dei2i_stream stream) {
+  DEI2I_REQUIRE(a && loss && scratch && n > 0, "l1: bad arguments");
   unsigned blocks = nblocks(n, 256 * 8);
   if (blocks > 148 * 4) blocks = 148 * 4;
-  l1_kernel<<<blocks, 256, 0, ST>>>(a, b, n, loss, grad_a, grad_b, grad_scale, accumulate_grad);
-  return LAUNCH_OK("l1_kernel");
+  l1_kernel<<<blocks, 256, 0, ST>>>(a, b, n, scratch, grad_a, grad_b, grad_scale, accumulate_grad);
+  if (int rc = LAUNCH_OK("l1_kernel")) return rc;
+  return launch_partial_sum(scratch, (int)blocks, 1, loss, nullptr, 1.f, 0.f, ST);
 }
 
 
 extern "C" int dei2i_mse(const float* a, const float* b, long long n, float* loss, float* grad_a, float* grad_b, float grad_scale,
-                         int accumulate_grad, dei2i_stream stream) {
-  DEI2I_REQUIRE(a && loss && n > 0, "mse: bad arguments");
-  DEI2I_CUDA(cudaMemsetAsync(loss, 0, sizeof(float), ST));
+                         int accumulate_grad, float* scratch, dei2i_stream stream) {
+  DEI2I_REQUIRE(a && loss && scratch && n > 0, "mse: bad arguments");
   unsigned blocks = nblocks(n, 256 * 8);
   if (blocks > 148 * 4) blocks = 148 * 4;
-  mse_kernel<<<blocks, 256, 0, ST>>>(a, b, n, loss, grad_a, grad_b, grad_scale, accumulate_grad);
-  return LAUNCH_OK("mse_kernel");
+  mse_kernel<<<blocks, 256, 0, ST>>>(a, b, n, scratch, grad_a, grad_b, grad_scale, accumulate_grad);
+  if (int rc = LAUNCH_OK("mse_kernel")) return rc;
+  return launch_partial_sum(scratch, (int)blocks, 1, loss, nullptr, 1.f, 0.f, ST);
 }
 extern "C" int dei2i_ce_soft(const float* logits, const float* targets, int B, int C, float* loss, float* grad, float grad_scale,
                              dei2i_stream stream) {

@@ -18,10 +18,11 @@ from .ops import ConvSpec
 
 class Nhwc:
     """BF16 NHWC activation carrier. ``t``: [N,H,W,C_ld] (C_ld % 8 == 0), ``c``: real channels."""
-    __slots__ = ("t", "c", "cls5", "pad", "key")
+    __slots__ = ("t", "c", "cls5", "pad", "key", "stats")
 
     def __init__(self, t: torch.Tensor, c: int):
         self.t, self.c, self.cls5 = t, c, None
+        self.stats = None  # ('batch' | 'sample', fp32 [groups,2,C_ld]) (mean, var) of ``t`` emitted by the producing convolution's epilogue
         self.key = None  # identity of the tensor a label map was made from (SPADE caches gamma|beta per label tensor)
         self.pad = 0  # pixels of reflect padding already present on every side of ``t`` (written by the producer for its consumer)
 
@@ -161,43 +162,64 @@ def from_nhwc(a: Nhwc) -> torch.Tensor:
     return _FromNhwc.apply(a.t, a.c)
 
 
+# Statistics out of the convolution epilogue (dei2i_conv_epilogue.stats_partial) for outputs of up to this many channels.  Measured on
+# the 256 x 256 / batch 32 step: 0 -> 81.73 ms, 128 -> 81.78 ms, 512 -> 82.31 ms per step - the epilogue work costs what the separate
+# statistics pass over the (mostly L2-resident) tensor saves, so the consumer computes them by default (dei2i_channel_stats).
+EPI_STATS_MAX_COUT = int(os.environ.get("DEI2I_EPI_STATS_MAX_COUT", "0"))
+
+
 class _Conv(Function):
-    """y = act(scale*conv(x) + bias + noise_w*noise) + residual   and its dgrad / wgrad / bias / noise-weight grads."""
+    """y = act(scale*conv(x) + bias + noise_w*noise) + residual   and its dgrad / wgrad / bias / noise-weight grads.
+    want_stats: the epilogue also emits the (mean, var) statistics its BatchNorm / InstanceNorm consumer needs (second, non-
+    differentiable output; None where the kernel cannot).  out_pad: y carries the reflect padding of the convolution that consumes
+    it (written by the same call); the gradient then arrives for the padded tensor and is folded in the backward - fused into
+    the activation backward where there is one."""
 
     @staticmethod
-    def forward(ctx, x, w_param, bias, noise_w, residual, wts: Weights, spec: ConvSpec, act, noise, out_fp32, logical_hw):
+    def forward(ctx, x, w_param, bias, noise_w, residual, wts: Weights, spec: ConvSpec, act, noise, out_fp32, logical_hw,
+                want_stats=None, out_pad=0):
         assert not (act and residual is not None), "activation mask cannot be recovered once a residual is added"
+        assert not (out_pad and residual is not None)
         # nn.Conv2d(padding_mode='reflect') = F.pad(reflect) + valid convolution (torch's own _conv_forward): the mirrored
         # border is materialised once (it is also what wgrad re-reads), the convolution itself then runs on the TMA path
         ctx.rpad = spec.pad if (spec.pad_mode == "reflect" and spec.pad > 0 and logical_hw is None) else 0
         if ctx.rpad:
             x = ops.reflect_pad(x, ctx.rpad)
             spec = spec.unpadded()
-        y = ops.conv2d_fwd(x, wts.w_fwd, spec, bias=bias, noise=noise, noise_weight=noise_w, residual=residual, act=act,
-                           out_fp32=out_fp32, logical_hw=logical_hw, scale=wts.scale)
-        ctx.wts, ctx.spec, ctx.act, ctx.noise, ctx.logical_hw = wts, spec, act, noise, logical_hw
+        res = ops.conv2d_fwd(x, wts.w_fwd, spec, bias=bias, noise=noise, noise_weight=noise_w, residual=residual, act=act,
+                             out_fp32=out_fp32, logical_hw=logical_hw, scale=wts.scale, want_stats=want_stats, out_pad=out_pad)
+        y, stats = res if want_stats is not None else (res, None)
+        ctx.wts, ctx.spec, ctx.act, ctx.noise, ctx.logical_hw, ctx.out_pad = wts, spec, act, noise, logical_hw, out_pad
         ctx.has = (bias is not None, noise_w is not None, residual is not None)
         ctx.save_for_backward(x, y if act else None)
-        return y
+        if want_stats is None:
+            return y
+        if stats is None:
+            stats = y.new_zeros(0, dtype=torch.float32)  # "not available": the consumer computes them itself
+        ctx.mark_non_differentiable(stats)
+        return y, stats
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, _dstats=None):
         x, y = ctx.saved_tensors
         wts, spec = ctx.wts, ctx.spec
         has_bias, has_noise, has_res = ctx.has
         if dy.dtype != torch.bfloat16:
             dy = dy.to(torch.bfloat16)
         dy = dy.contiguous()
-        d_res = dy if (has_res and ctx.needs_input_grad[4]) else None
         d_bias = None
         need_bias = has_bias and ctx.needs_input_grad[2]
+        pad = ctx.out_pad
         if ctx.act or need_bias:
             yb = y if (y is None or y.dtype == torch.bfloat16) else y.to(torch.bfloat16)
-            dz, d_bias = ops.act_bwd(yb, dy, ctx.act, want_dx=bool(ctx.act), want_bias_grad=need_bias)
-            if ctx.act:
+            dz, d_bias = ops.act_bwd(yb, dy, ctx.act, want_dx=bool(ctx.act) or pad > 0, want_bias_grad=need_bias, pad=pad)
+            if ctx.act or pad:
                 dy = dz
             if d_bias is not None:
                 d_bias = d_bias[: spec.cout]
+        elif pad:
+            dy = ops.reflect_fold(dy, pad)
+        d_res = dy if (has_res and ctx.needs_input_grad[4]) else None
         d_nw = None
         if has_noise and ctx.needs_input_grad[3]:
             d_nw = ops.noise_wgrad(dy, ctx.noise, torch.empty(1, device=dy.device), spec.cout).reshape(1, 1, 1, 1)
@@ -211,15 +233,34 @@ class _Conv(Function):
         if ctx.needs_input_grad[1]:
             dw = torch.empty(spec.cout, spec.cin, spec.kh, spec.kw_, dtype=torch.float32, device=dy.device)
             ops.conv2d_wgrad(x, dy, dw, spec, sn=wts.sn, logical_hw=ctx.logical_hw)
-        return dx, dw, d_bias, d_nw, d_res, None, None, None, None, None, None
+        return dx, dw, d_bias, d_nw, d_res, None, None, None, None, None, None, None, None
 
 
 def conv(x: Nhwc, conv_mod, spec: ConvSpec, training: bool, bias=None, act=None, noise=None, noise_w=None,
-         residual: Optional[Nhwc] = None, out_fp32=False, logical_hw=None, wts: Weights = None) -> Nhwc:
+         residual: Optional[Nhwc] = None, out_fp32=False, logical_hw=None, wts: Weights = None, want_stats=None, out_pad=0) -> Nhwc:
+    """want_stats ('batch' | 'sample'): ask the epilogue for the statistics of the output (carrier ``.stats``); out_pad: ask it to
+    write the consumer's reflect padding (carrier ``.pad``) - granted only where the TMA kernel runs the geometry."""
     wts = wts or prepare_conv(conv_mod, spec, training)
-    y = _Conv.apply(x.t, conv_param(conv_mod), bias, noise_w, residual.t if residual is not None else None, wts, spec, act,
-                    noise, out_fp32, logical_hw)
-    return Nhwc(y, spec.cout)
+    if want_stats is not None and spec.cout_ld > EPI_STATS_MAX_COUT:
+        want_stats = None
+    if out_pad:
+        n, h, w = x.t.shape[0], x.t.shape[1], x.t.shape[2]
+        if spec.pad_mode == "reflect" and spec.pad > 0:  # _Conv pads the input first and runs the 'valid' convolution
+            geo, h, w = spec.unpadded(), h + 2 * spec.pad, w + 2 * spec.pad
+        else:
+            geo = spec
+        if out_fp32 or logical_hw is not None or residual is not None or not ops.conv_fwd_is_tma(geo, n, h, w):
+            out_pad = 0
+    res = _Conv.apply(x.t, conv_param(conv_mod), bias, noise_w, residual.t if residual is not None else None, wts, spec, act,
+                      noise, out_fp32, logical_hw, want_stats, out_pad)
+    if want_stats is None:
+        out = Nhwc(res, spec.cout)
+    else:
+        out = Nhwc(res[0], spec.cout)
+        if res[1].numel():
+            out.stats = (want_stats, res[1])
+    out.pad = out_pad
+    return out
 
 
 def rowpack_applicable(spec: ConvSpec) -> bool:
@@ -246,18 +287,24 @@ class _RowpackConv(Function):
     over C <= 8 channels runs as a kh x 1 convolution over 64 channels on the TMA / tcgen05 kernels."""
 
     @staticmethod
-    def forward(ctx, x, w_param, wts_sn, scale, spec: ConvSpec):
+    def forward(ctx, x, w_param, wts_sn, scale, spec: ConvSpec, want_stats=None):
         spec2 = ConvSpec(64, spec.cout, spec.kh, 1, 0, "zeros", 1)
         w_fwd, w_dg = _rowpack_weight(w_param, spec, spec2)
         xp = ops.rowpack_fwd(x.contiguous().float(), spec.kw_, spec.pad)
         ctx.flops = spec.flops(x.shape[0], x.shape[2], x.shape[3])  # algorithmic FLOPs of the ORIGINAL kh x kw x C convolution
-        y = ops.conv2d_fwd(xp, w_fwd, spec2, scale=scale, alg_flops=ctx.flops)
+        res = ops.conv2d_fwd(xp, w_fwd, spec2, scale=scale, alg_flops=ctx.flops, want_stats=want_stats)
         ctx.spec, ctx.spec2, ctx.w_dg, ctx.scale, ctx.sn = spec, spec2, w_dg, scale, wts_sn
         ctx.save_for_backward(xp)
-        return y
+        if want_stats is None:
+            return res
+        y, stats = res
+        if stats is None:
+            stats = y.new_zeros(0, dtype=torch.float32)
+        ctx.mark_non_differentiable(stats)
+        return y, stats
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, _dstats=None):
         (xp,) = ctx.saved_tensors
         spec, spec2 = ctx.spec, ctx.spec2
         dy = dy.contiguous()
@@ -276,10 +323,10 @@ class _RowpackConv(Function):
                 dw = (g - dot * torch.outer(u, v).view_as(w0)) * inv[0]
             else:
                 dw = g.contiguous()
-        return dx, dw, None, None, None
+        return dx, dw, None, None, None, None
 
 
-def rowpack_conv(x: torch.Tensor, conv_mod, spec: ConvSpec, training: bool) -> Nhwc:
+def rowpack_conv(x: torch.Tensor, conv_mod, spec: ConvSpec, training: bool, want_stats=None) -> Nhwc:
     """Stem convolution on a plain fp32 NCHW image (bias-free).  Spectral norm as in prepare_conv."""
     sn = scale = None
     if hasattr(conv_mod, "weight_orig"):
@@ -294,7 +341,15 @@ def rowpack_conv(x: torch.Tensor, conv_mod, spec: ConvSpec, training: bool) -> N
         scale = inv
     else:
         w = conv_mod.weight
-    return Nhwc(_RowpackConv.apply(x, w, sn, scale, spec), spec.cout)
+    if want_stats is not None and spec.cout_ld > EPI_STATS_MAX_COUT:
+        want_stats = None
+    res = _RowpackConv.apply(x, w, sn, scale, spec, want_stats)
+    if want_stats is None:
+        return Nhwc(res, spec.cout)
+    out = Nhwc(res[0], spec.cout)
+    if res[1].numel():
+        out.stats = (want_stats, res[1])
+    return out
 
 
 def linear(x: torch.Tensor, lin: torch.nn.Linear, act=None) -> torch.Tensor:
@@ -361,12 +416,15 @@ def conv_cat(x: Nhwc, conv_a, conv_b, spec: ConvSpec, out_fp32=False) -> Nhwc:
     return Nhwc(y, spec.cout)
 
 
+BN_FUSED_FOLD = os.environ.get("DEI2I_BN_FUSED_FOLD", "0") != "0"
+
+
 class _BatchNorm(Function):
     @staticmethod
-    def forward(ctx, x, gamma, beta, residual, bn, training, act, out_pad):
+    def forward(ctx, x, gamma, beta, residual, bn, training, act, out_pad, stats=None):
         y, save = ops.bn_fwd(x, gamma.detach(), beta.detach(), bn.running_mean, bn.running_var, training, act=act,
                              residual=residual, momentum=bn.momentum if bn.momentum is not None else 0.1, eps=bn.eps,
-                             out_pad=out_pad)
+                             out_pad=out_pad, stats=stats)
         if training and bn.num_batches_tracked is not None:
             bn.num_batches_tracked += 1
         ctx.training, ctx.act, ctx.has_res, ctx.out_pad = training, act, residual is not None, out_pad
@@ -377,16 +435,21 @@ class _BatchNorm(Function):
     def backward(ctx, dy):
         x, gamma, beta, save = ctx.saved_tensors
         dy = dy.contiguous()
-        if ctx.out_pad:  # the consumer's gradient covers the padded frame: fold the mirrored border back (adjoint of the padding)
-            dy = ops.reflect_fold(dy, ctx.out_pad)
-        dx, dg, db = ops.bn_bwd(x, dy, gamma.detach(), beta.detach(), save, ctx.training, act=ctx.act)
-        return dx, dg, db, (dy if ctx.has_res else None), None, None, None, None
+        pad = ctx.out_pad
+        # dei2i_bn_bwd can fold the padded gradient while reading it, but measured slower than fold + dense backward (592 vs 373 us
+        # on the 256 x 256 x 64 layer): the separate pass stays the default.  The residual branch needs the folded tensor anyway.
+        if pad and (ctx.has_res or not BN_FUSED_FOLD):
+            dy, pad = ops.reflect_fold(dy, pad), 0
+        # the consumer's gradient covers the padded frame: bn_bwd folds the mirrored border back while reading it
+        dx, dg, db = ops.bn_bwd(x, dy, gamma.detach(), beta.detach(), save, ctx.training, act=ctx.act, dy_pad=pad)
+        return dx, dg, db, (dy if ctx.has_res else None), None, None, None, None, None
 
 
 def batch_norm(x: Nhwc, bn: torch.nn.BatchNorm2d, act=None, residual: Optional[Nhwc] = None, out_pad: int = 0) -> Nhwc:
     """out_pad > 0: the result already carries the reflect padding of the convolution that consumes it (Nhwc.pad)."""
     training = bn.training or not bn.track_running_stats
-    y = _BatchNorm.apply(x.t, bn.weight, bn.bias, residual.t if residual is not None else None, bn, training, act, out_pad)
+    stats = x.stats[1] if (training and x.stats is not None and x.stats[0] == "batch") else None
+    y = _BatchNorm.apply(x.t, bn.weight, bn.bias, residual.t if residual is not None else None, bn, training, act, out_pad, stats)
     out = Nhwc(y, x.c)
     out.pad = out_pad
     return out
@@ -394,8 +457,8 @@ def batch_norm(x: Nhwc, bn: torch.nn.BatchNorm2d, act=None, residual: Optional[N
 
 class _Spade(Function):
     @staticmethod
-    def forward(ctx, x, gb, up, relu, eps):
-        out, mr = ops.spade_fwd(x, gb, up, relu, eps)
+    def forward(ctx, x, gb, up, relu, eps, stats=None):
+        out, mr = ops.spade_fwd(x, gb, up, relu, eps, stats=stats)
         ctx.up, ctx.relu = up, relu
         ctx.save_for_backward(x, gb, out, mr)
         return out
@@ -404,19 +467,24 @@ class _Spade(Function):
     def backward(ctx, dout):
         x, gb, out, mr = ctx.saved_tensors
         dgb, dx = ops.spade_bwd(x, gb, out, dout.contiguous(), mr, ctx.up, ctx.relu)
-        return dx, dgb, None, None, None
+        return dx, dgb, None, None, None, None
 
 
 def spade_modulate(x: Nhwc, gb: Nhwc, up=1, relu=True, eps=1e-5) -> Nhwc:
-    return Nhwc(_Spade.apply(x.t, gb.t, up, relu, eps), x.c)
+    return Nhwc(_Spade.apply(x.t, gb.t, up, relu, eps, _sample_stats(x)), x.c)
+
+
+def _sample_stats(x: Nhwc):
+    """Per-image statistics the producing convolution already emitted for this carrier, else None (computed by the consumer)."""
+    return x.stats[1] if (x.stats is not None and x.stats[0] == "sample") else None
 
 
 class _SpadeCls(Function):
     """SPADE modulation with gamma|beta on the [N,5,5,2C] border-class map of a constant label map."""
 
     @staticmethod
-    def forward(ctx, x, gb5, up, relu, eps, out_pad):
-        out, mr = ops.spade_cls_fwd(x, gb5, up, relu, eps, out_pad)
+    def forward(ctx, x, gb5, up, relu, eps, out_pad, stats=None):
+        out, mr = ops.spade_cls_fwd(x, gb5, up, relu, eps, out_pad, stats=stats)
         ctx.up, ctx.relu, ctx.out_pad = up, relu, out_pad
         ctx.save_for_backward(x, gb5, out, mr)
         return out
@@ -425,11 +493,11 @@ class _SpadeCls(Function):
     def backward(ctx, dout):
         x, gb5, out, mr = ctx.saved_tensors
         dgb5, dx = ops.spade_cls_bwd(x, gb5, out, dout.contiguous(), mr, ctx.up, ctx.relu, ctx.out_pad)
-        return dx, dgb5.to(torch.bfloat16), None, None, None, None
+        return dx, dgb5.to(torch.bfloat16), None, None, None, None, None
 
 
 def spade_modulate_cls(x: Nhwc, gb5: Nhwc, up=1, relu=True, eps=1e-5, out_pad=0) -> Nhwc:
-    return Nhwc(_SpadeCls.apply(x.t, gb5.t, up, relu, eps, out_pad), x.c)
+    return Nhwc(_SpadeCls.apply(x.t, gb5.t, up, relu, eps, out_pad, _sample_stats(x)), x.c)
 
 
 class _UpsamplePad(Function):

@@ -161,29 +161,35 @@ class ConvBlock(nn.Module):
         conv = self.conv_block[0]
         if plain and ROWPACK_STEM and self._norm is not None and conv.bias is None and Fn.rowpack_applicable(self._spec):
             # generator stem (3->64, 7x7 reflect): row-packed image -> 7x1 convolution over 64 channels on the TMA kernels
-            y = Fn.rowpack_conv(x, conv, self._spec, conv.training)
+            y = Fn.rowpack_conv(x, conv, self._spec, conv.training, want_stats=_bn_stats(self._norm))
             y = Fn.batch_norm(y, self._norm, act=self._act, residual=residual, out_pad=out_pad if carrier_out else 0)
             return y if carrier_out else _edge(y)
         xa = Fn.to_nhwc(x)
         if carrier_out:
             plain = False
-        if plain or self._norm is None:
+        if plain:
             out_pad = 0
         spec = _consumer_spec(self._spec, xa)
         if self._norm is None:
             assert residual is None
+            # no norm layer: the convolution epilogue itself writes the next convolution's reflect padding (granted on the TMA kernel)
             y = Fn.conv(xa, conv, spec, conv.training, bias=conv.bias, act=self._act,
-                        out_fp32=self._act in ("tanh", "sigmoid"))
+                        out_fp32=self._act in ("tanh", "sigmoid"), out_pad=out_pad)
             if y.t.dtype != torch.bfloat16 and not plain:
                 y = Fn.Nhwc(y.t.to(torch.bfloat16), y.c)
         else:
-            y = Fn.conv(xa, conv, spec, conv.training, bias=conv.bias)
+            y = Fn.conv(xa, conv, spec, conv.training, bias=conv.bias, want_stats=_bn_stats(self._norm))
             y = Fn.batch_norm(y, self._norm, act=self._act, residual=residual, out_pad=out_pad)
         return _edge(y) if plain else y
 
     def reflect_pad_in(self) -> int:
         """Reflect padding this block's convolution wants on its input (what a producer may pre-write), else 0."""
         return _fusable_pad(self._spec)
+
+
+def _bn_stats(bn) -> str:
+    """'batch' when the BatchNorm that follows a convolution normalises with batch statistics (the epilogue then emits them)."""
+    return "batch" if (bn.training or not bn.track_running_stats) else None
 
 
 def _edge(y: Fn.Nhwc) -> torch.Tensor:
@@ -329,14 +335,17 @@ class NormConvBlock(nn.Module):
             raise NotImplementedError("NormConvBlock on the CUDA path fuses ReLU (or no activation) into the SPADE kernel")
         self._relu = act_layer == "relu"
 
-    def forward(self, x, labels, style_feat=None):
+    def forward(self, x, labels, style_feat=None, stats_out=False, out_pad=0):
+        """stats_out: the output feeds another SPADE block - its per-image statistics come out of the convolution epilogue;
+        out_pad: reflect padding the next convolution (the generator heads) wants pre-written on the output."""
         plain = not isinstance(x, Fn.Nhwc)
         xa = Fn.to_nhwc(x)
         s = self.norm(xa, labels, up=self._up, relu=self._relu, out_pad=_fusable_pad(self._spec))
         n, _, h, w = s.shape
         ho, wo = self._spec.out_hw(h, w)
         noise, nw = _noise_args(self.noise, n, ho, wo, s.t.device)
-        y = Fn.conv(s, self.conv, _consumer_spec(self._spec, s), self.conv.training, bias=self.conv.bias, noise=noise, noise_w=nw)
+        y = Fn.conv(s, self.conv, _consumer_spec(self._spec, s), self.conv.training, bias=self.conv.bias, noise=noise, noise_w=nw,
+                    want_stats="sample" if (stats_out and not plain) else None, out_pad=0 if plain else out_pad)
         return Fn.from_nhwc(y) if plain else y
 
     def update_alpha(self, epoch, num_epochs):
@@ -375,18 +384,20 @@ class NormResBlock(nn.Module):
             raise NotImplementedError("NormResBlock on the CUDA path fuses ReLU (or no activation) into the SPADE kernel")
         self._relu = act_layer == "relu"
 
-    def forward(self, x, labels, style_feat=None):
+    def forward(self, x, labels, style_feat=None, stats_out=False):
+        """stats_out: the output feeds another SPADE block (its per-image statistics then come out of the convolution epilogue)."""
         plain = not isinstance(x, Fn.Nhwc)
         xa = Fn.to_nhwc(x)
         n, _, h, w = xa.shape
         dev = xa.t.device
         s = self.norm_0(xa, labels, relu=self._relu, out_pad=_fusable_pad(self._spec0))
         noise, nw = _noise_args(self.noise_0, n, h, w, dev)
-        y = Fn.conv(s, self.conv_0, _consumer_spec(self._spec0, s), self.conv_0.training, bias=self.conv_0.bias, noise=noise, noise_w=nw)
+        y = Fn.conv(s, self.conv_0, _consumer_spec(self._spec0, s), self.conv_0.training, bias=self.conv_0.bias, noise=noise, noise_w=nw,
+                    want_stats="sample")
         s = self.norm_1(y, labels, relu=self._relu, out_pad=_fusable_pad(self._spec1))
         noise, nw = _noise_args(self.noise_1, n, h, w, dev)
         y = Fn.conv(s, self.conv_1, _consumer_spec(self._spec1, s), self.conv_1.training, bias=self.conv_1.bias, noise=noise, noise_w=nw,
-                    residual=xa)
+                    residual=xa, want_stats="sample" if (stats_out and not plain) else None)
         return Fn.from_nhwc(y) if plain else y
 
     def update_alpha(self, epoch, num_epochs):

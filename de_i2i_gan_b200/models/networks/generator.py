@@ -4,7 +4,8 @@ from torch import nn
 
 from ... import functional as Fn
 from ...ops import ConvSpec
-from .architecture import ConvBlock, DeConvBlock, NormConvBlock, NormResBlock, ResBlock, _edge, _spec_of, next_pad, same_frame
+from .architecture import (ConvBlock, DeConvBlock, NormConvBlock, NormResBlock, ResBlock, _consumer_spec, _edge, _fusable_pad, _spec_of,
+                           next_pad, same_frame)
 from .base_network import BaseNetwork
 
 
@@ -101,11 +102,15 @@ class DefectGanGenerator(BaseNetwork):
             feat = blk(feat, labels, out_pad=next_pad(enc, i)) if isinstance(blk, ConvBlock) else blk(feat, labels)
         for blk in self.enc_res_blk:
             feat = blk(feat, labels)
+        # every decoder block but the last feeds a SPADE (its per-image statistics come out of the convolution epilogue); the last
+        # one feeds the 3x3 reflect heads (their padding comes out of it)
+        dec = list(self.dec_blk)
         for blk in self.dec_res_blk:
-            feat = blk(feat, seg, style_feat)
-        for blk in self.dec_blk:
-            feat = blk(feat, seg, style_feat)
+            feat = blk(feat, seg, style_feat, stats_out=True)
+        for i, blk in enumerate(dec):
+            last = i + 1 == len(dec)
+            feat = blk(feat, seg, style_feat, stats_out=not last, out_pad=_fusable_pad(self._head_spec) if last else 0)
         # NOTE generator.py:266-267 (host-synchronising isnan().any() + nan_to_num_) is not reproduced: it is the
         # identity on finite activations and would cost a device->host sync per forward.
-        hd = Fn.conv_cat(feat, self.foreground_head._conv, self.distribution_head._conv, self._head_spec, out_fp32=True)
+        hd = Fn.conv_cat(feat, self.foreground_head._conv, self.distribution_head._conv, _consumer_spec(self._head_spec, feat), out_fp32=True)
         return Fn.compose(hd.t, x, self.cycle_gan)

@@ -144,28 +144,48 @@ def _kind(op, spec, flops):
     return f"conv_{op}_" + ("tiny" if flops < 2e9 else spec.klass)
 
 
+def conv_fwd_is_tma(spec: ConvSpec, n, h, w) -> bool:
+    """True when dei2i_conv2d_fwd runs this geometry on the TMA / tcgen05 kernel (which can emit statistics / a padded output)."""
+    g = spec.geom(n, h, w)
+    return bool(_lib.load().dei2i_conv2d_fwd_path(C.byref(g)))
+
+
 def conv2d_fwd(x, w_fwd, spec: ConvSpec, bias=None, noise=None, noise_weight=None, residual=None, act=None,
-               out_fp32=False, logical_hw=None, scale=None, alg_flops=None):
-    """x: bf16 [N,Hs,Ws,Cin_ld]; logical_hw=(H,W) nearest-resizes x on the fly. Returns [N,Ho,Wo,Cout_ld]."""
+               out_fp32=False, logical_hw=None, scale=None, alg_flops=None, want_stats=None, out_pad=0):
+    """x: bf16 [N,Hs,Ws,Cin_ld]; logical_hw=(H,W) nearest-resizes x on the fly. Returns [N,Ho,Wo,Cout_ld].
+    want_stats ('batch' | 'sample'): also returns the per-channel (mean, biased var) of the output over the batch / per image,
+    emitted tile by tile from the convolution epilogue - or None where that kernel does not apply.  out_pad > 0: the output is
+    [N,Ho+2p,Wo+2p,Cout_ld] with the reflect padding of its consumer in place (TMA kernel only; check conv_fwd_is_tma)."""
     _chk_act(x, "x")
     n, hs, ws, c = x.shape
     assert c == spec.cin_ld, (c, spec)
     h, w = logical_hw or (hs, ws)
     ho, wo = spec.out_hw(h, w)
-    y = torch.empty(n, ho, wo, spec.cout_ld, dtype=torch.float32 if out_fp32 else torch.bfloat16, device=x.device)
+    y = torch.empty(n, ho + 2 * out_pad, wo + 2 * out_pad, spec.cout_ld, dtype=torch.float32 if out_fp32 else torch.bfloat16, device=x.device)
     if residual is not None:
         _chk_act(residual, "residual")
-        assert residual.shape == y.shape
+        assert tuple(residual.shape) == (n, ho, wo, spec.cout_ld)
     if noise is not None:
         _chk_f32(noise, "noise")
         assert noise.numel() == n * ho * wo
     g = spec.geom(n, h, w, hs, ws)
-    e = ConvEpilogue(_p(scale), _p(bias), _p(noise), _p(noise_weight), _p(residual), ACT[act], int(out_fp32), None, 0)
+    lib = _lib.load()
+    partial = None
+    if want_stats is not None and not out_fp32 and logical_hw is None and lib.dei2i_conv2d_fwd_path(C.byref(g)) \
+            and (want_stats == "batch" or (ho * wo) % 128 == 0):
+        partial = torch.empty((n * ho * wo + 127) // 128, 2, spec.cout_ld, dtype=torch.float32, device=x.device)
+    e = ConvEpilogue(_p(scale), _p(bias), _p(noise), _p(noise_weight), _p(residual), ACT[act], int(out_fp32), _p(partial), int(out_pad))
     fl = alg_flops or spec.flops(n, ho, wo)
     with _Timed(_kind("fwd", spec, fl), fl, spec.tag(n, h, w)):
-        check(_lib.load().dei2i_conv2d_fwd(_p(x), _p(w_fwd), _p(y), C.byref(g), C.byref(e), _stream()), "dei2i_conv2d_fwd")
+        check(lib.dei2i_conv2d_fwd(_p(x), _p(w_fwd), _p(y), C.byref(g), C.byref(e), _stream()), "dei2i_conv2d_fwd")
     _log_kernel("fwd", spec.tag(n, h, w))
-    return y
+    if want_stats is None:
+        return y
+    stats = None
+    if partial is not None:
+        groups = n if want_stats == "sample" else 1
+        stats = stats_finalize(partial, (n * ho * wo) // groups, groups, spec.cout_ld)
+    return y, stats
 
 
 def conv2d_dgrad(dy, w_dgrad, spec: ConvSpec, in_hw, scale=None, alg_flops=None):
@@ -406,19 +426,38 @@ def gap_bwd(dout, hw):
 
 
 def channel_stats(x, per_sample: bool):
+    """-> fp32 [groups, 2, C]: per-channel (groups = 1) or per-(n, channel) mean and biased variance (deterministic, Welford-merged)."""
     _chk_act(x, "x")
     n, h, w, c = x.shape
+    lib = _lib.load()
     stats = torch.empty(n if per_sample else 1, 2, c, dtype=torch.float32, device=x.device)
+    need = lib.dei2i_channel_stats_scratch(n, h * w, c, int(per_sample))
+    scratch = torch.empty(max(need, 1), dtype=torch.float32, device=x.device)
     with _Timed("stream_channel_stats", x.numel() * 2, ""):
-        check(_lib.load().dei2i_channel_stats(_p(x), n, h * w, c, int(per_sample), _p(stats), _stream()), "dei2i_channel_stats")
+        check(lib.dei2i_channel_stats(_p(x), n, h * w, c, int(per_sample), _p(stats), _p(scratch), need, _stream()), "dei2i_channel_stats")
     return stats
 
 
-def bn_fwd(x, gamma, beta, running_mean, running_var, training, act=None, residual=None, momentum=0.1, eps=1e-5, out_pad=0):
-    """out_pad > 0: y is [N, H+2p, W+2p, C] and carries the reflect padding of its consumer (dei2i_bn_fwd_pad)."""
+def stats_finalize(partial, rows_per_group: int, groups: int, c: int, rows_per_tile: int = 128):
+    """Per-tile (mean, M2) pairs emitted by a convolution epilogue ([groups * T][2][ld]) -> fp32 [groups, 2, c] (mean, biased var)."""
+    t_total, _, ld = partial.shape
+    assert t_total % groups == 0, (partial.shape, groups)
+    stats = torch.empty(groups, 2, c, dtype=torch.float32, device=partial.device)
+    check(_lib.load().dei2i_stats_finalize(_p(partial), t_total // groups, rows_per_tile, rows_per_group, groups, c, ld, _p(stats),
+                                           _stream()), "dei2i_stats_finalize")
+    return stats
+
+
+def bn_fwd(x, gamma, beta, running_mean, running_var, training, act=None, residual=None, momentum=0.1, eps=1e-5, out_pad=0,
+           stats=None):
+    """out_pad > 0: y is [N, H+2p, W+2p, C] and carries the reflect padding of its consumer (dei2i_bn_fwd_pad).
+    stats: batch (mean, var) [1,2,C] already produced by the convolution epilogue (else computed here when training)."""
     _chk_act(x, "x")
     n, h, w, c = x.shape
-    stats = channel_stats(x, False) if training else None
+    if training and stats is None:
+        stats = channel_stats(x, False)
+    if not training:
+        stats = None
     save = torch.empty(2, c, dtype=torch.float32, device=x.device)
     if out_pad:
         y = torch.empty(n, h + 2 * out_pad, w + 2 * out_pad, c, dtype=x.dtype, device=x.device)
@@ -435,27 +474,32 @@ def bn_fwd(x, gamma, beta, running_mean, running_var, training, act=None, residu
     return y, save
 
 
-def bn_bwd(x, dy, gamma, beta, save, training, act=None):
+def bn_bwd(x, dy, gamma, beta, save, training, act=None, dy_pad=0):
+    """-> (dx, dgamma, dbeta).  dy_pad > 0: dy is the gradient of the padded forward output, folded while it is read."""
     _chk_act(x, "x")
     _chk_act(dy, "dy")
     n, h, w, c = x.shape
+    assert tuple(dy.shape) == (n, h + 2 * dy_pad, w + 2 * dy_pad, c), (dy.shape, x.shape, dy_pad)
+    lib = _lib.load()
     dx = torch.empty_like(x)
-    dgb = torch.empty(2, c, dtype=torch.float32, device=x.device)
-    scratch = torch.empty(2 * c, dtype=torch.float32, device=x.device)
-    with _Timed("stream_bn_bwd", x.numel() * 2 * 3, ""):
-        check(_lib.load().dei2i_bn_bwd(_p(x), _p(dy), _p(dx), _p(gamma), _p(beta), _p(save[0]), _p(save[1]), _p(dgb[0]),
-                                       _p(dgb[1]), _p(scratch), n, h * w, c, int(training), ACT[act], _stream()), "dei2i_bn_bwd")
-    return dx, dgb[0], dgb[1]
+    dbg = torch.empty(2, c, dtype=torch.float32, device=x.device)  # [dbeta | dgamma]
+    need = lib.dei2i_bn_bwd_scratch(n, h * w, c)
+    scratch = torch.empty(need, dtype=torch.float32, device=x.device)
+    with _Timed("stream_bn_bwd", x.numel() * 2 * 2 + dy.numel() * 2, ""):
+        check(lib.dei2i_bn_bwd(_p(x), _p(dy), _p(dx), _p(gamma), _p(beta), _p(save[0]), _p(save[1]), _p(dbg[1]), _p(dbg[0]),
+                               _p(scratch), need, n, h, w, c, int(training), ACT[act], int(dy_pad), _stream()), "dei2i_bn_bwd")
+    return dx, dbg[1], dbg[0]
 
 
-def spade_fwd(x, gb, up: int = 1, relu: bool = True, eps: float = 1e-5):
+def spade_fwd(x, gb, up: int = 1, relu: bool = True, eps: float = 1e-5, stats=None):
     """x: [N,H/up,W/up,C]; gb: [N,H,W,2C] -> out [N,H,W,C] = relu(IN(x)*(1+gamma)+beta); also returns mean_rstd."""
     _chk_act(x, "x")
     _chk_act(gb, "gb")
     n, hx, wx, c = x.shape
     h, w = hx * up, wx * up
     assert tuple(gb.shape) == (n, h, w, 2 * c), (gb.shape, x.shape, up)
-    stats = channel_stats(x, True)
+    if stats is None:
+        stats = channel_stats(x, True)
     out = torch.empty(n, h, w, c, dtype=torch.bfloat16, device=x.device)
     mr = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
     with _Timed("stream_spade_fwd", x.numel() * 2 + gb.numel() * 2 + out.numel() * 2, ""):
@@ -468,14 +512,16 @@ def spade_bwd(x, gb, out, dout, mean_rstd, up: int = 1, relu: bool = True):
     n, h, w, c = out.shape
     dgb = torch.empty_like(gb)
     dx = torch.empty_like(x)
-    scratch = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
+    lib = _lib.load()
+    need = lib.dei2i_image_reduce_scratch(n, h * w, c)
+    scratch = torch.empty(need, dtype=torch.float32, device=x.device)
     with _Timed("stream_spade_bwd", x.numel() * 2 + 2 * gb.numel() * 2 + 2 * out.numel() * 2 + dx.numel() * 2, ""):
-        check(_lib.load().dei2i_spade_bwd(_p(x), _p(gb), _p(out), _p(dout), _p(dgb), _p(dx), _p(mean_rstd), _p(scratch), n, h, w,
-                                          c, up, int(relu), _stream()), "dei2i_spade_bwd")
+        check(lib.dei2i_spade_bwd(_p(x), _p(gb), _p(out), _p(dout), _p(dgb), _p(dx), _p(mean_rstd), _p(scratch), need, n, h, w,
+                                  c, up, int(relu), _stream()), "dei2i_spade_bwd")
     return dgb, dx
 
 
-def spade_cls_fwd(x, gb5, up: int = 1, relu: bool = True, eps: float = 1e-5, out_pad: int = 0):
+def spade_cls_fwd(x, gb5, up: int = 1, relu: bool = True, eps: float = 1e-5, out_pad: int = 0, stats=None):
     """SPADE over a border-class map (constant label map): gb5 bf16 [N,5,5,2C]; otherwise like spade_fwd.  out_pad > 0: the
     output is [N,H+2p,W+2p,C] with the reflect padding of the consuming convolution already in place."""
     _chk_act(x, "x")
@@ -483,7 +529,8 @@ def spade_cls_fwd(x, gb5, up: int = 1, relu: bool = True, eps: float = 1e-5, out
     n, hx, wx, c = x.shape
     h, w = hx * up, wx * up
     assert tuple(gb5.shape) == (n, 5, 5, 2 * c), (gb5.shape, x.shape)
-    stats = channel_stats(x, True)
+    if stats is None:
+        stats = channel_stats(x, True)
     out = torch.empty(n, h + 2 * out_pad, w + 2 * out_pad, c, dtype=torch.bfloat16, device=x.device)
     mr = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
     with _Timed("stream_spade_cls_fwd", x.numel() * 2 + out.numel() * 2, ""):
@@ -499,21 +546,24 @@ def spade_cls_bwd(x, gb5, out, dout, mean_rstd, up: int = 1, relu: bool = True, 
     assert dout.shape == out.shape
     dgb5 = torch.empty(n, 5, 5, 2 * c, dtype=torch.float32, device=x.device)
     dx = torch.empty_like(x)
-    scratch = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
+    lib = _lib.load()
+    need = lib.dei2i_spade_cls_bwd_scratch(n, h, w, c, up)
+    scratch = torch.empty(need, dtype=torch.float32, device=x.device)
     with _Timed("stream_spade_cls_bwd", x.numel() * 2 * 2 + dout.numel() * 2, ""):
-        check(_lib.load().dei2i_spade_cls_bwd(_p(x), _p(gb5), _p(out), _p(dout), _p(dgb5), _p(dx), _p(mean_rstd), _p(scratch), n, h,
-                                              w, c, up, int(relu), out_pad, _stream()), "dei2i_spade_cls_bwd")
+        check(lib.dei2i_spade_cls_bwd(_p(x), _p(gb5), _p(out), _p(dout), _p(dgb5), _p(dx), _p(mean_rstd), _p(scratch), need, n, h,
+                                      w, c, up, int(relu), out_pad, _stream()), "dei2i_spade_cls_bwd")
     return dgb5, dx
 
 
-def adain_act_fwd(x, scale, shift, slope: float = 0.2, eps: float = 1e-5):
+def adain_act_fwd(x, scale, shift, slope: float = 0.2, eps: float = 1e-5, stats=None):
     """out = lrelu_slope(IN(x) * scale[n,c] + shift[n,c]); scale / shift fp32 [N,C].  Returns (out, mean_rstd)."""
     _chk_act(x, "x")
     _chk_f32(scale, "scale")
     _chk_f32(shift, "shift")
     n, h, w, c = x.shape
     assert tuple(scale.shape) == (n, c) and tuple(shift.shape) == (n, c), (scale.shape, shift.shape, x.shape)
-    stats = channel_stats(x, True)
+    if stats is None:
+        stats = channel_stats(x, True)
     out = torch.empty_like(x)
     mr = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
     check(_lib.load().dei2i_adain_act_fwd(_p(x), _p(out), _p(stats), _p(scale), _p(shift), _p(mr), n, h * w, c, float(slope), float(eps),
@@ -526,8 +576,11 @@ def adain_act_bwd(x, out, dout, scale, mean_rstd, slope: float = 0.2):
     n, h, w, c = x.shape
     dx = torch.empty_like(x)
     red = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
-    check(_lib.load().dei2i_adain_act_bwd(_p(x), _p(out), _p(dout), _p(dx), _p(scale), _p(mean_rstd), _p(red), n, h * w, c, float(slope),
-                                          _stream()), "dei2i_adain_act_bwd")
+    lib = _lib.load()
+    need = lib.dei2i_image_reduce_scratch(n, h * w, c)
+    scratch = torch.empty(need, dtype=torch.float32, device=x.device)
+    check(lib.dei2i_adain_act_bwd(_p(x), _p(out), _p(dout), _p(dx), _p(scale), _p(mean_rstd), _p(red), _p(scratch), need, n, h * w, c,
+                                  float(slope), _stream()), "dei2i_adain_act_bwd")
     return dx, red[:, 1], red[:, 0]
 
 
@@ -549,22 +602,27 @@ def axpby(a, b, sa: float, sb: float = 0.0):
     return out
 
 
-def act_bwd(y, dy, act, want_dx=True, want_bias_grad=False):
+def act_bwd(y, dy, act, want_dx=True, want_bias_grad=False, pad=0):
+    """dx = dy * act'(y), bias grad = column sums of dx.  pad > 0: y and dy are consumer-padded [N,H+2p,W+2p,C] (conv2d_fwd with
+    out_pad): dy is folded while it is read and dx comes back dense [N,H,W,C]."""
     _chk_act(dy, "dy")
-    c = dy.shape[3]
-    m = dy.numel() // c
-    dx = torch.empty_like(dy) if want_dx else None
+    n, hp, wp, c = dy.shape
+    h, w = hp - 2 * pad, wp - 2 * pad
+    m = n * h * w
+    dx = torch.empty(n, h, w, c, dtype=torch.bfloat16, device=dy.device) if want_dx else None
     bg = torch.empty(c, dtype=torch.float32, device=dy.device) if want_bias_grad else None
+    scratch = torch.empty(_lib.REDUCE_BLOCKS * c, dtype=torch.float32, device=dy.device) if want_bias_grad else None
     with _Timed("stream_act_bwd", dy.numel() * 2 * (int(y is not None) + 1 + int(want_dx)), ""):
-        check(_lib.load().dei2i_act_bwd(_p(y), _p(dy), _p(dx), _p(bg), m, c, ACT[act], _stream()), "dei2i_act_bwd")
+        check(_lib.load().dei2i_act_bwd(_p(y), _p(dy), _p(dx), _p(bg), _p(scratch), m, c, ACT[act], h, w, int(pad), _stream()), "dei2i_act_bwd")
     return dx, bg
 
 
 def noise_wgrad(dy, noise, dw, c_real, accumulate=False):
     c = dy.shape[3]
     m = dy.numel() // c
+    scratch = torch.empty(_lib.REDUCE_BLOCKS, dtype=torch.float32, device=dy.device)
     with _Timed("stream_noise_wgrad", dy.numel() * 2, ""):
-        check(_lib.load().dei2i_noise_wgrad(_p(dy), _p(noise), _p(dw), m, c, c_real, 1.0 if accumulate else 0.0, _stream()),
+        check(_lib.load().dei2i_noise_wgrad(_p(dy), _p(noise), _p(dw), _p(scratch), m, c, c_real, 1.0 if accumulate else 0.0, _stream()),
               "dei2i_noise_wgrad")
     return dw
 
@@ -603,16 +661,18 @@ def bce_logits(logits, targets=None, target_const=0.0, want_grad=True, grad_scal
 def l1(a, b=None, grad_a=None, grad_b=None, grad_scale=1.0, accumulate=False):
     _chk_f32(a, "a")
     loss = torch.empty((), dtype=torch.float32, device=a.device)
+    scratch = torch.empty(_lib.REDUCE_BLOCKS, dtype=torch.float32, device=a.device)
     check(_lib.load().dei2i_l1(_p(a), _p(b), a.numel(), _p(loss), _p(grad_a), _p(grad_b), float(grad_scale), int(accumulate),
-                               _stream()), "dei2i_l1")
+                               _p(scratch), _stream()), "dei2i_l1")
     return loss
 
 
 def mse(a, b=None, grad_a=None, grad_b=None, grad_scale=1.0, accumulate=False):
     _chk_f32(a, "a")
     loss = torch.empty((), dtype=torch.float32, device=a.device)
+    scratch = torch.empty(_lib.REDUCE_BLOCKS, dtype=torch.float32, device=a.device)
     check(_lib.load().dei2i_mse(_p(a), _p(b), a.numel(), _p(loss), _p(grad_a), _p(grad_b), float(grad_scale), int(accumulate),
-                                _stream()), "dei2i_mse")
+                                _p(scratch), _stream()), "dei2i_mse")
     return loss
 
 

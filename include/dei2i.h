@@ -25,6 +25,9 @@ typedef void* dei2i_stream; /* cudaStream_t */
 
 enum dei2i_status { DEI2I_OK = 0, DEI2I_ERR_CUDA = -1, DEI2I_ERR_INVALID = -2 };
 enum dei2i_act { DEI2I_ACT_NONE = 0, DEI2I_ACT_LRELU = 1 /* slope 0.2 */, DEI2I_ACT_RELU = 2, DEI2I_ACT_TANH = 3, DEI2I_ACT_SIGMOID = 4 };
+/* upper bound of the block count of the block-partial reductions (scratch sizing, see the individual entry points) */
+#define DEI2I_REDUCE_BLOCKS 2048
+
 enum dei2i_pad { DEI2I_PAD_ZEROS = 0, DEI2I_PAD_REFLECT = 1 };
 
 int dei2i_version(void);
@@ -167,10 +170,18 @@ int dei2i_rowpack_bwd(const void* dxp, float* dimg, int N, int C, int H, int W, 
 int dei2i_nchw_to_nhwc(const float* src, void* dst, int N, int C, int H, int W, int C_ld, dei2i_stream stream);
 int dei2i_nhwc_to_nchw(const void* src, float* dst, int N, int C, int H, int W, int C_ld, dei2i_stream stream);
 
-/* Per-channel (groups = 1) or per-(n,channel) (groups = N) sum and sum of squares of a bf16 NHWC tensor:
+/* Per-channel (groups = 1) or per-(n,channel) (groups = N) mean and BIASED variance of a bf16 NHWC tensor:
  * nn.BatchNorm2d / nn.InstanceNorm2d statistics (generator.py:71,113,124; normalization.py:14).
- * stats: fp32 [groups, 2, C] ([g][0][c] = sum, [g][1][c] = sum of squares), overwritten. */
-int dei2i_channel_stats(const void* x, int N, int HW, int C, int per_sample, float* stats, dei2i_stream stream);
+ * stats: fp32 [groups, 2, C] ([g][0][c] = mean, [g][1][c] = variance), overwritten.  Deterministic: per-block (mean, M2) pairs
+ * (shifted sums, no atomics) in `scratch` (>= dei2i_channel_stats_scratch(...) floats), merged in a fixed order (Chan et al.). */
+size_t dei2i_channel_stats_scratch(int N, int HW, int C, int per_sample);
+int dei2i_channel_stats(const void* x, int N, int HW, int C, int per_sample, float* stats, float* scratch, size_t scratch_floats,
+                        dei2i_stream stream);
+/* Second half of the statistics when the producer emitted the per-tile pairs itself (dei2i_conv_epilogue.stats_partial, 128 rows
+ * per tile): partial [groups * tiles_per_group][2][ld] (mean, M2), tile t of a group covering rows [t * rows_per_tile, ...) of the
+ * group's rows_per_group rows -> stats [groups, 2, C] (mean, biased variance).  Fixed merge order. */
+int dei2i_stats_finalize(const float* partial, int tiles_per_group, int rows_per_tile, long long rows_per_group, int groups, int C,
+                         int ld, float* stats, dei2i_stream stream);
 
 /* nn.BatchNorm2d (+ LeakyReLU(0.2) / residual add) forward, ConvBlock architecture.py:103-107, ResBlock :174-176.
  * training: uses batch statistics from `stats` (dei2i_channel_stats, groups=1), updates running stats
@@ -186,11 +197,14 @@ int dei2i_bn_fwd(const void* x, void* y, const void* residual, const float* stat
 int dei2i_bn_fwd_pad(const void* x, void* y, const void* residual, const float* stats, const float* gamma, const float* beta,
                      float* running_mean, float* running_var, float* save_mean, float* save_rstd, int N, int H, int W, int C,
                      int training, float momentum, float eps, int act, int out_pad, dei2i_stream stream);
-/* backward of the above: dx, dgamma, dbeta (fp32 [C], written). y is the forward OUTPUT before the residual add
- * is NOT needed: the activation mask is recomputed from x. scratch: fp32 [2*C]. */
+/* backward of the above: dx, dbeta | dgamma (fp32 [2, C] as ONE buffer, dbeta first; dgamma = dbeta + C).  The activation mask is
+ * recomputed from x (the forward output is not needed).  dy_pad > 0: dy is the gradient of the PADDED output of dei2i_bn_fwd_pad
+ * ([N, H+2p, W+2p, C]) and is folded while it is read (no dei2i_reflect_fold pass).  Deterministic: per-block partial sums in
+ * `scratch` (>= dei2i_bn_bwd_scratch(N, H*W, C) floats) finished in a fixed order. */
+size_t dei2i_bn_bwd_scratch(int N, int HW, int C);
 int dei2i_bn_bwd(const void* x, const void* dy, void* dx, const float* gamma, const float* beta, const float* save_mean,
-                 const float* save_rstd, float* dgamma, float* dbeta, float* scratch, int N, int HW, int C, int training,
-                 int act, dei2i_stream stream);
+                 const float* save_rstd, float* dgamma, float* dbeta, float* scratch, size_t scratch_floats, int N, int H, int W,
+                 int C, int training, int act, int dy_pad, dei2i_stream stream);
 
 /* SPADE modulation (normalization.py:24-37) + ReLU (architecture.py:244,347-348), optional 2x nearest up-sampling
  * of x (architecture.py:242): out = [relu](IN(x) * (1 + gamma) + beta), gamma/beta = first/second C columns of `gb`
@@ -198,9 +212,11 @@ int dei2i_bn_bwd(const void* x, const void* dy, void* dx, const float* gamma, co
  * stats from dei2i_channel_stats(per_sample=1) on x; writes mean_rstd fp32 [N,2,C] for the backward. */
 int dei2i_spade_fwd(const void* x, const void* gb, void* out, const float* stats, float* mean_rstd, int N, int H,
                     int W, int C, int up, int relu, float eps, dei2i_stream stream);
-/* backward: dgb (bf16 [N,H,W,2C]) and dx (bf16 [N,H/up,W/up,C]); scratch fp32 [N,2,C]. */
+/* backward: dgb (bf16 [N,H,W,2C]) and dx (bf16 [N,H/up,W/up,C]); scratch >= dei2i_image_reduce_scratch(N, H*W, C) floats
+ * (per-block partial sums, finished in a fixed order - no atomics). */
+size_t dei2i_image_reduce_scratch(int N, int HW, int C);
 int dei2i_spade_bwd(const void* x, const void* gb, const void* out, const void* dout, void* dgb, void* dx,
-                    const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, int relu,
+                    const float* mean_rstd, float* scratch, size_t scratch_floats, int N, int H, int W, int C, int up, int relu,
                     dei2i_stream stream);
 
 /* SPADE modulation over a border-class map: the training path feeds SPADE a 1x1 label map (defectgan_model.py:185-205),
@@ -209,7 +225,8 @@ int dei2i_spade_bwd(const void* x, const void* gb, const void* out, const void* 
  * H-1).  gb5: bf16 [N,5,5,2C] = the same convolutions evaluated on a constant 5x5 map; pixel (h,w) uses entry
  * (cls(h), cls(w)).  Exact restructuring of normalization.py:24-37, H, W >= 5.
  * backward: dgb5 fp32 [N,5,5,2C] (class-wise sums of the per-pixel gamma/beta gradients, written), dx bf16;
- * scratch fp32 [N,2,C].
+ * scratch >= dei2i_spade_cls_bwd_scratch(...) floats.  Deterministic: the interior class is reduced band by band, each frame
+ * class by its own block, everything summed in a fixed order (no atomics); the backward takes out_pad in {0, 1}.
  * out_pad > 0: `out` (and `dout` of the backward) is [N, H+2*out_pad, W+2*out_pad, C] and already carries the reflect
  * padding of the convolution that consumes it (architecture.py:228-233,320-337 padding_mode='reflect'): the forward writes the
  * mirrored border itself, the backward folds the padded gradient while reading it.
@@ -217,8 +234,9 @@ int dei2i_spade_bwd(const void* x, const void* gb, const void* out, const void* 
  * with the forward's own expression (`out` stays in the signature; it may be NULL). */
 int dei2i_spade_cls_fwd(const void* x, const void* gb5, void* out, const float* stats, float* mean_rstd, int N, int H,
                         int W, int C, int up, int relu, float eps, int out_pad, dei2i_stream stream);
+size_t dei2i_spade_cls_bwd_scratch(int N, int H, int W, int C, int up);
 int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* out, const void* dout, float* dgb5, void* dx,
-                        const float* mean_rstd, float* scratch, int N, int H, int W, int C, int up, int relu,
+                        const float* mean_rstd, float* scratch, size_t scratch_floats, int N, int H, int W, int C, int up, int relu,
                         int out_pad, dei2i_stream stream);
 
 /* ---- StarGAN-v2 normalisation (stargan-v2/core/model.py) ----
@@ -230,20 +248,23 @@ int dei2i_spade_cls_bwd(const void* x, const void* gb5, const void* out, const v
 int dei2i_adain_act_fwd(const void* x, void* out, const float* stats, const float* scale, const float* shift,
                         float* mean_rstd, int N, int HW, int C, float slope, float eps, dei2i_stream stream);
 int dei2i_adain_act_bwd(const void* x, const void* out, const void* dout, void* dx, const float* scale,
-                        const float* mean_rstd, float* dshift_dscale, int N, int HW, int C, float slope,
-                        dei2i_stream stream);
+                        const float* mean_rstd, float* dshift_dscale, float* scratch, size_t scratch_floats, int N, int HW, int C,
+                        float slope, dei2i_stream stream);  /* scratch >= dei2i_image_reduce_scratch(N, HW, C) floats */
 /* y = act(x) over n bf16 elements (pre-activation of the StarGAN-v2 ResBlk, model.py:56,62); n % 8 == 0. */
 int dei2i_act_fwd(const void* x, void* y, long long n, int act, dei2i_stream stream);
 /* out = sa * a + sb * b (b may be NULL) over n bf16 elements: residual merge (x + r) / sqrt(2), model.py:66-68,118-121. */
 int dei2i_axpby(const void* a, const void* b, void* out, long long n, float sa, float sb, dei2i_stream stream);
 
 /* act backward for fused conv epilogues: dx = dy * act'(y) computed from the saved OUTPUT y (bf16);
- * bias_grad (fp32 [C], may be NULL) receives sum over pixels of dx. */
-int dei2i_act_bwd(const void* y, const void* dy, void* dx, float* bias_grad, long long M, int C, int act,
-                  dei2i_stream stream);
+ * bias_grad (fp32 [C], may be NULL) receives the sum over pixels of dx (per-block partials in `scratch`, >= DEI2I_REDUCE_BLOCKS * C
+ * floats, finished in a fixed order).  pad > 0: y and dy are the consumer-PADDED tensors [N, H+2p, W+2p, C] written by
+ * dei2i_conv2d_fwd with out_pad: y is read at the interior, dy folded on read; dx is dense [N, H, W, C]; M = N * H * W. */
+int dei2i_act_bwd(const void* y, const void* dy, void* dx, float* bias_grad, float* scratch, long long M, int C, int act, int H,
+                  int W, int pad, dei2i_stream stream);
 
-/* NoiseInjection weight gradient: dw[0] (+)= sum_{m,c} dy[m,c] * noise[m]  (architecture.py:389). */
-int dei2i_noise_wgrad(const void* dy, const float* noise, float* dw, long long M, int C, int C_real, float beta,
+/* NoiseInjection weight gradient: dw[0] = beta * dw[0] + sum_{m,c} dy[m,c] * noise[m]  (architecture.py:389);
+ * scratch >= DEI2I_REDUCE_BLOCKS floats. */
+int dei2i_noise_wgrad(const void* dy, const float* noise, float* dw, float* scratch, long long M, int C, int C_real, float beta,
                       dei2i_stream stream);
 
 /* Generator heads + composition (generator.py:268-270): hd = fp32 [M,8] raw head convolution output
@@ -262,11 +283,11 @@ int dei2i_compose_bwd(const float* hd, const float* x, const float* dout, const 
 int dei2i_bce_logits(const float* logits, const float* targets, float target_const, long long n, float* loss,
                      float* grad, float grad_scale, dei2i_stream stream);
 int dei2i_l1(const float* a, const float* b, long long n, float* loss, float* grad_a, float* grad_b, float grad_scale,
-             int accumulate_grad, dei2i_stream stream);
+             int accumulate_grad, float* scratch /* >= DEI2I_REDUCE_BLOCKS floats */, dei2i_stream stream);
 
 /* mse: mse_loss(a, b) (b == NULL: zeros); same gradient conventions as dei2i_l1. */
 int dei2i_mse(const float* a, const float* b, long long n, float* loss, float* grad_a, float* grad_b, float grad_scale,
-              int accumulate_grad, dei2i_stream stream);
+              int accumulate_grad, float* scratch /* >= DEI2I_REDUCE_BLOCKS floats */, dei2i_stream stream);
 /* cce: cross_entropy(logits [B,C], class-probability targets [B,C]) = mean_b(-sum_c t log_softmax(z)). */
 int dei2i_ce_soft(const float* logits, const float* targets, int B, int C, float* loss, float* grad, float grad_scale,
                   dei2i_stream stream);

@@ -73,7 +73,10 @@ def main():
             dy = torch.randn_like(x)
             timeit(f"bn_fwd_pad c{c} h{h}", lambda: ops.bn_fwd(x, gamma, beta, rm, rv, True, act="leaky_relu", out_pad=1))
             timeit(f"bn_bwd c{c} h{h}", lambda: ops.bn_bwd(x, dy, gamma, beta, save, True, act="leaky_relu"))
+            dyp = torch.randn_like(y)
+            timeit(f"bn_bwd c{c} h{h} dy_pad=1", lambda: ops.bn_bwd(x, dyp, gamma, beta, save, True, act="leaky_relu", dy_pad=1))
             timeit(f"reflect_fold c{c} h{h}", lambda: ops.reflect_fold(y, 1))
+            timeit(f"channel_stats c{c} h{h}", lambda: ops.channel_stats(x, False))
 
 
 if __name__ == "__main__":

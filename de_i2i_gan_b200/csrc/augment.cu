@@ -1,0 +1,194 @@
+// DiffAugment (defectGAN/utils/diffaug.py:9-75) as fused streaming kernels on FP32 NCHW images - the tensors that sit between the
+// generator output and the discriminator input (defectgan_model.py:200-203, 266-271).
+//
+//   color        x1 = x + (b - 0.5);  x2 = (x1 - mean_c(x1)) * 2 s + mean_c(x1);  x3 = (x2 - mean_chw(x2)) * (k + 0.5) + mean_chw(x2)
+//   translation  y[i, j] = x3[i + tx, j + ty], zero outside the image (F.pad by one + clamped gather)
+//   cutout       y[i, j] = 0 inside the (clamped) ch x cw window centred at (ox, oy)
+//
+// The colour ops are point-wise, so they commute with the translation; saturation keeps every pixel's channel mean and brightness
+// adds a constant, hence mean_chw(x2) = mean_chw(x) + (b - 0.5): ONE reduction over the input, then ONE pass that reads x at the
+// translated position and writes y.  Backward: g3 = adjoint(translation, cutout)(dy); g2 = K g3 + (1 - K) mean_chw(g3);
+// g1 = S g2 + (1 - S) mean_c(g2) - again one reduction (over dy, restricted to the positions that survive the window and the
+// frame) and one pass.  Random parameters are drawn on the host side with the reference's torch calls; reductions are block-partial
+// sums finished in a fixed order (deterministic).
+#include <string.h>
+
+#include "common.cuh"
+#include "../../include/dei2i.h"
+
+namespace dei2i {
+void count_launch(int n = 1);
+
+struct AugGeom {
+  int N, C, H, W, policy;
+  int ch, cw;  // cutout window
+};
+
+// params per image: [0] b - 0.5, [1] S = 2 s, [2] K = k + 0.5, [3] tx, [4] ty, [5] ox, [6] oy, [7] unused
+DEVINL bool cut_out(const AugGeom& g, const float* __restrict__ p, int i, int j) {
+  if (!(g.policy & DEI2I_AUG_CUTOUT)) return false;
+  const int ox = (int)p[5], oy = (int)p[6];
+  // rows clamp(ox - ch/2 + [0, ch), 0, H - 1): a contiguous range (clamping only shortens it)
+  const int r0 = max(ox - g.ch / 2, 0), r1 = min(ox - g.ch / 2 + g.ch - 1, g.H - 1);
+  const int c0 = max(oy - g.cw / 2, 0), c1 = min(oy - g.cw / 2 + g.cw - 1, g.W - 1);
+  const int rr0 = min(r0, g.H - 1), rr1 = max(r1, 0), cc0 = min(c0, g.W - 1), cc1 = max(c1, 0);
+  return i >= rr0 && i <= rr1 && j >= cc0 && j <= cc1;
+}
+
+// part[n][blk] = sum over this block's pixels of sum_c v[n, c, i, j] * keep(i, j)   (keep == 1 for the forward: plain image sum)
+template <bool BWD>
+__global__ void __launch_bounds__(256)
+aug_sum_kernel(const float* __restrict__ v, const float* __restrict__ params, AugGeom g, float* __restrict__ part) {
+  __shared__ float sh[32];
+  const int n = blockIdx.y;
+  const float* p = params + n * 8;
+  const int HW = g.H * g.W;
+  const int tx = (g.policy & DEI2I_AUG_TRANSLATION) ? (int)p[3] : 0, ty = (g.policy & DEI2I_AUG_TRANSLATION) ? (int)p[4] : 0;
+  float acc = 0.f;
+  for (int px = blockIdx.x * blockDim.x + threadIdx.x; px < HW; px += gridDim.x * blockDim.x) {
+    bool keep = true;
+    if (BWD) {  // output position (i, j) contributes iff it is outside the cutout window and its source lies inside the image
+      const int i = px / g.W, j = px - i * g.W;
+      const int si = i + tx, sj = j + ty;
+      keep = !cut_out(g, p, i, j) && si >= 0 && si < g.H && sj >= 0 && sj < g.W;
+    }
+    if (keep)
+      for (int c = 0; c < g.C; ++c) acc += v[((size_t)n * g.C + c) * HW + px];
+  }
+  acc = warp_sum(acc);
+  const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+  if (l == 0) sh[w] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int k = 0; k < (int)(blockDim.x >> 5); ++k) t += sh[k];
+    part[(size_t)n * gridDim.x + blockIdx.x] = t;
+  }
+}
+
+__global__ void aug_sum_finish_kernel(const float* __restrict__ part, int nblk, float scale, float* __restrict__ out) {
+  const int n = threadIdx.x;  // one thread per image, blocks summed in order
+  float t = 0.f;
+  for (int b = 0; b < nblk; ++b) t += part[(size_t)n * nblk + b];
+  out[n] = t * scale;
+}
+
+constexpr int kAugMaxC = 4;
+
+__global__ void __launch_bounds__(256)
+aug_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, const float* __restrict__ params, const float* __restrict__ mean,
+               AugGeom g) {
+  const int n = blockIdx.y;
+  const float* p = params + n * 8;
+  const int HW = g.H * g.W;
+  const bool color = g.policy & DEI2I_AUG_COLOR;
+  const float b = color ? p[0] : 0.f, S = color ? p[1] : 1.f, K = color ? p[2] : 1.f;
+  const float M = color ? mean[n] + b : 0.f;
+  const int tx = (g.policy & DEI2I_AUG_TRANSLATION) ? (int)p[3] : 0, ty = (g.policy & DEI2I_AUG_TRANSLATION) ? (int)p[4] : 0;
+  for (int px = blockIdx.x * blockDim.x + threadIdx.x; px < HW; px += gridDim.x * blockDim.x) {
+    const int i = px / g.W, j = px - i * g.W;
+    const int si = i + tx, sj = j + ty;
+    const bool live = !cut_out(g, p, i, j) && si >= 0 && si < g.H && sj >= 0 && sj < g.W;
+    float v[kAugMaxC];
+    float m = 0.f;
+#pragma unroll
+    for (int c = 0; c < kAugMaxC; ++c)
+      if (c < g.C) {
+        v[c] = live ? x[((size_t)n * g.C + c) * HW + si * g.W + sj] + b : 0.f;
+        m += v[c];
+      }
+    m /= (float)g.C;
+#pragma unroll
+    for (int c = 0; c < kAugMaxC; ++c)
+      if (c < g.C) {
+        const float x2 = (v[c] - m) * S + m;
+        y[((size_t)n * g.C + c) * HW + px] = live ? (x2 - M) * K + M : 0.f;
+      }
+  }
+}
+
+// dx[n, c, si, sj] for every SOURCE position: the gradient arrives from output (si - tx, sj - ty) if that lies in the image and outside
+// the cutout window; the two mean terms reach every source position.
+__global__ void __launch_bounds__(256)
+aug_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, const float* __restrict__ params, const float* __restrict__ gmean,
+               AugGeom g) {
+  const int n = blockIdx.y;
+  const float* p = params + n * 8;
+  const int HW = g.H * g.W;
+  const bool color = g.policy & DEI2I_AUG_COLOR;
+  const float S = color ? p[1] : 1.f, K = color ? p[2] : 1.f;
+  const float G = color ? gmean[n] : 0.f;  // mean over (c, h, w) of g3
+  const int tx = (g.policy & DEI2I_AUG_TRANSLATION) ? (int)p[3] : 0, ty = (g.policy & DEI2I_AUG_TRANSLATION) ? (int)p[4] : 0;
+  for (int px = blockIdx.x * blockDim.x + threadIdx.x; px < HW; px += gridDim.x * blockDim.x) {
+    const int si = px / g.W, sj = px - si * g.W;
+    const int i = si - tx, j = sj - ty;
+    const bool live = i >= 0 && i < g.H && j >= 0 && j < g.W && !cut_out(g, p, i, j);
+    float g2[kAugMaxC];
+    float m = 0.f;
+#pragma unroll
+    for (int c = 0; c < kAugMaxC; ++c)
+      if (c < g.C) {
+        const float g3 = live ? dy[((size_t)n * g.C + c) * HW + i * g.W + j] : 0.f;
+        g2[c] = K * g3 + (1.f - K) * G;
+        m += g2[c];
+      }
+    m /= (float)g.C;
+#pragma unroll
+    for (int c = 0; c < kAugMaxC; ++c)
+      if (c < g.C) dx[((size_t)n * g.C + c) * HW + px] = S * g2[c] + (1.f - S) * m;
+  }
+}
+
+static int aug_geom(AugGeom& g, int N, int C, int H, int W, int policy) {
+  DEI2I_REQUIRE(N > 0 && N <= 1024 && C > 0 && C <= kAugMaxC && H > 0 && W > 0, "diffaug: bad sizes (C <= %d, N <= 1024)", kAugMaxC);
+  DEI2I_REQUIRE((policy & ~(DEI2I_AUG_COLOR | DEI2I_AUG_TRANSLATION | DEI2I_AUG_CUTOUT)) == 0, "diffaug: unknown policy bits");
+  g.N = N; g.C = C; g.H = H; g.W = W; g.policy = policy;
+  g.ch = (int)(H * 0.5 + 0.5); g.cw = (int)(W * 0.5 + 0.5);  // diffaug.py:56 (ratio 0.5)
+  return 0;
+}
+static int aug_blocks(int H, int W, int N) {
+  int b = (H * W + 1023) / 1024;
+  const int cap = (148 * 8 + N - 1) / N;
+  return b < 1 ? 1 : (b > cap ? cap : b);
+}
+
+}  // namespace dei2i
+
+using namespace dei2i;
+#define ST ((cudaStream_t)stream)
+
+extern "C" size_t dei2i_diffaug_scratch(int N, int H, int W) { return (size_t)N * (aug_blocks(H, W, N) + 1); }
+
+extern "C" int dei2i_diffaug_fwd(const float* x, float* y, const float* params, float* scratch, int N, int C, int H, int W, int policy,
+                                 dei2i_stream stream) {
+  DEI2I_REQUIRE(x && y && params && scratch, "diffaug_fwd: null pointer");
+  AugGeom g;
+  if (int rc = aug_geom(g, N, C, H, W, policy)) return rc;
+  const int nb = aug_blocks(H, W, N);
+  float* mean = scratch + (size_t)N * nb;
+  if (policy & DEI2I_AUG_COLOR) {
+    aug_sum_kernel<false><<<dim3(nb, N), 256, 0, ST>>>(x, params, g, scratch);
+    aug_sum_finish_kernel<<<1, N, 0, ST>>>(scratch, nb, 1.f / ((float)C * H * W), mean);
+    count_launch(2);
+  }
+  aug_fwd_kernel<<<dim3(nb, N), 256, 0, ST>>>(x, y, params, mean, g);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "aug_fwd_kernel");
+}
+
+extern "C" int dei2i_diffaug_bwd(const float* dy, float* dx, const float* params, float* scratch, int N, int C, int H, int W, int policy,
+                                 dei2i_stream stream) {
+  DEI2I_REQUIRE(dy && dx && params && scratch, "diffaug_bwd: null pointer");
+  AugGeom g;
+  if (int rc = aug_geom(g, N, C, H, W, policy)) return rc;
+  const int nb = aug_blocks(H, W, N);
+  float* gmean = scratch + (size_t)N * nb;
+  if (policy & DEI2I_AUG_COLOR) {
+    aug_sum_kernel<true><<<dim3(nb, N), 256, 0, ST>>>(dy, params, g, scratch);
+    aug_sum_finish_kernel<<<1, N, 0, ST>>>(scratch, nb, 1.f / ((float)C * H * W), gmean);
+    count_launch(2);
+  }
+  aug_bwd_kernel<<<dim3(nb, N), 256, 0, ST>>>(dy, dx, params, gmean, g);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "aug_bwd_kernel");
+}

@@ -6,12 +6,14 @@ and network train/eval switching as the reference; the networks are the mirrored
 forward/backward run libdei2i.so, the losses are ``BaseModel._cal_loss`` (fused reduction kernels).  Packed BF16
 weights are built once per loss computation (``Fn.weight_cache``): the 4 G and 2 D passes of a G-step share them.
 
-Not on this path ("next"): the MAE modes, the SEAN / AdaIN style variants, DiffAugment policies
-and the image-grid helpers - they raise NotImplementedError instead of silently falling back to PyTorch.
+``opt.diff_aug`` (DiffAugment policies, utils/diffaug.py) runs on the fused augmentation kernels.
+Not on this path ("next"): the SEAN / AdaIN style variants and the image-grid helpers - they raise
+NotImplementedError instead of silently falling back to PyTorch.
 """
 import torch
 
 from .. import functional as Fn
+from ..utils.diffaug import DiffAugment
 from .base_model import BaseModel
 from .networks.discriminator import DefectGanDiscriminator
 from .networks.generator import DefectGanGenerator
@@ -28,8 +30,6 @@ class DefectGanModel(BaseModel):
         assert image_size & (image_size - 1) == 0, "Image size must be a power of 2"
         if opt.style_norm_block_type != "spade":
             raise NotImplementedError(f"style_norm_block_type={opt.style_norm_block_type!r}: only 'spade' is on the CUDA hot path")
-        if getattr(opt, "diff_aug", ""):
-            raise NotImplementedError("DiffAugment policies are not on the CUDA hot path yet (SURVEY.md 8f n3)")
         self.netG = DefectGanGenerator(opt).to(opt.device, non_blocking=True)
         self.netD = DefectGanDiscriminator(opt).to(opt.device, non_blocking=True)
         if getattr(opt, "is_train", False) or hasattr(opt, "clf_loss_type"):
@@ -76,8 +76,9 @@ class DefectGanModel(BaseModel):
         fake_normals, nm_prob = self.netG(df_data, nm_labels)
         recover_defects, rec_nm_prob = self.netG(fake_normals, df_labels)
 
-        fd_src, fd_cls = self.netD(fake_defects)
-        fn_src, fn_cls = self.netD(fake_normals)
+        policy = getattr(self.opt, "diff_aug", "")  # defectgan_model.py:200-203: the reconstruction terms use the un-augmented images
+        fd_src, fd_cls = self.netD(DiffAugment(fake_defects, policy))
+        fn_src, fn_cls = self.netD(DiffAugment(fake_normals, policy))
 
         gan = _mean([self._cal_loss(fd_src, 1.0, "bce"), self._cal_loss(fn_src, 1.0, "bce")])
         clf = _mean([self._cal_loss(fd_cls, df_labels.view_as(fd_cls), self.clf_loss_type),
@@ -97,6 +98,9 @@ class DefectGanModel(BaseModel):
         with torch.no_grad():
             fake_defects, _ = self.netG(bg_data, df_labels)
             fake_normals, _ = self.netG(df_data, nm_labels)
+        policy = getattr(self.opt, "diff_aug", "")  # defectgan_model.py:266-271: fakes first, then the real defect / background batches
+        fake_defects, fake_normals = DiffAugment(fake_defects, policy), DiffAugment(fake_normals, policy)
+        df_data, bg_data = DiffAugment(df_data, policy), DiffAugment(bg_data, policy)
         fd_src, _ = self.netD(fake_defects.detach_())
         fn_src, _ = self.netD(fake_normals.detach_())
         rd_src, rd_cls = self.netD(df_data)

@@ -708,6 +708,28 @@ def ema_(p, p_ema, beta):
     check(_lib.load().dei2i_ema(_p(p), _p(p_ema), p.numel(), float(beta), _stream()), "dei2i_ema")
 
 
+def diffaug_fwd(x, params, bits: int):
+    """DiffAugment forward on fp32 NCHW [N,C<=4,H,W]; params fp32 [N,8] (utils/diffaug.py), bits = dei2i_aug flags."""
+    _chk_f32(x, "x")
+    _chk_f32(params, "params")
+    n, c, h, w = x.shape
+    lib = _lib.load()
+    y = torch.empty_like(x)
+    scratch = torch.empty(lib.dei2i_diffaug_scratch(n, h, w), dtype=torch.float32, device=x.device)
+    check(lib.dei2i_diffaug_fwd(_p(x), _p(y), _p(params), _p(scratch), n, c, h, w, int(bits), _stream()), "dei2i_diffaug_fwd")
+    return y
+
+
+def diffaug_bwd(dy, params, bits: int):
+    _chk_f32(dy, "dy")
+    n, c, h, w = dy.shape
+    lib = _lib.load()
+    dx = torch.empty_like(dy)
+    scratch = torch.empty(lib.dei2i_diffaug_scratch(n, h, w), dtype=torch.float32, device=dy.device)
+    check(lib.dei2i_diffaug_bwd(_p(dy), _p(dx), _p(params), _p(scratch), n, c, h, w, int(bits), _stream()), "dei2i_diffaug_bwd")
+    return dx
+
+
 def launch_count() -> int:
     return int(_lib.load().dei2i_launch_count())
 

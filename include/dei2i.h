@@ -310,6 +310,19 @@ int dei2i_clamp(float* p, long long n, float lo, float hi, dei2i_stream stream);
 /* p_ema = lerp(p, p_ema, beta): StarGAN-v2 moving_average (stargan-v2/core/solver.py:549-551). */
 int dei2i_ema(const float* p, float* p_ema, long long n, float beta, dei2i_stream stream);
 
+/* ---- DiffAugment (defectGAN/utils/diffaug.py:9-75) on FP32 NCHW images [N, C <= 4, H, W] - between the generator output and the
+ * discriminator input (defectgan_model.py:200-203,266-271).  policy = OR of the flags below, applied in the reference's order
+ * color (brightness, saturation, contrast) -> translation (ratio 1/8) -> cutout (ratio 1/2), fused into one pass (+ one per-image
+ * reduction for the contrast mean).  params fp32 [N, 8], drawn by the caller with the reference's torch calls:
+ * [0] brightness - 0.5, [1] 2 * saturation, [2] contrast + 0.5, [3] translation_x (rows), [4] translation_y (columns),
+ * [5] cutout offset_x, [6] offset_y, [7] unused.  scratch >= dei2i_diffaug_scratch(N, H, W) floats.  bwd: dx = J^T dy. */
+enum dei2i_aug { DEI2I_AUG_COLOR = 1, DEI2I_AUG_TRANSLATION = 2, DEI2I_AUG_CUTOUT = 4 };
+size_t dei2i_diffaug_scratch(int N, int H, int W);
+int dei2i_diffaug_fwd(const float* x, float* y, const float* params, float* scratch, int N, int C, int H, int W, int policy,
+                      dei2i_stream stream);
+int dei2i_diffaug_bwd(const float* dy, float* dx, const float* params, float* scratch, int N, int C, int H, int W, int policy,
+                      dei2i_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -192,3 +192,157 @@ extern "C" int dei2i_diffaug_bwd(const float* dy, float* dx, const float* params
   count_launch();
   return check_cuda(cudaGetLastError(), "aug_bwd_kernel");
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// MAE pre-training input (defectgan_model.py:361-383): masked_imgs = imgs * m + token * (1 - m)  (MaskToken.forward,
+// architecture.py:411-414) with m the shifted patch mask of generate_shifted_mask (utils/util.py:60-71): a coarse Bernoulli
+// grid [N, gh, gw] nearest-upsampled by patch_size and cropped at (h_shift, w_shift), evaluated on the fly from the coarse
+// grid - the full-resolution mask is written once as an output because the caller returns it.
+// token: broadcastable [tn, tc, th, tw] with every extent 1 or full (zero / scalar / vector / position / full / per-image mean).
+namespace dei2i {
+struct MaskGeom {
+  int N, C, H, W, patch, hs, ws, gh, gw;
+  int tn, tc, th, tw;  // token extents
+};
+DEVINL float coarse_mask(const float* __restrict__ coarse, const MaskGeom& g, int n, int i, int j) {
+  return coarse[((size_t)n * g.gh + (i + g.hs) / g.patch) * g.gw + (j + g.ws) / g.patch];
+}
+__global__ void __launch_bounds__(256)
+mask_token_fwd_kernel(const float* __restrict__ img, const float* __restrict__ coarse, const float* __restrict__ token,
+                      float* __restrict__ out, float* __restrict__ mask, MaskGeom g) {
+  const int n = blockIdx.y;
+  const int HW = g.H * g.W;
+  for (int px = blockIdx.x * blockDim.x + threadIdx.x; px < HW; px += gridDim.x * blockDim.x) {
+    const int i = px / g.W, j = px - i * g.W;
+    const float m = coarse_mask(coarse, g, n, i, j);
+    if (mask != nullptr) mask[(size_t)n * HW + px] = m;
+    for (int c = 0; c < g.C; ++c) {
+      float t = 0.f;
+      if (token != nullptr)
+        t = token[(((size_t)(g.tn > 1 ? n : 0) * g.tc + (g.tc > 1 ? c : 0)) * g.th + (g.th > 1 ? i : 0)) * g.tw + (g.tw > 1 ? j : 0)];
+      const size_t o = ((size_t)n * g.C + c) * HW + px;
+      out[o] = img[o] * m + t * (1.f - m);
+    }
+  }
+}
+// per-(n, c) partial sums of img * m over the block's pixels ('mean' token: masked_imgs.mean((2,3)) / mask_ratio, architecture.py:416-418)
+__global__ void __launch_bounds__(256)
+mask_mean_kernel(const float* __restrict__ img, const float* __restrict__ coarse, float* __restrict__ part, MaskGeom g) {
+  __shared__ float sh[32];
+  const int n = blockIdx.y, c = blockIdx.z;
+  const int HW = g.H * g.W;
+  float acc = 0.f;
+  for (int px = blockIdx.x * blockDim.x + threadIdx.x; px < HW; px += gridDim.x * blockDim.x) {
+    const int i = px / g.W, j = px - i * g.W;
+    acc += img[((size_t)n * g.C + c) * HW + px] * coarse_mask(coarse, g, n, i, j);
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int k = 0; k < (int)(blockDim.x >> 5); ++k) t += sh[k];
+    part[((size_t)n * g.C + c) * gridDim.x + blockIdx.x] = t;
+  }
+}
+// gradient of a learnable token: d_token[e] = sum over the broadcast dimensions of dy * (1 - m).  One thread per token element for
+// the spatial tokens (position / full: loops over N [and C]); the scalar / vector tokens go through per-block partial sums.
+__global__ void __launch_bounds__(256)
+mask_token_bwd_spatial_kernel(const float* __restrict__ dy, const float* __restrict__ coarse, float* __restrict__ dtoken, MaskGeom g) {
+  const int HW = g.H * g.W;
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= g.tc * HW) return;
+  const int tc_i = e / HW, px = e - tc_i * HW;
+  const int i = px / g.W, j = px - i * g.W;
+  float acc = 0.f;
+  for (int n = 0; n < g.N; ++n) {
+    const float w = 1.f - coarse_mask(coarse, g, n, i, j);
+    if (w == 0.f) continue;
+    if (g.tc > 1) acc += dy[((size_t)n * g.C + tc_i) * HW + px] * w;
+    else
+      for (int c = 0; c < g.C; ++c) acc += dy[((size_t)n * g.C + c) * HW + px] * w;
+  }
+  dtoken[e] = acc;
+}
+__global__ void __launch_bounds__(256)
+mask_token_bwd_channel_kernel(const float* __restrict__ dy, const float* __restrict__ coarse, float* __restrict__ part, MaskGeom g) {
+  __shared__ float sh[32];
+  const int n = blockIdx.y, c = blockIdx.z;
+  const int HW = g.H * g.W;
+  float acc = 0.f;
+  for (int px = blockIdx.x * blockDim.x + threadIdx.x; px < HW; px += gridDim.x * blockDim.x) {
+    const int i = px / g.W, j = px - i * g.W;
+    acc += dy[((size_t)n * g.C + c) * HW + px] * (1.f - coarse_mask(coarse, g, n, i, j));
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int k = 0; k < (int)(blockDim.x >> 5); ++k) t += sh[k];
+    part[((size_t)c * g.N + n) * gridDim.x + blockIdx.x] = t;  // [C][N * blocks]: channel-major so that a channel's partials are contiguous
+  }
+}
+// out[v] = scale * sum_b part[v * nblk + b]  (fixed order, one thread per output)
+__global__ void rows_sum_kernel(const float* __restrict__ part, int V, int nblk, float scale, float* __restrict__ out) {
+  const int v = blockIdx.x * blockDim.x + threadIdx.x;
+  if (v >= V) return;
+  float t = 0.f;
+  for (int b = 0; b < nblk; ++b) t += part[(size_t)v * nblk + b];
+  out[v] = t * scale;
+}
+static int mask_geom(MaskGeom& g, int N, int C, int H, int W, int patch, int hs, int ws, int gh, int gw, const int* tdims) {
+  DEI2I_REQUIRE(N > 0 && C > 0 && H > 0 && W > 0 && patch > 0 && hs >= 0 && hs < patch && ws >= 0 && ws < patch, "mask_token: bad geometry");
+  DEI2I_REQUIRE((H + hs + patch - 1) / patch <= gh && (W + ws + patch - 1) / patch <= gw, "mask_token: coarse grid %dx%d too small", gh, gw);
+  g.N = N; g.C = C; g.H = H; g.W = W; g.patch = patch; g.hs = hs; g.ws = ws; g.gh = gh; g.gw = gw;
+  g.tn = tdims ? tdims[0] : 1; g.tc = tdims ? tdims[1] : 1; g.th = tdims ? tdims[2] : 1; g.tw = tdims ? tdims[3] : 1;
+  DEI2I_REQUIRE((g.tn == 1 || g.tn == N) && (g.tc == 1 || g.tc == C) && (g.th == 1 || g.th == H) && (g.tw == 1 || g.tw == W),
+                "mask_token: token extents must be 1 or the image's");
+  return 0;
+}
+}  // namespace dei2i
+
+extern "C" size_t dei2i_mask_token_scratch(int N, int C, int H, int W) { return (size_t)N * C * (aug_blocks(H, W, N) + 1); }
+
+extern "C" int dei2i_mask_token_fwd(const float* img, const float* coarse, const float* token, const int* token_dims, float* out,
+                                    float* mask, int N, int C, int H, int W, int patch, int h_shift, int w_shift, int gh, int gw,
+                                    dei2i_stream stream) {
+  DEI2I_REQUIRE(img && coarse && out && (token == nullptr || token_dims != nullptr), "mask_token_fwd: null pointer");
+  MaskGeom g;
+  if (int rc = mask_geom(g, N, C, H, W, patch, h_shift, w_shift, gh, gw, token ? token_dims : nullptr)) return rc;
+  mask_token_fwd_kernel<<<dim3(aug_blocks(H, W, N), N), 256, 0, ST>>>(img, coarse, token, out, mask, g);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "mask_token_fwd_kernel");
+}
+
+/* token_mean[n, c] = mean_{h,w}(img * m) / mask_ratio */
+extern "C" int dei2i_mask_mean(const float* img, const float* coarse, float* token_mean, float* scratch, float mask_ratio, int N, int C,
+                               int H, int W, int patch, int h_shift, int w_shift, int gh, int gw, dei2i_stream stream) {
+  DEI2I_REQUIRE(img && coarse && token_mean && scratch && mask_ratio > 0.f, "mask_mean: bad arguments");
+  MaskGeom g;
+  if (int rc = mask_geom(g, N, C, H, W, patch, h_shift, w_shift, gh, gw, nullptr)) return rc;
+  const int nb = aug_blocks(H, W, N);
+  mask_mean_kernel<<<dim3(nb, N, C), 256, 0, ST>>>(img, coarse, scratch, g);
+  rows_sum_kernel<<<(N * C + 255) / 256, 256, 0, ST>>>(scratch, N * C, nb, 1.f / ((float)H * W * mask_ratio), token_mean);
+  count_launch(2);
+  return check_cuda(cudaGetLastError(), "mask_mean_kernel");
+}
+
+extern "C" int dei2i_mask_token_bwd(const float* dy, const float* coarse, const int* token_dims, float* dtoken, float* scratch, int N,
+                                    int C, int H, int W, int patch, int h_shift, int w_shift, int gh, int gw, dei2i_stream stream) {
+  DEI2I_REQUIRE(dy && coarse && token_dims && dtoken && scratch, "mask_token_bwd: null pointer");
+  MaskGeom g;
+  if (int rc = mask_geom(g, N, C, H, W, patch, h_shift, w_shift, gh, gw, token_dims)) return rc;
+  DEI2I_REQUIRE(g.tn == 1 && ((g.th == 1 && g.tw == 1) || (g.th == H && g.tw == W)), "mask_token_bwd: learnable tokens are [1, 1|C, 1, 1] or [1, 1|C, H, W]");
+  if (g.th > 1) {
+    mask_token_bwd_spatial_kernel<<<(g.tc * H * W + 255) / 256, 256, 0, ST>>>(dy, coarse, dtoken, g);
+    count_launch();
+    return check_cuda(cudaGetLastError(), "mask_token_bwd_spatial_kernel");
+  }
+  const int nb = aug_blocks(H, W, N);
+  mask_token_bwd_channel_kernel<<<dim3(nb, N, C), 256, 0, ST>>>(dy, coarse, scratch, g);
+  if (g.tc > 1) rows_sum_kernel<<<1, 256, 0, ST>>>(scratch, C, N * nb, 1.f, dtoken);
+  else rows_sum_kernel<<<1, 32, 0, ST>>>(scratch, 1, C * N * nb, 1.f, dtoken);
+  count_launch(2);
+  return check_cuda(cudaGetLastError(), "mask_token_bwd_channel_kernel");
+}

@@ -1811,14 +1811,14 @@ __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, 
 // inside a CUDA graph while the learning rate / bias corrections change
 __global__ void adam_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v, long long n,
                                 const float* __restrict__ hyper, float beta1, float beta2, float eps) {
-  const float step_size = __ldg(hyper), inv_sqrt_bc2 = __ldg(hyper + 1);
+  const float step_size = __ldg(hyper), inv_sqrt_bc2 = __ldg(hyper + 1), decay = __ldg(hyper + 2);  // decay = 1 - lr * wd (AdamW), 1 for Adam
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
     const float gi = g[i];
     const float mi = beta1 * m[i] + (1.f - beta1) * gi;
     const float vi = beta2 * v[i] + (1.f - beta2) * gi * gi;
     m[i] = mi;
     v[i] = vi;
-    p[i] -= step_size * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
+    p[i] = p[i] * decay - step_size * mi / (sqrtf(vi) * inv_sqrt_bc2 + eps);
   }
 }
 

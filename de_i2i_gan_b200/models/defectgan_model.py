@@ -6,7 +6,9 @@ and network train/eval switching as the reference; the networks are the mirrored
 forward/backward run libdei2i.so, the losses are ``BaseModel._cal_loss`` (fused reduction kernels).  Packed BF16
 weights are built once per loss computation (``Fn.weight_cache``): the 4 G and 2 D passes of a G-step share them.
 
-``opt.diff_aug`` (DiffAugment policies, utils/diffaug.py) runs on the fused augmentation kernels.
+``opt.diff_aug`` (DiffAugment policies, utils/diffaug.py) runs on the fused augmentation kernels; the MAE pre-training modes
+('mae_generator' / 'mae_discriminator' / 'mae_inference', defectgan_model.py:106-171) run the same networks behind the fused
+mask-token kernel.
 Not on this path ("next"): the SEAN / AdaIN style variants and the image-grid helpers - they raise
 NotImplementedError instead of silently falling back to PyTorch.
 """
@@ -14,7 +16,9 @@ import torch
 
 from .. import functional as Fn
 from ..utils.diffaug import DiffAugment
+from ..utils.util import draw_shifted_mask
 from .base_model import BaseModel
+from .networks.architecture import MaskToken
 from .networks.discriminator import DefectGanDiscriminator
 from .networks.generator import DefectGanGenerator
 
@@ -35,6 +39,8 @@ class DefectGanModel(BaseModel):
         if getattr(opt, "is_train", False) or hasattr(opt, "clf_loss_type"):
             assert opt.clf_loss_type is not None, "clf_loss_type should be initialized in dataset"
             self.clf_loss_type = opt.clf_loss_type
+        if hasattr(opt, "mask_token_type"):  # learnable mask token of the MAE pre-training path (defectgan_model.py:30-32)
+            self.mask_token = MaskToken(opt).to(opt.device, non_blocking=True)
 
     # ------------------------------------------------------------------------------------------------ dispatch
     def __call__(self, mode, data, labels, df_data=None, img_only=False, mask=None):
@@ -42,8 +48,29 @@ class DefectGanModel(BaseModel):
         data, labels = data.to(dev, non_blocking=True), labels.to(dev, non_blocking=True)
         if df_data is not None:
             df_data = df_data.to(dev, non_blocking=True)
-        if mode.startswith("mae"):
-            raise NotImplementedError(f"mode {mode!r}: the MAE pre-training path is not on the CUDA hot path yet (SURVEY.md 8f n1)")
+        if mode.startswith("mae"):  # defectgan_model.py:55-80
+            if mode == "mae_generator":
+                self.netD.eval()
+                self.netG.train()
+                with Fn.weight_cache():
+                    return self._compute_mae_generator_loss(data, labels)
+            if mode == "mae_discriminator":
+                self.netD.train()
+                self.netG.eval()
+                with Fn.weight_cache():
+                    return self._compute_mae_discriminator_loss(data, labels)
+            if mode == "mae_inference":
+                self.netD.eval()
+                self.netG.eval()
+                with torch.no_grad(), Fn.weight_cache():
+                    if self.opt.split_training:
+                        rec_loss, gan_loss, _ = self._compute_mae_inference_loss(data, labels)
+                        _, clf_loss = self._compute_mae_discriminator_loss(data, labels)
+                        return rec_loss, gan_loss, clf_loss
+                    return self._compute_mae_inference_loss(data, labels)
+            if mode == "mae_generate_grid":
+                raise NotImplementedError("mae_generate_grid (TensorBoard image grids, host side) is out of the hot-path scope")
+            raise ValueError(f"|mode {mode}| is invalid")
         if mode == "generator":
             self.netD.eval()
             self.netG.train()
@@ -110,6 +137,58 @@ class DefectGanModel(BaseModel):
         clf = _mean([self._cal_loss(rd_cls, df_labels.view_as(rd_cls), self.clf_loss_type),
                      self._cal_loss(rn_cls, nm_labels.view_as(rn_cls), self.clf_loss_type)])
         return gan, clf
+
+    # ------------------------------------------------------------------------------------------------ MAE pre-training
+    def _repair_mask(self, imgs, labels, mask=None):
+        """defectgan_model.py:361-383 (spade branch): shifted patch mask -> mask token -> generator.  The mask is drawn with the
+        reference's host RNG calls (utils.util.draw_shifted_mask) and blended on the device in one pass (MaskToken.blend)."""
+        if mask is None:
+            coarse, hs, ws = draw_shifted_mask(imgs.size(), self.opt.patch_size, self.opt.mask_ratio)
+            masked_imgs, masks = self.mask_token.blend(imgs, coarse, hs, ws, self.opt.patch_size)
+        else:
+            masks = mask.to(self.opt.device, non_blocking=True)
+            masked_imgs = self.mask_token(imgs, masks)
+        predicted_imgs, _ = self.netG(masked_imgs, self._expand_seg(labels))
+        return predicted_imgs, masks
+
+    def _mae_adv_terms(self, predicted_imgs, labels):
+        fake_src, fake_cls = self.netD(predicted_imgs)
+        return self._cal_loss(fake_src, 1.0, "bce"), self._cal_loss(fake_cls, labels, self.clf_loss_type)
+
+    def _compute_mae_generator_loss(self, imgs, labels):
+        """defectgan_model.py:106-132: L1 reconstruction of the full image from the masked one (+ adversarial / classification terms
+        through the discriminator unless --split_training).  Returns (rec, gan, clf)."""
+        predicted_imgs, _ = self._repair_mask(imgs, labels)
+        rec_loss = self._cal_loss(predicted_imgs, imgs, "l1")
+        if self.opt.split_training:
+            zero = torch.zeros([], device=rec_loss.device)
+            return rec_loss, zero, zero.clone()
+        gan_loss, clf_loss = self._mae_adv_terms(predicted_imgs, labels)
+        return rec_loss, gan_loss, clf_loss
+
+    @torch.no_grad()
+    def _compute_mae_inference_loss(self, imgs, labels):
+        """defectgan_model.py:134-150."""
+        predicted_imgs, _ = self._repair_mask(imgs, labels)
+        rec_loss = self._cal_loss(predicted_imgs, imgs, "l1")
+        if self.opt.split_training:
+            zero = torch.zeros([], device=rec_loss.device)
+            return rec_loss, zero, zero.clone()
+        gan_loss, clf_loss = self._mae_adv_terms(predicted_imgs, labels)
+        return rec_loss, gan_loss, clf_loss
+
+    def _compute_mae_discriminator_loss(self, imgs, labels):
+        """defectgan_model.py:152-171: real images -> classification (+ real / repaired adversarial terms unless --split_training).
+        Returns (gan, clf)."""
+        real_src, real_cls = self.netD(imgs)
+        clf_loss = self._cal_loss(real_cls, labels, self.clf_loss_type)
+        if self.opt.split_training:
+            return torch.zeros([], device=clf_loss.device), clf_loss
+        with torch.no_grad():
+            predicted_imgs, _ = self._repair_mask(imgs, labels)
+        fake_src, _ = self.netD(predicted_imgs.detach_())
+        gan = _mean([self._cal_loss(fake_src, 0.0, "bce"), self._cal_loss(real_src, 1.0, "bce")])
+        return gan, clf_loss
 
     def _compute_clf_loss(self, imgs, labels):
         """defectgan_model.py:294-300."""

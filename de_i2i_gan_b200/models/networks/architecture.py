@@ -402,3 +402,71 @@ class NormResBlock(nn.Module):
 
     def update_alpha(self, epoch, num_epochs):
         pass
+
+
+class _MaskBlend(torch.autograd.Function):
+    """masked = imgs * m + token * (1 - m); differentiable in the (learnable) token only - the images are data."""
+
+    @staticmethod
+    def forward(ctx, imgs, token, coarse, hs, ws, patch):
+        out, mask = Fn.ops.mask_token_fwd(imgs, coarse, hs, ws, patch, token=token)
+        ctx.geo = (hs, ws, patch, tuple(token.shape) if token is not None else None)
+        ctx.save_for_backward(coarse)
+        ctx.mark_non_differentiable(mask)
+        return out, mask
+
+    @staticmethod
+    def backward(ctx, dy, _dmask):
+        (coarse,) = ctx.saved_tensors
+        hs, ws, patch, tshape = ctx.geo
+        dtok = None
+        if tshape is not None and ctx.needs_input_grad[1]:
+            dtok = Fn.ops.mask_token_bwd(dy.contiguous().float(), coarse, hs, ws, patch, tshape)
+        return None, dtok, None, None, None, None
+
+
+class MaskToken(nn.Module):
+    """architecture.py:392-418: replaces the masked-out patches by a token - zero, the per-image mean of the visible pixels
+    ('mean'), or a learnable scalar / per-channel vector / per-position map / full image.  Same parameter name and shapes (state-dict
+    key ``mask_token``).  ``forward(imgs, masks)`` is the reference's formula on a materialised mask (drop-in use);
+    ``blend(imgs, coarse, h_shift, w_shift, patch_size)`` is the fused path used by DefectGanModel._repair_mask: the shifted patch mask
+    is evaluated on the fly from the coarse Bernoulli grid (utils.util.draw_shifted_mask) by dei2i_mask_token_fwd."""
+
+    def __init__(self, opt):
+        super().__init__()
+        self.mask_token_type = opt.mask_token_type
+        self.mask_ratio = opt.mask_ratio
+        if self.mask_token_type in ("zero", "mean"):
+            self.mask_token = 0
+        elif self.mask_token_type == "scalar":
+            self.mask_token = nn.Parameter(torch.zeros(1, 1, 1, 1))
+        elif self.mask_token_type == "vector":
+            self.mask_token = nn.Parameter(torch.zeros(1, opt.input_nc, 1, 1))
+        elif self.mask_token_type == "position":
+            self.mask_token = nn.Parameter(torch.zeros(1, 1, opt.image_size, opt.image_size))
+        elif self.mask_token_type == "full":
+            self.mask_token = nn.Parameter(torch.zeros(1, opt.input_nc, opt.image_size, opt.image_size))
+        else:
+            raise ValueError("Unknown mask token type: {}".format(self.mask_token_type))
+
+    def forward(self, imgs, masks):
+        masked_imgs = imgs * masks
+        if self.mask_token_type == "mean":
+            self._calc_mean_mask_token(masked_imgs)
+        return masked_imgs + self.mask_token * (1 - masks)
+
+    def _calc_mean_mask_token(self, masked_imgs):
+        img_mean = masked_imgs.mean(dim=(2, 3)) / self.mask_ratio
+        self.mask_token = img_mean.reshape(*img_mean.size()[:2], 1, 1)
+
+    def blend(self, imgs, coarse, h_shift, w_shift, patch_size):
+        """-> (masked_imgs, masks [B,1,H,W]) on the fused kernels."""
+        imgs = imgs.contiguous().float()
+        coarse = coarse.to(imgs.device, non_blocking=True).contiguous().float()
+        token = None
+        if self.mask_token_type == "mean":
+            token = Fn.ops.mask_mean(imgs, coarse, h_shift, w_shift, patch_size, self.mask_ratio)
+            self.mask_token = token  # the reference keeps the last per-image mean on the module too (architecture.py:416-418)
+        elif isinstance(self.mask_token, nn.Parameter):
+            token = self.mask_token
+        return _MaskBlend.apply(imgs, token, coarse, int(h_shift), int(w_shift), int(patch_size))

@@ -692,7 +692,8 @@ def adam(p, g, m, v, lr, beta1, beta2, eps, step):
 
 
 def adam_dev(p, g, m, v, hyper, beta1, beta2, eps):
-    """Adam step with hyper = device fp32 [lr / (1 - beta1^t), 1 / sqrt(1 - beta2^t)] (CUDA-graph friendly)."""
+    """Adam / AdamW step with hyper = device fp32 [lr / (1 - beta1^t), 1 / sqrt(1 - beta2^t), 1 - lr * decoupled_weight_decay]
+    (CUDA-graph friendly)."""
     check(_lib.load().dei2i_adam_dev(_p(p), _p(g), _p(m), _p(v), p.numel(), _p(hyper), beta1, beta2, eps, _stream()), "dei2i_adam_dev")
 
 
@@ -706,6 +707,50 @@ def clamp_(p, lo, hi):
 
 def ema_(p, p_ema, beta):
     check(_lib.load().dei2i_ema(_p(p), _p(p_ema), p.numel(), float(beta), _stream()), "dei2i_ema")
+
+
+def _tdims(t):
+    return (C.c_int * 4)(*[int(v) for v in t.shape]) if t is not None else None
+
+
+def mask_token_fwd(img, coarse, h_shift, w_shift, patch, token=None, want_mask=True):
+    """masked = img * m + token * (1 - m) (MaskToken.forward): img fp32 NCHW, coarse fp32 [N,gh,gw] Bernoulli grid, token None or a
+    broadcastable fp32 4-D tensor.  Returns (masked, mask [N,1,H,W] or None)."""
+    _chk_f32(img, "img")
+    _chk_f32(coarse, "coarse")
+    n, c, h, w = img.shape
+    out = torch.empty_like(img)
+    mask = torch.empty(n, 1, h, w, dtype=torch.float32, device=img.device) if want_mask else None
+    if token is not None:
+        _chk_f32(token, "token")
+        assert token.dim() == 4
+    check(_lib.load().dei2i_mask_token_fwd(_p(img), _p(coarse), _p(token), _tdims(token), _p(out), _p(mask), n, c, h, w, int(patch),
+                                           int(h_shift), int(w_shift), coarse.shape[1], coarse.shape[2], _stream()), "dei2i_mask_token_fwd")
+    return out, mask
+
+
+def mask_mean(img, coarse, h_shift, w_shift, patch, mask_ratio):
+    """'mean' mask token: [N,C,1,1] = mean_{h,w}(img * m) / mask_ratio (architecture.py:416-418)."""
+    _chk_f32(img, "img")
+    n, c, h, w = img.shape
+    lib = _lib.load()
+    tok = torch.empty(n, c, 1, 1, dtype=torch.float32, device=img.device)
+    scratch = torch.empty(lib.dei2i_mask_token_scratch(n, c, h, w), dtype=torch.float32, device=img.device)
+    check(lib.dei2i_mask_mean(_p(img), _p(coarse), _p(tok), _p(scratch), float(mask_ratio), n, c, h, w, int(patch), int(h_shift),
+                              int(w_shift), coarse.shape[1], coarse.shape[2], _stream()), "dei2i_mask_mean")
+    return tok
+
+
+def mask_token_bwd(dy, coarse, h_shift, w_shift, patch, token_shape):
+    """Gradient of a learnable mask token of shape ``token_shape`` ([1,1|C,1,1] or [1,1|C,H,W])."""
+    _chk_f32(dy, "dy")
+    n, c, h, w = dy.shape
+    lib = _lib.load()
+    dtok = torch.empty(tuple(token_shape), dtype=torch.float32, device=dy.device)
+    scratch = torch.empty(lib.dei2i_mask_token_scratch(n, c, h, w), dtype=torch.float32, device=dy.device)
+    check(lib.dei2i_mask_token_bwd(_p(dy), _p(coarse), (C.c_int * 4)(*[int(v) for v in token_shape]), _p(dtok), _p(scratch), n, c, h, w,
+                                   int(patch), int(h_shift), int(w_shift), coarse.shape[1], coarse.shape[2], _stream()), "dei2i_mask_token_bwd")
+    return dtok
 
 
 def diffaug_fwd(x, params, bits: int):

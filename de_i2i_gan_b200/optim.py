@@ -23,12 +23,25 @@ def _align(n: int, a: int = 64) -> int:
 
 
 class FlatAdam(torch.optim.Optimizer):
-    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0):
-        defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay)
+    def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0, decoupled=False):
+        """decoupled=True: torch.optim.AdamW semantics (p *= 1 - lr * weight_decay before the Adam update) instead of Adam's L2 term."""
+        defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=weight_decay, decoupled=decoupled)
         super().__init__(params, defaults)
         self._flat = []  # per group: dict(p=, g=, m=, v=, step=)
         for group in self.param_groups:
             self._flat.append(self._flatten(group["params"]))
+
+    def add_param_group(self, param_group):
+        """torch.optim.Optimizer.add_param_group + a flat buffer for the new group (MAETrainer adds the mask token's parameters to
+        the generator's optimizer, mae_trainer.py:28).  A group without parameters (non-learnable token types) is ignored."""
+        params = param_group["params"]
+        params = [params] if isinstance(params, torch.Tensor) else list(params)
+        if not params:
+            return
+        param_group = dict(param_group, params=params)
+        super().add_param_group(param_group)
+        if hasattr(self, "_flat") and len(self._flat) < len(self.param_groups):
+            self._flat.append(self._flatten(self.param_groups[-1]["params"]))
 
     @staticmethod
     def _flatten(params: List[torch.Tensor]):
@@ -92,9 +105,10 @@ class FlatAdam(torch.optim.Optimizer):
             b1, b2 = group["betas"]
             t = f["step"]
             if "hyper" not in f:
-                f["hyper"] = torch.zeros(2, dtype=torch.float32, device=f["p"].device)
-            # pageable source: the runtime stages the 8 bytes before returning, so the host may run ahead safely
-            f["hyper"].copy_(torch.tensor([float(group["lr"]) / (1.0 - b1 ** t), 1.0 / (1.0 - b2 ** t) ** 0.5], dtype=torch.float32))
+                f["hyper"] = torch.zeros(3, dtype=torch.float32, device=f["p"].device)
+            decay = 1.0 - float(group["lr"]) * float(group.get("weight_decay", 0.0)) if group.get("decoupled", False) else 1.0
+            # pageable source: the runtime stages the 12 bytes before returning, so the host may run ahead safely
+            f["hyper"].copy_(torch.tensor([float(group["lr"]) / (1.0 - b1 ** t), 1.0 / (1.0 - b2 ** t) ** 0.5, decay], dtype=torch.float32))
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -108,7 +122,7 @@ class FlatAdam(torch.optim.Optimizer):
             self.advance()
         for group, f in zip(self.param_groups, self._flat):
             b1, b2 = group["betas"]
-            if group.get("weight_decay", 0.0):  # torch.optim.Adam: grad += wd * param (StarGAN-v2 solver.py:72-80)
+            if group.get("weight_decay", 0.0) and not group.get("decoupled", False):  # torch.optim.Adam: grad += wd * param (StarGAN-v2 solver.py:72-80)
                 f["g"].add_(f["p"], alpha=float(group["weight_decay"]))
             ops.adam_dev(f["p"], f["g"], f["m"], f["v"], f["hyper"], float(b1), float(b2), float(group["eps"]))
         return loss

@@ -59,6 +59,22 @@ def wgan_options(**over) -> SimpleNamespace:
     return opt
 
 
+def pretrain_options(**over) -> SimpleNamespace:
+    """PreTrainOptions (options/defectgan_options.py:143-189): the MAE pre-training namespace - batch 32, AdamW lr 1.5e-4, cosine
+    schedule (lr_decay 0.05), loss weights [rec, cls_d, cls_g] = [10, 3, 1], mask ratio 0.75, patch 8, 'position' mask token."""
+    kw = dict(batch_size=32, save_latest_freq=300, num_display_images=4, save_img_freq=1, optimizer="adamw", num_epochs=200,
+              lr=[1.5e-4], scheduler="cos", lr_decay=0.05, loss_weight=[10, 3, 1], num_critics=1)
+    extra = dict(mask_ratio=0.75, split_training=False, mask_token_type="position", patch_size=8)
+    for k in list(over):
+        if k in extra:
+            extra[k] = over.pop(k)
+    kw.update(over)
+    opt = train_options(**kw)
+    for k, v in extra.items():
+        setattr(opt, k, v)
+    return opt
+
+
 def readme_recipe(**over) -> SimpleNamespace:
     """defectGAN/README.md:21-24: the documented DefectGAN training recipe adds --add_noise --use_spectral."""
     kw = dict(add_noise=True, use_spectral=True)

@@ -57,8 +57,10 @@ class BaseTrainer:
             make = lambda ps, lr: FlatAdam(ps, lr=lr, betas=(0.5, 0.999))  # noqa: E731  base_trainer.py:79-81
         elif opt.optimizer == "rmsprop":
             make = lambda ps, lr: FlatRMSprop(ps, lr=lr)  # noqa: E731
-        elif opt.optimizer in ("sgd", "adamw"):
-            raise NotImplementedError(f"optimizer {opt.optimizer!r} has no CUDA kernel on this path (adam | rmsprop)")
+        elif opt.optimizer == "adamw":  # base_trainer.py:82-84: optim.AdamW(betas=(0.9, 0.95)), torch's default weight_decay 1e-2
+            make = lambda ps, lr: FlatAdam(ps, lr=lr, betas=(0.9, 0.95), weight_decay=1e-2, decoupled=True)  # noqa: E731
+        elif opt.optimizer == "sgd":
+            raise NotImplementedError("optimizer 'sgd' has no CUDA kernel on this path (adam | adamw | rmsprop)")
         else:
             raise NameError(f"optimizer named {opt.optimizer} not defined")
         self.optimizers, self.reducers = {}, {}

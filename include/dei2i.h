@@ -296,8 +296,9 @@ int dei2i_ce_soft(const float* logits, const float* targets, int B, int C, float
 int dei2i_adam(float* p, const float* g, float* m, float* v, long long n, float lr, float beta1, float beta2,
                float eps, int step, dei2i_stream stream);
 
-/* The same step with the two per-step scalars in DEVICE memory: hyper[0] = lr / (1 - beta1^step),
- * hyper[1] = 1 / sqrt(1 - beta2^step).  The launch arguments are then constant from step to step, so the optimizer step
+/* The same step with the per-step scalars in DEVICE memory: hyper[0] = lr / (1 - beta1^step),
+ * hyper[1] = 1 / sqrt(1 - beta2^step), hyper[2] = 1 - lr * weight_decay for torch.optim.AdamW's decoupled decay (base_trainer.py:
+ * 82-84, the MAE pre-training default) or 1 for Adam.  The launch arguments are then constant from step to step, so the optimizer step
  * can be part of a captured CUDA graph of the whole D-step / G-step (trainers/defectgan_trainer.py:138-180). */
 int dei2i_adam_dev(float* p, const float* g, float* m, float* v, long long n, const float* hyper, float beta1, float beta2,
                    float eps, dei2i_stream stream);
@@ -322,6 +323,20 @@ int dei2i_diffaug_fwd(const float* x, float* y, const float* params, float* scra
                       dei2i_stream stream);
 int dei2i_diffaug_bwd(const float* dy, float* dx, const float* params, float* scratch, int N, int C, int H, int W, int policy,
                       dei2i_stream stream);
+
+/* ---- MAE pre-training input (defectgan_model.py:361-383; MaskToken, architecture.py:392-418; generate_shifted_mask, utils/util.py:60-71)
+ * masked = img * m + token * (1 - m) on FP32 NCHW images, m evaluated on the fly from the coarse Bernoulli grid `coarse` [N, gh, gw]
+ * (nearest-upsampled by `patch`, cropped at (h_shift, w_shift)); `mask` (optional, [N,1,H,W]) receives m.  token: NULL (zero token) or a
+ * broadcastable tensor of extents token_dims[4] (host int array), each 1 or the image's.  dei2i_mask_mean: the 'mean' token
+ * [N, C] = mean_{h,w}(img * m) / mask_ratio.  dei2i_mask_token_bwd: gradient of a learnable token ([1,1|C,1,1] or [1,1|C,H,W]).
+ * scratch >= dei2i_mask_token_scratch(N, C, H, W) floats. */
+size_t dei2i_mask_token_scratch(int N, int C, int H, int W);
+int dei2i_mask_token_fwd(const float* img, const float* coarse, const float* token, const int* token_dims, float* out, float* mask,
+                         int N, int C, int H, int W, int patch, int h_shift, int w_shift, int gh, int gw, dei2i_stream stream);
+int dei2i_mask_mean(const float* img, const float* coarse, float* token_mean, float* scratch, float mask_ratio, int N, int C, int H,
+                    int W, int patch, int h_shift, int w_shift, int gh, int gw, dei2i_stream stream);
+int dei2i_mask_token_bwd(const float* dy, const float* coarse, const int* token_dims, float* dtoken, float* scratch, int N, int C, int H,
+                         int W, int patch, int h_shift, int w_shift, int gh, int gw, dei2i_stream stream);
 
 #ifdef __cplusplus
 }

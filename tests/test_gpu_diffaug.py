@@ -47,12 +47,12 @@ def test_defectgan_model_with_diff_aug_steps():
     from de_i2i_gan_b200 import options
     from de_i2i_gan_b200.models.defectgan_model import DefectGanModel
     from de_i2i_gan_b200.synthetic import synthetic_batch
-    opt = options.readme_recipe(image_size=64, batch_size=2, ngf=16, ndf=8, hidden_nc=32, diff_aug="color,translation,cutout")
+    opt = options.readme_recipe(image_size=128, batch_size=2, ngf=16, ndf=8, hidden_nc=32, diff_aug="color,translation,cutout")
     opt.device = torch.device("cuda", 0)
     torch.manual_seed(1)
     model = DefectGanModel(opt)
     model.init_weights()
-    bg, labels, df = [t.cuda() for t in synthetic_batch(2, 64, seed=0)]
+    bg, labels, df = [t.cuda() for t in synthetic_batch(2, 128, seed=0)]
     gan, clf = model("discriminator", bg, labels, df)
     (gan + clf).backward()
     assert all(torch.isfinite(p.grad).all() for p in model.netD.parameters() if p.grad is not None)

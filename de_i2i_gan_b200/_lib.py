@@ -88,6 +88,24 @@ SIGNATURES = {
     "dei2i_rmsprop": (_I, [_P, _P, _P, _LL, _F, _F, _F, _P]),
     "dei2i_clamp": (_I, [_P, _LL, _F, _F, _P]),
     "dei2i_ema": (_I, [_P, _P, _LL, _F, _P]),
+    "dei2i_pack_weight_f32": (_I, [_P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),
+    "dei2i_conv2d_fwd_f32": (_I, [_P, _P, _P, C.POINTER(ConvGeom), C.POINTER(ConvEpilogue), _P]),
+    "dei2i_conv2d_dgrad_f32": (_I, [_P, _P, _P, C.POINTER(ConvGeom), _P, _P]),
+    "dei2i_conv2d_wgrad_f32_workspace": (_SZ, [C.POINTER(ConvGeom)]),
+    "dei2i_conv2d_wgrad_f32": (_I, [_P, _P, _P, _I, _F, C.POINTER(ConvGeom), _P, _P, _P, _P, _P, _SZ, _P]),
+    "dei2i_nchw_to_nhwc_f32": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_nhwc_to_nchw_f32": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_channel_stats_f32": (_I, [_P, _I, _I, _I, _I, _P, _P]),
+    "dei2i_bn_fwd_f32": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _I, _P]),
+    "dei2i_bn_bwd_f32": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_spade_cls_fwd_f32": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _I, _P]),
+    "dei2i_spade_cls_bwd_f32": (_I, [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _I, _P]),
+    "dei2i_spade_fwd_f32": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
+    "dei2i_reflect_pad_f32": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_reflect_fold_f32": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_act_bwd_f32": (_I, [_P, _P, _P, _P, _LL, _I, _I, _P]),
+    "dei2i_noise_wgrad_f32": (_I, [_P, _P, _P, _LL, _I, _I, _F, _P]),
+    "dei2i_compose_bwd_f32": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "dei2i_mask_token_scratch": (_SZ, [_I, _I, _I, _I]),
     "dei2i_mask_token_fwd": (_I, [_P, _P, _P, C.POINTER(C.c_int), _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P]),
     "dei2i_mask_mean": (_I, [_P, _P, _P, _P, _F, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P]),

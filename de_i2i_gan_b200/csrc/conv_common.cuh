@@ -112,6 +112,10 @@ void wgrad_tma_plan(TmaWgradParams& p);
 int run_wgrad_tma(const void* x, int N, int H, int W, int C, const void* dy, int cout_ld, TmaWgradParams& p, int upper,
                   int upper_w, cudaStream_t st);
 
+// conv_igemm.cu
+int wgrad_second_pass(float* partial, int splits, const dei2i_conv_geom* g, int Cin_real, int Kf, float* dw, float beta,
+                      const float* sn_w_orig, const float* sn_u, const float* sn_v, const float* sn_inv_sigma, cudaStream_t st);
+
 // conv_skinny.cu
 int wgrad_narrow_splits(int Kreal, int Cout_ld, long long M);
 int run_wgrad_narrow(const Gather& g, const void* dy, int Cout, int Cout_ld, int Kf, float* partial, int splits, cudaStream_t st);

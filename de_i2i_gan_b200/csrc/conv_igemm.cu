@@ -629,6 +629,45 @@ static bool tma_applicable(const dei2i_conv_geom* g, int k_channels, long long M
   return true;
 }
 
+// Second pass of every weight gradient (shared by the BF16 tcgen05 kernels and the FP32 path): sums the split partials
+// [splits, Cout, Kf] in a fixed order, re-lays [co][tap][ci] -> [co][ci][tap], and applies the spectral-norm backward
+// dW_orig = (dW - <dW, W/sigma> u v^T) / sigma when the four sn pointers are given.  partial needs 1024 floats of slack at its end.
+int wgrad_second_pass(float* partial, int splits, const dei2i_conv_geom* g, int Cin_real, int Kf, float* dw, float beta,
+                      const float* sn_w_orig, const float* sn_u, const float* sn_v, const float* sn_inv_sigma, cudaStream_t st) {
+  const int taps = g->kh * g->kw;
+  float* dot = partial + (size_t)splits * g->Cout * Kf;  // [0] = <dW, W/sigma>, [1..] block sums
+  const long long total = (long long)g->Cout * Cin_real * taps;
+  // reduction tile width (input channels): 256 when that still leaves >= 4 blocks per SM and the tile fits 48 KB, else 64 / 16
+  const bool red_vec = Cin_real % 4 == 0 && (((uintptr_t)dw | (uintptr_t)sn_v | (uintptr_t)sn_w_orig) & 15) == 0;
+  int red_sh = 4;
+  if (red_vec && Cin_real % 256 == 0 && (long long)g->Cout * (Cin_real / 256) >= 4 * 148 && taps * 260 * 4 <= 48 * 1024) red_sh = 8;
+  else if ((long long)g->Cout * ((Cin_real + 63) / 64) >= 2 * 148) red_sh = 6;
+  const int red_ci = 1 << red_sh;
+  const int red_tiles = g->Cout * ((Cin_real + red_ci - 1) / red_ci);
+  const size_t red_smem = (size_t)taps * (red_ci + 4) * sizeof(float);
+  DEI2I_REQUIRE(red_smem <= 48 * 1024, "conv2d_wgrad: filter too large for the reduction tile");
+  if (sn_u != nullptr) {
+    const int nb = red_tiles < 1023 ? red_tiles : 1023;
+    if (red_vec)
+      wgrad_dot_kernel<true><<<nb, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, sn_w_orig, sn_inv_sigma,
+                                                        dot + 1, red_sh);
+    else
+      wgrad_dot_kernel<false><<<nb, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, sn_w_orig, sn_inv_sigma,
+                                                         dot + 1, red_sh);
+    sum_blocks_kernel<<<1, 256, 0, st>>>(dot + 1, nb, dot);
+    count_launch(2);
+    DEI2I_CUDA(cudaGetLastError());
+  }
+  if (red_vec)
+    wgrad_reduce_kernel<true><<<(unsigned)red_tiles, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, dw, beta,
+                                                                          dot, sn_u, sn_v, sn_inv_sigma, red_sh);
+  else
+    wgrad_reduce_kernel<false><<<(unsigned)red_tiles, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, dw, beta,
+                                                                           dot, sn_u, sn_v, sn_inv_sigma, red_sh);
+  count_launch();
+  return check_cuda(cudaGetLastError(), "wgrad_reduce_kernel launch");
+}
+
 }  // namespace dei2i
 
 using namespace dei2i;
@@ -901,35 +940,5 @@ extern "C" int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int 
     }
     if (rc) return rc;
   }
-  float* dot = partial + (size_t)splits * g->Cout * Kf;  // [0] = <dW, W/sigma>, [1..] block sums
-  const long long total = (long long)g->Cout * Cin_real * taps;
-  // reduction tile width (input channels): 256 when that still leaves >= 4 blocks per SM and the tile fits 48 KB, else 64 / 16
-  const bool red_vec = Cin_real % 4 == 0 && (((uintptr_t)dw | (uintptr_t)sn_v | (uintptr_t)sn_w_orig) & 15) == 0;
-  int red_sh = 4;
-  if (red_vec && Cin_real % 256 == 0 && (long long)g->Cout * (Cin_real / 256) >= 4 * 148 && taps * 260 * 4 <= 48 * 1024) red_sh = 8;
-  else if ((long long)g->Cout * ((Cin_real + 63) / 64) >= 2 * 148) red_sh = 6;
-  const int red_ci = 1 << red_sh;
-  const int red_tiles = g->Cout * ((Cin_real + red_ci - 1) / red_ci);
-  const size_t red_smem = (size_t)taps * (red_ci + 4) * sizeof(float);
-  DEI2I_REQUIRE(red_smem <= 48 * 1024, "conv2d_wgrad: filter too large for the reduction tile");
-  if (sn_u != nullptr) {
-    const int nb = red_tiles < 1023 ? red_tiles : 1023;
-    if (red_vec)
-      wgrad_dot_kernel<true><<<nb, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, sn_w_orig, sn_inv_sigma,
-                                                        dot + 1, red_sh);
-    else
-      wgrad_dot_kernel<false><<<nb, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, sn_w_orig, sn_inv_sigma,
-                                                         dot + 1, red_sh);
-    sum_blocks_kernel<<<1, 256, 0, st>>>(dot + 1, nb, dot);
-    count_launch(2);
-    DEI2I_CUDA(cudaGetLastError());
-  }
-  if (red_vec)
-    wgrad_reduce_kernel<true><<<(unsigned)red_tiles, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, dw, beta,
-                                                                          dot, sn_u, sn_v, sn_inv_sigma, red_sh);
-  else
-    wgrad_reduce_kernel<false><<<(unsigned)red_tiles, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, dw, beta,
-                                                                           dot, sn_u, sn_v, sn_inv_sigma, red_sh);
-  count_launch();
-  return check_cuda(cudaGetLastError(), "wgrad_reduce_kernel launch");
+  return wgrad_second_pass(partial, splits, g, Cin_real, Kf, dw, beta, sn_w_orig, sn_u, sn_v, sn_inv_sigma, st);
 }

@@ -1686,8 +1686,9 @@ __global__ void compose_fwd_kernel(const float* __restrict__ hd, const float* __
   prob[i] = pr;
   if (out_nhwc != nullptr) *reinterpret_cast<uint4*>(out_nhwc + i * 8) = pack8(o);
 }
+template <bool F32OUT>
 __global__ void compose_bwd_kernel(const float* __restrict__ hd, const float* __restrict__ x, const float* __restrict__ dout,
-                                   const float* __restrict__ dprob, __nv_bfloat16* __restrict__ dhd, float* __restrict__ dx, int N,
+                                   const float* __restrict__ dprob, void* __restrict__ dhd_, float* __restrict__ dx, int N,
                                    int HW, int cycle_gan) {
   const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= (long long)N * HW) return;
@@ -1713,7 +1714,13 @@ __global__ void compose_bwd_kernel(const float* __restrict__ hd, const float* __
     }
   }
   o[3] = dp * pr * (1.f - pr);
-  *reinterpret_cast<uint4*>(dhd + i * 8) = pack8(o);
+  if (F32OUT) {
+    float* dhd = reinterpret_cast<float*>(dhd_);
+    *reinterpret_cast<float4*>(dhd + i * 8) = make_float4(o[0], o[1], o[2], o[3]);
+    *reinterpret_cast<float4*>(dhd + i * 8 + 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+  } else {
+    *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(dhd_) + i * 8) = pack8(o);
+  }
 }
 
 // ------------------------------------------------------------------------------------------ losses
@@ -2300,7 +2307,13 @@ extern "C" int dei2i_compose_fwd(const float* hd, const float* x, float* out, fl
 extern "C" int dei2i_compose_bwd(const float* hd, const float* x, const float* dout, const float* dprob, void* dhd, float* dx, int N,
                                  int H, int W, int cycle_gan, dei2i_stream stream) {
   DEI2I_REQUIRE(hd && x && dhd, "compose_bwd: null pointer");
-  compose_bwd_kernel<<<nblocks((long long)N * H * W, 256), 256, 0, ST>>>(hd, x, dout, dprob, (__nv_bfloat16*)dhd, dx, N, H * W, cycle_gan);
+  compose_bwd_kernel<false><<<nblocks((long long)N * H * W, 256), 256, 0, ST>>>(hd, x, dout, dprob, dhd, dx, N, H * W, cycle_gan);
+  return LAUNCH_OK("compose_bwd_kernel");
+}
+extern "C" int dei2i_compose_bwd_f32(const float* hd, const float* x, const float* dout, const float* dprob, float* dhd, float* dx, int N,
+                                     int H, int W, int cycle_gan, dei2i_stream stream) {
+  DEI2I_REQUIRE(hd && x && dhd, "compose_bwd_f32: null pointer");
+  compose_bwd_kernel<true><<<nblocks((long long)N * H * W, 256), 256, 0, ST>>>(hd, x, dout, dprob, dhd, dx, N, H * W, cycle_gan);
   return LAUNCH_OK("compose_bwd_kernel");
 }
 

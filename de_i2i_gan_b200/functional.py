@@ -204,14 +204,14 @@ class _Conv(Function):
         x, y = ctx.saved_tensors
         wts, spec = ctx.wts, ctx.spec
         has_bias, has_noise, has_res = ctx.has
-        if dy.dtype != torch.bfloat16:
-            dy = dy.to(torch.bfloat16)
+        if dy.dtype != ops.ACT_DTYPE:
+            dy = dy.to(ops.ACT_DTYPE)
         dy = dy.contiguous()
         d_bias = None
         need_bias = has_bias and ctx.needs_input_grad[2]
         pad = ctx.out_pad
         if ctx.act or need_bias:
-            yb = y if (y is None or y.dtype == torch.bfloat16) else y.to(torch.bfloat16)
+            yb = y if (y is None or y.dtype == ops.ACT_DTYPE) else y.to(ops.ACT_DTYPE)
             dz, d_bias = ops.act_bwd(yb, dy, ctx.act, want_dx=bool(ctx.act) or pad > 0, want_bias_grad=need_bias, pad=pad)
             if ctx.act or pad:
                 dy = dz
@@ -264,8 +264,8 @@ def conv(x: Nhwc, conv_mod, spec: ConvSpec, training: bool, bias=None, act=None,
 
 
 def rowpack_applicable(spec: ConvSpec) -> bool:
-    """Few-channel wide-filter stride-1 'same' reflect convolutions (the generator stem 3->64 7x7)."""
-    return (spec.cin <= 8 and 1 < spec.kw_ <= 8 and spec.stride == 1 and spec.pad_mode == "reflect"
+    """Few-channel wide-filter stride-1 'same' reflect convolutions (the generator stem 3->64 7x7); BF16 path only."""
+    return (ops.ACT_DTYPE == torch.bfloat16 and spec.cin <= 8 and 1 < spec.kw_ <= 8 and spec.stride == 1 and spec.pad_mode == "reflect"
             and 2 * spec.pad == spec.kh - 1 and spec.kh == spec.kw_ and spec.cout_ld >= 64)
 
 
@@ -358,7 +358,7 @@ def linear(x: torch.Tensor, lin: torch.nn.Linear, act=None) -> torch.Tensor:
     spec = ConvSpec(cin, cout, 1)
     w4 = lin.weight.view(cout, cin, 1, 1)
     wts = Weights(*_pack(w4, spec), None, None)
-    xb = x.to(torch.bfloat16)
+    xb = x.to(ops.ACT_DTYPE)
     if spec.cin_ld != cin:
         xb = torch.nn.functional.pad(xb, (0, spec.cin_ld - cin))
     y = _Conv.apply(xb.reshape(x.shape[0], 1, 1, spec.cin_ld).contiguous(), w4, lin.bias, None, None, wts, spec, act, None, True, None)
@@ -386,8 +386,8 @@ class _ConvCat(Function):
     def backward(ctx, dy):
         (x,) = ctx.saved_tensors
         spec, ca = ctx.spec, ctx.ca
-        if dy.dtype != torch.bfloat16:
-            dy = dy.to(torch.bfloat16)
+        if dy.dtype != ops.ACT_DTYPE:
+            dy = dy.to(ops.ACT_DTYPE)
         dy = dy.contiguous()
         dba = dbb = None
         if ctx.has_bias:
@@ -493,7 +493,7 @@ class _SpadeCls(Function):
     def backward(ctx, dout):
         x, gb5, out, mr = ctx.saved_tensors
         dgb5, dx = ops.spade_cls_bwd(x, gb5, out, dout.contiguous(), mr, ctx.up, ctx.relu, ctx.out_pad)
-        return dx, dgb5.to(torch.bfloat16), None, None, None, None, None
+        return dx, dgb5.to(ops.ACT_DTYPE), None, None, None, None, None
 
 
 def spade_modulate_cls(x: Nhwc, gb5: Nhwc, up=1, relu=True, eps=1e-5, out_pad=0) -> Nhwc:
@@ -689,8 +689,8 @@ class _ConvL(Function):
     def backward(ctx, dy):
         x, w = ctx.saved_tensors
         spec = ctx.spec
-        if dy.dtype != torch.bfloat16:
-            dy = dy.to(torch.bfloat16)
+        if dy.dtype != ops.ACT_DTYPE:
+            dy = dy.to(ops.ACT_DTYPE)
         dx = _DgradL.apply(dy, w, spec, (x.shape[1], x.shape[2])) if ctx.needs_input_grad[0] else None
         dw = db = None
         if _input_grad_only:

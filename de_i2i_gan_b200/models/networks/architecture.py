@@ -175,8 +175,8 @@ class ConvBlock(nn.Module):
             # no norm layer: the convolution epilogue itself writes the next convolution's reflect padding (granted on the TMA kernel)
             y = Fn.conv(xa, conv, spec, conv.training, bias=conv.bias, act=self._act,
                         out_fp32=self._act in ("tanh", "sigmoid"), out_pad=out_pad)
-            if y.t.dtype != torch.bfloat16 and not plain:
-                y = Fn.Nhwc(y.t.to(torch.bfloat16), y.c)
+            if y.t.dtype != Fn.ops.ACT_DTYPE and not plain:
+                y = Fn.Nhwc(y.t.to(Fn.ops.ACT_DTYPE), y.c)
         else:
             y = Fn.conv(xa, conv, spec, conv.training, bias=conv.bias, want_stats=_bn_stats(self._norm))
             y = Fn.batch_norm(y, self._norm, act=self._act, residual=residual, out_pad=out_pad)
@@ -251,7 +251,7 @@ class DeConvBlock(nn.Module):
             fp32 = self._act in ("tanh", "sigmoid")
             y = Fn.conv(xa, conv, self._spec, conv.training, bias=conv.bias, noise=noise, noise_w=nw, act=self._act, out_fp32=fp32)
             if fp32 and not plain:
-                y = Fn.Nhwc(y.t.to(torch.bfloat16), y.c)
+                y = Fn.Nhwc(y.t.to(Fn.ops.ACT_DTYPE), y.c)
         else:
             y = Fn.conv(xa, conv, self._spec, conv.training, bias=conv.bias, noise=noise, noise_w=nw)
             y = Fn.batch_norm(y, self.de_conv_block[self._norm_idx], act=self._act)

@@ -1,6 +1,7 @@
 """Thin torch-tensor wrappers over the C ABI (include/dei2i.h).  PyTorch is plumbing here: device memory,
 streams.  Activations are BF16 tensors of shape [N, H, W, C] (NHWC, contiguous, C a multiple of 8)."""
 import ctypes as C
+import os
 from dataclasses import dataclass
 
 import torch
@@ -9,6 +10,24 @@ from . import _lib
 from ._lib import ConvEpilogue, ConvGeom, check
 
 ACT = {None: 0, "none": 0, "leaky_relu": 1, "relu": 2, "tanh": 3, "sigmoid": 4}
+
+# Activation storage type of the path.  bf16 (default): the production kernels (tcgen05 / TMA, BF16 storage, FP32 accumulation).
+# fp32 (DEI2I_KERNELS=fp32 or set_precision('fp32')): the FP32-parity path of csrc/fp32_path.cu - exact FP32 arithmetic on FP32 NHWC
+# activations, for comparing with the FP32 reference at the north-star's 1e-3 tolerance.  Every wrapper below dispatches on the dtype
+# of the activation it is given; ACT_DTYPE decides what the model-edge converters and the weight packer produce.
+ACT_DTYPE = torch.float32 if os.environ.get("DEI2I_KERNELS", "bf16").lower() in ("fp32", "f32") else torch.bfloat16
+
+
+def set_precision(name: str):
+    """'bf16' | 'fp32' - returns the previous name.  Switch only between loss computations (packed weights are cached per scope)."""
+    global ACT_DTYPE
+    old = "fp32" if ACT_DTYPE == torch.float32 else "bf16"
+    ACT_DTYPE = {"bf16": torch.bfloat16, "fp32": torch.float32, "f32": torch.float32}[name.lower()]
+    return old
+
+
+def is_f32(t) -> bool:
+    return t.dtype == torch.float32
 PAD = {"zeros": 0, "reflect": 1}
 
 
@@ -58,8 +77,8 @@ def _p(t):
 
 
 def _chk_act(t: torch.Tensor, name: str):
-    if not (t.is_cuda and t.dtype == torch.bfloat16 and t.is_contiguous() and t.dim() == 4 and t.shape[3] % 8 == 0):
-        raise ValueError(f"{name}: expected a contiguous CUDA bf16 [N,H,W,C%8==0] tensor, got {t.dtype} {tuple(t.shape)}")
+    if not (t.is_cuda and t.dtype in (torch.bfloat16, torch.float32) and t.is_contiguous() and t.dim() == 4 and t.shape[3] % 8 == 0):
+        raise ValueError(f"{name}: expected a contiguous CUDA bf16 (or fp32-path) [N,H,W,C%8==0] tensor, got {t.dtype} {tuple(t.shape)}")
 
 
 def _chk_f32(t: torch.Tensor, name: str):
@@ -130,9 +149,14 @@ def pack_weight(w: torch.Tensor, spec: ConvSpec, inv_sigma: torch.Tensor = None,
     """fp32 [Cout,Cin,kh,kw] (optionally scaled by the device scalar inv_sigma) -> packed bf16 GEMM operands."""
     _chk_f32(w, "w")
     assert tuple(w.shape) == (spec.cout, spec.cin, spec.kh, spec.kw_), (w.shape, spec)
-    w_fwd = torch.empty(spec.cout, spec.kf, dtype=torch.bfloat16, device=w.device)
-    w_dg = torch.empty(spec.cin_ld, spec.kd, dtype=torch.bfloat16, device=w.device) if need_dgrad else None
+    w_fwd = torch.empty(spec.cout, spec.kf, dtype=ACT_DTYPE, device=w.device)
+    w_dg = torch.empty(spec.cin_ld, spec.kd, dtype=ACT_DTYPE, device=w.device) if need_dgrad else None
     lib = _lib.load()
+    if ACT_DTYPE == torch.float32:
+        assert inv_sigma is None
+        check(lib.dei2i_pack_weight_f32(_p(w), spec.cout, spec.cin, spec.kh, spec.kw_, spec.cin_ld, spec.cout_ld, _p(w_fwd), _p(w_dg),
+                                        _stream()), "dei2i_pack_weight_f32")
+        return w_fwd, w_dg
     check(lib.dei2i_pack_weight(_p(w), _p(inv_sigma), spec.cout, spec.cin, spec.kh, spec.kw_, spec.cin_ld, spec.cout_ld,
                                 _p(w_fwd), _p(w_dg), _stream()), "dei2i_pack_weight")
     return w_fwd, w_dg
@@ -146,6 +170,8 @@ def _kind(op, spec, flops):
 
 def conv_fwd_is_tma(spec: ConvSpec, n, h, w) -> bool:
     """True when dei2i_conv2d_fwd runs this geometry on the TMA / tcgen05 kernel (which can emit statistics / a padded output)."""
+    if ACT_DTYPE == torch.float32:
+        return False
     g = spec.geom(n, h, w)
     return bool(_lib.load().dei2i_conv2d_fwd_path(C.byref(g)))
 
@@ -161,7 +187,8 @@ def conv2d_fwd(x, w_fwd, spec: ConvSpec, bias=None, noise=None, noise_weight=Non
     assert c == spec.cin_ld, (c, spec)
     h, w = logical_hw or (hs, ws)
     ho, wo = spec.out_hw(h, w)
-    y = torch.empty(n, ho + 2 * out_pad, wo + 2 * out_pad, spec.cout_ld, dtype=torch.float32 if out_fp32 else torch.bfloat16, device=x.device)
+    f32 = is_f32(x)
+    y = torch.empty(n, ho + 2 * out_pad, wo + 2 * out_pad, spec.cout_ld, dtype=torch.float32 if (out_fp32 or f32) else torch.bfloat16, device=x.device)
     if residual is not None:
         _chk_act(residual, "residual")
         assert tuple(residual.shape) == (n, ho, wo, spec.cout_ld)
@@ -170,6 +197,14 @@ def conv2d_fwd(x, w_fwd, spec: ConvSpec, bias=None, noise=None, noise_weight=Non
         assert noise.numel() == n * ho * wo
     g = spec.geom(n, h, w, hs, ws)
     lib = _lib.load()
+    if f32:  # FP32-parity path: one exact kernel for every geometry
+        assert out_pad == 0 and w_fwd.dtype == torch.float32
+        e = ConvEpilogue(_p(scale), _p(bias), _p(noise), _p(noise_weight), _p(residual), ACT[act], 1, None, 0)
+        fl = alg_flops or spec.flops(n, ho, wo)
+        with _Timed(_kind("fwd", spec, fl), fl, spec.tag(n, h, w)):
+            check(lib.dei2i_conv2d_fwd_f32(_p(x), _p(w_fwd), _p(y), C.byref(g), C.byref(e), _stream()), "dei2i_conv2d_fwd_f32")
+        _log_kernel("fwd", spec.tag(n, h, w))
+        return y if want_stats is None else (y, None)
     partial = None
     if want_stats is not None and not out_fp32 and logical_hw is None and lib.dei2i_conv2d_fwd_path(C.byref(g)) \
             and (want_stats == "batch" or (ho * wo) % 128 == 0):
@@ -197,6 +232,13 @@ def conv2d_dgrad(dy, w_dgrad, spec: ConvSpec, in_hw, scale=None, alg_flops=None)
     g = spec.geom(n, h, w)
     lib = _lib.load()
     flops = alg_flops or spec.flops(n, dy.shape[1], dy.shape[2])
+    if is_f32(dy):
+        p = spec.pad if spec.pad_mode == "reflect" else 0
+        dxp = torch.empty(n, h + 2 * p, w + 2 * p, spec.cin_ld, dtype=torch.float32, device=dy.device)
+        with _Timed(_kind("dgrad", spec, flops), flops, spec.tag(n, h, w)):
+            check(lib.dei2i_conv2d_dgrad_f32(_p(dy), _p(w_dgrad), _p(dxp), C.byref(g), _p(scale), _stream()), "dei2i_conv2d_dgrad_f32")
+        _log_kernel("dgrad", spec.tag(n, h, w))
+        return reflect_fold(dxp, p) if p else dxp
     if spec.pad_mode == "reflect" and spec.pad > 0:
         p = spec.pad
         dxp = torch.empty(n, h + 2 * p, w + 2 * p, spec.cin_ld, dtype=torch.bfloat16, device=dy.device)
@@ -217,7 +259,10 @@ def reflect_pad(x, pad: int):
     """bf16 [N,H,W,C] -> [N,H+2p,W+2p,C], F.pad(mode='reflect')."""
     _chk_act(x, "x")
     n, h, w, c = x.shape
-    xp = torch.empty(n, h + 2 * pad, w + 2 * pad, c, dtype=torch.bfloat16, device=x.device)
+    xp = torch.empty(n, h + 2 * pad, w + 2 * pad, c, dtype=x.dtype, device=x.device)
+    if is_f32(x):
+        check(_lib.load().dei2i_reflect_pad_f32(_p(x), _p(xp), n, h, w, c, pad, _stream()), "dei2i_reflect_pad_f32")
+        return xp
     with _Timed("stream_reflect_pad", x.numel() * 2 + xp.numel() * 2, ""):
         check(_lib.load().dei2i_reflect_pad(_p(x), _p(xp), n, h, w, c, pad, _stream()), "dei2i_reflect_pad")
     return xp
@@ -228,7 +273,10 @@ def reflect_fold(dxp, pad: int):
     _chk_act(dxp, "dxp")
     n, hp, wp, c = dxp.shape
     h, w = hp - 2 * pad, wp - 2 * pad
-    dx = torch.empty(n, h, w, c, dtype=torch.bfloat16, device=dxp.device)
+    dx = torch.empty(n, h, w, c, dtype=dxp.dtype, device=dxp.device)
+    if is_f32(dxp):
+        check(_lib.load().dei2i_reflect_fold_f32(_p(dxp), _p(dx), n, h, w, c, pad, _stream()), "dei2i_reflect_fold_f32")
+        return dx
     with _Timed("stream_reflect_fold", dxp.numel() * 2 + dx.numel() * 2, ""):
         check(_lib.load().dei2i_reflect_fold(_p(dxp), _p(dx), n, h, w, c, pad, _stream()), "dei2i_reflect_fold")
     return dx
@@ -258,6 +306,16 @@ def conv2d_wgrad(x, dy, dw, spec: ConvSpec, accumulate=False, sn=None, logical_h
     h, w = logical_hw or (hs, ws)
     g = spec.geom(n, h, w, hs, ws)
     lib = _lib.load()
+    if is_f32(x):
+        nbytes = lib.dei2i_conv2d_wgrad_f32_workspace(C.byref(g))
+        wsb = _workspace(nbytes, x.device)
+        w0, u, v, inv = sn if sn is not None else (None, None, None, None)
+        fl = alg_flops or spec.flops(n, dy.shape[1], dy.shape[2])
+        with _Timed(_kind("wgrad", spec, fl), fl, spec.tag(n, h, w)):
+            check(lib.dei2i_conv2d_wgrad_f32(_p(x), _p(dy), _p(dw), spec.cin, 1.0 if accumulate else 0.0, C.byref(g), _p(w0), _p(u), _p(v),
+                                             _p(inv), _p(wsb), wsb.numel(), _stream()), "dei2i_conv2d_wgrad_f32")
+        _log_kernel("wgrad", spec.tag(n, h, w))
+        return dw
     nbytes = lib.dei2i_conv2d_wgrad_workspace(C.byref(g), spec.cin)
     wsb = _workspace(nbytes, x.device)
     w0, u, v, inv = sn if sn is not None else (None, None, None, None)
@@ -316,7 +374,10 @@ def nchw_to_nhwc(x: torch.Tensor, c_ld: int = None):
     _chk_f32(x, "x")
     n, c, h, w = x.shape
     c_ld = c_ld or pad8(c)
-    y = torch.empty(n, h, w, c_ld, dtype=torch.bfloat16, device=x.device)
+    y = torch.empty(n, h, w, c_ld, dtype=ACT_DTYPE, device=x.device)
+    if ACT_DTYPE == torch.float32:
+        check(_lib.load().dei2i_nchw_to_nhwc_f32(_p(x), _p(y), n, c, h, w, c_ld, _stream()), "dei2i_nchw_to_nhwc_f32")
+        return y
     check(_lib.load().dei2i_nchw_to_nhwc(_p(x), _p(y), n, c, h, w, c_ld, _stream()), "dei2i_nchw_to_nhwc")
     return y
 
@@ -325,6 +386,9 @@ def nhwc_to_nchw(x: torch.Tensor, c: int):
     _chk_act(x, "x")
     n, h, w, c_ld = x.shape
     y = torch.empty(n, c, h, w, dtype=torch.float32, device=x.device)
+    if is_f32(x):
+        check(_lib.load().dei2i_nhwc_to_nchw_f32(_p(x), _p(y), n, c, h, w, c_ld, _stream()), "dei2i_nhwc_to_nchw_f32")
+        return y
     check(_lib.load().dei2i_nhwc_to_nchw(_p(x), _p(y), n, c, h, w, c_ld, _stream()), "dei2i_nhwc_to_nchw")
     return y
 
@@ -431,6 +495,9 @@ def channel_stats(x, per_sample: bool):
     n, h, w, c = x.shape
     lib = _lib.load()
     stats = torch.empty(n if per_sample else 1, 2, c, dtype=torch.float32, device=x.device)
+    if is_f32(x):
+        check(lib.dei2i_channel_stats_f32(_p(x), n, h * w, c, int(per_sample), _p(stats), _stream()), "dei2i_channel_stats_f32")
+        return stats
     need = lib.dei2i_channel_stats_scratch(n, h * w, c, int(per_sample))
     scratch = torch.empty(max(need, 1), dtype=torch.float32, device=x.device)
     with _Timed("stream_channel_stats", x.numel() * 2, ""):
@@ -459,6 +526,12 @@ def bn_fwd(x, gamma, beta, running_mean, running_var, training, act=None, residu
     if not training:
         stats = None
     save = torch.empty(2, c, dtype=torch.float32, device=x.device)
+    if is_f32(x):
+        y = torch.empty_like(x)
+        check(_lib.load().dei2i_bn_fwd_f32(_p(x), _p(y), _p(residual), _p(stats), _p(gamma), _p(beta), _p(running_mean), _p(running_var),
+                                           _p(save[0]), _p(save[1]), n, h * w, c, int(training), momentum, eps, ACT[act], _stream()),
+              "dei2i_bn_fwd_f32")
+        return (reflect_pad(y, out_pad) if out_pad else y), save
     if out_pad:
         y = torch.empty(n, h + 2 * out_pad, w + 2 * out_pad, c, dtype=x.dtype, device=x.device)
         with _Timed("stream_bn_fwd", x.numel() * 2 + y.numel() * 2 + (residual.numel() * 2 if residual is not None else 0), ""):
@@ -483,6 +556,12 @@ def bn_bwd(x, dy, gamma, beta, save, training, act=None, dy_pad=0):
     lib = _lib.load()
     dx = torch.empty_like(x)
     dbg = torch.empty(2, c, dtype=torch.float32, device=x.device)  # [dbeta | dgamma]
+    if is_f32(x):
+        if dy_pad:
+            dy = reflect_fold(dy, dy_pad)
+        check(lib.dei2i_bn_bwd_f32(_p(x), _p(dy), _p(dx), _p(gamma), _p(beta), _p(save[0]), _p(save[1]), _p(dbg), n, h * w, c,
+                                   int(training), ACT[act], _stream()), "dei2i_bn_bwd_f32")
+        return dx, dbg[1], dbg[0]
     need = lib.dei2i_bn_bwd_scratch(n, h * w, c)
     scratch = torch.empty(need, dtype=torch.float32, device=x.device)
     with _Timed("stream_bn_bwd", x.numel() * 2 * 2 + dy.numel() * 2, ""):
@@ -500,8 +579,12 @@ def spade_fwd(x, gb, up: int = 1, relu: bool = True, eps: float = 1e-5, stats=No
     assert tuple(gb.shape) == (n, h, w, 2 * c), (gb.shape, x.shape, up)
     if stats is None:
         stats = channel_stats(x, True)
-    out = torch.empty(n, h, w, c, dtype=torch.bfloat16, device=x.device)
+    out = torch.empty(n, h, w, c, dtype=x.dtype, device=x.device)
     mr = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
+    if is_f32(x):
+        check(_lib.load().dei2i_spade_fwd_f32(_p(x), _p(gb), _p(out), _p(stats), _p(mr), n, h, w, c, up, int(relu), eps, _stream()),
+              "dei2i_spade_fwd_f32")
+        return out, mr
     with _Timed("stream_spade_fwd", x.numel() * 2 + gb.numel() * 2 + out.numel() * 2, ""):
         check(_lib.load().dei2i_spade_fwd(_p(x), _p(gb), _p(out), _p(stats), _p(mr), n, h, w, c, up, int(relu), eps, _stream()),
               "dei2i_spade_fwd")
@@ -510,6 +593,9 @@ def spade_fwd(x, gb, up: int = 1, relu: bool = True, eps: float = 1e-5, stats=No
 
 def spade_bwd(x, gb, out, dout, mean_rstd, up: int = 1, relu: bool = True):
     n, h, w, c = out.shape
+    if is_f32(x):
+        raise NotImplementedError("FP32-parity path: the dense SPADE backward (spatial label maps in training) is not built; "
+                                  "training feeds 1x1 label maps (class-map path)")
     dgb = torch.empty_like(gb)
     dx = torch.empty_like(x)
     lib = _lib.load()
@@ -531,8 +617,12 @@ def spade_cls_fwd(x, gb5, up: int = 1, relu: bool = True, eps: float = 1e-5, out
     assert tuple(gb5.shape) == (n, 5, 5, 2 * c), (gb5.shape, x.shape)
     if stats is None:
         stats = channel_stats(x, True)
-    out = torch.empty(n, h + 2 * out_pad, w + 2 * out_pad, c, dtype=torch.bfloat16, device=x.device)
+    out = torch.empty(n, h + 2 * out_pad, w + 2 * out_pad, c, dtype=x.dtype, device=x.device)
     mr = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
+    if is_f32(x):
+        check(_lib.load().dei2i_spade_cls_fwd_f32(_p(x), _p(gb5), _p(out), _p(stats), _p(mr), n, h, w, c, up, int(relu), eps, out_pad,
+                                                  _stream()), "dei2i_spade_cls_fwd_f32")
+        return out, mr
     with _Timed("stream_spade_cls_fwd", x.numel() * 2 + out.numel() * 2, ""):
         check(_lib.load().dei2i_spade_cls_fwd(_p(x), _p(gb5), _p(out), _p(stats), _p(mr), n, h, w, c, up, int(relu), eps, out_pad,
                                               _stream()), "dei2i_spade_cls_fwd")
@@ -547,6 +637,11 @@ def spade_cls_bwd(x, gb5, out, dout, mean_rstd, up: int = 1, relu: bool = True, 
     dgb5 = torch.empty(n, 5, 5, 2 * c, dtype=torch.float32, device=x.device)
     dx = torch.empty_like(x)
     lib = _lib.load()
+    if is_f32(x):
+        red = torch.empty(n, 2, c, dtype=torch.float32, device=x.device)
+        check(lib.dei2i_spade_cls_bwd_f32(_p(x), _p(gb5), _p(dout), _p(dgb5), _p(dx), _p(mean_rstd), _p(red), n, h, w, c, up, int(relu),
+                                          out_pad, _stream()), "dei2i_spade_cls_bwd_f32")
+        return dgb5, dx
     need = lib.dei2i_spade_cls_bwd_scratch(n, h, w, c, up)
     scratch = torch.empty(need, dtype=torch.float32, device=x.device)
     with _Timed("stream_spade_cls_bwd", x.numel() * 2 * 2 + dout.numel() * 2, ""):
@@ -609,8 +704,12 @@ def act_bwd(y, dy, act, want_dx=True, want_bias_grad=False, pad=0):
     n, hp, wp, c = dy.shape
     h, w = hp - 2 * pad, wp - 2 * pad
     m = n * h * w
-    dx = torch.empty(n, h, w, c, dtype=torch.bfloat16, device=dy.device) if want_dx else None
+    dx = torch.empty(n, h, w, c, dtype=dy.dtype, device=dy.device) if want_dx else None
     bg = torch.empty(c, dtype=torch.float32, device=dy.device) if want_bias_grad else None
+    if is_f32(dy):
+        assert pad == 0
+        check(_lib.load().dei2i_act_bwd_f32(_p(y), _p(dy), _p(dx), _p(bg), m, c, ACT[act], _stream()), "dei2i_act_bwd_f32")
+        return dx, bg
     scratch = torch.empty(_lib.REDUCE_BLOCKS * c, dtype=torch.float32, device=dy.device) if want_bias_grad else None
     with _Timed("stream_act_bwd", dy.numel() * 2 * (int(y is not None) + 1 + int(want_dx)), ""):
         check(_lib.load().dei2i_act_bwd(_p(y), _p(dy), _p(dx), _p(bg), _p(scratch), m, c, ACT[act], h, w, int(pad), _stream()), "dei2i_act_bwd")
@@ -620,6 +719,10 @@ def act_bwd(y, dy, act, want_dx=True, want_bias_grad=False, pad=0):
 def noise_wgrad(dy, noise, dw, c_real, accumulate=False):
     c = dy.shape[3]
     m = dy.numel() // c
+    if is_f32(dy):
+        check(_lib.load().dei2i_noise_wgrad_f32(_p(dy), _p(noise), _p(dw), m, c, c_real, 1.0 if accumulate else 0.0, _stream()),
+              "dei2i_noise_wgrad_f32")
+        return dw
     scratch = torch.empty(_lib.REDUCE_BLOCKS, dtype=torch.float32, device=dy.device)
     with _Timed("stream_noise_wgrad", dy.numel() * 2, ""):
         check(_lib.load().dei2i_noise_wgrad(_p(dy), _p(noise), _p(dw), _p(scratch), m, c, c_real, 1.0 if accumulate else 0.0, _stream()),
@@ -641,8 +744,12 @@ def compose_fwd(hd, x, cycle_gan=False, want_nhwc=True):
 
 def compose_bwd(hd, x, dout, dprob, cycle_gan=False, want_dx=True):
     n, h, w, _ = hd.shape
-    dhd = torch.empty(n, h, w, 8, dtype=torch.bfloat16, device=hd.device)
+    dhd = torch.empty(n, h, w, 8, dtype=ACT_DTYPE, device=hd.device)
     dx = torch.empty(n, 3, h, w, dtype=torch.float32, device=hd.device) if want_dx else None
+    if ACT_DTYPE == torch.float32:
+        check(_lib.load().dei2i_compose_bwd_f32(_p(hd), _p(x), _p(dout), _p(dprob), _p(dhd), _p(dx), n, h, w, int(cycle_gan), _stream()),
+              "dei2i_compose_bwd_f32")
+        return dhd, dx
     with _Timed("stream_compose", hd.numel() * 4 + x.numel() * 4 + dhd.numel() * 2 + (dout.numel() * 4 if dout is not None else 0), ""):
         check(_lib.load().dei2i_compose_bwd(_p(hd), _p(x), _p(dout), _p(dprob), _p(dhd), _p(dx), n, h, w, int(cycle_gan),
                                             _stream()), "dei2i_compose_bwd")

@@ -338,6 +338,43 @@ int dei2i_mask_mean(const float* img, const float* coarse, float* token_mean, fl
 int dei2i_mask_token_bwd(const float* dy, const float* coarse, const int* token_dims, float* dtoken, float* scratch, int N, int C, int H,
                          int W, int patch, int h_shift, int w_shift, int gh, int gw, dei2i_stream stream);
 
+/* ---- FP32-parity path (north-star: per-layer outputs and gradients within 1e-3 relative in FP32; the reference trains in FP32,
+ * defectgan_model.py:54).  The same operators on FP32 NHWC activations [N, H, W, C_ld] with exact FP32 arithmetic (CUDA-core FMA,
+ * fixed-order reductions): every function has the semantics of its BF16 sibling above, with `float*` activations.  Packed weights are
+ * FP32 [Cout, Kf] / [Cin, Kd] (same k order).  dei2i_conv2d_fwd_f32 honours scale / bias / noise / act / residual (FP32) of the
+ * epilogue struct (stats_partial, out_pad, out_fp32 unused).  Selected by tensor dtype in the Python wrappers (DEI2I_KERNELS=fp32). */
+int dei2i_pack_weight_f32(const float* w, int Cout, int Cin_real, int kh, int kw, int Cin, int Cout_ld, float* w_fwd, float* w_dgrad,
+                          dei2i_stream stream);
+int dei2i_conv2d_fwd_f32(const float* x, const float* w_fwd, float* y, const dei2i_conv_geom* g, const dei2i_conv_epilogue* e,
+                         dei2i_stream stream);
+int dei2i_conv2d_dgrad_f32(const float* dy, const float* w_dgrad, float* dx, const dei2i_conv_geom* g, const float* scale,
+                           dei2i_stream stream);
+size_t dei2i_conv2d_wgrad_f32_workspace(const dei2i_conv_geom* g);
+int dei2i_conv2d_wgrad_f32(const float* x, const float* dy, float* dw, int Cin_real, float beta, const dei2i_conv_geom* g,
+                           const float* sn_w_orig, const float* sn_u, const float* sn_v, const float* sn_inv_sigma, void* workspace,
+                           size_t workspace_bytes, dei2i_stream stream);
+int dei2i_nchw_to_nhwc_f32(const float* src, float* dst, int N, int C, int H, int W, int C_ld, dei2i_stream stream);
+int dei2i_nhwc_to_nchw_f32(const float* src, float* dst, int N, int C, int H, int W, int C_ld, dei2i_stream stream);
+int dei2i_channel_stats_f32(const float* x, int N, int HW, int C, int per_sample, float* stats, dei2i_stream stream);
+int dei2i_bn_fwd_f32(const float* x, float* y, const float* residual, const float* stats, const float* gamma, const float* beta,
+                     float* running_mean, float* running_var, float* save_mean, float* save_rstd, int N, int HW, int C, int training,
+                     float momentum, float eps, int act, dei2i_stream stream);
+int dei2i_bn_bwd_f32(const float* x, const float* dy, float* dx, const float* gamma, const float* beta, const float* save_mean,
+                     const float* save_rstd, float* dbeta_dgamma, int N, int HW, int C, int training, int act, dei2i_stream stream);
+int dei2i_spade_cls_fwd_f32(const float* x, const float* gb5, float* out, const float* stats, float* mean_rstd, int N, int H, int W,
+                            int C, int up, int relu, float eps, int out_pad, dei2i_stream stream);
+int dei2i_spade_cls_bwd_f32(const float* x, const float* gb5, const float* dout, float* dgb5, float* dx, const float* mean_rstd,
+                            float* red, int N, int H, int W, int C, int up, int relu, int out_pad, dei2i_stream stream);
+int dei2i_spade_fwd_f32(const float* x, const float* gb, float* out, const float* stats, float* mean_rstd, int N, int H, int W, int C,
+                        int up, int relu, float eps, dei2i_stream stream);
+int dei2i_reflect_pad_f32(const float* x, float* xp, int N, int H, int W, int C, int pad, dei2i_stream stream);
+int dei2i_reflect_fold_f32(const float* dxp, float* dx, int N, int H, int W, int C, int pad, dei2i_stream stream);
+int dei2i_act_bwd_f32(const float* y, const float* dy, float* dx, float* bias_grad, long long M, int C, int act, dei2i_stream stream);
+int dei2i_noise_wgrad_f32(const float* dy, const float* noise, float* dw, long long M, int C, int C_real, float beta,
+                          dei2i_stream stream);
+int dei2i_compose_bwd_f32(const float* hd, const float* x, const float* dout, const float* dprob, float* dhd, float* dx, int N, int H,
+                          int W, int cycle_gan, dei2i_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

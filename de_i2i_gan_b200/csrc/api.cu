@@ -31,6 +31,7 @@ int g_tune_conv_bn = 0;
 int g_tune_wgrad_bn = 0;
 int g_tune_wgrad_waves = 0;
 int g_tune_tma_ms = 0;
+int g_tune_f32_tf32 = 0;   // FP32-parity path: 1 = forward / dgrad of TMA-able geometries on the kind::tf32 tensor-core kernel
 int g_tune_conv_path = 0;  // 0 = auto (TMA im2col kernels where applicable), 1 = always the cp.async gather kernels
 static std::atomic<long long> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
@@ -79,8 +80,18 @@ static EncodeTiledFn get_encode() {
   return fn;
 }
 
+static int encode_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t row_pitch_bytes,
+                          uint32_t box_inner, uint32_t box_outer, int swizzle128, CUtensorMapDataType dt);
 int encode_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t row_pitch_bytes,
                         uint32_t box_inner, uint32_t box_outer, int swizzle128) {
+  return encode_tmap_2d(out, base, inner, outer, row_pitch_bytes, box_inner, box_outer, swizzle128, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16);
+}
+int encode_tmap_2d_f32(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t row_pitch_bytes,
+                       uint32_t box_inner, uint32_t box_outer, int swizzle128) {
+  return encode_tmap_2d(out, base, inner, outer, row_pitch_bytes, box_inner, box_outer, swizzle128, CU_TENSOR_MAP_DATA_TYPE_FLOAT32);
+}
+static int encode_tmap_2d(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t row_pitch_bytes,
+                          uint32_t box_inner, uint32_t box_outer, int swizzle128, CUtensorMapDataType dt) {
   bind_primary_context();
   EncodeTiledFn fn = get_encode();
   if (fn == nullptr) {
@@ -95,7 +106,7 @@ int encode_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint
   cuuint64_t strides[1] = {row_pitch_bytes};
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+  CUresult r = fn(out, dt, 2, const_cast<void*>(base), dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle128 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -110,9 +121,23 @@ typedef CUresult (*EncodeIm2colFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t
                                    const int*, const int*, cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave,
                                    CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
+static int encode_tmap_im2col(CUtensorMap* out, const void* base, uint64_t C, uint64_t W, uint64_t H, uint64_t N, int lower_w,
+                              int upper_w, int lower_h, int upper_h, uint32_t stride, uint32_t channels_per_pixel,
+                              uint32_t pixels_per_column, CUtensorMapDataType dt, uint64_t esz);
 int encode_tmap_im2col_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t W, uint64_t H, uint64_t N, int lower_w,
                             int upper_w, int lower_h, int upper_h, uint32_t stride, uint32_t channels_per_pixel,
                             uint32_t pixels_per_column) {
+  return encode_tmap_im2col(out, base, C, W, H, N, lower_w, upper_w, lower_h, upper_h, stride, channels_per_pixel, pixels_per_column,
+                            CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2);
+}
+int encode_tmap_im2col_f32(CUtensorMap* out, const void* base, uint64_t C, uint64_t W, uint64_t H, uint64_t N, int lower_w, int upper_w,
+                           int lower_h, int upper_h, uint32_t stride, uint32_t channels_per_pixel, uint32_t pixels_per_column) {
+  return encode_tmap_im2col(out, base, C, W, H, N, lower_w, upper_w, lower_h, upper_h, stride, channels_per_pixel, pixels_per_column,
+                            CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4);
+}
+static int encode_tmap_im2col(CUtensorMap* out, const void* base, uint64_t C, uint64_t W, uint64_t H, uint64_t N, int lower_w,
+                              int upper_w, int lower_h, int upper_h, uint32_t stride, uint32_t channels_per_pixel,
+                              uint32_t pixels_per_column, CUtensorMapDataType dt, uint64_t esz) {
   bind_primary_context();
   static EncodeIm2colFn fn = nullptr;
   static int driver_version = 0;
@@ -129,16 +154,16 @@ int encode_tmap_im2col_bf16(CUtensorMap* out, const void* base, uint64_t C, uint
     set_error("cuTensorMapEncodeIm2col is not available (no CUDA driver / no sm_100 device)");
     return DEI2I_ERR_CUDA;
   }
-  if ((reinterpret_cast<uintptr_t>(base) & 15) != 0 || (C * 2) % 16 != 0) {
+  if ((reinterpret_cast<uintptr_t>(base) & 15) != 0 || (C * esz) % 16 != 0) {
     set_error("im2col TMA operand must be 16-byte aligned (base %p, C %llu)", base, (unsigned long long)C);
     return DEI2I_ERR_INVALID;
   }
   cuuint64_t dims[4] = {C, W, H, N};
-  cuuint64_t strides[3] = {C * 2, W * C * 2, H * W * C * 2};
+  cuuint64_t strides[3] = {C * esz, W * C * esz, H * W * C * esz};
   int lo[2] = {lower_w, lower_h};
   int up[2] = {upper_w, upper_h};
   cuuint32_t estr[4] = {1, stride, stride, 1};
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(base), dims, strides, lo, up, channels_per_pixel,
+  CUresult r = fn(out, dt, 4, const_cast<void*>(base), dims, strides, lo, up, channels_per_pixel,
                   pixels_per_column, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -148,7 +173,7 @@ int encode_tmap_im2col_bf16(CUtensorMap* out, const void* base, uint64_t C, uint
   }
   // Known driver issue (drivers <= 13.1; same workaround as CUTLASS make_im2col_tma_copy_desc): for tensors smaller than
   // 128 KiB a descriptor bit must be cleared or the load faults.
-  if (driver_version <= 13010 && C * W * H * N * 2 < 131072)
+  if (driver_version <= 13010 && C * W * H * N * esz < 131072)
     reinterpret_cast<uint64_t*>(out)[1] &= ~(1llu << 21);
   return 0;
 }
@@ -166,6 +191,7 @@ extern "C" int dei2i_set_tuning(const char* key, int value) {
   else if (!strcmp(key, "wgrad_bn")) slot = &dei2i::g_tune_wgrad_bn;
   else if (!strcmp(key, "wgrad_waves")) slot = &dei2i::g_tune_wgrad_waves;
   else if (!strcmp(key, "conv_path")) slot = &dei2i::g_tune_conv_path;
+  else if (!strcmp(key, "f32_tf32")) slot = &dei2i::g_tune_f32_tf32;
   else if (!strcmp(key, "tma_ms")) slot = &dei2i::g_tune_tma_ms;
   if (slot == nullptr) return -1;
   int old = *slot;

@@ -29,6 +29,11 @@ int check_cuda(cudaError_t e, const char* what);
 // cuTensorMapEncodeTiled resolved through the runtime (no link-time libcuda dependency)
 int encode_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer,
                         uint64_t row_pitch_bytes, uint32_t box_inner, uint32_t box_outer, int swizzle128);
+// the same for FP32 elements (TF32 tensor-core path of the FP32-parity mode)
+int encode_tmap_2d_f32(CUtensorMap* out, const void* base, uint64_t inner, uint64_t outer, uint64_t row_pitch_bytes,
+                       uint32_t box_inner, uint32_t box_outer, int swizzle128);
+int encode_tmap_im2col_f32(CUtensorMap* out, const void* base, uint64_t C, uint64_t W, uint64_t H, uint64_t N, int lower_w, int upper_w,
+                           int lower_h, int upper_h, uint32_t stride, uint32_t channels_per_pixel, uint32_t pixels_per_column);
 
 // NHWC activation [N, H, W, C] as an im2col tensor map: bounding box [lower, dim + upper) in W and H, traversal stride.
 int encode_tmap_im2col_bf16(CUtensorMap* out, const void* base, uint64_t C, uint64_t W, uint64_t H, uint64_t N, int lower_w,
@@ -141,6 +146,15 @@ DEVINL void tc_mma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint3
       ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// kind::tf32: FP32 bit patterns in shared memory, the tensor core uses the upper 19 bits; K = 8 elements (32 bytes) per instruction
+DEVINL void tc_mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}\n"
+      ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
 DEVINL void tc_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // 32 lanes x 32 consecutive fp32 columns: thread t of the warp receives row (lane base + t)
@@ -183,6 +197,12 @@ DEVINL uint64_t make_smem_desc(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t 
 //      a_major bit 15, b_major bit 16 (0 = K-major, 1 = MN-major), N>>3 at [17,23), M>>4 at [24,29)
 __host__ __device__ constexpr uint32_t make_idesc_bf16(int M, int N, int a_mn_major, int b_mn_major) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
+         ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// kind::tf32: a/b_format = 2 (tf32), c_format = 1 (f32)
+__host__ __device__ constexpr uint32_t make_idesc_tf32(int M, int N, int a_mn_major, int b_mn_major) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)a_mn_major << 15) | ((uint32_t)b_mn_major << 16) |
          ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 

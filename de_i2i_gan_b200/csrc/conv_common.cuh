@@ -65,6 +65,7 @@ struct Epilogue {
   int ld;     // output pitch (elements)
   int ncols;  // real columns that carry bias (Cout)
   float* stats;  // optional [ceil(M / 128)][2][ld] per-tile (mean, M2) of the stored output (TMA kernels, bf16 output only)
+  int res_fp32;  // residual is fp32 [M, ld] (FP32-storage TF32 kernel; needs out_fp32)
 };
 
 
@@ -116,6 +117,10 @@ int run_wgrad_tma(const void* x, int N, int H, int W, int C, const void* dy, int
 int wgrad_second_pass(float* partial, int splits, const dei2i_conv_geom* g, int Cin_real, int Kf, float* dw, float beta,
                       const float* sn_w_orig, const float* sn_u, const float* sn_v, const float* sn_inv_sigma, cudaStream_t st);
 
+// TF32 tensor-core variants of the FP32-parity path; return 1 when the geometry is not eligible
+int conv_fwd_tf32(const float* x, const float* w_fwd, float* y, const dei2i_conv_geom* g, const dei2i_conv_epilogue* e, cudaStream_t st);
+int conv_dgrad_tf32(const float* dy, const float* w_dgrad, float* dx, const dei2i_conv_geom* g, const float* scale, cudaStream_t st);
+
 // conv_skinny.cu
 int wgrad_narrow_splits(int Kreal, int Cout_ld, long long M);
 int run_wgrad_narrow(const Gather& g, const void* dy, int Cout, int Cout_ld, int Kf, float* partial, int splits, cudaStream_t st);
@@ -135,6 +140,6 @@ int run_conv_c8(const Gather& g, const Epilogue& e, const void* wmat, int rows, 
 
 // returns 0 on success; the caller has checked applicability (see tma_conv_applicable)
 int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, int rows, int K, const TmaConvParams& p,
-                 int upper, int upper_w, cudaStream_t st);
+                 int upper, int upper_w, cudaStream_t st, bool tf32 = false);
 
 }  // namespace dei2i

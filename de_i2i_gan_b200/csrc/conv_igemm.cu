@@ -668,6 +668,64 @@ int wgrad_second_pass(float* partial, int splits, const dei2i_conv_geom* g, int 
   return check_cuda(cudaGetLastError(), "wgrad_reduce_kernel launch");
 }
 
+// ---- FP32-storage TF32 tensor-core variants (FP32-parity path with DEI2I_KERNELS=tf32): the same TMA-im2col geometry rules with 32
+// channels per 128-byte row.  Return 1 when the geometry is not eligible (the caller then runs the exact FP32 FMA kernel).
+extern int g_tune_f32_tf32;
+static bool tf32_applicable(const dei2i_conv_geom* g, int k_channels) {
+  if (!g_tune_f32_tf32) return false;
+  if (g->pad_mode == DEI2I_PAD_REFLECT && g->pad > 0) return false;
+  if (g->Hs != g->H || g->Ws != g->W) return false;
+  if (g->kh > 16 || g->kw > 16 || g->pad > 64 || g->stride > 8) return false;
+  if (g->kh != g->kw && g->pad != 0) return false;
+  return k_channels % 32 == 0 && k_channels >= 32;
+}
+int conv_fwd_tf32(const float* x, const float* w_fwd, float* y, const dei2i_conv_geom* g, const dei2i_conv_epilogue* e, cudaStream_t st) {
+  if (!tf32_applicable(g, g->Cin) || g->Cout_ld < 32) return 1;
+  const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
+  TmaConvParams t;
+  memset(&t, 0, sizeof(t));
+  t.Ho = Ho; t.Wo = Wo; t.M = (long long)g->N * Ho * Wo; t.stride = g->stride; t.lower = -g->pad; t.lower_w = -g->pad;
+  t.kh = g->kh; t.kw = g->kw; t.flip = 0; t.cin_blocks = g->Cin / 32; t.num_kb = g->kh * g->kw * t.cin_blocks;
+  t.b_sub = 1; t.b_kw = g->kw;
+  t.om.linear = 1;
+  t.e.scale = e->scale; t.e.bias = e->bias; t.e.noise = e->noise; t.e.noise_weight = e->noise_weight;
+  t.e.residual = (const __nv_bfloat16*)e->residual; t.e.res_fp32 = 1; t.e.out = y; t.e.act = e->act; t.e.out_fp32 = 1;
+  t.e.ld = g->Cout_ld; t.e.ncols = g->Cout;
+  // the packed FP32 weight rows are Kf = round_up(K, 64) long (K itself need only be a multiple of 32 here)
+  return run_conv_tma(x, g->N, g->H, g->W, g->Cin, w_fwd, g->Cout, round_up(g->kh * g->kw * g->Cin, 64), t, g->pad - (g->kh - 1),
+                      g->pad - (g->kw - 1), st, true);
+}
+int conv_dgrad_tf32(const float* dy, const float* w_dgrad, float* dx, const dei2i_conv_geom* g, const float* scale, cudaStream_t st) {
+  if (!tf32_applicable(g, g->Cout_ld) || g->Cin < 32) return 1;
+  const int Ho = conv_out_dim(g->H, g->kh, g->stride, g->pad), Wo = conv_out_dim(g->W, g->kw, g->stride, g->pad);
+  if (g->stride > 1) {
+    if (!(g->pad == 0 && g->kh == g->kw && g->kh % g->stride == 0 && (g->H - g->kh) % g->stride == 0 && (g->W - g->kw) % g->stride == 0)) return 1;
+    const int sd = g->stride, kt = g->kh / sd;
+    for (int py = 0; py < sd; ++py)
+      for (int px = 0; px < sd; ++px) {
+        TmaConvParams t;
+        memset(&t, 0, sizeof(t));
+        t.Ho = g->H / sd; t.Wo = g->W / sd; t.M = (long long)g->N * t.Ho * t.Wo; t.stride = 1; t.lower = -(kt - 1); t.lower_w = -(kt - 1);
+        t.kh = kt; t.kw = kt; t.flip = 1; t.cin_blocks = g->Cout_ld / 32; t.num_kb = kt * kt * t.cin_blocks;
+        t.b_sub = sd; t.b_py = py; t.b_px = px; t.b_kw = g->kw;
+        t.om.linear = 0; t.om.Ho = t.Ho; t.om.Wo = t.Wo; t.om.OH = g->H; t.om.OW = g->W; t.om.osy = sd; t.om.osx = sd;
+        t.om.oy0 = py; t.om.ox0 = px;
+        t.e.scale = scale; t.e.out = dx; t.e.act = 0; t.e.out_fp32 = 1; t.e.ld = g->Cin; t.e.ncols = g->Cin;
+        if (int rc = run_conv_tma(dy, g->N, Ho, Wo, g->Cout_ld, w_dgrad, g->Cin, round_up(g->kh * g->kw * g->Cout_ld, 64), t, 0, 0, st, true))
+          return rc;
+      }
+    return 0;
+  }
+  TmaConvParams t;
+  memset(&t, 0, sizeof(t));
+  t.Ho = g->H; t.Wo = g->W; t.M = (long long)g->N * g->H * g->W; t.stride = 1; t.lower = g->pad - (g->kh - 1); t.lower_w = g->pad - (g->kw - 1);
+  t.kh = g->kh; t.kw = g->kw; t.flip = 1; t.cin_blocks = g->Cout_ld / 32; t.num_kb = g->kh * g->kw * t.cin_blocks;
+  t.b_sub = 1; t.b_kw = g->kw;
+  t.om.linear = 1;
+  t.e.scale = scale; t.e.out = dx; t.e.act = 0; t.e.out_fp32 = 1; t.e.ld = g->Cin; t.e.ncols = g->Cin;
+  return run_conv_tma(dy, g->N, Ho, Wo, g->Cout_ld, w_dgrad, g->Cin, round_up(g->kh * g->kw * g->Cout_ld, 64), t, -g->pad, -g->pad, st, true);
+}
+
 }  // namespace dei2i
 
 using namespace dei2i;

@@ -46,9 +46,12 @@ DEVINL void chan_merge(float& n, float& mean, float& m2, float nb, float mb, flo
   n = nt;
 }
 
-template <int BLOCK_N, int STAGES, int MS>
+// TF32 = true: FP32 activations / weights in shared memory (32 channels per 128-byte row), kind::tf32 MMA (K = 8 per instruction),
+// FP32 output - the tensor-core variant of the FP32-parity path.
+template <int BLOCK_N, int STAGES, int MS, bool TF32 = false>
 __global__ void __launch_bounds__(kTmaThreads, 1)
 conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const TmaConvParams p) {
+  constexpr int KC = TF32 ? 32 : 64;  // channels per 128-byte shared-memory row
   using S = TmaSmem<BLOCK_N, STAGES, MS>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -119,8 +122,8 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           const int orr = p.flip ? p.kh - 1 - r : r;
 #pragma unroll
           for (int ms = 0; ms < MS; ++ms)
-            tma_load_im2col_4d(a_dst + ms * kTmaATile, &tmap_a, &full_bar[stage], cb * 64, cw[ms], ch[ms], img[ms], (uint16_t)os, (uint16_t)orr);
-          const int bcol = (((p.b_py + p.b_sub * r) * p.b_kw + (p.b_px + p.b_sub * s)) * p.cin_blocks + cb) * 64;
+            tma_load_im2col_4d(a_dst + ms * kTmaATile, &tmap_a, &full_bar[stage], cb * KC, cw[ms], ch[ms], img[ms], (uint16_t)os, (uint16_t)orr);
+          const int bcol = (((p.b_py + p.b_sub * r) * p.b_kw + (p.b_px + p.b_sub * s)) * p.cin_blocks + cb) * KC;
           tma_load_2d(a_dst + MS * kTmaATile, &tmap_b, &full_bar[stage], bcol, n_tile * BLOCK_N);
           if (++cb == p.cin_blocks) {
             cb = 0;
@@ -132,7 +135,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   } else if (warp == 9) {
     // =========================== MMA issuer ===========================
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, BLOCK_N, 0, 0);
+      constexpr uint32_t idesc = TF32 ? make_idesc_tf32(128, BLOCK_N, 0, 0) : make_idesc_bf16(128, BLOCK_N, 0, 0);
       uint32_t it = 0, tcount = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
         const uint32_t buf = tcount & 1u;
@@ -151,7 +154,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           for (int ms = 0; ms < MS; ++ms) {
             const uint64_t a_desc = make_smem_desc(a_addr + ms * kTmaATile, 16, 1024, 2);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) tc_mma_bf16(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+            for (int k = 0; k < 4; ++k) {
+              if (TF32) tc_mma_tf32(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+              else tc_mma_bf16(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+            }
           }
           tc_commit(&empty_bar[stage]);
         }
@@ -250,7 +256,24 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
               f[t] = fmaxf(v, v * slope);
             }
           }
-          if (e.residual != nullptr) {  // bf16 [M, ld], linear rows; only with bf16 output (CW == 32)
+          if (e.residual != nullptr && e.res_fp32) {  // fp32 [M, ld] residual with fp32 output (CW == 16): 4 x 16-byte chunks per row
+#pragma unroll
+            for (int itr = 0; itr < 4; ++itr) {
+              const int r = itr * 8 + sub_r;
+              const long long mr = m_base + qw * 32 + r;
+              float4 rv = make_float4(0.f, 0.f, 0.f, 0.f);
+              if (mr < p.M && nbase + sub_j * 4 < e.ld)
+                rv = __ldg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(e.residual) + mr * e.ld + nbase + sub_j * 4));
+              *reinterpret_cast<float4*>(stage + r * 64 + ((sub_j ^ ((r >> 1) & 3)) << 4)) = rv;
+            }
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float4 rr = *reinterpret_cast<const float4*>(stage + lane * 64 + ((j ^ my_sw) << 4));
+              f[4 * j] += rr.x; f[4 * j + 1] += rr.y; f[4 * j + 2] += rr.z; f[4 * j + 3] += rr.w;
+            }
+            __syncwarp();
+          } else if (e.residual != nullptr) {  // bf16 [M, ld], linear rows; only with bf16 output (CW == 32)
 #pragma unroll
             for (int itr = 0; itr < 4; ++itr) {
               const int r = itr * 8 + sub_r;
@@ -351,7 +374,7 @@ static int num_sms() {
   return g_num_sms;
 }
 
-template <int BN, int ST, int MS>
+template <int BN, int ST, int MS, bool TF32 = false>
 static int launch_tma(const CUtensorMap& ta, const CUtensorMap& tb, const TmaConvParams& p, cudaStream_t st) {
   using S = TmaSmem<BN, ST, MS>;
   static_assert(S::kTotal + 4096 + 4096 <= 227 * 1024, "shared memory budget (dynamic + the static bias copy + the statistics scratch)");
@@ -359,23 +382,37 @@ static int launch_tma(const CUtensorMap& ta, const CUtensorMap& tb, const TmaCon
   static_assert(2 * MS * BN <= 512, "TMEM columns");
   static bool attr_done = false;
   if (!attr_done) {
-    DEI2I_CUDA(cudaFuncSetAttribute(conv_tma_kernel<BN, ST, MS>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+    DEI2I_CUDA(cudaFuncSetAttribute(conv_tma_kernel<BN, ST, MS, TF32>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
     attr_done = true;
   }
   const int total = p.m_tiles * p.n_tiles;
   const int grid = total < num_sms() ? total : num_sms();
-  conv_tma_kernel<BN, ST, MS><<<grid, kTmaThreads, S::kTotal, st>>>(ta, tb, p);
+  conv_tma_kernel<BN, ST, MS, TF32><<<grid, kTmaThreads, S::kTotal, st>>>(ta, tb, p);
   count_launch();
-  trace_kernel("conv_tma<%d,%d,%d>", BN, ST, MS);
+  trace_kernel(TF32 ? "conv_tma_tf32<%d,%d,%d>" : "conv_tma<%d,%d,%d>", BN, ST, MS);
   return check_cuda(cudaGetLastError(), "conv_tma_kernel launch");
 }
 
 extern int g_tune_tma_ms;  // 0 = auto, 1 / 2 = force the number of 128-pixel sub-tiles per work tile
 int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, int rows, int K, const TmaConvParams& p_in,
-                 int upper, int upper_w, cudaStream_t st) {
+                 int upper, int upper_w, cudaStream_t st, bool tf32) {
   TmaConvParams p = p_in;
   int bn = 256;
   while (bn > 64 && bn / 2 >= rows) bn /= 2;
+  if (tf32) {  // FP32 operands: 32 channels per 128-byte row, one 128-pixel tile per work tile
+    CUtensorMap ta, tb;
+    if (int rc = encode_tmap_im2col_f32(&ta, x, (uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N, p.lower_w, upper_w, p.lower, upper,
+                                        (uint32_t)p.stride, 32, 128))
+      return rc;
+    if (int rc = encode_tmap_2d_f32(&tb, wmat, (uint64_t)K, (uint64_t)rows, (uint64_t)K * 4, 32, (uint32_t)bn, 1)) return rc;
+    p.n_tiles = (rows + bn - 1) / bn;
+    p.m_tiles = (int)((p.M + 127) / 128);
+    switch (bn) {
+      case 256: return launch_tma<256, 4, 1, true>(ta, tb, p, st);
+      case 128: return launch_tma<128, 6, 1, true>(ta, tb, p, st);
+      default: return launch_tma<64, 8, 1, true>(ta, tb, p, st);
+    }
+  }
   // (Narrowing BLOCK_N to put more CTAs on the few-pixel / many-channel discriminator tail was measured and dropped: 1024 -> 2048
   // at 4 x 4 went 101 -> 90 us but 512 -> 1024 at 8 x 8 went 50 -> 89 us - every extra N tile re-loads the same A tiles.)
   CUtensorMap ta, tb;

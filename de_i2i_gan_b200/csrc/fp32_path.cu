@@ -226,6 +226,10 @@ extern "C" int dei2i_conv2d_fwd_f32(const float* x, const float* w_fwd, float* y
                 "conv2d_fwd_f32: bad geometry / unsupported epilogue field");
   const int Ho = out_dim(g->H, g->kh, g->stride, g->pad), Wo = out_dim(g->W, g->kw, g->stride, g->pad);
   DEI2I_REQUIRE(Ho > 0 && Wo > 0, "conv2d_fwd_f32: empty output");
+  {  // DEI2I_KERNELS=tf32: kind::tf32 tcgen05 kernel where the TMA-im2col rules admit the geometry
+    const int rc = conv_fwd_tf32(x, w_fwd, y, g, e, ST);
+    if (rc != 1) return rc;
+  }
   GatherF gg;
   fill_gather(gg, x, g, Ho, Wo);
   EpiF ep{e->scale, e->bias, e->noise, e->noise_weight, (const float*)e->residual, y, e->act, g->Cout_ld, g->Cout};
@@ -242,6 +246,10 @@ extern "C" int dei2i_conv2d_dgrad_f32(const float* dy, const float* w_dgrad, flo
   DEI2I_REQUIRE(dy && w_dgrad && dx && g, "conv2d_dgrad_f32: null pointer");
   DEI2I_REQUIRE(g->Hs == g->H && g->Ws == g->W, "conv2d_dgrad_f32: resized inputs are not supported");
   const int Ho = out_dim(g->H, g->kh, g->stride, g->pad), Wo = out_dim(g->W, g->kw, g->stride, g->pad);
+  {
+    const int rc = conv_dgrad_tf32(dy, w_dgrad, dx, g, scale, ST);
+    if (rc != 1) return rc;
+  }
   const bool full = g->pad_mode == DEI2I_PAD_REFLECT;  // reflect: gradient of the PADDED input (the caller folds it)
   const int Hd = full ? g->H + 2 * g->pad : g->H, Wd = full ? g->W + 2 * g->pad : g->W;
   GatherF gg;

@@ -15,15 +15,28 @@ ACT = {None: 0, "none": 0, "leaky_relu": 1, "relu": 2, "tanh": 3, "sigmoid": 4}
 # fp32 (DEI2I_KERNELS=fp32 or set_precision('fp32')): the FP32-parity path of csrc/fp32_path.cu - exact FP32 arithmetic on FP32 NHWC
 # activations, for comparing with the FP32 reference at the north-star's 1e-3 tolerance.  Every wrapper below dispatches on the dtype
 # of the activation it is given; ACT_DTYPE decides what the model-edge converters and the weight packer produce.
-ACT_DTYPE = torch.float32 if os.environ.get("DEI2I_KERNELS", "bf16").lower() in ("fp32", "f32") else torch.bfloat16
+#   tf32: FP32 storage as above, forward / dgrad of the TMA-able convolutions on the kind::tf32 tcgen05 kernel (10-bit mantissa
+#   products, FP32 accumulation): the fast FP32-storage mode; weight gradients and everything else stay exact FP32.
+_KERNELS = os.environ.get("DEI2I_KERNELS", "bf16").lower()
+ACT_DTYPE = torch.float32 if _KERNELS in ("fp32", "f32", "tf32") else torch.bfloat16
+PRECISION = "bf16"
 
 
 def set_precision(name: str):
-    """'bf16' | 'fp32' - returns the previous name.  Switch only between loss computations (packed weights are cached per scope)."""
-    global ACT_DTYPE
-    old = "fp32" if ACT_DTYPE == torch.float32 else "bf16"
-    ACT_DTYPE = {"bf16": torch.bfloat16, "fp32": torch.float32, "f32": torch.float32}[name.lower()]
+    """'bf16' | 'fp32' | 'tf32' - returns the previous name.  Switch only between loss computations (packed weights are cached per scope)."""
+    global ACT_DTYPE, PRECISION
+    name = {"f32": "fp32"}.get(name.lower(), name.lower())
+    old = PRECISION
+    ACT_DTYPE = {"bf16": torch.bfloat16, "fp32": torch.float32, "tf32": torch.float32}[name]
+    PRECISION = name
+    _lib.load().dei2i_set_tuning(b"f32_tf32", 1 if name == "tf32" else 0)
     return old
+
+
+if _KERNELS in ("fp32", "f32", "tf32"):
+    PRECISION = "tf32" if _KERNELS == "tf32" else "fp32"
+    if PRECISION == "tf32":
+        _lib.load().dei2i_set_tuning(b"f32_tf32", 1)
 
 
 def is_f32(t) -> bool:

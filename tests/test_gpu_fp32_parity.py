@@ -237,3 +237,89 @@ def test_c1_d_step_and_g_step_fp32():
     # Adam's first step is -lr * sign(g): elements whose gradient is ~0 (most of the 33 M weights of D's last layer at this point) flip
     # sign on 1e-6 differences, so the update cosine measures those - the gradients themselves agree to 1e-6 (test above)
     assert cos_d > 0.9, cos_d
+
+
+# ---------------------------------------------------------------------------------------------------------------- TF32 variant
+TF32_CASES = {
+    "valid3x3_64": (2, 64, 18, 18, 64, 3, 1, 0),
+    "valid4x4s2_64_128": (2, 64, 34, 34, 128, 4, 2, 0),
+    "zero3x3_256": (1, 256, 16, 16, 256, 3, 1, 1),
+    "zero3x3_128_512_bias": (2, 128, 12, 12, 512, 3, 1, 1),
+    "ragged_m": (1, 32, 11, 13, 96, 3, 1, 1),
+}
+
+
+@pytest.mark.parametrize("case", list(TF32_CASES))
+def test_conv_tf32_tensor_core_variant(case):
+    """DEI2I_KERNELS=tf32: forward / dgrad of the TMA-able geometries on conv_tma_kernel<..., TF32> (kind::tf32 tcgen05, FP32 storage,
+    FP32 accumulation) vs torch FP32.  TF32 keeps 10 mantissa bits of each operand: measured 2e-4 .. 6e-4 of the output's max (bar
+    2e-3); the weight gradient stays on the exact FP32 kernel (1e-6)."""
+    from de_i2i_gan_b200 import ops
+    old = ops.set_precision("tf32")
+    try:
+        n, cin, h, w, cout, k, s, p = TF32_CASES[case]
+        g = torch.Generator().manual_seed(3)
+        x = torch.randn(n, cin, h, w, generator=g).requires_grad_(True)
+        wt = (torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5).requires_grad_(True)
+        b = torch.randn(cout, generator=g) if "bias" in case else None
+        y_ref = F.conv2d(x, wt, b, stride=s, padding=p)
+        dy = torch.randn(y_ref.shape, generator=g)
+        dx_ref, dw_ref = torch.autograd.grad(y_ref, (x, wt), dy)
+        spec = ops.ConvSpec(cin, cout, k, s, p, "zeros")
+        w_fwd, w_dg = ops.pack_weight(wt.detach().cuda(), spec)
+        xd, dyd = _nhwc(x.detach()), _nhwc(dy)
+        y = ops.conv2d_fwd(xd, w_fwd, spec, bias=b.cuda() if b is not None else None)
+        k_fwd = ops.last_kernel()
+        dx = ops.conv2d_dgrad(dyd, w_dg, spec, (h, w))
+        k_dg = ops.last_kernel()
+        dw = torch.empty(cout, cin, k, k, device="cuda")
+        ops.conv2d_wgrad(xd, dyd, dw, spec)
+        torch.cuda.synchronize()
+        e = dict(fwd=rel_err(y[..., :cout].permute(0, 3, 1, 2), y_ref), dgrad=rel_err(dx[..., :cin].permute(0, 3, 1, 2), dx_ref),
+                 wgrad=rel_err(dw, dw_ref))
+        _report("conv_tf32/" + case, **e, kernels=[k_fwd, k_dg])
+        assert k_fwd.startswith("conv_tma_tf32<") and k_dg.startswith("conv_tma_tf32<"), (k_fwd, k_dg)
+        assert e["fwd"] < 2e-3 and e["dgrad"] < 2e-3 and e["wgrad"] < 1e-4, e
+    finally:
+        ops.set_precision(old)
+
+
+def test_c1_generator_tf32_error_table():
+    """The full-width generator (config 1) with the TF32 tensor-core convolutions: outputs within 1e-3 of the FP32 oracle, gradients
+    reported per parameter (profiles/r02e_fp32_parity.jsonl) - TF32's 10-bit mantissa does not hold 1e-3 through the backward chain,
+    which is why the exact FP32 kernels are the parity mode and TF32 the fast FP32-storage mode."""
+    from oracle import defectgan_ref as R
+    from de_i2i_gan_b200 import ops
+    from de_i2i_gan_b200.models.networks.generator import DefectGanGenerator
+    from de_i2i_gan_b200.synthetic import synthetic_batch
+    old = ops.set_precision("tf32")
+    try:
+        g_state, _ = _states(128)
+        bg, labels, _ = synthetic_batch(4, 128, seed=0)
+        noises = _draw(_noise_shapes(4, 128, 1), 7)
+        G = DefectGanGenerator(_opt(128, 4))
+        G.load_state_dict(g_state)
+        G.cuda().train()
+        q = _inject(noises)
+        try:
+            ops.KERNEL_LOG = log = []
+            out, prob = G(bg.cuda(), labels.cuda())
+            (out.square().mean() + prob.mean()).backward()
+            assert not q
+        finally:
+            ops.KERNEL_LOG = None
+            _clear()
+        st = _req_grad(R.clone_state(g_state))
+        o_ref, p_ref = R.generator_forward(st, bg, labels, True, R.NoiseSource(noises))
+        (o_ref.square().mean() + p_ref.mean()).backward()
+        ref = _ref_grads(st)
+        a = torch.cat([p.grad.detach().float().cpu().flatten() for n, p in G.named_parameters() if n in ref])
+        b = torch.cat([ref[n].flatten() for n, p in G.named_parameters() if n in ref])
+        glob = ((a - b).norm() / b.norm()).item()
+        e_out, e_prob = rel_err(out, o_ref), rel_err(prob, p_ref)
+        used = sorted({k for _, _, names in log for k in names.split("+") if k})
+        _report("c1_tf32/generator", out=e_out, prob=e_prob, global_grad=glob, kernels=used)
+        assert any(k.startswith("conv_tma_tf32<") for k in used), used
+        assert e_out < 5e-3 and e_prob < 5e-3 and glob < 2e-2, (e_out, e_prob, glob)
+    finally:
+        ops.set_precision(old)

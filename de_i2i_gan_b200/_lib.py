@@ -86,6 +86,7 @@ SIGNATURES = {
     "dei2i_adam": (_I, [_P, _P, _P, _P, _LL, _F, _F, _F, _F, _I, _P]),
     "dei2i_adam_dev": (_I, [_P, _P, _P, _P, _LL, _P, _F, _F, _F, _P]),
     "dei2i_rmsprop": (_I, [_P, _P, _P, _LL, _F, _F, _F, _P]),
+    "dei2i_rmsprop_dev": (_I, [_P, _P, _P, _LL, _P, _F, _F, _P]),
     "dei2i_clamp": (_I, [_P, _LL, _F, _F, _P]),
     "dei2i_ema": (_I, [_P, _P, _LL, _F, _P]),
     "dei2i_pack_weight_f32": (_I, [_P, _I, _I, _I, _I, _I, _I, _P, _P, _P]),

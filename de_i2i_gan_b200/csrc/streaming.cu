@@ -1838,6 +1838,16 @@ __global__ void rmsprop_kernel(float* __restrict__ p, const float* __restrict__ 
     p[i] -= lr * gi / (sqrtf(vi) + eps);
   }
 }
+__global__ void rmsprop_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ sq, long long n,
+                                   const float* __restrict__ hyper, float alpha, float eps) {
+  const float lr = __ldg(hyper);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gi = g[i];
+    const float s = alpha * sq[i] + (1.f - alpha) * gi * gi;
+    sq[i] = s;
+    p[i] -= lr * gi / (sqrtf(s) + eps);
+  }
+}
 __global__ void clamp_kernel(float* __restrict__ p, long long n, float lo, float hi) {
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
     p[i] = fminf(fmaxf(p[i], lo), hi);
@@ -2375,6 +2385,14 @@ extern "C" int dei2i_rmsprop(float* p, const float* g, float* sq, long long n, f
   if (blocks > 148 * 16) blocks = 148 * 16;
   rmsprop_kernel<<<blocks, 256, 0, ST>>>(p, g, sq, n, lr, alpha, eps);
   return LAUNCH_OK("rmsprop_kernel");
+}
+extern "C" int dei2i_rmsprop_dev(float* p, const float* g, float* sq, long long n, const float* hyper, float alpha, float eps,
+                                 dei2i_stream stream) {
+  DEI2I_REQUIRE(p && g && sq && hyper && n > 0, "rmsprop_dev: bad arguments");
+  unsigned blocks = nblocks(n, 256 * 4);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  rmsprop_dev_kernel<<<blocks, 256, 0, ST>>>(p, g, sq, n, hyper, alpha, eps);
+  return LAUNCH_OK("rmsprop_dev_kernel");
 }
 extern "C" int dei2i_clamp(float* p, long long n, float lo, float hi, dei2i_stream stream) {
   DEI2I_REQUIRE(p && n > 0 && lo <= hi, "clamp: bad arguments");

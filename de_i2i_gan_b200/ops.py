@@ -821,6 +821,11 @@ def rmsprop(p, g, sq, lr, alpha=0.99, eps=1e-8):
     check(_lib.load().dei2i_rmsprop(_p(p), _p(g), _p(sq), p.numel(), lr, alpha, eps, _stream()), "dei2i_rmsprop")
 
 
+def rmsprop_dev(p, g, sq, hyper, alpha=0.99, eps=1e-8):
+    """RMSprop step with the learning rate in device memory (hyper[0]) - CUDA-graph friendly."""
+    check(_lib.load().dei2i_rmsprop_dev(_p(p), _p(g), _p(sq), p.numel(), _p(hyper), alpha, eps, _stream()), "dei2i_rmsprop_dev")
+
+
 def clamp_(p, lo, hi):
     check(_lib.load().dei2i_clamp(_p(p), p.numel(), float(lo), float(hi), _stream()), "dei2i_clamp")
 

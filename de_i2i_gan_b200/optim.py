@@ -137,16 +137,27 @@ class FlatRMSprop(FlatAdam):
         torch.optim.Optimizer.__init__(self, params, dict(lr=lr, alpha=alpha, eps=eps))
         self._flat = [self._flatten(g["params"]) for g in self.param_groups]
 
+    def advance(self):
+        """Host half of a step (see FlatAdam.advance): the learning rate goes to device memory so that a captured step sees the
+        scheduler's updates."""
+        for group, f in zip(self.param_groups, self._flat):
+            f["step"] += 1
+            if "hyper" not in f:
+                f["hyper"] = torch.zeros(1, dtype=torch.float32, device=f["p"].device)
+            f["hyper"].copy_(torch.tensor([float(group["lr"])], dtype=torch.float32))
+
     @torch.no_grad()
     def step(self, closure=None):
         loss = None
         if closure is not None:
             with torch.enable_grad():
                 loss = closure()
-        self._rebind()
+        capturing = torch.cuda.is_available() and torch.cuda.is_current_stream_capturing()
+        if not capturing:
+            self._rebind()
+            self.advance()
         for group, f in zip(self.param_groups, self._flat):
-            f["step"] += 1
-            ops.rmsprop(f["p"], f["g"], f["v"], float(group["lr"]), float(group["alpha"]), float(group["eps"]))
+            ops.rmsprop_dev(f["p"], f["g"], f["v"], f["hyper"], float(group["alpha"]), float(group["eps"]))
         return loss
 
     @torch.no_grad()

@@ -307,6 +307,8 @@ int dei2i_adam_dev(float* p, const float* g, float* m, float* v, long long n, co
  * options/wgan_options.py:49-57) and the WGAN weight clipping p.data.clamp_(lo, hi) (models/wgan_model.py:18-21). */
 int dei2i_rmsprop(float* p, const float* g, float* square_avg, long long n, float lr, float alpha, float eps,
                   dei2i_stream stream);
+/* the same step with the learning rate in DEVICE memory (hyper[0]): constant launch arguments, CUDA-graph capturable */
+int dei2i_rmsprop_dev(float* p, const float* g, float* sq, long long n, const float* hyper, float alpha, float eps, dei2i_stream stream);
 int dei2i_clamp(float* p, long long n, float lo, float hi, dei2i_stream stream);
 /* p_ema = lerp(p, p_ema, beta): StarGAN-v2 moving_average (stargan-v2/core/solver.py:549-551). */
 int dei2i_ema(const float* p, float* p_ema, long long n, float beta, dei2i_stream stream);

@@ -111,6 +111,8 @@ SIGNATURES = {
     "dei2i_mask_token_fwd": (_I, [_P, _P, _P, C.POINTER(C.c_int), _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P]),
     "dei2i_mask_mean": (_I, [_P, _P, _P, _P, _F, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P]),
     "dei2i_mask_token_bwd": (_I, [_P, _P, C.POINTER(C.c_int), _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _I, _P]),
+    "dei2i_augment_scratch": (_SZ, [_I, _I]),
+    "dei2i_augment_train": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "dei2i_diffaug_scratch": (_SZ, [_I, _I, _I]),
     "dei2i_diffaug_fwd": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "dei2i_diffaug_bwd": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),

@@ -346,3 +346,123 @@ extern "C" int dei2i_mask_token_bwd(const float* dy, const float* coarse, const 
   count_launch(2);
   return check_cuda(cudaGetLastError(), "mask_token_bwd_channel_kernel");
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Training input pipeline on the device (train_defectgan.py:57-65): Resize(1.5 S) -> RandomResizedCrop(S, scale (0.6, 1)) ->
+// random horizontal / vertical flip -> ColorJitter(brightness, saturation, contrast 0.2) -> ToTensor -> Normalize(0.5, 0.5),
+// as ONE kernel from the decoded uint8 HWC image to the FP32 NCHW batch the trainer consumes.  The two resampling stages
+// compose to one affine map from output pixel to source pixel; it is sampled with the triangle (bilinear, antialiased) filter
+// PIL / torchvision use, support = max(1, source pixels per output pixel).  Random parameters come from the host
+// (data/pipeline.py): params fp32 [N, 12] = crop box in SOURCE pixels (y0, x0, h, w), flip_h, flip_v, jitter factors
+// (brightness, contrast, saturation) and their order (3 slots, op ids 0 / 1 / 2).
+namespace dei2i {
+DEVINL float tri(float t) { t = fabsf(t); return t < 1.f ? 1.f - t : 0.f; }
+__global__ void __launch_bounds__(256)
+augment_train_kernel(const uint8_t* __restrict__ src, const long long* __restrict__ src_off, const int* __restrict__ src_hw,
+                     const float* __restrict__ params, float* __restrict__ out, int N, int S) {
+  const int n = blockIdx.y;
+  const float* p = params + n * 12;
+  const int H = src_hw[2 * n], W = src_hw[2 * n + 1];
+  const uint8_t* img = src + src_off[n];
+  const float y0 = p[0], x0 = p[1], ch = p[2], cw = p[3];
+  const bool fh = p[4] > 0.5f, fv = p[5] > 0.5f;
+  const float sy = ch / (float)S, sx = cw / (float)S;           // source pixels per output pixel
+  const float ry = fmaxf(sy, 1.f), rx = fmaxf(sx, 1.f);         // filter support (antialias when down-sampling)
+  for (int px = blockIdx.x * blockDim.x + threadIdx.x; px < S * S; px += gridDim.x * blockDim.x) {
+    int oy = px / S, ox = px - oy * S;
+    const int ty = fv ? S - 1 - oy : oy, tx = fh ? S - 1 - ox : ox;  // flips act on the cropped image
+    const float cy = y0 + (ty + 0.5f) * sy, cx = x0 + (tx + 0.5f) * sx;  // centre in source coordinates (pixel centres at +0.5)
+    // taps stay inside the crop box (the crop happens before the final resize, so its edge is the image edge for the filter)
+    const int ya = max((int)floorf(cy - ry), max((int)floorf(y0), 0)), yb = min((int)ceilf(cy + ry), min((int)ceilf(y0 + ch), H));
+    const int xa = max((int)floorf(cx - rx), max((int)floorf(x0), 0)), xb = min((int)ceilf(cx + rx), min((int)ceilf(x0 + cw), W));
+    float acc[3] = {0.f, 0.f, 0.f}, wsum = 0.f;
+    for (int y = ya; y < yb; ++y) {
+      const float wy = tri((y + 0.5f - cy) / ry);
+      if (wy == 0.f) continue;
+      for (int x = xa; x < xb; ++x) {
+        const float w = wy * tri((x + 0.5f - cx) / rx);
+        if (w == 0.f) continue;
+        const uint8_t* q = img + ((size_t)y * W + x) * 3;
+        acc[0] += w * q[0]; acc[1] += w * q[1]; acc[2] += w * q[2];
+        wsum += w;
+      }
+    }
+    float v[3];
+#pragma unroll
+    for (int c = 0; c < 3; ++c) v[c] = wsum > 0.f ? acc[c] / (wsum * 255.f) : 0.f;
+    out[((size_t)n * 3 + 0) * S * S + px] = v[0];
+    out[((size_t)n * 3 + 1) * S * S + px] = v[1];
+    out[((size_t)n * 3 + 2) * S * S + px] = v[2];
+  }
+}
+// ColorJitter + Normalize on the resampled [0, 1] batch, in place.  order: 3 op ids (0 brightness, 1 contrast, 2 saturation);
+// contrast blends with the mean grey level of the CURRENT image, so each contrast op is preceded by a per-image reduction.
+__global__ void __launch_bounds__(256)
+jitter_gray_sum_kernel(const float* __restrict__ x, float* __restrict__ part, int S2) {
+  __shared__ float sh[32];
+  const int n = blockIdx.y;
+  float acc = 0.f;
+  for (int px = blockIdx.x * blockDim.x + threadIdx.x; px < S2; px += gridDim.x * blockDim.x) {
+    const float* q = x + (size_t)n * 3 * S2 + px;
+    acc += 0.299f * q[0] + 0.587f * q[S2] + 0.114f * q[2 * S2];
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int k = 0; k < (int)(blockDim.x >> 5); ++k) t += sh[k];
+    part[(size_t)n * gridDim.x + blockIdx.x] = t;
+  }
+}
+__global__ void __launch_bounds__(256)
+jitter_apply_kernel(float* __restrict__ x, const float* __restrict__ params, const float* __restrict__ gray_mean, int S2, int op_slot,
+                    int normalize) {
+  const int n = blockIdx.y;
+  const float* p = params + n * 12;
+  const int op = op_slot >= 0 ? (int)p[9 + op_slot] : -1;
+  const float f = op >= 0 ? p[6 + op] : 1.f;
+  const float gm = op == 1 ? gray_mean[n] : 0.f;
+  for (int px = blockIdx.x * blockDim.x + threadIdx.x; px < S2; px += gridDim.x * blockDim.x) {
+    float* q = x + (size_t)n * 3 * S2 + px;
+    float v[3] = {q[0], q[S2], q[2 * S2]};
+    if (op == 0) {  // brightness: blend with black
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v[c] = fminf(fmaxf(v[c] * f, 0.f), 1.f);
+    } else if (op == 1) {  // contrast: blend with the mean grey level
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v[c] = fminf(fmaxf(f * v[c] + (1.f - f) * gm, 0.f), 1.f);
+    } else if (op == 2) {  // saturation: blend with the pixel's grey level
+      const float g = 0.299f * v[0] + 0.587f * v[1] + 0.114f * v[2];
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v[c] = fminf(fmaxf(f * v[c] + (1.f - f) * g, 0.f), 1.f);
+    }
+    if (normalize) {
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v[c] = (v[c] - 0.5f) * 2.f;
+    }
+    q[0] = v[0]; q[S2] = v[1]; q[2 * S2] = v[2];
+  }
+}
+}  // namespace dei2i
+
+extern "C" size_t dei2i_augment_scratch(int N, int S) { return (size_t)N * (aug_blocks(S, S, N) + 1); }
+
+extern "C" int dei2i_augment_train(const void* src_u8, const long long* src_offsets, const int* src_hw, const float* params, float* out,
+                                   float* scratch, int N, int S, int jitter, dei2i_stream stream) {
+  DEI2I_REQUIRE(src_u8 && src_offsets && src_hw && params && out && scratch && N > 0 && N <= 1024 && S > 0, "augment_train: bad arguments");
+  const int nb = aug_blocks(S, S, N);
+  augment_train_kernel<<<dim3(nb, N), 256, 0, ST>>>((const uint8_t*)src_u8, src_offsets, src_hw, params, out, N, S);
+  count_launch();
+  float* gm = scratch + (size_t)N * nb;
+  for (int slot = 0; slot < (jitter ? 3 : 0); ++slot) {
+    // the grey mean is only consumed by a contrast op; computing it for every slot keeps the launch sequence static (graph friendly)
+    jitter_gray_sum_kernel<<<dim3(nb, N), 256, 0, ST>>>(out, scratch, S * S);
+    aug_sum_finish_kernel<<<1, N, 0, ST>>>(scratch, nb, 1.f / ((float)S * S), gm);
+    jitter_apply_kernel<<<dim3(nb, N), 256, 0, ST>>>(out, params, gm, S * S, slot, 0);
+    count_launch(3);
+  }
+  jitter_apply_kernel<<<dim3(nb, N), 256, 0, ST>>>(out, params, gm, S * S, -1, 1);  // Normalize(0.5, 0.5)
+  count_launch();
+  return check_cuda(cudaGetLastError(), "augment_train_kernel");
+}

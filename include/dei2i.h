@@ -377,6 +377,15 @@ int dei2i_noise_wgrad_f32(const float* dy, const float* noise, float* dw, long l
 int dei2i_compose_bwd_f32(const float* hd, const float* x, const float* dout, const float* dprob, float* dhd, float* dx, int N, int H,
                           int W, int cycle_gan, dei2i_stream stream);
 
+/* ---- training input pipeline on the device (train_defectgan.py:57-65): Resize(1.5 S) -> RandomResizedCrop(S) -> flips -> ColorJitter ->
+ * ToTensor -> Normalize(0.5, 0.5) from decoded uint8 HWC images (concatenated in `src_u8`, image n at byte offset src_offsets[n] with
+ * size src_hw[2n] x src_hw[2n+1], all in device memory) to the FP32 NCHW batch `out` [N, 3, S, S].  params fp32 [N, 12]: crop box in
+ * source pixels (y0, x0, h, w), flip_h, flip_v, brightness / contrast / saturation factors, the order of the three jitter ops (op ids
+ * 0 / 1 / 2), unused.  Antialiased bilinear (triangle) resampling as PIL / torchvision.  scratch >= dei2i_augment_scratch(N, S) floats. */
+size_t dei2i_augment_scratch(int N, int S);
+int dei2i_augment_train(const void* src_u8, const long long* src_offsets, const int* src_hw, const float* params, float* out,
+                        float* scratch, int N, int S, int jitter, dei2i_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

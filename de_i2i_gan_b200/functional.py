@@ -731,6 +731,10 @@ class _AdainAct(Function):
 
 def adain_act(x: Nhwc, scale: torch.Tensor, shift: torch.Tensor, slope=0.2, eps=1e-5) -> Nhwc:
     """lrelu_slope(IN(x) * scale[n,c] + shift[n,c]); scale / shift fp32 [N,C] (AdaIN: 1 + gamma, beta; affine IN: weight, bias)."""
+    c_ld = x.t.shape[3]
+    if scale.shape[1] != c_ld:  # carrier channels are padded to a multiple of 8: the padding lanes stay zero (scale = shift = 0)
+        scale = torch.nn.functional.pad(scale, (0, c_ld - scale.shape[1]))
+        shift = torch.nn.functional.pad(shift, (0, c_ld - shift.shape[1]))
     return Nhwc(_AdainAct.apply(x.t, scale, shift, slope, eps), x.c)
 
 

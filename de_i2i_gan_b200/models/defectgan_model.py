@@ -1,5 +1,5 @@
-"""DefectGanModel (models/defectgan_model.py:19-104,173-314,385-421) on the sm_100a kernels: the loss graphs of the
-'generator' / 'discriminator' / 'inference' / 'inference_classifier' modes, SPADE variant.
+"""DefectGanModel (models/defectgan_model.py:19-104,173-314,385-428) on the sm_100a kernels: the loss graphs of the
+'generator' / 'discriminator' / 'inference' / 'inference_classifier' modes; SPADE, SEAN and AdaIN style variants.
 
 Same constructor, ``__call__(mode, data, labels, df_data=None, img_only=False, mask=None)`` contract, return values
 and network train/eval switching as the reference; the networks are the mirrored modules of ``models.networks`` whose
@@ -9,9 +9,11 @@ weights are built once per loss computation (``Fn.weight_cache``): the 4 G and 2
 ``opt.diff_aug`` (DiffAugment policies, utils/diffaug.py) runs on the fused augmentation kernels; the MAE pre-training modes
 ('mae_generator' / 'mae_discriminator' / 'mae_inference', defectgan_model.py:106-171) run the same networks behind the fused
 mask-token kernel.
-Not on this path ("next"): the SEAN / AdaIN style variants and the image-grid helpers - they raise
-NotImplementedError instead of silently falling back to PyTorch.
+Not on this path: the image-grid helpers and SEAN's `style_distill` (fails in the reference itself, see normalization.SEAN) -
+they raise NotImplementedError instead of silently falling back to PyTorch.
 """
+import random
+
 import torch
 
 from .. import functional as Fn
@@ -20,6 +22,7 @@ from ..utils.util import draw_shifted_mask
 from .base_model import BaseModel
 from .networks.architecture import MaskToken
 from .networks.discriminator import DefectGanDiscriminator
+from .networks.extractor import StyleExtractor
 from .networks.generator import DefectGanGenerator
 
 
@@ -32,8 +35,8 @@ class DefectGanModel(BaseModel):
         super().__init__(opt)
         image_size = opt.image_size
         assert image_size & (image_size - 1) == 0, "Image size must be a power of 2"
-        if opt.style_norm_block_type != "spade":
-            raise NotImplementedError(f"style_norm_block_type={opt.style_norm_block_type!r}: only 'spade' is on the CUDA hot path")
+        if opt.style_norm_block_type not in ("spade", "sean", "adain"):
+            raise ValueError(f"|style_norm_block_type {opt.style_norm_block_type}| is invalid")
         self.netG = DefectGanGenerator(opt).to(opt.device, non_blocking=True)
         self.netD = DefectGanDiscriminator(opt).to(opt.device, non_blocking=True)
         if getattr(opt, "is_train", False) or hasattr(opt, "clf_loss_type"):
@@ -41,6 +44,17 @@ class DefectGanModel(BaseModel):
             self.clf_loss_type = opt.clf_loss_type
         if hasattr(opt, "mask_token_type"):  # learnable mask token of the MAE pre-training path (defectgan_model.py:30-32)
             self.mask_token = MaskToken(opt).to(opt.device, non_blocking=True)
+        # style embedding (defectgan_model.py:34-47)
+        if opt.style_norm_block_type == "sean":
+            if opt.sean_alpha is not None:
+                self.netG.set_sean_alpha(opt.sean_alpha)
+            if opt.sean_alpha != 0 and not (opt.phase == "test" and opt.use_running_stats):
+                assert opt.embed_path is not None, "embed_path should be initialized if style_norm_block_type is sean and sean_alpha is not 0"
+                self.embeddings = torch.load(opt.embed_path)
+                for label, embeds in self.embeddings.items():
+                    self.embeddings[label] = [e.to(opt.device, non_blocking=True) for e in embeds]
+        elif opt.style_norm_block_type == "adain":
+            self.netE = StyleExtractor(opt).to(opt.device, non_blocking=True)
 
     # ------------------------------------------------------------------------------------------------ dispatch
     def __call__(self, mode, data, labels, df_data=None, img_only=False, mask=None):
@@ -97,11 +111,16 @@ class DefectGanModel(BaseModel):
     def _compute_generator_loss(self, bg_data, df_labels, df_data):
         """defectgan_model.py:173-249: normal->defect->normal and defect->normal->defect cycles (4 G passes, train mode),
         2 D passes (eval mode), adversarial + classification + reconstruction + spatial-distribution cycle / constraint."""
-        nm_labels, df_labels = self._labels(df_labels)
-        fake_defects, df_prob = self.netG(bg_data, df_labels)
-        recover_normals, rec_df_prob = self.netG(fake_defects, nm_labels)
-        fake_normals, nm_prob = self.netG(df_data, nm_labels)
-        recover_defects, rec_nm_prob = self.netG(fake_normals, df_labels)
+        nm_labels, nm_feat, df_labels, df_feat = self._get_label_and_style_feat(bg_data, df_labels, df_data)
+        track = self.opt.style_norm_block_type == "sean" and self.opt.use_running_stats
+        if track:
+            self.netG.track_running_stats = True
+        fake_defects, df_prob = self.netG(bg_data, df_labels, df_feat)
+        recover_normals, rec_df_prob = self.netG(fake_defects, nm_labels, nm_feat)
+        fake_normals, nm_prob = self.netG(df_data, nm_labels, nm_feat)
+        recover_defects, rec_nm_prob = self.netG(fake_normals, df_labels, df_feat)
+        if track:
+            self.netG.track_running_stats = False
 
         policy = getattr(self.opt, "diff_aug", "")  # defectgan_model.py:200-203: the reconstruction terms use the un-augmented images
         fd_src, fd_cls = self.netD(DiffAugment(fake_defects, policy))
@@ -121,10 +140,10 @@ class DefectGanModel(BaseModel):
     def _compute_discriminator_loss(self, bg_data, df_labels, df_data):
         """defectgan_model.py:251-292: 2 G passes without grad (eval mode), 4 D passes (train mode: one spectral-norm
         power iteration each), 4 adversarial + 2 classification terms."""
-        nm_labels, df_labels = self._labels(df_labels)
+        nm_labels, nm_feat, df_labels, df_feat = self._get_label_and_style_feat(bg_data, df_labels, df_data)
         with torch.no_grad():
-            fake_defects, _ = self.netG(bg_data, df_labels)
-            fake_normals, _ = self.netG(df_data, nm_labels)
+            fake_defects, _ = self.netG(bg_data, df_labels, df_feat)
+            fake_normals, _ = self.netG(df_data, nm_labels, nm_feat)
         policy = getattr(self.opt, "diff_aug", "")  # defectgan_model.py:266-271: fakes first, then the real defect / background batches
         fake_defects, fake_normals = DiffAugment(fake_defects, policy), DiffAugment(fake_normals, policy)
         df_data, bg_data = DiffAugment(df_data, policy), DiffAugment(bg_data, policy)
@@ -148,7 +167,9 @@ class DefectGanModel(BaseModel):
         else:
             masks = mask.to(self.opt.device, non_blocking=True)
             masked_imgs = self.mask_token(imgs, masks)
-        predicted_imgs, _ = self.netG(masked_imgs, self._expand_seg(labels))
+        kind = self.opt.style_norm_block_type
+        style_feat = self._get_style_embeds(labels) if kind == "sean" else self.netE(imgs, labels) if kind == "adain" else None
+        predicted_imgs, _ = self.netG(masked_imgs, self._expand_seg(labels), style_feat)
         return predicted_imgs, masks
 
     def _mae_adv_terms(self, predicted_imgs, labels):
@@ -228,8 +249,10 @@ class DefectGanModel(BaseModel):
         return tuple(o.clone() for o in st["out"])
 
     def _generate_fake(self, data, labels):
-        """defectgan_model.py:302-314 (spade branch): labels [B,label_nc] or a spatial map [B,label_nc,h,w]."""
-        return self.netG(data, self._expand_seg(labels))
+        """defectgan_model.py:302-314: labels [B,label_nc] or (spade) a spatial map [B,label_nc,h,w]."""
+        kind = self.opt.style_norm_block_type
+        style_feat = self._get_style_embeds(labels) if kind == "sean" else self.netE(data, labels) if kind == "adain" else None
+        return self.netG(data, self._expand_seg(labels), style_feat)
 
     # ------------------------------------------------------------------------------------------------ helpers
     def _cal_loss(self, logits, targets, loss_type):
@@ -246,8 +269,41 @@ class DefectGanModel(BaseModel):
         raise ValueError(f"|labels dim {labels.dim()}| is invalid")
 
     def _labels(self, df_labels):
-        """defectgan_model.py:410-421 (spade branch): normal label = one-hot class 0; both as [B,label_nc,1,1] maps."""
+        """defectgan_model.py:413-416: normal label = one-hot class 0; both as [B,label_nc,1,1] maps (the generator reads the rows
+        back for the vector-conditioned SEAN / AdaIN norms)."""
         df_labels = df_labels.float()
         nm_labels = torch.zeros_like(df_labels)
         nm_labels[:, 0] = 1
         return self._expand_seg(nm_labels), self._expand_seg(df_labels)
+
+    def _get_style_embeds(self, labels):
+        """defectgan_model.py:394-411: `num_embeds` stored embeddings per sample, drawn (python `random.choices`, as the reference)
+        from the list kept for the sample's label combination; zeros when that list is empty."""
+        if self.opt.sean_alpha == 0:
+            return None
+        if self.opt.use_running_stats and self.netG.inference_running_stats:
+            return torch.randn(labels.size(0), self.opt.hidden_nc).to(self.netG.device)
+        num_embeds = self.opt.num_embeds
+        rows = []
+        for label in labels.reshape(labels.size(0), -1).int().tolist():
+            pool = self.embeddings[tuple(label)]
+            if not pool:
+                rows.append(torch.zeros(num_embeds, self.opt.embed_nc, device=self.netG.device))
+            else:
+                rows.append(torch.stack(random.choices(pool, k=num_embeds)))
+        return torch.stack(rows)
+
+    def _get_label_and_style_feat(self, bg_data, df_labels, df_data):
+        """defectgan_model.py:413-428."""
+        kind = self.opt.style_norm_block_type
+        nm_rows = torch.zeros_like(df_labels, dtype=torch.float)
+        nm_rows[:, 0] = 1
+        nm_feat = df_feat = None
+        if kind == "sean":
+            nm_feat = self._get_style_embeds(nm_rows)
+            df_feat = self._get_style_embeds(df_labels)
+        elif kind == "adain":
+            nm_feat = self.netE(bg_data, nm_rows)
+            df_feat = self.netE(df_data, df_labels)
+        nm_labels, df_labels = self._labels(df_labels)
+        return nm_labels, nm_feat, df_labels, df_feat

@@ -17,7 +17,7 @@ from torch.nn.utils import spectral_norm  # old hook API, as the reference (arch
 
 from ... import functional as Fn
 from ...ops import ConvSpec
-from .normalization import SPADE
+from .normalization import SEAN, SPADE, AdaIN
 
 FUSE_REFLECT_PAD = os.environ.get("DEI2I_FUSE_REFLECT_PAD", "1") != "0"
 ROWPACK_STEM = os.environ.get("DEI2I_ROWPACK_STEM", "1") != "0"
@@ -132,7 +132,7 @@ def _apply_sn(blocks, use_spectral):
 
 
 class ConvBlock(nn.Module):
-    """architecture.py:79-118: [spectral] Conv2d -> [BatchNorm2d] -> activation."""
+    """architecture.py:79-118: [spectral] Conv2d -> [BatchNorm2d | InstanceNorm2d] -> activation."""
 
     def __init__(self, f_in, f_out, kernel_size=(3, 3), stride=(1, 1), padding=0, padding_mode="zeros", bias=False,
                  norm_layer=None, act_layer=None, use_spectral=False):
@@ -147,8 +147,13 @@ class ConvBlock(nn.Module):
         self._spec = _spec_of(self.conv_block[0])
         self._act = act_layer
         self._has_norm = norm_layer is not None
-        if self._has_norm and not isinstance(self.conv_block[1], nn.BatchNorm2d):
-            raise NotImplementedError("ConvBlock on the CUDA path supports norm_layer in (None, nn.BatchNorm2d)")
+        self._inorm = self._has_norm and isinstance(self.conv_block[1], nn.InstanceNorm2d)
+        if self._has_norm and not isinstance(self.conv_block[1], (nn.BatchNorm2d, nn.InstanceNorm2d)):
+            raise NotImplementedError("ConvBlock on the CUDA path supports norm_layer in (None, nn.BatchNorm2d, nn.InstanceNorm2d)")
+        if self._inorm:
+            inorm = self.conv_block[1]
+            if inorm.track_running_stats or act_layer not in _IN_SLOPE:
+                raise NotImplementedError("ConvBlock + InstanceNorm2d on the CUDA path: per-image statistics, (leaky) ReLU or no activation")
 
     @property
     def _norm(self):  # not an attribute: registering the sub-module twice would duplicate its state-dict keys
@@ -159,6 +164,18 @@ class ConvBlock(nn.Module):
         BatchNorm kernel itself (`reflect_pad_of(next_block)`); the result then has ``.pad == out_pad``."""
         plain = not isinstance(x, Fn.Nhwc)
         conv = self.conv_block[0]
+        if self._inorm:
+            # StyleExtractor (extractor.py:60-69): conv -> InstanceNorm2d -> activation [+ residual]; normalisation, affine (if any)
+            # and activation are ONE pass of the AdaIN kernel with per-image scale / shift rows
+            xa = Fn.to_nhwc(x)
+            y = Fn.conv(xa, conv, _consumer_spec(self._spec, xa), conv.training, bias=conv.bias)
+            inorm, n = self.conv_block[1], xa.shape[0]
+            one = inorm.weight if inorm.affine else torch.ones(self._spec.cout, device=y.t.device)
+            zero = inorm.bias if inorm.affine else torch.zeros(self._spec.cout, device=y.t.device)
+            y = Fn.adain_act(y, one.float().expand(n, -1), zero.float().expand(n, -1), slope=_IN_SLOPE[self._act], eps=inorm.eps)
+            if residual is not None:
+                y = Fn.add_scaled(y, residual, 1.0)
+            return y if (carrier_out or not plain) else _edge(y)
         if plain and ROWPACK_STEM and self._norm is not None and conv.bias is None and Fn.rowpack_applicable(self._spec):
             # generator stem (3->64, 7x7 reflect): row-packed image -> 7x1 convolution over 64 channels on the TMA kernels
             y = Fn.rowpack_conv(x, conv, self._spec, conv.training, want_stats=_bn_stats(self._norm))
@@ -185,6 +202,9 @@ class ConvBlock(nn.Module):
     def reflect_pad_in(self) -> int:
         """Reflect padding this block's convolution wants on its input (what a producer may pre-write), else 0."""
         return _fusable_pad(self._spec)
+
+
+_IN_SLOPE = {None: 1.0, "relu": 0.0, "leaky_relu": 0.2}  # the AdaIN kernel's activation is LeakyReLU(slope)
 
 
 def _bn_stats(bn) -> str:
@@ -259,14 +279,14 @@ class DeConvBlock(nn.Module):
 
 
 class ResBlock(nn.Module):
-    """architecture.py:121-176 (down_scale=False as used by DefectGAN, generator.py:118-126):
-    x + ConvBlock(act=None)(ConvBlock(act)(x)); the residual add is fused into the second BatchNorm kernel."""
+    """architecture.py:121-176: shortcut(x) + ConvBlock(act=None)([AvgPool2d] ConvBlock(act)(x)).  DefectGAN's encoder uses it with
+    BatchNorm and the identity shortcut (generator.py:118-126: the add is fused into the second BatchNorm kernel); the
+    StyleExtractor with InstanceNorm2d and `down_scale=True` (extractor.py:60-69: AvgPool2d(2, 2) between the two blocks and a
+    1x1 ConvBlock + AvgPool2d shortcut)."""
 
     def __init__(self, f_in, f_out, kernel_size=(3, 3), stride=(1, 1), padding=0, padding_mode="zeros", bias=False,
                  norm_layer=nn.InstanceNorm2d, act_layer="relu", use_spectral=False, down_scale=False):
         super().__init__()
-        if down_scale:
-            raise NotImplementedError("ResBlock(down_scale=True) is not used by DefectGAN and not on the CUDA path")
         if norm_layer is None:
             raise NotImplementedError("ResBlock without a norm layer")
         self.down_scale = down_scale
@@ -274,13 +294,23 @@ class ResBlock(nn.Module):
                             bias=bias, norm_layer=norm_layer, act_layer=act_layer, use_spectral=use_spectral),
                   ConvBlock(f_in, f_out, kernel_size=kernel_size, stride=stride, padding=padding, padding_mode=padding_mode,
                             bias=bias, norm_layer=norm_layer, act_layer=None, use_spectral=use_spectral)]
+        if down_scale:
+            blocks.insert(1, nn.AvgPool2d(2, 2))
+            self.conv_s = nn.Sequential(ConvBlock(f_in, f_out, kernel_size=(1, 1), stride=(1, 1), padding=0, padding_mode=padding_mode,
+                                                  bias=False, norm_layer=norm_layer, act_layer=None, use_spectral=use_spectral),
+                                        nn.AvgPool2d(2, 2))
         self.res_block = nn.Sequential(*blocks)
 
     def forward(self, x, seg=None):
         plain = not isinstance(x, Fn.Nhwc)
         xa = Fn.to_nhwc(x)
-        y = self.res_block[0](xa, out_pad=self.res_block[1].reflect_pad_in())
-        y = self.res_block[1](y, residual=xa)
+        first, last = self.res_block[0], self.res_block[-1]
+        if self.down_scale:
+            y = Fn.avg_pool(first(xa), 2)
+            y = last(y, residual=Fn.avg_pool(self.conv_s[0](xa), 2))
+        else:
+            y = first(xa, out_pad=last.reflect_pad_in())
+            y = last(y, residual=xa)
         return Fn.from_nhwc(y) if plain else y
 
 
@@ -304,12 +334,27 @@ def _consumer_spec(spec: ConvSpec, x: "Fn.Nhwc") -> ConvSpec:
     return spec
 
 
-def _style_norm(kind, label_nc, nc, hidden_nc, kernel_size, padding, norm_layer):
+def _style_norm(kind, label_nc, nc, hidden_nc, kernel_size, padding, norm_layer, embed_nc=None, style_distill=False):
+    """architecture.py:211-226 / 297-320: the style normalisation of a NormConvBlock / NormResBlock."""
     if kind == "spade":
         return SPADE(label_nc, nc, hidden_nc=hidden_nc, kernel_size=kernel_size, padding=padding, norm_layer=norm_layer)
-    if kind in ("sean", "adain"):
-        raise NotImplementedError(f"style_norm_block_type={kind!r}: only the SPADE variant is on the CUDA hot path (SURVEY 8f, next)")
+    if kind == "sean":
+        assert embed_nc is not None, "embed_nc must be specified for SEAN"
+        return SEAN(embed_nc, nc, label_nc, hidden_nc=hidden_nc, norm_layer=norm_layer, style_distill=style_distill)
+    if kind == "adain":
+        return AdaIN(nc, hidden_nc=hidden_nc, norm_layer=norm_layer, denorm_type="linear")
     raise ValueError(f"Unknown style norm block type: {kind}")
+
+
+def _style_forward(kind, norm, x, labels, style_feat, up, relu, out_pad):
+    """norm_forward of architecture.py:246-253 / 362-369 with the fused followers (2x up-sampling, ReLU, reflect border)."""
+    if kind == "spade":
+        return norm(x, labels, up=up, relu=relu, out_pad=out_pad)
+    if isinstance(labels, Fn.Nhwc):  # the generator hands SPADE a carrier; the vector norms want the [N, label_nc] rows
+        labels = labels.t[:, 0, 0, : labels.c].float()
+    if kind == "sean":
+        return norm(x, labels, style_feat, up=up, relu=relu)
+    return norm(x, style_feat, up=up, relu=relu)
 
 
 class NormConvBlock(nn.Module):
@@ -323,7 +368,7 @@ class NormConvBlock(nn.Module):
         self.up = nn.Upsample(scale_factor=2) if up_scale else nn.Identity()
         self.noise = NoiseInjection() if add_noise else nn.Identity()
         self.style_norm_block_type = style_norm_block_type
-        self.norm = _style_norm(style_norm_block_type, label_nc, f_in, hidden_nc, (3, 3), padding, norm_layer)
+        self.norm = _style_norm(style_norm_block_type, label_nc, f_in, hidden_nc, (3, 3), padding, norm_layer, embed_nc, style_distill)
         self.conv = nn.Conv2d(f_in, f_out, kernel_size=kernel_size, stride=stride, padding=padding,
                               padding_mode=padding_mode, bias=bias)
         self.act = get_act_layer(act_layer)
@@ -340,7 +385,7 @@ class NormConvBlock(nn.Module):
         out_pad: reflect padding the next convolution (the generator heads) wants pre-written on the output."""
         plain = not isinstance(x, Fn.Nhwc)
         xa = Fn.to_nhwc(x)
-        s = self.norm(xa, labels, up=self._up, relu=self._relu, out_pad=_fusable_pad(self._spec))
+        s = _style_forward(self.style_norm_block_type, self.norm, xa, labels, style_feat, self._up, self._relu, _fusable_pad(self._spec))
         n, _, h, w = s.shape
         ho, wo = self._spec.out_hw(h, w)
         noise, nw = _noise_args(self.noise, n, ho, wo, s.t.device)
@@ -349,7 +394,8 @@ class NormConvBlock(nn.Module):
         return Fn.from_nhwc(y) if plain else y
 
     def update_alpha(self, epoch, num_epochs):
-        pass
+        if hasattr(self.norm, "update_alpha"):
+            self.norm.update_alpha(epoch, num_epochs)
 
 
 class NormResBlock(nn.Module):
@@ -368,9 +414,9 @@ class NormResBlock(nn.Module):
         self.noise_1 = NoiseInjection() if add_noise else nn.Identity()
         f_mid = min(f_in, f_out)
         self.style_norm_block_type = style_norm_block_type
-        self.norm_0 = _style_norm(style_norm_block_type, label_nc, f_in, hidden_nc, kernel_size, padding, norm_layer)
-        self.norm_1 = _style_norm(style_norm_block_type, label_nc, f_mid, hidden_nc, kernel_size, padding, norm_layer)
-        self.norm_s = _style_norm(style_norm_block_type, label_nc, f_in, hidden_nc, kernel_size, padding, norm_layer)
+        self.norm_0 = _style_norm(style_norm_block_type, label_nc, f_in, hidden_nc, kernel_size, padding, norm_layer, embed_nc, style_distill)
+        self.norm_1 = _style_norm(style_norm_block_type, label_nc, f_mid, hidden_nc, kernel_size, padding, norm_layer, embed_nc, style_distill)
+        self.norm_s = _style_norm(style_norm_block_type, label_nc, f_in, hidden_nc, kernel_size, padding, norm_layer, embed_nc, style_distill)
         self.act = get_act_layer(act_layer)
         mk = lambda a, b: nn.Conv2d(a, b, kernel_size=kernel_size, stride=stride, padding=padding,  # noqa: E731
                                     padding_mode=padding_mode, bias=bias)
@@ -390,11 +436,12 @@ class NormResBlock(nn.Module):
         xa = Fn.to_nhwc(x)
         n, _, h, w = xa.shape
         dev = xa.t.device
-        s = self.norm_0(xa, labels, relu=self._relu, out_pad=_fusable_pad(self._spec0))
+        kind = self.style_norm_block_type
+        s = _style_forward(kind, self.norm_0, xa, labels, style_feat, 1, self._relu, _fusable_pad(self._spec0))
         noise, nw = _noise_args(self.noise_0, n, h, w, dev)
         y = Fn.conv(s, self.conv_0, _consumer_spec(self._spec0, s), self.conv_0.training, bias=self.conv_0.bias, noise=noise, noise_w=nw,
                     want_stats="sample")
-        s = self.norm_1(y, labels, relu=self._relu, out_pad=_fusable_pad(self._spec1))
+        s = _style_forward(kind, self.norm_1, y, labels, style_feat, 1, self._relu, _fusable_pad(self._spec1))
         noise, nw = _noise_args(self.noise_1, n, h, w, dev)
         y = Fn.conv(s, self.conv_1, _consumer_spec(self._spec1, s), self.conv_1.training, bias=self.conv_1.bias, noise=noise, noise_w=nw,
                     residual=xa, want_stats="sample" if (stats_out and not plain) else None)
@@ -470,3 +517,37 @@ class MaskToken(nn.Module):
         elif isinstance(self.mask_token, nn.Parameter):
             token = self.mask_token
         return _MaskBlend.apply(imgs, token, coarse, int(h_shift), int(w_shift), int(patch_size))
+
+
+class EmbedEncoder(nn.Module):
+    """architecture.py:420-431 (imported by extractor.py; only the commented-out StyleExtractor used it)."""
+
+    def __init__(self, embed_nc, hidden_nc):
+        super().__init__()
+        self.mlp_shared = nn.Sequential(nn.Linear(embed_nc, hidden_nc), nn.ReLU(inplace=True),
+                                        nn.Linear(hidden_nc, hidden_nc), nn.ReLU(inplace=True))
+
+    def forward(self, feat):
+        if feat.dim() == 3:
+            feat = feat.mean(dim=1)
+        h = Fn.linear(feat.float(), self.mlp_shared[0], act="relu")
+        return Fn.linear(h, self.mlp_shared[2], act="relu")
+
+
+class LatentDecoder(nn.Module):
+    """architecture.py:434-448: labels | N(0, 1) noise -> two Linear + ReLU.  The noise is drawn on the host exactly as the
+    reference draws it (`torch.randn(...).to(device)`), so a seeded run sees the same values."""
+
+    def __init__(self, label_nc, hidden_nc, latent_dim):
+        super().__init__()
+        self.mlp_latent = nn.Sequential(nn.Linear(latent_dim, hidden_nc // 2), nn.ReLU(inplace=True),
+                                        nn.Linear(hidden_nc // 2, hidden_nc), nn.ReLU(inplace=True))
+        self.noise_dim = latent_dim - label_nc
+
+    def forward(self, labels):
+        if labels.dim() == 4:
+            labels = labels.view(labels.size(0), -1)
+        noise = torch.randn(labels.size(0), self.noise_dim).to(labels.device)
+        latent = torch.cat([labels.float(), noise], dim=1)
+        h = Fn.linear(latent, self.mlp_latent[0], act="relu")
+        return Fn.linear(h, self.mlp_latent[2], act="relu")

@@ -1,4 +1,6 @@
-"""DefectGanGenerator (models/networks/generator.py:52-275) on the sm_100a kernels; SPADE variant, skip_conn=False."""
+"""DefectGanGenerator (models/networks/generator.py:52-328) on the sm_100a kernels; SPADE / SEAN / AdaIN variants, skip_conn=False."""
+import math
+
 import torch
 from torch import nn
 
@@ -7,6 +9,7 @@ from ...ops import ConvSpec
 from .architecture import (ConvBlock, DeConvBlock, NormConvBlock, NormResBlock, ResBlock, _consumer_spec, _edge, _fusable_pad, _spec_of,
                            next_pad, same_frame)
 from .base_network import BaseNetwork
+from .normalization import SEAN
 
 
 class WGanGenerator(BaseNetwork):
@@ -114,3 +117,51 @@ class DefectGanGenerator(BaseNetwork):
         # identity on finite activations and would cost a device->host sync per forward.
         hd = Fn.conv_cat(feat, self.foreground_head._conv, self.distribution_head._conv, _consumer_spec(self._head_spec, feat), out_fp32=True)
         return Fn.compose(hd.t, x, self.cycle_gan)
+
+    # ---- SEAN bookkeeping (generator.py:276-328) ----
+    def _seans(self):
+        return [m for m in self.modules() if isinstance(m, SEAN)]
+
+    def update_per_epoch(self, epoch):
+        super().update_per_epoch(epoch)
+        alpha = (1 + math.cos(math.pi * epoch / self.opt.num_epochs)) / 2
+        if self.opt.style_norm_block_type == "sean":
+            if self.opt.sean_alpha is None:
+                self.set_sean_alpha(alpha)
+            if self.opt.use_running_stats:
+                self.update_stats()
+
+    def set_sean_alpha(self, alpha):
+        for m in self._seans():
+            m.set_alpha(alpha)
+
+    def enable_sean_distill_loss(self, enable_distill_loss):
+        for m in self._seans():
+            m.distill_loss = enable_distill_loss
+
+    def get_sean_distill_loss(self):
+        return {"latent": [], "embed": []}  # style_distill is not mirrored (normalization.SEAN docstring)
+
+    def update_stats(self):
+        for m in self._seans():
+            m.update_stats()
+
+    @property
+    def track_running_stats(self):
+        for m in self._seans():
+            return m.track_running_stats
+
+    @track_running_stats.setter
+    def track_running_stats(self, value):
+        for m in self._seans():
+            m.track_running_stats = value
+
+    @property
+    def inference_running_stats(self):
+        for m in self._seans():
+            return m.inference_running_stats
+
+    @inference_running_stats.setter
+    def inference_running_stats(self, value):
+        for m in self._seans():
+            m.inference_running_stats = value

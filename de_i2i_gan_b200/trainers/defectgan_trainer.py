@@ -56,7 +56,8 @@ class GraphedStep:
             self.states[key] = {}
             return self.body(*inputs)
         if "graph" not in st:
-            dev = self.optimizer.flat_params[0].device
+            first = self.optimizer[0] if isinstance(self.optimizer, (list, tuple)) else self.optimizer
+            dev = first.flat_params[0].device
             st["static"] = [torch.empty(t.shape, dtype=t.dtype, device=dev) for t in inputs]
             self._stage(st["static"], inputs)
             torch.cuda.synchronize()
@@ -68,7 +69,8 @@ class GraphedStep:
             st["graph"] = graph
         else:
             self._stage(st["static"], inputs)
-        self.optimizer.advance()
+        for o in (self.optimizer if isinstance(self.optimizer, (list, tuple)) else (self.optimizer,)):
+            o.advance()
         st["graph"].replay()
         return st["out"]
 
@@ -79,6 +81,8 @@ class DefectGanTrainer(BaseTrainer):
         assert len(opt.loss_weight) == 5, f"length of loss weights must be 5, not {len(opt.loss_weight)}"
         self.loss_weights = dict(zip(("clf_d", "clf_g", "rec", "sd_cyc", "sd_con"), opt.loss_weight))
         self.loss_types = ["gan", "clf", "aux"]
+        if opt.style_norm_block_type == "sean" and opt.style_distill:
+            self.loss_types.append("distill")  # never reached: DefectGanGenerator refuses style_distill (normalization.SEAN)
         self._init_losses()
         if opt.phase == "val":
             raise NotImplementedError("--phase val (FID / IS / LPIPS with downloaded Inception weights) is out of the hot-path scope")
@@ -88,13 +92,26 @@ class DefectGanTrainer(BaseTrainer):
         if use_graph is None:
             use_graph = os.environ.get("DEI2I_CUDA_GRAPH", "1") != "0"
         use_graph = bool(use_graph) and torch.device(opt.device).type == "cuda"
+        # the style vector of the AdaIN variant comes from a third network, netE, stepped with the generator
+        # (defectgan_trainer.py:140-141,162-163)
+        self._has_e = "E" in self.optimizers
+        # host-side draws inside the loss graph cannot be captured: SEAN picks stored embeddings with python's `random.choices`
+        # (defectgan_model.py:408), the sean_alpha == 0 StyleExtractor draws its noise on the host (extractor.py:85)
+        kind = opt.style_norm_block_type
+        if (kind == "sean" and opt.sean_alpha != 0) or (kind == "adain" and opt.sean_alpha == 0):
+            use_graph = False
         pool, staged = [None], {}
+        g_opts = [self.optimizers["G"], self.optimizers["E"]] if self._has_e else self.optimizers["G"]
         self._graphed = {"D": GraphedStep(self._d_body, self.optimizers["D"], use_graph, pool, staged),
-                         "G": GraphedStep(self._g_body, self.optimizers["G"], use_graph, pool, staged, reuse_staged=True)}
+                         "G": GraphedStep(self._g_body, g_opts, use_graph, pool, staged, reuse_staged=True)}
 
     def _init_lr(self, opt):
         assert len(opt.lr) in (1, 2), f"length of lr must be 1 or 2, not {len(opt.lr)}"
         self.lr = {"D": opt.lr[0], "G": opt.lr[1]} if len(opt.lr) == 2 else opt.lr[0]
+        if isinstance(self.lr, dict) and opt.style_norm_block_type == "adain":
+            # the reference's dict has no 'E' entry and _create_optimizer raises KeyError for netE (base_trainer.py:86-88); the
+            # extractor is stepped with the generator, so it takes the generator's rate (mae_trainer.py:35 does the same)
+            self.lr["E"] = opt.lr[1]
 
     def _init_losses(self):
         self.losses = {t: defaultdict(list) for t in self.loss_types}
@@ -103,6 +120,8 @@ class DefectGanTrainer(BaseTrainer):
     def _g_body(self, bg_data, df_labels, df_data):
         """zero_grad -> loss graph -> weighted sum -> backward -> (all-reduce) -> Adam; returns the 5 loss scalars stacked."""
         self.optimizers["G"].zero_grad()
+        if self._has_e:
+            self.optimizers["E"].zero_grad()
         for p in self._d_params:
             p.requires_grad_(False)
         try:
@@ -114,6 +133,8 @@ class DefectGanTrainer(BaseTrainer):
             for p in self._d_params:
                 p.requires_grad_(True)
         self._reduce_and_step("G")
+        if self._has_e:
+            self._reduce_and_step("E")
         return torch.stack([gan.detach(), clf.detach(), rec.detach(), cyc.detach(), con.detach()])
 
     def _d_body(self, bg_data, df_labels, df_data):

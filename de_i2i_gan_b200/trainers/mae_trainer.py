@@ -21,9 +21,8 @@ class MAETrainer(BaseTrainer):
         super().__init__(opt)
         self.loss_weights = {"rec": opt.loss_weight[0], "clf_D": opt.loss_weight[1], "clf_G": opt.loss_weight[2]}
         self.loss_types = ["rec", "gan", "clf"]
-        if opt.style_norm_block_type != "spade":
-            raise NotImplementedError("MAETrainer on the CUDA path: style_norm_block_type='spade'")
         self._init_losses()
+        self._has_e = "E" in self.optimizers  # AdaIN variant: the StyleExtractor is stepped with the generator (mae_trainer.py:123-139)
         self.data_types = data_types
         # add mask_token's param (mae_trainer.py:28)
         self.optimizers["G"].add_param_group({"params": self.model.mask_token.parameters()})
@@ -32,6 +31,8 @@ class MAETrainer(BaseTrainer):
     def _init_lr(self, opt):
         assert len(opt.lr) in (1, 2), f"length of lr must be 1 or 2, not {len(opt.lr)}"
         self.lr = {"D": opt.lr[0], "G": opt.lr[1]} if len(opt.lr) == 2 else opt.lr[0]
+        if opt.style_norm_block_type == "adain" and isinstance(self.lr, dict):  # mae_trainer.py:34-35 (which fails on a scalar lr)
+            self.lr["E"] = opt.lr[1]
 
     def _init_losses(self):
         self.losses = {t: defaultdict(list) for t in self.loss_types}
@@ -40,6 +41,8 @@ class MAETrainer(BaseTrainer):
     def _train_generator_once(self, data, labels):
         """mae_trainer.py:121-146."""
         self.optimizers["G"].zero_grad()
+        if self._has_e:
+            self.optimizers["E"].zero_grad()
         for p in self._d_params:  # the reference computes D's gradients here and discards them at D's next zero_grad
             p.requires_grad_(False)
         try:
@@ -50,6 +53,8 @@ class MAETrainer(BaseTrainer):
             for p in self._d_params:
                 p.requires_grad_(True)
         self._reduce_and_step("G")
+        if self._has_e:
+            self._reduce_and_step("E")
         vals = torch.stack([rec_loss.detach(), gan_loss.detach(), clf_loss.detach()]).tolist()
         self.losses["rec"]["train"].append(vals[0])
         self.losses["gan"]["G"].append(vals[1])

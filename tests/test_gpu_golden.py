@@ -55,7 +55,7 @@ def _clear_noise():
     A.set_noise_source(None)
 
 
-def _grad_check(named_params, ref_grads, tag):
+def _grad_check(named_params, ref_grads, tag, l2_bar=8e-2):
     """Whole-network gradients after a ~30-layer BF16 backward chain: rounding compounds through the normalisation
     layers' cancellations, so element-wise max-norm bounds are meaningless for the small-gradient parameters (the CPU
     oracle with BF16 rounding emulated at the same points shows the same: tests/test_bf16_emulation.py).  Checked:
@@ -69,7 +69,7 @@ def _grad_check(named_params, ref_grads, tag):
         got[n], ref[n] = p.grad.detach().float().cpu().flatten(), ref_grads[n].flatten()
     a, b = torch.cat(list(got.values())), torch.cat(list(ref.values()))
     rel_l2 = ((a - b).norm() / b.norm()).item()
-    assert rel_l2 < 8e-2, (tag, "global rel L2", rel_l2)
+    assert rel_l2 < l2_bar, (tag, "global rel L2", rel_l2)
     gnorm = b.norm().item()
     worst = 1.0
     for n in ref:

@@ -280,7 +280,7 @@ def setup_defectgan(args, cfg, dev, rank):
         normalization.CONSTANT_LABEL_CLASSES = False
     B, H = cfg["batch"], cfg["image_size"]
     torch.manual_seed(123)  # fix_rand_seed(123), train_defectgan.py:120 - identical initial weights on every rank
-    opt = options.readme_recipe(image_size=H, batch_size=B, num_critics=1, num_epochs=10, iters_per_epoch=10 ** 6,
+    opt = options.readme_recipe(image_size=H, batch_size=B, num_critics=1, num_epochs=10, iters_per_epoch=10 ** 6, save_latest_freq=10 ** 9,
                                 name="bench", ckpt_dir=__import__("pathlib").Path("/tmp/dei2i_bench_ckpt"))
     opt.device = dev
     trainer = find_trainer_using_model_name(opt.model)(opt)
@@ -295,12 +295,22 @@ def setup_defectgan(args, cfg, dev, rank):
         trainer._train_discriminator_once(b, l, d)
         trainer._train_generator_once(b, l, d)
 
+    def host_epoch(k):
+        """The e2e leg: K iterations through the trainer's own epoch loop (DefectGanTrainer._train_epoch = the body of trainer.train,
+        defectgan_trainer.py:91-120) fed by loaders that hand out the pinned host batch - the call a user of the reference makes.
+        Every iteration copies its 50 MB over PCIe (the loop starts the copy of iteration i + 1 under iteration i) and reads its
+        seven loss scalars back."""
+        b, l, d = host
+        defects = ((d, l, None) for _ in range(k))
+        background = iter(lambda: (b, None, None), None)
+        trainer._train_epoch({"defects": defects, "background": background}, 1)
+
     def eager():
         was = any(g.enabled for g in trainer._graphed.values())
         for g in trainer._graphed.values():
             g.enabled = False
         return was
-    return dict(step=step, host=host, d2h=7 * 4, eager=eager, dense_ref_tflop=DENSE_TFLOP_PER_IMG_256 * B * (H / 256) ** 2,
+    return dict(step=step, host=host, host_epoch=host_epoch, d2h=7 * 4, eager=eager, dense_ref_tflop=DENSE_TFLOP_PER_IMG_256 * B * (H / 256) ** 2,
                 extra={"spade": ("dense full-resolution gamma|beta convolutions" if args.spade_dense else
                                  "gamma|beta evaluated exactly on the 5x5 border-class map of the 1x1 training label map "
                                  "(results identical; FLOPs of the dense evaluation are NOT credited - see executed vs reference TFLOP)")})
@@ -405,13 +415,16 @@ def run_ours(args, cfg):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(inputs, steps, profile):
+    def timed(inputs, steps, profile, epoch=None):
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ops.PROFILE = [] if profile else None
         barrier()
         ev0.record()
-        for _ in range(steps):
-            step(inputs)
+        if epoch is not None:
+            epoch(steps)
+        else:
+            for _ in range(steps):
+                step(inputs)
         ev1.record()
         barrier()
         prof, ops.PROFILE = ops.PROFILE, None
@@ -433,8 +446,12 @@ def run_ours(args, cfg):
     if args.skip_e2e:
         ms_e2e = float("nan")
     else:
-        step(host)  # warm the pinned-host path once
-        ms_e2e, _ = timed(host, args.steps, False)
+        epoch = S.get("host_epoch")
+        if epoch is not None:
+            epoch(2)  # warm the pinned-host path (landing buffers, copy stream)
+        else:
+            step(host)
+        ms_e2e, _ = timed(host, args.steps, False, epoch=epoch)
     mem_gb = torch.cuda.max_memory_allocated() / 2 ** 30
     # per-kernel pass: a replayed CUDA graph cannot be bracketed kernel by kernel, so the SAME kernels are launched eagerly for
     # the same K steps right after the timed region, every convolution / streaming launch between two CUDA events on the

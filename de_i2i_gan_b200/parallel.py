@@ -51,6 +51,9 @@ def broadcast_module(module: torch.nn.Module, src: int = 0, group=None):
 # take SMs away and push every 148-CTA kernel into a second wave while a bucket is in flight, which costs more than the
 # < 1 ms of exposed NVLink time of a 50-180 MB all-reduce (8 GPUs: 2953.7 vs 2935.7 img/s, 2 GPUs: 747.1 vs 741.8).
 OVERLAP = os.environ.get("DEI2I_DDP_OVERLAP", "0") != "0"
+# Diagnostic only (tools/gpu_scale.sh): replicas run without exchanging gradients, which separates the cost of the collective from the
+# max-over-ranks spread of N power-capped GPUs in a scaling measurement.  Never set it for training.
+SKIP_ALLREDUCE = os.environ.get("DEI2I_DDP_SKIP_ALLREDUCE", "0") == "1"
 
 
 class BucketReducer:
@@ -92,7 +95,7 @@ class BucketReducer:
         if b["done"]:
             return
         b["done"] = True
-        if self.world == 1:
+        if self.world == 1 or SKIP_ALLREDUCE:
             return
         view = self.flat[b["lo"]:b["hi"]]
         if self._stream is not None:
@@ -113,7 +116,7 @@ class BucketReducer:
 
     def finish(self):
         """All buckets reduced and visible to the current stream; re-arms the counters for the next backward."""
-        if not OVERLAP and self.world > 1 and not all(b["done"] for b in self.buckets):
+        if not OVERLAP and self.world > 1 and not SKIP_ALLREDUCE and not all(b["done"] for b in self.buckets):
             # one all-reduce of the whole flat vector after the backward (see OVERLAP)
             for b in self.buckets:
                 b["done"] = True
@@ -126,7 +129,7 @@ class BucketReducer:
                 self.flat.div_(self.world)
         for b in self.buckets:
             self._launch(b)
-        if self._stream is not None and self.world > 1:
+        if self._stream is not None and self.world > 1 and not SKIP_ALLREDUCE:
             torch.cuda.current_stream().wait_stream(self._stream)
         self.reset()
 

@@ -35,15 +35,52 @@ class GraphedStep:
         # The D-step and the G-step of one iteration are fed the same batch (defectgan_trainer.py:91-112): the second step takes
         # a device-to-device copy instead of a second trip over PCIe.  Shared between the two GraphedSteps of a trainer.
         self.staged = staged if staged is not None else {}
+        self._copy_stream, self._landing, self._prefetched = None, {}, None
+
+    @staticmethod
+    def _key(t):
+        return (t.data_ptr(), t._version, tuple(t.shape), t.dtype)
+
+    def prefetch(self, *inputs):
+        """Start the host-to-device copy of the NEXT call's inputs on a side stream, so that it runs under the step in flight instead
+        of in front of its own (8 ranks copying 50 MB each at the same instant share PCIe switches; with a gradient all-reduce per step
+        the slowest copy of every step is exposed on every rank).  The call that later receives the same pinned tensors takes a
+        device-to-device copy from the landing buffers.  Pageable tensors are left to the ordinary path."""
+        if not self.enabled or not all((not t.is_cuda) and t.is_pinned() for t in inputs):
+            return
+        if self._copy_stream is None:
+            self._copy_stream = torch.cuda.Stream()
+        sig = tuple((tuple(t.shape), t.dtype) for t in inputs)
+        bufs = self._landing.get(sig)
+        if bufs is None:
+            dev = (self.optimizer[0] if isinstance(self.optimizer, (list, tuple)) else self.optimizer).flat_params[0].device
+            bufs = self._landing[sig] = [torch.empty(t.shape, dtype=t.dtype, device=dev) for t in inputs]
+        # the landing buffers may still be the source of the previous call's device-to-device copies on the compute stream
+        self._copy_stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self._copy_stream):
+            for b, t in zip(bufs, inputs):
+                b.copy_(t, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+        self._prefetched = ({self._key(t): b for t, b in zip(inputs, bufs)}, ev)
 
     def _stage(self, statics, inputs):
         fresh = {}
+        landed, ev = self._prefetched if self._prefetched is not None else ({}, None)
+        waited = False
         for s, t in zip(statics, inputs):
-            key = (t.data_ptr(), t._version, tuple(t.shape), t.dtype)
+            key = self._key(t)
             src = self.staged.get(key) if (self.reuse_staged and not t.is_cuda) else None
+            if src is None and not t.is_cuda and key in landed:
+                if not waited:
+                    torch.cuda.current_stream().wait_event(ev)
+                    waited = True
+                src = landed[key]
             s.copy_(src if src is not None else t, non_blocking=True)
             if not t.is_cuda:
                 fresh[key] = s
+        if waited:
+            self._prefetched = None
         self.staged.clear()
         self.staged.update(fresh)
 
@@ -154,9 +191,13 @@ class DefectGanTrainer(BaseTrainer):
         self.losses["aux"]["cyc"].append(vals[3])
         self.losses["aux"]["con"].append(vals[4])
 
-    def _train_discriminator_once(self, bg_data, df_labels, df_data):
-        """defectgan_trainer.py:170-180."""
-        vals = self._graphed["D"](bg_data, df_labels, df_data).tolist()
+    def _train_discriminator_once(self, bg_data, df_labels, df_data, upcoming=None):
+        """defectgan_trainer.py:170-180.  ``upcoming``: the next iteration's (bg_data, df_labels, df_data), if the caller already holds it -
+        its host-to-device copy is started under this step (GraphedStep.prefetch)."""
+        out = self._graphed["D"](bg_data, df_labels, df_data)
+        if upcoming is not None:
+            self._graphed["D"].prefetch(*upcoming)
+        vals = out.tolist()
         self.losses["gan"]["D"].append(vals[0])
         self.losses["clf"]["D"].append(vals[1])
 
@@ -178,16 +219,24 @@ class DefectGanTrainer(BaseTrainer):
     def _train_epoch(self, data_loaders, epoch):
         """defectgan_trainer.py:91-120 (progress bar omitted): one D-step per iteration, one G-step every
         ``num_critics`` iterations, 'latest' checkpoint + iter.txt every ``save_latest_freq`` iterations."""
-        for df_data, df_labels, _ in data_loaders["defects"]:
+        def batches():
+            for df_data, df_labels, _ in data_loaders["defects"]:
+                bg_data, _, _ = next(data_loaders["background"])
+                yield bg_data[: df_data.size(0)], df_labels, df_data
+
+        it = batches()
+        cur = next(it, None)
+        while cur is not None:
+            nxt = next(it, None)  # one batch of look-ahead: its copy to the device runs under this iteration's steps
             self.iters += 1
-            bg_data, _, _ = next(data_loaders["background"])
-            bg_data = bg_data[: df_data.size(0)]
-            self._train_discriminator_once(bg_data, df_labels, df_data)
+            bg_data, df_labels, df_data = cur
+            self._train_discriminator_once(bg_data, df_labels, df_data, upcoming=nxt)
             if self.iters % self.opt.num_critics == 0:
                 self._train_generator_once(bg_data, df_labels, df_data)
             if self.iters % self.opt.save_latest_freq == 0 and self.rank == 0:
                 self.model.save("latest")
                 np.savetxt(self.iter_record_path, (epoch, self.iters), fmt="%i", delimiter=",")
+            cur = nxt
 
     def _make_writer(self):
         if self.rank != 0 or getattr(self.opt, "log_dir", None) is None:

@@ -103,3 +103,37 @@ def test_graphed_inference_matches_eager(tmp_path, monkeypatch):
     # replay with stale weights or inputs is off by > 1e-1: tools/debug_graph_inf.py)
     assert (out_g - out_e).abs().max().item() < 3e-2 and (prob_g - prob_e).abs().max().item() < 3e-2
     assert (out_g - out_e).abs().mean().item() < 2e-3
+
+
+def test_epoch_loop_prefetch_is_invisible(tmp_path):
+    """DefectGanTrainer._train_epoch starts the host-to-device copy of batch i + 1 under iteration i (GraphedStep.prefetch) when the
+    loader hands out pinned tensors: the losses of every iteration are bit-identical to the same loop fed pageable tensors (which
+    take the ordinary in-line copy) - landing buffers are never read before their copy has finished nor overwritten while in use."""
+    from de_i2i_gan_b200.models.networks import architecture as A
+    g = torch.Generator().manual_seed(9)
+    batches = []
+    for _ in range(6):
+        bg = torch.randn(2, 3, 128, 128, generator=g).clamp(-1, 1)
+        df = torch.randn(2, 3, 128, 128, generator=g).clamp(-1, 1)
+        lab = (torch.rand(2, 6, generator=g) > 0.5).float()
+        lab[:, 0] = 0
+        batches.append((bg, lab, df))
+    A.set_noise_source(_noise)
+    try:
+        runs = {}
+        for pinned in (False, True):
+            tr = _trainer(True, tmp_path)
+            conv = (lambda t: t.pin_memory()) if pinned else (lambda t: t.clone())
+            data = [tuple(conv(t) for t in b) for b in batches]
+            calls = []
+            orig = tr._graphed["D"].prefetch
+            tr._graphed["D"].prefetch = lambda *a, _o=orig: (calls.append(1), _o(*a))[1]
+            loaders = {"defects": ((df, lab, None) for bg, lab, df in data), "background": iter([(bg, None, None) for bg, lab, df in data])}
+            tr._train_epoch(loaders, 1)
+            torch.cuda.synchronize()
+            assert tr.iters == 6 and len(calls) == 5  # every batch but the first is announced one iteration ahead
+            assert (tr._graphed["D"]._copy_stream is not None) == pinned
+            runs[pinned] = [list(tr.losses[a][b]) for a, b in (("gan", "D"), ("clf", "D"), ("gan", "G"), ("aux", "rec"), ("aux", "cyc"))]
+        assert runs[True] == runs[False]
+    finally:
+        A.set_noise_source(None)

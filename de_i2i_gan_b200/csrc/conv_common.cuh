@@ -90,6 +90,10 @@ struct TmaConvParams {
   // Plain convolutions: b_sub = 1, b_py = b_px = 0, b_kw = kw.  Strided dgrad = stride^2 stride-1 sub-convolutions over dY,
   // one per output parity (py, px), each using every stride-th tap of the full filter.
   int b_sub, b_py, b_px, b_kw;
+  // npar > 1: ONE launch covers all b_sub^2 parity sub-convolutions - work tile = (m tile, n tile, parity), parity fastest so that
+  // the CTAs of a wave share the dY tiles (identical for the four parities) in L2; the tile's (py, px) replace b_py / b_px and are
+  // added to om.oy0 / om.ox0.  Four launches of 28 .. 64 CTAs each become one of 112 .. 148.
+  int npar;
   int num_kb;      // taps * cin_blocks
   int m_tiles, n_tiles;
   OutMap om;

@@ -701,20 +701,15 @@ int conv_dgrad_tf32(const float* dy, const float* w_dgrad, float* dx, const dei2
   if (g->stride > 1) {
     if (!(g->pad == 0 && g->kh == g->kw && g->kh % g->stride == 0 && (g->H - g->kh) % g->stride == 0 && (g->W - g->kw) % g->stride == 0)) return 1;
     const int sd = g->stride, kt = g->kh / sd;
-    for (int py = 0; py < sd; ++py)
-      for (int px = 0; px < sd; ++px) {
-        TmaConvParams t;
-        memset(&t, 0, sizeof(t));
-        t.Ho = g->H / sd; t.Wo = g->W / sd; t.M = (long long)g->N * t.Ho * t.Wo; t.stride = 1; t.lower = -(kt - 1); t.lower_w = -(kt - 1);
-        t.kh = kt; t.kw = kt; t.flip = 1; t.cin_blocks = g->Cout_ld / 32; t.num_kb = kt * kt * t.cin_blocks;
-        t.b_sub = sd; t.b_py = py; t.b_px = px; t.b_kw = g->kw;
-        t.om.linear = 0; t.om.Ho = t.Ho; t.om.Wo = t.Wo; t.om.OH = g->H; t.om.OW = g->W; t.om.osy = sd; t.om.osx = sd;
-        t.om.oy0 = py; t.om.ox0 = px;
-        t.e.scale = scale; t.e.out = dx; t.e.act = 0; t.e.out_fp32 = 1; t.e.ld = g->Cin; t.e.ncols = g->Cin;
-        if (int rc = run_conv_tma(dy, g->N, Ho, Wo, g->Cout_ld, w_dgrad, g->Cin, round_up(g->kh * g->kw * g->Cout_ld, 64), t, 0, 0, st, true))
-          return rc;
-      }
-    return 0;
+    TmaConvParams t;
+    memset(&t, 0, sizeof(t));
+    t.Ho = g->H / sd; t.Wo = g->W / sd; t.M = (long long)g->N * t.Ho * t.Wo; t.stride = 1; t.lower = -(kt - 1); t.lower_w = -(kt - 1);
+    t.kh = kt; t.kw = kt; t.flip = 1; t.cin_blocks = g->Cout_ld / 32; t.num_kb = kt * kt * t.cin_blocks;
+    t.b_sub = sd; t.b_py = 0; t.b_px = 0; t.b_kw = g->kw; t.npar = sd * sd;
+    t.om.linear = 0; t.om.Ho = t.Ho; t.om.Wo = t.Wo; t.om.OH = g->H; t.om.OW = g->W; t.om.osy = sd; t.om.osx = sd;
+    t.om.oy0 = 0; t.om.ox0 = 0;
+    t.e.scale = scale; t.e.out = dx; t.e.act = 0; t.e.out_fp32 = 1; t.e.ld = g->Cin; t.e.ncols = g->Cin;
+    return run_conv_tma(dy, g->N, Ho, Wo, g->Cout_ld, w_dgrad, g->Cin, round_up(g->kh * g->kw * g->Cout_ld, 64), t, 0, 0, st, true);
   }
   TmaConvParams t;
   memset(&t, 0, sizeof(t));
@@ -820,22 +815,17 @@ extern "C" int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx,
       (g->W - g->kw) % g->stride == 0 && tma_applicable(g, g->Cout_ld, 0)) {
     // fractionally-strided ("transposed") convolution as stride^2 dense stride-1 sub-convolutions over dY:
     //   dX[s*a + py, s*b + px] = sum_{t,u} dY[a - t, b - u] * W[py + s*t, px + s*u]      (no multiply-by-zero work)
+    // All stride^2 parities in ONE launch (TmaConvParams::npar): the deep discriminator layers have 7 .. 16 work tiles per parity.
     const int sd = g->stride, kt = g->kh / sd;
-    for (int py = 0; py < sd; ++py)
-      for (int px = 0; px < sd; ++px) {
-        TmaConvParams t;
-        memset(&t, 0, sizeof(t));
-        t.Ho = g->H / sd; t.Wo = g->W / sd; t.M = (long long)g->N * t.Ho * t.Wo; t.stride = 1; t.lower = -(kt - 1); t.lower_w = -(kt - 1);
-        t.kh = kt; t.kw = kt; t.flip = 1; t.cin_blocks = g->Cout_ld / 64; t.num_kb = kt * kt * t.cin_blocks;
-        t.b_sub = sd; t.b_py = py; t.b_px = px; t.b_kw = g->kw;
-        t.om.linear = 0; t.om.Ho = t.Ho; t.om.Wo = t.Wo; t.om.OH = g->H; t.om.OW = g->W; t.om.osy = sd; t.om.osx = sd;
-        t.om.oy0 = py; t.om.ox0 = px;
-        t.e.scale = scale; t.e.out = dx; t.e.act = 0; t.e.out_fp32 = out_fp32; t.e.ld = g->Cin; t.e.ncols = g->Cin;
-        if (int rc = run_conv_tma(dy, g->N, Ho, Wo, g->Cout_ld, w_dgrad, g->Cin, g->kh * g->kw * g->Cout_ld, t, 0, 0,
-                                  (cudaStream_t)stream))
-          return rc;
-      }
-    return 0;
+    TmaConvParams t;
+    memset(&t, 0, sizeof(t));
+    t.Ho = g->H / sd; t.Wo = g->W / sd; t.M = (long long)g->N * t.Ho * t.Wo; t.stride = 1; t.lower = -(kt - 1); t.lower_w = -(kt - 1);
+    t.kh = kt; t.kw = kt; t.flip = 1; t.cin_blocks = g->Cout_ld / 64; t.num_kb = kt * kt * t.cin_blocks;
+    t.b_sub = sd; t.b_py = 0; t.b_px = 0; t.b_kw = g->kw; t.npar = sd * sd;
+    t.om.linear = 0; t.om.Ho = t.Ho; t.om.Wo = t.Wo; t.om.OH = g->H; t.om.OW = g->W; t.om.osy = sd; t.om.osx = sd;
+    t.om.oy0 = 0; t.om.ox0 = 0;
+    t.e.scale = scale; t.e.out = dx; t.e.act = 0; t.e.out_fp32 = out_fp32; t.e.ld = g->Cin; t.e.ncols = g->Cin;
+    return run_conv_tma(dy, g->N, Ho, Wo, g->Cout_ld, w_dgrad, g->Cin, g->kh * g->kw * g->Cout_ld, t, 0, 0, (cudaStream_t)stream);
   }
   const bool full = g->pad_mode == DEI2I_PAD_REFLECT;
   const int Hd = full ? g->H + 2 * g->pad : g->H, Wd = full ? g->W + 2 * g->pad : g->W;

@@ -64,7 +64,8 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   constexpr uint32_t kTmemCols = 2 * MS * BLOCK_N < 32 ? 32 : 2 * MS * BLOCK_N;
-  const int total_tiles = p.m_tiles * p.n_tiles;
+  const int npar = p.npar > 1 ? p.npar : 1;
+  const int total_tiles = p.m_tiles * p.n_tiles * npar;
   __shared__ __align__(16) float bias_s[1024];
   __shared__ float2 wstat[2][2][4][32];  // [epilogue group][parity][row quarter][column]: (mean, M2) of 32 rows
   const bool bias_in_smem = p.e.bias != nullptr && p.n_tiles * BLOCK_N <= 1024;
@@ -98,8 +99,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       const int HoWo = p.Ho * p.Wo;
       uint32_t it = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
-        const int m_tile = tile / p.n_tiles;
-        const int n_tile = tile - m_tile * p.n_tiles;
+        const int par = tile % npar, t2 = tile / npar;
+        const int b_py = npar > 1 ? par / p.b_sub : p.b_py, b_px = npar > 1 ? par % p.b_sub : p.b_px;
+        const int m_tile = t2 / p.n_tiles;
+        const int n_tile = t2 - m_tile * p.n_tiles;
         int img[MS], cw[MS], ch[MS];
 #pragma unroll
         for (int ms = 0; ms < MS; ++ms) {
@@ -123,7 +126,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 #pragma unroll
           for (int ms = 0; ms < MS; ++ms)
             tma_load_im2col_4d(a_dst + ms * kTmaATile, &tmap_a, &full_bar[stage], cb * KC, cw[ms], ch[ms], img[ms], (uint16_t)os, (uint16_t)orr);
-          const int bcol = (((p.b_py + p.b_sub * r) * p.b_kw + (p.b_px + p.b_sub * s)) * p.cin_blocks + cb) * KC;
+          const int bcol = (((b_py + p.b_sub * r) * p.b_kw + (b_px + p.b_sub * s)) * p.cin_blocks + cb) * KC;
           tma_load_2d(a_dst + MS * kTmaATile, &tmap_b, &full_bar[stage], bcol, n_tile * BLOCK_N);
           if (++cb == p.cin_blocks) {
             cb = 0;
@@ -187,8 +190,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     const int my_sw = (lane >> 1) & 3;  // swizzle of this lane's own row
     uint32_t ti = 0, spar = 0;
     for (int tile = blockIdx.x + eg * gridDim.x; tile < total_tiles; tile += 2 * gridDim.x, ++ti) {
-      const int m_tile = tile / p.n_tiles;
-      const int n0 = (tile - m_tile * p.n_tiles) * BLOCK_N;
+      const int par = tile % npar, t2 = tile / npar;
+      const int oy0 = om.oy0 + (npar > 1 ? par / p.b_sub : 0), ox0 = om.ox0 + (npar > 1 ? par % p.b_sub : 0);
+      const int m_tile = t2 / p.n_tiles;
+      const int n0 = (t2 - m_tile * p.n_tiles) * BLOCK_N;
       mbar_wait(&tfull_bar[eg], ti & 1u);
       tc_fence_after();
 #pragma unroll 1
@@ -205,7 +210,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           const int rem = (int)(m - (long long)img * HoWo);
           const int pr = rem / om.Wo;
           const int qc = rem - pr * om.Wo;
-          orow = ((long long)img * om.OH + (pr * om.osy + om.oy0)) * om.OW + (qc * om.osx + om.ox0);
+          orow = ((long long)img * om.OH + (pr * om.osy + oy0)) * om.OW + (qc * om.osx + ox0);
         }
         float nz = 0.f;
         if (e.noise != nullptr && row_ok) nz = __ldg(e.noise + m) * nzw;
@@ -385,7 +390,7 @@ static int launch_tma(const CUtensorMap& ta, const CUtensorMap& tb, const TmaCon
     DEI2I_CUDA(cudaFuncSetAttribute(conv_tma_kernel<BN, ST, MS, TF32>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
     attr_done = true;
   }
-  const int total = p.m_tiles * p.n_tiles;
+  const int total = p.m_tiles * p.n_tiles * (p.npar > 1 ? p.npar : 1);
   const int grid = total < num_sms() ? total : num_sms();
   conv_tma_kernel<BN, ST, MS, TF32><<<grid, kTmaThreads, S::kTotal, st>>>(ta, tb, p);
   count_launch();
@@ -424,7 +429,7 @@ int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, in
   // narrow N: two 128-pixel A tiles share each B tile (halves the weight traffic per FLOP through L2 / shared memory) as long
   // as that still leaves every SM a couple of work tiles
   const long long mt2 = (p.M + 255) / 256;
-  int ms = (bn <= 128 && mt2 * p.n_tiles >= 2ll * num_sms()) ? 2 : 1;
+  int ms = (bn <= 128 && mt2 * p.n_tiles * (p.npar > 1 ? p.npar : 1) >= 2ll * num_sms()) ? 2 : 1;
   if (g_tune_tma_ms == 1 || (g_tune_tma_ms == 2 && bn <= 128)) ms = g_tune_tma_ms;
   p.m_tiles = (int)((p.M + 128 * ms - 1) / (128 * ms));
   if (ms == 2) return bn == 128 ? launch_tma<128, 4, 2>(ta, tb, p, st) : launch_tma<64, 5, 2>(ta, tb, p, st);

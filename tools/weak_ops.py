@@ -54,6 +54,11 @@ def main():
     if "d5" in names:
         conv_case(32, 1024, 10, 10, 2048, 4, 4, 2, "fdw")
         conv_case(32, 512, 18, 18, 1024, 4, 4, 2, "fdw")
+    if "dlayers" in names:  # the discriminator's strided 4x4 chain (pre-padded inputs) at 256^2 and the generator's two encoder convs
+        for cin, hin in ((64, 130), (128, 66), (256, 34), (512, 18), (1024, 10)):
+            conv_case(32, cin, hin, hin, 2 * cin, 4, 4, 2, "d")
+        conv_case(32, 64, 258, 258, 128, 4, 4, 2, "d")
+        conv_case(32, 128, 130, 130, 256, 4, 4, 2, "d")
     if "heads" in names:
         conv_case(32, 64, 258, 258, 4, 3, 3, 1, "fdw")
     if "spade_bwd" in names:

@@ -51,6 +51,23 @@ def weight_cache():
             _cache = None
 
 
+BATCH_LABEL_SETS = os.environ.get("DEI2I_BATCH_LABEL_SETS", "1") != "0"  # A/B switch of announce_label_sets
+
+
+def label_key(labels: torch.Tensor):
+    """Identity of a label tensor inside one weight_cache() scope (the generator stamps it on the carrier it hands to SPADE)."""
+    return (labels.data_ptr(), labels._version, tuple(labels.shape))
+
+
+def announce_label_sets(*label_tensors):
+    """The loss graphs of a training step condition the generator on TWO label tensors (defect labels, normal labels:
+    defectgan_model.py:185-205).  Announced at the top of a weight_cache() scope, every SPADE module evaluates its class-map
+    convolutions for both in ONE batched pass (models/networks/normalization.py) - half the launches of kernels that are
+    launch-latency bound (32 x 25 pixels each).  No effect outside a scope or when fewer than two tensors are given."""
+    if _cache is not None and len(label_tensors) > 1 and BATCH_LABEL_SETS:
+        _cache["label_sets"] = tuple(label_tensors)
+
+
 class Weights:
     __slots__ = ("w_fwd", "w_dgrad", "scale", "sn")
 

@@ -306,4 +306,6 @@ class DefectGanModel(BaseModel):
             nm_feat = self.netE(bg_data, nm_rows)
             df_feat = self.netE(df_data, df_labels)
         nm_labels, df_labels = self._labels(df_labels)
+        if kind == "spade":  # both label tensors of the loss graph go through each SPADE module's class-map convolutions together
+            Fn.announce_label_sets(df_labels, nm_labels)
         return nm_labels, nm_feat, df_labels, df_feat

@@ -97,7 +97,7 @@ class DefectGanGenerator(BaseNetwork):
         if labels.dim() == 2:
             labels = labels.reshape(labels.size(0), labels.size(1), 1, 1)
         seg = Fn.to_nhwc(labels.float())
-        seg.key = (labels.data_ptr(), labels._version, tuple(labels.shape))
+        seg.key = Fn.label_key(labels)
         Fn.prefetch_spectral_norm(self, self.training)
         enc = list(self.enc_blk)
         feat = self.stem(x, carrier_out=True, out_pad=next_pad([self.stem] + enc, 0))

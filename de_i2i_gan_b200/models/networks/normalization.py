@@ -33,6 +33,32 @@ class SPADE(nn.Module):
         self._shared_spec = ConvSpec(label_nc, hidden_nc, k, 1, pad, "zeros")
         self._gb_spec = ConvSpec(hidden_nc, 2 * norm_nc, k, 1, pad, "zeros")
 
+    def _gb5(self, cls5):
+        """mlp_shared -> ReLU -> (mlp_gamma | mlp_beta as one N = 2C convolution) on [n, 5, 5, label_nc] border-class maps."""
+        sconv = self.mlp_shared[0]
+        actv = Fn.conv(cls5, sconv, self._shared_spec, self.training, bias=sconv.bias, act="relu")
+        return Fn.conv_cat(actv, self.mlp_gamma, self.mlp_beta, self._gb_spec)
+
+    def _gb5_for_label_sets(self, seg, n, ck):
+        """All label tensors announced for this scope (Fn.announce_label_sets) in one batched evaluation; each set's slice is cached
+        under its own key, the one asked for is returned.  None when `seg` is not one of the announced sets."""
+        sets = Fn._cache.get("label_sets")
+        if not sets or seg.key not in [Fn.label_key(t) for t in sets] or any(tuple(t.shape) != tuple(sets[0].shape) for t in sets):
+            return None
+        cat = Fn._cache.get(("cls5cat", n))
+        if cat is None:
+            maps = [Fn.to_nhwc(t.float()) for t in sets]
+            cat = Fn.Nhwc(torch.cat([m.t.expand(n, 5, 5, m.t.shape[3]) for m in maps], dim=0).contiguous(), maps[0].c)
+            Fn._cache[("cls5cat", n)] = cat
+        gb_all = self._gb5(cat)
+        mine = None
+        for t, part in zip(sets, torch.split(gb_all.t, n, dim=0)):
+            k = ("gb5", id(self), Fn.label_key(t)) + ck[3:]
+            Fn._cache[k] = Fn.Nhwc(part, gb_all.c)
+            if k == ck:
+                mine = Fn._cache[k]
+        return mine
+
     def forward(self, x, segmap, up=1, relu=False, out_pad=0):
         """x: NCHW tensor (drop-in) or Nhwc; segmap: [B,label_nc,h,w] NCHW or Nhwc.  ``up`` / ``relu`` are the fused
         followers used by NormConvBlock / NormResBlock (architecture.py:242-244,347-348); defaults = reference SPADE.
@@ -43,13 +69,10 @@ class SPADE(nn.Module):
         seg = Fn.to_nhwc(segmap)
         n, _, hx, wx = xa.shape
         h, w = hx * up, wx * up
-        sconv = self.mlp_shared[0]
         if CONSTANT_LABEL_CLASSES and seg.t.shape[1] == 1 and seg.t.shape[2] == 1 and h >= 5 and w >= 5 \
                 and self._shared_spec.k == 3 and self._shared_spec.pad == 1:
             # 1x1 label map (every training call, defectgan_model.py:185-205): the nearest-resized map is constant, so
             # mlp_shared -> mlp_gamma|mlp_beta are evaluated on the 5x5 border-class map (exact; dei2i_spade_cls_fwd)
-            if seg.cls5 is None:
-                seg.cls5 = Fn.Nhwc(seg.t.expand(n, 5, 5, seg.t.shape[3]).contiguous(), seg.c)
             # gamma|beta depend on the label tensor and this module's weights only: the four generator passes of a G-step use
             # two label tensors (df_labels, nm_labels, nm_labels, df_labels - defectgan_model.py:185-205), so inside one
             # weight_cache() scope (= one loss computation, weights fixed) each is evaluated once and shared; autograd sums
@@ -58,15 +81,19 @@ class SPADE(nn.Module):
             if Fn._cache is not None and seg.key is not None:
                 ck = ("gb5", id(self), seg.key, n, self.training, torch.is_grad_enabled())
             gb5 = Fn._cache.get(ck) if ck is not None else None
+            if gb5 is None and ck is not None:
+                gb5 = self._gb5_for_label_sets(seg, n, ck)
             if gb5 is None:
-                actv = Fn.conv(seg.cls5, sconv, self._shared_spec, self.training, bias=sconv.bias, act="relu")
-                gb5 = Fn.conv_cat(actv, self.mlp_gamma, self.mlp_beta, self._gb_spec)
+                if seg.cls5 is None:
+                    seg.cls5 = Fn.Nhwc(seg.t.expand(n, 5, 5, seg.t.shape[3]).contiguous(), seg.c)
+                gb5 = self._gb5(seg.cls5)
                 if ck is not None:
                     Fn._cache[ck] = gb5
             pad = 0 if plain else out_pad
             out = Fn.spade_modulate_cls(xa, gb5, up=up, relu=relu, eps=self.param_free_norm.eps, out_pad=pad)
             out.pad = pad
             return Fn.from_nhwc(out) if plain else out
+        sconv = self.mlp_shared[0]
         actv = Fn.conv(seg, sconv, self._shared_spec, self.training, bias=sconv.bias, act="relu", logical_hw=(h, w))
         gb = Fn.conv_cat(actv, self.mlp_gamma, self.mlp_beta, self._gb_spec)
         out = Fn.spade_modulate(xa, gb, up=up, relu=relu, eps=self.param_free_norm.eps)

@@ -185,6 +185,26 @@ def from_nhwc(a: Nhwc) -> torch.Tensor:
 EPI_STATS_MAX_COUT = int(os.environ.get("DEI2I_EPI_STATS_MAX_COUT", "0"))
 
 
+_grad_sink = False
+
+
+@contextmanager
+def accumulate_into_grad(enabled=True):
+    """Around a trainer's ``loss.backward()``: weight gradients of the convolutions are accumulated by the wgrad kernel itself
+    (beta = 1) straight into the parameter's existing ``.grad`` buffer - FlatAdam's flat gradient vector, zeroed by zero_grad - instead
+    of being returned to autograd, whose AccumulateGrad then launches one `grad += dw` kernel per arrival (318 per D-step + G-step).
+    Same FP32 additions in the same order (the kernel fuses a spectral-normed weight's final `* 1/sigma` with the accumulate into one
+    FMA: last-bit differences in a few elements).  Not for ``torch.autograd.grad`` and not while
+    post-accumulate-grad hooks must fire (the bucketed all-reduce overlap): those leave it off and get the ordinary path."""
+    global _grad_sink
+    outer = _grad_sink
+    _grad_sink = bool(enabled)
+    try:
+        yield
+    finally:
+        _grad_sink = outer
+
+
 class _Conv(Function):
     """y = act(scale*conv(x) + bias + noise_w*noise) + residual   and its dgrad / wgrad / bias / noise-weight grads.
     want_stats: the epilogue also emits the (mean, var) statistics its BatchNorm / InstanceNorm consumer needs (second, non-
@@ -208,6 +228,7 @@ class _Conv(Function):
         y, stats = res if want_stats is not None else (res, None)
         ctx.wts, ctx.spec, ctx.act, ctx.noise, ctx.logical_hw, ctx.out_pad = wts, spec, act, noise, logical_hw, out_pad
         ctx.has = (bias is not None, noise_w is not None, residual is not None)
+        ctx.w_param = w_param
         ctx.save_for_backward(x, y if act else None)
         if want_stats is None:
             return y
@@ -248,8 +269,14 @@ class _Conv(Function):
                 dx = ops.reflect_fold(dx, ctx.rpad)
         dw = None
         if ctx.needs_input_grad[1]:
-            dw = torch.empty(spec.cout, spec.cin, spec.kh, spec.kw_, dtype=torch.float32, device=dy.device)
-            ops.conv2d_wgrad(x, dy, dw, spec, sn=wts.sn, logical_hw=ctx.logical_hw)
+            w = ctx.w_param
+            sink = w.grad if (_grad_sink and w.is_leaf) else None
+            if sink is not None and sink.dtype == torch.float32 and sink.is_contiguous() \
+                    and tuple(sink.shape) == (spec.cout, spec.cin, spec.kh, spec.kw_):
+                ops.conv2d_wgrad(x, dy, sink, spec, sn=wts.sn, logical_hw=ctx.logical_hw, accumulate=True)  # accumulate_into_grad
+            else:
+                dw = torch.empty(spec.cout, spec.cin, spec.kh, spec.kw_, dtype=torch.float32, device=dy.device)
+                ops.conv2d_wgrad(x, dy, dw, spec, sn=wts.sn, logical_hw=ctx.logical_hw)
         return dx, dw, d_bias, d_nw, d_res, None, None, None, None, None, None, None, None
 
 

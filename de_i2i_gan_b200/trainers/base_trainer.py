@@ -8,6 +8,7 @@ import numpy as np
 import torch
 from torch import optim
 
+from .. import functional as Fn
 from .. import parallel
 from ..models import create_model
 from ..optim import FlatAdam, FlatRMSprop
@@ -93,6 +94,12 @@ class BaseTrainer:
     def _update_per_epoch(self, epoch=None):
         for sched in self.schedulers.values():
             sched.step()
+
+    def _backward(self, loss):
+        """loss.backward() with the weight gradients accumulated by the wgrad kernels themselves (Fn.accumulate_into_grad); the
+        bucketed all-reduce overlap needs autograd's post-accumulate hooks and keeps the ordinary path."""
+        with Fn.accumulate_into_grad(not (self.world_size > 1 and parallel.OVERLAP)):
+            loss.backward()
 
     # ------------------------------------------------------------------------------------------------ data parallel
     def _reduce_and_step(self, name):

@@ -165,7 +165,7 @@ class DefectGanTrainer(BaseTrainer):
             gan, clf, rec, cyc, con = self.model("generator", bg_data, df_labels, df_data)
             w = self.loss_weights
             g_loss = gan + clf * w["clf_g"] + rec * w["rec"] + cyc * w["sd_cyc"] + con * w["sd_con"]
-            g_loss.backward()
+            self._backward(g_loss)
         finally:
             for p in self._d_params:
                 p.requires_grad_(True)
@@ -178,7 +178,7 @@ class DefectGanTrainer(BaseTrainer):
         self.optimizers["D"].zero_grad()
         gan, clf = self.model("discriminator", bg_data, df_labels, df_data)
         d_loss = gan + clf * self.loss_weights["clf_d"]
-        d_loss.backward()
+        self._backward(d_loss)
         self._reduce_and_step("D")
         return torch.stack([gan.detach(), clf.detach()])
 

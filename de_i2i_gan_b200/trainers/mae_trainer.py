@@ -48,7 +48,7 @@ class MAETrainer(BaseTrainer):
         try:
             rec_loss, gan_loss, clf_loss = self.model("mae_generator", data, labels)
             g_loss = gan_loss + rec_loss * self.loss_weights["rec"] + clf_loss * self.loss_weights["clf_G"]
-            g_loss.backward()
+            self._backward(g_loss)
         finally:
             for p in self._d_params:
                 p.requires_grad_(True)
@@ -65,7 +65,7 @@ class MAETrainer(BaseTrainer):
         self.optimizers["D"].zero_grad()
         gan_loss, clf_loss = self.model("mae_discriminator", data, labels)
         d_loss = gan_loss + clf_loss * self.loss_weights["clf_D"]
-        d_loss.backward()
+        self._backward(d_loss)
         self._reduce_and_step("D")
         vals = torch.stack([gan_loss.detach(), clf_loss.detach()]).tolist()
         self.losses["gan"]["D"].append(vals[0])

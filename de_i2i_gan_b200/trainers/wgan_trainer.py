@@ -110,7 +110,7 @@ class WGanTrainer(BaseTrainer):
                 fake_data = self.model.netG(noise)
                 fake_logits = self.model.netD(fake_data)
                 g_loss = -fake_logits.mean()
-                g_loss.backward()
+                self._backward(g_loss)
         finally:
             for p in self._d_params:
                 p.requires_grad_(True)
@@ -126,7 +126,7 @@ class WGanTrainer(BaseTrainer):
             fake_logits = self.model.netD(fake_data.detach_())
             real_logits = self.model.netD(real_data)
             d_loss = -(real_logits.mean() - fake_logits.mean())
-            d_loss.backward()
+            self._backward(d_loss)
         self._reduce_and_step("D")
         return torch.cat([d_loss.detach().reshape(1), real_logits.detach().flatten(), fake_logits.detach().flatten()])
 

@@ -31,6 +31,7 @@ int g_tune_conv_bn = 0;
 int g_tune_wgrad_bn = 0;
 int g_tune_wgrad_waves = 0;
 int g_tune_tma_ms = 0;
+int g_tune_wgrad_swap = 1;   // 1 = operand-swapped wgrad where applicable (conv_igemm.cu), 0 = always the ordinary operand roles
 int g_tune_f32_tf32 = 0;   // FP32-parity path: 1 = forward / dgrad of TMA-able geometries on the kind::tf32 tensor-core kernel
 int g_tune_conv_path = 0;  // 0 = auto (TMA im2col kernels where applicable), 1 = always the cp.async gather kernels
 static std::atomic<long long> g_launches{0};
@@ -193,6 +194,7 @@ extern "C" int dei2i_set_tuning(const char* key, int value) {
   else if (!strcmp(key, "conv_path")) slot = &dei2i::g_tune_conv_path;
   else if (!strcmp(key, "f32_tf32")) slot = &dei2i::g_tune_f32_tf32;
   else if (!strcmp(key, "tma_ms")) slot = &dei2i::g_tune_tma_ms;
+  else if (!strcmp(key, "wgrad_swap")) slot = &dei2i::g_tune_wgrad_swap;
   if (slot == nullptr) return -1;
   int old = *slot;
   *slot = value;

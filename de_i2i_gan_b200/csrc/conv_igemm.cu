@@ -28,6 +28,7 @@ extern int g_tune_conv_stages;  // 0 = auto
 extern int g_tune_conv_bn;      // 0 = auto
 extern int g_tune_wgrad_bn;     // 0 = auto
 extern int g_tune_wgrad_waves;
+extern int g_tune_wgrad_swap;
 extern int g_tune_conv_path;
 void count_launch(int n = 1);
 void trace_kernel(const char* fmt, ...);
@@ -895,6 +896,40 @@ static void wgrad_plan(const dei2i_conv_geom* g, int& bn, int& splits, int& pb_p
   splits = (num_pb + pb_per_split - 1) / pb_per_split;
 }
 
+// Operand-swapped wgrad for few output channels on many input channels (the 128 -> 64 decoder convolution at 256^2):
+//   P'[ci, (tap', co)] = sum over INPUT pixels m' of  x[m', ci] * dY[m' - tap, co]        tap' = taps - 1 - tap
+// x is read ONCE per pixel block as the plain [pixels, Cin] matrix (MMA M = Cin: no zero rows), the small dY tile is what gets
+// re-read per tap (im2col over dY exactly as in dgrad).  Per 64 pixels: 3 x 16 KB of x + 9 x 8 KB of dY = 120 KB through
+// L2 -> shared memory and three 128 x 192 accumulators, instead of 5 x 8 KB of dY + 18 x 8 KB of im2col'ed x = 184 KB and five
+// 128 x 256 accumulators of which half the rows are padding - the kernel is bound by exactly that fill (9 TB/s measured).
+static bool wgrad_swap_applicable(const dei2i_conv_geom* g) {
+  if (g_tune_wgrad_swap == 0) return false;
+  return g->stride == 1 && g->pad == 0 && g->Cout_ld == 64 && g->Cin % 128 == 0 && g->Cin <= 256 && g->kh * g->kw <= 16 &&
+         g->Hs == g->H && g->Ws == g->W;
+}
+static void fill_wgrad_swap(const dei2i_conv_geom* g, TmaWgradParams& t) {
+  memset(&t, 0, sizeof(t));
+  t.Ho = g->H; t.Wo = g->W;  // traversal over input pixels
+  t.M = (long long)g->N * g->H * g->W;
+  t.stride = 1; t.lower = -(g->kh - 1); t.lower_w = -(g->kw - 1); t.kw = g->kw; t.cin_blocks = 1;
+  t.num_boxes = g->kh * g->kw;
+  t.cout = g->Cin; t.Kf = g->kh * g->kw * 64;
+  wgrad_tma_plan(t);
+}
+// sum of the swapped partials over the splits (fixed order) into the ordinary layout P[co][tap * Cin + ci] with one split
+__global__ void __launch_bounds__(256)
+wgrad_swap_fold_kernel(const float* __restrict__ part, int splits, int Cin, int Cout, int taps, float* __restrict__ out) {
+  const int Kfp = taps * 64;
+  const int total = Cin * Kfp;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int ci = i / Kfp, k = i - ci * Kfp;
+    const int tp = k >> 6, co = k & 63;
+    float acc = 0.f;
+    for (int s = 0; s < splits; ++s) acc += part[(size_t)s * total + i];
+    if (co < Cout) out[(size_t)co * taps * Cin + (taps - 1 - tp) * Cin + ci] = acc;
+  }
+}
+
 extern "C" size_t dei2i_conv2d_wgrad_workspace(const dei2i_conv_geom* g, int Cin_real) {
   (void)Cin_real;
   if (g == nullptr || check_geom(g)) return 0;
@@ -919,7 +954,14 @@ extern "C" size_t dei2i_conv2d_wgrad_workspace(const dei2i_conv_geom* g, int Cin
       if (t.splits > splits) splits = t.splits;
     }
   }
-  return (size_t)splits * g->Cout * Kf * sizeof(float) + 1024 * sizeof(float) + 256;
+  size_t bytes = (size_t)splits * g->Cout * Kf * sizeof(float) + 1024 * sizeof(float) + 256;
+  if (wgrad_tma_applicable(g, 0) && wgrad_swap_applicable(g)) {
+    TmaWgradParams t;
+    fill_wgrad_swap(g, t);
+    const size_t need = ((size_t)t.splits * g->Cin * t.Kf + (size_t)g->Cout * Kf + 1024) * sizeof(float) + 256;
+    if (need > bytes) bytes = need;
+  }
+  return bytes;
 }
 
 template <int BN, int ST>
@@ -960,7 +1002,18 @@ extern "C" int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int 
   p.g.M = (long long)g->N * Ho * Wo;
   float* partial = (float*)workspace;
   const int taps = g->kh * g->kw;
-  if (wgrad_tma_applicable(g, p.g.M)) {
+  if (wgrad_tma_applicable(g, p.g.M) && wgrad_swap_applicable(g)) {
+    TmaWgradParams t;
+    fill_wgrad_swap(g, t);
+    t.partial = partial;
+    if (int rc = run_wgrad_tma(dy, g->N, Ho, Wo, g->Cout_ld, x, g->Cin, t, 0, 0, st)) return rc;
+    trace_kernel("+swap");
+    float* folded = partial + (size_t)t.splits * g->Cin * t.Kf;
+    wgrad_swap_fold_kernel<<<(g->Cin * t.Kf + 255) / 256, 256, 0, st>>>(partial, t.splits, g->Cin, g->Cout, taps, folded);
+    count_launch();
+    DEI2I_CUDA(cudaGetLastError());
+    return wgrad_second_pass(folded, 1, g, Cin_real, Kf, dw, beta, sn_w_orig, sn_u, sn_v, sn_inv_sigma, st);
+  } else if (wgrad_tma_applicable(g, p.g.M)) {
     TmaWgradParams t;
     fill_wgrad_tma(g, t);
     t.partial = partial;

@@ -480,8 +480,8 @@ wgrad_tma_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_const
   t /= p.splits;
   const int k_tile = t % p.k_tiles;
   const int co_group = t / p.k_tiles;
-  const int box0 = k_tile * 4;
-  const int nb = min(4, p.num_boxes - box0);  // boxes in this tile
+  const int box0 = k_tile * p.boxes_per_tile;
+  const int nb = min(p.boxes_per_tile, p.num_boxes - box0);  // boxes in this tile
   const int co0 = co_group * 128 * CO_T;
   const int pb0 = split * p.pb_per_split;
   const int pb1 = min(p.num_pb, pb0 + p.pb_per_split);
@@ -620,6 +620,8 @@ void wgrad_tma_plan(TmaWgradParams& p) {
   const int co_t = p.cout > 128 ? 2 : 1;
   p.co_groups = (p.cout + 128 * co_t - 1) / (128 * co_t);
   p.k_tiles = (p.num_boxes + 3) / 4;
+  p.boxes_per_tile = (p.num_boxes + p.k_tiles - 1) / p.k_tiles;
+  p.k_tiles = (p.num_boxes + p.boxes_per_tile - 1) / p.boxes_per_tile;
   p.num_pb = (int)((p.M + 63) / 64);
   const int tiles = p.co_groups * p.k_tiles;
   int splits = num_sms() / tiles;

@@ -182,7 +182,12 @@ def from_nhwc(a: Nhwc) -> torch.Tensor:
 # Statistics out of the convolution epilogue (dei2i_conv_epilogue.stats_partial) for outputs of up to this many channels.  Measured on
 # the 256 x 256 / batch 32 step: 0 -> 81.73 ms, 128 -> 81.78 ms, 512 -> 82.31 ms per step - the epilogue work costs what the separate
 # statistics pass over the (mostly L2-resident) tensor saves, so the consumer computes them by default (dei2i_channel_stats).
-EPI_STATS_MAX_COUT = int(os.environ.get("DEI2I_EPI_STATS_MAX_COUT", "0"))
+# Statistics of a convolution's output for its BatchNorm / InstanceNorm consumer out of the convolution epilogue (per-tile (mean, M2)
+# pairs, merged in a fixed order) instead of a separate pass over the stored tensor.  Worth it where the main loop leaves the
+# epilogue warps slack - 128 and 256 output channels: 77.2 -> 76.1 ms per step - and not for the 64-channel layers at 256^2, whose
+# epilogue is on the critical path (+1.0 ms) - measured on one box, tools/gpu_ab.sh.
+EPI_STATS_MAX_COUT = int(os.environ.get("DEI2I_EPI_STATS_MAX_COUT", "256"))
+EPI_STATS_MIN_COUT = int(os.environ.get("DEI2I_EPI_STATS_MIN_COUT", "128"))
 
 
 _grad_sink = False
@@ -285,7 +290,7 @@ def conv(x: Nhwc, conv_mod, spec: ConvSpec, training: bool, bias=None, act=None,
     """want_stats ('batch' | 'sample'): ask the epilogue for the statistics of the output (carrier ``.stats``); out_pad: ask it to
     write the consumer's reflect padding (carrier ``.pad``) - granted only where the TMA kernel runs the geometry."""
     wts = wts or prepare_conv(conv_mod, spec, training)
-    if want_stats is not None and spec.cout_ld > EPI_STATS_MAX_COUT:
+    if want_stats is not None and not (EPI_STATS_MIN_COUT <= spec.cout_ld <= EPI_STATS_MAX_COUT):
         want_stats = None
     if out_pad:
         n, h, w = x.t.shape[0], x.t.shape[1], x.t.shape[2]
@@ -385,7 +390,7 @@ def rowpack_conv(x: torch.Tensor, conv_mod, spec: ConvSpec, training: bool, want
         scale = inv
     else:
         w = conv_mod.weight
-    if want_stats is not None and spec.cout_ld > EPI_STATS_MAX_COUT:
+    if want_stats is not None and not (EPI_STATS_MIN_COUT <= spec.cout_ld <= EPI_STATS_MAX_COUT):
         want_stats = None
     res = _RowpackConv.apply(x, w, sn, scale, spec, want_stats)
     if want_stats is None:

@@ -85,6 +85,11 @@ CONV_CASES = {
     "heads_valid_4": (2, 64, 18, 18, 4, 3, 1, 0, "zeros", False, None),
     "heads_valid_128_zero": (1, 128, 12, 12, 3, 3, 1, 1, "zeros", False, None),
     "heads_zero_64_wide": (3, 64, 9, 150, 4, 3, 1, 1, "zeros", False, None),   # 5 pixel chunks, zero frame, image restarts
+    # operand-swapped wgrad (Cout <= 64 on Cin = 128 / 256, valid stride-1): x as the plain pixel matrix, dY im2col'ed per tap
+    "wgrad_swap_128_64": (2, 128, 20, 24, 64, 3, 1, 0, "zeros", False, None),
+    "wgrad_swap_256_60_ragged": (3, 256, 11, 13, 60, 3, 1, 0, "zeros", False, None),
+    "wgrad_swap_128_64_k4": (2, 128, 12, 12, 64, 4, 1, 0, "zeros", False, None),
+    "wgrad_swap_128_64_1x1": (2, 128, 9, 9, 64, 1, 1, 0, "zeros", False, None),
     "heads_valid_64_rows": (2, 64, 163, 34, 3, 3, 1, 0, "zeros", False, None),  # > 148 output rows per image: multi-row strips
     "d_cls_valid4x4": (4, 128, 4, 4, 6, 4, 1, 0, "zeros", False, None),
     # discriminator outputs at full width (conv_narrow_fwd_kernel: <= 8 output channels, K = taps * 2048)
@@ -231,7 +236,7 @@ WGRAD_CASES = ["res3x3_64", "res3x3_256", "enc4x4s2", "stem7x7", "spade_shared_8
                "tma_zero3x3_256", "tma_persistent_200tiles", "tma_valid4x4s2", "tma_dgrad_s2_to8", "c8_stem_valid7x7",
                "c8_zero3x3_nores", "c8_spade_shared_big", "spade_shared_1x1seg", "heads_valid_4", "heads_valid_128_zero",
                "d_cls_valid4x4", "heads_zero_64_wide", "heads_valid_64_rows", "tma_ragged_m100", "tma_ragged_m75_s2",
-               "spade_cls_gb_5x5"]
+               "spade_cls_gb_5x5", "wgrad_swap_128_64", "wgrad_swap_256_60_ragged", "wgrad_swap_128_64_k4", "wgrad_swap_128_64_1x1"]
 
 
 @pytest.mark.parametrize("case", WGRAD_CASES)
@@ -249,8 +254,18 @@ def test_conv_wgrad(case):
     e1 = rel_err(dw.cpu(), dw_ref)
     ops.conv2d_wgrad(to_dev(x), to_dev(dy), dw, spec, accumulate=True, logical_hw=(h, w) if rs else None)
     e2 = rel_err(dw.cpu(), 2 * dw_ref)
-    _report("conv_wgrad/" + case, err=e1, err_acc=e2)
+    _report("conv_wgrad/" + case, err=e1, err_acc=e2, kernel=ops.last_kernel())
     assert e1 < TOL_F32 and e2 < TOL_F32, (e1, e2)
+    if case.startswith("wgrad_swap"):
+        assert "swap" in ops.last_kernel(), ops.last_kernel()
+        ops.set_tuning("wgrad_swap", 0)  # and the ordinary operand roles on the same inputs
+        try:
+            dw2 = torch.zeros_like(dw)
+            ops.conv2d_wgrad(to_dev(x), to_dev(dy), dw2, spec)
+            assert "swap" not in ops.last_kernel()
+        finally:
+            ops.set_tuning("wgrad_swap", 1)
+        assert rel_err(dw2.cpu(), dw_ref) < TOL_F32
 
 
 def test_wgrad_spectral_backward_and_power_iteration():

@@ -47,6 +47,9 @@ def main():
         conv_case(32, 128, 258, 258, 64, 3, 3, 1, "fd")
     if "wgrad64" in names:
         conv_case(32, 128, 258, 258, 64, 3, 3, 1, "w")
+        ops.set_tuning("wgrad_swap", 0)
+        conv_case(32, 128, 258, 258, 64, 3, 3, 1, "w")
+        ops.set_tuning("wgrad_swap", 1)
     if "c256" in names:
         conv_case(32, 256, 66, 66, 256, 3, 3, 1, "fdw")
     if "stem" in names:

@@ -481,8 +481,9 @@ wgrad_reduce_kernel(const float* __restrict__ partial, int splits, int Cout, int
 // <dW, W/sigma> over the real elements (spectral-norm backward); deterministic: fixed tile -> block assignment, fixed order
 template <bool VEC>
 __global__ void __launch_bounds__(256)
-wgrad_dot_kernel(const float* __restrict__ partial, int splits, int Cout, int Kf, int Cin, int Cin_real, int taps,
-                 const float* __restrict__ w_orig, const float* __restrict__ inv_sigma, float* __restrict__ blocksums, int sh) {
+wgrad_dot_kernel(float* __restrict__ partial, int splits, int Cout, int Kf, int Cin, int Cin_real, int taps,
+                 const float* __restrict__ w_orig, const float* __restrict__ inv_sigma, float* __restrict__ blocksums, int sh,
+                 int store_sum) {
   extern __shared__ float4 T4[];
   float* T = reinterpret_cast<float*>(T4);
   const int ct = 1 << sh, pitch = ct + 4;
@@ -507,6 +508,23 @@ wgrad_dot_kernel(const float* __restrict__ partial, int splits, int Cout, int Kf
     __syncthreads();
     wgrad_tile_load<VEC>(partial, splits, (long long)Cout * Kf, Kf, Cin, Cin_real, taps, co, ci0, sh, pitch, T);
     __syncthreads();
+    if (store_sum && splits > 1) {
+      // the split sums of this tile replace split 0 in place (tiles are disjoint): wgrad_reduce_kernel then reads one split
+      // instead of summing all of them a second time
+      float* dst = partial + (long long)co * Kf + ci0;
+      if (VEC) {
+        const int sh4 = sh - 2;
+        for (int idx = threadIdx.x; idx < (taps << sh4); idx += blockDim.x) {
+          const int tap = idx >> sh4, j = (idx & ((1 << sh4) - 1)) * 4;
+          if (ci0 + j < Cin_real) *reinterpret_cast<float4*>(dst + tap * Cin + j) = *reinterpret_cast<const float4*>(T + tap * pitch + j);
+        }
+      } else {
+        for (int idx = threadIdx.x; idx < (taps << sh); idx += blockDim.x) {
+          const int tap = idx >> sh, j = idx & ((1 << sh) - 1);
+          if (ci0 + j < Cin_real) dst[tap * Cin + j] = T[tap * pitch + j];
+        }
+      }
+    }
     if (VEC) {
 #pragma unroll
       for (int r = 0; r < 4; ++r) {
@@ -647,23 +665,25 @@ int wgrad_second_pass(float* partial, int splits, const dei2i_conv_geom* g, int 
   const int red_tiles = g->Cout * ((Cin_real + red_ci - 1) / red_ci);
   const size_t red_smem = (size_t)taps * (red_ci + 4) * sizeof(float);
   DEI2I_REQUIRE(red_smem <= 48 * 1024, "conv2d_wgrad: filter too large for the reduction tile");
+  int red_splits = splits;
   if (sn_u != nullptr) {
     const int nb = red_tiles < 1023 ? red_tiles : 1023;
     if (red_vec)
       wgrad_dot_kernel<true><<<nb, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, sn_w_orig, sn_inv_sigma,
-                                                        dot + 1, red_sh);
+                                                        dot + 1, red_sh, 1);
     else
       wgrad_dot_kernel<false><<<nb, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, sn_w_orig, sn_inv_sigma,
-                                                         dot + 1, red_sh);
+                                                         dot + 1, red_sh, 1);
+    red_splits = 1;  // the dot pass left the split sums in split 0
     sum_blocks_kernel<<<1, 256, 0, st>>>(dot + 1, nb, dot);
     count_launch(2);
     DEI2I_CUDA(cudaGetLastError());
   }
   if (red_vec)
-    wgrad_reduce_kernel<true><<<(unsigned)red_tiles, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, dw, beta,
+    wgrad_reduce_kernel<true><<<(unsigned)red_tiles, 256, red_smem, st>>>(partial, red_splits, g->Cout, Kf, g->Cin, Cin_real, taps, dw, beta,
                                                                           dot, sn_u, sn_v, sn_inv_sigma, red_sh);
   else
-    wgrad_reduce_kernel<false><<<(unsigned)red_tiles, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, dw, beta,
+    wgrad_reduce_kernel<false><<<(unsigned)red_tiles, 256, red_smem, st>>>(partial, red_splits, g->Cout, Kf, g->Cin, Cin_real, taps, dw, beta,
                                                                            dot, sn_u, sn_v, sn_inv_sigma, red_sh);
   count_launch();
   return check_cuda(cudaGetLastError(), "wgrad_reduce_kernel launch");

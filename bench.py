@@ -361,7 +361,15 @@ def setup_stargan(args, cfg, dev, rank):
         x, xr, xr2, y_org, y_trg, z, z2 = [t.to(dev, non_blocking=True) for t in inputs]
         inp = SimpleNamespace(x_src=x, y_src=y_org, x_ref=xr, x_ref2=xr2, y_ref=y_trg, z_trg=z, z_trg2=z2)
         S.train_iteration(st, a, inp)
-    return dict(step=step, host=host, d2h=14 * 4, eager=lambda: False, dense_ref_tflop=None, extra={})
+    def eager():
+        steps = getattr(st, "_sub_steps", None)
+        was = False
+        if steps is not None:
+            for gs in steps[2].values():
+                was = was or gs.enabled
+                gs.enabled = False
+        return was
+    return dict(step=step, host=host, d2h=14 * 4, eager=eager, dense_ref_tflop=None, extra={})
 
 
 def setup_inference(args, cfg, dev, rank):

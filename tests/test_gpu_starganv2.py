@@ -179,3 +179,38 @@ def test_adain_act_kernel(slope):
     assert rel_err(back(out), ref) < 1e-2
     dx, dsc, dsh = ops.adain_act_bwd(to(x), out, to(dout), sc.detach().cuda(), mr, slope)
     assert rel_err(back(dx), dx_r) < 2e-2 and rel_err(dsc.cpu(), dsc_r) < 1e-2 and rel_err(dsh.cpu(), dsh_r) < 1e-2
+
+
+def test_train_iteration_graphed_matches_eager(monkeypatch):
+    """`train_iteration` runs its four sub-steps as CUDA graphs (call 1 eager, call 2 captures, then replays) and reads the fourteen
+    loss scalars with one transfer: over four iterations with fresh inputs and the decaying diversity weight it returns the same
+    python floats, and leaves the same parameters, as the un-graphed path (DEI2I_CUDA_GRAPH=0) from the same seeded state."""
+    from de_i2i_gan_b200.stargan_v2.core import solver as S
+    mk = lambda: SimpleNamespace(img_size=64, style_dim=16, latent_dim=8, num_domains=2, w_hpf=0, norm_type="adain", num_embeds=1,  # noqa: E731
+                                 lambda_reg=1.0, lambda_sty=1.0, lambda_ds=2.0, lambda_cyc=1.0, lr=1e-4, f_lr=1e-6, beta1=0.0, beta2=0.99,
+                                 weight_decay=1e-4, ds_iter=10)
+    g = torch.Generator().manual_seed(3)
+    B = 2
+    img = lambda: torch.randn(B, 3, 64, 64, generator=g).clamp_(-1, 1).cuda()  # noqa: E731
+    batches = [SimpleNamespace(x_src=img(), y_src=torch.tensor([0, 1]).cuda(), x_ref=img(), x_ref2=img(), y_ref=torch.tensor([1, 0]).cuda(),
+                               z_trg=torch.randn(B, 8, generator=g).cuda(), z_trg2=torch.randn(B, 8, generator=g).cuda()) for _ in range(4)]
+    runs = []
+    for graphed in (True, False):
+        monkeypatch.setenv("DEI2I_CUDA_GRAPH", "1" if graphed else "0")
+        torch.manual_seed(11)
+        args = mk()
+        st = S.build_training_state(args, torch.device("cuda", 0))
+        vals = []
+        for inp in batches:
+            logs = S.train_iteration(st, args, inp)
+            assert [sorted(vars(l)) for l in logs] == [["fake", "real", "reg"]] * 2 + [["adv", "cyc", "ds", "sty"]] * 2
+            vals += [v for l in logs for v in vars(l).values()]
+        assert all(isinstance(v, float) for v in vals)
+        assert abs(args.lambda_ds - (2.0 - 4 * 2.0 / 10)) < 1e-9
+        used = [gs for gs in st._sub_steps[2].values() if any("graph" in s_ for s_ in gs.states.values())]
+        assert len(used) == (4 if graphed else 0)
+        params = torch.cat([p.detach().flatten().cpu() for net in list(vars(st.nets).values()) + list(vars(st.nets_ema).values())
+                            for p in net.parameters()])
+        runs.append((vals, params))
+    assert runs[0][0] == pytest.approx(runs[1][0], rel=1e-5, abs=1e-6)
+    assert torch.allclose(runs[0][1], runs[1][1], rtol=1e-5, atol=1e-7)

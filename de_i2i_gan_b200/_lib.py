@@ -64,6 +64,8 @@ SIGNATURES = {
     "dei2i_nhwc_to_nchw": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
     "dei2i_channel_stats_scratch": (_SZ, [_I, _I, _I, _I]),
     "dei2i_channel_stats": (_I, [_P, _I, _I, _I, _I, _P, _P, _SZ, _P]),
+    "dei2i_channel_stats_static_max_floats": (_SZ, []),
+    "dei2i_channel_stats_static": (_I, [_P, _I, _I, _I, _I, _P, _P]),
     "dei2i_stats_finalize": (_I, [_P, _I, _I, _LL, _I, _I, _I, _P, _P]),
     "dei2i_bn_fwd": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _F, _F, _I, _P]),
     "dei2i_bn_fwd_pad": (_I, [_P, _P, _P, _P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _F, _F, _I, _I, _P]),

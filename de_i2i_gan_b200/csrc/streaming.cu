@@ -2,6 +2,7 @@
 // All of them are bandwidth bound: 16-byte (8 x bf16) accesses, channel-contiguous (NHWC) so that a warp
 // touches whole 128-byte lines, warp-shuffle + shared-memory reductions for the per-channel statistics.
 #include <string.h>
+#include <mutex>
 
 #include "common.cuh"
 #include "../../include/dei2i.h"
@@ -2022,6 +2023,55 @@ extern "C" int dei2i_channel_stats(const void* x, int N, int HW, int C, int per_
   DEI2I_REQUIRE(scratch_floats >= (size_t)groups * chunks * 2 * C, "channel_stats: scratch too small (dei2i_channel_stats_scratch)");
   if (shmem > 48 * 1024)
     DEI2I_CUDA(cudaFuncSetAttribute(channel_stats_partial_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shmem));
+  channel_stats_partial_kernel<<<dim3(chunks, groups), threads, shmem, ST>>>((const uint4*)x, ppg, C / 8, chunk, scratch);
+  if (int rc = LAUNCH_OK("channel_stats_partial_kernel")) return rc;
+  return launch_stats_finalize(scratch, (int)chunks, chunk, ppg, groups, C, C, stats, ST);
+}
+
+// ---- dei2i_channel_stats for callers that cannot allocate (no reference counterpart)
+// The per-block (mean, M2) pairs live in a file-scope device array instead of a caller-provided buffer.  Every GPU that loads the
+// library holds these 4 MiB until exit.  In HOST code `g_stats_static_scratch` is only a stand-in for the symbol, not a device
+// address: its address is looked up once per device with cudaGetSymbolAddress (with that device current) and that pointer is what
+// the kernels get.  Nothing has to start at zero: channel_stats_partial_kernel overwrites every pair the finalize pass reads.  All
+// calls on a device share the array, so calls that overlap on the GPU (different streams without an ordering between them) race.
+static __device__ __align__(256) float g_stats_static_scratch[DEI2I_STATS_STATIC_MAX_FLOATS];
+
+static int stats_static_scratch_ptr(float** out) {
+  constexpr int kMaxDev = 64;
+  static float* ptr[kMaxDev] = {nullptr};
+  static std::mutex mu;
+  int dev = -1;
+  DEI2I_CUDA(cudaGetDevice(&dev));
+  DEI2I_REQUIRE(dev >= 0 && dev < kMaxDev, "channel_stats_static: device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (ptr[dev] == nullptr) {
+    float* q = nullptr;
+    DEI2I_CUDA(cudaGetSymbolAddress((void**)&q, g_stats_static_scratch));  // address of this device's copy of the array
+    DEI2I_REQUIRE(q != nullptr, "channel_stats_static: cudaGetSymbolAddress returned a null address");
+    ptr[dev] = q;
+  }
+  *out = ptr[dev];
+  return 0;
+}
+
+extern "C" size_t dei2i_channel_stats_static_max_floats(void) { return (size_t)DEI2I_STATS_STATIC_MAX_FLOATS; }
+
+extern "C" int dei2i_channel_stats_static(const void* x, int N, int HW, int C, int per_sample, float* stats, dei2i_stream stream) {
+  DEI2I_REQUIRE(x && stats && N >= 1 && HW >= 1, "channel_stats_static: bad arguments");
+  const int groups = per_sample ? N : 1;
+  const long long ppg = per_sample ? (long long)HW : (long long)N * HW;
+  int threads, chunk;
+  unsigned chunks;
+  size_t shmem;
+  if (int rc = launch_channel_reduce_cfg(C, ppg, groups, threads, chunk, chunks, shmem)) return rc;
+  const size_t need = (size_t)groups * chunks * 2 * C;
+  DEI2I_REQUIRE(need <= (size_t)DEI2I_STATS_STATIC_MAX_FLOATS,
+                "channel_stats_static: N=%d HW=%d C=%d per_sample=%d needs %zu scratch floats, the built-in array holds %zu "
+                "(DEI2I_STATS_STATIC_MAX_FLOATS); use dei2i_channel_stats with a caller-provided buffer",
+                N, HW, C, per_sample, need, (size_t)DEI2I_STATS_STATIC_MAX_FLOATS);
+  DEI2I_REQUIRE(shmem <= 48 * 1024, "channel_stats_static: unexpected shared-memory size %zu", shmem);
+  float* scratch = nullptr;
+  if (int rc = stats_static_scratch_ptr(&scratch)) return rc;
   channel_stats_partial_kernel<<<dim3(chunks, groups), threads, shmem, ST>>>((const uint4*)x, ppg, C / 8, chunk, scratch);
   if (int rc = LAUNCH_OK("channel_stats_partial_kernel")) return rc;
   return launch_stats_finalize(scratch, (int)chunks, chunk, ppg, groups, C, C, stats, ST);

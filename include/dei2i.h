@@ -177,6 +177,17 @@ int dei2i_nhwc_to_nchw(const void* src, float* dst, int N, int C, int H, int W, 
 size_t dei2i_channel_stats_scratch(int N, int HW, int C, int per_sample);
 int dei2i_channel_stats(const void* x, int N, int HW, int C, int per_sample, float* stats, float* scratch, size_t scratch_floats,
                         dei2i_stream stream);
+/* dei2i_channel_stats without a scratch argument, for callers that must not allocate (CUDA-graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc).  No counterpart in the reference.  Same arguments,
+ * same kernels and bit-identical results; the per-block pairs go to a file-scope `static __device__` array of
+ * DEI2I_STATS_STATIC_MAX_FLOATS floats (4 MiB, held by every GPU that loads the library until exit) whose device address is looked
+ * up once per device with cudaGetSymbolAddress.  Calls no cudaMalloc / cudaFree / allocating routine.  Shapes that need more
+ * scratch than that (dei2i_channel_stats_scratch(...) > the maximum) return DEI2I_ERR_INVALID with a message (dei2i_last_error) - use dei2i_channel_stats.
+ * Every call on a device shares the one array (it keeps the last call's contents; nothing needs clearing, each call overwrites what
+ * it reads): calls that overlap on the GPU - concurrent streams with no ordering between them - race. */
+#define DEI2I_STATS_STATIC_MAX_FLOATS (1u << 20)
+size_t dei2i_channel_stats_static_max_floats(void);
+int dei2i_channel_stats_static(const void* x, int N, int HW, int C, int per_sample, float* stats, dei2i_stream stream);
 /* Second half of the statistics when the producer emitted the per-tile pairs itself (dei2i_conv_epilogue.stats_partial, 128 rows
  * per tile): partial [groups * tiles_per_group][2][ld] (mean, M2), tile t of a group covering rows [t * rows_per_tile, ...) of the
  * group's rows_per_group rows -> stats [groups, 2, C] (mean, biased variance).  Fixed merge order. */

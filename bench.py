@@ -295,6 +295,12 @@ def setup_defectgan(args, cfg, dev, rank):
         trainer._train_discriminator_once(b, l, d)
         trainer._train_generator_once(b, l, d)
 
+    def last_losses():
+        """The seven loss scalars of the most recent D-step + G-step (what the trainer logs; already on the host)."""
+        L = trainer.losses
+        return {"gan_d": L["gan"]["D"][-1], "clf_d": L["clf"]["D"][-1], "gan_g": L["gan"]["G"][-1], "clf_g": L["clf"]["G"][-1],
+                "rec": L["aux"]["rec"][-1], "cyc": L["aux"]["cyc"][-1], "con": L["aux"]["con"][-1]}
+
     def host_epoch(k):
         """The e2e leg: K iterations through the trainer's own epoch loop (DefectGanTrainer._train_epoch = the body of trainer.train,
         defectgan_trainer.py:91-120) fed by loaders that hand out the pinned host batch - the call a user of the reference makes.
@@ -310,7 +316,7 @@ def setup_defectgan(args, cfg, dev, rank):
         for g in trainer._graphed.values():
             g.enabled = False
         return was
-    return dict(step=step, host=host, host_epoch=host_epoch, d2h=7 * 4, eager=eager, dense_ref_tflop=DENSE_TFLOP_PER_IMG_256 * B * (H / 256) ** 2,
+    return dict(step=step, host=host, host_epoch=host_epoch, last_losses=last_losses, d2h=7 * 4, eager=eager, dense_ref_tflop=DENSE_TFLOP_PER_IMG_256 * B * (H / 256) ** 2,
                 extra={"spade": ("dense full-resolution gamma|beta convolutions" if args.spade_dense else
                                  "gamma|beta evaluated exactly on the 5x5 border-class map of the 1x1 training label map "
                                  "(results identical; FLOPs of the dense evaluation are NOT credited - see executed vs reference TFLOP)")})
@@ -446,6 +452,15 @@ def run_ours(args, cfg):
     warm = max(args.warmup, 3)
     for _ in range(warm):  # call 1 eager, call 2 captures the CUDA graphs, call 3+ replay
         step(resident)
+    # a timed number of a step that has diverged is worthless: the losses the warm-up logged (eager call, capture, graph replays) must be
+    # finite and of sane magnitude; they go into the JSON line (parity against the oracle is the business of tests/ and smoke())
+    check = None
+    if "last_losses" in S:
+        import math
+        check = S["last_losses"]()
+        bad = [k for k, v in check.items() if not math.isfinite(v) or abs(v) > 1e3]
+        if bad:
+            raise SystemExit(f"bench.py: losses after warm-up are not finite / out of range: { {k: check[k] for k in bad} } - refusing to time this run")
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
@@ -564,6 +579,7 @@ def run_ours(args, cfg):
         "e2e": {"value": B * world / (ms_e2e * 1e-3 / args.steps), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": ms_e2e / args.steps},
         "gpu_launches": launches, "clocks": clk, "roofline": roofline, "cpu_baseline": cpu, "incumbent": inc,
+        "check": {"losses_after_warmup": check, "finite": True} if check is not None else None,
     }))
     _finish(world)
 

@@ -25,6 +25,11 @@ class SnItem(C.Structure):  # dei2i_sn_item
                 ("v_snap", C.c_void_p), ("rows", C.c_int), ("cols", C.c_int)]
 
 
+class PackItem(C.Structure):  # dei2i_pack_item
+    _fields_ = [("w", C.c_void_p), ("w2", C.c_void_p), ("w_fwd", C.c_void_p), ("w_dgrad", C.c_void_p), ("rows_w", C.c_int),
+                ("Cout", C.c_int), ("Cin_real", C.c_int), ("kh", C.c_int), ("kw", C.c_int), ("Cin", C.c_int), ("Cout_ld", C.c_int)]
+
+
 _P, _I, _F, _LL, _SZ = C.c_void_p, C.c_int, C.c_float, C.c_longlong, C.c_size_t
 
 # name -> (restype, argtypes); mirrors include/dei2i.h one to one
@@ -41,6 +46,7 @@ SIGNATURES = {
     "dei2i_conv2d_dgrad": (_I, [_P, _P, _P, C.POINTER(ConvGeom), _P, _I, _P]),
     "dei2i_reflect_fold": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
     "dei2i_reflect_pad": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_pack_weight_multi": (_I, [C.POINTER(PackItem), _I, _P]),
     "dei2i_conv2d_wgrad_workspace": (_SZ, [C.POINTER(ConvGeom), _I]),
     "dei2i_conv2d_wgrad": (_I, [_P, _P, _P, _I, _F, C.POINTER(ConvGeom), _P, _P, _P, _P, _P, _SZ, _P]),
     "dei2i_spectral_norm": (_I, [_P, _P, _P, _I, _I, _I, _F, _P, _P, _P]),

@@ -68,6 +68,61 @@ __global__ void pack_dgrad_kernel(const float* __restrict__ w, const float* __re
   out[i] = __float2bfloat16(v);
 }
 
+// many weights per launch: the item table travels as a kernel parameter; a block finds its item by scanning the block prefix
+constexpr int kPackBatch = 32;
+struct PackBatch {
+  const float* w[kPackBatch];
+  const float* w2[kPackBatch];
+  __nv_bfloat16* fwd[kPackBatch];
+  __nv_bfloat16* dg[kPackBatch];
+  int rows_w[kPackBatch], Cout[kPackBatch], Cin_real[kPackBatch], taps[kPackBatch], Cin[kPackBatch], Cout_ld[kPackBatch];
+  int Kf[kPackBatch], Kd[kPackBatch];
+  int blk_fwd[kPackBatch];      // blocks of the forward matrix of item j (the dgrad matrix follows)
+  int blk[kPackBatch + 1];      // block prefix over items (fwd + dgrad blocks)
+  int count;
+};
+constexpr int kPackPerBlock = 1024;
+__global__ void __launch_bounds__(256) pack_multi_kernel(const __grid_constant__ PackBatch t) {
+  int j = 0;
+  while (j + 1 < t.count && (int)blockIdx.x >= t.blk[j + 1]) ++j;
+  const int b = blockIdx.x - t.blk[j];
+  const int Cout = t.Cout[j], Cin_real = t.Cin_real[j], taps = t.taps[j], Cin = t.Cin[j], rows_w = t.rows_w[j];
+  const float* __restrict__ w = t.w[j];
+  const float* __restrict__ w2 = t.w2[j];
+  if (b < t.blk_fwd[j]) {
+    const int Kf = t.Kf[j];
+    const long long total = (long long)Cout * Kf;
+    __nv_bfloat16* __restrict__ out = t.fwd[j];
+#pragma unroll
+    for (int r = 0; r < kPackPerBlock / 256; ++r) {
+      const long long i = (long long)b * kPackPerBlock + r * 256 + threadIdx.x;
+      if (i >= total) break;
+      const int co = (int)(i / Kf), k = (int)(i - (long long)co * Kf);
+      const int tap = k / Cin, ci = k - tap * Cin;
+      float v = 0.f;
+      if (tap < taps && ci < Cin_real)
+        v = co < rows_w ? w[((long long)co * Cin_real + ci) * taps + tap] : w2[((long long)(co - rows_w) * Cin_real + ci) * taps + tap];
+      out[i] = __float2bfloat16(v);
+    }
+  } else {
+    const int bb = b - t.blk_fwd[j];
+    const int Kd = t.Kd[j], Cout_ld = t.Cout_ld[j];
+    const long long total = (long long)Cin * Kd;
+    __nv_bfloat16* __restrict__ out = t.dg[j];
+#pragma unroll
+    for (int r = 0; r < kPackPerBlock / 256; ++r) {
+      const long long i = (long long)bb * kPackPerBlock + r * 256 + threadIdx.x;
+      if (i >= total) break;
+      const int ci = (int)(i / Kd), k = (int)(i - (long long)ci * Kd);
+      const int tap = k / Cout_ld, co = k - tap * Cout_ld;
+      float v = 0.f;
+      if (tap < taps && co < Cout && ci < Cin_real)
+        v = co < rows_w ? w[((long long)co * Cin_real + ci) * taps + tap] : w2[((long long)(co - rows_w) * Cin_real + ci) * taps + tap];
+      out[i] = __float2bfloat16(v);
+    }
+  }
+}
+
 DEVINL int reflect_idx(int i, int n) { return i < 0 ? -i : (i >= n ? 2 * n - 2 - i : i); }
 
 // out / dout of a consumer-padded SPADE output ([N, H+2pad, W+2pad, C]): the activation at (h, w) sits at (h+pad, w+pad); its
@@ -1879,6 +1934,36 @@ extern "C" int dei2i_pack_weight(const float* w, const float* inv_sigma, int Cou
     pack_dgrad_kernel<<<nblocks((long long)Cin * Kd, 256), 256, 0, ST>>>(w, inv_sigma, Cout, Cin_real, taps, Cin, Cout_ld, Kd,
                                                                          (__nv_bfloat16*)w_dgrad);
     return LAUNCH_OK("pack_dgrad_kernel");
+  }
+  return 0;
+}
+
+extern "C" int dei2i_pack_weight_multi(const dei2i_pack_item* items, int count, dei2i_stream stream) {
+  DEI2I_REQUIRE(items && count >= 0, "pack_weight_multi: bad arguments");
+  for (int base = 0; base < count; base += kPackBatch) {
+    PackBatch t;
+    memset(&t, 0, sizeof(t));
+    t.count = count - base < kPackBatch ? count - base : kPackBatch;
+    for (int j = 0; j < t.count; ++j) {
+      const dei2i_pack_item& it = items[base + j];
+      DEI2I_REQUIRE(it.w && it.w_fwd && it.Cout > 0 && it.Cin_real > 0 && it.kh > 0 && it.kw > 0, "pack_weight_multi: bad item %d", base + j);
+      DEI2I_REQUIRE(it.Cin % 8 == 0 && it.Cin >= it.Cin_real && it.Cout_ld % 8 == 0 && it.Cout_ld >= it.Cout,
+                    "pack_weight_multi: bad channel padding in item %d", base + j);
+      DEI2I_REQUIRE(it.w2 ? (it.rows_w > 0 && it.rows_w < it.Cout) : it.rows_w == it.Cout, "pack_weight_multi: bad rows_w in item %d", base + j);
+      const int taps = it.kh * it.kw;
+      t.w[j] = it.w; t.w2[j] = it.w2; t.fwd[j] = (__nv_bfloat16*)it.w_fwd; t.dg[j] = (__nv_bfloat16*)it.w_dgrad;
+      t.rows_w[j] = it.rows_w; t.Cout[j] = it.Cout; t.Cin_real[j] = it.Cin_real; t.taps[j] = taps; t.Cin[j] = it.Cin; t.Cout_ld[j] = it.Cout_ld;
+      t.Kf[j] = (taps * it.Cin + 63) / 64 * 64;
+      t.Kd[j] = (taps * it.Cout_ld + 63) / 64 * 64;
+      const long long nf = ((long long)it.Cout * t.Kf[j] + kPackPerBlock - 1) / kPackPerBlock;
+      const long long nd = it.w_dgrad ? ((long long)it.Cin * t.Kd[j] + kPackPerBlock - 1) / kPackPerBlock : 0;
+      DEI2I_REQUIRE(t.blk[j] + nf + nd < (1ll << 30), "pack_weight_multi: too many blocks");
+      t.blk_fwd[j] = (int)nf;
+      t.blk[j + 1] = t.blk[j] + (int)(nf + nd);
+    }
+    if (t.count == 0) break;
+    pack_multi_kernel<<<t.blk[t.count], 256, 0, ST>>>(t);
+    if (int rc = LAUNCH_OK("pack_multi_kernel")) return rc;
   }
   return 0;
 }

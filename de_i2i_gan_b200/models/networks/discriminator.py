@@ -63,6 +63,7 @@ class DefectGanDiscriminator(BaseNetwork):
         assert isinstance(x, torch.Tensor), "x must be Original Images: Torch.Tensor"
         feat = Fn.to_nhwc(x)
         Fn.prefetch_spectral_norm(self, self.training)
+        Fn.prefetch_packs(self)
         enc = list(self.enc_blk)
         for i, blk in enumerate(enc):
             feat = blk(feat, out_pad=next_pad(enc, i)) if isinstance(blk, ConvBlock) else blk(feat)

@@ -99,6 +99,7 @@ class DefectGanGenerator(BaseNetwork):
         seg = Fn.to_nhwc(labels.float())
         seg.key = Fn.label_key(labels)
         Fn.prefetch_spectral_norm(self, self.training)
+        Fn.prefetch_packs(self)
         enc = list(self.enc_blk)
         feat = self.stem(x, carrier_out=True, out_pad=next_pad([self.stem] + enc, 0))
         for i, blk in enumerate(enc):

@@ -175,6 +175,38 @@ def pack_weight(w: torch.Tensor, spec: ConvSpec, inv_sigma: torch.Tensor = None,
     return w_fwd, w_dg
 
 
+def pack_weight_multi(entries):
+    """entries: [(w, w2 | None, spec)] - `spec.cout` rows in total, the first `w.shape[0]` from w, the rest from w2.  All packed BF16
+    matrices (forward and dgrad layout) of the list in one launch per 32 entries, carved out of ONE allocation.
+    -> [(w_fwd, w_dgrad)].  BF16 mode only (the FP32-parity path packs per weight)."""
+    assert ACT_DTYPE == torch.bfloat16
+    if not entries:
+        return []
+    dev = entries[0][0].device
+    al = lambda k: (k + 127) // 128 * 128  # noqa: E731  256-byte aligned matrices (TMA global addresses need 16)
+    sizes = [(spec.cout * spec.kf, spec.cin_ld * spec.kd) for _, _, spec in entries]
+    flat = torch.empty(sum(al(a) + al(b) for a, b in sizes), dtype=torch.bfloat16, device=dev)
+    items = (_lib.PackItem * len(entries))()
+    off, res = 0, []
+    for i, ((w, w2, spec), (nf, nd)) in enumerate(zip(entries, sizes)):
+        _chk_f32(w, "w")
+        rows = w.shape[0] + (w2.shape[0] if w2 is not None else 0)
+        assert rows == spec.cout and tuple(w.shape[1:]) == (spec.cin, spec.kh, spec.kw_) and w.is_contiguous(), (w.shape, spec)
+        if w2 is not None:
+            _chk_f32(w2, "w2")
+            assert tuple(w2.shape[1:]) == tuple(w.shape[1:]) and w2.is_contiguous()
+        w_fwd = flat[off:off + nf].view(spec.cout, spec.kf)
+        off += al(nf)
+        w_dg = flat[off:off + nd].view(spec.cin_ld, spec.kd)
+        off += al(nd)
+        it = items[i]
+        it.w, it.w2, it.w_fwd, it.w_dgrad = _p(w), _p(w2), _p(w_fwd), _p(w_dg)
+        it.rows_w, it.Cout, it.Cin_real, it.kh, it.kw, it.Cin, it.Cout_ld = w.shape[0], spec.cout, spec.cin, spec.kh, spec.kw_, spec.cin_ld, spec.cout_ld
+        res.append((w_fwd, w_dg))
+    check(_lib.load().dei2i_pack_weight_multi(items, len(entries), _stream()), "dei2i_pack_weight_multi")
+    return res
+
+
 def _kind(op, spec, flops):
     """Timing class of a convolution launch: 'dense' (tcgen05, tensor-bound), 'skinny' (HBM-bound by construction) or
     'tiny' (< 2 GFLOP: the 5x5 SPADE class-map convolutions, classifier heads, linears - launch-latency bound)."""

@@ -78,6 +78,20 @@ typedef struct dei2i_conv_epilogue {
 int dei2i_pack_weight(const float* w, const float* inv_sigma, int Cout, int Cin_real, int kh, int kw, int Cin,
                       int Cout_ld, void* w_fwd, void* w_dgrad, dei2i_stream stream);
 
+/* dei2i_pack_weight for many weights in one launch per 32 items (a DefectGAN network has ~50 convolutions whose ~8 us packing
+ * launches are pure latency; same call sites).  items is a HOST array.  w2 != NULL packs the row-wise concatenation [w ; w2]
+ * (rows_w rows from w, the rest from w2: SPADE's mlp_gamma | mlp_beta and the two generator heads, normalization.py:21-22,
+ * generator.py:224-241) without materialising it.  Results are bit-identical to dei2i_pack_weight without inv_sigma. */
+typedef struct dei2i_pack_item {
+  const float* w;
+  const float* w2; /* or NULL */
+  void* w_fwd;
+  void* w_dgrad;   /* or NULL */
+  int rows_w;      /* rows taken from w (= Cout when w2 is NULL) */
+  int Cout, Cin_real, kh, kw, Cin, Cout_ld;
+} dei2i_pack_item;
+int dei2i_pack_weight_multi(const dei2i_pack_item* items, int count, dei2i_stream stream);
+
 /* y = act(scale*conv(x) + bias + noise_weight*noise) + residual    (nn.Conv2d forward + fused followers) */
 int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const dei2i_conv_geom* g,
                      const dei2i_conv_epilogue* e, dei2i_stream stream);

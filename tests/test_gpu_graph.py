@@ -167,3 +167,33 @@ def test_wgrad_accumulating_into_grad_buffers_matches_autograd_accumulation(tmp_
         assert float(diff.max()) <= 1e-7 and int((diff > 0).sum()) < 1e-3 * diff.numel(), (float(diff.max()), int((diff > 0).sum()))
     finally:
         A.set_noise_source(None)
+
+
+def test_network_level_weight_packing_is_invisible(tmp_path, monkeypatch):
+    """Fn.prefetch_packs (all weights of a network packed in one launch at the top of its forward) vs the per-convolution packing:
+    identical losses and parameters after three D + G steps, and far fewer launches."""
+    from de_i2i_gan_b200 import functional as Fn, ops
+    from de_i2i_gan_b200.models.networks import architecture as A
+    g = torch.Generator().manual_seed(4)
+    bg = torch.randn(2, 3, 128, 128, generator=g).clamp(-1, 1).cuda()
+    df = torch.randn(2, 3, 128, 128, generator=g).clamp(-1, 1).cuda()
+    lab = torch.tensor([[0., 1, 0, 0, 1, 0], [0., 0, 0, 1, 0, 0]]).cuda()
+    A.set_noise_source(_noise)
+    try:
+        runs = []
+        for multi in (True, False):
+            monkeypatch.setattr(Fn, "PACK_MULTI", multi)
+            tr = _trainer(False, tmp_path)
+            for it in range(3):
+                l0 = ops.launch_count()
+                tr._train_discriminator_once(bg, lab, df)
+                tr._train_generator_once(bg, lab, df)
+                launches = ops.launch_count() - l0
+            torch.cuda.synchronize()
+            params = torch.cat([p.detach().flatten().cpu() for net in tr.model.networks.values() for p in net.parameters()])
+            losses = [list(v) for t in tr.losses.values() for v in t.values()]
+            runs.append((params, losses, launches))
+        assert torch.equal(runs[0][0], runs[1][0]) and runs[0][1] == runs[1][1]
+        assert runs[0][2] < runs[1][2] - 100, (runs[0][2], runs[1][2])
+    finally:
+        A.set_noise_source(None)

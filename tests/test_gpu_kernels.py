@@ -827,3 +827,30 @@ def test_bn_fwd_writes_consumer_padding(pad, act, with_res):
     assert (yp != ref).float().mean().item() < 0.01
     assert torch.allclose(savep, save0, rtol=1e-6, atol=1e-7) and torch.allclose(rm1, rm0, rtol=1e-6, atol=1e-7)
     assert torch.allclose(rv1, rv0, rtol=1e-6, atol=1e-7)
+
+
+def test_pack_weight_multi_matches_per_weight_packing():
+    """dei2i_pack_weight_multi (one launch per 32 weights, incl. the row-wise concatenation of two weights) against dei2i_pack_weight:
+    bit-identical forward and dgrad matrices; 40 items -> two launches."""
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(21)
+    entries, want = [], []
+    shapes = [(64, 3, 7, 7), (128, 64, 4, 4), (256, 256, 3, 3), (6, 128, 3, 3), (1, 64, 3, 3), (48, 24, 1, 1), (64, 64, 7, 1)] * 5
+    for i, (co, ci, kh, kw) in enumerate(shapes):
+        w = torch.randn(co, ci, kh, kw, generator=g).cuda()
+        spec = ops.ConvSpec(ci, co, kh, 1, 0, "zeros", kw if kw != kh else 0)
+        entries.append((w, None, spec))
+        want.append(ops.pack_weight(w, spec))
+    for ca, cb, ci in ((256, 256, 128), (3, 1, 64), (5, 120, 16), (64, 64, 128), (8, 8, 8)):
+        wa, wb = torch.randn(ca, ci, 3, 3, generator=g).cuda(), torch.randn(cb, ci, 3, 3, generator=g).cuda()
+        spec = ops.ConvSpec(ci, ca + cb, 3, 1, 1, "zeros")
+        entries.append((wa, wb, spec))
+        want.append(ops.pack_weight(torch.cat([wa, wb], 0).contiguous(), spec))
+    l0 = ops.launch_count()
+    got = ops.pack_weight_multi(entries)
+    assert ops.launch_count() - l0 == 2
+    torch.cuda.synchronize()
+    for (gf, gd), (wf, wd), (w, _, spec) in zip(got, want, entries):
+        assert gf.shape == wf.shape and gd.shape == wd.shape
+        assert torch.equal(gf, wf) and torch.equal(gd, wd), spec
+        assert gf.data_ptr() % 256 == 0 and gd.data_ptr() % 256 == 0

@@ -31,6 +31,8 @@ int g_tune_conv_bn = 0;
 int g_tune_wgrad_bn = 0;
 int g_tune_wgrad_waves = 0;
 int g_tune_tma_ms = 0;
+int g_tune_mma_issue = -1;   // conv_tma_kernel MMA issue loop: -1 = auto by N tile, 1 = warp-uniform with an elected lane, 0 = single thread
+int g_tune_conv_ring = 1;    // 1 = kh x 1 convolutions on the row-ring kernel where applicable (conv_tma.cu)
 int g_tune_wgrad_swap = 1;   // 1 = operand-swapped wgrad where applicable (conv_igemm.cu), 0 = always the ordinary operand roles
 int g_tune_f32_tf32 = 0;   // FP32-parity path: 1 = forward / dgrad of TMA-able geometries on the kind::tf32 tensor-core kernel
 int g_tune_conv_path = 0;  // 0 = auto (TMA im2col kernels where applicable), 1 = always the cp.async gather kernels
@@ -195,6 +197,8 @@ extern "C" int dei2i_set_tuning(const char* key, int value) {
   else if (!strcmp(key, "f32_tf32")) slot = &dei2i::g_tune_f32_tf32;
   else if (!strcmp(key, "tma_ms")) slot = &dei2i::g_tune_tma_ms;
   else if (!strcmp(key, "wgrad_swap")) slot = &dei2i::g_tune_wgrad_swap;
+  else if (!strcmp(key, "conv_ring")) slot = &dei2i::g_tune_conv_ring;
+  else if (!strcmp(key, "mma_issue")) slot = &dei2i::g_tune_mma_issue;
   if (slot == nullptr) return -1;
   int old = *slot;
   *slot = value;

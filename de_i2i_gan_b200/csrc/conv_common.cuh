@@ -94,6 +94,7 @@ struct TmaConvParams {
   // the CTAs of a wave share the dY tiles (identical for the four parities) in L2; the tile's (py, px) replace b_py / b_px and are
   // added to om.oy0 / om.ox0.  Four launches of 28 .. 64 CTAs each become one of 112 .. 148.
   int npar;
+  int issue_mode;  // set by run_conv_tma from the "mma_issue" tuning knob
   int num_kb;      // taps * cin_blocks
   int m_tiles, n_tiles;
   OutMap om;

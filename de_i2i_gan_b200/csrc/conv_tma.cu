@@ -137,8 +137,42 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     }
   } else if (warp == 9) {
     // =========================== MMA issuer ===========================
-    if (lane == 0) {
+    // The whole warp walks the loop, one elected lane issues (see conv_ring_kernel): stage addresses and descriptors stay in uniform
+    // registers and the MMAs of a k block go out back to back.  With `if (lane == 0)` around the loop every UTCHMMA was preceded by
+    // ~18 dependent instructions (~110 cycles) - hidden under a 128-cycle N = 256 MMA, but THE bound for N = 64 / 128.
+    if (p.issue_mode == 0) {  // A/B switch (dei2i_set_tuning("mma_issue", 0)): the per-thread loop this kernel had before
+      if (lane == 0) {
+        constexpr uint32_t idesc = TF32 ? make_idesc_tf32(128, BLOCK_N, 0, 0) : make_idesc_bf16(128, BLOCK_N, 0, 0);
+        uint32_t it = 0, tcount = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+          const uint32_t buf = tcount & 1u;
+          mbar_wait(&tempty_bar[buf], ((tcount >> 1) & 1u) ^ 1u);
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + buf * (MS * BLOCK_N);
+          for (int kb = 0; kb < p.num_kb; ++kb, ++it) {
+            const uint32_t stage = it % STAGES;
+            mbar_wait(&full_bar[stage], (it / STAGES) & 1u);
+            tc_fence_after();
+            const uint32_t a_addr = smem_u32(smem + stage * S::kStage);
+            const uint64_t b_desc = make_smem_desc(a_addr + MS * kTmaATile, 16, 1024, 2);
+#pragma unroll
+            for (int ms = 0; ms < MS; ++ms) {
+              const uint64_t a_desc = make_smem_desc(a_addr + ms * kTmaATile, 16, 1024, 2);
+#pragma unroll
+              for (int k = 0; k < 4; ++k) {
+                if (TF32) tc_mma_tf32(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+                else tc_mma_bf16(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+              }
+            }
+            tc_commit(&empty_bar[stage]);
+          }
+          tc_commit(&tfull_bar[buf]);
+        }
+      }
+    } else {
       constexpr uint32_t idesc = TF32 ? make_idesc_tf32(128, BLOCK_N, 0, 0) : make_idesc_bf16(128, BLOCK_N, 0, 0);
+      const uint64_t desc_hi = make_smem_desc(0, 16, 1024, 2);
+      const uint32_t smem_base = smem_u32(smem);
       uint32_t it = 0, tcount = 0;
       for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
         const uint32_t buf = tcount & 1u;
@@ -151,20 +185,30 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           const uint32_t ph = (it / STAGES) & 1u;
           mbar_wait(&full_bar[stage], ph);
           tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem + stage * S::kStage);
-          const uint64_t b_desc = make_smem_desc(a_addr + MS * kTmaATile, 16, 1024, 2);
+          const uint32_t a_addr = smem_base + stage * S::kStage;
+          const uint64_t b_desc = desc_hi | (uint64_t)(((a_addr + MS * kTmaATile) & 0x3FFFFu) >> 4);
+          if (elect_one()) {
 #pragma unroll
-          for (int ms = 0; ms < MS; ++ms) {
-            const uint64_t a_desc = make_smem_desc(a_addr + ms * kTmaATile, 16, 1024, 2);
+            for (int ms = 0; ms < MS; ++ms) {
+              const uint64_t a_desc = desc_hi | (uint64_t)(((a_addr + ms * kTmaATile) & 0x3FFFFu) >> 4);
+              if (TF32) {
+                if (kb == 0) tc_mma_tf32(d_tmem + ms * BLOCK_N, a_desc, b_desc, idesc, 0);
+                else tc_mma_tf32(d_tmem + ms * BLOCK_N, a_desc, b_desc, idesc, 1);
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              if (TF32) tc_mma_tf32(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
-              else tc_mma_bf16(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+                for (int k = 1; k < 4; ++k) tc_mma_tf32(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, 1);
+              } else {
+                if (kb == 0) tc_mma_bf16(d_tmem + ms * BLOCK_N, a_desc, b_desc, idesc, 0);
+                else tc_mma_bf16(d_tmem + ms * BLOCK_N, a_desc, b_desc, idesc, 1);
+#pragma unroll
+                for (int k = 1; k < 4; ++k) tc_mma_bf16(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, 1);
+              }
             }
+            tc_commit(&empty_bar[stage]);
           }
-          tc_commit(&empty_bar[stage]);
+          __syncwarp();
         }
-        tc_commit(&tfull_bar[buf]);
+        if (elect_one()) tc_commit(&tfull_bar[buf]);
+        __syncwarp();
       }
     }
   } else {
@@ -379,6 +423,218 @@ static int num_sms() {
   return g_num_sms;
 }
 
+// ======================================================================================================================
+// Row-ring variant for kh x 1 filters (the row-packed generator stem, generator.py:76-86: 7 x 1 over 64 packed channels, forward and
+// dgrad).  The generic kernel fetches a 128-pixel A tile per filter tap: for a kh x 1 filter the tap r tile of output row y IS the
+// tap r - 1 tile of output row y + 1, so every input tile travels L2 -> shared memory kh times and the kernel sits at the fill
+// bandwidth (168 KB per 128 output pixels, 196 TFLOP/s).  Here a CTA walks DOWN a 128-pixel column block: input-row tiles live in a
+// ring of kRingSlots slots, each fetched once and used by kh consecutive output rows; the weights of all taps stay resident.
+// Per output row: ONE 16 KB tile in, kh x 4 MMAs (128 x 64 x 16), one accumulator out.  Epilogue: scale only, BF16, linear rows.
+constexpr int kRingSlots = 9;
+constexpr int kRingKh = 7;  // resident weight blocks (8 KB each)
+struct RingSmem {
+  static constexpr int kB = kRingKh * 64 * 128;
+  static constexpr int kRing = kRingSlots * kTmaATile;
+  static constexpr int kStageOut = kB + kRing;
+  static constexpr int kBarOff = kStageOut + 8 * 2048;
+  static constexpr int kTotal = kBarOff + (2 * kRingSlots + 5) * 8 + 16 + 1024;
+};
+
+__global__ void __launch_bounds__(kTmaThreads, 1)
+conv_ring_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const TmaConvParams p,
+                 long long tiles_per_cta, long long total_tiles) {
+  using S = RingSmem;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* b_smem = smem;
+  uint8_t* ring = smem + S::kB;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
+  uint64_t* empty_bar = full_bar + kRingSlots;
+  uint64_t* tfull_bar = empty_bar + kRingSlots;  // [2]
+  uint64_t* tempty_bar = tfull_bar + 2;          // [2]
+  uint64_t* w_bar = tempty_bar + 2;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(w_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  constexpr uint32_t kTmemCols = 128;  // two 64-column accumulators
+  const int kh = p.kh;
+  const int CB = p.Wo / 128;
+  const long long t0 = (long long)blockIdx.x * tiles_per_cta;
+  const long long t1 = t0 + tiles_per_cta < total_tiles ? t0 + tiles_per_cta : total_tiles;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kRingSlots; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tfull_bar[b], 1);
+      mbar_init(&tempty_bar[b], 128);
+    }
+    mbar_init(w_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 8 && lane == 0) {
+    tma_prefetch_desc(&tmap_a);
+    tma_prefetch_desc(&tmap_b);
+  }
+  if (warp == 9) tmem_alloc(tmem_ptr_smem, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 8) {
+    // =========================== TMA producer ===========================
+    if (lane == 0 && t0 < t1) {
+      mbar_arrive_expect_tx(w_bar, (uint32_t)kh * 8192u);
+      for (int r = 0; r < kh; ++r) tma_load_2d(b_smem + r * 8192, &tmap_b, w_bar, r * p.b_kw * 64, 0);
+      uint32_t L = 0;  // row-tile loads issued so far
+      for (long long t = t0; t < t1;) {
+        const long long strip = t / p.Ho;
+        const int ya = (int)(t - strip * p.Ho);
+        const int yb = (int)((long long)p.Ho < ya + (t1 - t) ? (long long)p.Ho : ya + (t1 - t));
+        const int img = (int)(strip / CB), cb = (int)(strip - (long long)img * CB);
+        for (int j = ya; j < yb + kh - 1; ++j, ++L) {
+          const uint32_t slot = L % kRingSlots;
+          mbar_wait(&empty_bar[slot], ((L / kRingSlots) & 1u) ^ 1u);
+          mbar_arrive_expect_tx(&full_bar[slot], (uint32_t)kTmaATile);
+          const int jb = j < p.Ho - 1 ? j : p.Ho - 1;  // base rows are confined to the traversal box; the rest is a filter offset
+          tma_load_im2col_4d(ring + slot * kTmaATile, &tmap_a, &full_bar[slot], 0, cb * 128 + p.lower_w, jb + p.lower, img, (uint16_t)0,
+                             (uint16_t)(j - jb));
+        }
+        t += yb - ya;
+      }
+    }
+  } else if (warp == 9) {
+    // =========================== MMA issuer ===========================
+    // The whole warp walks the loop and one elected lane issues: descriptors and addresses are then warp-uniform values that live
+    // in uniform registers.  With `if (lane == 0)` around the loop the compiler computes them per thread and moves them to uniform
+    // registers before every UTCHMMA - 18 dependent instructions, ~120 cycles per MMA, which is what bounds 128 x 64 x 16 MMAs
+    // (32 cycles of tensor work each; measured: 205 us with the fill solved, 105 us without the MMAs).
+    if (t0 < t1) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, 64, 0, 0);
+      mbar_wait(w_bar, 0);
+      tc_fence_after();
+      const uint32_t b_addr = smem_u32(b_smem), ring_addr = smem_u32(ring);
+      const uint64_t desc_hi = make_smem_desc(0, 16, 1024, 2);  // everything but the 14-bit start address
+      uint32_t L0 = 0, tcount = 0;  // first load of the current segment, accumulator counter
+      for (long long t = t0; t < t1;) {
+        const long long strip = t / p.Ho;
+        const int ya = (int)(t - strip * p.Ho);
+        const int nrows = (int)((long long)p.Ho - ya < t1 - t ? (long long)p.Ho - ya : t1 - t);
+        for (int y = 0; y < nrows; ++y, ++tcount) {
+          const uint32_t buf = tcount & 1u;
+          mbar_wait(&tempty_bar[buf], ((tcount >> 1) & 1u) ^ 1u);
+          for (int r = (y == 0 ? 0 : kh - 1); r < kh; ++r) {  // rows y .. y + kh - 2 were waited for by earlier output rows
+            const uint32_t L = L0 + y + r;
+            mbar_wait(&full_bar[L % kRingSlots], (L / kRingSlots) & 1u);
+          }
+          tc_fence_after();
+          const uint32_t d_tmem = tmem_base + buf * 64;
+          uint32_t slot = (L0 + y) % kRingSlots;
+          for (int r = 0; r < kh; ++r) {
+            const int wr = p.flip ? kh - 1 - r : r;
+            const uint64_t a_desc = desc_hi | (uint64_t)(((ring_addr + slot * kTmaATile) & 0x3FFFFu) >> 4);
+            const uint64_t b_desc = desc_hi | (uint64_t)(((b_addr + wr * 8192) & 0x3FFFFu) >> 4);
+            if (elect_one()) {
+              if (r == 0) tc_mma_bf16(d_tmem, a_desc, b_desc, idesc, 0);
+              else tc_mma_bf16(d_tmem, a_desc, b_desc, idesc, 1);
+              tc_mma_bf16(d_tmem, a_desc + 2, b_desc + 2, idesc, 1);
+              tc_mma_bf16(d_tmem, a_desc + 4, b_desc + 4, idesc, 1);
+              tc_mma_bf16(d_tmem, a_desc + 6, b_desc + 6, idesc, 1);
+            }
+            __syncwarp();
+            if (++slot == kRingSlots) slot = 0;
+          }
+          if (elect_one()) {
+            tc_commit(&empty_bar[(L0 + y) % kRingSlots]);  // input row y is not needed by later output rows
+            if (y == nrows - 1)
+              for (int r = 1; r < kh; ++r) tc_commit(&empty_bar[(L0 + y + r) % kRingSlots]);  // end of the segment: the tail rows too
+            tc_commit(&tfull_bar[buf]);
+          }
+          __syncwarp();
+        }
+        L0 += nrows + kh - 1;
+        t += nrows;
+      }
+    }
+  } else if (t0 < t1) {
+    // =========================== epilogue (two groups of four warps, one per accumulator buffer) ===========================
+    const int eg = warp >> 2, qw = warp & 3;
+    const Epilogue& e = p.e;
+    const float osc = e.scale != nullptr ? __ldg(e.scale) : 1.f;
+    uint8_t* stage = smem + S::kStageOut + warp * 2048;
+    const int sub_r = lane >> 2, sub_j = lane & 3;
+    const int my_sw = (lane >> 1) & 3;
+    uint32_t tcount = 0;
+    for (long long t = t0; t < t1; ++t, ++tcount) {
+      if ((int)(tcount & 1u) != eg) continue;
+      const long long strip = t / p.Ho;
+      const int y = (int)(t - strip * p.Ho);
+      const int img = (int)(strip / CB), cb = (int)(strip - (long long)img * CB);
+      const long long m_base = ((long long)img * p.Ho + y) * p.Wo + cb * 128 + qw * 32;  // first output row of this warp
+      mbar_wait(&tfull_bar[eg], (tcount >> 1) & 1u);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < 64; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(qw * 32) << 16) + eg * 64 + (uint32_t)c, v);
+        tc_wait_ld();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          float f[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) f[k] = __uint_as_float(v[8 * j + k]) * osc;
+          *reinterpret_cast<uint4*>(stage + lane * 64 + ((j ^ my_sw) << 4)) =
+              make_uint4(pack_bf16(f[0], f[1]), pack_bf16(f[2], f[3]), pack_bf16(f[4], f[5]), pack_bf16(f[6], f[7]));
+        }
+        __syncwarp();
+#pragma unroll
+        for (int itr = 0; itr < 4; ++itr) {
+          const int r = itr * 8 + sub_r;
+          const uint4 val = *reinterpret_cast<const uint4*>(stage + r * 64 + ((sub_j ^ ((r >> 1) & 3)) << 4));
+          *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(e.out) + ((m_base + r) * e.ld + c + sub_j * 8) * 2) = val;
+        }
+        __syncwarp();
+      }
+      tc_fence_before();
+      mbar_arrive(&tempty_bar[eg]);
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 9) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+extern int g_tune_conv_ring;  // 1 (default): kh x 1 convolutions that qualify run on conv_ring_kernel
+static bool conv_ring_applicable(const TmaConvParams& p, int rows, int C, int W, int bn) {
+  const Epilogue& e = p.e;
+  return g_tune_conv_ring != 0 && bn == 64 && rows <= 64 && C == 64 && p.cin_blocks == 1 && p.kw == 1 && p.kh >= 2 && p.kh <= kRingKh &&
+         p.stride == 1 && p.lower_w == 0 && p.Wo == W && p.Wo % 128 == 0 && p.om.linear && p.npar <= 1 && p.b_sub == 1 && e.bias == nullptr &&
+         e.noise == nullptr && e.residual == nullptr && e.act == 0 && !e.out_fp32 && e.stats == nullptr && e.ld == 64 &&
+         p.M == (p.M / ((long long)p.Ho * p.Wo)) * p.Ho * p.Wo && p.Ho >= p.kh;
+}
+static int launch_conv_ring(const CUtensorMap& ta, const CUtensorMap& tb, const TmaConvParams& p, cudaStream_t st) {
+  static_assert(RingSmem::kTotal <= 227 * 1024 && RingSmem::kTotal > 114 * 1024, "shared memory budget / one CTA per SM");
+  static bool attr_done = false;
+  if (!attr_done) {
+    DEI2I_CUDA(cudaFuncSetAttribute(conv_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, RingSmem::kTotal));
+    attr_done = true;
+  }
+  const long long total = (p.M / ((long long)p.Ho * p.Wo)) * (p.Wo / 128) * p.Ho;  // (image, column block, output row)
+  const int grid = total < num_sms() ? (int)total : num_sms();
+  const long long per = (total + grid - 1) / grid;
+  conv_ring_kernel<<<grid, kTmaThreads, RingSmem::kTotal, st>>>(ta, tb, p, per, total);
+  count_launch();
+  trace_kernel("conv_ring<%d>", p.kh);
+  return check_cuda(cudaGetLastError(), "conv_ring_kernel launch");
+}
+
 template <int BN, int ST, int MS, bool TF32 = false>
 static int launch_tma(const CUtensorMap& ta, const CUtensorMap& tb, const TmaConvParams& p, cudaStream_t st) {
   using S = TmaSmem<BN, ST, MS>;
@@ -399,11 +655,15 @@ static int launch_tma(const CUtensorMap& ta, const CUtensorMap& tb, const TmaCon
 }
 
 extern int g_tune_tma_ms;  // 0 = auto, 1 / 2 = force the number of 128-pixel sub-tiles per work tile
+extern int g_tune_mma_issue;  // -1 (default): warp-uniform MMA issue loop for N <= 128, single-thread loop for N = 256; 0 / 1 force one
 int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, int rows, int K, const TmaConvParams& p_in,
                  int upper, int upper_w, cudaStream_t st, bool tf32) {
   TmaConvParams p = p_in;
   int bn = 256;
   while (bn > 64 && bn / 2 >= rows) bn /= 2;
+  // same-box A/B: N = 64 454 -> 392 us (128 -> 64 at 256^2), N = 128 339 -> 337 us, N = 256 114.0 -> 115.5 us (the elect / syncwarp per k
+  // block costs where a 128-cycle MMA already hid the issue overhead)
+  p.issue_mode = g_tune_mma_issue >= 0 ? g_tune_mma_issue : (bn <= 128 ? 1 : 0);
   if (tf32) {  // FP32 operands: 32 channels per 128-byte row, one 128-pixel tile per work tile
     CUtensorMap ta, tb;
     if (int rc = encode_tmap_im2col_f32(&ta, x, (uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N, p.lower_w, upper_w, p.lower, upper,
@@ -426,6 +686,7 @@ int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, in
     return rc;
   if (int rc = encode_tmap_2d_bf16(&tb, wmat, (uint64_t)K, (uint64_t)rows, (uint64_t)K * 2, 64, (uint32_t)bn, 1)) return rc;
   p.n_tiles = (rows + bn - 1) / bn;
+  if (conv_ring_applicable(p, rows, C, W, bn)) return launch_conv_ring(ta, tb, p, st);
   // narrow N: two 128-pixel A tiles share each B tile (halves the weight traffic per FLOP through L2 / shared memory) as long
   // as that still leaves every SM a couple of work tiles
   const long long mt2 = (p.M + 255) / 256;

@@ -854,3 +854,39 @@ def test_pack_weight_multi_matches_per_weight_packing():
         assert gf.shape == wf.shape and gd.shape == wd.shape
         assert torch.equal(gf, wf) and torch.equal(gd, wd), spec
         assert gf.data_ptr() % 256 == 0 and gd.data_ptr() % 256 == 0
+
+
+@pytest.mark.parametrize("n,ho,w,kh", [(4, 40, 256, 7), (2, 20, 128, 7), (3, 9, 256, 3), (1, 150, 128, 7), (33, 7, 128, 7)])
+def test_conv_ring_khx1_forward_and_dgrad(n, ho, w, kh):
+    """conv_ring_kernel (kh x 1 filters over 64 channels, the row-packed stem): forward and dgrad against torch and against the generic
+    TMA kernel on the same inputs.  Shapes make CTAs own one row, several rows, and ranges that cross image / column-block borders."""
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(100 + n + ho)
+    h = ho + kh - 1
+    x = q(torch.randn(n, 64, h, w, generator=g))
+    wt = q(torch.randn(64, 64, kh, 1, generator=g) / (8 * kh ** 0.5))
+    sc = torch.tensor([0.7], device="cuda")
+    spec = ops.ConvSpec(64, 64, kh, 1, 0, "zeros", 1)
+    w_fwd, w_dg = ops.pack_weight(wt.cuda(), spec)
+    xr = x.clone().requires_grad_(True)
+    yr = 0.7 * F.conv2d(xr, wt)
+    dy = q(torch.randn(yr.shape, generator=g))
+    (dx_ref,) = torch.autograd.grad(yr, xr, dy)
+    outs = {}
+    for ring in (1, 0):
+        ops.set_tuning("conv_ring", ring)
+        try:
+            y = ops.conv2d_fwd(to_dev(x), w_fwd, spec, scale=sc)
+            k_f = ops.last_kernel()
+            dx = ops.conv2d_dgrad(to_dev(dy), w_dg, spec, (h, w), scale=sc)
+            k_d = ops.last_kernel()
+        finally:
+            ops.set_tuning("conv_ring", 1)
+        torch.cuda.synchronize()
+        assert ("conv_ring" in k_f) == bool(ring) and ("conv_ring" in k_d) == bool(ring), (k_f, k_d)
+        outs[ring] = (from_dev(y, 64), from_dev(dx, 64))
+    e_f, e_d = rel_err(outs[1][0], yr.detach()), rel_err(outs[1][1], dx_ref)
+    _report(f"conv_ring/{n}x{ho}x{w}k{kh}", fwd=e_f, dgrad=e_d, vs_generic_fwd=rel_err(outs[1][0], outs[0][0]), vs_generic_dgrad=rel_err(outs[1][1], outs[0][1]))
+    assert e_f < TOL_BF16 and e_d < TOL_BF16, (e_f, e_d)
+    assert torch.equal(outs[1][0], outs[0][0]) or rel_err(outs[1][0], outs[0][0]) < 4e-3
+    assert torch.equal(outs[1][1], outs[0][1]) or rel_err(outs[1][1], outs[0][1]) < 4e-3

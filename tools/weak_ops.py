@@ -41,6 +41,8 @@ def conv_case(n, cin, h, w, cout, kh, kw, s, which="fdw"):
 
 
 def main():
+    if os.environ.get("MMA_ISSUE"):
+        ops.set_tuning("mma_issue", int(os.environ["MMA_ISSUE"]))
     names = sys.argv[1:] or ["fwd64", "wgrad64", "stem", "d5", "spade_bwd", "bn", "heads"]
     g = torch.Generator(device="cuda").manual_seed(0)
     if "fwd64" in names:
@@ -54,6 +56,9 @@ def main():
         conv_case(32, 256, 66, 66, 256, 3, 3, 1, "fdw")
     if "stem" in names:
         conv_case(32, 64, 262, 256, 64, 7, 1, 1, "fdw")
+        ops.set_tuning("conv_ring", 0)
+        conv_case(32, 64, 262, 256, 64, 7, 1, 1, "fd")
+        ops.set_tuning("conv_ring", 1)
     if "d5" in names:
         conv_case(32, 1024, 10, 10, 2048, 4, 4, 2, "fdw")
         conv_case(32, 512, 18, 18, 1024, 4, 4, 2, "fdw")

@@ -48,11 +48,20 @@ DEVINL void chan_merge(float& n, float& mean, float& m2, float nb, float mb, flo
 
 // TF32 = true: FP32 activations / weights in shared memory (32 channels per 128-byte row), kind::tf32 MMA (K = 8 per instruction),
 // FP32 output - the tensor-core variant of the FP32-parity path.
-template <int BLOCK_N, int STAGES, int MS, bool TF32 = false>
+// PAIR = true: launched as 2-CTA clusters; the pair runs ONE M = 256 (cta_group::2) MMA per k step - CTA r owns pixel tile 2 v + r of
+// work item v and loads its own A tile plus HALF of the weight tile (rows r * BLOCK_N / 2 ..), so every MMA reads half the B bytes per
+// SM from shared memory (the single-CTA SS-mode MMA is bound by its operand reads: 4 KB of A + 8 KB of B per 128-cycle N = 256 MMA)
+// and the L2 -> shared-memory fill drops from 48 KB to 32 KB per k block.  Only the even CTA issues MMAs; full barriers live in the
+// even CTA (both producers credit their bytes there), empty / accumulator-ready barriers are signalled in both by multicast commits.
+template <int BLOCK_N, int STAGES, int MS, bool TF32 = false, bool PAIR = false>
 __global__ void __launch_bounds__(kTmaThreads, 1)
 conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const TmaConvParams p) {
   constexpr int KC = TF32 ? 32 : 64;  // channels per 128-byte shared-memory row
-  using S = TmaSmem<BLOCK_N, STAGES, MS>;
+  using S = TmaSmem<PAIR ? BLOCK_N / 2 : BLOCK_N, STAGES, MS>;
+  static_assert(!PAIR || (MS == 1 && !TF32 && BLOCK_N == 256), "pair kernel: one 128-pixel tile per CTA, BF16, N = 256");
+  const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;
+  const int tile0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;       // first work item of this CTA (pair)
+  const int tstep = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
@@ -65,7 +74,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   const int lane = threadIdx.x & 31;
   constexpr uint32_t kTmemCols = 2 * MS * BLOCK_N < 32 ? 32 : 2 * MS * BLOCK_N;
   const int npar = p.npar > 1 ? p.npar : 1;
-  const int total_tiles = p.m_tiles * p.n_tiles * npar;
+  const int total_tiles = (PAIR ? (p.m_tiles + 1) / 2 : p.m_tiles) * p.n_tiles * npar;
   __shared__ __align__(16) float bias_s[1024];
   __shared__ float2 wstat[2][2][4][32];  // [epilogue group][parity][row quarter][column]: (mean, M2) of 32 rows
   const bool bias_in_smem = p.e.bias != nullptr && p.n_tiles * BLOCK_N <= 1024;
@@ -79,7 +88,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tfull_bar[b], 1);
-      mbar_init(&tempty_bar[b], 128);
+      mbar_init(&tempty_bar[b], PAIR ? 256 : 128);  // pair: the epilogue threads of both CTAs release the leader's accumulator
     }
     fence_barrier_init();
   }
@@ -87,9 +96,13 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     tma_prefetch_desc(&tmap_a);
     tma_prefetch_desc(&tmap_b);
   }
-  if (warp == 9) tmem_alloc(tmem_ptr_smem, kTmemCols);
+  if (warp == 9) {
+    if (PAIR) tmem_alloc2(tmem_ptr_smem, kTmemCols);
+    else tmem_alloc(tmem_ptr_smem, kTmemCols);
+  }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // both CTAs' barriers are initialised before either touches the other's
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr_smem;
 
@@ -98,11 +111,11 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     if (lane == 0) {
       const int HoWo = p.Ho * p.Wo;
       uint32_t it = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      for (int tile = tile0; tile < total_tiles; tile += tstep) {
         const int par = tile % npar, t2 = tile / npar;
         const int b_py = npar > 1 ? par / p.b_sub : p.b_py, b_px = npar > 1 ? par % p.b_sub : p.b_px;
-        const int m_tile = t2 / p.n_tiles;
-        const int n_tile = t2 - m_tile * p.n_tiles;
+        const int m_tile = PAIR ? (t2 / p.n_tiles) * 2 + (int)cta_rank : t2 / p.n_tiles;
+        const int n_tile = t2 - (t2 / p.n_tiles) * p.n_tiles;
         int img[MS], cw[MS], ch[MS];
 #pragma unroll
         for (int ms = 0; ms < MS; ++ms) {
@@ -120,14 +133,20 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           const uint32_t ph = (it / STAGES) & 1u;
           mbar_wait(&empty_bar[stage], ph ^ 1u);
           uint8_t* a_dst = smem + stage * S::kStage;
-          mbar_arrive_expect_tx(&full_bar[stage], S::kStage);
           const int os = p.flip ? p.kw - 1 - s : s;
           const int orr = p.flip ? p.kh - 1 - r : r;
-#pragma unroll
-          for (int ms = 0; ms < MS; ++ms)
-            tma_load_im2col_4d(a_dst + ms * kTmaATile, &tmap_a, &full_bar[stage], cb * KC, cw[ms], ch[ms], img[ms], (uint16_t)os, (uint16_t)orr);
           const int bcol = (((b_py + p.b_sub * r) * p.b_kw + (b_px + p.b_sub * s)) * p.cin_blocks + cb) * KC;
-          tma_load_2d(a_dst + MS * kTmaATile, &tmap_b, &full_bar[stage], bcol, n_tile * BLOCK_N);
+          if (PAIR) {
+            if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * S::kStage);  // this CTA's bytes and the peer's
+            tma2_load_im2col_4d(a_dst, &tmap_a, &full_bar[stage], cb * KC, cw[0], ch[0], img[0], (uint16_t)os, (uint16_t)orr);
+            tma2_load_2d(a_dst + kTmaATile, &tmap_b, &full_bar[stage], bcol, n_tile * BLOCK_N + (int)cta_rank * (BLOCK_N / 2));
+          } else {
+            mbar_arrive_expect_tx(&full_bar[stage], S::kStage);
+#pragma unroll
+            for (int ms = 0; ms < MS; ++ms)
+              tma_load_im2col_4d(a_dst + ms * kTmaATile, &tmap_a, &full_bar[stage], cb * KC, cw[ms], ch[ms], img[ms], (uint16_t)os, (uint16_t)orr);
+            tma_load_2d(a_dst + MS * kTmaATile, &tmap_b, &full_bar[stage], bcol, n_tile * BLOCK_N);
+          }
           if (++cb == p.cin_blocks) {
             cb = 0;
             if (++s == p.kw) { s = 0; ++r; }
@@ -140,11 +159,13 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     // The whole warp walks the loop, one elected lane issues (see conv_ring_kernel): stage addresses and descriptors stay in uniform
     // registers and the MMAs of a k block go out back to back.  With `if (lane == 0)` around the loop every UTCHMMA was preceded by
     // ~18 dependent instructions (~110 cycles) - hidden under a 128-cycle N = 256 MMA, but THE bound for N = 64 / 128.
-    if (p.issue_mode == 0) {  // A/B switch (dei2i_set_tuning("mma_issue", 0)): the per-thread loop this kernel had before
+    if (PAIR && cta_rank != 0) {
+      // the odd CTA of a pair issues nothing: its tile is computed by the leader's M = 256 MMAs
+    } else if (p.issue_mode == 0) {  // A/B switch (dei2i_set_tuning("mma_issue", 0)): the per-thread loop this kernel had before
       if (lane == 0) {
-        constexpr uint32_t idesc = TF32 ? make_idesc_tf32(128, BLOCK_N, 0, 0) : make_idesc_bf16(128, BLOCK_N, 0, 0);
+        constexpr uint32_t idesc = TF32 ? make_idesc_tf32(128, BLOCK_N, 0, 0) : make_idesc_bf16(PAIR ? 256 : 128, BLOCK_N, 0, 0);
         uint32_t it = 0, tcount = 0;
-        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+        for (int tile = tile0; tile < total_tiles; tile += tstep, ++tcount) {
           const uint32_t buf = tcount & 1u;
           mbar_wait(&tempty_bar[buf], ((tcount >> 1) & 1u) ^ 1u);
           tc_fence_after();
@@ -161,12 +182,15 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
                 if (TF32) tc_mma_tf32(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+                else if (PAIR) tc_mma2_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
                 else tc_mma_bf16(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
               }
             }
-            tc_commit(&empty_bar[stage]);
+            if (PAIR) tc_commit2(&empty_bar[stage]);
+            else tc_commit(&empty_bar[stage]);
           }
-          tc_commit(&tfull_bar[buf]);
+          if (PAIR) tc_commit2(&tfull_bar[buf]);
+          else tc_commit(&tfull_bar[buf]);
         }
       }
     } else {
@@ -174,7 +198,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       const uint64_t desc_hi = make_smem_desc(0, 16, 1024, 2);
       const uint32_t smem_base = smem_u32(smem);
       uint32_t it = 0, tcount = 0;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++tcount) {
+      for (int tile = tile0; tile < total_tiles; tile += tstep, ++tcount) {
         const uint32_t buf = tcount & 1u;
         const uint32_t bph = (tcount >> 1) & 1u;
         mbar_wait(&tempty_bar[buf], bph ^ 1u);
@@ -233,11 +257,11 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
     const int sub_r = lane >> 2, sub_j = lane & 3;
     const int my_sw = (lane >> 1) & 3;  // swizzle of this lane's own row
     uint32_t ti = 0, spar = 0;
-    for (int tile = blockIdx.x + eg * gridDim.x; tile < total_tiles; tile += 2 * gridDim.x, ++ti) {
+    for (int tile = tile0 + eg * tstep; tile < total_tiles; tile += 2 * tstep, ++ti) {
       const int par = tile % npar, t2 = tile / npar;
       const int oy0 = om.oy0 + (npar > 1 ? par / p.b_sub : 0), ox0 = om.ox0 + (npar > 1 ? par % p.b_sub : 0);
-      const int m_tile = t2 / p.n_tiles;
-      const int n0 = (t2 - m_tile * p.n_tiles) * BLOCK_N;
+      const int m_tile = PAIR ? (t2 / p.n_tiles) * 2 + (int)cta_rank : t2 / p.n_tiles;
+      const int n0 = (t2 - (t2 / p.n_tiles) * p.n_tiles) * BLOCK_N;
       mbar_wait(&tfull_bar[eg], ti & 1u);
       tc_fence_after();
 #pragma unroll 1
@@ -401,14 +425,17 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         }
       }  // ms
       tc_fence_before();
-      mbar_arrive(&tempty_bar[eg]);
+      if (PAIR) mbar_arrive_leader(&tempty_bar[eg]);
+      else mbar_arrive(&tempty_bar[eg]);
     }
   }
   tc_fence_before();
   __syncthreads();
+  if (PAIR) cluster_sync_all();  // neither CTA leaves (or frees TMEM) while the other may still signal it
   if (warp == 9) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, kTmemCols);
+    if (PAIR) tmem_dealloc2(tmem_base, kTmemCols);
+    else tmem_dealloc(tmem_base, kTmemCols);
   }
 }
 
@@ -654,6 +681,39 @@ static int launch_tma(const CUtensorMap& ta, const CUtensorMap& tb, const TmaCon
   return check_cuda(cudaGetLastError(), "conv_tma_kernel launch");
 }
 
+// cta_group::2 launch: 2-CTA clusters, one pair per two SMs
+template <int ST>
+static int launch_tma_pair(const CUtensorMap& ta, const CUtensorMap& tb, const TmaConvParams& p, cudaStream_t st) {
+  using S = TmaSmem<128, ST, 1>;
+  static_assert(S::kTotal + 4096 + 4096 <= 227 * 1024 && S::kTotal > 114 * 1024, "shared memory budget / one CTA per SM");
+  auto kern = conv_tma_kernel<256, ST, 1, false, true>;
+  static bool attr_done = false;
+  if (!attr_done) {
+    DEI2I_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
+    attr_done = true;
+  }
+  const int items = ((p.m_tiles + 1) / 2) * p.n_tiles;
+  const int pairs = items < num_sms() / 2 ? items : num_sms() / 2;
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(2 * pairs, 1, 1);
+  cfg.blockDim = dim3(kTmaThreads, 1, 1);
+  cfg.dynamicSmemBytes = S::kTotal;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  DEI2I_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
+  count_launch();
+  trace_kernel("conv_tma_pair<256,%d>", ST);
+  return check_cuda(cudaGetLastError(), "conv_tma_kernel (pair) launch");
+}
+
+extern int g_tune_tma_pair;  // 1: N = 256 tiles on CTA pairs (cta_group::2) where applicable, 0: single-CTA kernel
 extern int g_tune_tma_ms;  // 0 = auto, 1 / 2 = force the number of 128-pixel sub-tiles per work tile
 extern int g_tune_mma_issue;  // -1 (default): warp-uniform MMA issue loop for N <= 128, single-thread loop for N = 256; 0 / 1 force one
 int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, int rows, int K, const TmaConvParams& p_in,
@@ -687,6 +747,13 @@ int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, in
   if (int rc = encode_tmap_2d_bf16(&tb, wmat, (uint64_t)K, (uint64_t)rows, (uint64_t)K * 2, 64, (uint32_t)bn, 1)) return rc;
   p.n_tiles = (rows + bn - 1) / bn;
   if (conv_ring_applicable(p, rows, C, W, bn)) return launch_conv_ring(ta, tb, p, st);
+  if (g_tune_tma_pair != 0 && bn == 256 && rows % 256 == 0 && p.npar <= 1 && (p.M + 127) / 128 >= 2) {
+    CUtensorMap tb2;  // each CTA of a pair loads 128 of the 256 weight rows of an N tile
+    if (int rc = encode_tmap_2d_bf16(&tb2, wmat, (uint64_t)K, (uint64_t)rows, (uint64_t)K * 2, 64, 128, 1)) return rc;
+    p.m_tiles = (int)((p.M + 127) / 128);
+    p.issue_mode = 0;
+    return launch_tma_pair<6>(ta, tb2, p, st);
+  }
   // narrow N: two 128-pixel A tiles share each B tile (halves the weight traffic per FLOP through L2 / shared memory) as long
   // as that still leaves every SM a couple of work tiles
   const long long mt2 = (p.M + 255) / 256;

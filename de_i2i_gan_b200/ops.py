@@ -17,6 +17,7 @@ ACT = {None: 0, "none": 0, "leaky_relu": 1, "relu": 2, "tanh": 3, "sigmoid": 4}
 # of the activation it is given; ACT_DTYPE decides what the model-edge converters and the weight packer produce.
 #   tf32: FP32 storage as above, forward / dgrad of the TMA-able convolutions on the kind::tf32 tcgen05 kernel (10-bit mantissa
 #   products, FP32 accumulation): the fast FP32-storage mode; weight gradients and everything else stay exact FP32.
+_env_tuned = False  # DEI2I_TUNE applied (ensure_env_tuning)
 _KERNELS = os.environ.get("DEI2I_KERNELS", "bf16").lower()
 ACT_DTYPE = torch.float32 if _KERNELS in ("fp32", "f32", "tf32") else torch.bfloat16
 PRECISION = "bf16"
@@ -80,6 +81,8 @@ def pad8(c: int) -> int:
 
 
 def _stream():
+    if not _env_tuned:
+        ensure_env_tuning()
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 
@@ -943,3 +946,18 @@ def last_kernel() -> str:
 
 def set_tuning(key: str, value: int) -> int:
     return int(_lib.load().dei2i_set_tuning(key.encode(), int(value)))
+
+
+def _apply_env_tuning():
+    """DEI2I_TUNE="key=value,key=value": dei2i_set_tuning knobs from the environment (A/B runs of bench.py / the tools)."""
+    spec = os.environ.get("DEI2I_TUNE", "")
+    for kv in filter(None, (t.strip() for t in spec.split(","))):
+        k, v = kv.split("=")
+        set_tuning(k.strip(), int(v))
+
+
+def ensure_env_tuning():
+    global _env_tuned
+    if not _env_tuned:
+        _env_tuned = True
+        _apply_env_tuning()

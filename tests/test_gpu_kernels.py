@@ -890,3 +890,43 @@ def test_conv_ring_khx1_forward_and_dgrad(n, ho, w, kh):
     assert e_f < TOL_BF16 and e_d < TOL_BF16, (e_f, e_d)
     assert torch.equal(outs[1][0], outs[0][0]) or rel_err(outs[1][0], outs[0][0]) < 4e-3
     assert torch.equal(outs[1][1], outs[0][1]) or rel_err(outs[1][1], outs[0][1]) < 4e-3
+
+
+@pytest.mark.parametrize("n,cin,h,cout,k,s", [(2, 256, 34, 256, 3, 1), (3, 64, 21, 512, 3, 1), (5, 128, 18, 256, 4, 2), (1, 256, 18, 256, 3, 1),
+                                              (5, 256, 13, 768, 3, 1)])
+def test_conv_pair_kernel_matches_torch_and_single_cta(n, cin, h, cout, k, s):
+    """CTA-pair (tcgen05 cta_group::2, M = 256) variant of the N = 256 convolution tile: forward with the fused epilogue and dgrad
+    against torch and against the single-CTA kernel; odd tile counts (the second CTA of the last pair has no pixels) included."""
+    from de_i2i_gan_b200 import ops
+    g = torch.Generator().manual_seed(7 * n + cin)
+    x = q(torch.randn(n, cin, h, h, generator=g))
+    wt = q(torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5)
+    b = torch.randn(cout, generator=g)
+    spec = ops.ConvSpec(cin, cout, k, s, 0, "zeros")
+    w_fwd, w_dg = ops.pack_weight(wt.cuda(), spec)
+    xr = x.clone().requires_grad_(True)
+    yr = F.leaky_relu(F.conv2d(xr, wt, b, stride=s), 0.2)
+    pre = F.conv2d(x, wt, None, stride=s)
+    dy = q(torch.randn(pre.shape, generator=g))
+    (dx_ref,) = torch.autograd.grad(F.conv2d(xr, wt, None, stride=s), xr, dy)
+    outs = {}
+    for pair in (1, 0):
+        ops.set_tuning("tma_pair", pair)
+        try:
+            y = ops.conv2d_fwd(to_dev(x), w_fwd, spec, bias=b.cuda(), act="leaky_relu")
+            k_f = ops.last_kernel()
+            dx = ops.conv2d_dgrad(to_dev(dy), w_dg, spec, (h, h)) if cin % 256 == 0 and s == 1 else None
+            k_d = ops.last_kernel()
+        finally:
+            ops.set_tuning("tma_pair", 1)
+        torch.cuda.synchronize()
+        assert ("pair" in k_f) == bool(pair), k_f
+        outs[pair] = (from_dev(y, cout), from_dev(dx, cin) if dx is not None else None)
+        if dx is not None:
+            assert ("pair" in k_d) == bool(pair), k_d
+    e_f = rel_err(outs[1][0], yr.detach())
+    assert e_f < TOL_BF16, e_f
+    assert torch.equal(outs[1][0], outs[0][0])
+    if outs[1][1] is not None:
+        assert rel_err(outs[1][1], dx_ref) < TOL_BF16
+        assert torch.equal(outs[1][1], outs[0][1])

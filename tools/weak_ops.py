@@ -43,6 +43,8 @@ def conv_case(n, cin, h, w, cout, kh, kw, s, which="fdw"):
 def main():
     if os.environ.get("MMA_ISSUE"):
         ops.set_tuning("mma_issue", int(os.environ["MMA_ISSUE"]))
+    if os.environ.get("TMA_PAIR"):
+        ops.set_tuning("tma_pair", int(os.environ["TMA_PAIR"]))
     names = sys.argv[1:] or ["fwd64", "wgrad64", "stem", "d5", "spade_bwd", "bn", "heads"]
     g = torch.Generator(device="cuda").manual_seed(0)
     if "fwd64" in names:

@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(kTmaThreads, 1)
 conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, const TmaConvParams p) {
   constexpr int KC = TF32 ? 32 : 64;  // channels per 128-byte shared-memory row
   using S = TmaSmem<PAIR ? BLOCK_N / 2 : BLOCK_N, STAGES, MS>;
-  static_assert(!PAIR || (MS == 1 && !TF32 && BLOCK_N == 256), "pair kernel: one 128-pixel tile per CTA, BF16, N = 256");
+  static_assert(!PAIR || !TF32, "pair kernel: BF16 only");
   const uint32_t cta_rank = PAIR ? cluster_ctarank() : 0u;
   const int tile0 = PAIR ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;       // first work item of this CTA (pair)
   const int tstep = PAIR ? (int)(gridDim.x >> 1) : (int)gridDim.x;
@@ -138,8 +138,10 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           const int bcol = (((b_py + p.b_sub * r) * p.b_kw + (b_px + p.b_sub * s)) * p.cin_blocks + cb) * KC;
           if (PAIR) {
             if (cta_rank == 0) mbar_arrive_expect_tx(&full_bar[stage], 2 * S::kStage);  // this CTA's bytes and the peer's
-            tma2_load_im2col_4d(a_dst, &tmap_a, &full_bar[stage], cb * KC, cw[0], ch[0], img[0], (uint16_t)os, (uint16_t)orr);
-            tma2_load_2d(a_dst + kTmaATile, &tmap_b, &full_bar[stage], bcol, n_tile * BLOCK_N + (int)cta_rank * (BLOCK_N / 2));
+#pragma unroll
+            for (int ms = 0; ms < MS; ++ms)
+              tma2_load_im2col_4d(a_dst + ms * kTmaATile, &tmap_a, &full_bar[stage], cb * KC, cw[ms], ch[ms], img[ms], (uint16_t)os, (uint16_t)orr);
+            tma2_load_2d(a_dst + MS * kTmaATile, &tmap_b, &full_bar[stage], bcol, n_tile * BLOCK_N + (int)cta_rank * (BLOCK_N / 2));
           } else {
             mbar_arrive_expect_tx(&full_bar[stage], S::kStage);
 #pragma unroll
@@ -182,7 +184,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 #pragma unroll
               for (int k = 0; k < 4; ++k) {
                 if (TF32) tc_mma_tf32(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
-                else if (PAIR) tc_mma2_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
+                else if (PAIR) tc_mma2_bf16(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
                 else tc_mma_bf16(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, (kb | k) != 0);
               }
             }
@@ -194,7 +196,7 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         }
       }
     } else {
-      constexpr uint32_t idesc = TF32 ? make_idesc_tf32(128, BLOCK_N, 0, 0) : make_idesc_bf16(128, BLOCK_N, 0, 0);
+      constexpr uint32_t idesc = TF32 ? make_idesc_tf32(128, BLOCK_N, 0, 0) : make_idesc_bf16(PAIR ? 256 : 128, BLOCK_N, 0, 0);
       const uint64_t desc_hi = make_smem_desc(0, 16, 1024, 2);
       const uint32_t smem_base = smem_u32(smem);
       uint32_t it = 0, tcount = 0;
@@ -220,6 +222,11 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                 else tc_mma_tf32(d_tmem + ms * BLOCK_N, a_desc, b_desc, idesc, 1);
 #pragma unroll
                 for (int k = 1; k < 4; ++k) tc_mma_tf32(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, 1);
+              } else if (PAIR) {
+                if (kb == 0) tc_mma2_bf16(d_tmem + ms * BLOCK_N, a_desc, b_desc, idesc, 0);
+                else tc_mma2_bf16(d_tmem + ms * BLOCK_N, a_desc, b_desc, idesc, 1);
+#pragma unroll
+                for (int k = 1; k < 4; ++k) tc_mma2_bf16(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, 1);
               } else {
                 if (kb == 0) tc_mma_bf16(d_tmem + ms * BLOCK_N, a_desc, b_desc, idesc, 0);
                 else tc_mma_bf16(d_tmem + ms * BLOCK_N, a_desc, b_desc, idesc, 1);
@@ -227,11 +234,15 @@ conv_tma_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
                 for (int k = 1; k < 4; ++k) tc_mma_bf16(d_tmem + ms * BLOCK_N, a_desc + 2 * k, b_desc + 2 * k, idesc, 1);
               }
             }
-            tc_commit(&empty_bar[stage]);
+            if (PAIR) tc_commit2(&empty_bar[stage]);
+            else tc_commit(&empty_bar[stage]);
           }
           __syncwarp();
         }
-        if (elect_one()) tc_commit(&tfull_bar[buf]);
+        if (elect_one()) {
+          if (PAIR) tc_commit2(&tfull_bar[buf]);
+          else tc_commit(&tfull_bar[buf]);
+        }
         __syncwarp();
       }
     }
@@ -682,11 +693,11 @@ static int launch_tma(const CUtensorMap& ta, const CUtensorMap& tb, const TmaCon
 }
 
 // cta_group::2 launch: 2-CTA clusters, one pair per two SMs
-template <int ST>
+template <int BN, int ST, int MS>
 static int launch_tma_pair(const CUtensorMap& ta, const CUtensorMap& tb, const TmaConvParams& p, cudaStream_t st) {
-  using S = TmaSmem<128, ST, 1>;
+  using S = TmaSmem<BN / 2, ST, MS>;
   static_assert(S::kTotal + 4096 + 4096 <= 227 * 1024 && S::kTotal > 114 * 1024, "shared memory budget / one CTA per SM");
-  auto kern = conv_tma_kernel<256, ST, 1, false, true>;
+  auto kern = conv_tma_kernel<BN, ST, MS, false, true>;
   static bool attr_done = false;
   if (!attr_done) {
     DEI2I_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal));
@@ -709,7 +720,7 @@ static int launch_tma_pair(const CUtensorMap& ta, const CUtensorMap& tb, const T
   cfg.numAttrs = 1;
   DEI2I_CUDA(cudaLaunchKernelEx(&cfg, kern, ta, tb, p));
   count_launch();
-  trace_kernel("conv_tma_pair<256,%d>", ST);
+  trace_kernel("conv_tma_pair<%d,%d,%d>", BN, ST, MS);
   return check_cuda(cudaGetLastError(), "conv_tma_kernel (pair) launch");
 }
 
@@ -752,7 +763,13 @@ int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, in
     if (int rc = encode_tmap_2d_bf16(&tb2, wmat, (uint64_t)K, (uint64_t)rows, (uint64_t)K * 2, 64, 128, 1)) return rc;
     p.m_tiles = (int)((p.M + 127) / 128);
     p.issue_mode = 0;
-    return launch_tma_pair<6>(ta, tb2, p, st);
+    return launch_tma_pair<256, 6, 1>(ta, tb2, p, st);
+  }
+  if (g_tune_tma_pair >= 2 && bn == 128 && rows % 128 == 0 && p.npar <= 1 && (p.M + 255) / 256 * p.n_tiles >= 4ll * num_sms()) {
+    CUtensorMap tb2;  // N = 128 tiles on pairs: two 128-pixel tiles per CTA, 64 of the 128 weight rows each
+    if (int rc = encode_tmap_2d_bf16(&tb2, wmat, (uint64_t)K, (uint64_t)rows, (uint64_t)K * 2, 64, 64, 1)) return rc;
+    p.m_tiles = (int)((p.M + 255) / 256);
+    return launch_tma_pair<128, 5, 2>(ta, tb2, p, st);
   }
   // narrow N: two 128-pixel A tiles share each B tile (halves the weight traffic per FLOP through L2 / shared memory) as long
   // as that still leaves every SM a couple of work tiles

@@ -292,7 +292,7 @@ def test_c2_discriminator_loss_full_batch_vs_fp32_torch():
     used = kl.variants()
     _report("c2/discriminator_loss_b32", losses=e, grads=worst, kernels=used)
     assert max(e.values()) < TOL_ACT, e
-    for want in ("conv_tma_pair<256,6>", "conv_tma<128,4,2>", "conv_tma<64,5,2>"):
+    for want in ("conv_tma_pair<256,6,1>", "conv_tma<128,4,2>", "conv_tma<64,5,2>"):
         assert want in used, (want, used)
 
 
@@ -377,16 +377,16 @@ def _nchw(y_nhwc, c):
 # Every row of profiles/r01m_conv_breakdown_head.json (the bench's per-geometry table at 256x256, batch 32); inputs carry their
 # reflect padding already ('valid' convolutions), exactly as the networks run them.
 C2_GEOMETRIES = {
-    "res_256_256_3x3_in66": (32, 256, 66, 66, 256, 3, 3, 1, "conv_tma_pair<256,6>", "conv_tma_pair<256,6>", "wgrad_tma<2,3>"),
-    "dec1_128_64_3x3_in258": (32, 128, 258, 258, 64, 3, 3, 1, "conv_tma<64,5,2>", "conv_tma<128,4,2>", "wgrad_tma<1,4>"),
-    "dec0_256_128_3x3_in130": (32, 256, 130, 130, 128, 3, 3, 1, "conv_tma<128,4,2>", "conv_tma_pair<256,6>", "wgrad_tma<1,4>"),
-    "enc0_64_128_4x4s2_in258": (32, 64, 258, 258, 128, 4, 4, 2, "conv_tma<128,4,2>", "conv_tma<64", "wgrad_tma<1,4>"),
-    "enc1_128_256_4x4s2_in130": (32, 128, 130, 130, 256, 4, 4, 2, "conv_tma_pair<256,6>", "conv_tma<128", "wgrad_tma<2,3>"),
+    "res_256_256_3x3_in66": (32, 256, 66, 66, 256, 3, 3, 1, "conv_tma_pair<256,6,1>", "conv_tma_pair<256,6,1>", "wgrad_tma<2,3>"),
+    "dec1_128_64_3x3_in258": (32, 128, 258, 258, 64, 3, 3, 1, "conv_tma<64,5,2>", "conv_tma_pair<128,5,2>", "wgrad_tma<1,4>"),
+    "dec0_256_128_3x3_in130": (32, 256, 130, 130, 128, 3, 3, 1, "conv_tma_pair<128,5,2>", "conv_tma_pair<256,6,1>", "wgrad_tma<1,4>"),
+    "enc0_64_128_4x4s2_in258": (32, 64, 258, 258, 128, 4, 4, 2, "conv_tma_pair<128,5,2>", "conv_tma<64", "wgrad_tma<1,4>"),
+    "enc1_128_256_4x4s2_in130": (32, 128, 130, 130, 256, 4, 4, 2, "conv_tma_pair<256,6,1>", "conv_tma<128", "wgrad_tma<2,3>"),
     "d1_64_128_4x4s2_in130": (32, 64, 130, 130, 128, 4, 4, 2, "conv_tma<128", "conv_tma<64", "wgrad_tma<1,4>"),
-    "d2_128_256_4x4s2_in66": (32, 128, 66, 66, 256, 4, 4, 2, "conv_tma_pair<256,6>", "conv_tma<128", "wgrad_tma<2,3>"),
+    "d2_128_256_4x4s2_in66": (32, 128, 66, 66, 256, 4, 4, 2, "conv_tma_pair<256,6,1>", "conv_tma<128", "wgrad_tma<2,3>"),
     "d3_256_512_4x4s2_in34": (32, 256, 34, 34, 512, 4, 4, 2, "conv_tma_pair<", "conv_tma", "wgrad_tma<2,3>"),
     "d4_512_1024_4x4s2_in18": (32, 512, 18, 18, 1024, 4, 4, 2, "conv_tma_pair<", "conv_tma", "wgrad_tma<2,3>"),
-    "d5_1024_2048_4x4s2_in10": (32, 1024, 10, 10, 2048, 4, 4, 2, "conv_tma_pair<256,6>", "conv_tma", "wgrad_tma<2,3>"),
+    "d5_1024_2048_4x4s2_in10": (32, 1024, 10, 10, 2048, 4, 4, 2, "conv_tma_pair<256,6,1>", "conv_tma", "wgrad_tma<2,3>"),
     "stem_rowpacked_64_64_7x1_in262x256": (32, 64, 262, 256, 64, 7, 1, 1, "conv_ring<7>", "conv_ring<7>", "wgrad_tma<1,4>"),
     "heads_64_4_3x3_in258": (32, 64, 258, 258, 4, 3, 3, 1, "conv_heads_fwd", "conv_c8_fwd", "wgrad_heads_mma"),
     "d0_3_64_4x4s2_in258": (32, 3, 258, 258, 64, 4, 4, 2, "conv_c8_fwd", None, "wgrad_c8"),

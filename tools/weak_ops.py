@@ -54,6 +54,9 @@ def main():
         ops.set_tuning("wgrad_swap", 0)
         conv_case(32, 128, 258, 258, 64, 3, 3, 1, "w")
         ops.set_tuning("wgrad_swap", 1)
+    if "n128" in names:
+        conv_case(32, 256, 130, 130, 128, 3, 3, 1, "fd")
+        conv_case(32, 64, 258, 258, 128, 4, 4, 2, "f")
     if "c256" in names:
         conv_case(32, 256, 66, 66, 256, 3, 3, 1, "fdw")
     if "stem" in names:

@@ -116,6 +116,10 @@ struct TmaWgradParams {
 };
 
 void wgrad_tma_plan(TmaWgradParams& p);
+bool wgrad_ring_applicable(const TmaWgradParams& p, int kh, int C, int W, int cout_ld);
+int wgrad_ring_splits(const TmaWgradParams& p);
+int run_wgrad_ring(const void* x, int N, int H, int W, int C, const void* dy, int cout_ld, TmaWgradParams& p, int kh, int upper, int upper_w,
+                   cudaStream_t st);
 int run_wgrad_tma(const void* x, int N, int H, int W, int C, const void* dy, int cout_ld, TmaWgradParams& p, int upper,
                   int upper_w, cudaStream_t st);
 

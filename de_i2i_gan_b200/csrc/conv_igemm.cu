@@ -974,6 +974,11 @@ extern "C" size_t dei2i_conv2d_wgrad_workspace(const dei2i_conv_geom* g, int Cin
       if (t.splits > splits) splits = t.splits;
     }
   }
+  if (wgrad_tma_applicable(g, 0)) {
+    TmaWgradParams t;
+    fill_wgrad_tma(g, t);
+    if (wgrad_ring_applicable(t, g->kh, g->Cin, g->W, g->Cout_ld) && wgrad_ring_splits(t) > splits) splits = wgrad_ring_splits(t);
+  }
   size_t bytes = (size_t)splits * g->Cout * Kf * sizeof(float) + 1024 * sizeof(float) + 256;
   if (wgrad_tma_applicable(g, 0) && wgrad_swap_applicable(g)) {
     TmaWgradParams t;
@@ -1022,6 +1027,15 @@ extern "C" int dei2i_conv2d_wgrad(const void* x, const void* dy, float* dw, int 
   p.g.M = (long long)g->N * Ho * Wo;
   float* partial = (float*)workspace;
   const int taps = g->kh * g->kw;
+  if (wgrad_tma_applicable(g, p.g.M)) {
+    TmaWgradParams t;
+    fill_wgrad_tma(g, t);
+    if (wgrad_ring_applicable(t, g->kh, g->Cin, g->W, g->Cout_ld)) {
+      t.partial = partial;
+      if (int rc = run_wgrad_ring(x, g->N, g->H, g->W, g->Cin, dy, g->Cout_ld, t, g->kh, g->pad - (g->kh - 1), g->pad - (g->kw - 1), st)) return rc;
+      return wgrad_second_pass(partial, t.splits, g, Cin_real, Kf, dw, beta, sn_w_orig, sn_u, sn_v, sn_inv_sigma, st);
+    }
+  }
   if (wgrad_tma_applicable(g, p.g.M) && wgrad_swap_applicable(g)) {
     TmaWgradParams t;
     fill_wgrad_swap(g, t);

@@ -986,4 +986,207 @@ int run_wgrad_tma(const void* x, int N, int H, int W, int C, const void* dy, int
   return launch_wgrad_tma<1, 4>(tdy, tx, p, st);
 }
 
+
+// ======================================================================================================================
+// Row-ring wgrad for kh x 1 filters over 64 input channels (the row-packed stem).  The generic kernel fetches one im2col box of x per
+// filter tap and 64-pixel block: 7 x 8 KB + 16 KB of dY per 64 pixels, and is bound by that fill (337 us).  Here a CTA walks down a
+// 64-pixel column block; the x tile of input row j is fetched once and serves as tap r of output row j - r.  The ring is MIRRORED
+// (row j lands in slots j % R and j % R + R) so that the kh tiles of any output row are contiguous in shared memory and can be fed
+// to the tensor core as ONE wide B operand (N = 256 for taps 0-3, N = 64 (kh - 4) for the rest) exactly like the generic kernel's
+// four-box stages: 16 + 16 KB per 64 pixels instead of 72.  One accumulator [128 co x kh * 64] per CTA for its whole pixel range.
+constexpr int kWRingR = 10;      // ring rows (kh in use + lead)
+constexpr int kWRingDy = 3;      // dY stages
+struct WRingSmem {
+  static constexpr int kX = 2 * kWRingR * 8192;  // mirrored ring of 64 pix x 64 ci tiles
+  static constexpr int kDy = kWRingDy * 16384;   // 64 pix x 128 co
+  static constexpr int kStageOut = kX + kDy;
+  static constexpr int kBarOff = kStageOut + 4 * 4096;
+  static constexpr int kTotal = kBarOff + (2 * kWRingR + 2 * kWRingDy + 1) * 8 + 16 + 1024;
+};
+
+__global__ void __launch_bounds__(kWgTmaThreads, 1)
+wgrad_ring_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ CUtensorMap tmap_x, const TmaWgradParams p,
+                  long long tiles_per_cta, long long total_tiles, int kh) {
+  using S = WRingSmem;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* xring = smem;
+  uint8_t* dys = smem + S::kX;
+  uint64_t* xfull = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
+  uint64_t* xempty = xfull + kWRingR;
+  uint64_t* dfull = xempty + kWRingR;
+  uint64_t* dempty = dfull + kWRingDy;
+  uint64_t* tfull_bar = dempty + kWRingDy;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tfull_bar + 1);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  constexpr uint32_t kTmemCols = 512;
+  const int CB = p.Wo / 64;
+  const long long t0 = (long long)blockIdx.x * tiles_per_cta;
+  const long long t1 = t0 + tiles_per_cta < total_tiles ? t0 + tiles_per_cta : total_tiles;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kWRingR; ++s) {
+      mbar_init(&xfull[s], 1);
+      mbar_init(&xempty[s], 1);
+    }
+    for (int s = 0; s < kWRingDy; ++s) {
+      mbar_init(&dfull[s], 1);
+      mbar_init(&dempty[s], 1);
+    }
+    mbar_init(tfull_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 4 && lane == 0) {
+    tma_prefetch_desc(&tmap_dy);
+    tma_prefetch_desc(&tmap_x);
+  }
+  if (warp == 5) tmem_alloc(tmem_ptr_smem, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 4) {
+    // =========================== TMA producer: per output row one dY tile, per input row one x tile (twice) ===========================
+    if (lane == 0 && t0 < t1) {
+      uint32_t L = 0, D = 0;  // x rows / dY tiles issued
+      for (long long t = t0; t < t1;) {
+        const long long strip = t / p.Ho;
+        const int ya = (int)(t - strip * p.Ho);
+        const int yb = (int)((long long)p.Ho < ya + (t1 - t) ? (long long)p.Ho : ya + (t1 - t));
+        const int img = (int)(strip / CB), cb = (int)(strip - (long long)img * CB);
+        // input rows ya .. yb + kh - 2 and output rows ya .. yb - 1, interleaved in the order the MMA warp consumes them
+        int jx = ya;
+        for (int y = ya; y < yb; ++y) {
+          for (; jx <= y + kh - 1; ++jx, ++L) {
+            const uint32_t slot = L % kWRingR;
+            mbar_wait(&xempty[slot], ((L / kWRingR) & 1u) ^ 1u);
+            mbar_arrive_expect_tx(&xfull[slot], 2 * 8192);
+            const int jb = jx < p.Ho - 1 ? jx : p.Ho - 1;
+            tma_load_im2col_4d(xring + slot * 8192, &tmap_x, &xfull[slot], 0, cb * 64 + p.lower_w, jb + p.lower, img, (uint16_t)0, (uint16_t)(jx - jb));
+            tma_load_im2col_4d(xring + (slot + kWRingR) * 8192, &tmap_x, &xfull[slot], 0, cb * 64 + p.lower_w, jb + p.lower, img, (uint16_t)0,
+                               (uint16_t)(jx - jb));
+          }
+          const uint32_t ds = D % kWRingDy;
+          mbar_wait(&dempty[ds], ((D / kWRingDy) & 1u) ^ 1u);
+          mbar_arrive_expect_tx(&dfull[ds], 16384);
+          const long long m0 = ((long long)img * p.Ho + y) * p.Wo + cb * 64;
+          tma_load_2d(dys + ds * 16384, &tmap_dy, &dfull[ds], 0, (int)m0);
+          tma_load_2d(dys + ds * 16384 + 8192, &tmap_dy, &dfull[ds], 64, (int)m0);
+          ++D;
+        }
+        t += yb - ya;
+      }
+    }
+  } else if (warp == 5) {
+    // =========================== MMA issuer ===========================
+    if (lane == 0 && t0 < t1) {
+      const int n1 = kh < 4 ? kh : 4, n2 = kh - n1;  // taps per MMA group
+      const uint32_t idesc1 = make_idesc_bf16(128, n1 * 64, 1, 1);
+      const uint32_t idesc2 = make_idesc_bf16(128, (n2 > 0 ? n2 : 1) * 64, 1, 1);
+      uint32_t L0 = 0, D = 0;
+      bool first = true;
+      for (long long t = t0; t < t1;) {
+        const long long strip = t / p.Ho;
+        const int ya = (int)(t - strip * p.Ho);
+        const int nrows = (int)((long long)p.Ho - ya < t1 - t ? (long long)p.Ho - ya : t1 - t);
+        for (int y = 0; y < nrows; ++y, ++D) {
+          for (int r = (y == 0 ? 0 : kh - 1); r < kh; ++r) {
+            const uint32_t L = L0 + y + r;
+            mbar_wait(&xfull[L % kWRingR], (L / kWRingR) & 1u);
+          }
+          const uint32_t ds = D % kWRingDy;
+          mbar_wait(&dfull[ds], (D / kWRingDy) & 1u);
+          tc_fence_after();
+          const uint32_t slot = (L0 + y) % kWRingR;  // tap r sits at slot + r (mirrored ring: no wrap)
+          const uint64_t a_desc = make_smem_desc(smem_u32(dys + ds * 16384), 8192, 1024, 2);
+          const uint64_t b1 = make_smem_desc(smem_u32(xring + slot * 8192), 8192, 1024, 2);
+          const uint64_t b2 = make_smem_desc(smem_u32(xring + (slot + 4) * 8192), 8192, 1024, 2);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {  // 16 pixels per MMA
+            tc_mma_bf16(tmem_base, a_desc + (uint64_t)(128 * k), b1 + (uint64_t)(128 * k), idesc1, !(first && k == 0));
+            if (n2 > 0) tc_mma_bf16(tmem_base + 256, a_desc + (uint64_t)(128 * k), b2 + (uint64_t)(128 * k), idesc2, !(first && k == 0));
+          }
+          first = false;
+          tc_commit(&dempty[ds]);
+          tc_commit(&xempty[slot]);  // input row y is not needed by later output rows
+          if (y == nrows - 1)
+            for (int r = 1; r < kh; ++r) tc_commit(&xempty[(L0 + y + r) % kWRingR]);
+        }
+        L0 += nrows + kh - 1;
+        t += nrows;
+      }
+      tc_commit(tfull_bar);
+    }
+  } else if (t0 < t1) {
+    // =========================== epilogue: fp32 partial [split = CTA][co][kh * 64] ===========================
+    mbar_wait(tfull_bar, 0);
+    tc_fence_after();
+    uint8_t* stage = smem + S::kStageOut + warp * 4096;
+    const int sub_r = lane >> 3, sub_j = lane & 7;
+    const int co_w = warp * 32;
+    if (co_w < p.cout) {
+#pragma unroll 1
+      for (int c = 0; c < kh * 64; c += 32) {
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c, v);
+        tc_wait_ld();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(stage + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        __syncwarp();
+#pragma unroll
+        for (int itr = 0; itr < 8; ++itr) {
+          const int r = itr * 4 + sub_r;
+          const uint4 val = *reinterpret_cast<const uint4*>(stage + r * 128 + ((sub_j ^ (r & 7)) << 4));
+          if (co_w + r < p.cout)
+            *reinterpret_cast<uint4*>(p.partial + ((long long)blockIdx.x * p.cout + co_w + r) * p.Kf + c + sub_j * 4) = val;
+        }
+        __syncwarp();
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 5) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+extern int g_tune_wgrad_ring;
+bool wgrad_ring_applicable(const TmaWgradParams& p, int kh, int C, int W, int cout_ld) {
+  return g_tune_wgrad_ring != 0 && p.kw == 1 && kh >= 2 && kh < kWRingR && C == 64 && cout_ld == 64 && p.cout <= 64 && p.stride == 1 &&
+         p.lower_w == 0 && p.Wo == W && p.Wo % 64 == 0 && p.Ho >= kh && p.Kf == kh * 64 &&
+         p.M == (p.M / ((long long)p.Ho * p.Wo)) * p.Ho * p.Wo;
+}
+int wgrad_ring_splits(const TmaWgradParams& p) {
+  const long long total = (p.M / ((long long)p.Ho * p.Wo)) * (p.Wo / 64) * p.Ho;
+  const int grid = total < num_sms() ? (int)total : num_sms();
+  const long long per = (total + grid - 1) / grid;
+  return (int)((total + per - 1) / per);
+}
+int run_wgrad_ring(const void* x, int N, int H, int W, int C, const void* dy, int cout_ld, TmaWgradParams& p, int kh, int upper, int upper_w,
+                   cudaStream_t st) {
+  CUtensorMap tdy, tx;
+  if (int rc = encode_tmap_2d_bf16(&tdy, dy, (uint64_t)cout_ld, (uint64_t)p.M, (uint64_t)cout_ld * 2, 64, 64, 1)) return rc;
+  if (int rc = encode_tmap_im2col_bf16(&tx, x, (uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N, p.lower_w, upper_w, p.lower, upper, 1u, 64, 64))
+    return rc;
+  static_assert(WRingSmem::kTotal <= 227 * 1024 && WRingSmem::kTotal > 114 * 1024, "shared memory budget / one CTA per SM");
+  static bool attr_done = false;
+  if (!attr_done) {
+    DEI2I_CUDA(cudaFuncSetAttribute(wgrad_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WRingSmem::kTotal));
+    attr_done = true;
+  }
+  const long long total = (p.M / ((long long)p.Ho * p.Wo)) * (p.Wo / 64) * p.Ho;
+  const int grid = wgrad_ring_splits(p);
+  const long long per = (total + (total < num_sms() ? total : num_sms()) - 1) / (total < num_sms() ? total : num_sms());
+  p.splits = grid;
+  wgrad_ring_kernel<<<grid, kWgTmaThreads, WRingSmem::kTotal, st>>>(tdy, tx, p, per, total, kh);
+  count_launch();
+  trace_kernel("wgrad_ring<%d>", kh);
+  return check_cuda(cudaGetLastError(), "wgrad_ring_kernel launch");
+}
+
 }  // namespace dei2i

@@ -885,8 +885,26 @@ def test_conv_ring_khx1_forward_and_dgrad(n, ho, w, kh):
         torch.cuda.synchronize()
         assert ("conv_ring" in k_f) == bool(ring) and ("conv_ring" in k_d) == bool(ring), (k_f, k_d)
         outs[ring] = (from_dev(y, 64), from_dev(dx, 64))
+    # weight gradient on the row-ring wgrad kernel (mirrored ring, one accumulator per CTA) vs torch and vs the generic kernel
+    wr = wt.clone().requires_grad_(True)
+    (dw_ref,) = torch.autograd.grad(F.conv2d(x, wr), wr, dy)
+    dws = {}
+    for ring in (1, 0):
+        ops.set_tuning("wgrad_ring", ring)
+        try:
+            dw = torch.full(wt.shape, 3.0, device="cuda")
+            ops.conv2d_wgrad(to_dev(x), to_dev(dy), dw, spec)
+            k_w = ops.last_kernel()
+            ops.conv2d_wgrad(to_dev(x), to_dev(dy), dw, spec, accumulate=True)
+        finally:
+            ops.set_tuning("wgrad_ring", 1)
+        torch.cuda.synchronize()
+        assert ("wgrad_ring" in k_w) == bool(ring), k_w
+        dws[ring] = dw.cpu()
+    e_w = rel_err(dws[1], 2 * dw_ref)
+    assert e_w < TOL_F32 and rel_err(dws[1], dws[0]) < TOL_F32, (e_w, rel_err(dws[1], dws[0]))
     e_f, e_d = rel_err(outs[1][0], yr.detach()), rel_err(outs[1][1], dx_ref)
-    _report(f"conv_ring/{n}x{ho}x{w}k{kh}", fwd=e_f, dgrad=e_d, vs_generic_fwd=rel_err(outs[1][0], outs[0][0]), vs_generic_dgrad=rel_err(outs[1][1], outs[0][1]))
+    _report(f"conv_ring/{n}x{ho}x{w}k{kh}", fwd=e_f, dgrad=e_d, wgrad=e_w, vs_generic_fwd=rel_err(outs[1][0], outs[0][0]), vs_generic_dgrad=rel_err(outs[1][1], outs[0][1]))
     assert e_f < TOL_BF16 and e_d < TOL_BF16, (e_f, e_d)
     assert torch.equal(outs[1][0], outs[0][0]) or rel_err(outs[1][0], outs[0][0]) < 4e-3
     assert torch.equal(outs[1][1], outs[0][1]) or rel_err(outs[1][1], outs[0][1]) < 4e-3

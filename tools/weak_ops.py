@@ -61,9 +61,9 @@ def main():
         conv_case(32, 256, 66, 66, 256, 3, 3, 1, "fdw")
     if "stem" in names:
         conv_case(32, 64, 262, 256, 64, 7, 1, 1, "fdw")
-        ops.set_tuning("conv_ring", 0)
-        conv_case(32, 64, 262, 256, 64, 7, 1, 1, "fd")
-        ops.set_tuning("conv_ring", 1)
+        ops.set_tuning("wgrad_ring", 0)
+        conv_case(32, 64, 262, 256, 64, 7, 1, 1, "w")
+        ops.set_tuning("wgrad_ring", 1)
     if "d5" in names:
         conv_case(32, 1024, 10, 10, 2048, 4, 4, 2, "fdw")
         conv_case(32, 512, 18, 18, 1024, 4, 4, 2, "fdw")

@@ -108,6 +108,7 @@ struct TmaWgradParams {
   int cin_blocks;    // Cin / 64
   int num_boxes;     // taps * cin_blocks  (64-wide K slices of the packed weight layout)
   int k_tiles;       // ceil(num_boxes / 4)
+  int pair;            // 1: planned for wgrad_pair_kernel (CTA pairs, [256 co x boxes_per_tile <= 8 boxes] per pair)
   int boxes_per_tile;  // ceil(num_boxes / k_tiles) <= 4: 9 boxes run as 3 + 3 + 3, not 4 + 4 + 1 (every k tile gets the same number of CTAs)
   int co_groups;     // ceil(Cout / (128 * CO_T))
   int splits, pb_per_split, num_pb;  // 64-pixel blocks

@@ -960,8 +960,217 @@ static int launch_wgrad_tma(const CUtensorMap& tdy, const CUtensorMap& tx, const
   return check_cuda(cudaGetLastError(), "wgrad_tma_kernel launch");
 }
 
+
+// ======================================================================================================================
+// CTA-pair wgrad (Cout >= 256): the single-CTA kernel keeps a [256 co x 256 k] tile per CTA and needs 64 KB of operands per 1024 MMA
+// cycles - more than the L2 -> shared-memory path delivers (it runs at 77 % of what the forward reaches).  A pair keeps
+// [256 co x 512 k]: CTA r loads the dY tile of ITS 128 output channels (16 KB) and half of the up-to-eight x boxes (32 KB) per 64
+// pixels, the leader issues two M = 256 (cta_group::2) MMAs per 16 pixels - 48 KB per 1024 cycles per CTA.  Accumulators: 128 lanes
+// x 512 columns in each CTA (its co rows x all k columns of the tile).
+// MEASURED (same box): 256 -> 256 3x3 137.0 vs 135.4 us, 512 -> 1024 58.7 vs 60.2 us - no gain: the first pass of these layers already runs
+// at the power-limited tensor rate (~105 of the 135 us; the rest is the second pass over the split partials).  Bit-exact, kept behind
+// dei2i_set_tuning("wgrad_pair", 1), off by default.
+constexpr int kWPairStages = 4;
+struct WPairSmem {
+  static constexpr int kATile = 16384;     // 64 pix x 128 co (this CTA's half of the 256)
+  static constexpr int kBTile = 4 * 8192;  // this CTA's half of up to 8 boxes
+  static constexpr int kStage = kATile + kBTile;
+  static constexpr int kStageOut = kWPairStages * kStage;
+  static constexpr int kBarOff = kStageOut + 4 * 4096;
+  static constexpr int kTotal = kBarOff + (2 * kWPairStages + 1) * 8 + 16 + 1024;
+};
+
+__global__ void __launch_bounds__(kWgTmaThreads, 1)
+wgrad_pair_kernel(const __grid_constant__ CUtensorMap tmap_dy, const __grid_constant__ CUtensorMap tmap_x, const TmaWgradParams p) {
+  using S = WPairSmem;
+  constexpr int STAGES = kWPairStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tfull_bar = empty_bar + STAGES;
+  uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tfull_bar + 1);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  constexpr uint32_t kTmemCols = 512;
+  const uint32_t rank = cluster_ctarank();
+
+  // work tile of the pair
+  int t = blockIdx.x >> 1;
+  const int split = t % p.splits;
+  t /= p.splits;
+  const int k_tile = t % p.k_tiles;
+  const int co_group = t / p.k_tiles;
+  const int box0 = k_tile * p.boxes_per_tile;
+  const int rest = p.num_boxes - box0;
+  const int nb = rest < p.boxes_per_tile ? rest : p.boxes_per_tile;  // even, <= 8
+  const int n1 = nb < 4 ? nb : 4, n2 = nb - n1;                       // boxes of the two MMAs (N = 64 n1, 64 n2)
+  const int h1 = n1 / 2, h2 = n2 / 2;                                 // ... of which this CTA holds half
+  const int co0 = co_group * 256 + (int)rank * 128;
+  const int pb0 = split * p.pb_per_split;
+  const int pb1 = p.num_pb < pb0 + p.pb_per_split ? p.num_pb : pb0 + p.pb_per_split;
+  const int nsteps = pb1 - pb0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(tfull_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 4 && lane == 0) {
+    tma_prefetch_desc(&tmap_dy);
+    tma_prefetch_desc(&tmap_x);
+  }
+  if (warp == 5) tmem_alloc2(tmem_ptr_smem, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_ptr_smem;
+
+  if (warp == 4) {
+    if (lane == 0 && nsteps > 0) {
+      const int HoWo = p.Ho * p.Wo;
+      int b_cb[4], b_s[4], b_r[4];  // this CTA's boxes: h1 of MMA 1, then h2 of MMA 2
+      for (int g = 0; g < 4; ++g) {
+        int bx = box0;
+        if (g < h1) bx = box0 + (int)rank * h1 + g;
+        else if (g < h1 + h2) bx = box0 + n1 + (int)rank * h2 + (g - h1);
+        const int tap = bx / p.cin_blocks;
+        b_cb[g] = bx - tap * p.cin_blocks;
+        b_r[g] = tap / p.kw;
+        b_s[g] = tap - b_r[g] * p.kw;
+      }
+      const uint32_t stage_bytes = 2u * (uint32_t)(S::kATile + (h1 + h2) * 8192);  // both CTAs credit the leader's barrier
+      for (int it = 0; it < nsteps; ++it) {
+        const uint32_t stage = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1u;
+        mbar_wait(&empty_bar[stage], ph ^ 1u);
+        uint8_t* a_dst = smem + stage * S::kStage;
+        uint8_t* b_dst = a_dst + S::kATile;
+        if (rank == 0) mbar_arrive_expect_tx(&full_bar[stage], stage_bytes);
+        const long long m0 = (long long)(pb0 + it) * 64;
+        tma2_load_2d(a_dst, &tmap_dy, &full_bar[stage], co0, (int)m0);
+        tma2_load_2d(a_dst + 8192, &tmap_dy, &full_bar[stage], co0 + 64, (int)m0);
+        const int img = (int)(m0 / HoWo);
+        const int rem = (int)(m0 - (long long)img * HoWo);
+        const int pr = rem / p.Wo;
+        const int qc = rem - pr * p.Wo;
+        const int cw = qc * p.stride + p.lower_w, ch = pr * p.stride + p.lower;
+        for (int g = 0; g < h1 + h2; ++g)
+          tma2_load_im2col_4d(b_dst + g * 8192, &tmap_x, &full_bar[stage], b_cb[g] * 64, cw, ch, img, (uint16_t)b_s[g], (uint16_t)b_r[g]);
+      }
+    }
+  } else if (warp == 5) {
+    if (lane == 0 && nsteps > 0 && rank == 0) {
+      const uint32_t idesc1 = make_idesc_bf16(256, n1 * 64, 1, 1);
+      const uint32_t idesc2 = make_idesc_bf16(256, (n2 > 0 ? n2 : 2) * 64, 1, 1);
+      for (int it = 0; it < nsteps; ++it) {
+        const uint32_t stage = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1u;
+        mbar_wait(&full_bar[stage], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + stage * S::kStage);
+        const uint32_t b_addr = a_addr + S::kATile;
+        const uint64_t a_desc = make_smem_desc(a_addr, 8192, 1024, 2);
+        const uint64_t b1 = make_smem_desc(b_addr, 8192, 1024, 2);
+        const uint64_t b2 = make_smem_desc(b_addr + h1 * 8192, 8192, 1024, 2);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          tc_mma2_bf16(tmem_base, a_desc + (uint64_t)(128 * k), b1 + (uint64_t)(128 * k), idesc1, (it | k) != 0);
+          if (n2 > 0) tc_mma2_bf16(tmem_base + 256, a_desc + (uint64_t)(128 * k), b2 + (uint64_t)(128 * k), idesc2, (it | k) != 0);
+        }
+        tc_commit2(&empty_bar[stage]);
+      }
+      tc_commit2(tfull_bar);
+    }
+  } else if (nsteps > 0) {
+    mbar_wait(tfull_bar, 0);
+    tc_fence_after();
+    uint8_t* stage = smem + S::kStageOut + warp * 4096;
+    const int sub_r = lane >> 3, sub_j = lane & 7;
+    const int k0 = box0 * 64;
+    const int co_w = co0 + warp * 32;
+    if (co_w < p.cout) {
+#pragma unroll 1
+      for (int c = 0; c < nb * 64; c += 32) {  // n1 = 4 whenever a second MMA exists: TMEM column == c
+        uint32_t v[32];
+        tmem_ld_32x32b_x32(tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c, v);
+        tc_wait_ld();
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          *reinterpret_cast<uint4*>(stage + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        __syncwarp();
+#pragma unroll
+        for (int itr = 0; itr < 8; ++itr) {
+          const int r = itr * 4 + sub_r;
+          const uint4 val = *reinterpret_cast<const uint4*>(stage + r * 128 + ((sub_j ^ (r & 7)) << 4));
+          if (co_w + r < p.cout)
+            *reinterpret_cast<uint4*>(p.partial + ((long long)split * p.cout + co_w + r) * p.Kf + k0 + c + sub_j * 4) = val;
+        }
+        __syncwarp();
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();
+  if (warp == 5) {
+    tc_fence_after();
+    tmem_dealloc2(tmem_base, kTmemCols);
+  }
+}
+
+extern int g_tune_wgrad_pair;
+static bool wgrad_pair_ok(const TmaWgradParams& p) {
+  return g_tune_wgrad_pair != 0 && p.cout >= 256 && p.cout % 128 == 0 && p.num_boxes % 2 == 0 && p.num_boxes >= 8;
+}
+static int launch_wgrad_pair(const CUtensorMap& tdy, const CUtensorMap& tx, const TmaWgradParams& p, cudaStream_t st) {
+  static_assert(WPairSmem::kTotal <= 227 * 1024 && WPairSmem::kTotal > 114 * 1024, "shared memory budget / one CTA per SM");
+  static bool attr_done = false;
+  if (!attr_done) {
+    DEI2I_CUDA(cudaFuncSetAttribute(wgrad_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, WPairSmem::kTotal));
+    attr_done = true;
+  }
+  cudaLaunchConfig_t cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.gridDim = dim3(2 * p.co_groups * p.k_tiles * p.splits, 1, 1);
+  cfg.blockDim = dim3(kWgTmaThreads, 1, 1);
+  cfg.dynamicSmemBytes = WPairSmem::kTotal;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = 2;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  DEI2I_CUDA(cudaLaunchKernelEx(&cfg, wgrad_pair_kernel, tdy, tx, p));
+  count_launch();
+  trace_kernel("wgrad_pair<%d>", p.boxes_per_tile);
+  return check_cuda(cudaGetLastError(), "wgrad_pair_kernel launch");
+}
+
 // plan shared with the workspace-size query: fills co_groups / k_tiles / splits / pb_per_split / num_pb
 void wgrad_tma_plan(TmaWgradParams& p) {
+  p.num_pb = (int)((p.M + 63) / 64);
+  p.pair = 0;
+  if (wgrad_pair_ok(p)) {  // CTA pairs: [256 co x up to 8 boxes] per pair
+    p.co_groups = (p.cout + 255) / 256;
+    p.k_tiles = (p.num_boxes + 7) / 8;
+    p.boxes_per_tile = ((p.num_boxes + p.k_tiles - 1) / p.k_tiles + 1) & ~1;
+    p.k_tiles = (p.num_boxes + p.boxes_per_tile - 1) / p.boxes_per_tile;
+    const int tiles = p.co_groups * p.k_tiles;
+    int splits = (num_sms() / 2) / tiles;
+    if (splits < 1) splits = 1;
+    while (splits > 1 && p.num_pb / splits < 4) --splits;
+    p.pb_per_split = (p.num_pb + splits - 1) / splits;
+    p.splits = (p.num_pb + p.pb_per_split - 1) / p.pb_per_split;
+    p.pair = 1;
+    return;
+  }
   const int co_t = p.cout > 128 ? 2 : 1;
   p.co_groups = (p.cout + 128 * co_t - 1) / (128 * co_t);
   p.k_tiles = (p.num_boxes + 3) / 4;
@@ -982,6 +1191,7 @@ int run_wgrad_tma(const void* x, int N, int H, int W, int C, const void* dy, int
   if (int rc = encode_tmap_2d_bf16(&tdy, dy, (uint64_t)cout_ld, (uint64_t)p.M, (uint64_t)cout_ld * 2, 64, 64, 1)) return rc;
   if (int rc = encode_tmap_im2col_bf16(&tx, x, (uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N, p.lower_w, upper_w, p.lower, upper, (uint32_t)p.stride, 64, 64))
     return rc;
+  if (p.pair) return launch_wgrad_pair(tdy, tx, p, st);
   if (p.cout > 128) return launch_wgrad_tma<2, 3>(tdy, tx, p, st);
   return launch_wgrad_tma<1, 4>(tdy, tx, p, st);
 }

@@ -478,12 +478,13 @@ wgrad_reduce_kernel(const float* __restrict__ partial, int splits, int Cout, int
   }
 }
 
+static __device__ unsigned int g_dot_ticket = 0;  // blocks of the wgrad_dot_kernel in flight that have finished (see there)
 // <dW, W/sigma> over the real elements (spectral-norm backward); deterministic: fixed tile -> block assignment, fixed order
 template <bool VEC>
 __global__ void __launch_bounds__(256)
 wgrad_dot_kernel(float* __restrict__ partial, int splits, int Cout, int Kf, int Cin, int Cin_real, int taps,
                  const float* __restrict__ w_orig, const float* __restrict__ inv_sigma, float* __restrict__ blocksums, int sh,
-                 int store_sum) {
+                 int store_sum, float* __restrict__ total_out) {
   extern __shared__ float4 T4[];
   float* T = reinterpret_cast<float*>(T4);
   const int ct = 1 << sh, pitch = ct + 4;
@@ -563,18 +564,29 @@ wgrad_dot_kernel(float* __restrict__ partial, int splits, int Cout, int Kf, int 
     t = warp_sum(t);
     if (threadIdx.x == 0) blocksums[blockIdx.x] = t * inv_sigma[0];
   }
-}
-__global__ void sum_blocks_kernel(const float* __restrict__ in, int n, float* __restrict__ out) {
-  float acc = 0.f;
-  for (int i = threadIdx.x; i < n; i += blockDim.x) acc += in[i];
-  __shared__ float sh[32];
-  acc = warp_sum(acc);
-  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+  if (total_out == nullptr) return;
+  // the block that finishes last adds the block sums up in a fixed order (thread-strided partial sums, warp shuffles, one final warp - what the separate
+  // one-block kernel did before, bit for bit), which saves that launch; the ticket lives in a file-scope counter that the last block resets (one wgrad in flight per device at a time:
+  // they all run on the trainer's stream)
+  __shared__ bool last;
+  __threadfence();
+  if (threadIdx.x == 0) last = atomicAdd(&g_dot_ticket, 1u) == gridDim.x - 1;
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  float a2 = 0.f;
+  for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) a2 += __ldcg(blocksums + i);
+  a2 = warp_sum(a2);
+  __syncthreads();
+  if ((threadIdx.x & 31) == 0) wsum[threadIdx.x >> 5] = a2;
   __syncthreads();
   if (threadIdx.x < 32) {
-    float t = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.f;
+    float t = threadIdx.x < (blockDim.x >> 5) ? wsum[threadIdx.x] : 0.f;
     t = warp_sum(t);
-    if (threadIdx.x == 0) out[0] = t;
+    if (threadIdx.x == 0) {
+      total_out[0] = t;
+      g_dot_ticket = 0;
+    }
   }
 }
 
@@ -670,13 +682,12 @@ int wgrad_second_pass(float* partial, int splits, const dei2i_conv_geom* g, int 
     const int nb = red_tiles < 1023 ? red_tiles : 1023;
     if (red_vec)
       wgrad_dot_kernel<true><<<nb, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, sn_w_orig, sn_inv_sigma,
-                                                        dot + 1, red_sh, 1);
+                                                        dot + 1, red_sh, 1, dot);
     else
       wgrad_dot_kernel<false><<<nb, 256, red_smem, st>>>(partial, splits, g->Cout, Kf, g->Cin, Cin_real, taps, sn_w_orig, sn_inv_sigma,
-                                                         dot + 1, red_sh, 1);
+                                                         dot + 1, red_sh, 1, dot);
     red_splits = 1;  // the dot pass left the split sums in split 0
-    sum_blocks_kernel<<<1, 256, 0, st>>>(dot + 1, nb, dot);
-    count_launch(2);
+    count_launch(1);
     DEI2I_CUDA(cudaGetLastError());
   }
   if (red_vec)

@@ -123,6 +123,85 @@ __global__ void __launch_bounds__(256) pack_multi_kernel(const __grid_constant__
   }
 }
 
+// Tiled variant (filters of <= 16 taps): a block stages a [32 co x 32 ci x taps] tile of the FP32 weight in shared memory with coalesced
+// reads (the element-wise kernel above reads with a stride of `taps` floats: every 32-byte sector is fetched once per tap) and writes
+// both packed layouts from it with 64-byte runs.  Same values, same zero padding, bit for bit.
+constexpr int kPackTile = 32;
+struct PackBatchT {
+  const float* w[kPackBatch];
+  const float* w2[kPackBatch];
+  __nv_bfloat16* fwd[kPackBatch];
+  __nv_bfloat16* dg[kPackBatch];
+  int rows_w[kPackBatch], Cout[kPackBatch], Cin_real[kPackBatch], taps[kPackBatch], Cin[kPackBatch], Cout_ld[kPackBatch];
+  int Kf[kPackBatch], Kd[kPackBatch], ci_tiles[kPackBatch];
+  int blk[kPackBatch + 1];
+  int count;
+};
+__global__ void __launch_bounds__(256) pack_multi_tiled_kernel(const __grid_constant__ PackBatchT t) {
+  extern __shared__ __nv_bfloat16 pk_s[];
+  int j = 0;
+  while (j + 1 < t.count && (int)blockIdx.x >= t.blk[j + 1]) ++j;
+  const int b = blockIdx.x - t.blk[j];
+  const int Cout = t.Cout[j], Cin_real = t.Cin_real[j], taps = t.taps[j], Cin = t.Cin[j], Cout_ld = t.Cout_ld[j], rows_w = t.rows_w[j];
+  const int Kf = t.Kf[j], Kd = t.Kd[j];
+  const int cot = b / t.ci_tiles[j], cit = b - cot * t.ci_tiles[j];
+  const int co0 = cot * kPackTile, ci0 = cit * kPackTile;
+  const int TP = taps | 1;                      // odd pitch per input channel (halfwords)
+  const int RP = (kPackTile * TP + 2) | 1;      // odd row pitch
+  const int run = kPackTile * taps;             // contiguous floats of one output-channel row inside the tile
+  int nreal = (Cin_real - ci0) * taps;          // ... of which exist
+  nreal = nreal < 0 ? 0 : (nreal > run ? run : nreal);
+  for (int idx = threadIdx.x; idx < kPackTile * run; idx += 256) {
+    const int co_l = idx / run, e = idx - co_l * run;
+    const int co = co0 + co_l;
+    float v = 0.f;
+    if (co < Cout && e < nreal) {
+      const float* src = co < rows_w ? t.w[j] + (long long)co * Cin_real * taps : t.w2[j] + (long long)(co - rows_w) * Cin_real * taps;
+      v = __ldg(src + (long long)ci0 * taps + e);
+    }
+    const int ci_l = e / taps, tap = e - ci_l * taps;
+    pk_s[co_l * RP + ci_l * TP + tap] = __float2bfloat16(v);
+  }
+  __syncthreads();
+  __nv_bfloat16* __restrict__ of = t.fwd[j];
+  const unsigned short* pk_u = reinterpret_cast<const unsigned short*>(pk_s);
+  for (int idx = threadIdx.x; idx < kPackTile * run / 2; idx += 256) {  // forward layout: (co, tap, ci), ci fastest; two channels per thread
+    const int ci_l = (idx & (kPackTile / 2 - 1)) * 2;
+    const int r = idx >> 4;
+    const int co_l = r / taps, tap = r - co_l * taps;
+    const int co = co0 + co_l, ci = ci0 + ci_l;
+    if (co < Cout && ci < Cin)  // Cin % 8 == 0: both channels of the pair are in range; the address is 4-byte aligned
+      *reinterpret_cast<uint32_t*>(of + (long long)co * Kf + tap * Cin + ci) =
+          (uint32_t)pk_u[co_l * RP + ci_l * TP + tap] | ((uint32_t)pk_u[co_l * RP + (ci_l + 1) * TP + tap] << 16);
+  }
+  if (cit == 0) {  // zero tail of the K pitch
+    const int tail = Kf - taps * Cin;
+    for (int idx = threadIdx.x; idx < kPackTile * tail; idx += 256) {
+      const int co = co0 + idx / tail;
+      if (co < Cout) of[(long long)co * Kf + taps * Cin + idx % tail] = __float2bfloat16(0.f);
+    }
+  }
+  __nv_bfloat16* __restrict__ od = t.dg[j];
+  if (od != nullptr) {
+    for (int idx = threadIdx.x; idx < kPackTile * run / 2; idx += 256) {  // dgrad layout: (ci, tap, co), co fastest; two channels per thread
+      const int co_l = (idx & (kPackTile / 2 - 1)) * 2;
+      const int r = idx >> 4;
+      const int ci_l = r / taps, tap = r - ci_l * taps;
+      const int co = co0 + co_l, ci = ci0 + ci_l;
+      if (ci < Cin && co < Cout_ld)  // zero beyond Cout / Cin_real; Cout_ld % 8 == 0
+        *reinterpret_cast<uint32_t*>(od + (long long)ci * Kd + tap * Cout_ld + co) =
+            (uint32_t)pk_u[co_l * RP + ci_l * TP + tap] | ((uint32_t)pk_u[(co_l + 1) * RP + ci_l * TP + tap] << 16);
+    }
+    if (cot == 0) {
+      const int tail = Kd - taps * Cout_ld;
+      for (int idx = threadIdx.x; idx < kPackTile * tail; idx += 256) {
+        const int ci = ci0 + idx / tail;
+        if (ci < Cin) od[(long long)ci * Kd + taps * Cout_ld + idx % tail] = __float2bfloat16(0.f);
+      }
+    }
+  }
+}
+
 DEVINL int reflect_idx(int i, int n) { return i < 0 ? -i : (i >= n ? 2 * n - 2 - i : i); }
 
 // out / dout of a consumer-padded SPADE output ([N, H+2pad, W+2pad, C]): the activation at (h, w) sits at (h+pad, w+pad); its
@@ -1943,6 +2022,37 @@ extern "C" int dei2i_pack_weight(const float* w, const float* inv_sigma, int Cou
 extern "C" int dei2i_pack_weight_multi(const dei2i_pack_item* items, int count, dei2i_stream stream) {
   DEI2I_REQUIRE(items && count >= 0, "pack_weight_multi: bad arguments");
   for (int base = 0; base < count; base += kPackBatch) {
+    // tiled kernel when every filter of the batch has <= 16 taps (everything but raw 7 x 7 stems)
+    const int cnt = count - base < kPackBatch ? count - base : kPackBatch;
+    bool tiled = cnt > 0;
+    for (int j = 0; j < cnt; ++j) tiled = tiled && items[base + j].kh * items[base + j].kw <= 16;
+    if (tiled) {
+      PackBatchT t;
+      memset(&t, 0, sizeof(t));
+      t.count = cnt;
+      int max_taps = 1;
+      for (int j = 0; j < cnt; ++j) {
+        const dei2i_pack_item& it = items[base + j];
+        DEI2I_REQUIRE(it.w && it.w_fwd && it.Cout > 0 && it.Cin_real > 0 && it.kh > 0 && it.kw > 0, "pack_weight_multi: bad item %d", base + j);
+        DEI2I_REQUIRE(it.Cin % 8 == 0 && it.Cin >= it.Cin_real && it.Cout_ld % 8 == 0 && it.Cout_ld >= it.Cout,
+                      "pack_weight_multi: bad channel padding in item %d", base + j);
+        DEI2I_REQUIRE(it.w2 ? (it.rows_w > 0 && it.rows_w < it.Cout) : it.rows_w == it.Cout, "pack_weight_multi: bad rows_w in item %d", base + j);
+        const int taps = it.kh * it.kw;
+        max_taps = taps > max_taps ? taps : max_taps;
+        t.w[j] = it.w; t.w2[j] = it.w2; t.fwd[j] = (__nv_bfloat16*)it.w_fwd; t.dg[j] = (__nv_bfloat16*)it.w_dgrad;
+        t.rows_w[j] = it.rows_w; t.Cout[j] = it.Cout; t.Cin_real[j] = it.Cin_real; t.taps[j] = taps; t.Cin[j] = it.Cin; t.Cout_ld[j] = it.Cout_ld;
+        t.Kf[j] = (taps * it.Cin + 63) / 64 * 64;
+        t.Kd[j] = (taps * it.Cout_ld + 63) / 64 * 64;
+        t.ci_tiles[j] = (it.Cin + kPackTile - 1) / kPackTile;
+        const long long tiles = (long long)((it.Cout_ld + kPackTile - 1) / kPackTile) * t.ci_tiles[j];
+        DEI2I_REQUIRE(t.blk[j] + tiles < (1ll << 30), "pack_weight_multi: too many blocks");
+        t.blk[j + 1] = t.blk[j] + (int)tiles;
+      }
+      const int TP = max_taps | 1, RP = (kPackTile * TP + 2) | 1;
+      pack_multi_tiled_kernel<<<t.blk[cnt], 256, (size_t)kPackTile * RP * sizeof(__nv_bfloat16), ST>>>(t);
+      if (int rc = LAUNCH_OK("pack_multi_tiled_kernel")) return rc;
+      continue;
+    }
     PackBatch t;
     memset(&t, 0, sizeof(t));
     t.count = count - base < kPackBatch ? count - base : kPackBatch;

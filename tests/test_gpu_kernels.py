@@ -854,6 +854,17 @@ def test_pack_weight_multi_matches_per_weight_packing():
         assert gf.shape == wf.shape and gd.shape == wd.shape
         assert torch.equal(gf, wf) and torch.equal(gd, wd), spec
         assert gf.data_ptr() % 256 == 0 and gd.data_ptr() % 256 == 0
+    # batches without a > 16-tap filter take the shared-memory-tiled kernel: same bits
+    small = [(e, w_) for e, w_ in zip(entries, want) if e[2].kh * e[2].kw_ <= 16]
+    for (spec_extra) in ((3, 64, 4), (6, 128, 3), (100, 20, 2), (8, 1, 4)):  # ragged channel counts on the tiled path
+        ci, co, k = spec_extra
+        w = torch.randn(co, ci, k, k, generator=g).cuda()
+        sp = ops.ConvSpec(ci, co, k, 1, 0, "zeros")
+        small.append(((w, None, sp), ops.pack_weight(w, sp)))
+    got = ops.pack_weight_multi([e for e, _ in small])
+    torch.cuda.synchronize()
+    for (gf, gd), (e, (wf, wd)) in zip(got, small):
+        assert torch.equal(gf, wf) and torch.equal(gd, wd), e[2]
 
 
 @pytest.mark.parametrize("n,ho,w,kh", [(4, 40, 256, 7), (2, 20, 128, 7), (3, 9, 256, 3), (1, 150, 128, 7), (33, 7, 128, 7)])

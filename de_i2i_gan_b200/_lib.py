@@ -45,6 +45,7 @@ SIGNATURES = {
     "dei2i_reflect_border": (_I, [_P, _I, _I, _I, _I, _I, _P]),
     "dei2i_conv2d_dgrad": (_I, [_P, _P, _P, C.POINTER(ConvGeom), _P, _I, _P]),
     "dei2i_reflect_fold": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
+    "dei2i_reflect_fold_inplace": (_I, [_P, _I, _I, _I, _I, _I, _P]),
     "dei2i_reflect_pad": (_I, [_P, _P, _I, _I, _I, _I, _I, _P]),
     "dei2i_pack_weight_multi": (_I, [C.POINTER(PackItem), _I, _P]),
     "dei2i_conv2d_wgrad_workspace": (_SZ, [C.POINTER(ConvGeom), _I]),

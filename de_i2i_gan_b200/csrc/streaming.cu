@@ -902,8 +902,10 @@ __global__ void bn_fwd_pad_kernel(const uint4* __restrict__ x, uint4* __restrict
 __global__ void __launch_bounds__(256, 2)
 bn_bwd_reduce_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, const float* __restrict__ gamma,
                      const float* __restrict__ beta, const float* __restrict__ mean, const float* __restrict__ rstd,
-                     long long npix, int H, int W, int C8, int chunk, int act, int pad, float* __restrict__ part) {
+                     long long npix, int H, int W, int C8, int chunk, int act, int pad_arg, float* __restrict__ part) {
   extern __shared__ float sh[];  // [lanes][2][C]
+  const int pad = pad_arg < 0 ? -pad_arg : pad_arg;  // < 0: padded layout whose border was folded in place already (no mirror reads)
+  const bool fold = pad_arg > 0;
   const int c8 = threadIdx.x % C8;
   const int lane = threadIdx.x / C8;
   const int lanes = blockDim.x / C8;
@@ -950,7 +952,7 @@ bn_bwd_reduce_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, 
       float fx[8], fd[8];
       unpack8(vx[j], fx);
       unpack8(vd[j], fd);
-      if (pad > 0) fold_extras(dy, (long long)nn[j] * img_pix, hh[j], ww[j], H, W, pad, C8, c8, fd);
+      if (fold) fold_extras(dy, (long long)nn[j] * img_pix, hh[j], ww[j], H, W, pad, C8, c8, fd);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         float dz = fd[k];
@@ -983,7 +985,9 @@ __global__ void __launch_bounds__(256, 2)
 bn_bwd_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, uint4* __restrict__ dx,
                     const float* __restrict__ gamma, const float* __restrict__ beta, const float* __restrict__ mean,
                     const float* __restrict__ rstd, const float* __restrict__ red /*[2,C]*/, long long npix, int H, int W,
-                    int C8, int training, int act, int pad) {
+                    int C8, int training, int act, int pad_arg) {
+  const int pad = pad_arg < 0 ? -pad_arg : pad_arg;  // < 0: padded layout, border folded in place already
+  const bool fold = pad_arg > 0;
   const int c8 = threadIdx.x % C8;
   const int lane = threadIdx.x / C8;
   const int lanes = blockDim.x / C8;
@@ -1031,7 +1035,7 @@ bn_bwd_apply_kernel(const uint4* __restrict__ x, const uint4* __restrict__ dy, u
       float fx[8], fd[8];
       unpack8(vx[j], fx);
       unpack8(vd[j], fd);
-      if (pad > 0) fold_extras(dy, (long long)nn[j] * img_pix, hh[j], ww[j], H, W, pad, C8, c8, fd);
+      if (fold) fold_extras(dy, (long long)nn[j] * img_pix, hh[j], ww[j], H, W, pad, C8, c8, fd);
 #pragma unroll
       for (int k = 0; k < 8; ++k) {
         float dz = fd[k];
@@ -2080,6 +2084,30 @@ extern "C" int dei2i_pack_weight_multi(const dei2i_pack_item* items, int count, 
   return 0;
 }
 
+// In-place variant: the mirror images are added into the INTERIOR positions of the padded tensor itself (the frame is left as it
+// is).  Sources always have a coordinate in the frame, destinations never do, so there is no read-after-write hazard.  Only pixels
+// with a mirror image are touched (the rows 1 .. pad and H-1-pad .. H-2 entirely, of the others 2 * pad columns): ~3 % of a 256^2 map.
+__global__ void reflect_fold_inplace_kernel(uint4* __restrict__ t, int H, int W, int C8, int pad) {
+  const int n = blockIdx.x / H, h = blockIdx.x - n * H;
+  const int c8 = threadIdx.x % C8, lane = threadIdx.x / C8, lanes = blockDim.x / C8;
+  const int Wp = W + 2 * pad;
+  const long long img = (long long)n * (H + 2 * pad) * Wp;
+  const bool row_mirrored = (h >= 1 && h <= pad) || (h <= H - 2 && h >= H - 1 - pad);
+  const int ncols = row_mirrored ? W : 2 * pad;  // pad < (W - 1) / 2: the two column bands are disjoint
+  for (int i = lane; i < ncols; i += lanes) {
+    const int w = row_mirrored ? i : (i < pad ? 1 + i : W - 1 - pad + (i - pad));
+    float f[8];
+    load_folded(t, img, h, w, H, W, pad, C8, c8, f);
+    t[(img + (long long)(h + pad) * Wp + (w + pad)) * C8 + c8] = pack8(f);
+  }
+}
+extern "C" int dei2i_reflect_fold_inplace(void* dxp, int N, int H, int W, int C, int pad, dei2i_stream stream) {
+  DEI2I_REQUIRE(dxp && C % 8 == 0 && C <= 2048 && pad >= 1 && 2 * pad + 1 < H && 2 * pad + 1 < W, "reflect_fold_inplace: bad arguments");
+  const int C8 = C / 8, lanes = 256 / C8 > 0 ? 256 / C8 : 1;
+  reflect_fold_inplace_kernel<<<(unsigned)(N * H), lanes * C8, 0, ST>>>((uint4*)dxp, H, W, C8, pad);
+  return LAUNCH_OK("reflect_fold_inplace_kernel");
+}
+
 extern "C" int dei2i_reflect_fold(const void* dxp, void* dx, int N, int H, int W, int C, int pad, dei2i_stream stream) {
   DEI2I_REQUIRE(dxp && dx && C % 8 == 0 && pad >= 0 && pad < H && pad < W, "reflect_fold: bad arguments");
   const int C8 = C / 8, lanes = 256 / C8 > 0 ? 256 / C8 : 1;
@@ -2331,7 +2359,7 @@ extern "C" int dei2i_bn_bwd(const void* x, const void* dy, void* dx, const float
                             int W, int C, int training, int act, int dy_pad, dei2i_stream stream) {
   DEI2I_REQUIRE(x && dy && dx && gamma && beta && save_mean && save_rstd && dgamma && dbeta && scratch && C % 8 == 0 && C <= 2048,
                 "bn_bwd: bad arguments");
-  DEI2I_REQUIRE(dy_pad >= 0 && 2 * dy_pad + 1 < H && 2 * dy_pad + 1 < W, "bn_bwd: dy_pad (%d) too large", dy_pad);
+  DEI2I_REQUIRE(2 * abs(dy_pad) + 1 < H && 2 * abs(dy_pad) + 1 < W, "bn_bwd: dy_pad (%d) too large", dy_pad);
   DEI2I_REQUIRE(dgamma == dbeta + C, "bn_bwd: dbeta | dgamma must be one [2, C] buffer (dbeta first)");
   const long long npix = (long long)N * H * W;
   int threads, chunk;

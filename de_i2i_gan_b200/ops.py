@@ -595,18 +595,23 @@ def bn_fwd(x, gamma, beta, running_mean, running_var, training, act=None, residu
     return y, save
 
 
-def bn_bwd(x, dy, gamma, beta, save, training, act=None, dy_pad=0):
-    """-> (dx, dgamma, dbeta).  dy_pad > 0: dy is the gradient of the padded forward output, folded while it is read."""
+def bn_bwd(x, dy, gamma, beta, save, training, act=None, dy_pad=0, fold_in_place=False):
+    """-> (dx, dgamma, dbeta).  dy_pad > 0: dy is the gradient of the padded forward output, folded while it is read - or, with
+    fold_in_place, its border is first folded into its own interior (dei2i_reflect_fold_inplace: 3 % of the pixels; dy is MODIFIED)
+    and the kernels then read the interior through the padded pitch."""
     _chk_act(x, "x")
     _chk_act(dy, "dy")
     n, h, w, c = x.shape
     assert tuple(dy.shape) == (n, h + 2 * dy_pad, w + 2 * dy_pad, c), (dy.shape, x.shape, dy_pad)
     lib = _lib.load()
+    if dy_pad and fold_in_place and not is_f32(x):
+        check(lib.dei2i_reflect_fold_inplace(_p(dy), n, h, w, c, int(dy_pad), _stream()), "dei2i_reflect_fold_inplace")
+        dy_pad = -int(dy_pad)
     dx = torch.empty_like(x)
     dbg = torch.empty(2, c, dtype=torch.float32, device=x.device)  # [dbeta | dgamma]
     if is_f32(x):
         if dy_pad:
-            dy = reflect_fold(dy, dy_pad)
+            dy = reflect_fold(dy, abs(dy_pad))
         check(lib.dei2i_bn_bwd_f32(_p(x), _p(dy), _p(dx), _p(gamma), _p(beta), _p(save[0]), _p(save[1]), _p(dbg), n, h * w, c,
                                    int(training), ACT[act], _stream()), "dei2i_bn_bwd_f32")
         return dx, dbg[1], dbg[0]

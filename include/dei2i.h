@@ -110,6 +110,10 @@ int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx, const dei2
                        int out_fp32, dei2i_stream stream);
 /* dx[n,h,w,c] = sum of dxp over all padded positions that reflect onto (h,w); bf16 in / bf16 out */
 int dei2i_reflect_fold(const void* dxp, void* dx, int N, int H, int W, int C, int pad, dei2i_stream stream);
+/* The same fold done in place: mirror images are added into the interior positions of the padded tensor itself, the frame keeps its
+ * values (only the ~3 % of the pixels that have a mirror image are touched).  The interior of dxp is then the folded gradient, read
+ * with the padded pitch by consumers that accept it (dei2i_bn_bwd with dy_pad < 0). */
+int dei2i_reflect_fold_inplace(void* dxp, int N, int H, int W, int C, int pad, dei2i_stream stream);
 
 /* F.pad(x, (pad,)*4, mode='reflect') (what nn.Conv2d(padding_mode='reflect') does before its convolution,
  * architecture.py:95-100): x bf16 [N,H,W,C] -> xp bf16 [N,H+2p,W+2p,C].  The TMA-fed convolution kernels take zero / no
@@ -224,7 +228,8 @@ int dei2i_bn_fwd_pad(const void* x, void* y, const void* residual, const float* 
                      int training, float momentum, float eps, int act, int out_pad, dei2i_stream stream);
 /* backward of the above: dx, dbeta | dgamma (fp32 [2, C] as ONE buffer, dbeta first; dgamma = dbeta + C).  The activation mask is
  * recomputed from x (the forward output is not needed).  dy_pad > 0: dy is the gradient of the PADDED output of dei2i_bn_fwd_pad
- * ([N, H+2p, W+2p, C]) and is folded while it is read (no dei2i_reflect_fold pass).  Deterministic: per-block partial sums in
+ * ([N, H+2p, W+2p, C]) and is folded while it is read (no dei2i_reflect_fold pass); dy_pad < 0: the same padded layout with
+ * p = -dy_pad whose border was already folded IN PLACE by dei2i_reflect_fold_inplace (interior read only).  Deterministic: per-block partial sums in
  * `scratch` (>= dei2i_bn_bwd_scratch(N, H*W, C) floats) finished in a fixed order. */
 size_t dei2i_bn_bwd_scratch(int N, int HW, int C);
 int dei2i_bn_bwd(const void* x, const void* dy, void* dx, const float* gamma, const float* beta, const float* save_mean,

@@ -440,6 +440,21 @@ def test_batchnorm_bwd_fused_fold_and_repeatable():
     for u, v in zip(a, b):
         assert torch.equal(u, v)
     assert rel_err(a[0].float(), ref[0].float()) < 1e-2 and rel_err(a[1], ref[1]) < 5e-3 and rel_err(a[2], ref[2]) < 5e-3
+    # border folded in place (dei2i_reflect_fold_inplace), interior read through the padded pitch: the folded values are the ones
+    # reflect_fold produces (same additions, rounded to BF16 once), so this matches the dense path bit for bit; pad = 2 as well
+    for pad in (1, 2):
+        dyp = to_dev(q(torch.randn(n, c, h + 2 * pad, w + 2 * pad, generator=g)))
+        ref = ops.bn_bwd(x, ops.reflect_fold(dyp, pad), gamma, beta, save, True, act="leaky_relu")
+        frame = dyp.clone()
+        got = ops.bn_bwd(x, dyp, gamma, beta, save, True, act="leaky_relu", dy_pad=pad, fold_in_place=True)
+        torch.cuda.synchronize()
+        for u, v in zip(got, ref):
+            assert torch.equal(u, v), pad
+        inner = (slice(None), slice(pad, pad + h), slice(pad, pad + w))
+        assert torch.equal(dyp[inner], ops.reflect_fold(frame, pad))  # the interior now holds the folded gradient ...
+        mask = torch.ones_like(dyp, dtype=torch.bool)
+        mask[inner] = False
+        assert torch.equal(dyp[mask], frame[mask])                    # ... and the frame is untouched
 
 
 @pytest.mark.parametrize("up", [1, 2])

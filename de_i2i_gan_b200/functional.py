@@ -529,8 +529,8 @@ class _BatchNorm(Function):
         x, gamma, beta, save = ctx.saved_tensors
         dy = dy.contiguous()
         pad = ctx.out_pad
-        # dei2i_bn_bwd can fold the padded gradient while reading it, but measured slower than fold + dense backward (592 vs 373 us
-        # on the 256 x 256 x 64 layer): the separate pass stays the default.  The residual branch needs the folded tensor anyway.
+        # see BN_FUSED_FOLD: folding while reading measured slower than fold + dense backward (592 vs 373 us on the 256 x 256 x 64 layer);
+        # the in-place border fold is the default.  The residual branch needs the folded dense tensor anyway.
         if pad and (ctx.has_res or not BN_FUSED_FOLD):
             dy, pad = ops.reflect_fold(dy, pad), 0
         # the consumer's gradient covers the padded frame: bn_bwd folds the mirrored border back while reading it

@@ -32,7 +32,7 @@ int g_tune_wgrad_bn = 0;
 int g_tune_wgrad_waves = 0;
 int g_tune_tma_ms = 0;
 int g_tune_mma_issue = -1;   // conv_tma_kernel MMA issue loop: -1 = auto by N tile, 1 = warp-uniform with an elected lane, 0 = single thread
-int g_tune_tma_pair = 2;     // CTA pairs (tcgen05 cta_group::2), conv_tma.cu: 0 = never, 1 = N = 256 tiles, 2 = also large N = 128 layers
+int g_tune_tma_pair = 3;     // CTA pairs (tcgen05 cta_group::2), conv_tma.cu: 0 = never, 1 = N = 256 tiles, 2 = also large N = 128 layers, 3 = and N = 64
 int g_tune_wgrad_pair = 0;   // 1 = weight gradients with >= 256 output channels on CTA pairs (cta_group::2), conv_tma.cu; measured: no gain (off)
 int g_tune_wgrad_ring = 1;   // 1 = kh x 1 weight gradients on the row-ring kernel where applicable (conv_tma.cu)
 int g_tune_conv_ring = 1;    // 1 = kh x 1 convolutions on the row-ring kernel where applicable (conv_tma.cu)

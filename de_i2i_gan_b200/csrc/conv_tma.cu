@@ -771,6 +771,12 @@ int run_conv_tma(const void* x, int N, int H, int W, int C, const void* wmat, in
     p.m_tiles = (int)((p.M + 255) / 256);
     return launch_tma_pair<128, 5, 2>(ta, tb2, p, st);
   }
+  if (g_tune_tma_pair >= 3 && bn == 64 && rows % 64 == 0 && p.npar <= 1 && (p.M + 255) / 256 * p.n_tiles >= 4ll * num_sms()) {
+    CUtensorMap tb2;  // N = 64 tiles on pairs: 32 of the 64 weight rows per CTA
+    if (int rc = encode_tmap_2d_bf16(&tb2, wmat, (uint64_t)K, (uint64_t)rows, (uint64_t)K * 2, 64, 32, 1)) return rc;
+    p.m_tiles = (int)((p.M + 255) / 256);
+    return launch_tma_pair<64, 5, 2>(ta, tb2, p, st);
+  }
   // narrow N: two 128-pixel A tiles share each B tile (halves the weight traffic per FLOP through L2 / shared memory) as long
   // as that still leaves every SM a couple of work tiles
   const long long mt2 = (p.M + 255) / 256;

@@ -378,7 +378,7 @@ def _nchw(y_nhwc, c):
 # reflect padding already ('valid' convolutions), exactly as the networks run them.
 C2_GEOMETRIES = {
     "res_256_256_3x3_in66": (32, 256, 66, 66, 256, 3, 3, 1, "conv_tma_pair<256,6,1>", "conv_tma_pair<256,6,1>", "wgrad_tma<2,3>"),
-    "dec1_128_64_3x3_in258": (32, 128, 258, 258, 64, 3, 3, 1, "conv_tma<64,5,2>", "conv_tma_pair<128,5,2>", "wgrad_tma<1,4>"),
+    "dec1_128_64_3x3_in258": (32, 128, 258, 258, 64, 3, 3, 1, "conv_tma_pair<64,5,2>", "conv_tma_pair<128,5,2>", "wgrad_tma<1,4>"),
     "dec0_256_128_3x3_in130": (32, 256, 130, 130, 128, 3, 3, 1, "conv_tma_pair<128,5,2>", "conv_tma_pair<256,6,1>", "wgrad_tma<1,4>"),
     "enc0_64_128_4x4s2_in258": (32, 64, 258, 258, 128, 4, 4, 2, "conv_tma_pair<128,5,2>", "conv_tma<64", "wgrad_tma<1,4>"),
     "enc1_128_256_4x4s2_in130": (32, 128, 130, 130, 256, 4, 4, 2, "conv_tma_pair<256,6,1>", "conv_tma<128", "wgrad_tma<2,3>"),

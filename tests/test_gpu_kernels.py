@@ -962,7 +962,7 @@ def test_conv_pair_kernel_matches_torch_and_single_cta(n, cin, h, cout, k, s):
             dx = ops.conv2d_dgrad(to_dev(dy), w_dg, spec, (h, h)) if cin % 256 == 0 and s == 1 else None
             k_d = ops.last_kernel()
         finally:
-            ops.set_tuning("tma_pair", 2)
+            ops.set_tuning("tma_pair", 3)
         torch.cuda.synchronize()
         assert ("pair" in k_f) == bool(pair), k_f
         outs[pair] = (from_dev(y, cout), from_dev(dx, cin) if dx is not None else None)

@@ -31,7 +31,7 @@ def main():
     print("cuobjdump -sass de_i2i_gan_b200/libdei2i.so (sm_100a): instruction counts per kernel")
     print("UTCHMMA = tcgen05.mma (kind::f16 / tf32), UTMALDG = TMA load (tiled / im2col), UTMASTG = TMA store, UTCBAR = tcgen05.commit,")
     print("LDTM = tcgen05.ld, UTCATOMSWS = tcgen05.alloc / dealloc, SYNCS = mbarrier, UCGABAR = barrier.cluster, ELECT = elect.sync,")
-    print("LDGSTS = cp.async (gather kernels), HMMA = mma.sync (none expected on the product path), R2UR = register -> uniform register moves\n")
+    print("LDGSTS = cp.async (gather kernels), HMMA = mma.sync (only the 8 / 16-channel skinny kernels: < 1 % of the FLOPs, HBM- or latency-bound, DESIGN.md section 4), R2UR = register -> uniform register moves\n")
     for (k, c), n in zip(cnt.items(), names):
         n = re.sub(r'\((?:CUtensorMap|dei2i|float|__nv|void|int|unsigned|long|char|bool).*', '', n).replace('void ', '').replace('dei2i::', '')
         tags = ' '.join(f'{q}={c[q]}' for q in KEYS if c[q])

@@ -328,7 +328,7 @@ def setup_wgan(args, cfg, dev, rank):
     from de_i2i_gan_b200 import options
     from de_i2i_gan_b200.trainers.wgan_trainer import WGanTrainer
     B, H = cfg["batch"], cfg["image_size"]
-    opt = options.wgan_options(image_size=H, batch_size=B, ckpt_dir=Path("/tmp/dei2i_wgan_bench"), num_display_images=4)
+    opt = options.wgan_options(image_size=H, batch_size=B, ckpt_dir=Path("/tmp/dei2i_wgan_bench"), num_display_images=4, init_type="normal")
     opt.device = dev
     torch.manual_seed(123)
     tr = WGanTrainer(opt)

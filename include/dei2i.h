@@ -92,15 +92,19 @@ typedef struct dei2i_pack_item {
 } dei2i_pack_item;
 int dei2i_pack_weight_multi(const dei2i_pack_item* items, int count, dei2i_stream stream);
 
-/* y = act(scale*conv(x) + bias + noise_weight*noise) + residual    (nn.Conv2d forward + fused followers) */
+/* y = act(scale*conv(x) + bias + noise_weight*noise) + residual: the nn.Conv2d forward of ConvBlock / DeConvBlock / NormConvBlock /
+ * NormResBlock / SPADE (architecture.py:51-56,95-107,228-244,320-350; normalization.py:17-22,30-32) with the followers the modules apply
+ * right after it (spectral-norm 1/sigma :109-112, NoiseInjection :385-389, activation :106-107, residual add :350) */
 int dei2i_conv2d_fwd(const void* x, const void* w_fwd, void* y, const dei2i_conv_geom* g,
                      const dei2i_conv_epilogue* e, dei2i_stream stream);
 /* which forward kernel family dei2i_conv2d_fwd picks for g: 1 = TMA-im2col tcgen05 (supports stats_partial / out_pad), 0 = other */
 int dei2i_conv2d_fwd_path(const dei2i_conv_geom* g);
-/* mirrors the frame of an [N, H+2p, W+2p, C] bf16 tensor whose interior is written (F.pad(mode='reflect') in place) */
+/* mirrors the frame of an [N, H+2p, W+2p, C] bf16 tensor whose interior is written (F.pad(mode='reflect') in place: the padding
+ * nn.Conv2d(padding_mode='reflect') applies to its input, architecture.py:95-100) */
 int dei2i_reflect_border(void* y, int N, int H, int W, int C, int pad, dei2i_stream stream);
 
-/* Gradient w.r.t. the convolution input (autograd of nn.Conv2d: conv_transpose of dy with W).
+/* Gradient w.r.t. the convolution input (autograd of the nn.Conv2d calls listed at dei2i_conv2d_fwd, reached from loss.backward(),
+ * trainers/defectgan_trainer.py:160,177: conv_transpose of dy with W).
  * dy: bf16 [N,Ho,Wo,Cout_ld].  pad_mode zeros:   dx is [N,H,W,Cin].
  *                              pad_mode reflect: dx is over the PADDED domain [N,H+2p,W+2p,Cin]; fold it with
  *                              dei2i_reflect_fold (the backward of F.pad(mode='reflect')).
@@ -108,7 +112,8 @@ int dei2i_reflect_border(void* y, int N, int H, int W, int C, int pad, dei2i_str
  * Resized inputs (Hs != H) are not supported here. */
 int dei2i_conv2d_dgrad(const void* dy, const void* w_dgrad, void* dx, const dei2i_conv_geom* g, const float* scale,
                        int out_fp32, dei2i_stream stream);
-/* dx[n,h,w,c] = sum of dxp over all padded positions that reflect onto (h,w); bf16 in / bf16 out */
+/* dx[n,h,w,c] = sum of dxp over all padded positions that reflect onto (h,w); bf16 in / bf16 out: autograd of the reflect padding in
+ * front of every padding_mode='reflect' convolution (architecture.py:95-100) */
 int dei2i_reflect_fold(const void* dxp, void* dx, int N, int H, int W, int C, int pad, dei2i_stream stream);
 /* The same fold done in place: mirror images are added into the interior positions of the padded tensor itself, the frame keeps its
  * values (only the ~3 % of the pixels that have a mirror image are touched).  The interior of dxp is then the folded gradient, read
@@ -121,7 +126,8 @@ int dei2i_reflect_fold_inplace(void* dxp, int N, int H, int W, int C, int pad, d
  * pad = 0 convolution; its backward is dei2i_conv2d_dgrad over the padded domain followed by dei2i_reflect_fold. */
 int dei2i_reflect_pad(const void* x, void* xp, int N, int H, int W, int C, int pad, dei2i_stream stream);
 
-/* Gradient w.r.t. the weight (autograd of nn.Conv2d), split over pixels, deterministic two-pass reduction.
+/* Gradient w.r.t. the weight (autograd of the same nn.Conv2d calls; the spectral-norm term is the backward of
+ * torch.nn.utils.spectral_norm, architecture.py:68-71,109-112), split over pixels, deterministic two-pass reduction.
  *   dw  fp32 [Cout, Cin_real, kh, kw]; written (beta = 0) or accumulated (beta = 1).
  *   workspace: dei2i_conv2d_wgrad_workspace(g) bytes of device scratch.
  *   sn_u/sn_v/sn_w/sn_inv_sigma: when non-NULL apply the spectral-norm backward
@@ -184,7 +190,8 @@ int dei2i_gap_bwd(const float* dout, void* dx, int N, int HW, int C, dei2i_strea
 int dei2i_rowpack_fwd(const float* img, void* xp, int N, int C, int H, int W, int kw, int pad, dei2i_stream stream);
 int dei2i_rowpack_bwd(const void* dxp, float* dimg, int N, int C, int H, int W, int kw, int pad, dei2i_stream stream);
 
-/* NCHW fp32 <-> NHWC bf16 (channel pitch C_ld >= C, pad channels zero) at the model edge. */
+/* NCHW fp32 <-> NHWC bf16 (channel pitch C_ld >= C, pad channels zero) at the model edge: the images entering
+ * DefectGanModel.forward (defectgan_model.py:49-52) and the images / logits leaving the networks (generator.py:268-275, discriminator.py:92-98). */
 int dei2i_nchw_to_nhwc(const float* src, void* dst, int N, int C, int H, int W, int C_ld, dei2i_stream stream);
 int dei2i_nhwc_to_nchw(const void* src, float* dst, int N, int C, int H, int W, int C_ld, dei2i_stream stream);
 
@@ -285,7 +292,8 @@ int dei2i_act_fwd(const void* x, void* y, long long n, int act, dei2i_stream str
 /* out = sa * a + sb * b (b may be NULL) over n bf16 elements: residual merge (x + r) / sqrt(2), model.py:66-68,118-121. */
 int dei2i_axpby(const void* a, const void* b, void* out, long long n, float sa, float sb, dei2i_stream stream);
 
-/* act backward for fused conv epilogues: dx = dy * act'(y) computed from the saved OUTPUT y (bf16);
+/* act backward for fused conv epilogues (autograd of the LeakyReLU / ReLU / Tanh / Sigmoid that follow a convolution,
+ * architecture.py:106-107, generator.py:224-241, discriminator.py:60-75): dx = dy * act'(y) computed from the saved OUTPUT y (bf16);
  * bias_grad (fp32 [C], may be NULL) receives the sum over pixels of dx (per-block partials in `scratch`, >= DEI2I_REDUCE_BLOCKS * C
  * floats, finished in a fixed order).  pad > 0: y and dy are the consumer-PADDED tensors [N, H+2p, W+2p, C] written by
  * dei2i_conv2d_fwd with out_pad: y is read at the interior, dy folded on read; dx is dense [N, H, W, C]; M = N * H * W. */
